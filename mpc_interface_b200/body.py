@@ -1,0 +1,333 @@
+"""The Formulation: named dynamics, definitions, costs and constraints -> QP.
+
+Mirror of python/mpc_interface/body.py:14-348 with the same method names,
+argument meaning, return order ``(A, h, Q, q)`` (= qpsolvers ``G, h, P, q``)
+and error behaviour.  The bookkeeping (dict insertion orders, ``optim_ID`` /
+``given_ID`` ranges) is host code because it defines the bit-exact index
+layout; every matrix is produced on the GPU: the formulation is compiled into
+an affine plan (plan.py) and evaluated by the streaming kernels behind
+``mpci_assemble`` (include/mpci.h).  A single instance is a batch of one;
+``generate_all_qp_matrices_batched`` is the batched entry point.
+"""
+import numpy as np
+
+from . import tools as use
+from . import plan as _plan
+
+
+class _PreviewMatrices:
+    """``form.PM[var] -> (Mg, Mo)`` like the reference's dict (body.py:149-156),
+    downloaded lazily from the device-resident plan."""
+
+    def __init__(self, form):
+        self._form = form
+        self._cache = {}
+
+    def _polys(self):
+        return self._form._compiled().PM
+
+    def keys(self):
+        return self._polys().keys()
+
+    def __len__(self):
+        return len(self._polys())
+
+    def __iter__(self):
+        return iter(self._polys())
+
+    def __contains__(self, name):
+        return name in self._polys()
+
+    def __getitem__(self, name):
+        if name not in self._cache:
+            poly = self._polys()[name]
+            if set(poly.terms) - {()}:
+                raise ValueError(
+                    "'{}' depends on per-instance parameters; it has no single "
+                    "preview matrix".format(name)
+                )
+            ng = self._form.given_len
+            ops = self._form._ops()
+            dense = ops.download(poly.terms[()]) if () in poly.terms else np.zeros(
+                [poly.rows, poly.cols]
+            )
+            self._cache[name] = (dense[:, :ng].copy(), dense[:, ng:].copy())
+        return self._cache[name]
+
+    def items(self):
+        return ((k, self[k]) for k in self.keys())
+
+
+class Formulation:
+    def __init__(self, backend=None):
+        self.domain = {}
+        self.optim_variables = []
+        self.given_variables = []
+        self.optim_sizes = []
+        self.given_sizes = []
+        self.optim_len = 0
+        self.given_len = 0
+        self.optim_ID = {}
+        self.given_ID = {}
+        self.domain_ID = {"optim_ID": self.optim_ID, "given_ID": self.given_ID}
+
+        self.definitions = {}
+        self.dynamics = {}
+        self.of = {}
+        self.constraint_boxes = {}
+        self.constraints = {}
+        self.goals = {}
+        self.update_incorporations = use.do_not_update
+
+        self._backend = backend  # None -> the CUDA device backend (device.py)
+        self._plans = {}
+
+    # ------------------------------------------------------------------
+    # incorporations (body.py:38-94)
+    # ------------------------------------------------------------------
+    def _dirty(self):
+        self._plans = {}
+
+    def _require_defined(self, names, message):
+        for name in names:
+            assert name in self.definitions, message.format(name)
+
+    def incorporate_dynamics(self, name, new_dynamics):
+        self.domain.update(new_dynamics.domain)
+        self.dynamics[name] = new_dynamics
+        for variable in new_dynamics.all_variables:
+            self.of[variable] = name
+        self.definitions.update(new_dynamics.definitions)
+        self._dirty()
+
+    def incorporate_definition(self, name, new_definition):
+        self._require_defined(
+            new_definition.keys(),
+            "The definition must depend only on defined variables, but the "
+            "this definition depends on {}",
+        )
+        self.definitions[name] = new_definition
+        self._dirty()
+
+    def incorporate_definitions(self, dict_of_defs):
+        for name, combination in dict_of_defs.items():
+            self.incorporate_definition(name, combination)
+
+    def _require_limits_defined(self, limits):
+        for limit in limits:
+            self._require_defined(
+                [limit.variable + axis for axis in limit.axes],
+                "All constrained variables must be previously defined, "
+                "but '{}' was not defined.",
+            )
+
+    def incorporate_constraint(self, name, new_limits):
+        if not isinstance(new_limits, list):
+            new_limits = [new_limits]
+        self._require_limits_defined(new_limits)
+        self.constraints[name] = new_limits
+        self._dirty()
+
+    def incorporate_box(self, name, new_box):
+        self._require_limits_defined(new_box.constraints)
+        self.constraint_boxes[name] = new_box
+        self._dirty()
+
+    def incorporate_goal(self, name, new_goal):
+        self._require_defined(
+            [new_goal.variable + axis for axis in new_goal.axes],
+            "All constrained variables must be previously defined, "
+            "but '{}' was not defined.",
+        )
+        self.goals[name] = new_goal
+        self._dirty()
+
+    # ------------------------------------------------------------------
+    # index layout of the QP (body.py:97-136) -- integers, host side
+    # ------------------------------------------------------------------
+    def identify_qp_domain(self, optimization_domain):
+        self.optim_variables = optimization_domain
+        self.given_variables = [v for v in self.domain if v not in optimization_domain]
+        self.update_qp_sizes()
+        self.update_qp_IDs()
+
+    def update_qp_domain(self):
+        for behavior in self.dynamics.values():
+            if behavior.time_variant:
+                self.domain.update(behavior.domain)
+
+    def update_qp_sizes(self):
+        self.optim_sizes = [self.domain[v] for v in self.optim_variables]
+        self.given_sizes = [self.domain[v] for v in self.given_variables]
+        self.optim_len = sum(self.optim_sizes)
+        self.given_len = sum(self.given_sizes)
+
+    @staticmethod
+    def _consecutive_ranges(names, sizes):
+        out, start = {}, 0
+        for name, size in zip(names, sizes):
+            out[name] = range(start, start + size)
+            start += size
+        return out
+
+    def update_qp_IDs(self):
+        # only adds / overwrites keys, like body.py:135-136
+        self.optim_ID.update(self._consecutive_ranges(self.optim_variables, self.optim_sizes))
+        self.given_ID.update(self._consecutive_ranges(self.given_variables, self.given_sizes))
+        self._dirty()
+
+    def set_updating_rule(self, how_to_update=None):
+        self.update_incorporations = how_to_update
+
+    def update(self, **kargs):
+        self.update_incorporations(self, **kargs)
+        self.update_qp_domain()
+        self.update_qp_sizes()
+        self.update_qp_IDs()
+        self.make_preview_matrices()
+
+    # ------------------------------------------------------------------
+    # device plan
+    # ------------------------------------------------------------------
+    def _ops(self):
+        if self._backend is None:
+            from . import device
+
+            self._backend = device.DeviceBackend()
+        return self._backend
+
+    def _compiled(self, costs=None, limits=None):
+        key = self._signature(
+            list(self.goals.values()) if costs is None else costs,
+            _plan.ordered_limits(self) if limits is None else limits,
+        )
+        if key not in self._plans:
+            self._plans[key] = _plan.compile_plan(self, self._ops(), costs, limits)
+        return self._plans[key]
+
+    def make_preview_matrices(self):
+        """Rebuilds the preview matrices ``PM[var] = (Mg, Mo)`` with
+        ``var = Mg @ given + Mo @ optim`` (body.py:149-156) -- on the device,
+        as part of the plan -- after any change of the incorporated objects."""
+        self._dirty()
+        self.PM = _PreviewMatrices(self)
+        self._compiled()
+
+    def arrange_given(self, collector):
+        """Packs named (k, 1) arrays into the given column (body.py:195-207)."""
+        if not self.given_len:
+            return np.array([])
+        given = np.zeros([self.given_len, 1])
+        for variable, indices in self.given_ID.items():
+            given[indices] = collector[variable]
+        return given
+
+    # ------------------------------------------------------------------
+    # evaluation helpers
+    # ------------------------------------------------------------------
+    @staticmethod
+    def _signature(costs, limits):
+        def stamp(objs):
+            return tuple((id(o), getattr(o, "_stamp", 0)) for o in objs)
+
+        return (stamp(costs), stamp(limits))
+
+    def _run(self, given, params, costs=None, limits=None, out=None):
+        """Evaluates a (sub)plan for a batch: given [B, ng], params {name: [B]}."""
+        compiled = self._compiled(costs, limits)
+        if not hasattr(given, "device"):
+            given = np.asarray(given, dtype=np.float64)
+        batch = given.shape[0]
+        scalars = compiled.slots.evaluate(params or {}, batch)
+        return self._ops().assemble(compiled, scalars, given, batch, out)
+
+    def _single(self, given):
+        given = np.asarray(given, dtype=np.float64)
+        if given.size != self.given_len:
+            raise ValueError(
+                "matmul: the given vector has {} elements, the formulation expects "
+                "{}".format(given.size, self.given_len)
+            )
+        return given.reshape([1, self.given_len])
+
+    def preview(self, given, optim, variable, axes=None):
+        """Value of a variable along the horizon (body.py:209-219)."""
+        if axes is None:
+            Mg, Mo = self.PM[variable]
+            return Mg @ given + Mo @ optim
+        columns = []
+        for axis in axes:
+            Mg, Mo = self.PM[variable + axis]
+            columns.append(Mg @ given + Mo @ optim)
+        return np.hstack(columns)
+
+    def goal_distance(self, given, optim, goal_name):
+        """Squared distance to the aim of one goal (body.py:221-229)."""
+        goal = self.goals[goal_name]
+        value = 0
+        for i, axis in enumerate(goal.axes):
+            Mg, Mo = self.PM[goal.variable + axis]
+            gap = Mg @ given + Mo @ optim - goal.aim[:, i]
+            value += gap.T @ gap
+        return float(value)
+
+    def full_goal_distance(self, given, optim):
+        return sum(self.goal_distance(given, optim, name) for name in self.goals)
+
+    # ------------------------------------------------------------------
+    # QP matrices (body.py:236-348) -- one instance = a batch of one
+    # ------------------------------------------------------------------
+    def generate_qp_constraint(self, limit, given):
+        """Rows ``A z <= h`` of one limit (body.py:236-264)."""
+        out = self._run(self._single(given), None, costs=[], limits=[limit])
+        return out.G_numpy()[0], out.h_numpy()[0][:, None]
+
+    def generate_qp_cost(self, cost, given):
+        """``Q, q`` of one cost (body.py:266-302)."""
+        out = self._run(self._single(given), None, costs=[cost], limits=[])
+        return out.P_numpy()[0], out.q_numpy()[0][:, None]
+
+    def generate_all_qp_constraints(self, given):
+        """All limits stacked: constraints first, then boxes (body.py:304-320)."""
+        limits = _plan.ordered_limits(self)
+        if not limits:
+            raise ValueError("need at least one array to concatenate")
+        out = self._run(self._single(given), None, costs=[], limits=limits)
+        return out.G_numpy()[0], out.h_numpy()[0][:, None]
+
+    def generate_all_qp_costs(self, given):
+        """Sum over all goals (body.py:322-329)."""
+        out = self._run(self._single(given), None, costs=list(self.goals.values()), limits=[])
+        return out.P_numpy()[0], out.q_numpy()[0][:, None]
+
+    def generate_all_qp_matrices(self, given):
+        """Returns ``A, h, Q, q`` for ``A z <= h`` and ``0.5 z'Qz + q'z``
+        (body.py:333-348; the sign of q is the one the code and the example
+        use, see biped_mpc_loop.py:60)."""
+        if not _plan.ordered_limits(self):
+            raise ValueError("need at least one array to concatenate")
+        out = self._run(self._single(given), None)
+        return (
+            out.G_numpy()[0],
+            out.h_numpy()[0][:, None],
+            out.P_numpy()[0],
+            out.q_numpy()[0][:, None],
+        )
+
+    # ------------------------------------------------------------------
+    # batched entry point (new): device-resident outputs
+    # ------------------------------------------------------------------
+    def parameter_names(self):
+        """Names of the per-instance Param values the compiled plan needs."""
+        return self._compiled().slots.names()
+
+    def generate_all_qp_matrices_batched(self, given, params=None, out=None):
+        """Assembles a whole batch.
+
+        given  : [B, given_len] float64 (numpy, or a CUDA torch tensor)
+        params : {name: [B] array} for every ``Param`` used in the formulation
+        out    : optional ``QPBatch`` to overwrite (ring-buffer slot)
+
+        Returns a ``QPBatch`` with device tensors ``P [B,nv,nv]``, ``q [B,nv]``,
+        ``G [B,nc,nv]``, ``h [B,nc]`` (row-major, unpadded)."""
+        return self._run(given, params, out=out)

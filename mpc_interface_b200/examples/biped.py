@@ -1,0 +1,143 @@
+"""Biped walking MPC: LIP centre of mass driven by jerk + footsteps.
+
+The same problem as the reference's example
+(python/use_examples/simple_functional_example/biped_formulation.py:23-191
+with biped_configuration.py:11-52), written against this package.  ``omega``
+may be a float (one instance, as in the reference) or a ``Param`` so that the
+pendulum frequency differs between the instances of a batch; the velocity aims
+may be ``Param``s as well.
+"""
+from types import SimpleNamespace
+
+import numpy as np
+
+from .. import tools as now
+from ..body import Formulation
+from ..combinations import LineCombo
+from ..dynamics import ControlSystem, DomainVariable, ExtendedSystem
+from ..goal import Cost
+from ..restrictions import Box
+
+AXES = ["_x", "_y"]
+OPTIM = ["CoM_dddot_x", "Ds_x", "CoM_dddot_y", "Ds_y"]
+
+
+def default_configuration(horizon_lenght=None):
+    """Values of biped_configuration.py:11-52; ``horizon_lenght`` overrides
+    the default of num_steps * step_samples = 24."""
+    c = SimpleNamespace()
+    c.system = "J->CCC"
+    c.num_steps = 2
+    c.mpc_period = 0.1
+    c.ss_duration = round(11 * c.mpc_period, 5)
+    c.ds_duration = c.mpc_period
+    c.regular_step_duration = round(c.ss_duration + c.ds_duration, 5)
+    c.step_samples = int(round(c.regular_step_duration / c.mpc_period))
+    c.horizon_lenght = c.num_steps * c.step_samples if horizon_lenght is None else horizon_lenght
+    c.feet_sep = 0.08
+    c.foot_corner = np.array([0.1, 0.05])
+    c.stepping_corner = np.array([0.3, 0.1])
+    c.stepping_center = np.array([0, 2 * c.foot_corner[1] + c.stepping_corner[1] + c.feet_sep])
+    c.strt_y = c.feet_sep / 2 + c.foot_corner[1]
+    c.com_height = 0.877
+    c.gravity = [0, 0, -9.81]
+    c.omega = np.sqrt(-c.gravity[2] / c.com_height)
+    c.cop_safety_margin = 0.02
+    c.target_vel = np.array([0.6, 0, 0])
+    c.cost_weights = {
+        "minimize jerk": 0.001,
+        "track velocity": 0.01,
+        "relax ankles": 1,
+        "terminal": 0,
+    }
+    return c
+
+
+def formulate_biped(conf, omega=None, target_vel=None, backend=None):
+    """Builds the Formulation.  ``omega`` / ``target_vel`` default to the
+    configuration's numbers; pass ``Param``s to make them per-instance."""
+    w = conf.omega if omega is None else omega
+    vel = conf.target_vel if target_vel is None else target_vel
+    N = conf.horizon_lenght
+
+    # footsteps: s = 1*s0 + E*Ds with a 0/1 step-indicator matrix
+    steps = ExtendedSystem(
+        "Ds",
+        "s",
+        "s",
+        S=np.ones([N, 1]),
+        U=now.plan_steps(N, 0, regular_time=conf.step_samples),
+        axes=AXES,
+        how_to_update_matrices=now.update_step_matrices,
+        time_variant=True,
+    )
+    steps.define_output("stamps", {"s0": 1, "Ds": 1}, time_variant=True, how_to_update=now.adapt_size)
+
+    # centre of mass
+    lip = ControlSystem.from_name(conf.system, AXES, tau=conf.mpc_period, omega=conf.omega)
+    lip_ext = ExtendedSystem.from_cotrol_system(lip, "x", N)
+
+    # non-linearity bias, one sample per horizon step
+    bias = DomainVariable("n", N, AXES)
+
+    shift = np.diag(np.ones([N - 1]), 1)  # n enters one sample later
+    extra = {}
+    if conf.system == "J->CCC":
+        for ax in AXES:
+            extra["b" + ax] = LineCombo({"CoM" + ax: 1, "CoM_ddot" + ax: -1 / w**2})
+            extra["(b+n-s)" + ax] = LineCombo({"b" + ax: 1, "n" + ax: shift, "s" + ax: -1})
+            extra["(c-s)" + ax] = LineCombo({"CoM" + ax: 1, "s" + ax: -1})
+            extra["DCM" + ax] = LineCombo({"CoM" + ax: 1, "CoM_dot" + ax: 1 / w})
+            extra["(DCM-s)" + ax] = LineCombo({"DCM" + ax: 1, "s" + ax: -1})
+
+    foot = now.make_simetric_vertices(conf.foot_corner)
+    support_polygon = Box.task_space("(b+n-s)", foot, AXES)
+    stepping_area = Box.task_space(
+        "Ds",
+        now.make_simetric_vertices(conf.stepping_corner),
+        AXES,
+        how_to_update=now.update_stepping_area,
+        time_variant=True,
+    )
+    stepping_area.update(
+        step_count=0, n_next_steps=steps.domain["Ds_x"], xy_lenght=conf.stepping_center
+    )
+    last = range(N - 1, N)
+    terminal_constraint = Box.task_space("(DCM-s)", foot, AXES, schedule=last)
+    support_polygon.set_safety_margin(conf.cop_safety_margin)
+    terminal_constraint.set_safety_margin(conf.cop_safety_margin)
+
+    weights = conf.cost_weights
+    goals = {
+        "relax ankles x": Cost("(b+n-s)", weights["relax ankles"], aim=[0], axes=["_x"]),
+        "relax ankles y": Cost("(b+n-s)", weights["relax ankles"], aim=[0], axes=["_y"]),
+        "minimize jerk": Cost("CoM_dddot", weights["minimize jerk"], aim=[0, 0], axes=AXES),
+        "track vel_x": Cost("CoM_dot", weights["track velocity"], aim=vel[0], axes=["_x"]),
+        "track vel_y": Cost("CoM_dot", weights["track velocity"], aim=vel[1], axes=["_y"]),
+        "terminal_cost": Cost("(DCM-s)", weights["terminal"], aim=[0, 0], axes=AXES, schedule=last),
+    }
+
+    form = Formulation(backend=backend)
+    form.incorporate_dynamics("steps", steps)
+    form.incorporate_dynamics("LIP", lip_ext)
+    form.incorporate_dynamics("bias", bias)
+    form.incorporate_definitions(extra)
+    for name, goal in goals.items():
+        form.incorporate_goal(name, goal)
+    form.incorporate_box("stepping area", stepping_area)
+    form.incorporate_box("support_polygon", support_polygon)
+    form.incorporate_box("terminal_Constraint", terminal_constraint)
+    form.identify_qp_domain(list(OPTIM))
+    form.make_preview_matrices()
+
+    def tick(body, **kargs):
+        """Needs ``step_times`` and ``step_count`` (biped_formulation.py:156-187)."""
+        body.dynamics["steps"].update(step_times=kargs["step_times"], N=N)
+        body.constraint_boxes["stepping area"].update(
+            step_count=kargs["step_count"],
+            n_next_steps=body.dynamics["steps"].domain["Ds_x"],
+            xy_lenght=conf.stepping_center,
+        )
+
+    form.set_updating_rule(tick)
+    return form

@@ -1,0 +1,419 @@
+"""Compiler: Formulation -> affine assembly plan for the batched CUDA path.
+
+What varies between the instances of a batch is a vector of per-instance
+scalars ``s_b`` (Param expressions of LineCombo coefficients, cost weights and
+aims, params.py) and the given vector ``g_b``.  Every preview matrix of the
+reference (body.py:149-193) is then a polynomial in ``s_b`` whose coefficients
+are constant matrices, and so are the outputs of body.py:236-348:
+
+    P_b = sum_m  c_m(s_b) * DP_m                      (nv x nv)
+    G_b = sum_m  c_m(s_b) * DG_m                      (nc x nv)
+    [q_b; h_b] = sum_m c_m(s_b) * DY_m @ [g_b; 1]     (nv + nc)
+
+with monomials ``c_m(s) = prod_f s[idx_mf]``.  This module walks the
+formulation in the reference's order (definitions in insertion order, limits:
+constraints dict then boxes dict, costs in dict order), keeps the symbolic
+part (monomials, index layout, row offsets) on the host and sends every dense
+product / accumulation to ``ops`` -- the device backend (device.py: DMMA GEMM
+and 2-D axpy kernels of csrc/).  The result, an ``AffinePlan``, is what the
+streaming kernels of csrc/mpci_assemble.cu consume.
+
+No floating-point reduction happens in this file; numpy is used for
+placement of blocks into zero matrices (the scatter of body.py:158-177) and
+for structural scans (which tiles of DY are non-zero).
+"""
+import numbers
+
+import numpy as np
+
+from .params import Expr, is_expr
+
+MAX_FACTORS = 4  # factors per monomial the kernels accept (mpci.h: MPCI_MAX_FACTORS)
+MAX_TERMS = 8  # monomials per streamed array (mpci.h: MPCI_MAX_TERMS)
+QH_ROW_TILE = 128  # rows of [q; h] handled by one thread block (mpci.h)
+QH_K_TILE = 8  # granularity of the zero-skipping along [g; 1]
+
+
+class SlotTable:
+    """Distinct per-instance scalar expressions, in order of first use."""
+
+    def __init__(self):
+        self.exprs = []
+        self._index = {}
+
+    def slot(self, expr):
+        key = expr.key()
+        if key not in self._index:
+            self._index[key] = len(self.exprs)
+            self.exprs.append(expr)
+        return self._index[key]
+
+    def names(self):
+        out = []
+        for e in self.exprs:
+            for n in e.names():
+                if n not in out:
+                    out.append(n)
+        return out
+
+    def evaluate(self, values, batch):
+        """[batch, n_slots] float64 (at least one column so pointers stay valid)."""
+        out = np.ones([batch, max(1, len(self.exprs))])
+        for i, e in enumerate(self.exprs):
+            out[:, i] = e.evaluate(values)
+        return out
+
+
+def _mono(*parts):
+    """Merge slot tuples / None into one sorted monomial."""
+    slots = []
+    for p in parts:
+        if p is None:
+            continue
+        slots.extend(p if isinstance(p, tuple) else (p,))
+    return tuple(sorted(slots))
+
+
+class Poly:
+    """{monomial: matrix handle}; all matrices share one shape."""
+
+    def __init__(self, ops, rows, cols):
+        self.ops, self.rows, self.cols = ops, rows, cols
+        self.terms = {}
+
+    def acc(self, mono, src, alpha=1.0, rowscale=None):
+        """terms[mono] += alpha * rowscale * src  (rows of src / rowscale broadcast)."""
+        if mono not in self.terms:
+            self.terms[mono] = self.ops.zeros(self.rows, self.cols)
+        self.ops.axpy(self.terms[mono], src, float(alpha), rowscale)
+
+    def take_rows(self, index):
+        out = Poly(self.ops, len(index), self.cols)
+        for mono, H in self.terms.items():
+            out.terms[mono] = self.ops.rows(H, index)
+        return out
+
+    def left_multiply(self, matrix):
+        matrix = np.atleast_2d(np.asarray(matrix, dtype=np.float64))
+        out = Poly(self.ops, matrix.shape[0], self.cols)
+        M = self.ops.upload(matrix)
+        for mono, H in self.terms.items():
+            out.terms[mono] = self.ops.gemm(M, H)
+        return out
+
+
+def _scalar_kind(coef):
+    """('num', float) | ('expr', Expr) | ('mat', ndarray)"""
+    if is_expr(coef):
+        return "expr", coef
+    if isinstance(coef, numbers.Real):
+        return "num", float(coef)
+    arr = np.asarray(coef)
+    if arr.dtype == object:
+        raise TypeError("array coefficients holding Param expressions are not supported")
+    if arr.ndim == 0:
+        return "num", float(arr)
+    return "mat", arr.astype(np.float64)
+
+
+class AffinePlan:
+    """Host description + constant device arrays of one formulation structure."""
+
+    def __init__(self):
+        self.nv = self.ng = self.nc = 0
+        self.slots = None
+        self.monomials = []  # list of slot tuples (global table)
+        self.P_terms = []  # indices into monomials
+        self.G_terms = []
+        self.Y_terms = []
+        self.DP = self.DG = self.DY = None  # stacked constants [K, rows, cols]
+        self.row_offsets = []  # first row of every limit in G / h
+        self.limit_rows = []
+        self.qh_ranges = None  # int32 [n_ranges, 4]: (row tile, term, k0, k1)
+        self.qh_tile_ptr = None  # int32 [n_row_tiles + 1]
+        self.optim_ID = {}
+        self.given_ID = {}
+
+    def mono_table(self):
+        table = -np.ones([max(1, len(self.monomials)), MAX_FACTORS], dtype=np.int32)
+        for i, mono in enumerate(self.monomials):
+            table[i, : len(mono)] = mono
+        return table
+
+
+def _preview_polys(form, ops, slots):
+    """PM as polynomials: {variable: Poly of [rows x (ng + nv)]}  (body.py:149-193)."""
+    ng, nv = form.given_len, form.optim_len
+    width = ng + nv
+    PM = {}
+    for name, combo in form.definitions.items():
+        if name in form.of:  # body.py:158-177 -- scatter into zero matrices
+            rows = form.dynamics[form.of[name]].all_variables[name]
+            dense = np.zeros([rows, width])
+            for var, block in combo.items():
+                if is_expr(block):
+                    raise TypeError("dynamics blocks cannot be Param expressions")
+                if var in form.given_variables:
+                    ids = form.given_ID[var]
+                    dense[:, ids.start : ids.stop] = block
+                elif var in form.optim_variables:
+                    ids = form.optim_ID[var]
+                    dense[:, ng + ids.start : ng + ids.stop] = block
+                else:
+                    raise ValueError(
+                        "The variable {} in the definition of {} seems to not be "
+                        "given nor optimal.".format(var, name)
+                    )
+            poly = Poly(ops, rows, width)
+            poly.terms[()] = ops.upload(dense)
+        else:  # body.py:179-193 -- sum of coefficient * dependency
+            poly = None
+            for var, coef in combo.items():
+                kind, value = _scalar_kind(coef)
+                dep = PM[var]
+                if kind == "mat":
+                    term = dep.left_multiply(value)
+                    factor, alpha = None, 1.0
+                elif kind == "expr":
+                    term, factor, alpha = dep, slots.slot(value), 1.0
+                else:
+                    term, factor, alpha = dep, None, value
+                if poly is None:
+                    poly = Poly(ops, term.rows, width)
+                for mono, H in term.terms.items():
+                    poly.acc(_mono(mono, factor), H, alpha)
+        PM[name] = poly
+    return PM
+
+
+def ordered_limits(form):
+    """Row order of G/h: constraints dict, then boxes dict (body.py:306-318)."""
+    limits = [lim for area in form.constraints.values() for lim in area]
+    limits += [lim for box in form.constraint_boxes.values() for lim in box.constraints]
+    return limits
+
+
+def _limit_poly(form, ops, PM, limit):
+    """(Poly [c_rows x (ng+nv)], bound [c_rows x 1]) of one limit (body.py:236-264)."""
+    width = form.given_len + form.optim_len
+    rows = PM[limit.variable + limit.axes[0]].rows
+    nlines = limit.nlines
+    c_rows = rows if nlines is None else int(nlines)
+    schedule = range(rows) if not limit.schedule else limit.schedule
+    out = Poly(ops, c_rows, width)
+    multipliers = limit.matrices()
+    for a, axis in enumerate(limit.axes):
+        picked = PM[limit.variable + axis].take_rows(list(schedule))
+        c = np.asarray(multipliers[a], dtype=np.float64)
+        if limit.L:
+            term = picked.left_multiply(c)
+            for mono, H in term.terms.items():
+                out.acc(mono, H)
+        else:
+            k = c.shape[0]
+            if k != 1 and picked.rows != 1 and k != picked.rows:
+                raise ValueError(
+                    "operands could not be broadcast together with shapes "
+                    "({},1) ({},{})".format(k, picked.rows, width)
+                )
+            if max(k, picked.rows) not in (1, c_rows):
+                raise ValueError(
+                    "non-broadcastable output operand with shape ({},{})".format(c_rows, width)
+                )
+            for mono, H in picked.terms.items():
+                out.acc(mono, H, 1.0, rowscale=c[:, 0])
+    bound = np.asarray(limit.bound(), dtype=np.float64).reshape([-1, 1])
+    if bound.shape[0] not in (1, c_rows):
+        raise ValueError("the bound has {} rows for {} lines".format(bound.shape[0], c_rows))
+    return out, np.broadcast_to(bound, [c_rows, 1])
+
+
+def _aim_entry(aim, axis_index):
+    """The single aim value of one axis: ('num', x) or ('expr', e).
+    Multi-row aims do not work in the reference either (body.py:296-299
+    broadcasts (m,) against (rows,1)); they are refused here."""
+    column = aim[:, axis_index]
+    if column.shape[0] != 1:
+        raise ValueError(
+            "operands could not be broadcast together: an aim must have one row "
+            "per axis, got {}".format(column.shape[0])
+        )
+    value = column[0]
+    if is_expr(value):
+        return "expr", value
+    return "num", float(value)
+
+
+def _block_acc(poly, mono, view, src, alpha):
+    """poly.terms[mono][view] += alpha * src  (view = (r0, r1, c0, c1))."""
+    if mono not in poly.terms:
+        poly.terms[mono] = poly.ops.zeros(poly.rows, poly.cols)
+    dst = poly.ops.sub(poly.terms[mono], *view)
+    poly.ops.axpy(dst, src, float(alpha), None)
+
+
+def _cost_into(form, ops, PM, slots, cost, Pacc, Yacc):
+    """Adds one cost to the P and [q; h] accumulators (body.py:266-302)."""
+    ng, nv = form.given_len, form.optim_len
+    kind, w = _scalar_kind(cost.weight)
+    if kind == "mat":
+        raise TypeError("a cost weight must be a scalar")
+    w_slot, w_num = (slots.slot(w), 1.0) if kind == "expr" else (None, w)
+    if kind == "num" and w_num == 0.0:
+        return  # contributes exact zeros in the reference
+    rows = PM[cost.variable + cost.axes[0]].rows
+    schedule = list(range(rows) if not cost.schedule else cost.schedule)
+
+    for i, axis in enumerate(cost.axes):
+        V = PM[cost.variable + axis].take_rows(schedule)
+        if cost.L:
+            V = V.left_multiply(cost.L[i])
+        same = (not cost.crossed) or (
+            cost.cross == cost.variable and cost.cross_L is cost.L
+        )
+        if same:
+            C = V
+        else:
+            C = PM[cost.cross + axis].take_rows(schedule)
+            if cost.cross_L:
+                C = C.left_multiply(cost.cross_L[i])
+        if C.rows != V.rows:
+            raise ValueError(
+                "matmul: the cost variable has {} rows and its cross {}".format(V.rows, C.rows)
+            )
+        ones = ops.upload(np.ones([V.rows, 1]))
+        for m1, HV in V.terms.items():
+            Vo = ops.sub(HV, 0, V.rows, ng, ng + nv)
+            Vg = ops.sub(HV, 0, V.rows, 0, ng)
+            for m2, HC in C.terms.items():
+                mono = _mono(w_slot, m1, m2)
+                Co = ops.sub(HC, 0, C.rows, ng, ng + nv)
+                # Vo^T [Cg | Co]: the right block is the Hessian term (body.py:292),
+                # the left one multiplies given in the gradient (body.py:296)
+                T1 = ops.gemm(Vo, HC, transA=True)
+                _block_acc(Pacc, mono, (0, nv, 0, nv), ops.sub(T1, 0, nv, ng, ng + nv), w_num)
+                if ng:
+                    _block_acc(Yacc, mono, (0, nv, 0, ng), ops.sub(T1, 0, nv, 0, ng), w_num / 2)
+                    # Co^T Vg  (body.py:298)
+                    T2 = ops.gemm(Co, Vg, transA=True)
+                    _block_acc(Yacc, mono, (0, nv, 0, ng), T2, w_num / 2)
+        # aims: -(w/2) (Vo^T 1 caim + Co^T 1 aim)   (body.py:296-299)
+        for poly, aim in ((V, cost.cross_aim), (C, cost.aim)):
+            a_kind, a_val = _aim_entry(np.asarray(aim, dtype=object), i)
+            if a_kind == "num" and a_val == 0.0:
+                continue
+            a_slot, a_num = (slots.slot(a_val), 1.0) if a_kind == "expr" else (None, a_val)
+            for m, H in poly.terms.items():
+                colsum = ops.gemm(ops.sub(H, 0, poly.rows, ng, ng + nv), ones, transA=True)
+                _block_acc(
+                    Yacc, _mono(w_slot, m, a_slot), (0, nv, ng, ng + 1), colsum, -w_num * a_num / 2
+                )
+
+
+def _scan_qh_ranges(DY):
+    """Non-zero (row tile, term, k range) triples of the stacked DY constants.
+    Structural scan on the host (which tiles are worth multiplying)."""
+    K, rows, cols = DY.shape
+    n_tiles = (rows + QH_ROW_TILE - 1) // QH_ROW_TILE
+    ranges, ptr = [], [0]
+    for tile in range(n_tiles):
+        r0, r1 = tile * QH_ROW_TILE, min(rows, (tile + 1) * QH_ROW_TILE)
+        for term in range(K):
+            active = np.any(DY[term, r0:r1, :] != 0.0, axis=0)
+            k = 0
+            while k < cols:
+                if not active[k : k + QH_K_TILE].any():
+                    k += QH_K_TILE
+                    continue
+                k0 = k
+                while k < cols and active[k : k + QH_K_TILE].any():
+                    k += QH_K_TILE
+                ranges.append((tile, term, k0, min(k, cols)))
+        ptr.append(len(ranges))
+    table = np.array(ranges, dtype=np.int32).reshape([-1, 4])
+    return table, np.array(ptr, dtype=np.int32)
+
+
+def compile_plan(form, ops, costs=None, limits=None):
+    """Builds the AffinePlan of ``form`` with backend ``ops``.
+
+    ``costs`` / ``limits`` restrict the plan to some goals / limits (used by
+    ``generate_qp_cost`` / ``generate_qp_constraint``); default is everything,
+    in the reference's order."""
+    plan = AffinePlan()
+    slots = SlotTable()
+    ng, nv = form.given_len, form.optim_len
+    PM = _preview_polys(form, ops, slots)
+
+    limits = ordered_limits(form) if limits is None else list(limits)
+    costs = list(form.goals.values()) if costs is None else list(costs)
+
+    # ---- constraint rows -------------------------------------------------
+    pieces, bounds = [], []
+    for limit in limits:
+        poly, bound = _limit_poly(form, ops, PM, limit)
+        plan.row_offsets.append(sum(plan.limit_rows))
+        plan.limit_rows.append(poly.rows)
+        pieces.append(poly)
+        bounds.append(bound)
+    nc = sum(plan.limit_rows)
+
+    Gacc = Poly(ops, nc, nv)
+    Pacc = Poly(ops, nv, nv)
+    Yacc = Poly(ops, nv + nc, ng + 1)
+    if nc:
+        Yacc.terms[()] = ops.zeros(nv + nc, ng + 1)
+        col = np.vstack(bounds)
+        ops.axpy(ops.sub(Yacc.terms[()], nv, nv + nc, ng, ng + 1), ops.upload(col), 1.0, None)
+    for row0, poly in zip(plan.row_offsets, pieces):
+        for mono, H in poly.terms.items():
+            _block_acc(Gacc, mono, (row0, row0 + poly.rows, 0, nv),
+                       ops.sub(H, 0, poly.rows, ng, ng + nv), 1.0)
+            if ng:  # h = bound - Gg @ given  (body.py:262)
+                _block_acc(Yacc, mono, (nv + row0, nv + row0 + poly.rows, 0, ng),
+                           ops.sub(H, 0, poly.rows, 0, ng), -1.0)
+
+    # ---- costs -----------------------------------------------------------
+    for cost in costs:
+        _cost_into(form, ops, PM, slots, cost, Pacc, Yacc)
+    if not Pacc.terms:
+        Pacc.terms[()] = ops.zeros(nv, nv)
+    if not Gacc.terms:
+        Gacc.terms[()] = ops.zeros(nc, nv)
+    if not Yacc.terms:
+        Yacc.terms[()] = ops.zeros(nv + nc, ng + 1)
+
+    # ---- global monomial table and stacked constants ----------------------
+    table = {}
+
+    def index_of(mono):
+        if len(mono) > MAX_FACTORS:
+            raise NotImplementedError(
+                "a monomial of {} per-instance factors exceeds the kernel limit {}".format(
+                    len(mono), MAX_FACTORS
+                )
+            )
+        if mono not in table:
+            table[mono] = len(table)
+        return table[mono]
+
+    def finish(acc, what):
+        monos = sorted(acc.terms, key=lambda m: (len(m), m))
+        if len(monos) > MAX_TERMS and what != "Y":
+            raise NotImplementedError(
+                "{} needs {} monomials, the kernel limit is {}".format(what, len(monos), MAX_TERMS)
+            )
+        return [index_of(m) for m in monos], ops.stack([acc.terms[m] for m in monos])
+
+    plan.P_terms, plan.DP = finish(Pacc, "P")
+    plan.G_terms, plan.DG = finish(Gacc, "G")
+    plan.Y_terms, plan.DY = finish(Yacc, "Y")
+    plan.monomials = [m for m, _ in sorted(table.items(), key=lambda kv: kv[1])]
+    plan.qh_ranges, plan.qh_tile_ptr = _scan_qh_ranges(ops.download3(plan.DY))
+
+    plan.nv, plan.ng, plan.nc = nv, ng, nc
+    plan.slots = slots
+    plan.optim_ID = dict(form.optim_ID)
+    plan.given_ID = dict(form.given_ID)
+    plan.PM = PM
+    return plan

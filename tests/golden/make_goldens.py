@@ -1,0 +1,219 @@
+#!/usr/bin/env python3
+"""Generates the golden vectors under tests/golden/ from the UNMODIFIED
+reference (imported from /root/reference, build container only).
+
+    python tests/golden/make_goldens.py
+
+Inputs come from mpc_interface_b200.examples.synthetic (pure numpy RNG); every
+matrix in the .npz files is produced by the reference's own code:
+``formulate_biped`` + ``Formulation.generate_all_qp_matrices`` (body.py:333),
+``tools.extend_matrices`` (tools.py:14) and the pickle the reference's test
+suite pins (python/tests/LIP_matrices, test_dynamics.py:139-152).
+"""
+import os
+import pickle
+import sys
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REF = "/root/reference/python"
+sys.path.insert(0, ROOT)
+sys.path.insert(0, REF)
+sys.path.insert(0, REF + "/use_examples/simple_functional_example")
+sys.dont_write_bytecode = True
+
+import mpc_interface.body as ref_body  # noqa: E402
+import mpc_interface.combinations as ref_comb  # noqa: E402
+import mpc_interface.dynamics as ref_dyn  # noqa: E402
+import mpc_interface.goal as ref_goal  # noqa: E402
+import mpc_interface.restrictions as ref_res  # noqa: E402
+import mpc_interface.tools as ref_tools  # noqa: E402
+import biped_configuration  # noqa: E402
+from biped_formulation import formulate_biped  # noqa: E402
+
+from mpc_interface_b200.examples import synthetic  # noqa: E402
+from mpc_interface_b200.examples.generic import formulate_generic  # noqa: E402
+
+
+class RefAPI:
+    ControlSystem, ExtendedSystem = ref_dyn.ControlSystem, ref_dyn.ExtendedSystem
+    Formulation, LineCombo = ref_body.Formulation, ref_comb.LineCombo
+    Cost, Box, Constraint = ref_goal.Cost, ref_res.Box, ref_res.Constraint
+
+
+def save(name, **arrays):
+    path = os.path.join(HERE, name)
+    np.savez_compressed(path, **arrays)
+    print("{:28s} {:9.1f} kB".format(name, os.path.getsize(path) / 1e3))
+
+
+def layout(form):
+    """Integer layout as arrays: [start, stop] per variable, in dict order."""
+    out = {}
+    for kind in ("optim", "given"):
+        ids = getattr(form, kind + "_ID")
+        out[kind + "_names"] = np.array(list(ids.keys()))
+        out[kind + "_ranges"] = np.array([[r.start, r.stop] for r in ids.values()], dtype=np.int64)
+    return out
+
+
+def lip_pickle():
+    with open(REF + "/tests/LIP_matrices", "rb") as f:
+        data = pickle.load(f)
+    U, S = data["matrices"]
+    A = np.array([[1, 0.1, 0.1**2 / 2], [0, 1, 0.1], [0, 0, 1]])
+    LIP = ref_dyn.ControlSystem.from_name("J->CCC", tau=0.1, omega=3.3445)
+    save("lip_matrices.npz", U=U, S=S, A=np.array(LIP.A, dtype=float), B=np.array(LIP.B, dtype=float))
+    assert np.allclose(LIP.A, A)
+
+
+def extend_cases():
+    rng = np.random.default_rng(11)
+    out = {}
+    for tag, (n, m, N) in {"a": (3, 1, 9), "b": (8, 6, 20), "c": (12, 4, 50), "d": (1, 1, 5), "e": (6, 2, 33)}.items():
+        A = np.eye(n) + 0.1 * rng.normal(size=[n, n])
+        B = rng.normal(size=[n, m])
+        S, U = ref_tools.extend_matrices(N, A, B)
+        out.update({tag + "_A": A, tag + "_B": B, tag + "_S": S, tag + "_U": np.stack(U)})
+    save("extend_cases.npz", **out)
+
+
+def biped_conf(N):
+    conf = types.SimpleNamespace(
+        **{k: v for k, v in vars(biped_configuration).items() if not k.startswith("__")}
+    )
+    conf.horizon_lenght = N
+    return conf
+
+
+def set_omega(form, w):
+    """SURVEY Appendix C probe8: per-instance omega through the reference."""
+    for ax in ("_x", "_y"):
+        d = form.definitions["b" + ax]
+        d.matrices[d.variables.index("CoM_ddot" + ax)] = -1 / w**2
+        d = form.definitions["DCM" + ax]
+        d.matrices[d.variables.index("CoM_dot" + ax)] = 1 / w
+    form.make_preview_matrices()
+
+
+def biped_c1():
+    form = formulate_biped(biped_configuration)
+    collector = {v: np.zeros([s, 1]) for v, s in form.domain.items()}
+    collector["x0_y"][0] = biped_configuration.strt_y
+    collector["s0_y"][0] = biped_configuration.strt_y
+    given = form.arrange_given(collector)
+    A, h, Q, q = form.generate_all_qp_matrices(given)
+    PM_b = np.hstack(form.PM["(b+n-s)_x"])
+    save("biped_c1.npz", given=given, A=A, h=h, Q=Q, q=q, PM_bns_x=PM_b, **layout(form))
+
+
+def biped_batch(name, N, batch, seed, terminal_weight=None):
+    conf = biped_conf(N)
+    if terminal_weight is not None:
+        conf.cost_weights = dict(conf.cost_weights, terminal=terminal_weight)
+    form = formulate_biped(conf)
+    vals = synthetic.biped_inputs(seed, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    As, hs, Qs, qs = [], [], [], []
+    for b in range(batch):
+        set_omega(form, vals["omega"][b])
+        form.goals["track vel_x"].update(aim=vals["vel_x"][b])
+        form.goals["track vel_y"].update(aim=vals["vel_y"][b])
+        A, h, Q, q = form.generate_all_qp_matrices(given[b][:, None])
+        As.append(A), hs.append(h[:, 0]), Qs.append(Q), qs.append(q[:, 0])
+    save(
+        name,
+        seed=seed, N=N, terminal_weight=-1.0 if terminal_weight is None else terminal_weight,
+        given=given, omega=vals["omega"], vel_x=vals["vel_x"], vel_y=vals["vel_y"],
+        A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs), **layout(form),
+    )
+
+
+def biped_tick(N=24):
+    """Structure after Formulation.update (ragged sizes)."""
+    conf = biped_conf(N)
+    form = formulate_biped(conf)
+    n = conf.step_samples
+    out = {}
+    step_times = np.array([(i + 1) * n - 1 for i in range(form.domain["Ds_x"])])
+    step_count = 0
+    rng = np.random.default_rng(5)
+    for tick in range(14):
+        form.update(step_times=step_times, step_count=step_count)
+        if tick in (0, 11, 12, 13):
+            given = rng.normal(size=[form.given_len, 1]) * 0.05
+            A, h, Q, q = form.generate_all_qp_matrices(given)
+            out.update({"t%d_given" % tick: given, "t%d_A" % tick: A, "t%d_h" % tick: h,
+                        "t%d_Q" % tick: Q, "t%d_q" % tick: q,
+                        "t%d_step_times" % tick: step_times.copy(),
+                        "t%d_step_count" % tick: step_count})
+        step_times = step_times - 1
+        if step_times[0] == -1:
+            step_times = step_times + n
+            step_count += 1
+    save("biped_ticks.npz", **out)
+
+
+def test_body_case():
+    """The formulation of the reference's own test (python/tests/test_body.py:23-98):
+    L matrices, a crossed cost, x0 among the optimisation variables."""
+    LIP = ref_dyn.ControlSystem.from_name("J->CCC", tau=0.1, omega=3.5, axes=["_x", "_y"])
+    LIP_ext = ref_dyn.ExtendedSystem.from_cotrol_system(LIP, "x", 9)
+    E = ref_tools.plan_steps(9, 1, step_times=np.array([2, 5, 8]))[:, :, None]
+    steps = ref_dyn.ExtendedSystem(["Ds"], ["s"], "s", np.ones([9, 1, 1]), [E], ["_x", "_y"])
+    bias = ref_dyn.DomainVariable("n", 9, ["_x", "_y"])
+    body = ref_body.Formulation()
+    body.incorporate_dynamics("steps", steps)
+    body.incorporate_dynamics("LIP", LIP_ext)
+    body.incorporate_dynamics("n", bias)
+    body.incorporate_definitions({
+        "DCM_x": ref_comb.LineCombo({"CoM_x": 1, "CoM_dot_x": 1 / 3.5}),
+        "DCM_y": ref_comb.LineCombo({"CoM_y": 1, "CoM_dot_y": 1 / 3.5}),
+    })
+    body.incorporate_constraint("kinematics", ref_res.Constraint("CoM_x", 4))
+    body.incorporate_constraint(
+        "steppingArea", ref_res.Constraint("s", 10, arrow=[1, 1], axes=["_x", "_y"], L=np.eye(9)))
+    body.incorporate_goal("velocity", ref_goal.Cost("CoM_dot", aim=[1, 2], weight=10, axes=["_x", "_y"]))
+    body.incorporate_goal("stability", ref_goal.Cost("DCM_x", aim=2, weight=1))
+    body.incorporate_goal(
+        "terminal", ref_goal.Cost("CoM", aim=[50, 50], weight=100, axes=["_x", "_y"], schedule=range(8, 9)))
+    body.incorporate_goal("crossed", ref_goal.Cost("DCM_x", aim=2, weight=1, cross="s_y", cross_L=np.eye(9)))
+    vertices = np.array([[0, 1], [1, 0], [0, -1], [-1, 0]])
+    body.incorporate_box("kine", ref_res.Box.task_space("CoM", vertices, ["_x", "_y"]))
+    body.identify_qp_domain(["x0_x", "x0_y", "Ds_x", "Ds_y", "CoM_dddot_x", "CoM_dddot_y"])
+    body.make_preview_matrices()
+    given = np.random.default_rng(3).normal(size=[body.given_len, 1])
+    A, h, Q, q = body.generate_all_qp_matrices(given)
+    cQ, cq = body.generate_qp_cost(body.goals["crossed"], given)
+    A1, h1 = body.generate_qp_constraint(body.constraints["steppingArea"][0], given)
+    save("test_body.npz", given=given, A=A, h=h, Q=Q, q=q, cQ=cQ, cq=cq, A1=A1, h1=h1, **layout(body))
+
+
+def generic_case(name, seed, nx, nu, N, n_rows, batch):
+    A, B, Q, R = synthetic.generic_system(seed, nx, nu)
+    rows = np.random.default_rng(seed + 1).normal(size=[n_rows, nx])
+    vals = synthetic.generic_inputs(seed, batch, nx)
+    As, hs, Qs, qs = [], [], [], []
+    for b in range(batch):
+        form = formulate_generic(A, B, Q, R, N, rows, refs=list(vals["ref"][b]), api=RefAPI)
+        given = form.arrange_given({"x0": vals["x0"][b][:, None]})
+        Am, h, Qm, q = form.generate_all_qp_matrices(given)
+        As.append(Am), hs.append(h[:, 0]), Qs.append(Qm), qs.append(q[:, 0])
+    save(name, seed=seed, A_sys=A, B_sys=B, Q_w=Q, R_w=R, rows=rows, x0=vals["x0"], ref=vals["ref"],
+         A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs), N=N, **layout(form))
+
+
+if __name__ == "__main__":
+    lip_pickle()
+    extend_cases()
+    biped_c1()
+    biped_batch("biped_n24_batch.npz", 24, 6, 1001)
+    biped_batch("biped_n24_terminal.npz", 24, 3, 1006, terminal_weight=0.5)
+    biped_batch("biped_n100_batch.npz", 100, 2, 1002)
+    biped_tick()
+    test_body_case()
+    generic_case("generic_small.npz", 21, 4, 2, 10, 2, 3)
+    generic_case("generic_c4_shape.npz", 1004, 12, 4, 50, 4, 1)
