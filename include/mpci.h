@@ -1,0 +1,134 @@
+/* mpci.h -- C ABI of the B200 QP-assembly library (libmpci.so).
+ *
+ * Drop-in boundary for the matrix-generation path of Gepetto/mpc-interface.
+ * The reference has no FFI layer: its boundary is the Python object API
+ * (python/mpc_interface/body.py:333-348 `generate_all_qp_matrices`,
+ * python/mpc_interface/tools.py:14-33 `extend_matrices`) and one C++ free
+ * function, gecko::tools::extend_matrices (cpp/include/mpc-interface/tools.hh:24-25,
+ * cpp/src/tools.cc:83-144).  Every entry point below names the reference
+ * routine it replaces.  Plain pointers and sizes only; all matrices are
+ * row-major (C order) float64, exactly the layout of the reference's NumPy
+ * arrays.  "dev" pointers are CUDA device pointers, "host" pointers are host
+ * memory (pinned memory gives full PCIe speed).  `stream` is a cudaStream_t
+ * passed as void* (NULL = default stream); launches are asynchronous.
+ *
+ * Return value: 0 = ok, negative = invalid argument (see mpci_last_error()),
+ * positive = CUDA error code.  Nothing throws across this boundary.
+ */
+#ifndef MPCI_H
+#define MPCI_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPCI_VERSION 100
+#define MPCI_MAX_FACTORS 4   /* per-instance scalar factors of one monomial */
+#define MPCI_MAX_TERMS 8     /* monomials of one streamed array (P or G) */
+#define MPCI_QH_ROW_TILE 128 /* rows of [q; h] per thread block */
+
+int mpci_version(void);
+
+/* Thread-local description of the last error returned on this thread. */
+const char* mpci_last_error(void);
+
+/* Number of CUDA devices visible (0 without a driver / GPU). */
+int mpci_device_count(void);
+
+/* ---- K1: prediction matrices -------------------------------------------
+ * Replaces tools.extend_matrices (python/mpc_interface/tools.py:14-33) and
+ * gecko::tools::extend_matrices (cpp/src/tools.cc:83-144) for a batch of
+ * independent systems x+ = A x + B u.
+ *   A_dev [batch][n][n], B_dev [batch][n][m]
+ *   S_dev [batch][N][n][n]      S[k][c][i]    = (A^(k+1))[i][c]
+ *   U_dev [batch][m][N][N][n]   U[j][k][p][i] = (A^(k-p) B)[i][j], 0 for p > k
+ * (U[j] is the reference's list element j; the rank-4 order m,N,N,n is the one
+ * of the C++ tensor, cpp/src/tools.cc:139-143.)  S_dev or U_dev may be NULL.
+ */
+int mpci_extend_matrices(const double* A_dev, const double* B_dev, double* S_dev,
+                         double* U_dev, int batch, int n, int m, int N, void* stream);
+
+/* Compact form (what the assembly kernels consume):
+ *   Phi_dev [batch][N][n][n]  Phi[k][i][c] = (A^(k+1))[i][c]
+ *   Gam_dev [batch][N][n][m]  Gam[d][i][j] = (A^d B)[i][j]                    */
+int mpci_extend_compact(const double* A_dev, const double* B_dev, double* Phi_dev,
+                        double* Gam_dev, int batch, int n, int m, int N, void* stream);
+
+/* Host-pointer convenience: copies A, B in, runs K1, copies S, U out. */
+int mpci_extend_matrices_host(const double* A_host, const double* B_host, double* S_host,
+                              double* U_host, int batch, int n, int m, int N);
+
+/* ---- dense building blocks used while a plan is built -------------------
+ * The NumPy dots of body.py:184-191 (definitions), :254-255 (L-type limits)
+ * and :279-292 (cost products) for the constant coefficient matrices.
+ * C = alpha * op(A) @ B + beta * C on FP64 tensor cores (DMMA m8n8k4),
+ * op(A) = A (M x K, lda) or A^T (A stored K x M, lda) when transA != 0.
+ * Strided batch: matrix i starts at X + i * strideX.                        */
+int mpci_gemm(int transA, int M, int N, int K, double alpha, const double* A_dev, int lda,
+              long strideA, const double* B_dev, int ldb, long strideB, double beta,
+              double* C_dev, int ldc, long strideC, int batch, void* stream);
+
+/* dst[i][j] += alpha * rowscale[i or 0] * src[i or 0][j]   (rows x cols);
+ * src has src_rows (1 = broadcast) rows, rowscale n_rowscale (0 = none,
+ * 1 = broadcast) entries: the `c * Mo[schedule]` of body.py:258-259.       */
+int mpci_axpy2d(int rows, int cols, double alpha, const double* rowscale_dev, int n_rowscale,
+                const double* src_dev, int ld_src, int src_rows, double* dst_dev, int ld_dst,
+                void* stream);
+
+/* ---- the assembly plan ---------------------------------------------------
+ * One plan = one formulation structure (index layout + constant matrices).
+ * Per instance b the kernels evaluate
+ *     c_m(b)    = prod_f scalars[b][monomials[m][f]]        (index -1 = skip)
+ *     P[b]      = sum_t c_{P_terms[t]}(b) * DP[t]            nv x nv
+ *     G[b]      = sum_t c_{G_terms[t]}(b) * DG[t]            nc x nv
+ *     [q; h][b] = sum_t c_{Y_terms[t]}(b) * DY[t] @ [given[b]; 1]
+ * which is Formulation.generate_all_qp_matrices (body.py:333-348) for a
+ * formulation whose per-instance numbers are the scalars and `given`.       */
+typedef struct {
+  int nv, ng, nc;       /* optim_len, given_len, constraint rows             */
+  int n_scalars;        /* per-instance scalars (>= 1; column 0 may be dummy) */
+  int n_monomials;
+  const int* monomials; /* host [n_monomials][MPCI_MAX_FACTORS]               */
+  int n_P_terms;        /* <= MPCI_MAX_TERMS                                  */
+  const int* P_terms;   /* host [n_P_terms] indices into monomials            */
+  const double* DP_dev; /* dev  [n_P_terms][nv][nv]                           */
+  int n_G_terms;        /* <= MPCI_MAX_TERMS                                  */
+  const int* G_terms;
+  const double* DG_dev; /* dev  [n_G_terms][nc][nv]                           */
+  int n_Y_terms;
+  const int* Y_terms;
+  const double* DY_dev; /* dev  [n_Y_terms][nv + nc][ng + 1]                  */
+  int n_qh_ranges;      /* non-zero (row tile, term, k0, k1) blocks of DY     */
+  const int* qh_ranges; /* host [n_qh_ranges][4], grouped by row tile         */
+  const int* qh_tile_ptr; /* host [ceil((nv+nc)/MPCI_QH_ROW_TILE) + 1]        */
+} mpci_plan_desc;
+
+typedef struct mpci_plan mpci_plan;
+
+/* Copies the small host tables; keeps the DP/DG/DY device pointers (owned by
+ * the caller, must outlive the plan).  Allocates a transposed copy of DY.   */
+int mpci_plan_create(const mpci_plan_desc* desc, mpci_plan** plan_out);
+int mpci_plan_destroy(mpci_plan* plan);
+
+/* Device-resident assembly: replaces generate_all_qp_matrices for `batch`
+ * instances.  scalars_dev [batch][n_scalars], given_dev [batch][ng];
+ * outputs P_dev [batch][nv][nv], q_dev [batch][nv], G_dev [batch][nc][nv],
+ * h_dev [batch][nc], row-major and unpadded.  Any output may be NULL.       */
+int mpci_assemble(const mpci_plan* plan, const double* scalars_dev, const double* given_dev,
+                  double* P_dev, double* q_dev, double* G_dev, double* h_dev, long batch,
+                  void* stream);
+
+/* Same with HOST buffers: inputs are copied to the device and results back in
+ * chunks of `chunk` instances on two streams (copy/compute overlap).  The plan
+ * owns the device staging buffers (allocated on first use, freed by destroy). */
+int mpci_assemble_host(mpci_plan* plan, const double* scalars_host, const double* given_host,
+                       double* P_host, double* q_host, double* G_host, double* h_host,
+                       long batch, long chunk);
+
+/* Number of kernel launches one mpci_assemble call issues for this plan.    */
+int mpci_assemble_launches(const mpci_plan* plan);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPCI_H */

@@ -1,0 +1,351 @@
+"""ctypes binding of libmpci.so and the device backend of the plan compiler.
+
+PyTorch is used for device memory and streams only (allocation, slicing views,
+host<->device copies); every floating-point operation goes through the C ABI
+of include/mpci.h into the hand-written sm_100a kernels of csrc/.  There is no
+CPU path: a missing library or GPU raises ``RuntimeError``.
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libmpci.so")
+
+MAX_FACTORS = 4
+_c_double_p = ctypes.c_void_p
+_lib = None
+
+
+class PlanDesc(ctypes.Structure):
+    """mpci_plan_desc of include/mpci.h"""
+
+    _fields_ = [
+        ("nv", ctypes.c_int),
+        ("ng", ctypes.c_int),
+        ("nc", ctypes.c_int),
+        ("n_scalars", ctypes.c_int),
+        ("n_monomials", ctypes.c_int),
+        ("monomials", ctypes.c_void_p),
+        ("n_P_terms", ctypes.c_int),
+        ("P_terms", ctypes.c_void_p),
+        ("DP_dev", ctypes.c_void_p),
+        ("n_G_terms", ctypes.c_int),
+        ("G_terms", ctypes.c_void_p),
+        ("DG_dev", ctypes.c_void_p),
+        ("n_Y_terms", ctypes.c_int),
+        ("Y_terms", ctypes.c_void_p),
+        ("DY_dev", ctypes.c_void_p),
+        ("n_qh_ranges", ctypes.c_int),
+        ("qh_ranges", ctypes.c_void_p),
+        ("qh_tile_ptr", ctypes.c_void_p),
+    ]
+
+
+_SIGNATURES = {
+    "mpci_version": (ctypes.c_int, []),
+    "mpci_last_error": (ctypes.c_char_p, []),
+    "mpci_device_count": (ctypes.c_int, []),
+    "mpci_extend_matrices": (
+        ctypes.c_int,
+        [_c_double_p] * 4 + [ctypes.c_int] * 4 + [ctypes.c_void_p],
+    ),
+    "mpci_extend_compact": (
+        ctypes.c_int,
+        [_c_double_p] * 4 + [ctypes.c_int] * 4 + [ctypes.c_void_p],
+    ),
+    "mpci_extend_matrices_host": (ctypes.c_int, [_c_double_p] * 4 + [ctypes.c_int] * 4),
+    "mpci_gemm": (
+        ctypes.c_int,
+        [ctypes.c_int] * 4
+        + [ctypes.c_double, _c_double_p, ctypes.c_int, ctypes.c_long]
+        + [_c_double_p, ctypes.c_int, ctypes.c_long]
+        + [ctypes.c_double, _c_double_p, ctypes.c_int, ctypes.c_long, ctypes.c_int]
+        + [ctypes.c_void_p],
+    ),
+    "mpci_axpy2d": (
+        ctypes.c_int,
+        [ctypes.c_int, ctypes.c_int, ctypes.c_double, _c_double_p, ctypes.c_int]
+        + [_c_double_p, ctypes.c_int, ctypes.c_int, _c_double_p, ctypes.c_int, ctypes.c_void_p],
+    ),
+    "mpci_plan_create": (ctypes.c_int, [ctypes.POINTER(PlanDesc), ctypes.POINTER(ctypes.c_void_p)]),
+    "mpci_plan_destroy": (ctypes.c_int, [ctypes.c_void_p]),
+    "mpci_assemble": (
+        ctypes.c_int,
+        [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_void_p],
+    ),
+    "mpci_assemble_host": (
+        ctypes.c_int,
+        [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_long],
+    ),
+    "mpci_assemble_launches": (ctypes.c_int, [ctypes.c_void_p]),
+}
+
+
+def exported_symbols():
+    return sorted(_SIGNATURES)
+
+
+def lib():
+    """Loads libmpci.so (built in-tree by __graft_entry__.build / csrc/Makefile)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "the CUDA library {} is missing: run `make -C {}` (there is no CPU "
+                "fallback)".format(LIB_PATH, os.path.dirname(LIB_PATH))
+            )
+        loaded = ctypes.CDLL(LIB_PATH)
+        for name, (restype, argtypes) in _SIGNATURES.items():
+            fn = getattr(loaded, name)
+            fn.restype = restype
+            fn.argtypes = argtypes
+        _lib = loaded
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        message = lib().mpci_last_error().decode("utf-8", "replace")
+        if rc < 0:
+            raise ValueError("libmpci: {} (code {})".format(message, rc))
+        raise RuntimeError("libmpci: CUDA error {}: {}".format(rc, message))
+
+
+def require_gpu():
+    if lib().mpci_device_count() < 1:
+        raise RuntimeError(
+            "no CUDA device is visible: mpc_interface_b200 computes every matrix on "
+            "the GPU and has no CPU fallback"
+        )
+
+
+def _torch():
+    import torch
+
+    return torch
+
+
+def _stream_ptr():
+    return ctypes.c_void_p(_torch().cuda.current_stream().cuda_stream)
+
+
+def _ptr(tensor):
+    return ctypes.c_void_p(tensor.data_ptr()) if tensor is not None else ctypes.c_void_p(0)
+
+
+# ---------------------------------------------------------------------------
+# K1
+# ---------------------------------------------------------------------------
+def extend_matrices_host(N, A, B):
+    """A [batch,n,n], B [batch,n,m] (numpy) -> S [batch,N,n,n], U [batch,m,N,N,n]."""
+    require_gpu()
+    batch, n, m = B.shape
+    S = np.empty([batch, N, n, n])
+    U = np.empty([batch, m, N, N, n])
+    check(
+        lib().mpci_extend_matrices_host(
+            A.ctypes.data, B.ctypes.data, S.ctypes.data, U.ctypes.data, batch, n, m, N
+        )
+    )
+    return S, U
+
+
+def extend_matrices_device(N, A, B, dense=True):
+    """CUDA tensors in, CUDA tensors out.  dense=False returns the compact
+    impulse response (Phi [batch,N,n,n], Gam [batch,N,n,m])."""
+    require_gpu()
+    torch = _torch()
+    batch, n, m = B.shape
+    A = A.contiguous()
+    B = B.contiguous()
+    if dense:
+        S = torch.empty([batch, N, n, n], dtype=torch.float64, device=A.device)
+        U = torch.empty([batch, m, N, N, n], dtype=torch.float64, device=A.device)
+        check(lib().mpci_extend_matrices(_ptr(A), _ptr(B), _ptr(S), _ptr(U), batch, n, m, N, _stream_ptr()))
+        return S, U
+    Phi = torch.empty([batch, N, n, n], dtype=torch.float64, device=A.device)
+    Gam = torch.empty([batch, N, n, m], dtype=torch.float64, device=A.device)
+    check(lib().mpci_extend_compact(_ptr(A), _ptr(B), _ptr(Phi), _ptr(Gam), batch, n, m, N, _stream_ptr()))
+    return Phi, Gam
+
+
+# ---------------------------------------------------------------------------
+# batched outputs
+# ---------------------------------------------------------------------------
+class QPBatch:
+    """Device-resident QP matrices of a batch: ``P [B,nv,nv]``, ``q [B,nv]``,
+    ``G [B,nc,nv]``, ``h [B,nc]`` -- row-major and unpadded, i.e. instance b is
+    exactly the reference's C-ordered arrays (body.py:345-348)."""
+
+    def __init__(self, batch, nv, nc, device="cuda"):
+        torch = _torch()
+        kw = dict(dtype=torch.float64, device=device)
+        self.batch, self.nv, self.nc = batch, nv, nc
+        self.P = torch.empty([batch, nv, nv], **kw)
+        self.q = torch.empty([batch, nv], **kw)
+        self.G = torch.empty([batch, nc, nv], **kw)
+        self.h = torch.empty([batch, nc], **kw)
+
+    @staticmethod
+    def bytes_per_instance(nv, nc):
+        return 8 * (nv * nv + nv + nc * nv + nc)
+
+    def P_numpy(self):
+        return self.P.cpu().numpy()
+
+    def q_numpy(self):
+        return self.q.cpu().numpy()
+
+    def G_numpy(self):
+        return self.G.cpu().numpy()
+
+    def h_numpy(self):
+        return self.h.cpu().numpy()
+
+
+class DevicePlan:
+    """Owns the mpci_plan handle and keeps the constant tensors alive."""
+
+    def __init__(self, plan):
+        self.keep = (plan.DP, plan.DG, plan.DY)
+        table = np.ascontiguousarray(plan.mono_table(), dtype=np.int32)
+        P_terms = np.ascontiguousarray(plan.P_terms, dtype=np.int32)
+        G_terms = np.ascontiguousarray(plan.G_terms, dtype=np.int32)
+        Y_terms = np.ascontiguousarray(plan.Y_terms, dtype=np.int32)
+        ranges = np.ascontiguousarray(plan.qh_ranges, dtype=np.int32)
+        tile_ptr = np.ascontiguousarray(plan.qh_tile_ptr, dtype=np.int32)
+        desc = PlanDesc(
+            plan.nv, plan.ng, plan.nc, max(1, len(plan.slots.exprs)),
+            table.shape[0], table.ctypes.data,
+            len(P_terms), P_terms.ctypes.data, plan.DP.data_ptr(),
+            len(G_terms), G_terms.ctypes.data, plan.DG.data_ptr(),
+            len(Y_terms), Y_terms.ctypes.data, plan.DY.data_ptr(),
+            ranges.shape[0], ranges.ctypes.data, tile_ptr.ctypes.data,
+        )
+        handle = ctypes.c_void_p()
+        check(lib().mpci_plan_create(ctypes.byref(desc), ctypes.byref(handle)))
+        self.handle = handle
+        self.launches = lib().mpci_assemble_launches(handle)
+
+    def __del__(self):
+        handle, self.handle = getattr(self, "handle", None), None
+        if handle and _lib is not None:
+            _lib.mpci_plan_destroy(handle)
+
+
+class DeviceBackend:
+    """The ``ops`` interface of plan.py on CUDA tensors (float64)."""
+
+    def __init__(self, device=None):
+        require_gpu()
+        torch = _torch()
+        self.torch = torch
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+
+    # -- memory (plumbing) ---------------------------------------------------
+    def upload(self, array):
+        return self.torch.from_numpy(np.ascontiguousarray(array, dtype=np.float64)).to(self.device)
+
+    def zeros(self, rows, cols):
+        return self.torch.zeros([rows, cols], dtype=self.torch.float64, device=self.device)
+
+    def download(self, H):
+        return H.cpu().numpy()
+
+    download3 = download
+
+    def rows(self, H, index):
+        index = list(index)
+        if index and index == list(range(index[0], index[0] + len(index))):
+            return H[index[0] : index[0] + len(index)]
+        idx = self.torch.tensor(index, dtype=self.torch.long, device=self.device)
+        return H.index_select(0, idx)
+
+    def sub(self, H, r0, r1, c0, c1):
+        return H[r0:r1, c0:c1]
+
+    def stack(self, handles):
+        return self.torch.stack([h.contiguous() for h in handles]).contiguous()
+
+    # -- arithmetic (kernels of csrc/mpci_linalg.cu) ---------------------------
+    @staticmethod
+    def _ld(H):
+        if H.dim() != 2 or (H.shape[1] > 1 and H.stride(1) != 1):
+            raise ValueError("expected a row-major 2-D view")
+        return max(H.stride(0), H.shape[1], 1) if H.shape[0] > 1 else max(H.shape[1], 1)
+
+    def gemm(self, A, B, transA=False):
+        M, K = (A.shape[1], A.shape[0]) if transA else (A.shape[0], A.shape[1])
+        if B.shape[0] != K:
+            raise ValueError(
+                "matmul: mismatch in the contracted dimension ({} and {})".format(K, B.shape[0])
+            )
+        N = B.shape[1]
+        C = self.torch.empty([M, N], dtype=self.torch.float64, device=self.device)
+        check(
+            lib().mpci_gemm(
+                1 if transA else 0, M, N, K, 1.0, _ptr(A), self._ld(A), 0, _ptr(B), self._ld(B), 0,
+                0.0, _ptr(C), max(N, 1), 0, 1, _stream_ptr(),
+            )
+        )
+        return C
+
+    def axpy(self, dst, src, alpha, rowscale=None):
+        rows, cols = dst.shape
+        if src.shape[1] != cols or src.shape[0] not in (1, rows):
+            raise ValueError(
+                "operands could not be broadcast together with shapes {} {}".format(
+                    tuple(dst.shape), tuple(src.shape)
+                )
+            )
+        scale = None
+        if rowscale is not None:
+            scale = self.upload(np.asarray(rowscale, dtype=np.float64).reshape(-1))
+            if scale.shape[0] not in (1, rows):
+                raise ValueError("row multipliers do not match the {} rows".format(rows))
+        check(
+            lib().mpci_axpy2d(
+                rows, cols, float(alpha), _ptr(scale), 0 if scale is None else scale.shape[0],
+                _ptr(src), self._ld(src), src.shape[0], _ptr(dst), self._ld(dst), _stream_ptr(),
+            )
+        )
+
+    # -- the hot path ----------------------------------------------------------
+    def device_plan(self, plan):
+        if getattr(plan, "_device_plan", None) is None:
+            plan._device_plan = DevicePlan(plan)
+        return plan._device_plan
+
+    def assemble(self, plan, scalars, given, batch, out=None):
+        torch = self.torch
+        dp = self.device_plan(plan)
+        if not hasattr(scalars, "device"):
+            scalars = torch.from_numpy(np.ascontiguousarray(scalars, dtype=np.float64)).to(self.device)
+        if not hasattr(given, "device"):
+            given = torch.from_numpy(np.ascontiguousarray(given, dtype=np.float64)).to(self.device)
+        scalars = scalars.contiguous()
+        given = given.contiguous().reshape(batch, plan.ng)
+        if out is None:
+            out = QPBatch(batch, plan.nv, plan.nc, self.device)
+        elif (out.batch, out.nv, out.nc) != (batch, plan.nv, plan.nc):
+            raise ValueError("the output batch does not match the plan")
+        check(
+            lib().mpci_assemble(
+                dp.handle, _ptr(scalars), _ptr(given), _ptr(out.P), _ptr(out.q), _ptr(out.G),
+                _ptr(out.h), batch, _stream_ptr(),
+            )
+        )
+        return out
+
+    def assemble_host(self, plan, scalars, given, P, q, G, h, batch, chunk):
+        """Host (ideally pinned) numpy / CPU-tensor buffers in and out."""
+        dp = self.device_plan(plan)
+
+        def p(x):
+            if x is None:
+                return ctypes.c_void_p(0)
+            return ctypes.c_void_p(x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
+
+        check(lib().mpci_assemble_host(dp.handle, p(scalars), p(given), p(P), p(q), p(G), p(h), batch, chunk))

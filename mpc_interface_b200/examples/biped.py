@@ -53,7 +53,7 @@ def default_configuration(horizon_lenght=None):
     return c
 
 
-def formulate_biped(conf, omega=None, target_vel=None, backend=None):
+def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=True):
     """Builds the Formulation.  ``omega`` / ``target_vel`` default to the
     configuration's numbers; pass ``Param``s to make them per-instance."""
     w = conf.omega if omega is None else omega
@@ -128,7 +128,8 @@ def formulate_biped(conf, omega=None, target_vel=None, backend=None):
     form.incorporate_box("support_polygon", support_polygon)
     form.incorporate_box("terminal_Constraint", terminal_constraint)
     form.identify_qp_domain(list(OPTIM))
-    form.make_preview_matrices()
+    if preview:  # builds the device plan; False leaves a host-only description
+        form.make_preview_matrices()
 
     def tick(body, **kargs):
         """Needs ``step_times`` and ``step_count`` (biped_formulation.py:156-187)."""

@@ -1,0 +1,102 @@
+"""Builders shared by the CPU and GPU tests: formulations that correspond to
+the golden files of tests/golden/ (see make_goldens.py for the reference side)."""
+import os
+
+import numpy as np
+
+from mpc_interface_b200 import (
+    Box, Constraint, ControlSystem, Cost, DomainVariable, ExtendedSystem, Formulation,
+    LineCombo, Param,
+)
+from mpc_interface_b200 import tools as use
+from mpc_interface_b200.examples.biped import default_configuration, formulate_biped
+from mpc_interface_b200.examples.generic import formulate_generic
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = 1e-10  # north_star: relative error <= 1e-10 on P, q, G, h (normwise, per array)
+
+
+def golden(name):
+    return np.load(os.path.join(GOLDEN, name + ".npz"))
+
+
+def rel_err(x, ref):
+    x, ref = np.asarray(x, dtype=float), np.asarray(ref, dtype=float)
+    assert x.shape == ref.shape, (x.shape, ref.shape)
+    if ref.size == 0:
+        return 0.0
+    scale = np.max(np.abs(ref))
+    return float(np.max(np.abs(x - ref)) / (scale if scale > 0 else 1.0))
+
+
+def assert_qp_close(got, ref, tol=TOL):
+    """got / ref: (A, h, Q, q) tuples (any of them batched)."""
+    for name, x, r in zip("AhQq", got, ref):
+        err = rel_err(np.squeeze(x), np.squeeze(r))
+        assert err <= tol, "{}: relative error {:.3e} > {:.1e}".format(name, err, tol)
+
+
+def check_layout(form, g):
+    for kind in ("optim", "given"):
+        ids = getattr(form, kind + "_ID")
+        assert list(ids.keys()) == [str(s) for s in g[kind + "_names"]]
+        got = np.array([[r.start, r.stop] for r in ids.values()], dtype=np.int64)
+        assert np.array_equal(got, g[kind + "_ranges"])  # bit-exact integer layout
+
+
+def biped_batched(g, backend=None):
+    conf = default_configuration(int(g["N"]))
+    if float(g["terminal_weight"]) >= 0:
+        conf.cost_weights["terminal"] = float(g["terminal_weight"])
+    form = formulate_biped(
+        conf, omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")], backend=backend
+    )
+    params = {k: g[k] for k in ("omega", "vel_x", "vel_y")}
+    return form, params
+
+
+def body_test_formulation(backend=None):
+    """The formulation of the reference's python/tests/test_body.py:23-98."""
+    axes = ["_x", "_y"]
+    LIP = ControlSystem.from_name("J->CCC", tau=0.1, omega=3.5, axes=axes)
+    LIP_ext = ExtendedSystem.from_cotrol_system(LIP, "x", 9)
+    E = use.plan_steps(9, 1, step_times=np.array([2, 5, 8]))[:, :, None]
+    steps = ExtendedSystem(["Ds"], ["s"], "s", np.ones([9, 1, 1]), [E], axes)
+    bias = DomainVariable("n", 9, axes)
+    body = Formulation(backend=backend)
+    body.incorporate_dynamics("steps", steps)
+    body.incorporate_dynamics("LIP", LIP_ext)
+    body.incorporate_dynamics("n", bias)
+    body.incorporate_definitions(
+        {
+            "DCM_x": LineCombo({"CoM_x": 1, "CoM_dot_x": 1 / 3.5}),
+            "DCM_y": LineCombo({"CoM_y": 1, "CoM_dot_y": 1 / 3.5}),
+        }
+    )
+    body.incorporate_constraint("kinematics", Constraint("CoM_x", 4))
+    body.incorporate_constraint(
+        "steppingArea", Constraint("s", 10, arrow=[1, 1], axes=axes, L=np.eye(9))
+    )
+    body.incorporate_goal("velocity", Cost("CoM_dot", aim=[1, 2], weight=10, axes=axes))
+    body.incorporate_goal("stability", Cost("DCM_x", aim=2, weight=1))
+    body.incorporate_goal(
+        "terminal", Cost("CoM", aim=[50, 50], weight=100, axes=axes, schedule=range(8, 9))
+    )
+    body.incorporate_goal("crossed", Cost("DCM_x", aim=2, weight=1, cross="s_y", cross_L=np.eye(9)))
+    vertices = np.array([[0, 1], [1, 0], [0, -1], [-1, 0]])
+    body.incorporate_box("kine", Box.task_space("CoM", vertices, axes))
+    body.identify_qp_domain(["x0_x", "x0_y", "Ds_x", "Ds_y", "CoM_dddot_x", "CoM_dddot_y"])
+    body.make_preview_matrices()
+    return body
+
+
+def generic_batched(g, backend=None):
+    nx = g["A_sys"].shape[0]
+    refs = [Param("ref%d" % i) for i in range(nx)]
+    form = formulate_generic(
+        g["A_sys"], g["B_sys"], g["Q_w"], g["R_w"], int(g["N"]), g["rows"], refs=refs,
+        backend=backend,
+    )
+    params = {"ref%d" % i: g["ref"][:, i] for i in range(nx)}
+    given = g["x0"]  # the only given variable is x0
+    return form, params, given

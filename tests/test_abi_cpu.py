@@ -1,0 +1,68 @@
+"""The C-ABI library loads on a machine without a GPU and exports every symbol
+include/mpci.h declares; argument validation works without touching a device."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as entry
+    from mpc_interface_b200 import device
+
+    if not os.path.exists(device.LIB_PATH):
+        entry.build()
+    return device.lib()
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "mpci.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(mpci_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_and_binding_agree(lib):
+    from mpc_interface_b200 import device
+
+    names = declared_symbols()
+    assert names == device.exported_symbols()
+    for name in names:
+        assert getattr(lib, name) is not None
+
+
+def test_version_and_error_string(lib):
+    assert lib.mpci_version() == 100
+    assert isinstance(lib.mpci_last_error(), bytes)
+
+
+def test_argument_validation_needs_no_gpu(lib):
+    # negative sizes are refused before any CUDA call
+    rc = lib.mpci_extend_matrices(None, None, None, None, 1, 0, 1, 5, None)
+    assert rc < 0 and b"sizes must be positive" in lib.mpci_last_error()
+    rc = lib.mpci_extend_matrices(None, None, None, None, 1, 64, 1, 5, None)
+    assert rc < 0 and b"exceed" in lib.mpci_last_error()
+    rc = lib.mpci_gemm(0, -1, 1, 1, 1.0, None, 1, 0, None, 1, 0, 0.0, None, 1, 0, 1, None)
+    assert rc < 0
+    rc = lib.mpci_assemble(None, None, None, None, None, None, None, 4, None)
+    assert rc < 0 and b"NULL plan" in lib.mpci_last_error()
+    assert lib.mpci_plan_create(None, None) < 0
+    assert lib.mpci_plan_destroy(None) == 0
+
+
+def test_product_path_fails_loudly_without_gpu(lib):
+    """No CPU fallback: without a device every matrix-producing call raises."""
+    import numpy as np
+    from mpc_interface_b200 import tools
+
+    if lib.mpci_device_count() > 0:
+        pytest.skip("a GPU is visible")
+    with pytest.raises(RuntimeError):
+        tools.extend_matrices(5, np.eye(2), np.ones([2, 1]))
+    from mpc_interface_b200 import Formulation
+
+    with pytest.raises(RuntimeError):
+        Formulation()._ops()

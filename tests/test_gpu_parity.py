@@ -1,0 +1,261 @@
+"""Parity of the CUDA path (through the C ABI of include/mpci.h) with the
+oracle and with the golden vectors written by the unmodified reference.
+
+Tolerance: north_star asks for relative error <= 1e-10 on P, q, G, h; the
+metric is normwise per array, max|x - ref| / max|ref| (cases.TOL).  Integer
+layouts (optim_ID / given_ID, row offsets) must be equal bit for bit."""
+import numpy as np
+import pytest
+
+import _cases as cases
+from oracle import qp_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from mpc_interface_b200 import device
+
+    device.require_gpu()
+    return device
+
+
+# ---------------------------------------------------------------- K1
+def test_lip_pickle_golden(dev):
+    """The reference's only value-level pin of K1 (test_dynamics.py:139-152)."""
+    from mpc_interface_b200 import ControlSystem, ExtendedSystem
+
+    g = cases.golden("lip_matrices")
+    LIP = ControlSystem.from_name("J->CCC", tau=0.1, omega=3.3445)
+    ext = ExtendedSystem.from_cotrol_system(LIP, "x", 36)
+    assert np.isclose(ext.matrices[0], g["U"]).all()
+    assert np.isclose(ext.matrices[1], g["S"]).all()
+    assert cases.rel_err(ext.matrices[0], g["U"]) < 1e-13
+
+
+@pytest.mark.parametrize("tag", list("abcde"))
+def test_extend_matrices_cases(dev, tag):
+    from mpc_interface_b200 import tools
+
+    g = cases.golden("extend_cases")
+    A, B = g[tag + "_A"], g[tag + "_B"]
+    N = g[tag + "_S"].shape[0]
+    S, U = tools.extend_matrices(N, A, B)
+    assert S.shape == (N,) + A.shape and len(U) == B.shape[1] and U[0].shape == (N, N, A.shape[0])
+    assert cases.rel_err(S, g[tag + "_S"]) < 1e-12
+    assert cases.rel_err(np.stack(U), g[tag + "_U"]) < 1e-12
+    assert (np.stack(U)[:, np.triu_indices(N, 1)[0], np.triu_indices(N, 1)[1]] == 0).all()
+
+
+def test_extend_matrices_batched_device(dev):
+    import torch
+
+    rng = np.random.default_rng(0)
+    batch, n, m, N = 37, 6, 2, 40
+    A = np.eye(n) + 0.05 * rng.normal(size=[batch, n, n])
+    B = rng.normal(size=[batch, n, m])
+    S, U = dev.extend_matrices_device(N, torch.from_numpy(A).cuda(), torch.from_numpy(B).cuda())
+    Phi, Gam = dev.extend_matrices_device(
+        N, torch.from_numpy(A).cuda(), torch.from_numpy(B).cuda(), dense=False
+    )
+    S, U, Phi, Gam = (x.cpu().numpy() for x in (S, U, Phi, Gam))
+    for b in (0, 17, 36):
+        So, Uo = orc.extend_matrices(N, A[b], B[b])
+        assert cases.rel_err(S[b], So) < 1e-12 and cases.rel_err(U[b], np.stack(Uo)) < 1e-12
+        assert cases.rel_err(Phi[b], So.transpose(0, 2, 1)) < 1e-12
+        assert cases.rel_err(Gam[b][:, :, 0], Uo[0][:, 0, :]) < 1e-12
+
+
+def test_extend_matrices_errors(dev):
+    from mpc_interface_b200 import tools
+
+    with pytest.raises(ValueError):
+        tools.extend_matrices(5, np.eye(3), np.ones([2, 1]))
+    with pytest.raises(ValueError):
+        tools.extend_matrices(0, np.eye(3), np.ones([3, 1]))
+
+
+# ---------------------------------------------------------------- plan-time kernels
+@pytest.mark.parametrize("shape", [(1, 1, 1), (7, 5, 3), (64, 64, 16), (100, 218, 100), (218, 426, 100), (130, 70, 33)])
+@pytest.mark.parametrize("transA", [False, True])
+def test_dmma_gemm(dev, shape, transA):
+    ops = dev.DeviceBackend()
+    M, N, K = shape
+    rng = np.random.default_rng(M * 1000 + N)
+    A = rng.normal(size=[K, M] if transA else [M, K])
+    B = rng.normal(size=[K, N])
+    C = ops.download(ops.gemm(ops.upload(A), ops.upload(B), transA=transA))
+    ref = (A.T if transA else A) @ B
+    assert cases.rel_err(C, ref) < 1e-13
+    # strided views (what the plan compiler passes)
+    big = ops.upload(rng.normal(size=[K + 3, N + 9]))
+    Cv = ops.download(ops.gemm(ops.upload(A), ops.sub(big, 2, K + 2, 4, N + 4), transA=transA))
+    assert cases.rel_err(Cv, (A.T if transA else A) @ ops.download(big)[2 : K + 2, 4 : N + 4]) < 1e-13
+
+
+def test_axpy2d(dev):
+    ops = dev.DeviceBackend()
+    rng = np.random.default_rng(4)
+    dst0, src = rng.normal(size=[9, 13]), rng.normal(size=[9, 13])
+    scale = rng.normal(size=9)
+    d = ops.upload(dst0)
+    ops.axpy(d, ops.upload(src), 0.5, scale)
+    assert np.allclose(ops.download(d), dst0 + 0.5 * scale[:, None] * src, rtol=1e-15, atol=0)
+    d = ops.upload(dst0)
+    ops.axpy(d, ops.upload(src[:1]), -2.0, None)
+    assert np.allclose(ops.download(d), dst0 - 2.0 * src[:1], rtol=1e-15, atol=0)
+    with pytest.raises(ValueError):
+        ops.axpy(d, ops.upload(src[:4]), 1.0, None)
+
+
+# ---------------------------------------------------------------- the assembly path
+def test_biped_c1_single_instance(dev):
+    """Config 1: the repo example at its default horizon, one instance."""
+    g = cases.golden("biped_c1")
+    form = cases.formulate_biped(cases.default_configuration())
+    cases.check_layout(form, g)
+    A, h, Q, q = form.generate_all_qp_matrices(g["given"])
+    assert A.shape == (108, 52) and h.shape == (108, 1) and Q.shape == (52, 52) and q.shape == (52, 1)
+    cases.assert_qp_close((A, h, Q, q), (g["A"], g["h"], g["Q"], g["q"]))
+    Mg, Mo = form.PM["(b+n-s)_x"]
+    assert cases.rel_err(np.hstack([Mg, Mo]), g["PM_bns_x"]) < 1e-13
+
+
+@pytest.mark.parametrize("name", ["biped_n24_batch", "biped_n24_terminal", "biped_n100_batch"])
+def test_biped_batched_goldens(dev, name):
+    g = cases.golden(name)
+    form, params = cases.biped_batched(g)
+    cases.check_layout(form, g)
+    out = form.generate_all_qp_matrices_batched(g["given"], params)
+    assert out.P.is_cuda and out.P.shape == g["Q"].shape and out.G.shape == g["A"].shape
+    cases.assert_qp_close(
+        (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy()),
+        (g["A"], g["h"], g["Q"], g["q"]),
+    )
+
+
+@pytest.mark.parametrize("N,batch", [(24, 67), (100, 9)])
+def test_biped_vs_oracle_random(dev, N, batch):
+    """Seeded inputs of SURVEY 8(d), ragged batch sizes (not multiples of the
+    32 / 16 instance groups of the kernels)."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    conf = cases.default_configuration(N)
+    form = cases.formulate_biped(conf, omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")])
+    vals = synthetic.biped_inputs(77 + N, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    P, q, G, h = out.P_numpy(), out.q_numpy(), out.G_numpy(), out.h_numpy()
+    for b in sorted({0, 1, batch // 2, batch - 2, batch - 1}):
+        one = {k: float(v[b]) for k, v in params.items()}
+        ref = orc.all_qp_matrices(form, given[b][:, None], one)
+        cases.assert_qp_close((G[b], h[b], P[b], q[b]), ref)
+
+
+def test_reference_test_body_case(dev):
+    g = cases.golden("test_body")
+    body = cases.body_test_formulation()
+    cases.check_layout(body, g)
+    cases.assert_qp_close(body.generate_all_qp_matrices(g["given"]), (g["A"], g["h"], g["Q"], g["q"]))
+    cQ, cq = body.generate_qp_cost(body.goals["crossed"], g["given"])
+    assert cases.rel_err(cQ, g["cQ"]) < cases.TOL and cases.rel_err(cq, g["cq"]) < cases.TOL
+    kin = body.constraints["kinematics"][0]
+    A0, h0 = body.generate_qp_constraint(kin, g["given"])
+    assert (h0 == kin.bound()).all()  # given does not affect this limit (test_body.py:141-142)
+    A2, h2 = body.generate_all_qp_constraints(g["given"])
+    assert A2.shape == (54, body.optim_len) and h2.shape == (54, 1)
+
+
+@pytest.mark.parametrize("name", ["generic_small", "generic_c4_shape"])
+def test_generic_goldens(dev, name):
+    g = cases.golden(name)
+    form, params, given = cases.generic_batched(g)
+    out = form.generate_all_qp_matrices_batched(given, params)
+    cases.assert_qp_close(
+        (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy()),
+        (g["A"], g["h"], g["Q"], g["q"]),
+    )
+
+
+def test_biped_ticks_ragged_sizes(dev):
+    g = cases.golden("biped_ticks")
+    form = cases.formulate_biped(cases.default_configuration(24))
+    for tick in (0, 11, 12, 13):
+        form.update(step_times=g["t%d_step_times" % tick], step_count=int(g["t%d_step_count" % tick]))
+        got = form.generate_all_qp_matrices(g["t%d_given" % tick])
+        cases.assert_qp_close(got, tuple(g["t%d_%s" % (tick, k)] for k in "AhQq"))
+
+
+def test_host_buffer_entry_point_and_reuse(dev):
+    """mpci_assemble_host (chunked, two streams) equals the device-resident call;
+    an output batch can be reused as a ring slot."""
+    import torch
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    N, batch = 24, 150
+    form = cases.formulate_biped(
+        cases.default_configuration(N), omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")]
+    )
+    vals = synthetic.biped_inputs(5, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    again = form.generate_all_qp_matrices_batched(given, params, out=out)
+    assert again is out
+    plan = form._compiled()
+    scalars = torch.from_numpy(plan.slots.evaluate(params, batch)).pin_memory()
+    hp = torch.empty([batch, plan.nv, plan.nv], dtype=torch.float64).pin_memory()
+    hq = torch.empty([batch, plan.nv], dtype=torch.float64).pin_memory()
+    hG = torch.empty([batch, plan.nc, plan.nv], dtype=torch.float64).pin_memory()
+    hh = torch.empty([batch, plan.nc], dtype=torch.float64).pin_memory()
+    form._ops().assemble_host(plan, scalars, torch.from_numpy(given).pin_memory(), hp, hq, hG, hh, batch, 64)
+    assert torch.equal(hp, out.P.cpu()) and torch.equal(hG, out.G.cpu())
+    assert torch.equal(hq, out.q.cpu()) and torch.equal(hh, out.h.cpu())
+
+
+def test_full_width_properties(dev):
+    """Size-independent checks on a larger batch at N=100 (config 2 shape):
+    P symmetric, [q; h] affine in given, a checksum of checksums of G."""
+    import torch
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    N, batch = 100, 2048
+    form = cases.formulate_biped(
+        cases.default_configuration(N), omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")]
+    )
+    vals = synthetic.biped_inputs(1002, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    assert out.P.shape == (batch, 218, 218) and out.G.shape == (batch, 440, 218)
+    sym = (out.P - out.P.transpose(1, 2)).abs().amax().item()
+    assert sym <= 1e-12 * out.P.abs().amax().item()
+    # affine in given: f(g1) + f(g2) - f(0) == f(g1 + g2) with the same parameters
+    half = batch // 2
+    p2 = {k: np.concatenate([v[:half], v[:half]]) for k, v in params.items()}
+    g_sum = np.concatenate([given[:half] + given[half:], np.zeros_like(given[:half])])
+    o2 = form.generate_all_qp_matrices_batched(g_sum, p2)
+    p1 = {k: np.concatenate([v[:half], v[:half]]) for k, v in params.items()}
+    o1 = form.generate_all_qp_matrices_batched(given, p1)
+    lhs = o1.q[:half] + o1.q[half:] - o2.q[half:]
+    assert (lhs - o2.q[:half]).abs().amax().item() <= 1e-11 * o2.q.abs().amax().item()
+    lhs = o1.h[:half] + o1.h[half:] - o2.h[half:]
+    assert (lhs - o2.h[:half]).abs().amax().item() <= 1e-11 * o2.h.abs().amax().item()
+    # checksum of checksums: sum_b sum(G_b) == sum_t (sum_b c_t(b)) * sum(DG_t)
+    plan = form._compiled()
+    scal = plan.slots.evaluate(params, batch)
+    table = plan.mono_table()
+    coef = np.ones([batch, table.shape[0]])
+    for j in range(table.shape[0]):
+        for f in table[j]:
+            if f >= 0:
+                coef[:, j] *= scal[:, f]
+    sums = plan.DG.sum(dim=(1, 2)).cpu().numpy()
+    expect = float((coef[:, plan.G_terms].sum(axis=0) * sums).sum())
+    got = float(out.G.sum().item())
+    assert abs(got - expect) <= 1e-9 * max(1.0, abs(expect))

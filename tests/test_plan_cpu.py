@@ -1,0 +1,124 @@
+"""The plan compiler (symbolic host logic) against the goldens, on CPU.
+
+``NumpyBackend`` (tests/_numpy_backend.py) stands in for the CUDA backend so
+the monomial bookkeeping, row offsets and constant layout of plan.py can be
+checked without a GPU; the same comparisons run on the real kernels in
+test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+import _cases as cases
+from _numpy_backend import NumpyBackend
+from mpc_interface_b200 import Cost, Param, plan as planmod
+
+
+def test_biped_c1_single_instance(cpu_extend):
+    g = cases.golden("biped_c1")
+    form = cases.formulate_biped(cases.default_configuration(), backend=NumpyBackend())
+    A, h, Q, q = form.generate_all_qp_matrices(g["given"])
+    assert A.shape == (108, 52) and h.shape == (108, 1) and Q.shape == (52, 52) and q.shape == (52, 1)
+    cases.assert_qp_close((A, h, Q, q), (g["A"], g["h"], g["Q"], g["q"]))
+    Mg, Mo = form.PM["(b+n-s)_x"]
+    assert cases.rel_err(np.hstack([Mg, Mo]), g["PM_bns_x"]) < 1e-14
+    assert len(form.PM) == len(form.definitions) == 30
+
+
+@pytest.mark.parametrize("name", ["biped_n24_batch", "biped_n24_terminal", "biped_n100_batch"])
+def test_biped_batched(cpu_extend, name):
+    g = cases.golden(name)
+    form, params = cases.biped_batched(g, NumpyBackend())
+    out = form.generate_all_qp_matrices_batched(g["given"], params)
+    cases.assert_qp_close((out.G, out.h, out.P, out.q), (g["A"], g["h"], g["Q"], g["q"]))
+    compiled = form._compiled()
+    assert form.parameter_names() == ["omega", "vel_x", "vel_y"]
+    assert max(len(m) for m in compiled.monomials) <= planmod.MAX_FACTORS
+    assert compiled.row_offsets[0] == 0 and sum(compiled.limit_rows) == g["A"].shape[1]
+
+
+def test_plan_structure_biped_n100(cpu_extend):
+    g = cases.golden("biped_n100_batch")
+    form, _ = cases.biped_batched(g, NumpyBackend())
+    p = form._compiled()
+    assert (p.nv, p.ng, p.nc) == (218, 208, 440)
+    # stepping area 4 x 9, support polygon 4 x 100, terminal 4 x 1
+    assert p.limit_rows == [9] * 4 + [100] * 4 + [1] * 4
+    assert p.row_offsets == list(np.cumsum([0] + p.limit_rows[:-1]))
+    # P is a polynomial of degree 2 in -1/omega^2: 3 constant matrices
+    assert len(p.P_terms) == 3 and p.DP.shape == (3, 218, 218)
+    assert p.DG.shape[1:] == (440, 218) and p.DY.shape[1:] == (658, 209)
+    # integer tables the kernels index with
+    assert p.qh_tile_ptr[0] == 0 and p.qh_tile_ptr[-1] == len(p.qh_ranges)
+    assert (p.qh_ranges[:, 2] < p.qh_ranges[:, 3]).all()
+
+
+def test_reference_test_body_case(cpu_extend):
+    g = cases.golden("test_body")
+    body = cases.body_test_formulation(NumpyBackend())
+    got = body.generate_all_qp_matrices(g["given"])
+    cases.assert_qp_close(got, (g["A"], g["h"], g["Q"], g["q"]))
+    cQ, cq = body.generate_qp_cost(body.goals["crossed"], g["given"])
+    assert cases.rel_err(cQ, g["cQ"]) < 1e-12 and cases.rel_err(cq, g["cq"]) < 1e-12
+    assert np.abs(cQ - cQ.T).max() > 0  # crossed Hessians are not symmetrised (SURVEY B#3)
+    limit = body.constraints["steppingArea"][0]
+    A1, h1 = body.generate_qp_constraint(limit, g["given"])
+    assert cases.rel_err(A1, g["A1"]) < 1e-12 and cases.rel_err(h1, g["h1"]) < 1e-12
+    # the identity the reference's test asserts (test_body.py:138-142)
+    kin = body.constraints["kinematics"][0]
+    A0, h0 = body.generate_qp_constraint(kin, g["given"])
+    assert h0.shape == (9, 1) and A0.shape == (9, body.optim_len)
+    A2, h2 = body.generate_all_qp_constraints(g["given"])
+    assert A2.shape == (54, body.optim_len) and h2.shape == (54, 1)
+    Q, q = body.generate_all_qp_costs(g["given"])
+    assert cases.rel_err(Q, g["Q"]) < 1e-12 and cases.rel_err(q, g["q"]) < 1e-12
+
+
+@pytest.mark.parametrize("name", ["generic_small", "generic_c4_shape"])
+def test_generic_batched(cpu_extend, name):
+    g = cases.golden(name)
+    form, params, given = cases.generic_batched(g, NumpyBackend())
+    out = form.generate_all_qp_matrices_batched(given, params)
+    cases.assert_qp_close((out.G, out.h, out.P, out.q), (g["A"], g["h"], g["Q"], g["q"]))
+    # shared dynamics: P and G do not depend on the instance -> one constant term
+    assert form._compiled().P_terms == [0] and form._compiled().G_terms == [0]
+
+
+def test_biped_ticks_ragged_sizes(cpu_extend):
+    """Formulation.update changes nv / nc between ticks."""
+    g = cases.golden("biped_ticks")
+    conf = cases.default_configuration(24)
+    form = cases.formulate_biped(conf, backend=NumpyBackend())
+    sizes = set()
+    for tick in (0, 11, 12, 13):
+        form.update(step_times=g["t%d_step_times" % tick], step_count=int(g["t%d_step_count" % tick]))
+        got = form.generate_all_qp_matrices(g["t%d_given" % tick])
+        ref = tuple(g["t%d_%s" % (tick, k)] for k in "AhQq")
+        assert got[0].shape == ref[0].shape
+        cases.assert_qp_close(got, ref)
+        sizes.add(got[0].shape)
+    assert len(sizes) > 1
+
+
+def test_update_invalidates_plan(cpu_extend):
+    form = cases.formulate_biped(cases.default_configuration(), backend=NumpyBackend())
+    given = np.zeros([form.given_len, 1])
+    q0 = form.generate_all_qp_matrices(given)[3]
+    form.goals["track vel_x"].update(aim=0.1)
+    q1 = form.generate_all_qp_matrices(given)[3]
+    assert np.abs(q0 - q1).max() > 0
+
+
+def test_per_instance_weight_and_errors(cpu_extend):
+    form = cases.formulate_biped(cases.default_configuration(), backend=NumpyBackend())
+    form.incorporate_goal("extra", Cost("CoM", Param("w_extra"), aim=[0.0, 0.0], axes=["_x", "_y"]))
+    given = np.zeros([2, form.given_len])
+    out = form.generate_all_qp_matrices_batched(given, {"w_extra": np.array([0.0, 2.0])})
+    base = cases.formulate_biped(cases.default_configuration(), backend=NumpyBackend())
+    ref = base.generate_all_qp_matrices_batched(given[:1])
+    assert cases.rel_err(out.P[0], ref.P[0]) < 1e-14
+    assert np.abs(out.P[1] - ref.P[0]).max() > 0
+    with pytest.raises(KeyError):
+        form.generate_all_qp_matrices_batched(given, {})
+    with pytest.raises(ValueError):  # multi-row aims do not work in the reference either
+        bad = cases.formulate_biped(cases.default_configuration(), backend=NumpyBackend())
+        bad.goals["track vel_x"].update(aim=np.ones([3, 1]))
+        bad.generate_all_qp_matrices(np.zeros([bad.given_len, 1]))
