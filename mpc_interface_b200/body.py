@@ -235,7 +235,7 @@ class Formulation:
     def _run(self, given, params, costs=None, limits=None, out=None):
         """Evaluates a (sub)plan for a batch: given [B, ng], params {name: [B]}."""
         compiled = self._compiled(costs, limits)
-        if not hasattr(given, "device"):
+        if isinstance(given, (np.ndarray, list, tuple)):  # anything else: a device tensor
             given = np.asarray(given, dtype=np.float64)
         batch = given.shape[0]
         scalars = compiled.slots.evaluate(params or {}, batch)

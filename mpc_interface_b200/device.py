@@ -321,9 +321,9 @@ class DeviceBackend:
     def assemble(self, plan, scalars, given, batch, out=None):
         torch = self.torch
         dp = self.device_plan(plan)
-        if not hasattr(scalars, "device"):
+        if not torch.is_tensor(scalars):
             scalars = torch.from_numpy(np.ascontiguousarray(scalars, dtype=np.float64)).to(self.device)
-        if not hasattr(given, "device"):
+        if not torch.is_tensor(given):
             given = torch.from_numpy(np.ascontiguousarray(given, dtype=np.float64)).to(self.device)
         scalars = scalars.contiguous()
         given = given.contiguous().reshape(batch, plan.ng)
