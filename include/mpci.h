@@ -128,6 +128,62 @@ int mpci_assemble_host(mpci_plan* plan, const double* scalars_host, const double
 /* Number of kernel launches one mpci_assemble call issues for this plan.    */
 int mpci_assemble_launches(const mpci_plan* plan);
 
+/* ---- per-instance dynamics: the condensed LTI problem ---------------------
+ * Mode B of DESIGN.md: every instance b has its own x+ = A_b x + B_b u, so the
+ * prediction matrices (tools.py:14-33), the Hessian contraction
+ * sum_c w_c Vo^T Co (body.py:292), the gradient (body.py:293-300) and the
+ * constraint rows (body.py:236-264) are all computed per instance by one fused
+ * kernel.  The formulation is lowered (mpc_interface_b200/lti.py) to stage
+ * tables over the n states z_i and m inputs u_j of the plant:
+ *   Qxx [n][n], Quu [m][m]   sum over costs of w * (variable form) x (cross form)
+ *   Tx  [n][n_scalars + 1]   (w/2)(cv*caim + cc*aim) as an affine map of the
+ *   Tu  [m][n_scalars + 1]    per-instance scalars (last column = constant)
+ *   groups: limit g has N rows  arrow[k] * (cx . x_{k+1} + cu . u_k) <= bound[k]
+ * Optimisation vector: input-major, z = [u_0(0..N-1), u_1(0..N-1), ...] (the
+ * reference's optim_ID order for such a formulation); given = x0.
+ *   P[(j,p),(j',p')] = sum_{k>=max(p,p')} Gam_{k-p}[:,j]^T Qxx Gam_{k-p'}[:,j'] + Quu[j][j'] d_pp'
+ *   q[(j,p)]         = sum_{k>=p} Gam_{k-p}[:,j]^T (sym(Qxx) A^{k+1} x0 - tx) - tu[j]
+ *   G[g*N+k,(j,p)]   = arrow[k] * (cx . Gam_{k-p}[:,j] [p<=k] + cu[j] [p==k])
+ *   h[g*N+k]         = bound[k] - arrow[k] * cx . A^{k+1} x0
+ * with Gam_d = A^d B.  All tables are host pointers, copied at creation.      */
+typedef struct {
+  int n, m, N;
+  int n_scalars;           /* columns of Tx/Tu minus one (may be 0)           */
+  int n_groups;            /* nc = n_groups * N                               */
+  const double* Qxx;       /* [n][n]                                          */
+  const double* Quu;       /* [m][m]                                          */
+  const double* Tx;        /* [n][n_scalars + 1]                              */
+  const double* Tu;        /* [m][n_scalars + 1]                              */
+  const double* grp_cx;    /* [n_groups][n]                                   */
+  const double* grp_cu;    /* [n_groups][m]                                   */
+  const double* grp_arrow; /* [n_groups][N]                                   */
+  const double* grp_bound; /* [n_groups][N]                                   */
+} mpci_lti_desc;
+
+typedef struct mpci_lti_plan mpci_lti_plan;
+
+int mpci_lti_plan_create(const mpci_lti_desc* desc, mpci_lti_plan** plan_out);
+int mpci_lti_plan_destroy(mpci_lti_plan* plan);
+
+/* hessian_mode: 0 = dense contraction on the FP64 tensor cores (DMMA) with
+ * block-triangular skipping; 1 = displacement recursion
+ * P[p,p'] = P[p+1,p'+1] + Gam_{N-1-p}^T Qxx Gam_{N-1-p'} (O(N^2) flops).     */
+#define MPCI_LTI_HESSIAN_DMMA 0
+#define MPCI_LTI_HESSIAN_RECURSION 1
+
+/* A_dev [batch][n][n] (strideA = n*n) or one shared matrix (strideA = 0);
+ * B_dev likewise ([n][m]); x0_dev [batch][n]; scalars_dev [batch][n_scalars]
+ * (may be NULL when n_scalars == 0).  Outputs as in mpci_assemble with
+ * nv = m*N, nc = n_groups*N; any output may be NULL.                          */
+int mpci_lti_assemble(const mpci_lti_plan* plan, const double* A_dev, long strideA,
+                      const double* B_dev, long strideB, const double* x0_dev,
+                      const double* scalars_dev, double* P_dev, double* q_dev, double* G_dev,
+                      double* h_dev, long batch, int hessian_mode, void* stream);
+
+/* Flops the Hessian phase of one instance executes in `hessian_mode`
+ * (for the FP64 roofline; the structural count is SURVEY.md 8(d)).            */
+double mpci_lti_hessian_flops(const mpci_lti_plan* plan, int hessian_mode);
+
 #ifdef __cplusplus
 }
 #endif

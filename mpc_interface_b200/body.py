@@ -321,13 +321,45 @@ class Formulation:
         """Names of the per-instance Param values the compiled plan needs."""
         return self._compiled().slots.names()
 
-    def generate_all_qp_matrices_batched(self, given, params=None, out=None):
+    def generate_all_qp_matrices_batched(self, given, params=None, out=None, dynamics=None,
+                                         hessian="dmma"):
         """Assembles a whole batch.
 
-        given  : [B, given_len] float64 (numpy, or a CUDA torch tensor)
-        params : {name: [B] array} for every ``Param`` used in the formulation
-        out    : optional ``QPBatch`` to overwrite (ring-buffer slot)
+        given    : [B, given_len] float64 (numpy, or a CUDA torch tensor)
+        params   : {name: [B] array} for every ``Param`` used in the formulation
+        out      : optional ``QPBatch`` to overwrite (ring-buffer slot)
+        dynamics : ``{name: (A, B)}`` with ``A [B,n,n]``, ``B [B,n,m]`` -- one plant
+                   per instance replacing the matrices the dynamics ``name`` was
+                   built with (the formulation then only fixes the structure);
+                   everything, prediction matrices included, is computed per
+                   instance by the fused kernel of csrc/mpci_lti.cu (lti.py).
+        hessian  : with ``dynamics``: "dmma" (dense contraction on the FP64 tensor
+                   cores) or "recursion" (displacement recursion, O(N^2) flops)
 
         Returns a ``QPBatch`` with device tensors ``P [B,nv,nv]``, ``q [B,nv]``,
         ``G [B,nc,nv]``, ``h [B,nc]`` (row-major, unpadded)."""
-        return self._run(given, params, out=out)
+        if dynamics is None:
+            return self._run(given, params, out=out)
+        from . import lti
+
+        if len(dynamics) != 1:
+            raise NotImplementedError("exactly one dynamics can vary per instance")
+        (name, (A, B)), = dynamics.items()
+        if name not in self.dynamics:
+            raise KeyError("no dynamics named '{}' was incorporated".format(name))
+        modes = {"dmma": lti.HESSIAN_DMMA, "recursion": lti.HESSIAN_RECURSION}
+        if hessian not in modes:
+            raise ValueError("hessian must be 'dmma' or 'recursion'")
+        return lti.assemble(self.lti_plan(name), A, B, given, params, out, modes[hessian])
+
+    def lti_plan(self, name):
+        """The condensed LTI plan of this formulation with ``name`` as the
+        per-instance plant (cached until the formulation changes)."""
+        from . import lti
+
+        key = ("lti", name) + self._signature(
+            list(self.goals.values()), _plan.ordered_limits(self)
+        )
+        if key not in self._plans:
+            self._plans[key] = lti.lower(self, name)
+        return self._plans[key]

@@ -1,0 +1,529 @@
+// Per-instance dynamics: the whole condensed LTI QP of one instance in one CTA.
+//
+// Mode B of DESIGN.md.  Reference path, per instance: tools.extend_matrices
+// (python/mpc_interface/tools.py:14-33), Formulation.make_preview_matrices
+// (body.py:149-193), generate_qp_cost (body.py:266-302) for every cost and
+// generate_qp_constraint (body.py:236-264) for every limit -- for a formulation
+// whose variables are point-wise linear forms of the plant's states and inputs
+// (lowered to stage tables by mpc_interface_b200/lti.py, see include/mpci.h).
+//
+// Phases of one instance (everything below lives in shared memory):
+//   1. Gam'_d = A^d [B | x0], d = 0..N, by parallel prefix doubling
+//   2. gz/wz: zero-padded Toeplitz generators Gam and W = Qxx Gam;  r_k
+//   3. P   -- FP64 tensor cores (DMMA.8x8x4) with block-triangular skipping, or
+//             the displacement recursion (O(N^2) flops)
+//   4. q   -- correlation of Gam with r
+//   5. G,h -- generated row by row, 16-byte coalesced stores
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "mpci_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kPadL = 40;  // zeros before d = 0 of every generator (>= 8*max(TM,TN)+3)
+constexpr int kPadR = 8;   // zeros after d = N-1
+constexpr int TM = 2, TN = 4;  // 8x8 DMMA tiles per warp tile (rows x cols)
+
+struct LtiArgs {
+  int n, m, N, S, n_groups;
+  int Nk;  // N rounded up to a multiple of 4
+  int LD;  // kPadL + Nk + kPadR
+  const double *Qxx, *Quu, *Tx, *Tu, *cx, *cu, *arrow, *bound;  // device tables
+  const int* grp_state;  // 1 if the group has a non-zero cx
+  const double *A, *B, *x0, *scalars;
+  long strideA, strideB;
+  double *P, *q, *G, *h;
+  long batch;
+  int hessian_mode;
+};
+
+struct Smem {
+  double *A, *M0, *M1, *Q, *gp, *gz, *wz, *r, *tx, *tu, *cg;
+};
+
+__host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD) {
+  return (size_t)4 * n * n + (size_t)(N + 1) * n * (m + 1) + (size_t)2 * n * m * LD +
+         (size_t)n * N + n + m + (size_t)m * (N + 2);
+}
+
+__device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
+  Smem s;
+  const int n = a.n, m = a.m, N = a.N;
+  s.A = base;
+  s.M0 = s.A + n * n;
+  s.M1 = s.M0 + n * n;
+  s.Q = s.M1 + n * n;
+  s.gp = s.Q + n * n;
+  s.gz = s.gp + (size_t)(N + 1) * n * (m + 1);
+  s.wz = s.gz + (size_t)n * m * a.LD;
+  s.r = s.wz + (size_t)n * m * a.LD;
+  s.tx = s.r + (size_t)n * N;
+  s.tu = s.tx + n;
+  s.cg = s.tu + m;
+  return s;
+}
+
+__device__ __forceinline__ void dmma8x8x4(double& d0, double& d1, double a, double b) {
+  asm volatile(
+      "mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+      : "+d"(d0), "+d"(d1)
+      : "d"(a), "d"(b));
+}
+
+// ---------------------------------------------------------------------------
+// phase 1 + 2: prediction data of instance b
+// ---------------------------------------------------------------------------
+__device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
+  const int n = a.n, m = a.m, N = a.N, w = a.m + 1, tid = threadIdx.x;
+  const double* Ab = a.A + b * a.strideA;
+  const double* Bb = a.B + b * a.strideB;
+  const double* xb = a.x0 + b * n;
+  for (int e = tid; e < n * n; e += kThreads) {
+    const double v = Ab[e];
+    s.A[e] = v;
+    s.M0[e] = v;
+    s.Q[e] = a.Qxx[e];
+  }
+  for (int e = tid; e < n * w; e += kThreads) {
+    const int i = e / w, c = e % w;
+    s.gp[e] = (c < m) ? Bb[i * m + c] : xb[i];
+  }
+  // per-instance offsets of the gradient: t = T[:, S] + T[:, :S] @ scalars_b
+  for (int e = tid; e < n + m; e += kThreads) {
+    const double* T = (e < n) ? a.Tx + (long)e * (a.S + 1) : a.Tu + (long)(e - n) * (a.S + 1);
+    double acc = T[a.S];
+    for (int k = 0; k < a.S; ++k) acc = fma(T[k], a.scalars[b * a.S + k], acc);
+    if (e < n) s.tx[e] = acc; else s.tu[e - n] = acc;
+  }
+  __syncthreads();
+
+  // prefix doubling: Gam'_{have+d} = A^have Gam'_d,  A^(2 have) = (A^have)^2
+  double* M0 = s.M0;
+  double* M1 = s.M1;
+  const int blk = n * w;
+  for (int have = 1; have < N + 1;) {
+    const int cnt = min(have, N + 1 - have);
+    const int total = cnt * blk;
+    for (int e = tid; e < total + n * n; e += kThreads) {
+      if (e < total) {
+        const int d = e / blk, rem = e % blk, i = rem / w, c = rem % w;
+        const double* src = s.gp + (size_t)d * blk + c;
+        double acc = 0.0;
+        for (int l = 0; l < n; ++l) acc = fma(M0[i * n + l], src[l * w], acc);
+        s.gp[(size_t)(have + d) * blk + rem] = acc;
+      } else {
+        const int e2 = e - total, i = e2 / n, c = e2 % n;
+        double acc = 0.0;
+        for (int l = 0; l < n; ++l) acc = fma(M0[i * n + l], M0[l * n + c], acc);
+        M1[e2] = acc;
+      }
+    }
+    __syncthreads();
+    double* t = M0; M0 = M1; M1 = t;
+    have += cnt;
+  }
+
+  // zero-padded generators: gz[i][j][kPadL + d] = Gam_d[i][j], wz = (Qxx Gam_d)[i][j]
+  const int LD = a.LD;
+  for (int e = tid; e < n * m * LD; e += kThreads) {
+    const int x = e % LD, ij = e / LD, i = ij / m, j = ij % m;
+    const int d = x - kPadL;
+    double g = 0.0, wv = 0.0;
+    if (d >= 0 && d < N) {
+      const double* src = s.gp + (size_t)d * blk + j;
+      g = src[i * w];
+      for (int l = 0; l < n; ++l) wv = fma(s.Q[i * n + l], src[l * w], wv);
+    }
+    s.gz[e] = g;
+    s.wz[e] = wv;
+  }
+  // r[i][k] = sum_l sym(Qxx)[i][l] f_k[l] - tx[i],  f_k = Gam'_{k+1}[:, m]
+  for (int e = tid; e < n * N; e += kThreads) {
+    const int i = e / N, k = e % N;
+    const double* f = s.gp + (size_t)(k + 1) * blk + m;
+    double acc = -s.tx[i];
+    for (int l = 0; l < n; ++l)
+      acc = fma(0.5 * (s.Q[i * n + l] + s.Q[l * n + i]), f[l * w], acc);
+    s.r[e] = acc;
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------------------
+// phase 3a: P by the dense contraction on the FP64 tensor cores
+//   C[(j,p)][(j',p')] = sum_i sum_k gz[i][j][k-p] * wz[i][j'][k-p']
+// A warp owns (8 TM) x (8 TN) entries of one (j, j') block.  The DMMA operand
+// of lane (g = lane/4, t = lane%4) is one LDS.64: gz[..][k0 + t - p0 - g] --
+// 11 consecutive words per warp, so there are no bank conflicts; the zero
+// padding before d = 0 encodes causality (k >= p) without a branch.
+// ---------------------------------------------------------------------------
+__device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int np8 = (N + 7) / 8;
+  const int RT = (np8 + TM - 1) / TM, CT = (np8 + TN - 1) / TN;
+  const int tiles = m * m * RT * CT;
+  const bool vec_ok = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0);
+
+  for (int tile = warp; tile < tiles; tile += kWarps) {
+    // long k-loops (small p0, p0') first within every (j, j') block
+    const int ct = tile % CT, rt = (tile / CT) % RT, jj = tile / (CT * RT);
+    const int j = jj / m, jp = jj % m;
+    const int p0 = rt * 8 * TM, q0 = ct * 8 * TN;
+    // k runs downwards from N-1 in steps of 4 (lane t takes k = N-1-s0-t) until
+    // it passes max(p0, q0): below that every product has a factor with d < 0
+    const int span = N - max(p0, q0);
+    double acc[TM][TN][2];
+#pragma unroll
+    for (int x = 0; x < TM; ++x)
+#pragma unroll
+      for (int y = 0; y < TN; ++y) acc[x][y][0] = acc[x][y][1] = 0.0;
+
+    for (int i = 0; i < n; ++i) {
+      const double* ga = s.gz + (size_t)(i * m + j) * LD + kPadL + (N - 1 - t - p0 - g);
+      const double* wb = s.wz + (size_t)(i * m + jp) * LD + kPadL + (N - 1 - t - q0 - g);
+#pragma unroll 2
+      for (int s0 = 0; s0 < span; s0 += 4) {
+        double av[TM], bv[TN];
+#pragma unroll
+        for (int x = 0; x < TM; ++x) av[x] = ga[-s0 - 8 * x];
+#pragma unroll
+        for (int y = 0; y < TN; ++y) bv[y] = wb[-s0 - 8 * y];
+#pragma unroll
+        for (int x = 0; x < TM; ++x)
+#pragma unroll
+          for (int y = 0; y < TN; ++y) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
+      }
+    }
+    // epilogue: + Quu[j][j'] on the diagonal of the block, store
+    const double ruu = a.Quu[j * m + jp];
+#pragma unroll
+    for (int x = 0; x < TM; ++x) {
+      const int p = p0 + 8 * x + g;
+      if (p >= N) continue;
+      double* row = Pb + (size_t)(j * N + p) * nv + (size_t)jp * N;
+#pragma unroll
+      for (int y = 0; y < TN; ++y) {
+        const int c = q0 + 8 * y + 2 * t;
+        if (c >= N) continue;
+        double v0 = acc[x][y][0], v1 = acc[x][y][1];
+        if (c == p) v0 += ruu;
+        if (c + 1 == p) v1 += ruu;
+        if (vec_ok && c + 1 < N) {
+          __stcs(reinterpret_cast<double2*>(row + c), make_double2(v0, v1));
+        } else {
+          __stcs(row + c, v0);
+          if (c + 1 < N) __stcs(row + c + 1, v1);
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// phase 3b: P by the displacement recursion
+//   H[p][p'] = H[p+1][p'+1] + Gam_{N-1-p}^T W_{N-1-p'}    (per (j, j') block)
+// A thread owns one diagonal delta = p' - p of all m x m blocks and walks the
+// rows from p = N-1 up to 0, so that a warp writes consecutive p' of one row.
+// ---------------------------------------------------------------------------
+template <int M>
+__device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
+  const int n = a.n, N = a.N, LD = a.LD, nv = M * a.N;
+  for (int dl = threadIdx.x; dl < 2 * N - 1; dl += kThreads) {
+    const int delta = dl - (N - 1);
+    double acc[M][M];
+#pragma unroll
+    for (int x = 0; x < M; ++x)
+#pragma unroll
+      for (int y = 0; y < M; ++y) acc[x][y] = 0.0;
+    const int p_hi = min(N - 1, N - 1 - delta), p_lo = max(0, -delta);
+    for (int p = p_hi; p >= p_lo; --p) {
+      const int c = p + delta;
+      const double* ga = s.gz + kPadL + (N - 1 - p);
+      const double* wb = s.wz + kPadL + (N - 1 - c);
+      for (int i = 0; i < n; ++i) {
+        double gv[M], wv[M];
+#pragma unroll
+        for (int x = 0; x < M; ++x) gv[x] = ga[(size_t)(i * M + x) * LD];
+#pragma unroll
+        for (int y = 0; y < M; ++y) wv[y] = wb[(size_t)(i * M + y) * LD];
+#pragma unroll
+        for (int x = 0; x < M; ++x)
+#pragma unroll
+          for (int y = 0; y < M; ++y) acc[x][y] = fma(gv[x], wv[y], acc[x][y]);
+      }
+#pragma unroll
+      for (int x = 0; x < M; ++x)
+#pragma unroll
+        for (int y = 0; y < M; ++y) {
+          double v = acc[x][y];
+          if (delta == 0) v += a.Quu[x * M + y];
+          __stcs(Pb + (size_t)(x * N + p) * nv + (size_t)y * N + c, v);
+        }
+    }
+  }
+}
+
+// general m: one (j, j') block at a time
+__device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
+  const int diag = 2 * N - 1;
+  for (int e = threadIdx.x; e < m * m * diag; e += kThreads) {
+    const int dl = e % diag, jj = e / diag, j = jj / m, jp = jj % m;
+    const int delta = dl - (N - 1);
+    const int p_hi = min(N - 1, N - 1 - delta), p_lo = max(0, -delta);
+    const double ruu = (delta == 0) ? a.Quu[j * m + jp] : 0.0;
+    double acc = 0.0;
+    for (int p = p_hi; p >= p_lo; --p) {
+      const int c = p + delta;
+      for (int i = 0; i < n; ++i)
+        acc = fma(s.gz[(size_t)(i * m + j) * LD + kPadL + (N - 1 - p)],
+                  s.wz[(size_t)(i * m + jp) * LD + kPadL + (N - 1 - c)], acc);
+      __stcs(Pb + (size_t)(j * N + p) * nv + (size_t)jp * N + c, acc + ruu);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// phase 4: q[(j,p)] = sum_{d>=0} Gam_d[:,j] . r_{p+d} - tu[j]
+// ---------------------------------------------------------------------------
+__device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ qb) {
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD;
+  for (int e = threadIdx.x; e < m * N; e += kThreads) {
+    const int j = e / N, p = e % N;
+    double acc = 0.0;
+    for (int i = 0; i < n; ++i) {
+      const double* gam = s.gz + (size_t)(i * m + j) * LD + kPadL;
+      const double* r = s.r + (size_t)i * N + p;
+      for (int d = 0; d < N - p; ++d) acc = fma(gam[d], r[d], acc);
+    }
+    qb[e] = acc - s.tu[j];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// phase 5: constraint rows.  Group g, row k, column (j, p):
+//   G = arrow[k] * ((p <= k ? (cx . Gam_{k-p})[j] : 0) + (p == k ? cu[j] : 0))
+//   h = bound[k] - arrow[k] * cx . f_k
+// A warp writes one row at a time, a lane two consecutive doubles (16 bytes).
+// ---------------------------------------------------------------------------
+__device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restrict__ Gb,
+                                double* __restrict__ hb) {
+  const int n = a.n, m = a.m, N = a.N, w = a.m + 1, nv = a.m * a.N, tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int blk = n * w;
+  const int cgld = N + 2;
+  const bool vec_ok = (nv % 2 == 0) && (N % 2 == 0) && Gb &&
+                      ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0);
+  for (int grp = 0; grp < a.n_groups; ++grp) {
+    const double* cx = a.cx + (size_t)grp * n;
+    const double* cu = a.cu + (size_t)grp * m;
+    const double* arrow = a.arrow + (size_t)grp * N;
+    const bool state = a.grp_state[grp] != 0;
+    __syncthreads();  // cg of the previous group is no longer read
+    if (state) {
+      // cg[j][d] = sum_i cx[i] Gam_d[i][j]
+      for (int e = tid; e < m * N; e += kThreads) {
+        const int j = e / N, d = e % N;
+        const double* src = s.gp + (size_t)d * blk + j;
+        double acc = 0.0;
+        for (int i = 0; i < n; ++i) acc = fma(cx[i], src[i * w], acc);
+        s.cg[j * cgld + d] = acc;
+      }
+      __syncthreads();
+    }
+    if (hb) {
+      for (int k = tid; k < N; k += kThreads) {
+        double acc = 0.0;
+        if (state) {
+          const double* f = s.gp + (size_t)(k + 1) * blk + m;
+          for (int i = 0; i < n; ++i) acc = fma(cx[i], f[i * w], acc);
+        }
+        hb[(size_t)grp * N + k] = a.bound[(size_t)grp * N + k] - arrow[k] * acc;
+      }
+    }
+    if (!Gb) continue;
+    for (int k = warp; k < N; k += kWarps) {
+      const double ak = arrow[k];
+      double* row = Gb + ((size_t)grp * N + k) * nv;
+      if (vec_ok) {
+        for (int c = 2 * lane; c < nv; c += 64) {  // c and c+1 share j because N is even
+          const int j = c / N, p = c % N;
+          double v0 = 0.0, v1 = 0.0;
+          if (state) {
+            if (p <= k) v0 = s.cg[j * cgld + (k - p)];
+            if (p + 1 <= k) v1 = s.cg[j * cgld + (k - p - 1)];
+          }
+          if (p == k) v0 += cu[j];
+          if (p + 1 == k) v1 += cu[j];
+          __stcs(reinterpret_cast<double2*>(row + c), make_double2(ak * v0, ak * v1));
+        }
+      } else {
+        for (int c = lane; c < nv; c += 32) {
+          const int j = c / N, p = c % N;
+          double v = 0.0;
+          if (state && p <= k) v = s.cg[j * cgld + (k - p)];
+          if (p == k) v += cu[j];
+          __stcs(row + c, ak * v);
+        }
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+lti_assemble_kernel(LtiArgs a) {
+  extern __shared__ double lti_smem[];
+  const Smem s = carve(lti_smem, a);
+  const size_t nv = (size_t)a.m * a.N, nc = (size_t)a.n_groups * a.N;
+  for (long b = blockIdx.x; b < a.batch; b += gridDim.x) {
+    __syncthreads();  // the previous instance is done with shared memory
+    build_prediction(a, s, b);
+    if (a.P) {
+      double* Pb = a.P + (size_t)b * nv * nv;
+      if (a.hessian_mode == MPCI_LTI_HESSIAN_DMMA) hessian_dmma(a, s, Pb);
+      else if (a.m == 1) hessian_recursion<1>(a, s, Pb);
+      else if (a.m == 2) hessian_recursion<2>(a, s, Pb);
+      else if (a.m == 3) hessian_recursion<3>(a, s, Pb);
+      else if (a.m == 4) hessian_recursion<4>(a, s, Pb);
+      else hessian_recursion_any(a, s, Pb);
+    }
+    if (a.q) gradient(a, s, a.q + (size_t)b * nv);
+    if ((a.G || a.h) && a.n_groups)
+      constraint_rows(a, s, a.G ? a.G + (size_t)b * nc * nv : nullptr,
+                      a.h ? a.h + (size_t)b * nc : nullptr);
+  }
+}
+
+}  // namespace
+
+struct mpci_lti_plan {
+  int n, m, N, S, n_groups;
+  void* dev;  // one allocation holding every table
+  LtiArgs args;  // table pointers and sizes filled in, per-call fields zero
+  size_t smem_bytes;
+  int blocks_per_sm;
+};
+
+extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out) {
+  if (!d || !out) return mpci::fail(-3, "lti_plan_create: NULL argument");
+  *out = nullptr;
+  if (d->n < 1 || d->m < 1 || d->N < 1 || d->n_scalars < 0 || d->n_groups < 0)
+    return mpci::fail(-1, "lti_plan_create: bad sizes n=%d m=%d N=%d scalars=%d groups=%d", d->n,
+                      d->m, d->N, d->n_scalars, d->n_groups);
+  if (!d->Qxx || !d->Quu || !d->Tx || !d->Tu ||
+      (d->n_groups && (!d->grp_cx || !d->grp_cu || !d->grp_arrow || !d->grp_bound)))
+    return mpci::fail(-3, "lti_plan_create: NULL table");
+  const int n = d->n, m = d->m, N = d->N, S = d->n_scalars, G = d->n_groups;
+  const int Nk = (N + 3) / 4 * 4, LD = kPadL + Nk + kPadR;
+  const size_t smem = sizeof(double) * lti_smem_doubles(n, m, N, LD);
+  if (smem > 227 * 1024)
+    return mpci::fail(-8, "lti_plan_create: n=%d m=%d N=%d needs %zu bytes of shared memory "
+                      "(limit 232448)", n, m, N, smem);
+  // pack the tables: Qxx | Quu | Tx | Tu | cx | cu | arrow | bound | flags(int)
+  std::vector<double> host;
+  auto push = [&](const double* p, size_t count) {
+    const size_t off = host.size();
+    host.insert(host.end(), p, p + count);
+    return off;
+  };
+  const size_t oQ = push(d->Qxx, (size_t)n * n), oR = push(d->Quu, (size_t)m * m);
+  const size_t oTx = push(d->Tx, (size_t)n * (S + 1)), oTu = push(d->Tu, (size_t)m * (S + 1));
+  size_t ocx = 0, ocu = 0, oar = 0, obd = 0;
+  if (G) {
+    ocx = push(d->grp_cx, (size_t)G * n);
+    ocu = push(d->grp_cu, (size_t)G * m);
+    oar = push(d->grp_arrow, (size_t)G * N);
+    obd = push(d->grp_bound, (size_t)G * N);
+  }
+  std::vector<int> flags(G > 0 ? G : 1, 0);
+  for (int g = 0; g < G; ++g)
+    for (int i = 0; i < n; ++i)
+      if (d->grp_cx[(size_t)g * n + i] != 0.0) flags[g] = 1;
+  mpci_lti_plan* p = new mpci_lti_plan();
+  std::memset(p, 0, sizeof(*p));
+  const size_t bytes_d = host.size() * sizeof(double), bytes_i = flags.size() * sizeof(int);
+  cudaError_t e = cudaMalloc(&p->dev, bytes_d + bytes_i);
+  if (e == cudaSuccess) e = cudaMemcpy(p->dev, host.data(), bytes_d, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess)
+    e = cudaMemcpy(static_cast<char*>(p->dev) + bytes_d, flags.data(), bytes_i,
+                   cudaMemcpyHostToDevice);
+  if (e == cudaSuccess)  // the largest opt-in size: plans of different sizes share the kernel
+    e = cudaFuncSetAttribute(lti_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             227 * 1024);
+  int per_sm = 0;
+  if (e == cudaSuccess)
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lti_assemble_kernel, kThreads, smem);
+  if (e != cudaSuccess) {
+    int rc = mpci::cuda_fail(e, "lti_plan_create");
+    if (p->dev) cudaFree(p->dev);
+    delete p;
+    return rc;
+  }
+  const double* base = static_cast<const double*>(p->dev);
+  p->n = n; p->m = m; p->N = N; p->S = S; p->n_groups = G;
+  LtiArgs& a = p->args;
+  a.n = n; a.m = m; a.N = N; a.S = S; a.n_groups = G; a.Nk = Nk; a.LD = LD;
+  a.Qxx = base + oQ; a.Quu = base + oR; a.Tx = base + oTx; a.Tu = base + oTu;
+  a.cx = base + ocx; a.cu = base + ocu; a.arrow = base + oar; a.bound = base + obd;
+  a.grp_state = reinterpret_cast<const int*>(static_cast<const char*>(p->dev) + bytes_d);
+  p->smem_bytes = smem;
+  p->blocks_per_sm = per_sm < 1 ? 1 : per_sm;
+  *out = p;
+  return 0;
+}
+
+extern "C" int mpci_lti_plan_destroy(mpci_lti_plan* p) {
+  if (!p) return 0;
+  if (p->dev) cudaFree(p->dev);
+  delete p;
+  return 0;
+}
+
+extern "C" double mpci_lti_hessian_flops(const mpci_lti_plan* p, int mode) {
+  if (!p) return 0.0;
+  const double n = p->n, m = p->m, N = p->N;
+  if (mode == MPCI_LTI_HESSIAN_RECURSION) return 2.0 * n * m * m * N * N + 2.0 * n * n * m * N;
+  // executed by hessian_dmma: per warp tile n * (Nk - kstart)/4 steps of TM*TN DMMAs (512 flop)
+  const int np8 = (p->N + 7) / 8, RT = (np8 + TM - 1) / TM, CT = (np8 + TN - 1) / TN;
+  double steps = 0.0;
+  for (int rt = 0; rt < RT; ++rt)
+    for (int ct = 0; ct < CT; ++ct) {
+      const int p0 = rt * 8 * TM, q0 = ct * 8 * TN;
+      steps += (p->N - (p0 > q0 ? p0 : q0) + 3) / 4;
+    }
+  return steps * n * m * m * TM * TN * 512.0 + 2.0 * n * n * m * N;
+}
+
+extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long strideA,
+                                 const double* B, long strideB, const double* x0,
+                                 const double* scalars, double* P, double* q, double* G,
+                                 double* h, long batch, int mode, void* stream) {
+  if (!p) return mpci::fail(-3, "lti_assemble: NULL plan");
+  if (batch < 0) return mpci::fail(-1, "lti_assemble: negative batch");
+  if (batch == 0) return 0;
+  if (!A || !B || !x0) return mpci::fail(-3, "lti_assemble: NULL A, B or x0");
+  if (p->S > 0 && !scalars) return mpci::fail(-3, "lti_assemble: NULL scalars");
+  if (mode != MPCI_LTI_HESSIAN_DMMA && mode != MPCI_LTI_HESSIAN_RECURSION)
+    return mpci::fail(-1, "lti_assemble: unknown hessian_mode %d", mode);
+  if ((strideA != 0 && strideA < (long)p->n * p->n) || (strideB != 0 && strideB < (long)p->n * p->m))
+    return mpci::fail(-4, "lti_assemble: instance strides smaller than the matrices");
+  LtiArgs a = p->args;
+  a.A = A; a.B = B; a.x0 = x0; a.scalars = scalars; a.strideA = strideA; a.strideB = strideB;
+  a.P = P; a.q = q; a.G = G; a.h = h; a.batch = batch; a.hessian_mode = mode;
+  int dev = 0, sms = 148;
+  MPCI_CUDA(cudaGetDevice(&dev));
+  MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  MPCI_CUDA(cudaFuncSetAttribute(lti_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 227 * 1024));  // per device: the plan may be used on another GPU
+  const long resident = (long)sms * p->blocks_per_sm;
+  const unsigned grid = (unsigned)(batch < resident ? batch : resident);
+  lti_assemble_kernel<<<grid, kThreads, p->smem_bytes, mpci::as_stream(stream)>>>(a);
+  MPCI_LAUNCH_CHECK("lti_assemble_kernel");
+  return 0;
+}

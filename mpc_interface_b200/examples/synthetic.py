@@ -57,6 +57,15 @@ def generic_system(seed, nx, nu):
     return A, B, Q, R
 
 
+def generic_plants(seed, batch, nx, nu):
+    """Per-instance plants (A_b, B_b) of the generic configurations in
+    per-instance mode: the same distribution as ``generic_system``."""
+    rng = np.random.default_rng(seed + 13)
+    A = np.eye(nx) + 0.05 * rng.normal(size=[batch, nx, nx])
+    B = 0.1 * rng.normal(size=[batch, nx, nu])
+    return A, B
+
+
 def generic_inputs(seed, batch, nx):
     rng = np.random.default_rng(seed + 7)
     return {"x0": rng.normal(size=[batch, nx]), "ref": rng.normal(size=[batch, nx])}

@@ -206,7 +206,28 @@ def generic_case(name, seed, nx, nu, N, n_rows, batch):
          A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs), N=N, **layout(form))
 
 
+def generic_per_instance(name, seed, nx, nu, N, n_rows, batch):
+    """Every instance has its own plant (A_b, B_b): mode B of DESIGN.md."""
+    _, _, Q, R = synthetic.generic_system(seed, nx, nu)
+    A, B = synthetic.generic_plants(seed, batch, nx, nu)
+    rows = np.random.default_rng(seed + 1).normal(size=[n_rows, nx])
+    vals = synthetic.generic_inputs(seed, batch, nx)
+    As, hs, Qs, qs = [], [], [], []
+    for b in range(batch):
+        form = formulate_generic(A[b], B[b], Q, R, N, rows, refs=list(vals["ref"][b]), api=RefAPI)
+        given = form.arrange_given({"x0": vals["x0"][b][:, None]})
+        Am, h, Qm, q = form.generate_all_qp_matrices(given)
+        As.append(Am), hs.append(h[:, 0]), Qs.append(Qm), qs.append(q[:, 0])
+    save(name, seed=seed, A_sys=A, B_sys=B, Q_w=Q, R_w=R, rows=rows, x0=vals["x0"], ref=vals["ref"],
+         A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs), N=N, **layout(form))
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["per_instance"]:
+        generic_per_instance("generic_perinst_small.npz", 31, 4, 2, 10, 2, 4)
+        generic_per_instance("generic_perinst_odd.npz", 32, 3, 3, 7, 1, 3)
+        generic_per_instance("generic_perinst_mid.npz", 33, 6, 2, 40, 2, 2)
+        sys.exit(0)
     lip_pickle()
     extend_cases()
     biped_c1()

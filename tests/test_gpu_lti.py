@@ -1,0 +1,118 @@
+"""Parity of the per-instance-dynamics kernel (mpci_lti_assemble, through the
+C ABI) with the reference's golden vectors and with the oracle.
+
+Tolerance: relative error <= 1e-10 per array (cases.TOL), normwise."""
+import numpy as np
+import pytest
+
+import _cases as cases
+from oracle import qp_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from mpc_interface_b200 import device
+
+    device.require_gpu()
+    return device
+
+
+def _form(g, per_instance):
+    from mpc_interface_b200 import Param
+
+    nx = g["Q_w"].shape[0]
+    refs = [Param("ref%d" % i) for i in range(nx)]
+    A0 = g["A_sys"][0] if per_instance else g["A_sys"]
+    B0 = g["B_sys"][0] if per_instance else g["B_sys"]
+    form = cases.formulate_generic(A0, B0, g["Q_w"], g["R_w"], int(g["N"]), g["rows"], refs=refs)
+    params = {"ref%d" % i: g["ref"][:, i] for i in range(nx)}
+    return form, params
+
+
+@pytest.mark.parametrize("hessian", ["dmma", "recursion"])
+@pytest.mark.parametrize("name,per_instance", [
+    ("generic_perinst_small", True), ("generic_perinst_odd", True), ("generic_perinst_mid", True),
+    ("generic_small", False), ("generic_c4_shape", False)])
+def test_lti_matches_reference_goldens(dev, name, per_instance, hessian):
+    g = cases.golden(name)
+    form, params = _form(g, per_instance)
+    cases.check_layout(form, g)
+    out = form.generate_all_qp_matrices_batched(
+        g["x0"], params, dynamics={"plant": (g["A_sys"], g["B_sys"])}, hessian=hessian)
+    got = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+    cases.assert_qp_close(got, (g["A"], g["h"], g["Q"], g["q"]))
+
+
+def test_lti_agrees_with_affine_path_when_dynamics_are_shared(dev):
+    """Shared (A, B): mode A (plan constants + streams) and mode B must agree."""
+    g = cases.golden("generic_small")
+    form, params = _form(g, False)
+    a = form.generate_all_qp_matrices_batched(g["x0"], params)
+    b = form.generate_all_qp_matrices_batched(
+        g["x0"], params, dynamics={"plant": (g["A_sys"], g["B_sys"])})
+    for x, y in ((a.P, b.P), (a.q, b.q), (a.G, b.G), (a.h, b.h)):
+        assert cases.rel_err(y.cpu().numpy(), x.cpu().numpy()) <= cases.TOL
+
+
+@pytest.mark.parametrize("nx,nu,N,batch", [(12, 4, 50, 300), (6, 2, 100, 40), (2, 1, 5, 7), (5, 5, 13, 9)])
+def test_lti_random_batches_against_oracle(dev, monkeypatch, nx, nu, N, batch):
+    """More instances than resident CTAs (persistent loop), odd sizes, m = 5
+    (general recursion kernel); checked against the oracle on a few instances."""
+    import mpc_interface_b200.tools as tools
+    from _numpy_backend import NumpyBackend
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    seed = 100 + nx
+    _, _, Q, R = synthetic.generic_system(seed, nx, nu)
+    A, B = synthetic.generic_plants(seed, batch, nx, nu)
+    rows = np.random.default_rng(seed + 1).normal(size=[2, nx])
+    vals = synthetic.generic_inputs(seed, batch, nx)
+    refs = [Param("ref%d" % i) for i in range(nx)]
+    form = cases.formulate_generic(A[0], B[0], Q, R, N, rows, refs=refs)
+    params = {"ref%d" % i: vals["ref"][:, i] for i in range(nx)}
+    outs = {}
+    for mode in ("dmma", "recursion"):
+        out = form.generate_all_qp_matrices_batched(
+            vals["x0"], params, dynamics={"plant": (A, B)}, hessian=mode)
+        outs[mode] = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+    monkeypatch.setattr(tools, "extend_matrices", orc.extend_matrices)
+    for b in sorted({0, batch // 2, batch - 1}):
+        ref_form = cases.formulate_generic(
+            A[b], B[b], Q, R, N, rows, refs=list(vals["ref"][b]), backend=NumpyBackend())
+        ref = orc.all_qp_matrices(ref_form, vals["x0"][b][:, None])
+        for mode in outs:
+            cases.assert_qp_close([x[b] for x in outs[mode]], ref)
+
+
+def test_lti_partial_outputs_and_errors(dev):
+    import ctypes
+
+    import torch
+    from mpc_interface_b200 import lti
+
+    g = cases.golden("generic_perinst_small")
+    form, params = _form(g, True)
+    plan = form.lti_plan("plant")
+    full = lti.assemble(plan, g["A_sys"], g["B_sys"], g["x0"], params)
+    # only q and h requested
+    dp = plan.device_plan()
+    A, B, x0 = (torch.from_numpy(np.ascontiguousarray(g[k])).cuda() for k in ("A_sys", "B_sys", "x0"))
+    scal = torch.from_numpy(plan.slots.evaluate(params, x0.shape[0])).cuda()
+    q = torch.zeros_like(full.q)
+    h = torch.zeros_like(full.h)
+    null = ctypes.c_void_p(0)
+    rc = dev.lib().mpci_lti_assemble(dp.handle, A.data_ptr(), 16, B.data_ptr(), 8, x0.data_ptr(),
+                                     scal.data_ptr(), null, q.data_ptr(), null, h.data_ptr(), 4, 0, null)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert torch.equal(q, full.q) and torch.equal(h, full.h)
+    # invalid arguments come back as negative codes, not crashes
+    assert dev.lib().mpci_lti_assemble(dp.handle, A.data_ptr(), 3, B.data_ptr(), 8, x0.data_ptr(),
+                                       scal.data_ptr(), null, null, null, null, 4, 0, null) < 0
+    assert dev.lib().mpci_lti_assemble(dp.handle, A.data_ptr(), 16, B.data_ptr(), 8, x0.data_ptr(),
+                                       scal.data_ptr(), null, null, null, null, 4, 7, null) < 0
+    with pytest.raises(ValueError):
+        lti.assemble(plan, g["A_sys"], g["B_sys"], g["x0"][:, :3], params)
