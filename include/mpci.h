@@ -25,7 +25,6 @@ extern "C" {
 #define MPCI_VERSION 100
 #define MPCI_MAX_FACTORS 4   /* per-instance scalar factors of one monomial */
 #define MPCI_MAX_TERMS 8     /* monomials of one streamed array (P or G) */
-#define MPCI_QH_ROW_TILE 128 /* rows of [q; h] per thread block */
 
 int mpci_version(void);
 
@@ -97,16 +96,20 @@ typedef struct {
   const double* DG_dev; /* dev  [n_G_terms][nc][nv]                           */
   int n_Y_terms;
   const int* Y_terms;
-  const double* DY_dev; /* dev  [n_Y_terms][nv + nc][ng + 1]                  */
-  int n_qh_ranges;      /* non-zero (row tile, term, k0, k1) blocks of DY     */
-  const int* qh_ranges; /* host [n_qh_ranges][4], grouped by row tile         */
-  const int* qh_tile_ptr; /* host [ceil((nv+nc)/MPCI_QH_ROW_TILE) + 1]        */
+  /* the constants DY[t] ([nv + nc] x [ng + 1]) as sparse rows: segment s =
+   * (row, term, nz_begin, nz_end), sorted by row; nz e = (Y_val[e], Y_col[e])
+   * with Y_col in [0, ng] (ng = the constant column).  All host pointers.   */
+  int n_Y_segs;
+  const int* Y_segs;    /* host [n_Y_segs][4]                                 */
+  int n_Y_nz;
+  const double* Y_val;  /* host [n_Y_nz]                                      */
+  const int* Y_col;     /* host [n_Y_nz]                                      */
 } mpci_plan_desc;
 
 typedef struct mpci_plan mpci_plan;
 
 /* Copies the small host tables; keeps the DP/DG/DY device pointers (owned by
- * the caller, must outlive the plan).  Allocates a transposed copy of DY.   */
+ * the caller, must outlive the plan) and a device copy of the sparse Y rows. */
 int mpci_plan_create(const mpci_plan_desc* desc, mpci_plan** plan_out);
 int mpci_plan_destroy(mpci_plan* plan);
 

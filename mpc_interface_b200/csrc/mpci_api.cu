@@ -1,4 +1,5 @@
 // C ABI: plan life cycle, device-resident assembly, host-buffer assembly.
+#include <algorithm>
 #include <cstring>
 
 #include "mpci_common.cuh"
@@ -65,73 +66,128 @@ extern "C" int mpci_plan_create(const mpci_plan_desc* d, mpci_plan** out) {
     rc = fill_stream(p->G, d->n_G_terms, d->G_terms, d->monomials, d->n_monomials, d->DG_dev,
                      (long)d->nc * d->nv, "G");
   const int rows = d->nv + d->nc, ngx = d->ng + 1;
-  const int n_tiles = (rows + MPCI_QH_ROW_TILE - 1) / MPCI_QH_ROW_TILE;
-  if (!rc && (d->n_Y_terms < 1 || !d->Y_terms || (rows > 0 && !d->DY_dev)))
+  if (!rc && (d->n_Y_terms < 1 || !d->Y_terms))
     rc = mpci::fail(-3, "plan_create: the [q;h] terms are missing");
-  if (!rc && d->n_qh_ranges > 0 && (!d->qh_ranges || !d->qh_tile_ptr))
-    rc = mpci::fail(-3, "plan_create: qh range tables are NULL");
+  if (!rc && (d->n_Y_segs < 0 || d->n_Y_nz < 0 ||
+              (d->n_Y_segs > 0 && (!d->Y_segs || !d->Y_val || !d->Y_col))))
+    rc = mpci::fail(-3, "plan_create: the sparse [q;h] rows are missing");
   if (!rc) {
-    for (int r = 0; r < d->n_qh_ranges; ++r) {
-      const int* q = d->qh_ranges + 4 * r;
-      if (q[0] < 0 || q[0] >= n_tiles || q[1] < 0 || q[1] >= d->n_Y_terms || q[2] < 0 ||
-          q[3] > ngx || q[2] > q[3]) {
-        rc = mpci::fail(-9, "plan_create: bad qh range %d (%d %d %d %d)", r, q[0], q[1], q[2],
-                        q[3]);
+    int last_row = 0, last_end = 0;
+    for (int s = 0; s < d->n_Y_segs; ++s) {
+      const int* g = d->Y_segs + 4 * s;  // (row, term, nz_begin, nz_end)
+      if (g[0] < last_row || g[0] >= rows || g[1] < 0 || g[1] >= d->n_Y_terms ||
+          g[2] != last_end || g[3] <= g[2] || g[3] > d->n_Y_nz) {
+        rc = mpci::fail(-9, "plan_create: bad [q;h] segment %d (%d %d %d %d)", s, g[0], g[1],
+                        g[2], g[3]);
         break;
+      }
+      last_row = g[0];
+      last_end = g[3];
+    }
+    for (int e = 0; !rc && e < d->n_Y_nz; ++e)
+      if (d->Y_col[e] < 0 || d->Y_col[e] >= ngx)
+        rc = mpci::fail(-9, "plan_create: [q;h] column %d out of %d", d->Y_col[e], ngx);
+  }
+  for (int j = 0; !rc && j < d->n_Y_terms; ++j)
+    if (d->Y_terms[j] < 0 || d->Y_terms[j] >= d->n_monomials)
+      rc = mpci::fail(-9, "plan_create: Y term %d names monomial %d", j, d->Y_terms[j]);
+  if (rc) { delete p; return rc; }
+
+  // Row chunks: at most kQhChunk consecutive rows, never across the q / h border
+  // (so a chunk is one contiguous run of q or of h).  Chunks are dealt to the
+  // warps longest-first (greedy balance of the non-zero count).
+  struct Chunk { int row0, nrows, seg_begin, seg_end; long work; };
+  std::vector<Chunk> chunks;
+  {
+    int s = 0;
+    for (int part = 0; part < 2; ++part) {
+      const int lo = part == 0 ? 0 : d->nv, hi = part == 0 ? d->nv : rows;
+      for (int r0 = lo; r0 < hi; r0 += mpci::kQhChunk) {
+        Chunk c{r0, std::min(mpci::kQhChunk, hi - r0), s, s, 0};
+        while (s < d->n_Y_segs && d->Y_segs[4 * s] < r0 + c.nrows) {
+          c.work += d->Y_segs[4 * s + 3] - d->Y_segs[4 * s + 2] + 2;
+          ++s;
+        }
+        c.seg_end = s;
+        c.work += c.nrows;
+        chunks.push_back(c);
       }
     }
   }
-  if (rc) { delete p; return rc; }
-
-  // device tables: factors of the Y terms | ranges | tile_ptr
-  std::vector<int> host;
-  for (int j = 0; j < d->n_Y_terms; ++j) {
-    const int m = d->Y_terms[j];
-    if (m < 0 || m >= d->n_monomials) {
-      delete p;
-      return mpci::fail(-9, "plan_create: Y term %d names monomial %d", j, m);
-    }
-    for (int f = 0; f < MPCI_MAX_FACTORS; ++f)
-      host.push_back(d->monomials[m * MPCI_MAX_FACTORS + f]);
+  std::vector<int> order(chunks.size());
+  for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+  std::stable_sort(order.begin(), order.end(),
+                   [&](int x, int y) { return chunks[x].work > chunks[y].work; });
+  std::vector<std::vector<int>> per_warp(mpci::kQhWarps);
+  std::vector<long> load(mpci::kQhWarps, 0);
+  for (int idx : order) {
+    int w = 0;
+    for (int k = 1; k < mpci::kQhWarps; ++k) if (load[k] < load[w]) w = k;
+    per_warp[w].push_back(idx);
+    load[w] += chunks[idx].work;
   }
-  const size_t off_ranges = host.size();
-  for (int i = 0; i < 4 * d->n_qh_ranges; ++i) host.push_back(d->qh_ranges[i]);
-  while (host.size() % 4) host.push_back(0);  // keep ranges int4-aligned relative to base
-  const size_t off_tiles = host.size();
-  for (int i = 0; i <= n_tiles; ++i) host.push_back(d->n_qh_ranges ? d->qh_tile_ptr[i] : 0);
+  // per-warp record streams: chunks -> rows -> (row, term) segments -> non-zeros
+  std::vector<mpci::QhNz> h_nz;
+  std::vector<int> h_chunks, h_nz_ptr(1, 0), h_chunk_ptr(1, 0);
+  for (int w = 0; w < mpci::kQhWarps; ++w) {
+    std::sort(per_warp[w].begin(), per_warp[w].end());
+    for (int idx : per_warp[w]) {
+      const Chunk& c = chunks[idx];
+      h_chunks.push_back(c.row0);
+      h_chunks.push_back(c.nrows);
+      int s = c.seg_begin;
+      for (int r = 0; r < c.nrows; ++r) {
+        const size_t row_start = h_nz.size();
+        while (s < c.seg_end && d->Y_segs[4 * s] == c.row0 + r) {
+          const int* g = d->Y_segs + 4 * s;
+          for (int e = g[2]; e < g[3]; ++e)
+            h_nz.push_back(mpci::QhNz{d->Y_val[e], d->Y_col[e], g[1]});
+          h_nz.back().meta |= mpci::kQhEndSeg;
+          ++s;
+        }
+        if (h_nz.size() == row_start)  // an all-zero row still has to be written
+          h_nz.push_back(mpci::QhNz{0.0, 0, mpci::kQhEndSeg});
+        h_nz.back().meta |= mpci::kQhEndRow;
+      }
+      h_nz.back().meta |= mpci::kQhEndChunk;
+    }
+    h_nz_ptr.push_back((int)h_nz.size());
+    h_chunk_ptr.push_back((int)h_chunks.size() / 2);
+  }
+  std::vector<int> h_factors;
+  for (int j = 0; j < d->n_Y_terms; ++j)
+    for (int f = 0; f < MPCI_MAX_FACTORS; ++f)
+      h_factors.push_back(d->monomials[d->Y_terms[j] * MPCI_MAX_FACTORS + f]);
 
-  // ranges must start on a 16-byte boundary: pad the factor block
-  std::vector<int> packed;
-  const size_t factors_len = off_ranges;
-  const size_t pad = (4 - factors_len % 4) % 4;
-  packed.insert(packed.end(), host.begin(), host.begin() + factors_len);
-  packed.insert(packed.end(), pad, 0);
-  packed.insert(packed.end(), host.begin() + off_ranges, host.end());
-  const size_t p_ranges = factors_len + pad, p_tiles = off_tiles + pad;
-
-  cudaError_t e = cudaMalloc(&p->dev_tables, packed.size() * sizeof(int));
-  if (e == cudaSuccess)
-    e = cudaMemcpy(p->dev_tables, packed.data(), packed.size() * sizeof(int),
-                   cudaMemcpyHostToDevice);
-  const size_t dyt_elems = (size_t)d->n_Y_terms * rows * ngx;
-  if (e == cudaSuccess && dyt_elems) e = cudaMalloc(&p->DYt, dyt_elems * sizeof(double));
+  // one device allocation: nz | chunks | factors | nz_ptr | chunk_ptr  (16-byte aligned parts)
+  auto align16 = [](size_t x) { return (x + 15) & ~size_t(15); };
+  const size_t o_nz = 0;
+  const size_t o_chunks = align16(o_nz + h_nz.size() * sizeof(mpci::QhNz));
+  const size_t o_factors = align16(o_chunks + h_chunks.size() * sizeof(int));
+  const size_t o_nzp = align16(o_factors + h_factors.size() * sizeof(int));
+  const size_t o_chp = align16(o_nzp + h_nz_ptr.size() * sizeof(int));
+  const size_t total = o_chp + h_chunk_ptr.size() * sizeof(int);
+  std::vector<char> blob(total, 0);
+  if (!h_nz.empty()) std::memcpy(&blob[o_nz], h_nz.data(), h_nz.size() * sizeof(mpci::QhNz));
+  if (!h_chunks.empty()) std::memcpy(&blob[o_chunks], h_chunks.data(), h_chunks.size() * sizeof(int));
+  std::memcpy(&blob[o_factors], h_factors.data(), h_factors.size() * sizeof(int));
+  std::memcpy(&blob[o_nzp], h_nz_ptr.data(), h_nz_ptr.size() * sizeof(int));
+  std::memcpy(&blob[o_chp], h_chunk_ptr.data(), h_chunk_ptr.size() * sizeof(int));
+  cudaError_t e = cudaMalloc(&p->dev_tables, total);
+  if (e == cudaSuccess) e = cudaMemcpy(p->dev_tables, blob.data(), total, cudaMemcpyHostToDevice);
   if (e != cudaSuccess) {
     rc = mpci::cuda_fail(e, "plan_create: device tables");
     mpci_plan_destroy(p);
     return rc;
   }
-  rc = mpci::launch_transpose(d->DY_dev, p->DYt, d->n_Y_terms, rows, ngx, nullptr);
-  if (!rc && (e = cudaDeviceSynchronize()) != cudaSuccess)
-    rc = mpci::cuda_fail(e, "plan_create: transpose");
-  if (rc) { mpci_plan_destroy(p); return rc; }
-
-  int* base = static_cast<int*>(p->dev_tables);
+  const char* base = static_cast<const char*>(p->dev_tables);
   p->Y.nv = d->nv; p->Y.ng = d->ng; p->Y.nc = d->nc;
   p->Y.n_scalars = d->n_scalars; p->Y.n_terms = d->n_Y_terms;
-  p->Y.factors = base;
-  p->Y.ranges = base + p_ranges;
-  p->Y.tile_ptr = base + p_tiles;
-  p->Y.DYt = p->DYt;
+  p->Y.nz = reinterpret_cast<const mpci::QhNz*>(base + o_nz);
+  p->Y.chunks = reinterpret_cast<const int2*>(base + o_chunks);
+  p->Y.factors = reinterpret_cast<const int*>(base + o_factors);
+  p->Y.warp_nz_ptr = reinterpret_cast<const int*>(base + o_nzp);
+  p->Y.warp_chunk_ptr = reinterpret_cast<const int*>(base + o_chp);
   *out = p;
   return 0;
 }
@@ -144,7 +200,6 @@ extern "C" int mpci_plan_destroy(mpci_plan* p) {
     if (p->slot_free[s]) cudaEventDestroy(p->slot_free[s]);
     if (p->streams[s]) cudaStreamDestroy(p->streams[s]);
   }
-  if (p->DYt) cudaFree(p->DYt);
   if (p->dev_tables) cudaFree(p->dev_tables);
   delete p;
   return 0;

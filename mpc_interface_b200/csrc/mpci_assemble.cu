@@ -12,7 +12,8 @@
 // stream_terms_kernel is bound by the HBM write of P and G (99.5 % of the
 // output bytes): constants stay in registers across a group of instances, every
 // thread issues 16-byte streaming stores, a warp covers 512 contiguous bytes.
-// qh_kernel is a small FP64 product that skips the all-zero blocks of DY.
+// qh_kernel is a sparse FP64 product (one instance per thread, the shared
+// sparsity pattern walked in lock-step).
 #include <cstdint>
 
 #include "mpci_common.cuh"
@@ -117,29 +118,42 @@ int launch_stream(const StreamArgs& a, const double* scalars, int n_scalars, dou
 // ---------------------------------------------------------------------------
 // [q; h] = sum_t c_t * DY_t @ [given; 1]
 // ---------------------------------------------------------------------------
-constexpr int kQhGroup = 16;  // instances per block
+// DY is sparse (axis blocks, triangular Toeplitz blocks, shifted diagonals:
+// 51 k non-zeros of 825 k entries at the biped N=100), and the sparsity is the
+// same for every instance.  So a THREAD owns an instance and a warp walks the
+// non-zeros of its rows in lock-step: the constant (value, column) is one
+// 16-byte load at a warp-uniform address, the instance's [given; 1] sits in
+// shared memory (column-major, padded: conflict free), one DFMA per non-zero.
+// Rows come in chunks of 8 that a warp stages in shared memory and writes out
+// as one 64-byte run per instance.
+constexpr int kQhInst = 32;                 // instances per block (one per lane)
+constexpr int kQhLd = kQhInst + 1;          // padded leading dimension of gs / cs
+constexpr int kQhTileLd = kQhChunk + 1;
 
-// DYt is the transposed copy built at plan creation: DYt[t][k][row], so that the
-// threads of a block (one row each) read consecutive addresses.
-__global__ void __launch_bounds__(MPCI_QH_ROW_TILE)
+__global__ void __launch_bounds__(kQhWarps * 32)
 qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict__ given,
           double* __restrict__ q, double* __restrict__ h, long batch) {
   extern __shared__ double sm[];
   const int ngx = a.ng + 1;
-  double* gs = sm;                       // [ngx][kQhGroup]
-  double* cs = sm + (long)ngx * kQhGroup;  // [n_terms][kQhGroup]
-  const long b0 = (long)blockIdx.y * kQhGroup;
-  const int group = (int)min((long)kQhGroup, batch - b0);
-  const int rows = a.nv + a.nc;
+  QhNz* ring = reinterpret_cast<QhNz*>(sm) + (threadIdx.x >> 5) * 32;  // [kQhWarps][32], 16-byte aligned
+  double* gs = sm + kQhWarps * 32 * (sizeof(QhNz) / sizeof(double));  // [ngx][kQhLd]
+  double* cs = gs + (size_t)ngx * kQhLd;             // [n_terms][kQhLd]
+  double* tiles = cs + (size_t)a.n_terms * kQhLd;    // [kQhWarps][kQhInst][kQhTileLd]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const long b0 = (long)blockIdx.x * kQhInst;
+  const int group = (int)min((long)kQhInst, batch - b0);
 
-  for (int e = threadIdx.x; e < ngx * kQhGroup; e += blockDim.x) {
-    const int k = e / kQhGroup, t = e % kQhGroup;  // conflict-free shared stores
-    double v = 0.0;
-    if (t < group) v = (k < a.ng) ? given[(b0 + t) * a.ng + k] : 1.0;
-    gs[e] = v;
+  // stage [given; 1] of the block's instances: coalesced reads, conflict-free writes
+  for (int t = warp; t < kQhInst; t += kQhWarps) {
+    const double* g = given + (b0 + t) * a.ng;
+    for (int k = lane; k < ngx; k += 32) {
+      double v = 0.0;
+      if (t < group) v = (k < a.ng) ? g[k] : 1.0;
+      gs[k * kQhLd + t] = v;
+    }
   }
-  for (int e = threadIdx.x; e < a.n_terms * kQhGroup; e += blockDim.x) {
-    const int j = e / kQhGroup, t = e % kQhGroup;
+  for (int e = tid; e < a.n_terms * kQhInst; e += blockDim.x) {
+    const int j = e / kQhInst, t = e % kQhInst;
     double c = 0.0;
     if (t < group) {
       c = 1.0;
@@ -149,88 +163,86 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
         if (idx >= 0) c *= s[idx];
       }
     }
-    cs[j * kQhGroup + t] = c;
+    cs[j * kQhLd + t] = c;
   }
   __syncthreads();
 
-  const int row = blockIdx.x * MPCI_QH_ROW_TILE + threadIdx.x;
-  if (row >= rows) return;
-  double y[kQhGroup];
+  double* tile = tiles + (size_t)warp * kQhInst * kQhTileLd;
+  const double* gl = gs + lane;
+  const double* cl = cs + lane;
+  const int e_begin = a.warp_nz_ptr[warp], e_end = a.warp_nz_ptr[warp + 1];
+  int ci = a.warp_chunk_ptr[warp];
+  double acc = 0.0, part = 0.0;
+  int r = 0;
+  // the warp's record stream comes in batches of 32: one coalesced 16-byte load
+  // per lane (the next batch is in flight while this one is consumed), parked in
+  // a 512-byte ring and read back as warp-uniform LDS.128
+  QhNz next = {0.0, 0, 0};
+  if (e_begin + lane < e_end) next = a.nz[e_begin + lane];
+  for (int base = e_begin; base < e_end; base += 32) {
+    ring[lane] = next;
+    if (base + 32 + lane < e_end) next = a.nz[base + 32 + lane];
+    __syncwarp();
+    const int cnt = min(32, e_end - base);
+#pragma unroll 4
+    for (int i = 0; i < cnt; ++i) {
+      const QhNz rec = ring[i];
+      part = fma(rec.val, gl[rec.col * kQhLd], part);
+      if (rec.meta & ~kQhTermMask) {  // warp-uniform
+        acc = fma(cl[(rec.meta & kQhTermMask) * kQhLd], part, acc);
+        part = 0.0;
+        if (rec.meta & kQhEndRow) {
+          tile[lane * kQhTileLd + r] = acc;
+          acc = 0.0;
+          ++r;
+        }
+        if (rec.meta & kQhEndChunk) {
+          const int2 chunk = a.chunks[ci++];  // (first row, rows)
+          __syncwarp();
+          // 8 lanes cover the chunk of one instance (64 contiguous bytes), 4 instances per pass
+          const bool is_q = chunk.x < a.nv;
+          double* out = is_q ? q : h;
+          if (out) {
+            const int rr = lane & (kQhChunk - 1), sub = lane / kQhChunk;
+            const long stride = is_q ? a.nv : a.nc;
+            const int row = is_q ? chunk.x : chunk.x - a.nv;
+            if (rr < chunk.y) {
 #pragma unroll
-  for (int t = 0; t < kQhGroup; ++t) y[t] = 0.0;
+              for (int it = 0; it < kQhInst / (32 / kQhChunk); ++it) {
+                const int t = it * (32 / kQhChunk) + sub;
+                if (t < group) out[(b0 + t) * stride + row + rr] = tile[t * kQhTileLd + rr];
+              }
+            }
+          }
+          __syncwarp();
+          r = 0;
+        }
+      }
+    }
+    __syncwarp();
+  }
+}
 
-  const int r_begin = a.tile_ptr[blockIdx.x], r_end = a.tile_ptr[blockIdx.x + 1];
-  for (int r = r_begin; r < r_end; ++r) {
-    const int4 range = reinterpret_cast<const int4*>(a.ranges)[r];  // (tile, term, k0, k1)
-    const double* d = a.DYt + ((long)range.y * ngx + range.z) * rows + row;
-    double acc[kQhGroup];
-#pragma unroll
-    for (int t = 0; t < kQhGroup; ++t) acc[t] = 0.0;
-    for (int k = range.z; k < range.w; ++k, d += rows) {
-      const double dv = *d;
-      const double2* g2 = reinterpret_cast<const double2*>(gs + k * kQhGroup);
-#pragma unroll
-      for (int t2 = 0; t2 < kQhGroup / 2; ++t2) {
-        const double2 g = g2[t2];
-        acc[2 * t2] = fma(dv, g.x, acc[2 * t2]);
-        acc[2 * t2 + 1] = fma(dv, g.y, acc[2 * t2 + 1]);
-      }
-    }
-    const double* c = cs + range.y * kQhGroup;
-#pragma unroll
-    for (int t = 0; t < kQhGroup; ++t) y[t] = fma(c[t], acc[t], y[t]);
-  }
-#pragma unroll
-  for (int t = 0; t < kQhGroup; ++t) {
-    if (t < group) {
-      if (row < a.nv) {
-        if (q) q[(b0 + t) * a.nv + row] = y[t];
-      } else if (h) {
-        h[(b0 + t) * a.nc + (row - a.nv)] = y[t];
-      }
-    }
-  }
+size_t qh_smem_bytes(const QhArgs& a) {
+  return sizeof(double) * ((size_t)(a.ng + 1 + a.n_terms) * kQhLd +
+                           (size_t)kQhWarps * kQhInst * kQhTileLd) +
+         sizeof(QhNz) * kQhWarps * 32;
 }
 
 int launch_qh(const QhArgs& a, const double* scalars, const double* given, double* q, double* h,
               long batch, cudaStream_t st) {
   const int rows = a.nv + a.nc;
   if (rows == 0 || batch == 0 || (!q && !h)) return 0;
-  const size_t smem = sizeof(double) * ((size_t)(a.ng + 1) + a.n_terms) * kQhGroup;
-  if (smem > 200 * 1024)
+  const size_t smem = qh_smem_bytes(a);
+  if (smem > 227 * 1024)
     return fail(-8, "assemble: given_len %d too large for the [q;h] kernel", a.ng);
   if (smem > 48 * 1024)
     MPCI_CUDA(cudaFuncSetAttribute(qh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));
-  dim3 grid((rows + MPCI_QH_ROW_TILE - 1) / MPCI_QH_ROW_TILE,
-            (unsigned)((batch + kQhGroup - 1) / kQhGroup));
-  if (grid.y > 65535) return fail(-6, "assemble: batch %ld too large for one launch", batch);
-  qh_kernel<<<grid, MPCI_QH_ROW_TILE, smem, st>>>(a, scalars, given, q, h, batch);
+  const long blocks = (batch + kQhInst - 1) / kQhInst;
+  if (blocks > 2147483647L) return fail(-6, "assemble: batch %ld too large for one launch", batch);
+  qh_kernel<<<(unsigned)blocks, kQhWarps * 32, smem, st>>>(a, scalars, given, q, h, batch);
   MPCI_LAUNCH_CHECK("qh_kernel");
-  return 0;
-}
-
-// DYt[t][k][row] = DY[t][row][k]
-__global__ void __launch_bounds__(256)
-transpose_kernel(const double* __restrict__ in, double* __restrict__ out, int n_terms, int rows,
-                 int cols) {
-  const long total = (long)n_terms * rows * cols;
-  const long stride = (long)gridDim.x * blockDim.x;
-  for (long e = (long)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride) {
-    const int row = e % rows;
-    const int k = (e / rows) % cols;
-    const long t = e / ((long)rows * cols);
-    out[e] = in[(t * rows + row) * cols + k];
-  }
-}
-
-int launch_transpose(const double* in, double* out, int n_terms, int rows, int cols,
-                     cudaStream_t st) {
-  const long total = (long)n_terms * rows * cols;
-  if (total == 0) return 0;
-  const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-  transpose_kernel<<<blocks, 256, 0, st>>>(in, out, n_terms, rows, cols);
-  MPCI_LAUNCH_CHECK("transpose_kernel");
   return 0;
 }
 

@@ -17,20 +17,33 @@ struct StreamArgs {
   long n_elems;
 };
 
+// [q; h]: sparse rows, one instance per thread (mpci_assemble.cu)
+constexpr int kQhWarps = 8;   // warps of a block; each owns a list of row chunks
+constexpr int kQhChunk = 8;   // rows per chunk (one 64-byte run per instance)
+
+struct QhNz {      // 16 bytes; a warp's records are consecutive, in processing order
+  double val;
+  int col;         // index into the staged [given; 1] of the instance
+  int meta;        // term | kQhEndSeg | kQhEndRow | kQhEndChunk
+};
+constexpr int kQhTermMask = 0xff;
+constexpr int kQhEndSeg = 0x100;    // last non-zero of a (row, term) segment
+constexpr int kQhEndRow = 0x200;    // ... of a row: the accumulator is the result
+constexpr int kQhEndChunk = 0x400;  // ... of a chunk of rows: write the chunk out
+
 struct QhArgs {
   int nv, ng, nc, n_scalars, n_terms;
-  const int* factors;   // dev [n_terms][MPCI_MAX_FACTORS]
-  const double* DYt;    // dev [n_terms][ng + 1][nv + nc]
-  const int* ranges;    // dev [n_ranges][4]
-  const int* tile_ptr;  // dev [n_tiles + 1]
+  const int* factors;      // dev [n_terms][MPCI_MAX_FACTORS]
+  const QhNz* nz;          // dev: per-warp streams, concatenated
+  const int* warp_nz_ptr;  // dev [kQhWarps + 1]
+  const int2* chunks;      // dev: (first row, rows) in the order the warps meet them
+  const int* warp_chunk_ptr;  // dev [kQhWarps + 1]
 };
 
 int launch_stream(const StreamArgs& a, const double* scalars, int n_scalars, double* out,
                   long batch, cudaStream_t st);
 int launch_qh(const QhArgs& a, const double* scalars, const double* given, double* q, double* h,
               long batch, cudaStream_t st);
-int launch_transpose(const double* in, double* out, int n_terms, int rows, int cols,
-                     cudaStream_t st);
 
 }  // namespace mpci
 
@@ -38,8 +51,7 @@ struct mpci_plan {
   int nv, ng, nc, n_scalars;
   mpci::StreamArgs P, G;
   mpci::QhArgs Y;
-  void* dev_tables;  // one allocation: factors | ranges | tile_ptr
-  double* DYt;
+  void* dev_tables;  // one allocation: nz | chunks | factors | warp pointers
   // staging of mpci_assemble_host (two slots), allocated on first use
   long slot_capacity;
   double* slot_in[2];   // scalars | given

@@ -36,10 +36,11 @@ class PlanDesc(ctypes.Structure):
         ("DG_dev", ctypes.c_void_p),
         ("n_Y_terms", ctypes.c_int),
         ("Y_terms", ctypes.c_void_p),
-        ("DY_dev", ctypes.c_void_p),
-        ("n_qh_ranges", ctypes.c_int),
-        ("qh_ranges", ctypes.c_void_p),
-        ("qh_tile_ptr", ctypes.c_void_p),
+        ("n_Y_segs", ctypes.c_int),
+        ("Y_segs", ctypes.c_void_p),
+        ("n_Y_nz", ctypes.c_int),
+        ("Y_val", ctypes.c_void_p),
+        ("Y_col", ctypes.c_void_p),
     ]
 
 
@@ -223,15 +224,16 @@ class DevicePlan:
         P_terms = np.ascontiguousarray(plan.P_terms, dtype=np.int32)
         G_terms = np.ascontiguousarray(plan.G_terms, dtype=np.int32)
         Y_terms = np.ascontiguousarray(plan.Y_terms, dtype=np.int32)
-        ranges = np.ascontiguousarray(plan.qh_ranges, dtype=np.int32)
-        tile_ptr = np.ascontiguousarray(plan.qh_tile_ptr, dtype=np.int32)
+        segs = np.ascontiguousarray(plan.Y_segs, dtype=np.int32)
+        val = np.ascontiguousarray(plan.Y_val, dtype=np.float64)
+        col = np.ascontiguousarray(plan.Y_col, dtype=np.int32)
         desc = PlanDesc(
             plan.nv, plan.ng, plan.nc, max(1, len(plan.slots.exprs)),
             table.shape[0], table.ctypes.data,
             len(P_terms), P_terms.ctypes.data, plan.DP.data_ptr(),
             len(G_terms), G_terms.ctypes.data, plan.DG.data_ptr(),
-            len(Y_terms), Y_terms.ctypes.data, plan.DY.data_ptr(),
-            ranges.shape[0], ranges.ctypes.data, tile_ptr.ctypes.data,
+            len(Y_terms), Y_terms.ctypes.data,
+            segs.shape[0], segs.ctypes.data, val.shape[0], val.ctypes.data, col.ctypes.data,
         )
         handle = ctypes.c_void_p()
         check(lib().mpci_plan_create(ctypes.byref(desc), ctypes.byref(handle)))

@@ -20,7 +20,7 @@ streaming kernels of csrc/mpci_assemble.cu consume.
 
 No floating-point reduction happens in this file; numpy is used for
 placement of blocks into zero matrices (the scatter of body.py:158-177) and
-for structural scans (which tiles of DY are non-zero).
+for structural scans (which entries of DY are non-zero).
 """
 import numbers
 
@@ -30,8 +30,6 @@ from .params import Expr, is_expr
 
 MAX_FACTORS = 4  # factors per monomial the kernels accept (mpci.h: MPCI_MAX_FACTORS)
 MAX_TERMS = 8  # monomials per streamed array (mpci.h: MPCI_MAX_TERMS)
-QH_ROW_TILE = 128  # rows of [q; h] handled by one thread block (mpci.h)
-QH_K_TILE = 8  # granularity of the zero-skipping along [g; 1]
 
 
 class SlotTable:
@@ -129,8 +127,9 @@ class AffinePlan:
         self.DP = self.DG = self.DY = None  # stacked constants [K, rows, cols]
         self.row_offsets = []  # first row of every limit in G / h
         self.limit_rows = []
-        self.qh_ranges = None  # int32 [n_ranges, 4]: (row tile, term, k0, k1)
-        self.qh_tile_ptr = None  # int32 [n_row_tiles + 1]
+        self.Y_segs = None  # int32 [n_segs, 4]: (row, term, nz_begin, nz_end) of DY
+        self.Y_val = None  # float64 [n_nz]
+        self.Y_col = None  # int32 [n_nz]
         self.optim_ID = {}
         self.given_ID = {}
 
@@ -310,28 +309,26 @@ def _cost_into(form, ops, PM, slots, cost, Pacc, Yacc):
                 )
 
 
-def _scan_qh_ranges(DY):
-    """Non-zero (row tile, term, k range) triples of the stacked DY constants.
-    Structural scan on the host (which tiles are worth multiplying)."""
+def _scan_qh_rows(DY):
+    """Sparse rows of the stacked DY constants for the [q; h] kernel.
+
+    Returns ``segs`` int32 [n_segs, 4] = (row, term, nz_begin, nz_end) sorted by
+    row then term, ``val`` float64 [n_nz] and ``col`` int32 [n_nz].  Structural
+    scan on the host (which entries are non-zero) -- values are copied, not
+    computed."""
     K, rows, cols = DY.shape
-    n_tiles = (rows + QH_ROW_TILE - 1) // QH_ROW_TILE
-    ranges, ptr = [], [0]
-    for tile in range(n_tiles):
-        r0, r1 = tile * QH_ROW_TILE, min(rows, (tile + 1) * QH_ROW_TILE)
-        for term in range(K):
-            active = np.any(DY[term, r0:r1, :] != 0.0, axis=0)
-            k = 0
-            while k < cols:
-                if not active[k : k + QH_K_TILE].any():
-                    k += QH_K_TILE
-                    continue
-                k0 = k
-                while k < cols and active[k : k + QH_K_TILE].any():
-                    k += QH_K_TILE
-                ranges.append((tile, term, k0, min(k, cols)))
-        ptr.append(len(ranges))
-    table = np.array(ranges, dtype=np.int32).reshape([-1, 4])
-    return table, np.array(ptr, dtype=np.int32)
+    mask = DY != 0.0
+    counts = mask.sum(axis=2).T  # [rows, K]
+    # entries ordered by (row, term, column)
+    by_row = np.ascontiguousarray(DY.transpose(1, 0, 2))
+    row_idx, term_idx, col_idx = np.nonzero(np.ascontiguousarray(mask.transpose(1, 0, 2)))
+    val = by_row[row_idx, term_idx, col_idx].astype(np.float64)
+    ends = np.cumsum(counts.reshape(-1))
+    begins = ends - counts.reshape(-1)
+    keep = counts.reshape(-1) > 0
+    rr, tt = np.divmod(np.arange(rows * K), K)
+    segs = np.stack([rr[keep], tt[keep], begins[keep], ends[keep]], axis=1).astype(np.int32)
+    return segs.reshape([-1, 4]), val, col_idx.astype(np.int32)
 
 
 def compile_plan(form, ops, costs=None, limits=None):
@@ -409,7 +406,7 @@ def compile_plan(form, ops, costs=None, limits=None):
     plan.G_terms, plan.DG = finish(Gacc, "G")
     plan.Y_terms, plan.DY = finish(Yacc, "Y")
     plan.monomials = [m for m, _ in sorted(table.items(), key=lambda kv: kv[1])]
-    plan.qh_ranges, plan.qh_tile_ptr = _scan_qh_ranges(ops.download3(plan.DY))
+    plan.Y_segs, plan.Y_val, plan.Y_col = _scan_qh_rows(ops.download3(plan.DY))
 
     plan.nv, plan.ng, plan.nc = nv, ng, nc
     plan.slots = slots

@@ -47,8 +47,15 @@ def test_plan_structure_biped_n100(cpu_extend):
     assert len(p.P_terms) == 3 and p.DP.shape == (3, 218, 218)
     assert p.DG.shape[1:] == (440, 218) and p.DY.shape[1:] == (658, 209)
     # integer tables the kernels index with
-    assert p.qh_tile_ptr[0] == 0 and p.qh_tile_ptr[-1] == len(p.qh_ranges)
-    assert (p.qh_ranges[:, 2] < p.qh_ranges[:, 3]).all()
+    segs = p.Y_segs
+    assert segs[0, 2] == 0 and segs[-1, 3] == len(p.Y_val) == len(p.Y_col)
+    assert (segs[:, 2] < segs[:, 3]).all() and (segs[1:, 2] == segs[:-1, 3]).all()
+    assert (np.diff(segs[:, 0]) >= 0).all() and p.Y_col.max() <= p.ng
+    # the sparse rows are exactly the non-zeros of the stacked constants
+    dense = np.zeros_like(p.DY)
+    for row, term, e0, e1 in segs:
+        dense[term, row, p.Y_col[e0:e1]] = p.Y_val[e0:e1]
+    assert np.array_equal(dense, p.DY)
 
 
 def test_reference_test_body_case(cpu_extend):
