@@ -141,7 +141,7 @@ extern "C" int mpci_plan_create(const mpci_plan_desc* d, mpci_plan** out) {
         while (s < c.seg_end && d->Y_segs[4 * s] == c.row0 + r) {
           const int* g = d->Y_segs + 4 * s;
           for (int e = g[2]; e < g[3]; ++e)
-            h_nz.push_back(mpci::QhNz{d->Y_val[e], d->Y_col[e], g[1]});
+            h_nz.push_back(mpci::QhNz{d->Y_val[e], d->Y_col[e] * mpci::kQhColStride, g[1]});
           h_nz.back().meta |= mpci::kQhEndSeg;
           ++s;
         }
@@ -200,6 +200,9 @@ extern "C" int mpci_plan_destroy(mpci_plan* p) {
     if (p->slot_free[s]) cudaEventDestroy(p->slot_free[s]);
     if (p->streams[s]) cudaStreamDestroy(p->streams[s]);
   }
+  if (p->side) cudaStreamDestroy(p->side);
+  if (p->fork) cudaEventDestroy(p->fork);
+  if (p->join) cudaEventDestroy(p->join);
   if (p->dev_tables) cudaFree(p->dev_tables);
   delete p;
   return 0;
@@ -221,16 +224,33 @@ extern "C" int mpci_assemble(const mpci_plan* p, const double* scalars, const do
   cudaStream_t st = mpci::as_stream(stream);
   // grid.y limits: split very large batches
   const long piece = 65535L * 16;
+  // [q;h] first, on the side stream, so that its blocks (one per SM) are resident
+  // while the P / G streams saturate HBM with the remaining thread slots
+  const bool overlap = (P || G) && (q || h) && (p->nv + p->nc) > 0;
+  cudaStream_t qh_stream = st;
+  if (overlap) {
+    if (!p->side) {
+      MPCI_CUDA(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
+      MPCI_CUDA(cudaEventCreateWithFlags(&p->fork, cudaEventDisableTiming));
+      MPCI_CUDA(cudaEventCreateWithFlags(&p->join, cudaEventDisableTiming));
+    }
+    MPCI_CUDA(cudaEventRecord(p->fork, st));
+    MPCI_CUDA(cudaStreamWaitEvent(p->side, p->fork, 0));
+    qh_stream = p->side;
+  }
   for (long b0 = 0; b0 < batch; b0 += piece) {
     const long nb = (batch - b0 < piece) ? batch - b0 : piece;
     const double* s = scalars + b0 * p->n_scalars;
-    int rc = 0;
-    if (P) rc = mpci::launch_stream(p->P, s, p->n_scalars, P + b0 * p->P.n_elems, nb, st);
+    int rc = mpci::launch_qh(p->Y, s, given ? given + b0 * p->ng : nullptr,
+                             q ? q + b0 * p->nv : nullptr, h ? h + b0 * p->nc : nullptr, nb,
+                             qh_stream);
+    if (!rc && P) rc = mpci::launch_stream(p->P, s, p->n_scalars, P + b0 * p->P.n_elems, nb, st);
     if (!rc && G) rc = mpci::launch_stream(p->G, s, p->n_scalars, G + b0 * p->G.n_elems, nb, st);
-    if (!rc)
-      rc = mpci::launch_qh(p->Y, s, given ? given + b0 * p->ng : nullptr,
-                           q ? q + b0 * p->nv : nullptr, h ? h + b0 * p->nc : nullptr, nb, st);
     if (rc) return rc;
+  }
+  if (overlap) {
+    MPCI_CUDA(cudaEventRecord(p->join, p->side));
+    MPCI_CUDA(cudaStreamWaitEvent(st, p->join, 0));
   }
   return 0;
 }

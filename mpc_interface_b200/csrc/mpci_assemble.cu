@@ -119,15 +119,14 @@ int launch_stream(const StreamArgs& a, const double* scalars, int n_scalars, dou
 // [q; h] = sum_t c_t * DY_t @ [given; 1]
 // ---------------------------------------------------------------------------
 // DY is sparse (axis blocks, triangular Toeplitz blocks, shifted diagonals:
-// 51 k non-zeros of 825 k entries at the biped N=100), and the sparsity is the
-// same for every instance.  So a THREAD owns an instance and a warp walks the
-// non-zeros of its rows in lock-step: the constant (value, column) is one
-// 16-byte load at a warp-uniform address, the instance's [given; 1] sits in
-// shared memory (column-major, padded: conflict free), one DFMA per non-zero.
-// Rows come in chunks of 8 that a warp stages in shared memory and writes out
-// as one 64-byte run per instance.
-constexpr int kQhInst = 32;                 // instances per block (one per lane)
-constexpr int kQhLd = kQhInst + 1;          // padded leading dimension of gs / cs
+// 25.6 k non-zeros of 825 k entries at the biped N=100), and the sparsity is the
+// same for every instance.  So a THREAD owns two instances and a warp walks the
+// non-zeros of its rows in lock-step: the constant (value, column) record is a
+// warp-uniform 16-byte shared-memory read, the two instances' [given; 1] entries
+// are one more (column-major double2, padded: conflict free), two DFMAs per
+// record.  Rows come in chunks of 4 that a warp stages in shared memory and
+// writes out as one 32-byte run per instance.
+constexpr int kQhInst = 64;                 // instances per block (two per lane)
 constexpr int kQhTileLd = kQhChunk + 1;
 
 __global__ void __launch_bounds__(kQhWarps * 32)
@@ -135,21 +134,25 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
           double* __restrict__ q, double* __restrict__ h, long batch) {
   extern __shared__ double sm[];
   const int ngx = a.ng + 1;
-  QhNz* ring = reinterpret_cast<QhNz*>(sm) + (threadIdx.x >> 5) * 32;  // [kQhWarps][32], 16-byte aligned
-  double* gs = sm + kQhWarps * 32 * (sizeof(QhNz) / sizeof(double));  // [ngx][kQhLd]
-  double* cs = gs + (size_t)ngx * kQhLd;             // [n_terms][kQhLd]
-  double* tiles = cs + (size_t)a.n_terms * kQhLd;    // [kQhWarps][kQhInst][kQhTileLd]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const long b0 = (long)blockIdx.x * kQhInst;
+  QhNz* ring = reinterpret_cast<QhNz*>(sm) + warp * 32;                // [kQhWarps][32]
+  double* gs = sm + kQhWarps * 32 * (sizeof(QhNz) / sizeof(double));   // [ngx][33] double2
+  double* cs = gs + (size_t)ngx * 2 * kQhColStride;                                  // [n_terms][33] double2
+  double* tiles = cs + (size_t)a.n_terms * 2 * kQhColStride;              // [kQhWarps][kQhInst][kQhTileLd]
+  // persistent: at most one block per SM, so that every block is resident at once
+  // and the P / G streams launched beside this kernel can use the other thread slots
+  for (long b0 = (long)blockIdx.x * kQhInst; b0 < batch; b0 += (long)gridDim.x * kQhInst) {
   const int group = (int)min((long)kQhInst, batch - b0);
+  __syncthreads();  // the previous group is done with gs / cs
 
-  // stage [given; 1] of the block's instances: coalesced reads, conflict-free writes
+  // stage [given; 1]: instance t sits in lane t % 32, half t / 32 of every column
   for (int t = warp; t < kQhInst; t += kQhWarps) {
     const double* g = given + (b0 + t) * a.ng;
+    double* dst = gs + (t & 31) * 2 + (t >> 5);
     for (int k = lane; k < ngx; k += 32) {
       double v = 0.0;
       if (t < group) v = (k < a.ng) ? g[k] : 1.0;
-      gs[k * kQhLd + t] = v;
+      dst[k * 66] = v;
     }
   }
   for (int e = tid; e < a.n_terms * kQhInst; e += blockDim.x) {
@@ -163,68 +166,81 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
         if (idx >= 0) c *= s[idx];
       }
     }
-    cs[j * kQhLd + t] = c;
+    cs[j * 66 + (t & 31) * 2 + (t >> 5)] = c;
   }
   __syncthreads();
 
   double* tile = tiles + (size_t)warp * kQhInst * kQhTileLd;
-  const double* gl = gs + lane;
-  const double* cl = cs + lane;
+  const double2* gl = reinterpret_cast<const double2*>(gs) + lane;
+  const double2* cl = reinterpret_cast<const double2*>(cs) + lane;
   const int e_begin = a.warp_nz_ptr[warp], e_end = a.warp_nz_ptr[warp + 1];
   int ci = a.warp_chunk_ptr[warp];
-  double acc = 0.0, part = 0.0;
+  double acc0 = 0.0, acc1 = 0.0, p0 = 0.0, p1 = 0.0;
   int r = 0;
-  // the warp's record stream comes in batches of 32: one coalesced 16-byte load
+  // The warp's record stream comes in batches of 32: one coalesced 16-byte load
   // per lane (the next batch is in flight while this one is consumed), parked in
-  // a 512-byte ring and read back as warp-uniform LDS.128
+  // a 512-byte ring and read back as warp-uniform LDS.128.  A ballot marks the
+  // records that end a segment, so the runs between them are a branch-free loop.
   QhNz next = {0.0, 0, 0};
   if (e_begin + lane < e_end) next = a.nz[e_begin + lane];
   for (int base = e_begin; base < e_end; base += 32) {
+    const int cnt = min(32, e_end - base);
     ring[lane] = next;
+    const unsigned flagged = __ballot_sync(0xffffffffu, lane < cnt && (next.meta & ~kQhTermMask));
     if (base + 32 + lane < e_end) next = a.nz[base + 32 + lane];
     __syncwarp();
-    const int cnt = min(32, e_end - base);
+    int i = 0;
+    while (i < cnt) {
+      const unsigned rest = flagged >> i;
+      const int stop = rest ? i + __ffs(rest) : cnt;  // one past the next flagged record
 #pragma unroll 4
-    for (int i = 0; i < cnt; ++i) {
-      const QhNz rec = ring[i];
-      part = fma(rec.val, gl[rec.col * kQhLd], part);
-      if (rec.meta & ~kQhTermMask) {  // warp-uniform
-        acc = fma(cl[(rec.meta & kQhTermMask) * kQhLd], part, acc);
-        part = 0.0;
-        if (rec.meta & kQhEndRow) {
-          tile[lane * kQhTileLd + r] = acc;
-          acc = 0.0;
-          ++r;
-        }
-        if (rec.meta & kQhEndChunk) {
-          const int2 chunk = a.chunks[ci++];  // (first row, rows)
-          __syncwarp();
-          // 8 lanes cover the chunk of one instance (64 contiguous bytes), 4 instances per pass
-          const bool is_q = chunk.x < a.nv;
-          double* out = is_q ? q : h;
-          if (out) {
-            const int rr = lane & (kQhChunk - 1), sub = lane / kQhChunk;
-            const long stride = is_q ? a.nv : a.nc;
-            const int row = is_q ? chunk.x : chunk.x - a.nv;
-            if (rr < chunk.y) {
+      for (; i < stop; ++i) {
+        const QhNz rec = ring[i];
+        const double2 g2 = gl[rec.col];
+        p0 = fma(rec.val, g2.x, p0);
+        p1 = fma(rec.val, g2.y, p1);
+      }
+      if (!rest) break;
+      const int meta = ring[i - 1].meta;  // the flagged record just consumed
+      const double2 c2 = cl[(meta & kQhTermMask) * 33];
+      acc0 = fma(c2.x, p0, acc0);
+      acc1 = fma(c2.y, p1, acc1);
+      p0 = p1 = 0.0;
+      if (meta & kQhEndRow) {
+        tile[lane * kQhTileLd + r] = acc0;
+        tile[(lane + 32) * kQhTileLd + r] = acc1;
+        acc0 = acc1 = 0.0;
+        ++r;
+      }
+      if (meta & kQhEndChunk) {
+        const int2 chunk = a.chunks[ci++];  // (first row, rows)
+        __syncwarp();
+        // 4 lanes cover the chunk of one instance (32 contiguous bytes), 8 instances per pass
+        const bool is_q = chunk.x < a.nv;
+        double* out = is_q ? q : h;
+        if (out) {
+          const int rr = lane & (kQhChunk - 1), sub = lane / kQhChunk;
+          const long stride = is_q ? a.nv : a.nc;
+          const int row = is_q ? chunk.x : chunk.x - a.nv;
+          if (rr < chunk.y) {
 #pragma unroll
-              for (int it = 0; it < kQhInst / (32 / kQhChunk); ++it) {
-                const int t = it * (32 / kQhChunk) + sub;
-                if (t < group) out[(b0 + t) * stride + row + rr] = tile[t * kQhTileLd + rr];
-              }
+            for (int it = 0; it < kQhInst / (32 / kQhChunk); ++it) {
+              const int t = it * (32 / kQhChunk) + sub;
+              if (t < group) out[(b0 + t) * stride + row + rr] = tile[t * kQhTileLd + rr];
             }
           }
-          __syncwarp();
-          r = 0;
         }
+        __syncwarp();
+        r = 0;
       }
     }
     __syncwarp();
   }
+  }  // groups of instances
 }
 
 size_t qh_smem_bytes(const QhArgs& a) {
-  return sizeof(double) * ((size_t)(a.ng + 1 + a.n_terms) * kQhLd +
+  return sizeof(double) * ((size_t)(a.ng + 1 + a.n_terms) * 66 +
                            (size_t)kQhWarps * kQhInst * kQhTileLd) +
          sizeof(QhNz) * kQhWarps * 32;
 }
@@ -239,9 +255,14 @@ int launch_qh(const QhArgs& a, const double* scalars, const double* given, doubl
   if (smem > 48 * 1024)
     MPCI_CUDA(cudaFuncSetAttribute(qh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));
-  const long blocks = (batch + kQhInst - 1) / kQhInst;
-  if (blocks > 2147483647L) return fail(-6, "assemble: batch %ld too large for one launch", batch);
-  qh_kernel<<<(unsigned)blocks, kQhWarps * 32, smem, st>>>(a, scalars, given, q, h, batch);
+  int dev = 0, sms = 148, per_sm = 1;
+  MPCI_CUDA(cudaGetDevice(&dev));
+  MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  MPCI_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, qh_kernel, kQhWarps * 32, smem));
+  const long groups = (batch + kQhInst - 1) / kQhInst;
+  const long resident = (long)sms * (per_sm < 1 ? 1 : per_sm);
+  const unsigned blocks = (unsigned)(groups < resident ? groups : resident);
+  qh_kernel<<<blocks, kQhWarps * 32, smem, st>>>(a, scalars, given, q, h, batch);
   MPCI_LAUNCH_CHECK("qh_kernel");
   return 0;
 }

@@ -18,14 +18,15 @@ struct StreamArgs {
 };
 
 // [q; h]: sparse rows, one instance per thread (mpci_assemble.cu)
-constexpr int kQhWarps = 8;   // warps of a block; each owns a list of row chunks
-constexpr int kQhChunk = 8;   // rows per chunk (one 64-byte run per instance)
+constexpr int kQhWarps = 16;  // warps of a block; each owns a list of row chunks
+constexpr int kQhChunk = 4;   // rows per chunk (one 32-byte run per instance)
 
 struct QhNz {      // 16 bytes; a warp's records are consecutive, in processing order
   double val;
-  int col;         // index into the staged [given; 1] of the instance
+  int col;         // column of [given; 1] times kQhColStride (index into the staged double2s)
   int meta;        // term | kQhEndSeg | kQhEndRow | kQhEndChunk
 };
+constexpr int kQhColStride = 33;  // double2 per staged column: 32 lanes x 2 instances, padded
 constexpr int kQhTermMask = 0xff;
 constexpr int kQhEndSeg = 0x100;    // last non-zero of a (row, term) segment
 constexpr int kQhEndRow = 0x200;    // ... of a row: the accumulator is the result
@@ -58,4 +59,8 @@ struct mpci_plan {
   double* slot_out[2];  // P | q | G | h
   cudaStream_t streams[2];
   cudaEvent_t slot_free[2];
+  // mpci_assemble runs the (shared-memory bound) [q;h] kernel beside the
+  // (HBM bound) P / G streams: a side stream forked from the caller's stream
+  mutable cudaStream_t side;
+  mutable cudaEvent_t fork, join;
 };
