@@ -154,7 +154,7 @@ def run_own(args):
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    from mpc_interface_b200 import Param, device
+    from mpc_interface_b200 import Param, device, sharding
     from mpc_interface_b200.examples import synthetic
     from mpc_interface_b200.examples.biped import default_configuration, formulate_biped
 
@@ -166,8 +166,7 @@ def run_own(args):
     ops = form._ops()
     nv, ng, nc = plan.nv, plan.ng, plan.nc
     # the whole logical batch comes from one seed; a rank takes its contiguous shard
-    vals = synthetic.biped_inputs(SEED, B * world, HORIZON)
-    vals = {k: v[rank * B:(rank + 1) * B] for k, v in vals.items()}
+    vals = sharding.shard_inputs(synthetic.biped_inputs(SEED, B * world, HORIZON), rank, world)
     given_h = synthetic.pack_given(form.given_ID, form.given_len, vals, B)
     params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
     scalars_h = plan.slots.evaluate(params, B)
@@ -205,10 +204,7 @@ def run_own(args):
     barrier()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
-    if distributed:
-        t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms = sharding.max_over_ranks(ms, world, "cuda")
 
     # per-kernel times on the launching stream (P stream, G stream, [q;h])
     def timed(fn, reps):
@@ -228,10 +224,8 @@ def run_own(args):
     t_qh = timed(lambda: call(null, out.q.data_ptr(), null, out.h.data_ptr()), reps)
 
     # optional final gather (not on the data path): per-shard checksums over NCCL
-    checksum = torch.stack([out.q.sum(), out.h.sum(), out.P.sum(), out.G.sum()])
-    if distributed:
-        gathered = [torch.zeros_like(checksum) for _ in range(world)]
-        dist.all_gather(gathered, checksum)
+    gathered = sharding.gather_small(sharding.checksums(out), world)
+    assert len(gathered) == world and all(bool(torch.isfinite(g).all()) for g in gathered)
 
     result = None
     if rank == 0:

@@ -1,0 +1,83 @@
+"""Data parallelism over independent MPC instances.
+
+Instances never interact (nothing in body.py:236-348 couples two of them), so a
+batch is split into contiguous shards, one per rank / GPU, and every rank
+assembles its shard with no data-path collective.  ``torch.distributed`` is
+used only around the path: a barrier for timing and an optional gather of small
+per-shard results (checksums, or q / h) for verification -- NCCL on the GPU box,
+gloo in the CPU tests.
+"""
+import numpy as np
+
+
+def shard_range(total, rank, world):
+    """Contiguous shard [start, stop) of ``total`` instances for ``rank``: sizes
+    differ by at most one, earlier ranks take the longer shards."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("rank {} outside a world of {}".format(rank, world))
+    base, extra = divmod(int(total), world)
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)
+
+
+def shard_inputs(values, rank, world):
+    """Slices every per-instance array of ``values`` ({name: array[B, ...]}) to
+    the rank's shard.  The logical batch is generated from ONE seed and sliced,
+    so results do not depend on the number of ranks."""
+    total = len(next(iter(values.values())))
+    start, stop = shard_range(total, rank, world)
+    return {name: array[start:stop] for name, array in values.items()}
+
+
+def checksums(out):
+    """[sum(q), sum(h), sum(P), sum(G)] of a shard as a float64 tensor on the
+    shard's device (a cheap fingerprint for the optional gather)."""
+    import torch
+
+    return torch.stack([out.q.sum(), out.h.sum(), out.P.sum(), out.G.sum()]).to(torch.float64)
+
+
+def gather_small(tensor, world):
+    """All-gather of a small per-shard tensor (same shape on every rank);
+    returns the list ordered by rank.  Not on the data path."""
+    import torch
+    import torch.distributed as dist
+
+    if world == 1 or not dist.is_initialized():
+        return [tensor]
+    parts = [torch.zeros_like(tensor) for _ in range(world)]
+    dist.all_gather(parts, tensor)
+    return parts
+
+
+def gather_rows(local, total, rank, world):
+    """All-gather of ragged row blocks (e.g. q or h of each shard) into the
+    [total, ...] array of the logical batch, in instance order."""
+    import torch
+    import torch.distributed as dist
+
+    if world == 1 or not dist.is_initialized():
+        return local
+    longest = shard_range(total, 0, world)
+    width = longest[1] - longest[0]
+    padded = torch.zeros((width,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    padded[: local.shape[0]] = local
+    parts = [torch.zeros_like(padded) for _ in range(world)]
+    dist.all_gather(parts, padded)
+    rows = []
+    for r, part in enumerate(parts):
+        start, stop = shard_range(total, r, world)
+        rows.append(part[: stop - start])
+    return torch.cat(rows)
+
+
+def max_over_ranks(value, world, device="cpu"):
+    """Max of a host float over the ranks (the timing rule of the bench)."""
+    import torch
+    import torch.distributed as dist
+
+    if world == 1 or not dist.is_initialized():
+        return float(value)
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())

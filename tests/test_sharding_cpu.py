@@ -1,0 +1,83 @@
+"""The N>1 host logic on CPU: world_size-2 gloo processes assemble their shards
+of one logical batch (NumPy stand-in backend: no GPU here) and the gathered
+result must equal the single-process result, bit for bit."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from mpc_interface_b200 import sharding
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+BATCH, N = 11, 12  # odd batch: ragged shards
+
+
+def test_shard_ranges_cover_the_batch():
+    for total in (0, 1, 7, 64, 1048576):
+        for world in (1, 2, 3, 8):
+            spans = [sharding.shard_range(total, r, world) for r in range(world)]
+            assert spans[0][0] == 0 and spans[-1][1] == total
+            assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
+            sizes = [b - a for a, b in spans]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        sharding.shard_range(10, 2, 2)
+
+
+def _assemble(rank, world):
+    sys.path.insert(0, HERE)
+    from _numpy_backend import NumpyBackend
+    from oracle import qp_oracle
+    import mpc_interface_b200.tools as tools
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+    from mpc_interface_b200.examples.biped import default_configuration, formulate_biped
+
+    tools.extend_matrices = qp_oracle.extend_matrices  # CPU test only
+    form = formulate_biped(default_configuration(N), omega=Param("omega"),
+                           target_vel=[Param("vel_x"), Param("vel_y")], backend=NumpyBackend())
+    vals = sharding.shard_inputs(synthetic.biped_inputs(7, BATCH, N), rank, world)
+    count = len(vals["omega"])
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, count)
+    out = form.generate_all_qp_matrices_batched(
+        given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")})
+    return out
+
+
+def _worker(rank, world, port, result_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    out = _assemble(rank, world)
+    q = sharding.gather_rows(torch.from_numpy(out.q), BATCH, rank, world)
+    h = sharding.gather_rows(torch.from_numpy(out.h), BATCH, rank, world)
+    sums = torch.tensor([out.q.sum(), out.h.sum(), out.P.sum(), out.G.sum()], dtype=torch.float64)
+    parts = sharding.gather_small(sums, world)
+    slowest = sharding.max_over_ranks(1.0 + rank, world)
+    dist.barrier()
+    if rank == 0:
+        np.savez(os.path.join(result_dir, "gathered.npz"), q=q.numpy(), h=h.numpy(),
+                 sums=torch.stack(parts).numpy(), slowest=slowest)
+    dist.destroy_process_group()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_two_gloo_ranks_reproduce_the_single_process_batch(tmp_path):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    got = np.load(tmp_path / "gathered.npz")
+    whole = _assemble(0, 1)
+    assert np.array_equal(got["q"], whole.q) and np.array_equal(got["h"], whole.h)
+    start, stop = sharding.shard_range(BATCH, 1, world)
+    assert np.isclose(got["sums"][1, 2], whole.P[start:stop].sum(), rtol=1e-12)
+    assert np.isclose(got["sums"][:, 3].sum(), whole.G.sum(), rtol=1e-12)
+    assert float(got["slowest"]) == 2.0
