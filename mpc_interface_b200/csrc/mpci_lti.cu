@@ -14,6 +14,7 @@
 //             the displacement recursion (O(N^2) flops)
 //   4. q   -- correlation of Gam with r
 //   5. G,h -- generated row by row, 16-byte coalesced stores
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <vector>
@@ -34,6 +35,8 @@ struct LtiArgs {
   int LD;  // kPadL + Nk + kPadR
   const double *Qxx, *Quu, *Tx, *Tu, *cx, *cu, *arrow, *bound;  // device tables
   const int* grp_state;  // 1 if the group has a non-zero cx
+  const int2* tiles;     // DMMA warp tiles (row tile, column tile) of one (j, j') block, longest first
+  int n_tiles;
   const double *A, *B, *x0, *scalars;
   long strideA, strideB;
   double *P, *q, *G, *h;
@@ -47,7 +50,7 @@ struct Smem {
 
 __host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD) {
   return (size_t)4 * n * n + (size_t)(N + 1) * n * (m + 1) + (size_t)2 * n * m * LD +
-         (size_t)n * N + n + m + (size_t)m * (N + 2);
+         (size_t)n * N + n + m + (size_t)m * (2 * N + 2) + N + m + n;
 }
 
 __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
@@ -96,28 +99,42 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   for (int e = tid; e < n + m; e += kThreads) {
     const double* T = (e < n) ? a.Tx + (long)e * (a.S + 1) : a.Tu + (long)(e - n) * (a.S + 1);
     double acc = T[a.S];
+#pragma unroll 4
     for (int k = 0; k < a.S; ++k) acc = fma(T[k], a.scalars[b * a.S + k], acc);
     if (e < n) s.tx[e] = acc; else s.tu[e - n] = acc;
   }
   __syncthreads();
 
-  // prefix doubling: Gam'_{have+d} = A^have Gam'_d,  A^(2 have) = (A^have)^2
+  // prefix doubling: Gam'_{have+d} = A^have Gam'_d,  A^(2 have) = (A^have)^2.
+  // A thread keeps one entry (i, c) of the n x (m+1) block and strides over d, so
+  // the index arithmetic (integer divisions) is done once, not per element.
   double* M0 = s.M0;
   double* M1 = s.M1;
   const int blk = n * w;
+  const int lane = tid & 31, warp = tid >> 5;
+  const int per = blk <= kThreads ? blk : kThreads;  // entries handled per pass over the block
+  const int dgroups = kThreads / per;                // concurrent values of d
+  const int dg = tid / per;
+  const int sq_i = tid / n, sq_c = tid % n;
   for (int have = 1; have < N + 1;) {
     const int cnt = min(have, N + 1 - have);
-    const int total = cnt * blk;
-    for (int e = tid; e < total + n * n; e += kThreads) {
-      if (e < total) {
-        const int d = e / blk, rem = e % blk, i = rem / w, c = rem % w;
-        const double* src = s.gp + (size_t)d * blk + c;
+    for (int rem = tid % per; rem < blk; rem += per) {
+      const int i = rem / w;
+      const double* Mi = M0 + i * n;
+      if (dg < dgroups)
+        for (int d = dg; d < cnt; d += dgroups) {
+          const double* src = s.gp + (size_t)d * blk + (rem - i * w);
+          double acc = 0.0;
+#pragma unroll 4
+          for (int l = 0; l < n; ++l) acc = fma(Mi[l], src[l * w], acc);
+          s.gp[(size_t)(have + d) * blk + rem] = acc;
+        }
+    }
+    if (have + cnt < N + 1) {  // the next power is only needed for another round
+      for (int e2 = tid; e2 < n * n; e2 += kThreads) {
+        const int i = (e2 == tid) ? sq_i : e2 / n, c = (e2 == tid) ? sq_c : e2 % n;
         double acc = 0.0;
-        for (int l = 0; l < n; ++l) acc = fma(M0[i * n + l], src[l * w], acc);
-        s.gp[(size_t)(have + d) * blk + rem] = acc;
-      } else {
-        const int e2 = e - total, i = e2 / n, c = e2 % n;
-        double acc = 0.0;
+#pragma unroll 4
         for (int l = 0; l < n; ++l) acc = fma(M0[i * n + l], M0[l * n + c], acc);
         M1[e2] = acc;
       }
@@ -128,27 +145,37 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   }
 
   // zero-padded generators: gz[i][j][kPadL + d] = Gam_d[i][j], wz = (Qxx Gam_d)[i][j]
+  // (a warp per (i, j) pair, lanes along d)
   const int LD = a.LD;
-  for (int e = tid; e < n * m * LD; e += kThreads) {
-    const int x = e % LD, ij = e / LD, i = ij / m, j = ij % m;
-    const int d = x - kPadL;
-    double g = 0.0, wv = 0.0;
-    if (d >= 0 && d < N) {
-      const double* src = s.gp + (size_t)d * blk + j;
-      g = src[i * w];
-      for (int l = 0; l < n; ++l) wv = fma(s.Q[i * n + l], src[l * w], wv);
+  for (int ij = warp; ij < n * m; ij += kWarps) {
+    const int i = ij / m, j = ij - i * m;
+    const double* Qi = s.Q + i * n;
+    double* gdst = s.gz + (size_t)ij * LD;
+    double* wdst = s.wz + (size_t)ij * LD;
+    for (int x = lane; x < LD; x += 32) {
+      const int d = x - kPadL;
+      double g = 0.0, wv = 0.0;
+      if (d >= 0 && d < N) {
+        const double* src = s.gp + (size_t)d * blk + j;
+        g = src[i * w];
+#pragma unroll 4
+        for (int l = 0; l < n; ++l) wv = fma(Qi[l], src[l * w], wv);
+      }
+      gdst[x] = g;
+      wdst[x] = wv;
     }
-    s.gz[e] = g;
-    s.wz[e] = wv;
   }
   // r[i][k] = sum_l sym(Qxx)[i][l] f_k[l] - tx[i],  f_k = Gam'_{k+1}[:, m]
-  for (int e = tid; e < n * N; e += kThreads) {
-    const int i = e / N, k = e % N;
-    const double* f = s.gp + (size_t)(k + 1) * blk + m;
-    double acc = -s.tx[i];
-    for (int l = 0; l < n; ++l)
-      acc = fma(0.5 * (s.Q[i * n + l] + s.Q[l * n + i]), f[l * w], acc);
-    s.r[e] = acc;
+  for (int i = warp; i < n; i += kWarps) {
+    const double txi = s.tx[i];
+    for (int k = lane; k < N; k += 32) {
+      const double* f = s.gp + (size_t)(k + 1) * blk + m;
+      double acc = -txi;
+#pragma unroll 4
+      for (int l = 0; l < n; ++l)
+        acc = fma(0.5 * (s.Q[i * n + l] + s.Q[l * n + i]), f[l * w], acc);
+      s.r[(size_t)i * N + k] = acc;
+    }
   }
   __syncthreads();
 }
@@ -165,30 +192,37 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
   const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
-  const int np8 = (N + 7) / 8;
-  const int RT = (np8 + TM - 1) / TM, CT = (np8 + TN - 1) / TN;
-  const int tiles = m * m * RT * CT;
+  const int mm = m * m;
   const bool vec_ok = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0);
 
-  for (int tile = warp; tile < tiles; tile += kWarps) {
-    // long k-loops (small p0, p0') first within every (j, j') block
-    const int ct = tile % CT, rt = (tile / CT) % RT, jj = tile / (CT * RT);
-    const int j = jj / m, jp = jj % m;
-    const int p0 = rt * 8 * TM, q0 = ct * 8 * TN;
+  // tiles are sorted by the length of their k-loop and dealt round-robin, the
+  // (j, j') blocks innermost: the eight warps get nearly equal work
+  for (int idx = warp; idx < a.n_tiles * mm; idx += kWarps) {
+    const int tt = idx / mm, jj = idx - tt * mm;
+    const int2 rc = a.tiles[tt];
+    const int j = jj / m, jp = jj - j * m;
+    const int p0 = rc.x * 8 * TM, q0 = rc.y * 8 * TN;
     // k runs downwards from N-1 in steps of 4 (lane t takes k = N-1-s0-t) until
-    // it passes max(p0, q0): below that every product has a factor with d < 0
+    // it passes max(p, p') of the 8x8 sub-tile: below that every product has a
+    // factor with d < 0 (block-triangular skipping, per sub-tile)
     const int span = N - max(p0, q0);
+    int sub_span[TM][TN];
     double acc[TM][TN][2];
 #pragma unroll
     for (int x = 0; x < TM; ++x)
 #pragma unroll
-      for (int y = 0; y < TN; ++y) acc[x][y][0] = acc[x][y][1] = 0.0;
+      for (int y = 0; y < TN; ++y) {
+        acc[x][y][0] = acc[x][y][1] = 0.0;
+        sub_span[x][y] = N - max(p0 + 8 * x, q0 + 8 * y);
+      }
 
+    // steps in which every sub-tile is inside its span run without predicates
+    const int full = max(0, N - max(p0 + 8 * (TM - 1), q0 + 8 * (TN - 1))) & ~3;
     for (int i = 0; i < n; ++i) {
       const double* ga = s.gz + (size_t)(i * m + j) * LD + kPadL + (N - 1 - t - p0 - g);
       const double* wb = s.wz + (size_t)(i * m + jp) * LD + kPadL + (N - 1 - t - q0 - g);
 #pragma unroll 2
-      for (int s0 = 0; s0 < span; s0 += 4) {
+      for (int s0 = 0; s0 < full; s0 += 4) {
         double av[TM], bv[TN];
 #pragma unroll
         for (int x = 0; x < TM; ++x) av[x] = ga[-s0 - 8 * x];
@@ -198,6 +232,18 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
         for (int x = 0; x < TM; ++x)
 #pragma unroll
           for (int y = 0; y < TN; ++y) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
+      }
+      for (int s0 = full; s0 < span; s0 += 4) {  // the triangular tail of the tile
+        double av[TM], bv[TN];
+#pragma unroll
+        for (int x = 0; x < TM; ++x) av[x] = ga[-s0 - 8 * x];
+#pragma unroll
+        for (int y = 0; y < TN; ++y) bv[y] = wb[-s0 - 8 * y];
+#pragma unroll
+        for (int x = 0; x < TM; ++x)
+#pragma unroll
+          for (int y = 0; y < TN; ++y)
+            if (s0 < sub_span[x][y]) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
       }
     }
     // epilogue: + Quu[j][j'] on the diagonal of the block, store
@@ -234,37 +280,48 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
 template <int M>
 __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
   const int n = a.n, N = a.N, LD = a.LD, nv = M * a.N;
-  for (int dl = threadIdx.x; dl < 2 * N - 1; dl += kThreads) {
+  for (int dl0 = 0; dl0 < 2 * N - 1; dl0 += kThreads) {
+    const int dl = dl0 + threadIdx.x;
     const int delta = dl - (N - 1);
+    const bool has = dl < 2 * N - 1;
+    // rows of this diagonal, and of the warp's 32 diagonals together: the lanes
+    // of a warp walk the SAME row p in every step (coalesced stores)
+    const int p_hi = has ? min(N - 1, N - 1 - delta) : -1;
+    const int p_lo = has ? max(0, -delta) : N;
+    const int w_hi = __reduce_max_sync(0xffffffffu, p_hi);
+    const int w_lo = __reduce_min_sync(0xffffffffu, p_lo);
     double acc[M][M];
 #pragma unroll
     for (int x = 0; x < M; ++x)
 #pragma unroll
       for (int y = 0; y < M; ++y) acc[x][y] = 0.0;
-    const int p_hi = min(N - 1, N - 1 - delta), p_lo = max(0, -delta);
-    for (int p = p_hi; p >= p_lo; --p) {
+    double ruu[M][M];
+#pragma unroll
+    for (int x = 0; x < M; ++x)
+#pragma unroll
+      for (int y = 0; y < M; ++y) ruu[x][y] = (delta == 0) ? a.Quu[x * M + y] : 0.0;
+    for (int p = w_hi; p >= w_lo; --p) {
+      if (p > p_hi || p < p_lo) continue;  // this diagonal has no entry in row p
       const int c = p + delta;
       const double* ga = s.gz + kPadL + (N - 1 - p);
       const double* wb = s.wz + kPadL + (N - 1 - c);
       for (int i = 0; i < n; ++i) {
         double gv[M], wv[M];
 #pragma unroll
-        for (int x = 0; x < M; ++x) gv[x] = ga[(size_t)(i * M + x) * LD];
+        for (int x = 0; x < M; ++x) gv[x] = ga[(i * M + x) * LD];
 #pragma unroll
-        for (int y = 0; y < M; ++y) wv[y] = wb[(size_t)(i * M + y) * LD];
+        for (int y = 0; y < M; ++y) wv[y] = wb[(i * M + y) * LD];
 #pragma unroll
         for (int x = 0; x < M; ++x)
 #pragma unroll
           for (int y = 0; y < M; ++y) acc[x][y] = fma(gv[x], wv[y], acc[x][y]);
       }
+      double* dst = Pb + (size_t)p * nv + c;
 #pragma unroll
       for (int x = 0; x < M; ++x)
 #pragma unroll
-        for (int y = 0; y < M; ++y) {
-          double v = acc[x][y];
-          if (delta == 0) v += a.Quu[x * M + y];
-          __stcs(Pb + (size_t)(x * N + p) * nv + (size_t)y * N + c, v);
-        }
+        for (int y = 0; y < M; ++y)
+          __stcs(dst + (size_t)x * N * nv + y * N, acc[x][y] + ruu[x][y]);
     }
   }
 }
@@ -272,14 +329,21 @@ __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __res
 // general m: one (j, j') block at a time
 __device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
   const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
-  const int diag = 2 * N - 1;
-  for (int e = threadIdx.x; e < m * m * diag; e += kThreads) {
-    const int dl = e % diag, jj = e / diag, j = jj / m, jp = jj % m;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int dchunks = (2 * N - 1 + 31) / 32;  // a warp takes 32 diagonals of one block
+  for (int item = warp; item < m * m * dchunks; item += kWarps) {
+    const int jj = item / dchunks, dc = item - jj * dchunks, j = jj / m, jp = jj - j * m;
+    const int dl = dc * 32 + lane;
     const int delta = dl - (N - 1);
-    const int p_hi = min(N - 1, N - 1 - delta), p_lo = max(0, -delta);
+    const bool has = dl < 2 * N - 1;
+    const int p_hi = has ? min(N - 1, N - 1 - delta) : -1;
+    const int p_lo = has ? max(0, -delta) : N;
+    const int w_hi = __reduce_max_sync(0xffffffffu, p_hi);
+    const int w_lo = __reduce_min_sync(0xffffffffu, p_lo);
     const double ruu = (delta == 0) ? a.Quu[j * m + jp] : 0.0;
     double acc = 0.0;
-    for (int p = p_hi; p >= p_lo; --p) {
+    for (int p = w_hi; p >= w_lo; --p) {
+      if (p > p_hi || p < p_lo) continue;
       const int c = p + delta;
       for (int i = 0; i < n; ++i)
         acc = fma(s.gz[(size_t)(i * m + j) * LD + kPadL + (N - 1 - p)],
@@ -295,14 +359,22 @@ __device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* _
 __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ qb) {
   const int n = a.n, m = a.m, N = a.N, LD = a.LD;
   for (int e = threadIdx.x; e < m * N; e += kThreads) {
-    const int j = e / N, p = e % N;
-    double acc = 0.0;
+    const int j = e / N, p = e - j * N;
+    const int len = N - p;
+    double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;  // four chains hide the DFMA latency
     for (int i = 0; i < n; ++i) {
-      const double* gam = s.gz + (size_t)(i * m + j) * LD + kPadL;
+      const double* gam = s.gz + (size_t)(i * m + j) * LD + kPadL;  // warp-uniform reads
       const double* r = s.r + (size_t)i * N + p;
-      for (int d = 0; d < N - p; ++d) acc = fma(gam[d], r[d], acc);
+      int d = 0;
+      for (; d + 3 < len; d += 4) {
+        acc0 = fma(gam[d], r[d], acc0);
+        acc1 = fma(gam[d + 1], r[d + 1], acc1);
+        acc2 = fma(gam[d + 2], r[d + 2], acc2);
+        acc3 = fma(gam[d + 3], r[d + 3], acc3);
+      }
+      for (; d < len; ++d) acc0 = fma(gam[d], r[d], acc0);
     }
-    qb[e] = acc - s.tu[j];
+    qb[e] = ((acc0 + acc1) + (acc2 + acc3)) - s.tu[j];
   }
 }
 
@@ -310,31 +382,39 @@ __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ q
 // phase 5: constraint rows.  Group g, row k, column (j, p):
 //   G = arrow[k] * ((p <= k ? (cx . Gam_{k-p})[j] : 0) + (p == k ? cu[j] : 0))
 //   h = bound[k] - arrow[k] * cx . f_k
-// A warp writes one row at a time, a lane two consecutive doubles (16 bytes).
+// With cgz[j][y] = (cx . Gam_{N-1-y})[j] for y < N and 0 for N <= y < 2N, row k
+// of block j is the window cgz[j][N-1-k .. 2N-2-k]: a sliding copy.  A lane keeps
+// its two columns and walks down the rows; a warp writes 512 contiguous bytes.
 // ---------------------------------------------------------------------------
 __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restrict__ Gb,
                                 double* __restrict__ hb) {
   const int n = a.n, m = a.m, N = a.N, w = a.m + 1, nv = a.m * a.N, tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
   const int blk = n * w;
-  const int cgld = N + 2;
-  const bool vec_ok = (nv % 2 == 0) && (N % 2 == 0) && Gb &&
-                      ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0);
+  const int cgld = 2 * N + 2;
+  double* arrow = s.cg + (size_t)m * cgld;  // [N]   the group's tables, staged per group
+  double* cu = arrow + N;                    // [m]
+  double* cx = cu + m;                       // [n]
+  const bool vec_ok = (N % 2 == 0) && Gb && ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0);
   for (int grp = 0; grp < a.n_groups; ++grp) {
-    const double* cx = a.cx + (size_t)grp * n;
-    const double* cu = a.cu + (size_t)grp * m;
-    const double* arrow = a.arrow + (size_t)grp * N;
     const bool state = a.grp_state[grp] != 0;
-    __syncthreads();  // cg of the previous group is no longer read
+    __syncthreads();  // the previous group's tables are no longer read
+    for (int e = tid; e < N + m + n; e += kThreads)
+      arrow[e] = (e < N) ? a.arrow[(size_t)grp * N + e]
+                         : (e < N + m ? a.cu[(size_t)grp * m + (e - N)]
+                                      : a.cx[(size_t)grp * n + (e - N - m)]);
+    __syncthreads();
     if (state) {
-      // cg[j][d] = sum_i cx[i] Gam_d[i][j]
-      for (int e = tid; e < m * N; e += kThreads) {
-        const int j = e / N, d = e % N;
-        const double* src = s.gp + (size_t)d * blk + j;
-        double acc = 0.0;
-        for (int i = 0; i < n; ++i) acc = fma(cx[i], src[i * w], acc);
-        s.cg[j * cgld + d] = acc;
-      }
+      for (int j = warp; j < m; j += kWarps)
+        for (int y = lane; y < 2 * N; y += 32) {
+          double acc = 0.0;
+          if (y < N) {
+            const double* src = s.gp + (size_t)(N - 1 - y) * blk + j;
+#pragma unroll 4
+            for (int i = 0; i < n; ++i) acc = fma(cx[i], src[i * w], acc);
+          }
+          s.cg[j * cgld + y] = acc;
+        }
       __syncthreads();
     }
     if (hb) {
@@ -342,34 +422,42 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
         double acc = 0.0;
         if (state) {
           const double* f = s.gp + (size_t)(k + 1) * blk + m;
+#pragma unroll 4
           for (int i = 0; i < n; ++i) acc = fma(cx[i], f[i * w], acc);
         }
         hb[(size_t)grp * N + k] = a.bound[(size_t)grp * N + k] - arrow[k] * acc;
       }
     }
     if (!Gb) continue;
-    for (int k = warp; k < N; k += kWarps) {
+    double* rows = Gb + (size_t)grp * N * nv;
+    for (int k = warp; k < N; k += kWarps) {  // a warp writes whole rows: contiguous nv doubles
       const double ak = arrow[k];
-      double* row = Gb + ((size_t)grp * N + k) * nv;
+      double* row = rows + (size_t)k * nv;
       if (vec_ok) {
-        for (int c = 2 * lane; c < nv; c += 64) {  // c and c+1 share j because N is even
-          const int j = c / N, p = c % N;
+        int j = 0, p = 2 * lane;  // column c = j N + p, advanced without divisions
+        while (p >= N) { p -= N; ++j; }
+        for (int c = 2 * lane; c < nv; c += 64) {
           double v0 = 0.0, v1 = 0.0;
           if (state) {
-            if (p <= k) v0 = s.cg[j * cgld + (k - p)];
-            if (p + 1 <= k) v1 = s.cg[j * cgld + (k - p - 1)];
+            const double* win = s.cg + j * cgld + (N - 1 - k) + p;
+            v0 = win[0];
+            v1 = win[1];
           }
           if (p == k) v0 += cu[j];
           if (p + 1 == k) v1 += cu[j];
           __stcs(reinterpret_cast<double2*>(row + c), make_double2(ak * v0, ak * v1));
+          p += 64;
+          while (p >= N) { p -= N; ++j; }
         }
       } else {
+        int j = 0, p = lane;
+        while (p >= N) { p -= N; ++j; }
         for (int c = lane; c < nv; c += 32) {
-          const int j = c / N, p = c % N;
-          double v = 0.0;
-          if (state && p <= k) v = s.cg[j * cgld + (k - p)];
+          double v = state ? s.cg[j * cgld + (N - 1 - k) + p] : 0.0;
           if (p == k) v += cu[j];
           __stcs(row + c, ak * v);
+          p += 32;
+          while (p >= N) { p -= N; ++j; }
         }
       }
     }
@@ -441,12 +529,26 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
     oar = push(d->grp_arrow, (size_t)G * N);
     obd = push(d->grp_bound, (size_t)G * N);
   }
+  // DMMA warp tiles of one (j, j') block, sorted by the length of their k-loop
+  const int np8 = (N + 7) / 8, RT = (np8 + TM - 1) / TM, CT = (np8 + TN - 1) / TN;
+  std::vector<int> tile_rc;
+  for (int span = N; span > 0; --span)
+    for (int rt = 0; rt < RT; ++rt)
+      for (int ct = 0; ct < CT; ++ct)
+        if (N - std::max(rt * 8 * TM, ct * 8 * TN) == span) {
+          tile_rc.push_back(rt);
+          tile_rc.push_back(ct);
+        }
   std::vector<int> flags(G > 0 ? G : 1, 0);
   for (int g = 0; g < G; ++g)
     for (int i = 0; i < n; ++i)
       if (d->grp_cx[(size_t)g * n + i] != 0.0) flags[g] = 1;
   mpci_lti_plan* p = new mpci_lti_plan();
   std::memset(p, 0, sizeof(*p));
+  const size_t n_flags = flags.size();
+  flags.insert(flags.end(), tile_rc.begin(), tile_rc.end());  // flags | tiles (int2), 8-byte aligned
+  if (n_flags % 2) flags.insert(flags.begin() + n_flags, 0);
+  const size_t tiles_off = (n_flags + 1) / 2 * 2;
   const size_t bytes_d = host.size() * sizeof(double), bytes_i = flags.size() * sizeof(int);
   cudaError_t e = cudaMalloc(&p->dev, bytes_d + bytes_i);
   if (e == cudaSuccess) e = cudaMemcpy(p->dev, host.data(), bytes_d, cudaMemcpyHostToDevice);
@@ -472,6 +574,8 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   a.Qxx = base + oQ; a.Quu = base + oR; a.Tx = base + oTx; a.Tu = base + oTu;
   a.cx = base + ocx; a.cu = base + ocu; a.arrow = base + oar; a.bound = base + obd;
   a.grp_state = reinterpret_cast<const int*>(static_cast<const char*>(p->dev) + bytes_d);
+  a.tiles = reinterpret_cast<const int2*>(a.grp_state + tiles_off);
+  a.n_tiles = (int)tile_rc.size() / 2;
   p->smem_bytes = smem;
   p->blocks_per_sm = per_sm < 1 ? 1 : per_sm;
   *out = p;
@@ -491,13 +595,16 @@ extern "C" double mpci_lti_hessian_flops(const mpci_lti_plan* p, int mode) {
   if (mode == MPCI_LTI_HESSIAN_RECURSION) return 2.0 * n * m * m * N * N + 2.0 * n * n * m * N;
   // executed by hessian_dmma: per warp tile n * (Nk - kstart)/4 steps of TM*TN DMMAs (512 flop)
   const int np8 = (p->N + 7) / 8, RT = (np8 + TM - 1) / TM, CT = (np8 + TN - 1) / TN;
-  double steps = 0.0;
+  double dmmas = 0.0;  // per (i, j, j'): one DMMA per 8x8 sub-tile and step of 4 inside its span
   for (int rt = 0; rt < RT; ++rt)
-    for (int ct = 0; ct < CT; ++ct) {
-      const int p0 = rt * 8 * TM, q0 = ct * 8 * TN;
-      steps += (p->N - (p0 > q0 ? p0 : q0) + 3) / 4;
-    }
-  return steps * n * m * m * TM * TN * 512.0 + 2.0 * n * n * m * N;
+    for (int ct = 0; ct < CT; ++ct)
+      for (int x = 0; x < TM; ++x)
+        for (int y = 0; y < TN; ++y) {
+          const int ps = rt * 8 * TM + 8 * x, qs = ct * 8 * TN + 8 * y;
+          const int span = p->N - (ps > qs ? ps : qs);
+          if (span > 0) dmmas += (span + 3) / 4;
+        }
+  return dmmas * n * m * m * 512.0 + 2.0 * n * n * m * N;
 }
 
 extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long strideA,
