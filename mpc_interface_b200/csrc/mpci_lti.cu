@@ -25,16 +25,15 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kPadL = 40;  // zeros before d = 0 of every generator (>= 8*max(TM,TN)+3)
-constexpr int kPadR = 8;   // zeros after d = N-1
+constexpr int kPadL = 36;  // zeros before d = 0 of every generator (>= 8*max(TM,TN)+3)
 constexpr int TM = 2, TN = 4;  // 8x8 DMMA tiles per warp tile (rows x cols)
 
 struct LtiArgs {
   int n, m, N, S, n_groups;
   int Nk;  // N rounded up to a multiple of 4
-  int LD;  // kPadL + Nk + kPadR
+  int LD;  // kPadL + Nk
   const double *Qxx, *Quu, *Tx, *Tu, *cx, *cu, *arrow, *bound;  // device tables
-  const int* grp_state;  // 1 if the group has a non-zero cx
+  const int* grp_state;  // bit 0: the group has a non-zero cx; bit 1: one arrow for all rows
   const int2* tiles;     // DMMA warp tiles (row tile, column tile) of one (j, j') block, longest first
   int n_tiles;
   const double *A, *B, *x0, *scalars;
@@ -45,12 +44,18 @@ struct LtiArgs {
 };
 
 struct Smem {
-  double *A, *M0, *M1, *Q, *gp, *gz, *wz, *r, *tx, *tu, *cg;
+  double *A, *M0, *M1, *Q, *gp, *gz, *wz, *r, *f, *tx, *tu, *cg;
 };
 
+// gp (the raw doubling output) is dead once gz, wz, r and f are built: the
+// constraint phase reuses its space (cg) for the row windows and group tables.
+__host__ __device__ inline size_t lti_scratch_doubles(int n, int m, int N) {
+  const size_t gp = (size_t)(N + 1) * n * (m + 1), cg = (size_t)m * 4 * N + N + m + n;
+  return ((gp > cg ? gp : cg) + 1) & ~(size_t)1;
+}
 __host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD) {
-  return (size_t)4 * n * n + (size_t)(N + 1) * n * (m + 1) + (size_t)2 * n * m * LD +
-         (size_t)n * N + n + m + (size_t)m * (2 * N + 2) + N + m + n;
+  return (size_t)4 * n * n + lti_scratch_doubles(n, m, N) + (size_t)2 * n * m * LD +
+         (size_t)2 * n * N + n + m;
 }
 
 __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
@@ -60,13 +65,14 @@ __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
   s.M0 = s.A + n * n;
   s.M1 = s.M0 + n * n;
   s.Q = s.M1 + n * n;
-  s.gp = s.Q + n * n;
-  s.gz = s.gp + (size_t)(N + 1) * n * (m + 1);
+  s.gp = s.Q + n * n;  // 4 n^2 doubles before it: 16-byte aligned (source of the bulk copies)
+  s.cg = s.gp;
+  s.gz = s.gp + lti_scratch_doubles(n, m, N);
   s.wz = s.gz + (size_t)n * m * a.LD;
   s.r = s.wz + (size_t)n * m * a.LD;
-  s.tx = s.r + (size_t)n * N;
+  s.f = s.r + (size_t)n * N;
+  s.tx = s.f + (size_t)n * N;
   s.tu = s.tx + n;
-  s.cg = s.tu + m;
   return s;
 }
 
@@ -175,6 +181,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
       for (int l = 0; l < n; ++l)
         acc = fma(0.5 * (s.Q[i * n + l] + s.Q[l * n + i]), f[l * w], acc);
       s.r[(size_t)i * N + k] = acc;
+      s.f[(size_t)i * N + k] = f[i * w];
     }
   }
   __syncthreads();
@@ -382,86 +389,106 @@ __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ q
 // phase 5: constraint rows.  Group g, row k, column (j, p):
 //   G = arrow[k] * ((p <= k ? (cx . Gam_{k-p})[j] : 0) + (p == k ? cu[j] : 0))
 //   h = bound[k] - arrow[k] * cx . f_k
-// With cgz[j][y] = (cx . Gam_{N-1-y})[j] for y < N and 0 for N <= y < 2N, row k
-// of block j is the window cgz[j][N-1-k .. 2N-2-k]: a sliding copy.  A lane keeps
-// its two columns and walks down the rows; a warp writes 512 contiguous bytes.
+// With cz[j][y] = (cx . Gam_{N-1-y})[j] for y < N-1, that plus cu[j] at y = N-1 and
+// 0 for N <= y < 2N, row k of block j is arrow[k] times the window
+// cz[j][N-1-k .. 2N-2-k]: a sliding copy.  When the arrow is the same for every
+// row (the usual case) cz is pre-scaled and the rows are written by the TMA engine:
+// one cp.async.bulk (shared -> global, N*8 bytes) per (row, block), issued by one
+// lane per warp; a second copy of cz shifted by one element keeps every source
+// 16-byte aligned.  Otherwise the warps scale and store the windows themselves.
 // ---------------------------------------------------------------------------
+__device__ __forceinline__ void bulk_store(double* dst, const double* src_smem, unsigned bytes) {
+  const unsigned src = (unsigned)__cvta_generic_to_shared(src_smem);
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n"
+               :: "l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+
 __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restrict__ Gb,
                                 double* __restrict__ hb) {
-  const int n = a.n, m = a.m, N = a.N, w = a.m + 1, nv = a.m * a.N, tid = threadIdx.x;
+  const int n = a.n, m = a.m, N = a.N, nv = a.m * a.N, tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
-  const int blk = n * w;
-  const int cgld = 2 * N + 2;
-  double* arrow = s.cg + (size_t)m * cgld;  // [N]   the group's tables, staged per group
-  double* cu = arrow + N;                    // [m]
-  double* cx = cu + m;                       // [n]
-  const bool vec_ok = (N % 2 == 0) && Gb && ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0);
+  const int czld = 2 * N;
+  double* cz = s.cg;                        // [m][2N]
+  double* cz1 = cz + (size_t)m * czld;      // [m][2N]   cz1[j][y] = cz[j][y + 1]
+  double* arrow = cz1 + (size_t)m * czld;   // [N]   the group's tables, staged per group
+  double* cu = arrow + N;                   // [m]
+  double* cx = cu + m;                      // [n]
+  const bool aligned = (N % 2 == 0) && Gb && ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0);
   for (int grp = 0; grp < a.n_groups; ++grp) {
-    const bool state = a.grp_state[grp] != 0;
-    __syncthreads();  // the previous group's tables are no longer read
+    const int flags = a.grp_state[grp];
+    const bool state = (flags & 1) != 0;
+    const bool bulk = aligned && (flags & 2);  // bit 1: the arrow is constant over the rows
+    if (lane == 0) bulk_wait_read();  // the TMA engine has read the previous group's windows
+    __syncthreads();
     for (int e = tid; e < N + m + n; e += kThreads)
       arrow[e] = (e < N) ? a.arrow[(size_t)grp * N + e]
                          : (e < N + m ? a.cu[(size_t)grp * m + (e - N)]
                                       : a.cx[(size_t)grp * n + (e - N - m)]);
     __syncthreads();
-    if (state) {
-      for (int j = warp; j < m; j += kWarps)
-        for (int y = lane; y < 2 * N; y += 32) {
-          double acc = 0.0;
-          if (y < N) {
-            const double* src = s.gp + (size_t)(N - 1 - y) * blk + j;
+    const double scale = bulk ? arrow[0] : 1.0;
+    for (int j = warp; j < m; j += kWarps)
+      for (int y = lane; y < 2 * N; y += 32) {
+        double acc = (y == N - 1) ? cu[j] : 0.0;
+        if (state && y < N) {
+          const double* src = s.gz + (size_t)j * a.LD + kPadL + (N - 1 - y);
 #pragma unroll 4
-            for (int i = 0; i < n; ++i) acc = fma(cx[i], src[i * w], acc);
-          }
-          s.cg[j * cgld + y] = acc;
+          for (int i = 0; i < n; ++i) acc = fma(cx[i], src[(size_t)i * m * a.LD], acc);
         }
-      __syncthreads();
-    }
+        acc *= scale;
+        cz[j * czld + y] = acc;
+        if (y > 0) cz1[j * czld + y - 1] = acc;
+        if (y == 2 * N - 1) cz1[j * czld + y] = 0.0;
+      }
     if (hb) {
       for (int k = tid; k < N; k += kThreads) {
         double acc = 0.0;
         if (state) {
-          const double* f = s.gp + (size_t)(k + 1) * blk + m;
 #pragma unroll 4
-          for (int i = 0; i < n; ++i) acc = fma(cx[i], f[i * w], acc);
+          for (int i = 0; i < n; ++i) acc = fma(cx[i], s.f[(size_t)i * N + k], acc);
         }
         hb[(size_t)grp * N + k] = a.bound[(size_t)grp * N + k] - arrow[k] * acc;
       }
     }
+    fence_async_smem();  // the windows must be visible to the async proxy
+    __syncthreads();
     if (!Gb) continue;
     double* rows = Gb + (size_t)grp * N * nv;
-    for (int k = warp; k < N; k += kWarps) {  // a warp writes whole rows: contiguous nv doubles
+    if (bulk) {
+      if (lane == 0) {
+        for (int k = warp; k < N; k += kWarps) {
+          const int start = N - 1 - k;
+          const double* win = (start & 1) ? cz1 + (start - 1) : cz + start;
+          double* row = rows + (size_t)k * nv;
+          for (int j = 0; j < m; ++j) bulk_store(row + j * N, win + j * czld, (unsigned)N * 8u);
+        }
+        bulk_commit();
+      }
+      continue;
+    }
+    for (int k = warp; k < N; k += kWarps) {
       const double ak = arrow[k];
       double* row = rows + (size_t)k * nv;
-      if (vec_ok) {
-        int j = 0, p = 2 * lane;  // column c = j N + p, advanced without divisions
-        while (p >= N) { p -= N; ++j; }
-        for (int c = 2 * lane; c < nv; c += 64) {
-          double v0 = 0.0, v1 = 0.0;
-          if (state) {
-            const double* win = s.cg + j * cgld + (N - 1 - k) + p;
-            v0 = win[0];
-            v1 = win[1];
-          }
-          if (p == k) v0 += cu[j];
-          if (p + 1 == k) v1 += cu[j];
-          __stcs(reinterpret_cast<double2*>(row + c), make_double2(ak * v0, ak * v1));
-          p += 64;
-          while (p >= N) { p -= N; ++j; }
+      const double* win = cz + (N - 1 - k);  // column c = j N + p reads win[c + j N]
+      if (aligned) {
+        for (int c = 2 * lane; c < nv; c += 64) {  // c and c+1 share j because N is even
+          int off = c;
+          for (int jj = 1; jj < m; ++jj) off += (c >= jj * N) ? N : 0;
+          __stcs(reinterpret_cast<double2*>(row + c), make_double2(ak * win[off], ak * win[off + 1]));
         }
       } else {
-        int j = 0, p = lane;
-        while (p >= N) { p -= N; ++j; }
         for (int c = lane; c < nv; c += 32) {
-          double v = state ? s.cg[j * cgld + (N - 1 - k) + p] : 0.0;
-          if (p == k) v += cu[j];
-          __stcs(row + c, ak * v);
-          p += 32;
-          while (p >= N) { p -= N; ++j; }
+          int off = c;
+          for (int jj = 1; jj < m; ++jj) off += (c >= jj * N) ? N : 0;
+          __stcs(row + c, ak * win[off]);
         }
       }
     }
   }
+  if (lane == 0) bulk_wait_read();
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -486,6 +513,7 @@ lti_assemble_kernel(LtiArgs a) {
       constraint_rows(a, s, a.G ? a.G + (size_t)b * nc * nv : nullptr,
                       a.h ? a.h + (size_t)b * nc : nullptr);
   }
+  if ((threadIdx.x & 31) == 0) bulk_wait_all();  // bulk stores of the last rows
 }
 
 }  // namespace
@@ -508,7 +536,7 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
       (d->n_groups && (!d->grp_cx || !d->grp_cu || !d->grp_arrow || !d->grp_bound)))
     return mpci::fail(-3, "lti_plan_create: NULL table");
   const int n = d->n, m = d->m, N = d->N, S = d->n_scalars, G = d->n_groups;
-  const int Nk = (N + 3) / 4 * 4, LD = kPadL + Nk + kPadR;
+  const int Nk = (N + 3) / 4 * 4, LD = kPadL + Nk;
   const size_t smem = sizeof(double) * lti_smem_doubles(n, m, N, LD);
   if (smem > 227 * 1024)
     return mpci::fail(-8, "lti_plan_create: n=%d m=%d N=%d needs %zu bytes of shared memory "
@@ -540,9 +568,13 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
           tile_rc.push_back(ct);
         }
   std::vector<int> flags(G > 0 ? G : 1, 0);
-  for (int g = 0; g < G; ++g)
+  for (int g = 0; g < G; ++g) {
     for (int i = 0; i < n; ++i)
-      if (d->grp_cx[(size_t)g * n + i] != 0.0) flags[g] = 1;
+      if (d->grp_cx[(size_t)g * n + i] != 0.0) flags[g] |= 1;
+    bool same = true;  // one arrow for all rows: the rows can be written as bulk copies
+    for (int k = 1; k < N; ++k) same = same && d->grp_arrow[(size_t)g * N + k] == d->grp_arrow[(size_t)g * N];
+    if (same) flags[g] |= 2;
+  }
   mpci_lti_plan* p = new mpci_lti_plan();
   std::memset(p, 0, sizeof(*p));
   const size_t n_flags = flags.size();

@@ -71,7 +71,18 @@ def test_lti_random_batches_against_oracle(dev, monkeypatch, nx, nu, N, batch):
     rows = np.random.default_rng(seed + 1).normal(size=[2, nx])
     vals = synthetic.generic_inputs(seed, batch, nx)
     refs = [Param("ref%d" % i) for i in range(nx)]
-    form = cases.formulate_generic(A[0], B[0], Q, R, N, rows, refs=refs)
+    from mpc_interface_b200 import Constraint
+
+    def with_row_arrows(f):
+        # one arrow / extreme per horizon sample: these rows cannot be bulk copies
+        signs = np.where(np.arange(N) % 3 == 0, -1.0, 1.0)
+        f.incorporate_constraint(
+            "per_row", Constraint("z0", np.linspace(1.0, 2.0, N), arrow=signs, center=np.linspace(-0.1, 0.1, N)))
+        f.incorporate_constraint("per_row_u", Constraint("u0", np.linspace(0.5, 1.5, N), arrow=-signs))
+        f.make_preview_matrices()
+        return f
+
+    form = with_row_arrows(cases.formulate_generic(A[0], B[0], Q, R, N, rows, refs=refs))
     params = {"ref%d" % i: vals["ref"][:, i] for i in range(nx)}
     outs = {}
     for mode in ("dmma", "recursion"):
@@ -80,8 +91,8 @@ def test_lti_random_batches_against_oracle(dev, monkeypatch, nx, nu, N, batch):
         outs[mode] = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
     monkeypatch.setattr(tools, "extend_matrices", orc.extend_matrices)
     for b in sorted({0, batch // 2, batch - 1}):
-        ref_form = cases.formulate_generic(
-            A[b], B[b], Q, R, N, rows, refs=list(vals["ref"][b]), backend=NumpyBackend())
+        ref_form = with_row_arrows(cases.formulate_generic(
+            A[b], B[b], Q, R, N, rows, refs=list(vals["ref"][b]), backend=NumpyBackend()))
         ref = orc.all_qp_matrices(ref_form, vals["x0"][b][:, None])
         for mode in outs:
             cases.assert_qp_close([x[b] for x in outs[mode]], ref)
