@@ -128,6 +128,24 @@ int mpci_assemble_host(mpci_plan* plan, const double* scalars_host, const double
                        double* P_host, double* q_host, double* G_host, double* h_host,
                        long batch, long chunk);
 
+/* ---- solver hand-off formats ---------------------------------------------
+ * The example feeds the solver scipy.sparse.csc_matrix(Q) / csc_matrix(A)
+ * (python/use_examples/simple_functional_example/biped_mpc_loop.py:57-60).  The
+ * sparsity pattern of P and G is the same for every instance of a batch, so the
+ * host derives it once (indices / indptr, bit-exact integers) and hands the
+ * library the constants gathered in that order; the same streaming kernels then
+ * write only the values:  Pc[b][e] = sum_t c_t(b) * DPc[t][e].
+ * DPc_dev [n_P_terms][nP], DGc_dev [n_G_terms][nG] (device, caller-owned; nP / nG
+ * even for 16-byte stores).  Any entry order works: CSC, upper triangle, ...   */
+int mpci_plan_set_compact(mpci_plan* plan, const double* DPc_dev, long nP,
+                          const double* DGc_dev, long nG);
+int mpci_assemble_compact(const mpci_plan* plan, const double* scalars_dev,
+                          const double* given_dev, double* Pc_dev, double* q_dev,
+                          double* Gc_dev, double* h_dev, long batch, void* stream);
+int mpci_assemble_compact_host(mpci_plan* plan, const double* scalars_host,
+                               const double* given_host, double* Pc_host, double* q_host,
+                               double* Gc_host, double* h_host, long batch, long chunk);
+
 /* Number of kernel launches one mpci_assemble call issues for this plan.    */
 int mpci_assemble_launches(const mpci_plan* plan);
 

@@ -232,14 +232,18 @@ class Formulation:
 
         return (stamp(costs), stamp(limits))
 
-    def _run(self, given, params, costs=None, limits=None, out=None):
+    def _run(self, given, params, costs=None, limits=None, out=None, layout="dense"):
         """Evaluates a (sub)plan for a batch: given [B, ng], params {name: [B]}."""
         compiled = self._compiled(costs, limits)
         if isinstance(given, (np.ndarray, list, tuple)):  # anything else: a device tensor
             given = np.asarray(given, dtype=np.float64)
         batch = given.shape[0]
         scalars = compiled.slots.evaluate(params or {}, batch)
-        return self._ops().assemble(compiled, scalars, given, batch, out)
+        if layout == "dense":
+            return self._ops().assemble(compiled, scalars, given, batch, out)
+        if layout not in ("csc", "csc_upper"):
+            raise ValueError("layout must be 'dense', 'csc' or 'csc_upper'")
+        return self._ops().assemble_csc(compiled, scalars, given, batch, out, layout == "csc_upper")
 
     def _single(self, given):
         given = np.asarray(given, dtype=np.float64)
@@ -322,7 +326,7 @@ class Formulation:
         return self._compiled().slots.names()
 
     def generate_all_qp_matrices_batched(self, given, params=None, out=None, dynamics=None,
-                                         hessian="dmma"):
+                                         hessian="dmma", layout="dense"):
         """Assembles a whole batch.
 
         given    : [B, given_len] float64 (numpy, or a CUDA torch tensor)
@@ -336,10 +340,18 @@ class Formulation:
         hessian  : with ``dynamics``: "dmma" (dense contraction on the FP64 tensor
                    cores) or "recursion" (displacement recursion, O(N^2) flops)
 
+        layout   : "dense" (default), or the solver hand-off "csc" / "csc_upper": only
+                   the CSC values of P and G are written (``QPBatchCSC``; one sparsity
+                   pattern for the batch, the int32 ``indices`` / ``indptr`` of
+                   ``scipy.sparse.csc_matrix`` as in biped_mpc_loop.py:57-58;
+                   "csc_upper" keeps the upper triangle of P for OSQP-style solvers)
+
         Returns a ``QPBatch`` with device tensors ``P [B,nv,nv]``, ``q [B,nv]``,
         ``G [B,nc,nv]``, ``h [B,nc]`` (row-major, unpadded)."""
         if dynamics is None:
-            return self._run(given, params, out=out)
+            return self._run(given, params, out=out, layout=layout)
+        if layout != "dense":
+            raise NotImplementedError("per-instance dynamics write the dense layout only")
         from . import lti
 
         if len(dynamics) != 1:

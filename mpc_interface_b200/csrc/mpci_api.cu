@@ -213,10 +213,42 @@ extern "C" int mpci_assemble_launches(const mpci_plan* p) {
   return (p->P.n_elems ? 1 : 0) + (p->G.n_elems ? 1 : 0) + ((p->nv + p->nc) ? 1 : 0);
 }
 
+namespace {
+int assemble_with(const mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::StreamArgs& Ga,
+                  const double* scalars, const double* given, double* P, double* q, double* G,
+                  double* h, long batch, void* stream);
+}
+
 extern "C" int mpci_assemble(const mpci_plan* p, const double* scalars, const double* given,
                              double* P, double* q, double* G, double* h, long batch,
                              void* stream) {
   if (!p) return mpci::fail(-3, "assemble: NULL plan");
+  return assemble_with(p, p->P, p->G, scalars, given, P, q, G, h, batch, stream);
+}
+
+extern "C" int mpci_plan_set_compact(mpci_plan* p, const double* DPc, long nP, const double* DGc,
+                                     long nG) {
+  if (!p) return mpci::fail(-3, "plan_set_compact: NULL plan");
+  if (nP < 0 || nG < 0 || (nP > 0 && !DPc) || (nG > 0 && !DGc))
+    return mpci::fail(-1, "plan_set_compact: bad sizes or NULL constants");
+  p->Pc = p->P; p->Pc.consts = DPc; p->Pc.n_elems = nP;
+  p->Gc = p->G; p->Gc.consts = DGc; p->Gc.n_elems = nG;
+  return 0;
+}
+
+extern "C" int mpci_assemble_compact(const mpci_plan* p, const double* scalars,
+                                     const double* given, double* Pc, double* q, double* Gc,
+                                     double* h, long batch, void* stream) {
+  if (!p) return mpci::fail(-3, "assemble_compact: NULL plan");
+  if ((Pc && !p->Pc.consts) || (Gc && !p->Gc.consts))
+    return mpci::fail(-3, "assemble_compact: mpci_plan_set_compact was not called");
+  return assemble_with(p, p->Pc, p->Gc, scalars, given, Pc, q, Gc, h, batch, stream);
+}
+
+namespace {
+int assemble_with(const mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::StreamArgs& Ga,
+                  const double* scalars, const double* given, double* P, double* q, double* G,
+                  double* h, long batch, void* stream) {
   if (batch < 0) return mpci::fail(-1, "assemble: negative batch");
   if (batch == 0) return 0;
   if (!scalars) return mpci::fail(-3, "assemble: NULL scalars");
@@ -244,8 +276,8 @@ extern "C" int mpci_assemble(const mpci_plan* p, const double* scalars, const do
     int rc = mpci::launch_qh(p->Y, s, given ? given + b0 * p->ng : nullptr,
                              q ? q + b0 * p->nv : nullptr, h ? h + b0 * p->nc : nullptr, nb,
                              qh_stream);
-    if (!rc && P) rc = mpci::launch_stream(p->P, s, p->n_scalars, P + b0 * p->P.n_elems, nb, st);
-    if (!rc && G) rc = mpci::launch_stream(p->G, s, p->n_scalars, G + b0 * p->G.n_elems, nb, st);
+    if (!rc && P) rc = mpci::launch_stream(Pa, s, p->n_scalars, P + b0 * Pa.n_elems, nb, st);
+    if (!rc && G) rc = mpci::launch_stream(Ga, s, p->n_scalars, G + b0 * Ga.n_elems, nb, st);
     if (rc) return rc;
   }
   if (overlap) {
@@ -254,19 +286,42 @@ extern "C" int mpci_assemble(const mpci_plan* p, const double* scalars, const do
   }
   return 0;
 }
+}  // namespace
+
+namespace {
+int assemble_host_with(mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::StreamArgs& Ga,
+                       const double* scalars, const double* given, double* P, double* q,
+                       double* G, double* h, long batch, long chunk);
+}
 
 extern "C" int mpci_assemble_host(mpci_plan* p, const double* scalars, const double* given,
                                   double* P, double* q, double* G, double* h, long batch,
                                   long chunk) {
   if (!p) return mpci::fail(-3, "assemble_host: NULL plan");
+  return assemble_host_with(p, p->P, p->G, scalars, given, P, q, G, h, batch, chunk);
+}
+
+extern "C" int mpci_assemble_compact_host(mpci_plan* p, const double* scalars,
+                                          const double* given, double* Pc, double* q, double* Gc,
+                                          double* h, long batch, long chunk) {
+  if (!p) return mpci::fail(-3, "assemble_compact_host: NULL plan");
+  if ((Pc && !p->Pc.consts) || (Gc && !p->Gc.consts))
+    return mpci::fail(-3, "assemble_compact_host: mpci_plan_set_compact was not called");
+  return assemble_host_with(p, p->Pc, p->Gc, scalars, given, Pc, q, Gc, h, batch, chunk);
+}
+
+namespace {
+int assemble_host_with(mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::StreamArgs& Ga,
+                       const double* scalars, const double* given, double* P, double* q,
+                       double* G, double* h, long batch, long chunk) {
   if (batch < 0 || chunk < 1) return mpci::fail(-1, "assemble_host: bad batch / chunk");
   if (batch == 0) return 0;
   if (!scalars || (p->ng > 0 && !given)) return mpci::fail(-3, "assemble_host: NULL input");
   if (chunk > batch) chunk = batch;
   const long in_per = p->n_scalars + p->ng;
-  const long nP = p->P.n_elems, nG = p->G.n_elems;
+  const long nP = Pa.n_elems, nG = Ga.n_elems;
   const long out_per = nP + p->nv + nG + p->nc;
-  if (p->slot_capacity < chunk) {
+  if (p->slot_capacity < chunk || p->slot_out_doubles < out_per * chunk) {
     for (int s = 0; s < 2; ++s) {
       if (p->slot_in[s]) cudaFree(p->slot_in[s]);
       if (p->slot_out[s]) cudaFree(p->slot_out[s]);
@@ -280,6 +335,7 @@ extern "C" int mpci_assemble_host(mpci_plan* p, const double* scalars, const dou
       if (!p->slot_free[s]) MPCI_CUDA(cudaEventCreateWithFlags(&p->slot_free[s], cudaEventDisableTiming));
     }
     p->slot_capacity = chunk;
+    p->slot_out_doubles = out_per * chunk;
   }
   int slot = 0;
   for (long b0 = 0; b0 < batch; b0 += chunk, slot ^= 1) {
@@ -296,8 +352,8 @@ extern "C" int mpci_assemble_host(mpci_plan* p, const double* scalars, const dou
     if (p->ng)
       MPCI_CUDA(cudaMemcpyAsync(d_g, given + b0 * p->ng, sizeof(double) * nb * p->ng,
                                 cudaMemcpyHostToDevice, st));
-    int rc = mpci_assemble(p, d_s, d_g, P ? d_P : nullptr, q ? d_q : nullptr, G ? d_G : nullptr,
-                           h ? d_h : nullptr, nb, st);
+    int rc = assemble_with(p, Pa, Ga, d_s, d_g, P ? d_P : nullptr, q ? d_q : nullptr,
+                           G ? d_G : nullptr, h ? d_h : nullptr, nb, st);
     if (rc) return rc;
     if (P) MPCI_CUDA(cudaMemcpyAsync(P + b0 * nP, d_P, sizeof(double) * nb * nP, cudaMemcpyDeviceToHost, st));
     if (q) MPCI_CUDA(cudaMemcpyAsync(q + b0 * p->nv, d_q, sizeof(double) * nb * p->nv, cudaMemcpyDeviceToHost, st));
@@ -308,3 +364,4 @@ extern "C" int mpci_assemble_host(mpci_plan* p, const double* scalars, const dou
   MPCI_CUDA(cudaStreamSynchronize(p->streams[1]));
   return 0;
 }
+}  // namespace

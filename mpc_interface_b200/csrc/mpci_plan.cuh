@@ -51,10 +51,12 @@ int launch_qh(const QhArgs& a, const double* scalars, const double* given, doubl
 struct mpci_plan {
   int nv, ng, nc, n_scalars;
   mpci::StreamArgs P, G;
+  mpci::StreamArgs Pc, Gc;  // compact constant sets (CSC values ...), mpci_plan_set_compact
   mpci::QhArgs Y;
   void* dev_tables;  // one allocation: nz | chunks | factors | warp pointers
   // staging of mpci_assemble_host (two slots), allocated on first use
-  long slot_capacity;
+  long slot_capacity;       // instances
+  long slot_out_doubles;    // doubles per output slot
   double* slot_in[2];   // scalars | given
   double* slot_out[2];  // P | q | G | h
   cudaStream_t streams[2];

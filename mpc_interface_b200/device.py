@@ -81,6 +81,16 @@ _SIGNATURES = {
         [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_long],
     ),
     "mpci_assemble_launches": (ctypes.c_int, [ctypes.c_void_p]),
+    "mpci_plan_set_compact": (
+        ctypes.c_int, [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long]),
+    "mpci_assemble_compact": (
+        ctypes.c_int,
+        [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_void_p],
+    ),
+    "mpci_assemble_compact_host": (
+        ctypes.c_int,
+        [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_long],
+    ),
     "mpci_lti_plan_create": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
     "mpci_lti_plan_destroy": (ctypes.c_int, [ctypes.c_void_p]),
     "mpci_lti_hessian_flops": (ctypes.c_double, [ctypes.c_void_p, ctypes.c_int]),
@@ -215,6 +225,37 @@ class QPBatch:
         return self.h.cpu().numpy()
 
 
+class QPBatchCSC:
+    """Solver hand-off layout: the values of ``P`` and ``G`` in CSC order with one
+    sparsity pattern for the whole batch (``P_indices`` / ``P_indptr`` ... are the
+    int32 arrays of ``scipy.sparse.csc_matrix``, see plan.CscPattern); ``q`` and
+    ``h`` stay dense.  ``csc(b)`` rebuilds scipy matrices of instance ``b``."""
+
+    def __init__(self, batch, nv, nc, P_pattern, G_pattern, device="cuda"):
+        torch = _torch()
+        kw = dict(dtype=torch.float64, device=device)
+        self.batch, self.nv, self.nc = batch, nv, nc
+        self.P_pattern, self.G_pattern = P_pattern, G_pattern
+        self._P = torch.empty([batch, P_pattern.padded], **kw)
+        self._G = torch.empty([batch, G_pattern.padded], **kw)
+        self.P_data = self._P[:, : P_pattern.nnz]
+        self.G_data = self._G[:, : G_pattern.nnz]
+        self.q = torch.empty([batch, nv], **kw)
+        self.h = torch.empty([batch, nc], **kw)
+
+    @staticmethod
+    def bytes_per_instance(nv, nc, P_pattern, G_pattern):
+        return 8 * (P_pattern.padded + G_pattern.padded + nv + nc)
+
+    def csc(self, b):
+        import scipy.sparse as sp
+
+        mats = []
+        for data, pat in ((self.P_data, self.P_pattern), (self.G_data, self.G_pattern)):
+            mats.append(sp.csc_matrix((data[b].cpu().numpy(), pat.indices, pat.indptr), shape=pat.shape))
+        return mats[0], mats[1]
+
+
 class DevicePlan:
     """Owns the mpci_plan handle and keeps the constant tensors alive."""
 
@@ -279,6 +320,11 @@ class DeviceBackend:
 
     def stack(self, handles):
         return self.torch.stack([h.contiguous() for h in handles]).contiguous()
+
+    def gather_flat(self, D, index):
+        """D [K, rows, cols] -> [K, len(index)] entries at flat positions (a copy, no arithmetic)."""
+        idx = self.torch.from_numpy(np.ascontiguousarray(index, dtype=np.int64)).to(self.device)
+        return D.reshape(D.shape[0], -1).index_select(1, idx).contiguous()
 
     # -- arithmetic (kernels of csrc/mpci_linalg.cu) ---------------------------
     @staticmethod
@@ -349,6 +395,56 @@ class DeviceBackend:
             )
         )
         return out
+
+    def compact(self, plan, upper_P=False):
+        """Registers the CSC constant sets with the device plan (once per layout)."""
+        from . import plan as _plan
+
+        key = "_csc_upper" if upper_P else "_csc"
+        if getattr(plan, key, None) is None:
+            setattr(plan, key, _plan.csc_patterns(plan, self, upper_P))
+        pP, pG, cP, cG = getattr(plan, key)
+        dp = self.device_plan(plan)
+        if getattr(dp, "compact_key", None) != key:
+            check(lib().mpci_plan_set_compact(dp.handle, _ptr(cP), pP.padded, _ptr(cG), pG.padded))
+            dp.compact_key = key
+            dp.keep_compact = (cP, cG)
+        return pP, pG
+
+    def assemble_csc(self, plan, scalars, given, batch, out=None, upper_P=False):
+        torch = self.torch
+        pP, pG = self.compact(plan, upper_P)
+        dp = self.device_plan(plan)
+        if not torch.is_tensor(scalars):
+            scalars = torch.from_numpy(np.ascontiguousarray(scalars, dtype=np.float64)).to(self.device)
+        if not torch.is_tensor(given):
+            given = torch.from_numpy(np.ascontiguousarray(given, dtype=np.float64)).to(self.device)
+        scalars = scalars.contiguous()
+        given = given.contiguous().reshape(batch, plan.ng)
+        if out is None:
+            out = QPBatchCSC(batch, plan.nv, plan.nc, pP, pG, self.device)
+        elif (out.batch, out.nv, out.nc, out.P_pattern.padded, out.G_pattern.padded) != (
+                batch, plan.nv, plan.nc, pP.padded, pG.padded):
+            raise ValueError("the output batch does not match the plan")
+        check(
+            lib().mpci_assemble_compact(
+                dp.handle, _ptr(scalars), _ptr(given), _ptr(out._P), _ptr(out.q), _ptr(out._G),
+                _ptr(out.h), batch, _stream_ptr(),
+            )
+        )
+        return out
+
+    def assemble_csc_host(self, plan, scalars, given, P, q, G, h, batch, chunk, upper_P=False):
+        """Host buffers; ``P`` [batch, P_pattern.padded], ``G`` [batch, G_pattern.padded]."""
+        self.compact(plan, upper_P)
+        dp = self.device_plan(plan)
+
+        def p(x):
+            if x is None:
+                return ctypes.c_void_p(0)
+            return ctypes.c_void_p(x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
+
+        check(lib().mpci_assemble_compact_host(dp.handle, p(scalars), p(given), p(P), p(q), p(G), p(h), batch, chunk))
 
     def assemble_host(self, plan, scalars, given, P, q, G, h, batch, chunk):
         """Host (ideally pinned) numpy / CPU-tensor buffers in and out."""

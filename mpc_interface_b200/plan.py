@@ -331,6 +331,40 @@ def _scan_qh_rows(DY):
     return segs.reshape([-1, 4]), val, col_idx.astype(np.int32)
 
 
+class CscPattern:
+    """Sparsity pattern shared by a batch, in scipy's CSC convention
+    (``scipy.sparse.csc_matrix(dense)``: int32 ``indices`` sorted by row inside
+    each column, int32 ``indptr``) -- what the reference's example hands to the
+    solver (biped_mpc_loop.py:57-58).  Derived STRUCTURALLY: an entry belongs to
+    the pattern when it is non-zero in any constant matrix of the affine plan, so
+    it is the same for every instance; an instance whose monomials happen to
+    cancel an entry exactly keeps an explicit 0.0 there (scipy would drop it)."""
+
+    def __init__(self, mask, upper=False):
+        rows, cols = mask.shape
+        if upper:
+            mask = np.triu(mask)
+        col_idx, row_idx = np.nonzero(mask.T)  # column-major order, rows ascending
+        self.shape = (rows, cols)
+        self.indices = row_idx.astype(np.int32)
+        self.indptr = np.concatenate([[0], np.cumsum(mask.sum(axis=0))]).astype(np.int32)
+        self.nnz = int(self.indices.shape[0])
+        self.flat = (row_idx.astype(np.int64) * cols + col_idx.astype(np.int64))  # gather index
+        self.padded = self.nnz + (self.nnz % 2)  # even, for 16-byte stores
+
+
+def csc_patterns(plan, ops, upper_P=False):
+    """(P pattern, G pattern, compact constants DPc [K, padded], DGc [K, padded])."""
+    out = []
+    for D, upper in ((plan.DP, upper_P), (plan.DG, False)):
+        host = ops.download3(D)
+        pattern = CscPattern(np.any(host != 0.0, axis=0), upper)
+        index = np.concatenate([pattern.flat, np.zeros(pattern.padded - pattern.nnz, dtype=np.int64)])
+        out.append((pattern, ops.gather_flat(D, index)))
+    (pP, cP), (pG, cG) = out
+    return pP, pG, cP, cG
+
+
 def compile_plan(form, ops, costs=None, limits=None):
     """Builds the AffinePlan of ``form`` with backend ``ops``.
 

@@ -58,6 +58,9 @@ class NumpyBackend:
     def stack(self, handles):
         return np.stack(handles)
 
+    def gather_flat(self, D, index):
+        return D.reshape(D.shape[0], -1)[:, index].copy()
+
     # what mpci_assemble computes ------------------------------------------
     def assemble(self, plan, scalars, given, batch, out=None):
         table = plan.mono_table()

@@ -259,3 +259,41 @@ def test_full_width_properties(dev):
     expect = float((coef[:, plan.G_terms].sum(axis=0) * sums).sum())
     got = float(out.G.sum().item())
     assert abs(got - expect) <= 1e-9 * max(1.0, abs(expect))
+
+
+@pytest.mark.parametrize("name", ["biped_n24_batch", "biped_n100_batch"])
+def test_csc_hand_off_layout(dev, name):
+    """layout="csc": values in scipy's CSC order with one pattern per batch; the
+    integer arrays equal scipy.sparse.csc_matrix of the reference's matrices bit
+    for bit, the values equal the dense path exactly."""
+    import scipy.sparse as sp
+    import torch
+
+    g = cases.golden(name)
+    form, params = cases.biped_batched(g)
+    dense = form.generate_all_qp_matrices_batched(g["given"], params)
+    out = form.generate_all_qp_matrices_batched(g["given"], params, layout="csc")
+    assert torch.equal(out.q, dense.q) and torch.equal(out.h, dense.h)
+    for b in range(g["Q"].shape[0]):
+        P, G = out.csc(b)
+        for got, ref_dense, mine in ((P, g["Q"][b], dense.P[b]), (G, g["A"][b], dense.G[b])):
+            ref = sp.csc_matrix(ref_dense)
+            assert np.array_equal(got.indices, ref.indices) and np.array_equal(got.indptr, ref.indptr)
+            assert got.indices.dtype == np.int32 and got.indptr.dtype == np.int32
+            assert cases.rel_err(got.data, ref.data) <= cases.TOL
+            assert np.array_equal(got.toarray(), mine.cpu().numpy())
+    up = form.generate_all_qp_matrices_batched(g["given"], params, layout="csc_upper")
+    assert np.array_equal(up.csc(0)[0].toarray(), np.triu(dense.P[0].cpu().numpy()))
+    # host-buffer entry point (what the e2e bench times)
+    plan = form._compiled()
+    ops = form._ops()
+    pP, pG = ops.compact(plan)
+    batch = g["given"].shape[0]
+    scalars = torch.from_numpy(plan.slots.evaluate(params, batch)).pin_memory()
+    hP = torch.empty([batch, pP.padded], dtype=torch.float64).pin_memory()
+    hG = torch.empty([batch, pG.padded], dtype=torch.float64).pin_memory()
+    hq = torch.empty([batch, plan.nv], dtype=torch.float64).pin_memory()
+    hh = torch.empty([batch, plan.nc], dtype=torch.float64).pin_memory()
+    ops.assemble_csc_host(plan, scalars, torch.from_numpy(g["given"]).pin_memory(), hP, hq, hG, hh, batch, 2)
+    assert torch.equal(hP[:, : pP.nnz], out.P_data.cpu()) and torch.equal(hG[:, : pG.nnz], out.G_data.cpu())
+    assert torch.equal(hq, out.q.cpu()) and torch.equal(hh, out.h.cpu())
