@@ -128,6 +128,18 @@ int mpci_assemble_host(mpci_plan* plan, const double* scalars_host, const double
                        double* P_host, double* q_host, double* G_host, double* h_host,
                        long batch, long chunk);
 
+/* ---- after the solve: preview and goal distance ---------------------------
+ * Formulation.preview (body.py:209-219), v = Mg given + Mo optim, is the same
+ * product as [q; h] with [given; optim] in the place of given: build a plan whose
+ * Y constants are the variable's preview matrices (nv = rows, ng = given + optim,
+ * nc = 0, DP_dev = DG_dev = NULL) and call mpci_assemble with only q requested.
+ * Formulation.goal_distance (body.py:221-229):
+ *   out[b] = sum_a sum_r (V[b][a][r] - aim[b * aim_stride + a])^2
+ * V_dev [batch][n_axes][rows], aim_dev [batch][>= n_axes] (aim_stride = 0: one aim
+ * row for the whole batch), out_dev [batch].                                   */
+int mpci_goal_distance(const double* V_dev, const double* aim_dev, long aim_stride, int rows,
+                       int n_axes, double* out_dev, long batch, void* stream);
+
 /* ---- solver hand-off formats ---------------------------------------------
  * The example feeds the solver scipy.sparse.csc_matrix(Q) / csc_matrix(A)
  * (python/use_examples/simple_functional_example/biped_mpc_loop.py:57-60).  The

@@ -364,6 +364,68 @@ class Formulation:
             raise ValueError("hessian must be 'dmma' or 'recursion'")
         return lti.assemble(self.lti_plan(name), A, B, given, params, out, modes[hessian])
 
+    # ------------------------------------------------------------------
+    # after the solve, batched (body.py:209-234)
+    # ------------------------------------------------------------------
+    def _preview_plan(self, names):
+        compiled = self._compiled()
+        cache = compiled.__dict__.setdefault("_previews", {})
+        key = tuple(names)
+        if key not in cache:
+            cache[key] = _plan.PreviewPlan(compiled, self._ops(), names)
+        return compiled, cache[key]
+
+    def _given_optim(self, given, optim):
+        ops = self._ops()
+        g, z = ops._to_device(given), ops._to_device(optim)
+        batch = z.shape[0]
+        g = g.reshape(batch, self.given_len)
+        z = z.reshape(batch, self.optim_len)
+        return ops.torch.cat([g, z], dim=1).contiguous(), batch
+
+    def preview_batched(self, given, optim, variable, axes=None, params=None):
+        """Batched ``preview`` (body.py:209-219): the value of ``variable`` along
+        the horizon for every instance, ``Mg @ given + Mo @ optim`` with the
+        per-instance preview matrices.  given [B, given_len], optim [B, optim_len]
+        (numpy or CUDA tensors).  Returns a CUDA tensor [B, rows] (``axes`` None)
+        or [B, rows, len(axes)] -- the reference's hstack over the axes."""
+        names = [variable] if axes is None else [variable + axis for axis in axes]
+        compiled, pplan = self._preview_plan(names)
+        if len(set(pplan.rows)) != 1:
+            raise ValueError("all the arrays must have the same number of rows")
+        gz, batch = self._given_optim(given, optim)
+        scalars = compiled.slots.evaluate(params or {}, batch)
+        values = self._ops().preview(pplan, scalars, gz, batch)
+        if axes is None:
+            return values
+        return values.reshape(batch, len(names), pplan.rows[0]).transpose(1, 2)
+
+    def goal_distance_batched(self, given, optim, goal_name, params=None):
+        """Batched ``goal_distance`` (body.py:221-229): squared distance to the aim
+        of one goal for every instance; a CUDA tensor [B]."""
+        goal = self.goals[goal_name]
+        names = [goal.variable + axis for axis in goal.axes]
+        compiled, pplan = self._preview_plan(names)
+        gz, batch = self._given_optim(given, optim)
+        scalars = compiled.slots.evaluate(params or {}, batch)
+        values = self._ops().preview(pplan, scalars, gz, batch)
+        aim = np.asarray(goal.aim, dtype=object)
+        if aim.shape[0] != 1:
+            raise ValueError("operands could not be broadcast together: an aim must have one row")
+        columns = []
+        for entry in aim[0]:
+            value = entry.evaluate(params or {}) if hasattr(entry, "evaluate") else float(entry)
+            columns.append(np.broadcast_to(np.asarray(value, dtype=np.float64), [batch]))
+        aims = np.stack(columns, axis=1)
+        return self._ops().goal_distance(values, aims, pplan.rows[0], len(names))
+
+    def full_goal_distance_batched(self, given, optim, params=None):
+        total = None
+        for name in self.goals:
+            d = self.goal_distance_batched(given, optim, name, params)
+            total = d if total is None else total + d
+        return total
+
     def lti_plan(self, name):
         """The condensed LTI plan of this formulation with ``name`` as the
         per-instance plant (cached until the formulation changes)."""

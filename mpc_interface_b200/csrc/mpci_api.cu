@@ -31,10 +31,9 @@ int fill_stream(mpci::StreamArgs& s, int n_terms, const int* terms, const int* m
                 int n_monomials, const double* consts, long n_elems, const char* what) {
   if (n_terms < 1 || n_terms > MPCI_MAX_TERMS)
     return mpci::fail(-7, "plan: %s has %d terms (1..%d allowed)", what, n_terms, MPCI_MAX_TERMS);
-  if (n_elems > 0 && !consts) return mpci::fail(-3, "plan: %s constants are NULL", what);
   s.n_terms = n_terms;
   s.consts = consts;
-  s.n_elems = n_elems;
+  s.n_elems = consts ? n_elems : 0;  // without constants the plan cannot write this array
   for (int k = 0; k < n_terms; ++k) {
     if (terms[k] < 0 || terms[k] >= n_monomials)
       return mpci::fail(-9, "plan: %s term %d names monomial %d of %d", what, k, terms[k],
@@ -253,6 +252,8 @@ int assemble_with(const mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::St
   if (batch == 0) return 0;
   if (!scalars) return mpci::fail(-3, "assemble: NULL scalars");
   if (p->ng > 0 && !given && (q || h)) return mpci::fail(-3, "assemble: NULL given");
+  if ((P && !Pa.consts) || (G && !Ga.consts))
+    return mpci::fail(-3, "assemble: the plan was created without the constants of P / G");
   cudaStream_t st = mpci::as_stream(stream);
   // grid.y limits: split very large batches
   const long piece = 65535L * 16;

@@ -105,7 +105,42 @@ axpy2d_kernel(int rows, int cols, double alpha, const double* __restrict__ rowsc
   }
 }
 
+// out[b] = sum_e (V[b][e] - aim[b * aim_stride + e / rows])^2 : one warp per instance
+__global__ void __launch_bounds__(256)
+goal_distance_kernel(const double* __restrict__ V, const double* __restrict__ aim, long aim_stride,
+                     int rows, int n_axes, double* __restrict__ out, long batch) {
+  const int lane = threadIdx.x & 31;
+  const long b = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (b >= batch) return;
+  const double* v = V + b * (long)rows * n_axes;
+  const double* t = aim + b * aim_stride;
+  double acc = 0.0;
+  for (int a = 0; a < n_axes; ++a) {
+    const double ta = t[a];
+    for (int r = lane; r < rows; r += 32) {
+      const double gap = v[(long)a * rows + r] - ta;
+      acc = fma(gap, gap, acc);
+    }
+  }
+  for (int off = 16; off; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (lane == 0) out[b] = acc;
+}
+
 }  // namespace
+
+extern "C" int mpci_goal_distance(const double* V, const double* aim, long aim_stride, int rows,
+                                  int n_axes, double* out, long batch, void* stream) {
+  if (rows < 0 || n_axes < 0 || batch < 0 || aim_stride < 0)
+    return mpci::fail(-1, "goal_distance: negative size");
+  if (batch == 0) return 0;
+  if (!V || !aim || !out) return mpci::fail(-3, "goal_distance: NULL pointer");
+  if (aim_stride != 0 && aim_stride < n_axes)
+    return mpci::fail(-4, "goal_distance: aim stride %ld smaller than %d axes", aim_stride, n_axes);
+  goal_distance_kernel<<<(unsigned)((batch + 7) / 8), 256, 0, mpci::as_stream(stream)>>>(
+      V, aim, aim_stride, rows, n_axes, out, batch);
+  MPCI_LAUNCH_CHECK("goal_distance_kernel");
+  return 0;
+}
 
 extern "C" int mpci_gemm(int transA, int M, int N, int K, double alpha, const double* A, int lda,
                          long strideA, const double* B, int ldb, long strideB, double beta,

@@ -81,6 +81,11 @@ _SIGNATURES = {
         [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_long],
     ),
     "mpci_assemble_launches": (ctypes.c_int, [ctypes.c_void_p]),
+    "mpci_goal_distance": (
+        ctypes.c_int,
+        [_c_double_p, _c_double_p, ctypes.c_long, ctypes.c_int, ctypes.c_int, _c_double_p,
+         ctypes.c_long, ctypes.c_void_p],
+    ),
     "mpci_plan_set_compact": (
         ctypes.c_int, [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long]),
     "mpci_assemble_compact": (
@@ -271,8 +276,8 @@ class DevicePlan:
         desc = PlanDesc(
             plan.nv, plan.ng, plan.nc, max(1, len(plan.slots.exprs)),
             table.shape[0], table.ctypes.data,
-            len(P_terms), P_terms.ctypes.data, plan.DP.data_ptr(),
-            len(G_terms), G_terms.ctypes.data, plan.DG.data_ptr(),
+            len(P_terms), P_terms.ctypes.data, plan.DP.data_ptr() if plan.DP is not None else 0,
+            len(G_terms), G_terms.ctypes.data, plan.DG.data_ptr() if plan.DG is not None else 0,
             len(Y_terms), Y_terms.ctypes.data,
             segs.shape[0], segs.ctypes.data, val.shape[0], val.ctypes.data, col.ctypes.data,
         )
@@ -395,6 +400,36 @@ class DeviceBackend:
             )
         )
         return out
+
+    def preview(self, pplan, scalars, given_optim, batch):
+        """Rows of a PreviewPlan for a batch: [batch, total rows] (device tensor)."""
+        torch = self.torch
+        dp = self.device_plan(pplan)
+        scalars = self._to_device(scalars)
+        values = torch.empty([batch, pplan.nv], dtype=torch.float64, device=self.device)
+        null = ctypes.c_void_p(0)
+        check(lib().mpci_assemble(dp.handle, _ptr(scalars), _ptr(given_optim), null, _ptr(values),
+                                  null, null, batch, _stream_ptr()))
+        return values
+
+    def goal_distance(self, values, aims, rows, n_axes):
+        """values [batch, n_axes * rows], aims [batch, n_axes] or [1, n_axes] -> [batch]."""
+        torch = self.torch
+        batch = values.shape[0]
+        aims = self._to_device(aims).reshape(-1, n_axes)
+        out = torch.empty([batch], dtype=torch.float64, device=self.device)
+        stride = n_axes if aims.shape[0] == batch and batch > 1 else 0
+        if aims.shape[0] not in (1, batch):
+            raise ValueError("aims must have 1 or {} rows".format(batch))
+        check(lib().mpci_goal_distance(_ptr(values), _ptr(aims), stride, rows, n_axes, _ptr(out),
+                                       batch, _stream_ptr()))
+        return out
+
+    def _to_device(self, x):
+        torch = self.torch
+        if not torch.is_tensor(x):
+            x = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float64))
+        return x.to(device=self.device, dtype=torch.float64).contiguous()
 
     def compact(self, plan, upper_P=False):
         """Registers the CSC constant sets with the device plan (once per layout)."""

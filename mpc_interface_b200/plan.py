@@ -331,6 +331,46 @@ def _scan_qh_rows(DY):
     return segs.reshape([-1, 4]), val, col_idx.astype(np.int32)
 
 
+class PreviewPlan:
+    """The rows of some named variables as a plan for the [q; h] kernel:
+    ``value = sum_m c_m(s_b) * D_m @ [given_b; optim_b; 1]`` (Formulation.preview,
+    body.py:209-219).  Shares the scalar slots of the assembly plan it is cut from."""
+
+    def __init__(self, compiled, ops, names):
+        polys = [compiled.PM[name] for name in names]
+        width = compiled.ng + compiled.nv
+        self.names = list(names)
+        self.rows = [p.rows for p in polys]
+        self.nv, self.ng, self.nc = sum(self.rows), width, 0  # the kernel's view of the sizes
+        self.slots = compiled.slots
+        monos = []
+        for p in polys:
+            for mono in p.terms:
+                if mono not in monos:
+                    monos.append(mono)
+        monos = sorted(monos, key=lambda m: (len(m), m)) or [()]
+        if any(len(m) > MAX_FACTORS for m in monos):
+            raise NotImplementedError("a monomial exceeds the kernel limit of factors")
+        self.monomials = monos
+        self.Y_terms = list(range(len(monos)))
+        self.P_terms, self.G_terms = [0], [0]
+        self.DP = self.DG = None
+        DY = np.zeros([len(monos), self.nv, width + 1])
+        row0 = 0
+        for p in polys:
+            for mono, H in p.terms.items():
+                DY[monos.index(mono), row0 : row0 + p.rows, :width] = ops.download(H)
+            row0 += p.rows
+        self.DY = DY
+        self.Y_segs, self.Y_val, self.Y_col = _scan_qh_rows(DY)
+
+    def mono_table(self):
+        table = -np.ones([max(1, len(self.monomials)), MAX_FACTORS], dtype=np.int32)
+        for i, mono in enumerate(self.monomials):
+            table[i, : len(mono)] = mono
+        return table
+
+
 class CscPattern:
     """Sparsity pattern shared by a batch, in scipy's CSC convention
     (``scipy.sparse.csc_matrix(dense)``: int32 ``indices`` sorted by row inside

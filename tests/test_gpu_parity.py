@@ -297,3 +297,49 @@ def test_csc_hand_off_layout(dev, name):
     ops.assemble_csc_host(plan, scalars, torch.from_numpy(g["given"]).pin_memory(), hP, hq, hG, hh, batch, 2)
     assert torch.equal(hP[:, : pP.nnz], out.P_data.cpu()) and torch.equal(hG[:, : pG.nnz], out.G_data.cpu())
     assert torch.equal(hq, out.q.cpu()) and torch.equal(hh, out.h.cpu())
+
+
+def test_preview_and_goal_distance_batched(dev):
+    """Formulation.preview / goal_distance (body.py:209-234)
+    for a batch with per-instance omega, against the oracle's preview matrices."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    N, batch = 24, 70
+    form = cases.formulate_biped(
+        cases.default_configuration(N), omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")])
+    vals = synthetic.biped_inputs(9, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    optim = np.random.default_rng(2).normal(size=[batch, form.optim_len])
+    dcm = form.preview_batched(given, optim, "DCM", ["_x", "_y"], params)
+    com = form.preview_batched(given, optim, "CoM_x", None, params)
+    assert tuple(dcm.shape) == (batch, N, 2) and tuple(com.shape) == (batch, N)
+    dist = form.goal_distance_batched(given, optim, "track vel_x", params)
+    total = form.full_goal_distance_batched(given, optim, params)
+    dcm, com, dist, total = (x.cpu().numpy() for x in (dcm, com, dist, total))
+    for b in (0, 31, 32, 63, 64, batch - 1):
+        one = {k: float(v[b]) for k, v in params.items()}
+        PM = orc.preview_matrices(form, one)
+        g, z = given[b][:, None], optim[b][:, None]
+        for a, axis in enumerate(("_x", "_y")):
+            ref = PM["DCM" + axis][0] @ g + PM["DCM" + axis][1] @ z
+            assert cases.rel_err(dcm[b, :, a], ref[:, 0]) <= cases.TOL
+        assert cases.rel_err(com[b], (PM["CoM_x"][0] @ g + PM["CoM_x"][1] @ z)[:, 0]) <= cases.TOL
+        ref_total = 0.0
+        for name, goal in form.goals.items():
+            d = 0.0
+            for i, axis in enumerate(goal.axes):
+                Mg, Mo = PM[goal.variable + axis]
+                aim = goal.aim[0, i]
+                aim = aim.evaluate(one) if hasattr(aim, "evaluate") else float(aim)
+                gap = Mg @ g + Mo @ z - aim
+                d += float((gap.T @ gap)[0, 0])
+            ref_total += d
+            if name == "track vel_x":
+                assert abs(dist[b] - d) <= cases.TOL * max(1.0, abs(d))
+        assert abs(total[b] - ref_total) <= cases.TOL * max(1.0, abs(ref_total))
+    # one instance through the reference-named single-instance calls
+    single = cases.formulate_biped(cases.default_configuration(N))
+    v = single.preview(given[0][:, None], optim[0][:, None], "CoM", ["_x", "_y"])
+    assert v.shape == (N, 2)
