@@ -222,6 +222,17 @@ class Formulation:
             given[indices] = collector[variable]
         return given
 
+    def arrange_given_batched(self, collector):
+        """Batched ``arrange_given``: ``{variable: array [B, size]}`` -> [B, given_len]
+        in the order of ``given_ID`` (body.py:195-207 for every instance)."""
+        batch = len(next(iter(collector.values()))) if collector else 0
+        given = np.zeros([batch, self.given_len])
+        for variable, indices in self.given_ID.items():
+            if variable in self.given_variables:
+                given[:, indices.start : indices.stop] = np.asarray(collector[variable]).reshape(
+                    batch, len(indices))
+        return given
+
     # ------------------------------------------------------------------
     # evaluation helpers
     # ------------------------------------------------------------------

@@ -142,3 +142,16 @@ def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=Tru
 
     form.set_updating_rule(tick)
     return form
+
+
+def structure_key(horizon_lenght):
+    """Structural key of one biped instance for ``receding.StructureBuckets``:
+    the steps inside the preview window (they fix E and the number of ``Ds``
+    variables, tools.py:79-101) and which foot steps next (the side of the
+    stepping-area centres, tools.py:158-165)."""
+    def key(step_times, step_count, **_):
+        times = np.asarray(step_times)
+        inside = times[(times >= 0) & (times < horizon_lenght - 1)]
+        return (tuple(int(t) for t in inside), int(step_count) % 2)
+
+    return key

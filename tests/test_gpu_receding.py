@@ -1,0 +1,70 @@
+"""Receding-horizon batches: robots at different walking
+phases have different QP structures (nv, nc change);
+StructureBuckets groups them, every bucket is one batched assembly."""
+import numpy as np
+import pytest
+
+import _cases as cases
+from oracle import qp_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _tick_sequence(n_ticks, step_samples, n_steps):
+    """(step_times, step_count) per tick: the count_steps logic of the example
+    loop (biped_mpc_loop.py:41-45), as in tests/golden/make_goldens.py."""
+    step_times = np.array([(i + 1) * step_samples - 1 for i in range(n_steps)])
+    step_count, out = 0, []
+    for _ in range(n_ticks):
+        out.append((step_times.copy(), step_count))
+        step_times = step_times - 1
+        if step_times[0] == -1:
+            step_times = step_times + step_samples
+            step_count += 1
+    return out
+
+
+@pytest.mark.parametrize("N", [24, 100])
+def test_structure_buckets_against_oracle(N):
+    from mpc_interface_b200 import Param, device
+    from mpc_interface_b200.examples import synthetic
+    from mpc_interface_b200.examples.biped import default_configuration, formulate_biped, structure_key
+    from mpc_interface_b200.receding import StructureBuckets
+
+    device.require_gpu()
+    conf = default_configuration(N)
+
+    def factory():
+        return formulate_biped(conf, omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")])
+
+    n_steps = factory().domain["Ds_x"]
+    ticks = _tick_sequence(30, conf.step_samples, n_steps)
+    batch = 50
+    rng = np.random.default_rng(N)
+    phase = rng.integers(0, len(ticks), size=batch)
+    kargs = [dict(step_times=ticks[t][0], step_count=ticks[t][1]) for t in phase]
+    vals = synthetic.biped_inputs(3, batch, N)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    buckets = StructureBuckets(factory, structure_key(N))
+    results = buckets.assemble(kargs, vals, params)
+    sizes = {(form.optim_len, out.nc) for _, _, form, out in results}
+    assert len(sizes) >= 2  # the structure really is ragged across the batch
+    assert sorted(np.concatenate([idx for _, idx, _, _ in results]).tolist()) == list(range(batch))
+    seen = len(buckets)
+    for _, idx, form, out in results:
+        assert out.P.shape == (len(idx), form.optim_len, form.optim_len)
+        for pos in (0, len(idx) - 1):
+            b = int(idx[pos])
+            ref_form = factory()
+            ref_form.update(**kargs[b])  # an independent formulation at that instance's phase
+            cases.check_layout(form, {  # same integer layout as the instance's own formulation
+                "optim_names": np.array(list(ref_form.optim_ID)), "given_names": np.array(list(ref_form.given_ID)),
+                "optim_ranges": np.array([[r.start, r.stop] for r in ref_form.optim_ID.values()]),
+                "given_ranges": np.array([[r.start, r.stop] for r in ref_form.given_ID.values()])})
+            given = ref_form.arrange_given({k: vals[k][b][:, None] for k in ref_form.given_ID})
+            ref = orc.all_qp_matrices(ref_form, given, {k: float(v[b]) for k, v in params.items()})
+            got = tuple(x[pos].cpu().numpy() for x in (out.G, out.h, out.P, out.q))
+            cases.assert_qp_close(got, ref)
+    # a second tick with the same phases reuses the compiled structures
+    buckets.assemble(kargs, vals, params)
+    assert len(buckets) == seen
