@@ -48,6 +48,17 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0}, "fallback"
 
 
+def measured_traffic(batch):
+    """dram read + write bytes of one G-stream launch, from the committed ncu --set full
+    capture (profiles/r01_traffic.json holds it per instance; a launch is linear in the
+    batch because nothing is re-read), or None."""
+    path = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if not os.path.exists(path):
+        return None
+    with open(path) as f:
+        return json.load(f)["dram_bytes_per_instance"] * batch
+
+
 # ---------------------------------------------------------------------------
 # CPU arm: the oracle port of the reference's path, on the host cores
 # ---------------------------------------------------------------------------
@@ -369,7 +380,9 @@ def main():
         "roofline": {
             "bound": "hbm", "kernel": "stream_terms_kernel<3,double2> (G stack)",
             "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-            "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_source": peak_kind,
+            "frac": achieved / peaks["hbm_gbs"], "traffic": measured_traffic(B),
+            "traffic_note": "ncu dram bytes per instance (batch 8192 capture) x this batch",
+            "peak_source": peak_kind,
             "algorithmic_bytes_per_launch": bytes_G,
         },
         "kernels_ms": {"P_stream": res["t_P"], "G_stream": res["t_G"], "qh": res["t_qh"]},
