@@ -53,9 +53,12 @@ def default_configuration(horizon_lenght=None):
     return c
 
 
-def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=True):
+def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=True, yaw=None):
     """Builds the Formulation.  ``omega`` / ``target_vel`` default to the
-    configuration's numbers; pass ``Param``s to make them per-instance."""
+    configuration's numbers; pass ``Param``s to make them per-instance.
+    ``yaw`` (float or ``Param``) turns the support polygon and the terminal box
+    by that angle with ``Box.rotate_in_TS`` (restrictions.py:437-457): the feet of
+    every instance of a batch may point somewhere else."""
     w = conf.omega if omega is None else omega
     vel = conf.target_vel if target_vel is None else target_vel
     N = conf.horizon_lenght
@@ -106,6 +109,9 @@ def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=Tru
     terminal_constraint = Box.task_space("(DCM-s)", foot, AXES, schedule=last)
     support_polygon.set_safety_margin(conf.cop_safety_margin)
     terminal_constraint.set_safety_margin(conf.cop_safety_margin)
+    if yaw is not None:
+        support_polygon.rotate_in_TS(now.rotation2D(yaw))
+        terminal_constraint.rotate_in_TS(now.rotation2D(yaw))
 
     weights = conf.cost_weights
     goals = {

@@ -71,7 +71,46 @@ class Expr:
             return -v[0]
         if self.op == "sqrt":
             return np.sqrt(v[0])
+        if self.op == "cos":
+            return np.cos(v[0])
+        if self.op == "sin":
+            return np.sin(v[0])
         raise ValueError("unknown operation " + self.op)
+
+    # -- polynomial form ---------------------------------------------------
+    def polynomial(self):
+        """``{atoms: coefficient}`` with ``self == sum coefficient * prod atoms``.
+
+        ``atoms`` is a tuple of Expr (sorted by structural key, repeated for
+        powers); an atom is a Param or a sub-expression that is not polynomial
+        (division by an expression, sqrt, cos, sin, non-integer powers).  Used
+        where an ARRAY of expressions multiplies matrices (constraint geometry,
+        restrictions.py): entries that share atoms then share one constant
+        matrix of the assembly plan instead of costing one each."""
+        op = self.op
+        if op in ("add", "sub"):
+            out = dict(_poly(self.args[0]))
+            sign = 1.0 if op == "add" else -1.0
+            for mono, c in _poly(self.args[1]).items():
+                out[mono] = out.get(mono, 0.0) + sign * c
+            return out
+        if op == "neg":
+            return {mono: -c for mono, c in _poly(self.args[0]).items()}
+        if op == "mul":
+            return _poly_mul(_poly(self.args[0]), _poly(self.args[1]))
+        if op == "div" and not isinstance(self.args[1], Expr):
+            return {mono: c / float(self.args[1]) for mono, c in _poly(self.args[0]).items()}
+        if op == "div":
+            inverse = {(Expr("div", (1.0, self.args[1])),): 1.0}
+            return _poly_mul(_poly(self.args[0]), inverse)
+        if op == "pow" and isinstance(self.args[0], Expr) and not isinstance(self.args[1], Expr):
+            e = float(self.args[1])
+            if e == int(e) and 0 <= e <= 4:
+                out = {(): 1.0}
+                for _ in range(int(e)):
+                    out = _poly_mul(out, _poly(self.args[0]))
+                return out
+        return {(self,): 1.0}
 
     # -- arithmetic --------------------------------------------------------
     @staticmethod
@@ -79,6 +118,11 @@ class Expr:
         return isinstance(x, (Expr, numbers.Real))
 
     def _bin(self, op, other, swap=False):
+        if isinstance(other, np.ndarray):  # array (op) expression: element by element
+            out = np.empty(other.shape, dtype=object)
+            for idx, x in np.ndenumerate(other):
+                out[idx] = self._bin(op, x, swap)
+            return out
         if not Expr._ok(other):
             return NotImplemented
         return Expr(op, (other, self) if swap else (self, other))
@@ -119,11 +163,18 @@ class Expr:
     def sqrt(self):
         return Expr("sqrt", (self,))
 
+    # numpy calls these on the elements of object arrays (np.cos(array_of_Expr))
+    def cos(self):
+        return Expr("cos", (self,))
+
+    def sin(self):
+        return Expr("sin", (self,))
+
     def __repr__(self):
         if self.op == "neg":
             return "(-{!r})".format(self.args[0])
-        if self.op == "sqrt":
-            return "sqrt({!r})".format(self.args[0])
+        if self.op in ("sqrt", "cos", "sin"):
+            return "{}({!r})".format(self.op, self.args[0])
         sym = {"add": "+", "sub": "-", "mul": "*", "div": "/", "pow": "**"}[self.op]
         return "({!r} {} {!r})".format(self.args[0], sym, self.args[1])
 
@@ -160,8 +211,63 @@ class Param(Expr):
         return self.name
 
 
+def _poly(x):
+    return x.polynomial() if isinstance(x, Expr) else {(): float(x)}
+
+
+def _poly_mul(a, b):
+    out = {}
+    for m1, c1 in a.items():
+        for m2, c2 in b.items():
+            mono = tuple(sorted(m1 + m2, key=lambda e: repr(e.key())))
+            out[mono] = out.get(mono, 0.0) + c1 * c2
+    return out
+
+
+def cos(x):
+    """cos of a float or of a per-instance expression."""
+    return x.cos() if isinstance(x, Expr) else np.cos(x)
+
+
+def sin(x):
+    return x.sin() if isinstance(x, Expr) else np.sin(x)
+
+
 def is_expr(x):
     return isinstance(x, Expr)
+
+
+def evaluate_array(x, values):
+    """float64 copy of an array whose entries may be expressions (ONE instance:
+    every parameter value a float)."""
+    arr = np.asarray(x)
+    if arr.dtype != object:
+        return arr.astype(np.float64)
+    out = np.empty(arr.shape, dtype=np.float64)
+    for idx, e in np.ndenumerate(arr):
+        out[idx] = e.evaluate(values) if isinstance(e, Expr) else e
+    return out
+
+
+def split_array(x):
+    """An array of numbers / expressions as ``[(atoms, float64 array)]`` with
+    ``x == sum prod(atoms) * array`` (atoms as in Expr.polynomial); purely numeric
+    arrays come back as one part with ``atoms == ()``."""
+    arr = np.asarray(x)
+    if arr.dtype != object:
+        return [((), arr.astype(np.float64))]
+    parts = {}
+    for idx, e in np.ndenumerate(arr):
+        for mono, c in _poly(e).items():
+            if c == 0.0:
+                continue
+            if mono not in parts:
+                parts[mono] = np.zeros(arr.shape)
+            parts[mono][idx] += c
+    if not parts:
+        return [((), np.zeros(arr.shape))]
+    order = sorted(parts, key=lambda m: (len(m), [repr(a.key()) for a in m]))
+    return [(m, parts[m]) for m in order]
 
 
 def contains_expr(x):

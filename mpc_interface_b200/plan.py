@@ -26,7 +26,7 @@ import numbers
 
 import numpy as np
 
-from .params import Expr, is_expr
+from .params import Expr, is_expr, split_array
 
 MAX_FACTORS = 4  # factors per monomial the kernels accept (mpci.h: MPCI_MAX_FACTORS)
 MAX_TERMS = 8  # monomials per streamed array (mpci.h: MPCI_MAX_TERMS)
@@ -192,8 +192,19 @@ def ordered_limits(form):
     return limits
 
 
-def _limit_poly(form, ops, PM, limit):
-    """(Poly [c_rows x (ng+nv)], bound [c_rows x 1]) of one limit (body.py:236-264)."""
+def _atoms_mono(slots, atoms):
+    """Slot indices of the atoms of one geometry monomial (params.split_array)."""
+    return tuple(slots.slot(a) for a in atoms)
+
+
+def _limit_poly(form, ops, PM, limit, slots):
+    """(Poly [c_rows x (ng+nv)], bound parts) of one limit (body.py:236-264).
+
+    ``arrow`` / ``center`` / ``extreme`` may hold per-instance expressions (a box
+    rotated by each instance's yaw, restrictions.py:437-457): every multiplier
+    array is split into ``sum_m prod(atoms_m) * C_m`` with numeric ``C_m`` and each
+    part goes through the numeric path with its atoms joined to the monomial.
+    The bound comes back as ``[(monomial, [c_rows x 1] array)]``."""
     width = form.given_len + form.optim_len
     rows = PM[limit.variable + limit.axes[0]].rows
     nlines = limit.nlines
@@ -203,28 +214,32 @@ def _limit_poly(form, ops, PM, limit):
     multipliers = limit.matrices()
     for a, axis in enumerate(limit.axes):
         picked = PM[limit.variable + axis].take_rows(list(schedule))
-        c = np.asarray(multipliers[a], dtype=np.float64)
-        if limit.L:
-            term = picked.left_multiply(c)
-            for mono, H in term.terms.items():
-                out.acc(mono, H)
-        else:
-            k = c.shape[0]
-            if k != 1 and picked.rows != 1 and k != picked.rows:
-                raise ValueError(
-                    "operands could not be broadcast together with shapes "
-                    "({},1) ({},{})".format(k, picked.rows, width)
-                )
-            if max(k, picked.rows) not in (1, c_rows):
-                raise ValueError(
-                    "non-broadcastable output operand with shape ({},{})".format(c_rows, width)
-                )
-            for mono, H in picked.terms.items():
-                out.acc(mono, H, 1.0, rowscale=c[:, 0])
-    bound = np.asarray(limit.bound(), dtype=np.float64).reshape([-1, 1])
-    if bound.shape[0] not in (1, c_rows):
-        raise ValueError("the bound has {} rows for {} lines".format(bound.shape[0], c_rows))
-    return out, np.broadcast_to(bound, [c_rows, 1])
+        for atoms, c in split_array(multipliers[a]):
+            extra = _atoms_mono(slots, atoms)
+            if limit.L:
+                term = picked.left_multiply(c)
+                for mono, H in term.terms.items():
+                    out.acc(_mono(mono, extra), H)
+            else:
+                k = c.shape[0]
+                if k != 1 and picked.rows != 1 and k != picked.rows:
+                    raise ValueError(
+                        "operands could not be broadcast together with shapes "
+                        "({},1) ({},{})".format(k, picked.rows, width)
+                    )
+                if max(k, picked.rows) not in (1, c_rows):
+                    raise ValueError(
+                        "non-broadcastable output operand with shape ({},{})".format(c_rows, width)
+                    )
+                for mono, H in picked.terms.items():
+                    out.acc(_mono(mono, extra), H, 1.0, rowscale=c[:, 0])
+    bound_parts = []
+    for atoms, col in split_array(limit.bound()):
+        col = col.reshape([-1, 1])
+        if col.shape[0] not in (1, c_rows):
+            raise ValueError("the bound has {} rows for {} lines".format(col.shape[0], c_rows))
+        bound_parts.append((_mono(_atoms_mono(slots, atoms)), np.broadcast_to(col, [c_rows, 1])))
+    return out, bound_parts
 
 
 def _aim_entry(aim, axis_index):
@@ -422,7 +437,7 @@ def compile_plan(form, ops, costs=None, limits=None):
     # ---- constraint rows -------------------------------------------------
     pieces, bounds = [], []
     for limit in limits:
-        poly, bound = _limit_poly(form, ops, PM, limit)
+        poly, bound = _limit_poly(form, ops, PM, limit, slots)
         plan.row_offsets.append(sum(plan.limit_rows))
         plan.limit_rows.append(poly.rows)
         pieces.append(poly)
@@ -434,8 +449,10 @@ def compile_plan(form, ops, costs=None, limits=None):
     Yacc = Poly(ops, nv + nc, ng + 1)
     if nc:
         Yacc.terms[()] = ops.zeros(nv + nc, ng + 1)
-        col = np.vstack(bounds)
-        ops.axpy(ops.sub(Yacc.terms[()], nv, nv + nc, ng, ng + 1), ops.upload(col), 1.0, None)
+    for row0, parts in zip(plan.row_offsets, bounds):  # the constant column of h
+        for mono, col in parts:
+            _block_acc(Yacc, mono, (nv + row0, nv + row0 + col.shape[0], ng, ng + 1),
+                       ops.upload(np.ascontiguousarray(col)), 1.0)
     for row0, poly in zip(plan.row_offsets, pieces):
         for mono, H in poly.terms.items():
             _block_acc(Gacc, mono, (row0, row0 + poly.rows, 0, nv),

@@ -12,6 +12,15 @@ in the reference, because it fixes the row order of G.
 import numpy as np
 
 from . import tools as use
+from .params import contains_expr, is_expr
+
+
+def _geometry(value, shape, as_float=False):
+    """``value`` as a 2-D array of ``shape``; object dtype when it holds
+    per-instance ``Param`` expressions (kept symbolic for the plan compiler,
+    which splits it into monomials x constant arrays)."""
+    arr = np.array(value, dtype=object if contains_expr(value) else None).reshape(shape)
+    return arr.astype(float) if (as_float and arr.dtype != object) else arr
 
 
 def _span(schedule):
@@ -31,7 +40,7 @@ class Constraint:
         self.L = []
         if L is not None:
             self.arrange_L(L)
-        self.extreme = np.array(extreme).reshape([-1, 1]).astype(float)
+        self.extreme = _geometry(extreme, [-1, 1], as_float=True)
         self.initialize_geometry(arrow, center)
         self.check_geometry()
         self.normalize()
@@ -81,7 +90,7 @@ class Constraint:
 
     def initialize_geometry(self, arrow, center):
         if arrow is not None:
-            self.arrow = np.array(arrow).reshape([-1, self.axes_len])
+            self.arrow = _geometry(arrow, [-1, self.axes_len])
         elif self.axes_len == 1:
             self.arrow = np.ones(self.extreme.shape)
         else:
@@ -91,7 +100,7 @@ class Constraint:
         if center is None:
             self.center = np.zeros([1, self.axes_len])
         else:
-            self.center = np.array(center).reshape([-1, self.axes_len])
+            self.center = _geometry(center, [-1, self.axes_len])
 
     def check_geometry(self):
         rows = self._geometry_rows()
@@ -111,7 +120,9 @@ class Constraint:
 
     def normalize(self):
         """Makes every extreme non-negative by flipping the row's arrow
-        (restrictions.py:181-194)."""
+        (restrictions.py:181-194).  The sign of a per-instance (``Param``)
+        extreme is not known here: such a row is left as written, the caller
+        promises it is non-negative for every instance."""
         n_arrow, n_extreme = self.arrow.shape[0], self.extreme.shape[0]
         if n_arrow != n_extreme:
             if n_arrow == 1:
@@ -119,6 +130,8 @@ class Constraint:
             elif n_extreme == 1:
                 self.extreme = np.resize(self.extreme, [n_arrow, 1])
         for i in range(self.extreme.shape[0]):
+            if is_expr(self.extreme[i, 0]):
+                continue
             if self.extreme[i] < 0:
                 self.extreme[i] = -self.extreme[i]
                 self.arrow[i] = -self.arrow[i]
@@ -153,11 +166,11 @@ class Constraint:
         if L is not None:
             self.arrange_L(L)
         if extreme is not None:
-            self.extreme = np.array(extreme).reshape([-1, 1])
+            self.extreme = _geometry(extreme, [-1, 1])
         if arrow is not None:
-            self.arrow = np.array(arrow).reshape([-1, self.axes_len])
+            self.arrow = _geometry(arrow, [-1, self.axes_len])
         if center is not None:
-            self.center = np.array(center).reshape([-1, self.axes_len])
+            self.center = _geometry(center, [-1, self.axes_len])
         if extreme is not None or arrow is not None:
             self.check_geometry()
             self.normalize()
@@ -292,7 +305,7 @@ class Box:
             limit.update(schedule=new_schedule)
 
     def translate_in_TS(self, translation):
-        self.ts_center += translation
+        self.ts_center = self.ts_center + translation  # (not +=: the translation may be a Param)
         for limit in self.constraints:
             limit.update(center=limit.center + translation)
 

@@ -9,6 +9,8 @@ host exactly as in the reference, because they define index layouts.
 """
 import numpy as np
 
+from . import params as _params
+
 # ---------------------------------------------------------------------------
 # prediction matrices (reference: tools.py:14-33)
 # ---------------------------------------------------------------------------
@@ -143,16 +145,24 @@ def recenter_support(box, **kargs):
 
 
 def rotation2D(angle):
-    c, s = np.cos(angle), np.sin(angle)
+    """[[c, -s], [s, c]]  (tools.py:217-220); ``angle`` may be a per-instance
+    ``Param`` expression, the matrix then holds expressions."""
+    c, s = _params.cos(angle), _params.sin(angle)
     return np.array([[c, -s], [s, c]])
 
 
 def rotation3D(angle, axis="z"):
+    """Rotation about one coordinate axis (tools.py:223-237); about "y" the 2-D
+    block lands transposed on rows/columns (0, 2), i.e. the right-handed
+    rotation, exactly as the reference fills it."""
     keep = {"x": 0, "y": 1, "z": 2}[axis]
     plane = [i for i in range(3) if i != keep]
-    R = np.zeros([3, 3])
+    block = rotation2D(angle)
+    if axis == "y":
+        block = block.T
+    R = np.zeros([3, 3], dtype=block.dtype)
     R[keep, keep] = 1
-    R[np.ix_(plane, plane)] = rotation2D(angle)
+    R[np.ix_(plane, plane)] = block
     return R
 
 

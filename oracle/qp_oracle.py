@@ -129,8 +129,22 @@ def _nlines(limit):
     return sizes[sizes != 1][0]
 
 
-def qp_constraint(limit, PM, given):
+def _numbers(x, params):
+    """Geometry of ONE instance as float64: entries that are per-instance
+    expressions of the host mirror are evaluated with ``params``."""
+    arr = np.asarray(x)
+    if arr.dtype != object:
+        return arr
+    out = np.empty(arr.shape)
+    for idx, e in np.ndenumerate(arr):
+        out[idx] = _value(e, params)
+    return out
+
+
+def qp_constraint(limit, PM, given, params=None):
     """(A, h) of one limit: A = sum_a c_a (*|@) Mo[sched], h = bound - cMg@given."""
+    arrow, center = _numbers(limit.arrow, params), _numbers(limit.center, params)
+    extreme = _numbers(limit.extreme, params)
     ng = PM[limit.variable + limit.axes[0]][0].shape[1]
     nv = PM[limit.variable + limit.axes[0]][1].shape[1]
     rows = PM[limit.variable + limit.axes[0]][0].shape[0]
@@ -140,10 +154,10 @@ def qp_constraint(limit, PM, given):
     cMo = np.zeros([c_rows, nv])
     sched = range(rows) if not limit.schedule else limit.schedule
     # restrictions.py:198-199
-    bound = limit.extreme + np.sum(limit.arrow * limit.center, axis=1).reshape([-1, 1])
+    bound = extreme + np.sum(arrow * center, axis=1).reshape([-1, 1])
     for i, axis in enumerate(limit.axes):
         Mg, Mo = PM[limit.variable + axis]
-        c = limit.arrow[:, i][:, None]                    # restrictions.py:175-179
+        c = arrow[:, i][:, None]                          # restrictions.py:175-179
         if limit.L:
             c = c * limit.L[i]
             cMg += c @ Mg[sched]
@@ -199,7 +213,7 @@ def all_qp_matrices(form, given, params=None, PM=None):
     """(A, h, Q, q) of one instance; ``given`` is a (ng, 1) column."""
     if PM is None:
         PM = preview_matrices(form, params)
-    parts = [qp_constraint(lim, PM, given) for lim in all_limits(form)]
+    parts = [qp_constraint(lim, PM, given, params) for lim in all_limits(form)]
     A = np.vstack([p[0] for p in parts])
     h = np.vstack([p[1] for p in parts])
     costs = [qp_cost(c, PM, given, params) for c in form.goals.values()]

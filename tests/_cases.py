@@ -55,6 +55,17 @@ def biped_batched(g, backend=None):
     return form, params
 
 
+def biped_yaw(g, backend=None):
+    """Per-instance feet orientation (golden biped_n*_yaw: the reference's
+    Box.rotate_in_TS applied instance by instance)."""
+    form = formulate_biped(
+        default_configuration(int(g["N"])), omega=Param("omega"),
+        target_vel=[Param("vel_x"), Param("vel_y")], yaw=Param("yaw"), backend=backend,
+    )
+    params = {k: g[k] for k in ("omega", "vel_x", "vel_y", "yaw")}
+    return form, params
+
+
 def body_test_formulation(backend=None):
     """The formulation of the reference's python/tests/test_body.py:23-98."""
     axes = ["_x", "_y"]

@@ -132,6 +132,32 @@ def biped_batch(name, N, batch, seed, terminal_weight=None):
     )
 
 
+def biped_yaw(name, N, batch, seed):
+    """Per-instance feet orientation: the support polygon and the terminal box
+    turned by yaw_b through the reference's Box.rotate_in_TS
+    (restrictions.py:437-457) on top of per-instance omega / aims."""
+    form = formulate_biped(biped_conf(N))
+    vals = synthetic.biped_inputs(seed, batch, N)
+    yaw = np.random.default_rng(seed + 7).uniform(-1.2, 1.2, batch)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    boxes = [form.constraint_boxes[k] for k in ("support_polygon", "terminal_Constraint")]
+    straight = [[lim.arrow.copy() for lim in box.constraints] for box in boxes]
+    As, hs, Qs, qs = [], [], [], []
+    for b in range(batch):
+        set_omega(form, vals["omega"][b])
+        form.goals["track vel_x"].update(aim=vals["vel_x"][b])
+        form.goals["track vel_y"].update(aim=vals["vel_y"][b])
+        for box, arrows in zip(boxes, straight):
+            for lim, arrow in zip(box.constraints, arrows):
+                lim.update(arrow=arrow.copy())  # rotate_in_TS turns the CURRENT arrows
+            box.rotate_in_TS(ref_tools.rotation2D(yaw[b]))
+        A, h, Q, q = form.generate_all_qp_matrices(given[b][:, None])
+        As.append(A), hs.append(h[:, 0]), Qs.append(Q), qs.append(q[:, 0])
+    save(name, seed=seed, N=N, given=given, omega=vals["omega"], vel_x=vals["vel_x"],
+         vel_y=vals["vel_y"], yaw=yaw, terminal_weight=-1.0,
+         A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs), **layout(form))
+
+
 def biped_tick(N=24):
     """Structure after Formulation.update (ragged sizes, SURVEY Appendix B#1)."""
     conf = biped_conf(N)
@@ -223,6 +249,10 @@ def generic_per_instance(name, seed, nx, nu, N, n_rows, batch):
 
 
 if __name__ == "__main__":
+    if sys.argv[1:] == ["yaw"]:
+        biped_yaw("biped_n24_yaw.npz", 24, 5, 1011)
+        biped_yaw("biped_n100_yaw.npz", 100, 2, 1012)
+        sys.exit(0)
     if sys.argv[1:] == ["per_instance"]:
         generic_per_instance("generic_perinst_small.npz", 31, 4, 2, 10, 2, 4)
         generic_per_instance("generic_perinst_odd.npz", 32, 3, 3, 7, 1, 3)

@@ -155,6 +155,49 @@ def test_biped_vs_oracle_random(dev, N, batch):
         cases.assert_qp_close((G[b], h[b], P[b], q[b]), ref)
 
 
+@pytest.mark.parametrize("name", ["biped_n24_yaw", "biped_n100_yaw"])
+def test_biped_per_instance_yaw_goldens(dev, name):
+    """Box.rotate_in_TS with a per-instance angle; the golden is the
+    reference's rotate_in_TS run instance by instance (make_goldens.py yaw)."""
+    g = cases.golden(name)
+    form, params = cases.biped_yaw(g)
+    cases.check_layout(form, g)
+    out = form.generate_all_qp_matrices_batched(g["given"], params)
+    cases.assert_qp_close(
+        (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy()),
+        (g["A"], g["h"], g["Q"], g["q"]),
+    )
+
+
+def test_biped_per_instance_geometry_vs_oracle(dev):
+    """Rotation + per-instance centre and scale of the support polygon, batch 45
+    at N=100 (7 streamed G terms), against the oracle."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    N, batch = 100, 45
+    form = cases.formulate_biped(
+        cases.default_configuration(N), omega=Param("omega"),
+        target_vel=[Param("vel_x"), Param("vel_y")], yaw=Param("yaw"), preview=False)
+    box = form.constraint_boxes["support_polygon"]
+    box.translate_in_TS(np.array([Param("cx"), Param("cy")]))
+    box.scale_box(Param("scale"))
+    form.make_preview_matrices()
+    vals = synthetic.biped_inputs(321, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    rng = np.random.default_rng(4)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    params.update(yaw=rng.uniform(-3, 3, batch), cx=rng.normal(size=batch) * 0.01,
+                  cy=rng.normal(size=batch) * 0.01, scale=rng.uniform(0.8, 1.2, batch))
+    out = form.generate_all_qp_matrices_batched(given, params)
+    P, q, G, h = out.P_numpy(), out.q_numpy(), out.G_numpy(), out.h_numpy()
+    assert np.abs(G[0] - G[1]).max() > 1e-3  # G really differs between instances
+    for b in (0, 1, 22, 44):
+        one = {k: float(v[b]) for k, v in params.items()}
+        ref = orc.all_qp_matrices(form, given[b][:, None], one)
+        cases.assert_qp_close((G[b], h[b], P[b], q[b]), ref)
+
+
 def test_reference_test_body_case(dev):
     g = cases.golden("test_body")
     body = cases.body_test_formulation()

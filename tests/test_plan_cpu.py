@@ -129,3 +129,72 @@ def test_per_instance_weight_and_errors(cpu_extend):
         bad = cases.formulate_biped(cases.default_configuration(), backend=NumpyBackend())
         bad.goals["track vel_x"].update(aim=np.ones([3, 1]))
         bad.generate_all_qp_matrices(np.zeros([bad.given_len, 1]))
+
+
+# ------------------------------------------------- per-instance constraint geometry
+@pytest.mark.parametrize("name", ["biped_n24_yaw", "biped_n100_yaw"])
+def test_biped_per_instance_yaw(cpu_extend, name):
+    """Box.rotate_in_TS with a Param angle: G becomes per-instance through the
+    monomials cos(yaw), sin(yaw) (x the omega ones), checked against the
+    reference's rotate_in_TS run instance by instance."""
+    g = cases.golden(name)
+    form, params = cases.biped_yaw(g, NumpyBackend())
+    cases.check_layout(form, g)
+    out = form.generate_all_qp_matrices_batched(g["given"], params)
+    cases.assert_qp_close((out.G, out.h, out.P, out.q), (g["A"], g["h"], g["Q"], g["q"]))
+    p = form._compiled()
+    assert sorted(form.parameter_names()) == ["omega", "vel_x", "vel_y", "yaw"]
+    # G: {1, -1/w^2, 1/w} for the straight boxes, {cos, sin} x {1, -1/w^2} and {cos, sin} x 1/w
+    assert len(p.G_terms) <= planmod.MAX_TERMS and len(p.P_terms) == 3
+
+
+def test_geometry_expressions_and_errors(cpu_extend):
+    from mpc_interface_b200 import Box, Constraint, tools as use
+    from mpc_interface_b200.params import cos, sin, split_array, evaluate_array
+
+    yaw, d = Param("yaw"), Param("d")
+    R = use.rotation2D(yaw)
+    assert R.dtype == object and use.rotation3D(yaw, "y").dtype == object
+    for axis in "xyz":  # numeric rotations are unchanged
+        R3 = use.rotation3D(0.3, axis)
+        assert np.allclose(R3 @ R3.T, np.eye(3)) and np.isclose(np.linalg.det(R3), 1)
+    assert np.allclose(use.rotation3D(0.3, "y")[0, 2], np.sin(0.3))  # right-handed about y
+    parts = dict(split_array(np.array([[1.0, 2.0]]) @ R.T))
+    assert set(len(m) for m in parts) == {1} and len(parts) == 2
+    # a polynomial keeps products of atoms together: (1 + d) * cos(yaw)
+    poly = ((1 + d) * cos(yaw)).polynomial()
+    assert sorted(len(m) for m in poly) == [1, 2]
+    assert np.isclose(evaluate_array(np.array([(1 + d) * sin(yaw)]), {"d": 2.0, "yaw": 0.5})[0], 3 * np.sin(0.5))
+
+    box = Box.task_space("CoM", use.make_simetric_vertices([0.1, 0.05]), ["_x", "_y"])
+    box.rotate_in_TS(R)
+    assert all(lim.arrow.dtype == object for lim in box.constraints)
+    box.translate_in_TS(np.array([d, 0.0]))      # per-instance centre -> per-instance bound
+    assert box.constraints[0].bound().dtype == object
+    lim = Constraint("CoM_x", d)                  # a Param extreme is not sign-normalised
+    assert lim.extreme.dtype == object and lim.arrow[0, 0] == 1.0
+    with pytest.raises(TypeError):
+        box.set_safety_margin(0.01)               # needs numeric arrows (norm of the arrow)
+
+
+def test_per_instance_center_and_extreme(cpu_extend):
+    """recenter / translate / scale with Params against the oracle (h only changes)."""
+    from mpc_interface_b200.examples import synthetic
+    from oracle import qp_oracle as orc
+
+    N, batch = 24, 4
+    form = cases.formulate_biped(cases.default_configuration(N), backend=NumpyBackend())
+    box = form.constraint_boxes["support_polygon"]
+    box.translate_in_TS(np.array([Param("cx"), Param("cy")]))
+    box.scale_box(Param("scale"))
+    vals = synthetic.biped_inputs(5, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    rng = np.random.default_rng(9)
+    params = {"cx": rng.normal(size=batch) * 0.01, "cy": rng.normal(size=batch) * 0.01,
+              "scale": rng.uniform(0.8, 1.2, batch)}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    for b in range(batch):
+        one = {k: float(v[b]) for k, v in params.items()}
+        ref = orc.all_qp_matrices(form, given[b][:, None], one)
+        cases.assert_qp_close((out.G[b], out.h[b], out.P[b], out.q[b]), ref)
+    assert form._compiled().G_terms == [0]        # G itself stays shared
