@@ -66,3 +66,17 @@ def test_product_path_fails_loudly_without_gpu(lib):
 
     with pytest.raises(RuntimeError):
         Formulation()._ops()
+
+
+def test_cpp_header_builds_and_links(lib):
+    """include/mpci_gecko.hh (gecko::tools::extend_matrices, cpp/include/mpc-interface/
+    tools.hh:24-25) compiles with g++ and links against libmpci.so; the values are
+    checked on the GPU (test_gpu_parity.py::test_gecko_cpp_extend_matrices)."""
+    import _gecko_build
+
+    done = _gecko_build.run("--link-only")
+    assert done.returncode == 0, done.stdout + done.stderr
+    assert "mpci version 100" in done.stdout
+    if lib.mpci_device_count() == 0:  # no CPU fallback behind the C++ face either
+        failed = _gecko_build.run()
+        assert failed.returncode != 0 and "extend_matrices" in (failed.stdout + failed.stderr)
