@@ -452,7 +452,7 @@ def compile_plan(form, ops, costs=None, limits=None):
     for row0, parts in zip(plan.row_offsets, bounds):  # the constant column of h
         for mono, col in parts:
             _block_acc(Yacc, mono, (nv + row0, nv + row0 + col.shape[0], ng, ng + 1),
-                       ops.upload(np.ascontiguousarray(col)), 1.0)
+                       ops.upload(np.array(col)), 1.0)
     for row0, poly in zip(plan.row_offsets, pieces):
         for mono, H in poly.terms.items():
             _block_acc(Gacc, mono, (row0, row0 + poly.rows, 0, nv),
