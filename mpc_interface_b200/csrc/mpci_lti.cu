@@ -30,8 +30,11 @@ constexpr int TM = 2, TN = 4;  // 8x8 DMMA tiles per warp tile (rows x cols)
 
 struct LtiArgs {
   int n, m, N, S, n_groups;
-  int Nk;  // N rounded up to a multiple of 4
-  int LD;  // kPadL + Nk
+  int pad;  // zeros before d = 0 of every generator row: kPadL (DMMA mode) or 0
+  int LD;   // row length of gz: pad + (N + 1 rounded up to a multiple of 4), plus the
+            // skew that keeps the strided DMMA operand loads of the scan conflict-free
+  int LDw;  // row length of wz, likewise
+  int scan; // recursion mode: 1 = DMMA row bands + diagonal scan (needs tb / prev), 0 = plain
   const double *Qxx, *Quu, *Tx, *Tu, *cx, *cu, *arrow, *bound;  // device tables
   const int* grp_state;  // bit 0: the group has a non-zero cx; bit 1: one arrow for all rows
   const int2* tiles;     // DMMA warp tiles (row tile, column tile) of one (j, j') block, longest first
@@ -44,18 +47,38 @@ struct LtiArgs {
 };
 
 struct Smem {
-  double *A, *M0, *M1, *Q, *gp, *gz, *wz, *r, *f, *tx, *tu, *cg;
+  double *A, *M0, *M1, *Q, *gz, *wz, *r, *tx, *tu, *cg, *tb;
 };
 
-// gp (the raw doubling output) is dead once gz, wz, r and f are built: the
-// constraint phase reuses its space (cg) for the row windows and group tables.
-__host__ __device__ inline size_t lti_scratch_doubles(int n, int m, int N) {
-  const size_t gp = (size_t)(N + 1) * n * (m + 1), cg = (size_t)m * 4 * N + N + m + n;
-  return ((gp > cg ? gp : cg) + 1) & ~(size_t)1;
+// Shared memory of one instance (doubles):
+//   A, M0, M1, Q   4 n^2
+//   gz  [n][m+1][LD]  gz[i][c][pad + d] = (A^d [B | x0])[i][c], d = 0..N: the doubling
+//                     writes straight into it; column c = m is the free response,
+//                     f_k[i] = gz[i][m][pad + 1 + k]
+//   wz  [n][m][LD]    (Qxx Gam_d)[i][j]; dead after P and q, so the constraint phase
+//                     keeps its row windows and group tables (cg) there
+//   r   [n][N],  tx [n],  tu [m]
+//   tb  [kWarps][8][40]   the warps' T patches (band scan of the recursion mode only)
+__host__ __device__ inline int lti_row_len(int N, int pad) { return pad + (N + 1 + 3) / 4 * 4; }
+__host__ __device__ inline size_t lti_wz_doubles(int n, int m, int N, int LD) {
+  const size_t wz = (size_t)n * m * LD, cg = (size_t)m * 4 * N + N + m + n;
+  return ((wz > cg ? wz : cg) + 1) & ~(size_t)1;
 }
-__host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD) {
-  return (size_t)4 * n * n + lti_scratch_doubles(n, m, N) + (size_t)2 * n * m * LD +
-         (size_t)2 * n * N + n + m;
+__host__ __device__ inline size_t lti_r_doubles(int n, int N) { return ((size_t)n * N + 1) & ~(size_t)1; }
+__host__ __device__ inline size_t lti_scan_doubles() { return (size_t)kWarps * 8 * 40; }
+__host__ __device__ inline size_t lti_gz_doubles(int n, int m, int LD) {
+  return ((size_t)n * (m + 1) * LD + 1) & ~(size_t)1;
+}
+// The scan reads its DMMA operands with lane (g, t) at word  -g + t * rows * LD: the 16
+// lanes of a half-warp hit 16 different 8-byte banks iff rows * LD = 4 or 12 (mod 16).
+__host__ __device__ inline int lti_skew(int LD, int rows) {
+  for (int x = LD; x < LD + 16; ++x)
+    if ((rows * x) % 16 == 4 || (rows * x) % 16 == 12) return x;
+  return LD;
+}
+__host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD, int LDw, int scan) {
+  return (size_t)4 * n * n + lti_gz_doubles(n, m, LD) + lti_wz_doubles(n, m, N, LDw) +
+         lti_r_doubles(n, N) + (scan ? lti_scan_doubles() : 0) + n + m;
 }
 
 __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
@@ -65,13 +88,12 @@ __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
   s.M0 = s.A + n * n;
   s.M1 = s.M0 + n * n;
   s.Q = s.M1 + n * n;
-  s.gp = s.Q + n * n;  // 4 n^2 doubles before it: 16-byte aligned (source of the bulk copies)
-  s.cg = s.gp;
-  s.gz = s.gp + lti_scratch_doubles(n, m, N);
-  s.wz = s.gz + (size_t)n * m * a.LD;
-  s.r = s.wz + (size_t)n * m * a.LD;
-  s.f = s.r + (size_t)n * N;
-  s.tx = s.f + (size_t)n * N;
+  s.gz = s.Q + n * n;
+  s.wz = s.gz + lti_gz_doubles(n, m, a.LD);  // an even number of doubles before it:
+  s.cg = s.wz;                               // 16-byte aligned (source of the bulk copies)
+  s.r = s.wz + lti_wz_doubles(n, m, N, a.LDw);
+  s.tb = s.r + lti_r_doubles(n, N);  // 16-byte aligned (double2 stores of the T tiles)
+  s.tx = s.tb + (a.scan ? lti_scan_doubles() : 0);
   s.tu = s.tx + n;
   return s;
 }
@@ -87,7 +109,8 @@ __device__ __forceinline__ void dmma8x8x4(double& d0, double& d1, double a, doub
 // phase 1 + 2: prediction data of instance b
 // ---------------------------------------------------------------------------
 __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
-  const int n = a.n, m = a.m, N = a.N, w = a.m + 1, tid = threadIdx.x;
+  const int n = a.n, m = a.m, N = a.N, w = a.m + 1, LD = a.LD, pad = a.pad, tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
   const double* Ab = a.A + b * a.strideA;
   const double* Bb = a.B + b * a.strideB;
   const double* xb = a.x0 + b * n;
@@ -97,9 +120,16 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     s.M0[e] = v;
     s.Q[e] = a.Qxx[e];
   }
+  // d = 0 of every row, and the zeros before it (causality of the DMMA operands)
   for (int e = tid; e < n * w; e += kThreads) {
-    const int i = e / w, c = e % w;
-    s.gp[e] = (c < m) ? Bb[i * m + c] : xb[i];
+    const int i = e / w, c = e - i * w;
+    s.gz[(size_t)e * LD + pad] = (c < m) ? Bb[i * m + c] : xb[i];
+  }
+  if (pad) {
+    for (int row = warp; row < n * w + n * m; row += kWarps) {
+      double* dst = row < n * w ? s.gz + (size_t)row * LD : s.wz + (size_t)(row - n * w) * a.LDw;
+      for (int x = lane; x < pad; x += 32) dst[x] = 0.0;
+    }
   }
   // per-instance offsets of the gradient: t = T[:, S] + T[:, :S] @ scalars_b
   for (int e = tid; e < n + m; e += kThreads) {
@@ -111,30 +141,33 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   }
   __syncthreads();
 
-  // prefix doubling: Gam'_{have+d} = A^have Gam'_d,  A^(2 have) = (A^have)^2.
-  // A thread keeps one entry (i, c) of the n x (m+1) block and strides over d, so
-  // the index arithmetic (integer divisions) is done once, not per element.
+  // prefix doubling: Gam'_{have+d} = A^have Gam'_d,  A^(2 have) = (A^have)^2, d = 0..N.
+  // Rows are (i, c) with d contiguous, so consecutive threads take consecutive d (no
+  // bank conflicts, M0 reads are broadcasts); `have` is a power of two, so the split
+  // of the flat index into (i, d) is a shift in every round but possibly the last.
   double* M0 = s.M0;
   double* M1 = s.M1;
-  const int blk = n * w;
-  const int lane = tid & 31, warp = tid >> 5;
-  const int per = blk <= kThreads ? blk : kThreads;  // entries handled per pass over the block
-  const int dgroups = kThreads / per;                // concurrent values of d
-  const int dg = tid / per;
-  const int sq_i = tid / n, sq_c = tid % n;
-  for (int have = 1; have < N + 1;) {
+  const int sq_i = tid / n, sq_c = tid - sq_i * n;
+  int sh = 0;
+  for (int have = 1; have < N + 1; ++sh) {
     const int cnt = min(have, N + 1 - have);
-    for (int rem = tid % per; rem < blk; rem += per) {
-      const int i = rem / w;
-      const double* Mi = M0 + i * n;
-      if (dg < dgroups)
-        for (int d = dg; d < cnt; d += dgroups) {
-          const double* src = s.gp + (size_t)d * blk + (rem - i * w);
-          double acc = 0.0;
-#pragma unroll 4
-          for (int l = 0; l < n; ++l) acc = fma(Mi[l], src[l * w], acc);
-          s.gp[(size_t)(have + d) * blk + rem] = acc;
+    const bool pow2 = cnt == have;
+    for (int c = 0; c < w; ++c) {
+      double* col = s.gz + (size_t)c * LD + pad;  // row (i, c) starts at col + i * w * LD
+      for (int e = tid; e < n * cnt; e += kThreads) {
+        const int i = pow2 ? (e >> sh) : e / cnt;
+        const int d = e - i * cnt;
+        const double* Mi = M0 + i * n;
+        const double* src = col + d;
+        double acc0 = 0.0, acc1 = 0.0;
+        int l = 0;
+        for (; l + 1 < n; l += 2) {
+          acc0 = fma(Mi[l], src[(size_t)l * w * LD], acc0);
+          acc1 = fma(Mi[l + 1], src[(size_t)(l + 1) * w * LD], acc1);
         }
+        if (l < n) acc0 = fma(Mi[l], src[(size_t)l * w * LD], acc0);
+        col[(size_t)i * w * LD + have + d] = acc0 + acc1;
+      }
     }
     if (have + cnt < N + 1) {  // the next power is only needed for another round
       for (int e2 = tid; e2 < n * n; e2 += kThreads) {
@@ -150,38 +183,29 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     have += cnt;
   }
 
-  // zero-padded generators: gz[i][j][kPadL + d] = Gam_d[i][j], wz = (Qxx Gam_d)[i][j]
-  // (a warp per (i, j) pair, lanes along d)
-  const int LD = a.LD;
+  // wz[i][j][pad + d] = (Qxx Gam_d)[i][j], d < N (a warp per (i, j) row, lanes along d)
   for (int ij = warp; ij < n * m; ij += kWarps) {
     const int i = ij / m, j = ij - i * m;
     const double* Qi = s.Q + i * n;
-    double* gdst = s.gz + (size_t)ij * LD;
-    double* wdst = s.wz + (size_t)ij * LD;
-    for (int x = lane; x < LD; x += 32) {
-      const int d = x - kPadL;
-      double g = 0.0, wv = 0.0;
-      if (d >= 0 && d < N) {
-        const double* src = s.gp + (size_t)d * blk + j;
-        g = src[i * w];
+    const double* src = s.gz + (size_t)j * LD + pad;
+    double* wdst = s.wz + (size_t)ij * a.LDw + pad;
+    for (int d = lane; d < N; d += 32) {
+      double wv = 0.0;
 #pragma unroll 4
-        for (int l = 0; l < n; ++l) wv = fma(Qi[l], src[l * w], wv);
-      }
-      gdst[x] = g;
-      wdst[x] = wv;
+      for (int l = 0; l < n; ++l) wv = fma(Qi[l], src[(size_t)l * w * LD + d], wv);
+      wdst[d] = wv;
     }
   }
   // r[i][k] = sum_l sym(Qxx)[i][l] f_k[l] - tx[i],  f_k = Gam'_{k+1}[:, m]
   for (int i = warp; i < n; i += kWarps) {
     const double txi = s.tx[i];
+    const double* f = s.gz + (size_t)m * LD + pad + 1;  // f_k[l] = f[l * w * LD + k]
     for (int k = lane; k < N; k += 32) {
-      const double* f = s.gp + (size_t)(k + 1) * blk + m;
       double acc = -txi;
 #pragma unroll 4
       for (int l = 0; l < n; ++l)
-        acc = fma(0.5 * (s.Q[i * n + l] + s.Q[l * n + i]), f[l * w], acc);
+        acc = fma(0.5 * (s.Q[i * n + l] + s.Q[l * n + i]), f[(size_t)l * w * LD + k], acc);
       s.r[(size_t)i * N + k] = acc;
-      s.f[(size_t)i * N + k] = f[i * w];
     }
   }
   __syncthreads();
@@ -226,8 +250,8 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
     // steps in which every sub-tile is inside its span run without predicates
     const int full = max(0, N - max(p0 + 8 * (TM - 1), q0 + 8 * (TN - 1))) & ~3;
     for (int i = 0; i < n; ++i) {
-      const double* ga = s.gz + (size_t)(i * m + j) * LD + kPadL + (N - 1 - t - p0 - g);
-      const double* wb = s.wz + (size_t)(i * m + jp) * LD + kPadL + (N - 1 - t - q0 - g);
+      const double* ga = s.gz + (size_t)(i * (m + 1) + j) * LD + kPadL + (N - 1 - t - p0 - g);
+      const double* wb = s.wz + (size_t)(i * m + jp) * a.LDw + kPadL + (N - 1 - t - q0 - g);
 #pragma unroll 2
       for (int s0 = 0; s0 < full; s0 += 4) {
         double av[TM], bv[TN];
@@ -302,22 +326,17 @@ __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __res
     for (int x = 0; x < M; ++x)
 #pragma unroll
       for (int y = 0; y < M; ++y) acc[x][y] = 0.0;
-    double ruu[M][M];
-#pragma unroll
-    for (int x = 0; x < M; ++x)
-#pragma unroll
-      for (int y = 0; y < M; ++y) ruu[x][y] = (delta == 0) ? a.Quu[x * M + y] : 0.0;
     for (int p = w_hi; p >= w_lo; --p) {
       if (p > p_hi || p < p_lo) continue;  // this diagonal has no entry in row p
       const int c = p + delta;
-      const double* ga = s.gz + kPadL + (N - 1 - p);
-      const double* wb = s.wz + kPadL + (N - 1 - c);
+      const double* ga = s.gz + a.pad + (N - 1 - p);
+      const double* wb = s.wz + a.pad + (N - 1 - c);
       for (int i = 0; i < n; ++i) {
         double gv[M], wv[M];
 #pragma unroll
-        for (int x = 0; x < M; ++x) gv[x] = ga[(i * M + x) * LD];
+        for (int x = 0; x < M; ++x) gv[x] = ga[(i * (M + 1) + x) * LD];
 #pragma unroll
-        for (int y = 0; y < M; ++y) wv[y] = wb[(i * M + y) * LD];
+        for (int y = 0; y < M; ++y) wv[y] = wb[(i * M + y) * a.LDw];
 #pragma unroll
         for (int x = 0; x < M; ++x)
 #pragma unroll
@@ -328,7 +347,8 @@ __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __res
       for (int x = 0; x < M; ++x)
 #pragma unroll
         for (int y = 0; y < M; ++y)
-          __stcs(dst + (size_t)x * N * nv + y * N, acc[x][y] + ruu[x][y]);
+          __stcs(dst + (size_t)x * N * nv + y * N,
+                 delta == 0 ? acc[x][y] + a.Quu[x * M + y] : acc[x][y]);
     }
   }
 }
@@ -353,9 +373,86 @@ __device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* _
       if (p > p_hi || p < p_lo) continue;
       const int c = p + delta;
       for (int i = 0; i < n; ++i)
-        acc = fma(s.gz[(size_t)(i * m + j) * LD + kPadL + (N - 1 - p)],
-                  s.wz[(size_t)(i * m + jp) * LD + kPadL + (N - 1 - c)], acc);
+        acc = fma(s.gz[(size_t)(i * (m + 1) + j) * LD + a.pad + (N - 1 - p)],
+                  s.wz[(size_t)(i * m + jp) * a.LDw + a.pad + (N - 1 - c)], acc);
       __stcs(Pb + (size_t)(j * N + p) * nv + (size_t)jp * N + c, acc + ruu);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// phase 3c: the displacement recursion, products on the tensor cores
+//   T[(j,p)][(j',c)] = Gam_{N-1-p}[:,j] . W_{N-1-c}[:,j']      (a rank-n product)
+//   P[(j,p)][(j',c)] = T + P[(j,p+1)][(j',c+1)]  (+ Quu[j][j'] on p == c)
+// A warp owns 32 adjacent diagonals of one (j, j') block, lane = diagonal, and walks
+// them bottom-up in bands of 8 rows.  Per band the warp forms the 8 x 40 patch of T
+// that its diagonals cross with five DMMA.8x8x4 per 4 states (one LDS per operand,
+// the tiles need no alignment because the operands are Toeplitz), parks it in its own
+// 2.5 kB of shared memory, and every lane then adds its 8 entries to the running sum
+// it keeps in a register: one LDS, one DADD and one coalesced store per entry of P
+// instead of 2 n LDS + n DFMA.  No block-wide barrier anywhere.
+// ---------------------------------------------------------------------------
+constexpr int kScanLd = 40;  // 32 diagonals + 8 rows
+// Entries of the patch that no active (p, c) consumes are never read back, so the
+// operand loads are NOT bounds-checked: a lane may fetch up to 47 doubles before wz or
+// N + 8 past a row end -- still inside this CTA's shared memory (mpci_lti_plan_create
+// only enables the scan when the layout guarantees it) -- and garbage there only
+// reaches its own row / column of T.  Only the padding of K to a multiple of 4 has to
+// contribute exact zeros.
+__device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1, nv = a.m * a.N;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int ksteps = (n + 3) / 4;
+  const int dchunks = (2 * N - 1 + 31) / 32;
+  double* tw = s.tb + (size_t)warp * 8 * kScanLd;
+  double2* tst = reinterpret_cast<double2*>(tw + g * kScanLd + 2 * t);  // this lane's C slots
+  const double* twl = tw + lane;                                         // this lane's diagonal
+  const long ga_step = (long)4 * w * LD, wb_step = (long)4 * m * a.LDw;
+  for (int item = warp; item < m * m * dchunks; item += kWarps) {
+    const int jj = item / dchunks, dc = item - jj * dchunks, j = jj / m, jp = jj - j * m;
+    const int d0 = dc * 32 - (N - 1);             // diagonal of lane 0 (delta = c - p)
+    const int delta = d0 + lane;
+    const int p_first = min(N - 1, N - 1 - d0);   // bottom-most row any lane touches
+    const int p_last = max(0, -min(d0 + 31, N - 1));  // top-most
+    // rows of this lane's diagonal: p_lo .. p_lo + p_rng (none when delta > N - 1)
+    const bool has = delta <= N - 1;
+    const int p_lo = has ? max(0, -delta) : N;
+    const unsigned p_rng = has ? (unsigned)(min(N - 1, N - 1 - delta) - p_lo) : 0u;
+    const double quu = (delta == 0) ? a.Quu[j * m + jp] : 0.0;
+    int p0 = N - 8 * ((N - 1 - p_first) / 8 + 1);  // rows p0 .. p0+7, bottom band first
+    const double* ga = s.gz + (size_t)(t * w + j) * LD + a.pad + (N - 1 - p0 - g);
+    const double* wb = s.wz + (size_t)(t * m + jp) * a.LDw + a.pad + (N - 1 - (p0 + d0) - g);
+    double* qd = Pb + (size_t)(j * N + p0 + 7) * nv + (size_t)jp * N + (p0 + 7 + delta);
+    const long qstep = (long)nv + 1;
+    double carry = 0.0;
+    for (; p0 + 7 >= p_last; p0 -= 8, ga += 8, wb += 8) {
+      double acc[5][2];
+#pragma unroll
+      for (int y = 0; y < 5; ++y) acc[y][0] = acc[y][1] = 0.0;
+      const double* gk = ga;
+      const double* wk = wb;
+      for (int ks = 0; ks < ksteps; ++ks, gk += ga_step, wk += wb_step) {
+        const bool k_ok = 4 * ks + t < n;
+        const double av = k_ok ? gk[0] : 0.0;
+        double bv[5];
+#pragma unroll
+        for (int y = 0; y < 5; ++y) bv[y] = k_ok ? wk[-8 * y] : 0.0;
+#pragma unroll
+        for (int y = 0; y < 5; ++y) dmma8x8x4(acc[y][0], acc[y][1], av, bv[y]);
+      }
+#pragma unroll
+      for (int y = 0; y < 5; ++y) tst[4 * y] = make_double2(acc[y][0], acc[y][1]);
+      __syncwarp();
+#pragma unroll
+      for (int r = 7; r >= 0; --r) {
+        if ((unsigned)(p0 + r - p_lo) <= p_rng) {
+          carry += twl[r * (kScanLd + 1)];
+          __stcs(qd, carry + quu);
+        }
+        qd -= qstep;
+      }
+      __syncwarp();
     }
   }
 }
@@ -370,7 +467,7 @@ __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ q
     const int len = N - p;
     double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;  // four chains hide the DFMA latency
     for (int i = 0; i < n; ++i) {
-      const double* gam = s.gz + (size_t)(i * m + j) * LD + kPadL;  // warp-uniform reads
+      const double* gam = s.gz + (size_t)(i * (m + 1) + j) * LD + a.pad;  // warp-uniform reads
       const double* r = s.r + (size_t)i * N + p;
       int d = 0;
       for (; d + 3 < len; d += 4) {
@@ -418,6 +515,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
   double* cu = arrow + N;                   // [m]
   double* cx = cu + m;                      // [n]
   const bool aligned = (N % 2 == 0) && Gb && ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0);
+  const double* fk = s.gz + (size_t)m * a.LD + a.pad + 1;  // f_k[i] = fk[i (m+1) LD + k]
   for (int grp = 0; grp < a.n_groups; ++grp) {
     const int flags = a.grp_state[grp];
     const bool state = (flags & 1) != 0;
@@ -434,9 +532,9 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
       for (int y = lane; y < 2 * N; y += 32) {
         double acc = (y == N - 1) ? cu[j] : 0.0;
         if (state && y < N) {
-          const double* src = s.gz + (size_t)j * a.LD + kPadL + (N - 1 - y);
+          const double* src = s.gz + (size_t)j * a.LD + a.pad + (N - 1 - y);
 #pragma unroll 4
-          for (int i = 0; i < n; ++i) acc = fma(cx[i], src[(size_t)i * m * a.LD], acc);
+          for (int i = 0; i < n; ++i) acc = fma(cx[i], src[(size_t)i * (m + 1) * a.LD], acc);
         }
         acc *= scale;
         cz[j * czld + y] = acc;
@@ -448,7 +546,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
         double acc = 0.0;
         if (state) {
 #pragma unroll 4
-          for (int i = 0; i < n; ++i) acc = fma(cx[i], s.f[(size_t)i * N + k], acc);
+          for (int i = 0; i < n; ++i) acc = fma(cx[i], fk[(size_t)i * (m + 1) * a.LD + k], acc);
         }
         hb[(size_t)grp * N + k] = a.bound[(size_t)grp * N + k] - arrow[k] * acc;
       }
@@ -491,7 +589,11 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
   if (lane == 0) bulk_wait_read();
 }
 
-__global__ void __launch_bounds__(kThreads)
+// One kernel per Hessian mode: the recursion needs neither the DMMA accumulators nor
+// the zero padding, so it is compiled for more resident CTAs per SM (the phases of
+// different instances -- latency-bound prediction, store-bound P / G -- then overlap).
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, MODE == MPCI_LTI_HESSIAN_RECURSION ? 3 : 2)
 lti_assemble_kernel(LtiArgs a) {
   extern __shared__ double lti_smem[];
   const Smem s = carve(lti_smem, a);
@@ -501,7 +603,8 @@ lti_assemble_kernel(LtiArgs a) {
     build_prediction(a, s, b);
     if (a.P) {
       double* Pb = a.P + (size_t)b * nv * nv;
-      if (a.hessian_mode == MPCI_LTI_HESSIAN_DMMA) hessian_dmma(a, s, Pb);
+      if (MODE == MPCI_LTI_HESSIAN_DMMA) hessian_dmma(a, s, Pb);
+      else if (a.scan) hessian_scan(a, s, Pb);
       else if (a.m == 1) hessian_recursion<1>(a, s, Pb);
       else if (a.m == 2) hessian_recursion<2>(a, s, Pb);
       else if (a.m == 3) hessian_recursion<3>(a, s, Pb);
@@ -518,12 +621,24 @@ lti_assemble_kernel(LtiArgs a) {
 
 }  // namespace
 
+static cudaError_t lti_opt_in_smem() {
+  cudaError_t e = cudaFuncSetAttribute(lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  return e;
+}
+
 struct mpci_lti_plan {
   int n, m, N, S, n_groups;
   void* dev;  // one allocation holding every table
   LtiArgs args;  // table pointers and sizes filled in, per-call fields zero
-  size_t smem_bytes;
-  int blocks_per_sm;
+  // per Hessian mode (index = MPCI_LTI_HESSIAN_*): the DMMA operands need kPadL zeros
+  // before every generator row, the recursion does not and so fits more CTAs per SM
+  int pad[2], LD[2], LDw[2], scan;
+  size_t smem_bytes[2];
+  int blocks_per_sm[2];
 };
 
 extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out) {
@@ -536,11 +651,27 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
       (d->n_groups && (!d->grp_cx || !d->grp_cu || !d->grp_arrow || !d->grp_bound)))
     return mpci::fail(-3, "lti_plan_create: NULL table");
   const int n = d->n, m = d->m, N = d->N, S = d->n_scalars, G = d->n_groups;
-  const int Nk = (N + 3) / 4 * 4, LD = kPadL + Nk;
-  const size_t smem = sizeof(double) * lti_smem_doubles(n, m, N, LD);
-  if (smem > 227 * 1024)
+  const int pads[2] = {kPadL, 0};
+  int LDs[2], LDws[2];
+  size_t smems[2];
+  for (int mode = 0; mode < 2; ++mode) {
+    LDs[mode] = LDws[mode] = lti_row_len(N, pads[mode]);
+    smems[mode] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], 0);
+  }
+  // the band scan of the recursion mode: skewed rows, the warps' T patches, and its
+  // unchecked operand loads reach 47 doubles before wz (hessian_scan)
+  const int LDg_scan = lti_skew(LDs[1], m + 1), LDw_scan = lti_skew(LDs[1], m);
+  const size_t smem_scan = sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, 1);
+  const int scan = smem_scan <= 227 * 1024 &&
+                   (size_t)4 * n * n + lti_gz_doubles(n, m, LDg_scan) >= 48;
+  if (scan) {
+    smems[MPCI_LTI_HESSIAN_RECURSION] = smem_scan;
+    LDs[1] = LDg_scan;
+    LDws[1] = LDw_scan;
+  }
+  if (smems[MPCI_LTI_HESSIAN_RECURSION] > 227 * 1024)
     return mpci::fail(-8, "lti_plan_create: n=%d m=%d N=%d needs %zu bytes of shared memory "
-                      "(limit 232448)", n, m, N, smem);
+                      "(limit 232448)", n, m, N, smems[MPCI_LTI_HESSIAN_RECURSION]);
   // pack the tables: Qxx | Quu | Tx | Tu | cx | cu | arrow | bound | flags(int)
   std::vector<double> host;
   auto push = [&](const double* p, size_t count) {
@@ -587,12 +718,17 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   if (e == cudaSuccess)
     e = cudaMemcpy(static_cast<char*>(p->dev) + bytes_d, flags.data(), bytes_i,
                    cudaMemcpyHostToDevice);
-  if (e == cudaSuccess)  // the largest opt-in size: plans of different sizes share the kernel
-    e = cudaFuncSetAttribute(lti_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             227 * 1024);
-  int per_sm = 0;
-  if (e == cudaSuccess)
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, lti_assemble_kernel, kThreads, smem);
+  if (e == cudaSuccess)  // the largest opt-in size: plans of different sizes share the kernels
+    e = lti_opt_in_smem();
+  int per_sm[2] = {0, 0};
+  for (int mode = 0; mode < 2 && e == cudaSuccess; ++mode)
+    if (smems[mode] <= 227 * 1024)
+      e = mode == MPCI_LTI_HESSIAN_DMMA
+              ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                    &per_sm[mode], lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA>, kThreads, smems[mode])
+              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                    &per_sm[mode], lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION>, kThreads,
+                    smems[mode]);
   if (e != cudaSuccess) {
     int rc = mpci::cuda_fail(e, "lti_plan_create");
     if (p->dev) cudaFree(p->dev);
@@ -602,14 +738,20 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   const double* base = static_cast<const double*>(p->dev);
   p->n = n; p->m = m; p->N = N; p->S = S; p->n_groups = G;
   LtiArgs& a = p->args;
-  a.n = n; a.m = m; a.N = N; a.S = S; a.n_groups = G; a.Nk = Nk; a.LD = LD;
+  a.n = n; a.m = m; a.N = N; a.S = S; a.n_groups = G;
   a.Qxx = base + oQ; a.Quu = base + oR; a.Tx = base + oTx; a.Tu = base + oTu;
   a.cx = base + ocx; a.cu = base + ocu; a.arrow = base + oar; a.bound = base + obd;
   a.grp_state = reinterpret_cast<const int*>(static_cast<const char*>(p->dev) + bytes_d);
   a.tiles = reinterpret_cast<const int2*>(a.grp_state + tiles_off);
   a.n_tiles = (int)tile_rc.size() / 2;
-  p->smem_bytes = smem;
-  p->blocks_per_sm = per_sm < 1 ? 1 : per_sm;
+  p->scan = scan;
+  for (int mode = 0; mode < 2; ++mode) {
+    p->pad[mode] = pads[mode];
+    p->LD[mode] = LDs[mode];
+    p->LDw[mode] = LDws[mode];
+    p->smem_bytes[mode] = smems[mode];
+    p->blocks_per_sm[mode] = per_sm[mode] < 1 ? 1 : per_sm[mode];
+  }
   *out = p;
   return 0;
 }
@@ -652,17 +794,27 @@ extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long s
     return mpci::fail(-1, "lti_assemble: unknown hessian_mode %d", mode);
   if ((strideA != 0 && strideA < (long)p->n * p->n) || (strideB != 0 && strideB < (long)p->n * p->m))
     return mpci::fail(-4, "lti_assemble: instance strides smaller than the matrices");
+  if (p->smem_bytes[mode] > 227 * 1024)
+    return mpci::fail(-8, "lti_assemble: n=%d m=%d N=%d needs %zu bytes of shared memory in the "
+                      "DMMA mode (limit 232448); use MPCI_LTI_HESSIAN_RECURSION", p->n, p->m, p->N,
+                      p->smem_bytes[mode]);
   LtiArgs a = p->args;
+  a.pad = p->pad[mode]; a.LD = p->LD[mode]; a.LDw = p->LDw[mode];
+  a.scan = (mode == MPCI_LTI_HESSIAN_RECURSION) ? p->scan : 0;
   a.A = A; a.B = B; a.x0 = x0; a.scalars = scalars; a.strideA = strideA; a.strideB = strideB;
   a.P = P; a.q = q; a.G = G; a.h = h; a.batch = batch; a.hessian_mode = mode;
   int dev = 0, sms = 148;
   MPCI_CUDA(cudaGetDevice(&dev));
   MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  MPCI_CUDA(cudaFuncSetAttribute(lti_assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 227 * 1024));  // per device: the plan may be used on another GPU
-  const long resident = (long)sms * p->blocks_per_sm;
+  MPCI_CUDA(lti_opt_in_smem());  // per device: the plan may be used on another GPU
+  const long resident = (long)sms * p->blocks_per_sm[mode];
   const unsigned grid = (unsigned)(batch < resident ? batch : resident);
-  lti_assemble_kernel<<<grid, kThreads, p->smem_bytes, mpci::as_stream(stream)>>>(a);
+  if (mode == MPCI_LTI_HESSIAN_DMMA)
+    lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA>
+        <<<grid, kThreads, p->smem_bytes[mode], mpci::as_stream(stream)>>>(a);
+  else
+    lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION>
+        <<<grid, kThreads, p->smem_bytes[mode], mpci::as_stream(stream)>>>(a);
   MPCI_LAUNCH_CHECK("lti_assemble_kernel");
   return 0;
 }
