@@ -10,7 +10,7 @@ tail -8 gpurun_out/pytest_gpu.log
 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; tail -2 gpurun_out/smoke.log
 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; tail -c 3000 gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 if [ "$1" = "noprof" ]; then exit 0; fi
-SHORT="python bench.py --steps 2 --warmup 3 --batch 8192 --e2e-batch 512 --no-cpu-baseline"
+SHORT="python bench.py --steps 2 --warmup 3 --batch 8192 --e2e-batch 512 --no-cpu-baseline --no-lti"
 $SHORT > gpurun_out/short_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
     --log-file gpurun_out/launches.csv $SHORT > gpurun_out/short_ncu.log 2>&1
