@@ -217,6 +217,12 @@ int mpci_lti_assemble(const mpci_lti_plan* plan, const double* A_dev, long strid
  * (for the FP64 roofline; the structural count is SURVEY.md 8(d)).            */
 double mpci_lti_hessian_flops(const mpci_lti_plan* plan, int hessian_mode);
 
+/* How the plan maps onto an SM in `hessian_mode` (for benchmarks and ncu cross-checks):
+ * info[0] = dynamic shared memory per CTA (bytes), info[1] = resident CTAs per SM,
+ * info[2] = 1 when the recursion uses the DMMA patch scan, info[3] / info[4] = row
+ * lengths (doubles) of the generator arrays gz / wz in shared memory.                   */
+int mpci_lti_plan_info(const mpci_lti_plan* plan, int hessian_mode, long info[5]);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,7 +23,13 @@
 
 namespace {
 
-constexpr int kThreads = 256;
+#ifndef MPCI_LTI_THREADS
+#define MPCI_LTI_THREADS 256
+#endif
+#ifndef MPCI_LTI_MINBLOCKS
+#define MPCI_LTI_MINBLOCKS 3  /* resident CTAs per SM the recursion kernel is compiled for */
+#endif
+constexpr int kThreads = MPCI_LTI_THREADS;
 constexpr int kWarps = kThreads / 32;
 constexpr int kPadL = 36;  // zeros before d = 0 of every generator (>= 8*max(TM,TN)+3)
 constexpr int TM = 2, TN = 4;  // 8x8 DMMA tiles per warp tile (rows x cols)
@@ -607,7 +613,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
 // the zero padding, so it is compiled for more resident CTAs per SM (the phases of
 // different instances -- latency-bound prediction, store-bound P / G -- then overlap).
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, MODE == MPCI_LTI_HESSIAN_RECURSION ? 3 : 2)
+__global__ void __launch_bounds__(kThreads, MODE == MPCI_LTI_HESSIAN_RECURSION ? MPCI_LTI_MINBLOCKS : (kThreads > 256 ? 1 : 2))
 lti_assemble_kernel(LtiArgs a) {
   extern __shared__ double lti_smem[];
   const Smem s = carve(lti_smem, a);
@@ -807,6 +813,18 @@ extern "C" double mpci_lti_hessian_flops(const mpci_lti_plan* p, int mode) {
           if (span > 0) dmmas += (span + 3) / 4;
         }
   return dmmas * n * m * m * 512.0 + 2.0 * n * n * m * N;
+}
+
+extern "C" int mpci_lti_plan_info(const mpci_lti_plan* p, int mode, long info[5]) {
+  if (!p || !info) return mpci::fail(-3, "lti_plan_info: NULL argument");
+  if (mode != MPCI_LTI_HESSIAN_DMMA && mode != MPCI_LTI_HESSIAN_RECURSION)
+    return mpci::fail(-1, "lti_plan_info: unknown hessian_mode %d", mode);
+  info[0] = (long)p->smem_bytes[mode];
+  info[1] = p->blocks_per_sm[mode];
+  info[2] = mode == MPCI_LTI_HESSIAN_RECURSION ? p->scan : 0;
+  info[3] = p->LD[mode];
+  info[4] = p->LDw[mode];
+  return 0;
 }
 
 extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long strideA,

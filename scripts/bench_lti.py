@@ -93,7 +93,7 @@ def run_config(name, batch=0, reps=5, peaks=None):
             "hbm_gbs_all": bytes_qp * B / (t_all * 1e-3) / 1e9,
             "hbm_gbs_Gh": 8.0 * (nc * nv + nc) * B / (t_G * 1e-3) / 1e9,
             "hbm_gbs_P": 8.0 * nv * nv * B / (t_P * 1e-3) / 1e9,
-            "hbm_peak_gbs": peaks["hbm_gbs"],
+            "hbm_peak_gbs": peaks["hbm_gbs"], "launch": plan.launch_info(mode),
         })
     del out
     return lines
