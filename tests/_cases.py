@@ -111,3 +111,20 @@ def generic_batched(g, backend=None):
     params = {"ref%d" % i: g["ref"][:, i] for i in range(nx)}
     given = g["x0"]  # the only given variable is x0
     return form, params, given
+
+
+def tiny_plant(backend=None, optim=("x0", "u"), with_limit=True, N=5):
+    """Edge shapes: ng = 0 when x0 is optimised, nc = 0 without limits, odd nv."""
+    rng = np.random.default_rng(0)
+    A = np.eye(3) + 0.1 * rng.normal(size=[3, 3])
+    B = rng.normal(size=[3, 1])
+    ext = ExtendedSystem.from_cotrol_system(ControlSystem(["u"], ["a", "b", "c"], A, B), "x", N)
+    form = Formulation(backend=backend)
+    form.incorporate_dynamics("plant", ext)
+    form.incorporate_goal("g1", Cost("a", Param("w"), aim=[Param("aim")]))
+    form.incorporate_goal("g2", Cost("u", 0.1, aim=[0.0]))
+    if with_limit:
+        form.incorporate_constraint("lim", Constraint("b", 3.0))
+    form.identify_qp_domain(list(optim))
+    form.make_preview_matrices()
+    return form

@@ -56,7 +56,8 @@ def test_lti_agrees_with_affine_path_when_dynamics_are_shared(dev):
         assert cases.rel_err(y.cpu().numpy(), x.cpu().numpy()) <= cases.TOL
 
 
-@pytest.mark.parametrize("nx,nu,N,batch", [(12, 4, 50, 300), (6, 2, 100, 40), (2, 1, 5, 7), (5, 5, 13, 9)])
+@pytest.mark.parametrize("nx,nu,N,batch", [(12, 4, 50, 300), (6, 2, 100, 40), (2, 1, 5, 7), (5, 5, 13, 9), (1, 1, 1, 3), (3, 2, 33, 20),
+                          (8, 6, 20, 10)])
 def test_lti_random_batches_against_oracle(dev, monkeypatch, nx, nu, N, batch):
     """More instances than resident CTAs (persistent loop), odd sizes, m = 5
     (general recursion kernel); checked against the oracle on a few instances."""
@@ -127,3 +128,20 @@ def test_lti_partial_outputs_and_errors(dev):
                                        scal.data_ptr(), null, null, null, null, 4, 7, null) < 0
     with pytest.raises(ValueError):
         lti.assemble(plan, g["A_sys"], g["B_sys"], g["x0"][:, :3], params)
+
+
+def test_lti_launch_info(dev):
+    """The plan reports how it maps onto an SM: the recursion kernel fits more CTAs than the
+    DMMA one (no zero padding, fewer registers) and uses the DMMA patch scan when its
+    unchecked loads are safe (not for a 1 x 1 x 1 problem)."""
+    from mpc_interface_b200 import lti
+
+    g = cases.golden("generic_c4_shape")
+    form, params, _ = cases.generic_batched(g)
+    plan = form.lti_plan("plant")
+    dm, rec = plan.launch_info(lti.HESSIAN_DMMA), plan.launch_info(lti.HESSIAN_RECURSION)
+    assert dm["scan"] == 0 and rec["scan"] == 1
+    assert rec["smem_bytes"] < dm["smem_bytes"] <= 227 * 1024
+    assert rec["ctas_per_sm"] >= dm["ctas_per_sm"] >= 1
+    # skewed rows: (rows * LD) mod 16 in {4, 12} for the strided DMMA operand loads
+    assert (5 * rec["ld_gz"]) % 16 in (4, 12) and (4 * rec["ld_wz"]) % 16 in (4, 12)

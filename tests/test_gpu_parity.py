@@ -209,6 +209,37 @@ def test_biped_per_instance_geometry_vs_oracle(dev):
         cases.assert_qp_close((G[b], h[b], P[b], q[b]), ref)
 
 
+@pytest.mark.parametrize("optim,with_limit", [(("x0", "u"), True), (("u",), False), (("x0", "u"), False)])
+@pytest.mark.parametrize("batch", [0, 1, 33])
+def test_edge_shapes(dev, optim, with_limit, batch):
+    """Empty given vector (x0 optimised), no constraint rows, odd nv (scalar stores),
+    empty / single / ragged batches -- against the oracle."""
+    form = cases.tiny_plant(optim=optim, with_limit=with_limit)
+    ng, nv = form.given_len, form.optim_len
+    assert ng == (0 if "x0" in optim else 3) and nv == (8 if "x0" in optim else 5)
+    rng = np.random.default_rng(batch)
+    given = rng.normal(size=[batch, ng])
+    params = {"w": rng.uniform(0.5, 2.0, batch), "aim": rng.normal(size=batch)}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    nc = 5 if with_limit else 0
+    assert out.P.shape == (batch, nv, nv) and out.q.shape == (batch, nv)
+    assert out.G.shape == (batch, nc, nv) and out.h.shape == (batch, nc)
+    P, q, G, h = out.P_numpy(), out.q_numpy(), out.G_numpy(), out.h_numpy()
+    for b in range(min(batch, 3)):
+        one = {k: float(v[b]) for k, v in params.items()}
+        PM = orc.preview_matrices(form, one)
+        g = given[b][:, None]
+        costs = [orc.qp_cost(c, PM, g, one) for c in form.goals.values()]
+        assert cases.rel_err(P[b], np.add.reduce([c[0] for c in costs])) <= cases.TOL
+        assert cases.rel_err(q[b], np.add.reduce([c[1] for c in costs])[:, 0]) <= cases.TOL
+        if with_limit:
+            A_ref, h_ref = orc.qp_constraint(form.constraints["lim"][0], PM, g, one)
+            assert cases.rel_err(G[b], A_ref) <= cases.TOL and cases.rel_err(h[b], h_ref[:, 0]) <= cases.TOL
+    if not with_limit:  # the single-instance API fails like the reference (np.vstack of nothing)
+        with pytest.raises(ValueError):
+            form.generate_all_qp_matrices(np.zeros([ng, 1]))
+
+
 def test_reference_test_body_case(dev):
     g = cases.golden("test_body")
     body = cases.body_test_formulation()
