@@ -54,11 +54,11 @@ struct LtiArgs {
 };
 
 struct Smem {
-  double *A, *M0, *M1, *Q, *gz, *wz, *r, *tx, *tu, *cg, *tb;
+  double *M0, *M1, *Q, *gz, *wz, *r, *tx, *tu, *cg, *tb;
 };
 
 // Shared memory of one instance (doubles):
-//   A, M0, M1, Q   4 n^2
+//   M0, M1, Q      3 n^2  (A^have ping-pong, Qxx)
 //   gz  [n][m+1][LD]  gz[i][c][pad + d] = (A^d [B | x0])[i][c], d = 0..N: the doubling
 //                     writes straight into it; column c = m is the free response,
 //                     f_k[i] = gz[i][m][pad + 1 + k]
@@ -77,6 +77,7 @@ __host__ __device__ inline size_t lti_aux_doubles(int n, int m, int N, int scan)
   const size_t cg = (size_t)2 * 4 * m * N, tb = scan ? (size_t)kWarps * 8 * 40 : 0;  // two window sets
   return ((cg > tb ? cg : tb) + 1) & ~(size_t)1;
 }
+__host__ __device__ inline size_t lti_mats_doubles(int n) { return ((size_t)3 * n * n + 1) & ~(size_t)1; }
 __host__ __device__ inline size_t lti_gz_doubles(int n, int m, int LD) {
   return ((size_t)n * (m + 1) * LD + 1) & ~(size_t)1;
 }
@@ -88,18 +89,17 @@ __host__ __device__ inline int lti_skew(int LD, int rows) {
   return LD;
 }
 __host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD, int LDw, int scan) {
-  return (size_t)4 * n * n + lti_gz_doubles(n, m, LD) + lti_wz_doubles(n, m, LDw) +
+  return lti_mats_doubles(n) + lti_gz_doubles(n, m, LD) + lti_wz_doubles(n, m, LDw) +
          lti_r_doubles(n, N) + lti_aux_doubles(n, m, N, scan) + n + m;
 }
 
 __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
   Smem s;
   const int n = a.n, m = a.m, N = a.N;
-  s.A = base;
-  s.M0 = s.A + n * n;
+  s.M0 = base;
   s.M1 = s.M0 + n * n;
   s.Q = s.M1 + n * n;
-  s.gz = s.Q + n * n;
+  s.gz = base + lti_mats_doubles(n);
   s.wz = s.gz + lti_gz_doubles(n, m, a.LD);
   s.r = s.wz + lti_wz_doubles(n, m, a.LDw);
   s.tb = s.r + lti_r_doubles(n, N);  // 16-byte aligned: double2 stores of the T tiles,
@@ -127,7 +127,6 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   const double* xb = a.x0 + b * n;
   for (int e = tid; e < n * n; e += kThreads) {
     const double v = Ab[e];
-    s.A[e] = v;
     s.M0[e] = v;
     s.Q[e] = a.Qxx[e];
   }
@@ -153,41 +152,58 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   __syncthreads();
 
   // prefix doubling: Gam'_{have+d} = A^have Gam'_d,  A^(2 have) = (A^have)^2, d = 0..N.
-  // Rows are (i, c) with d contiguous, so consecutive threads take consecutive d (no
-  // bank conflicts, M0 reads are broadcasts); `have` is a power of two, so the split
-  // of the flat index into (i, d) is a shift in every round but possibly the last.
+  // One flat index per round covers every (row (i, c), d) of the doubling AND the n^2
+  // entries of the squaring, so a round is a single pass of independent dot products
+  // (four accumulators each) between two barriers.  d is the fastest index: consecutive
+  // threads read consecutive words, the A^have reads are broadcasts.  Divisions by the
+  // run-time sizes are multiplications by precomputed reciprocals (exact below 2^16).
   double* M0 = s.M0;
   double* M1 = s.M1;
-  const int sq_i = tid / n, sq_c = tid - sq_i * n;
+  const unsigned magic_w = 0xFFFFFFFFu / (unsigned)w + 1u, magic_n = 0xFFFFFFFFu / (unsigned)n + 1u;
+  const int wLD = w * LD;
   int sh = 0;
-  for (int have = 1; have < N + 1; ++sh) {
+#ifndef MPCI_DBG_SKIP
+#define MPCI_DBG_SKIP 0  /* timing experiments only: 1 doubling, 2 wz, 4 r */
+#endif
+  for (int have = (MPCI_DBG_SKIP & 1) ? N + 1 : 1; have < N + 1; ++sh) {
     const int cnt = min(have, N + 1 - have);
     const bool pow2 = cnt == have;
-    for (int c = 0; c < w; ++c) {
-      double* col = s.gz + (size_t)c * LD + pad;  // row (i, c) starts at col + i * w * LD
-      for (int e = tid; e < n * cnt; e += kThreads) {
-        const int i = pow2 ? (e >> sh) : e / cnt;
-        const int d = e - i * cnt;
-        const double* Mi = M0 + i * n;
-        const double* src = col + d;
-        double acc0 = 0.0, acc1 = 0.0;
-        int l = 0;
-        for (; l + 1 < n; l += 2) {
-          acc0 = fma(Mi[l], src[(size_t)l * w * LD], acc0);
-          acc1 = fma(Mi[l + 1], src[(size_t)(l + 1) * w * LD], acc1);
-        }
-        if (l < n) acc0 = fma(Mi[l], src[(size_t)l * w * LD], acc0);
-        col[(size_t)i * w * LD + have + d] = acc0 + acc1;
+    const unsigned magic_cnt = pow2 ? 0u : 0xFFFFFFFFu / (unsigned)cnt + 1u;
+    const int n_dbl = n * w * cnt;
+    const int total = n_dbl + ((have + cnt < N + 1) ? n * n : 0);  // + the next power, if needed
+    for (int e = tid; e < total; e += kThreads) {
+      const double* x;  // left operand: a row of A^have, unit stride
+      const double* y;  // right operand, stride ys
+      double* out;
+      int ys;
+      if (e < n_dbl) {
+        const int row = pow2 ? (e >> sh) : (cnt == 1 ? e : (int)__umulhi((unsigned)e, magic_cnt));
+        const int d = e - row * cnt;
+        const int i = (int)__umulhi((unsigned)row, magic_w), c = row - i * w;
+        x = M0 + i * n;
+        y = s.gz + c * LD + pad + d;
+        ys = wLD;
+        out = s.gz + row * LD + pad + have + d;
+      } else {
+        const int e2 = e - n_dbl;
+        const int i = n == 1 ? e2 : (int)__umulhi((unsigned)e2, magic_n), c = e2 - i * n;
+        x = M0 + i * n;
+        y = M0 + c;
+        ys = n;
+        out = M1 + e2;
       }
-    }
-    if (have + cnt < N + 1) {  // the next power is only needed for another round
-      for (int e2 = tid; e2 < n * n; e2 += kThreads) {
-        const int i = (e2 == tid) ? sq_i : e2 / n, c = (e2 == tid) ? sq_c : e2 % n;
-        double acc = 0.0;
-#pragma unroll 4
-        for (int l = 0; l < n; ++l) acc = fma(M0[i * n + l], M0[l * n + c], acc);
-        M1[e2] = acc;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+      int l = 0;
+      for (; l + 3 < n; l += 4) {
+        const double x0 = x[l], x1 = x[l + 1], x2 = x[l + 2], x3 = x[l + 3];
+        const double y0 = y[l * ys], y1 = y[(l + 1) * ys], y2 = y[(l + 2) * ys], y3 = y[(l + 3) * ys];
+        a0 = fma(x0, y0, a0);
+        a1 = fma(x1, y1, a1);
+        a2 = fma(x2, y2, a2);
+        a3 = fma(x3, y3, a3);
       }
+      for (; l < n; ++l) a0 = fma(x[l], y[l * ys], a0);
+      *out = (a0 + a1) + (a2 + a3);
     }
     __syncthreads();
     double* t = M0; M0 = M1; M1 = t;
@@ -195,7 +211,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   }
 
   // wz[i][j][pad + d] = (Qxx Gam_d)[i][j], d < N (a warp per (i, j) row, lanes along d)
-  for (int ij = warp; ij < n * m; ij += kWarps) {
+  for (int ij = (MPCI_DBG_SKIP & 2) ? n * m : warp; ij < n * m; ij += kWarps) {
     const int i = ij / m, j = ij - i * m;
     const double* Qi = s.Q + i * n;
     const double* src = s.gz + (size_t)j * LD + pad;
@@ -208,7 +224,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     }
   }
   // r[i][k] = sum_l sym(Qxx)[i][l] f_k[l] - tx[i],  f_k = Gam'_{k+1}[:, m]
-  for (int i = warp; i < n; i += kWarps) {
+  for (int i = (MPCI_DBG_SKIP & 4) ? n : warp; i < n; i += kWarps) {
     const double txi = s.tx[i];
     const double* f = s.gz + (size_t)m * LD + pad + 1;  // f_k[l] = f[l * w * LD + k]
     for (int k = lane; k < N; k += 32) {
@@ -697,7 +713,7 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   const int LDg_scan = lti_skew(LDs[1], m + 1), LDw_scan = lti_skew(LDs[1], m);
   const size_t smem_scan = sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, 1);
   const int scan = smem_scan <= 227 * 1024 &&
-                   (size_t)4 * n * n + lti_gz_doubles(n, m, LDg_scan) >= 48;
+                   lti_mats_doubles(n) + lti_gz_doubles(n, m, LDg_scan) >= 48;
   if (scan) {
     smems[MPCI_LTI_HESSIAN_RECURSION] = smem_scan;
     LDs[1] = LDg_scan;
