@@ -162,10 +162,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   const unsigned magic_w = 0xFFFFFFFFu / (unsigned)w + 1u, magic_n = 0xFFFFFFFFu / (unsigned)n + 1u;
   const int wLD = w * LD;
   int sh = 0;
-#ifndef MPCI_DBG_SKIP
-#define MPCI_DBG_SKIP 0  /* timing experiments only: 1 doubling, 2 wz, 4 r */
-#endif
-  for (int have = (MPCI_DBG_SKIP & 1) ? N + 1 : 1; have < N + 1; ++sh) {
+  for (int have = 1; have < N + 1; ++sh) {
     const int cnt = min(have, N + 1 - have);
     const bool pow2 = cnt == have;
     const unsigned magic_cnt = pow2 ? 0u : 0xFFFFFFFFu / (unsigned)cnt + 1u;
@@ -211,7 +208,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   }
 
   // wz[i][j][pad + d] = (Qxx Gam_d)[i][j], d < N (a warp per (i, j) row, lanes along d)
-  for (int ij = (MPCI_DBG_SKIP & 2) ? n * m : warp; ij < n * m; ij += kWarps) {
+  for (int ij = warp; ij < n * m; ij += kWarps) {
     const int i = ij / m, j = ij - i * m;
     const double* Qi = s.Q + i * n;
     const double* src = s.gz + (size_t)j * LD + pad;
@@ -224,7 +221,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     }
   }
   // r[i][k] = sum_l sym(Qxx)[i][l] f_k[l] - tx[i],  f_k = Gam'_{k+1}[:, m]
-  for (int i = (MPCI_DBG_SKIP & 4) ? n : warp; i < n; i += kWarps) {
+  for (int i = warp; i < n; i += kWarps) {
     const double txi = s.tx[i];
     const double* f = s.gz + (size_t)m * LD + pad + 1;  // f_k[l] = f[l * w * LD + k]
     for (int k = lane; k < N; k += 32) {
