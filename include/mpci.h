@@ -24,7 +24,8 @@ extern "C" {
 
 #define MPCI_VERSION 100
 #define MPCI_MAX_FACTORS 4   /* per-instance scalar factors of one monomial */
-#define MPCI_MAX_TERMS 8     /* monomials of one streamed array (P or G) */
+#define MPCI_MAX_TERMS 32    /* monomials of one streamed array (P or G); up to 8 keep the
+                              * constants in registers, more are re-read through L1 / L2 */
 
 int mpci_version(void);
 

@@ -80,6 +80,70 @@ stream_terms_kernel(StreamArgs args, const double* __restrict__ scalars, int n_s
   }
 }
 
+// More than 8 monomials (e.g. several boxes turned by different per-instance angles):
+// the constants do not fit the register file, so every output vector re-reads its K
+// constant vectors through L1 / L2 (read-only path).  Same grid, same store pattern;
+// slower by the extra on-chip traffic, not by extra HBM bytes.
+template <typename VecT>
+__global__ void __launch_bounds__(kStreamThreads)
+stream_terms_generic(StreamArgs args, const double* __restrict__ scalars, int n_scalars,
+                     double* __restrict__ out, long batch) {
+  constexpr int V = sizeof(VecT) / sizeof(double);
+  __shared__ double coef[kStreamGroup][MPCI_MAX_TERMS];
+  const int K = args.n_terms;
+  const long b0 = (long)blockIdx.y * kStreamGroup;
+  const int group = (int)min((long)kStreamGroup, batch - b0);
+  for (int e = threadIdx.x; e < group * K; e += blockDim.x) {
+    const int t = e / K, k = e - t * K;
+    const double* s = scalars + (b0 + t) * n_scalars;
+    double c = 1.0;
+#pragma unroll
+    for (int f = 0; f < MPCI_MAX_FACTORS; ++f) {
+      const int idx = args.factors[k][f];
+      if (idx >= 0) c *= s[idx];
+    }
+    coef[t][k] = c;
+  }
+  __syncthreads();
+  const long n_vec = args.n_elems / V;
+  const long v = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= n_vec) return;
+  const VecT* src = reinterpret_cast<const VecT*>(args.consts) + v;
+  VecT* dst = reinterpret_cast<VecT*>(out + b0 * args.n_elems) + v;
+  for (int t = 0; t < group; ++t) {
+    VecT r;
+    if constexpr (V == 2) {
+      r.x = r.y = 0.0;
+      for (int k = 0; k < K; ++k) {
+        const VecT d = __ldg(src + (long)k * n_vec);
+        r.x = fma(coef[t][k], d.x, r.x);
+        r.y = fma(coef[t][k], d.y, r.y);
+      }
+    } else {
+      r = 0.0;
+      for (int k = 0; k < K; ++k) r = fma(coef[t][k], __ldg(src + (long)k * n_vec), r);
+    }
+    __stcs(dst, r);
+    dst += n_vec;
+  }
+}
+
+static int launch_stream_generic(const StreamArgs& a, const double* scalars, int n_scalars,
+                                 double* out, long batch, cudaStream_t st) {
+  const bool vec2 = (a.n_elems % 2 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15) == 0) &&
+                    ((reinterpret_cast<uintptr_t>(a.consts) & 15) == 0);
+  const long n_vec = vec2 ? a.n_elems / 2 : a.n_elems;
+  dim3 grid((unsigned)((n_vec + kStreamThreads - 1) / kStreamThreads),
+            (unsigned)((batch + kStreamGroup - 1) / kStreamGroup));
+  if (grid.y > 65535) return fail(-6, "assemble: batch %ld too large for one launch", batch);
+  if (vec2)
+    stream_terms_generic<double2><<<grid, kStreamThreads, 0, st>>>(a, scalars, n_scalars, out, batch);
+  else
+    stream_terms_generic<double><<<grid, kStreamThreads, 0, st>>>(a, scalars, n_scalars, out, batch);
+  MPCI_LAUNCH_CHECK("stream_terms_generic");
+  return 0;
+}
+
 template <int K>
 static int launch_stream_k(const StreamArgs& a, const double* scalars, int n_scalars, double* out,
                            long batch, cudaStream_t st) {
@@ -112,6 +176,8 @@ int launch_stream(const StreamArgs& a, const double* scalars, int n_scalars, dou
     case 7: return launch_stream_k<7>(a, scalars, n_scalars, out, batch, st);
     case 8: return launch_stream_k<8>(a, scalars, n_scalars, out, batch, st);
   }
+  if (a.n_terms > 8 && a.n_terms <= MPCI_MAX_TERMS)
+    return launch_stream_generic(a, scalars, n_scalars, out, batch, st);
   return fail(-7, "assemble: %d terms in one stream (limit %d)", a.n_terms, MPCI_MAX_TERMS);
 }
 

@@ -29,7 +29,7 @@ import numpy as np
 from .params import Expr, is_expr, split_array
 
 MAX_FACTORS = 4  # factors per monomial the kernels accept (mpci.h: MPCI_MAX_FACTORS)
-MAX_TERMS = 8  # monomials per streamed array (mpci.h: MPCI_MAX_TERMS)
+MAX_TERMS = 32  # monomials per streamed array (mpci.h: MPCI_MAX_TERMS; fast path up to 8)
 
 
 class SlotTable:

@@ -128,3 +128,27 @@ def tiny_plant(backend=None, optim=("x0", "u"), with_limit=True, N=5):
     form.identify_qp_domain(list(optim))
     form.make_preview_matrices()
     return form
+
+
+def biped_three_yaws(N, backend=None):
+    """Every box of the biped turned by its own per-instance angle: more than 8 streamed G
+    monomials (the kernels' generic path)."""
+    form = formulate_biped(default_configuration(N), omega=Param("omega"),
+                           target_vel=[Param("vel_x"), Param("vel_y")], backend=backend, preview=False)
+    for name, angle in (("support_polygon", "yaw_a"), ("terminal_Constraint", "yaw_b"),
+                        ("stepping area", "yaw_c")):
+        form.constraint_boxes[name].rotate_in_TS(use.rotation2D(Param(angle)))
+    form.make_preview_matrices()
+    return form
+
+
+def three_yaw_inputs(form, seed, batch, N):
+    from mpc_interface_b200.examples import synthetic
+
+    vals = synthetic.biped_inputs(seed, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    rng = np.random.default_rng(seed + 3)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    for k in ("yaw_a", "yaw_b", "yaw_c"):
+        params[k] = rng.uniform(-1.0, 1.0, batch)
+    return given, params

@@ -240,6 +240,21 @@ def test_edge_shapes(dev, optim, with_limit, batch):
             form.generate_all_qp_matrices(np.zeros([ng, 1]))
 
 
+@pytest.mark.parametrize("N,batch", [(24, 37), (100, 5)])
+def test_more_than_eight_streamed_terms(dev, N, batch):
+    """10 G monomials: stream_terms_generic (constants through L1 / L2 instead of
+    registers) against the oracle."""
+    form = cases.biped_three_yaws(N)
+    given, params = cases.three_yaw_inputs(form, 40 + N, batch, N)
+    assert len(form._compiled().G_terms) > 8
+    out = form.generate_all_qp_matrices_batched(given, params)
+    P, q, G, h = out.P_numpy(), out.q_numpy(), out.G_numpy(), out.h_numpy()
+    for b in sorted({0, batch // 2, batch - 1}):
+        one = {k: float(v[b]) for k, v in params.items()}
+        ref = orc.all_qp_matrices(form, given[b][:, None], one)
+        cases.assert_qp_close((G[b], h[b], P[b], q[b]), ref)
+
+
 def test_reference_test_body_case(dev):
     g = cases.golden("test_body")
     body = cases.body_test_formulation()

@@ -198,3 +198,20 @@ def test_per_instance_center_and_extreme(cpu_extend):
         ref = orc.all_qp_matrices(form, given[b][:, None], one)
         cases.assert_qp_close((out.G[b], out.h[b], out.P[b], out.q[b]), ref)
     assert form._compiled().G_terms == [0]        # G itself stays shared
+
+
+def test_more_than_eight_streamed_terms(cpu_extend):
+    """Three boxes with three per-instance angles: 10 G monomials (> 8, the generic
+    stream kernel on the device), still within plan.MAX_TERMS; against the oracle."""
+    from oracle import qp_oracle as orc
+
+    N, batch = 24, 3
+    form = cases.biped_three_yaws(N, NumpyBackend())
+    given, params = cases.three_yaw_inputs(form, 12, batch, N)
+    out = form.generate_all_qp_matrices_batched(given, params)
+    p = form._compiled()
+    assert 8 < len(p.G_terms) <= planmod.MAX_TERMS
+    for b in range(batch):
+        one = {k: float(v[b]) for k, v in params.items()}
+        ref = orc.all_qp_matrices(form, given[b][:, None], one)
+        cases.assert_qp_close((out.G[b], out.h[b], out.P[b], out.q[b]), ref)
