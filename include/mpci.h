@@ -221,8 +221,9 @@ double mpci_lti_hessian_flops(const mpci_lti_plan* plan, int hessian_mode);
 /* How the plan maps onto an SM in `hessian_mode` (for benchmarks and ncu cross-checks):
  * info[0] = dynamic shared memory per CTA (bytes), info[1] = resident CTAs per SM,
  * info[2] = 1 when the recursion uses the DMMA patch scan, info[3] / info[4] = row
- * lengths (doubles) of the generator arrays gz / wz in shared memory.                   */
-int mpci_lti_plan_info(const mpci_lti_plan* plan, int hessian_mode, long info[5]);
+ * lengths (doubles) of the generator arrays gz / wz in shared memory, info[5] = threads
+ * per CTA (256, or 384 when the shared memory allows only one CTA per SM anyway).       */
+int mpci_lti_plan_info(const mpci_lti_plan* plan, int hessian_mode, long info[6]);
 
 #ifdef __cplusplus
 }

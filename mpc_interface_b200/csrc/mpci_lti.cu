@@ -31,6 +31,7 @@ namespace {
 #endif
 constexpr int kThreads = MPCI_LTI_THREADS;
 constexpr int kWarps = kThreads / 32;
+constexpr int kWideThreads = 384;
 constexpr int kPadL = 36;  // zeros before d = 0 of every generator (>= 8*max(TM,TN)+3)
 constexpr int TM = 2, TN = 4;  // 8x8 DMMA tiles per warp tile (rows x cols)
 
@@ -64,7 +65,7 @@ struct Smem {
 //                     f_k[i] = gz[i][m][pad + 1 + k]
 //   wz  [n][m][LDw]   (Qxx Gam_d)[i][j]
 //   r   [n][N],  tx [n],  tu [m]
-//   aux = tb [kWarps][8][40] (the warps' T patches, scan only) / cg (row windows and
+//   aux = tb [warps][8][40] (the warps' T patches, scan only) / cg (row windows and
 //         group tables of the constraint phase)
 __host__ __device__ inline int lti_row_len(int N, int pad) { return pad + (N + 1 + 3) / 4 * 4; }
 __host__ __device__ inline size_t lti_wz_doubles(int n, int m, int LDw) {
@@ -73,8 +74,8 @@ __host__ __device__ inline size_t lti_wz_doubles(int n, int m, int LDw) {
 __host__ __device__ inline size_t lti_r_doubles(int n, int N) { return ((size_t)n * N + 1) & ~(size_t)1; }
 // aux: the constraint phase's row windows and group tables (cg) and, in the scan, the
 // warps' T patches (tb) share one region -- the two phases never run at the same time
-__host__ __device__ inline size_t lti_aux_doubles(int n, int m, int N, int scan) {
-  const size_t cg = (size_t)2 * 4 * m * N, tb = scan ? (size_t)kWarps * 8 * 40 : 0;  // two window sets
+__host__ __device__ inline size_t lti_aux_doubles(int n, int m, int N, int scan, int warps) {
+  const size_t cg = (size_t)2 * 4 * m * N, tb = scan ? (size_t)warps * 8 * 40 : 0;  // two window sets
   return ((cg > tb ? cg : tb) + 1) & ~(size_t)1;
 }
 __host__ __device__ inline size_t lti_mats_doubles(int n) { return ((size_t)3 * n * n + 1) & ~(size_t)1; }
@@ -88,9 +89,10 @@ __host__ __device__ inline int lti_skew(int LD, int rows) {
     if ((rows * x) % 16 == 4 || (rows * x) % 16 == 12) return x;
   return LD;
 }
-__host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD, int LDw, int scan) {
+__host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD, int LDw, int scan,
+                                                   int warps) {
   return lti_mats_doubles(n) + lti_gz_doubles(n, m, LD) + lti_wz_doubles(n, m, LDw) +
-         lti_r_doubles(n, N) + lti_aux_doubles(n, m, N, scan) + n + m;
+         lti_r_doubles(n, N) + lti_aux_doubles(n, m, N, scan, warps) + n + m;
 }
 
 __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
@@ -104,7 +106,7 @@ __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
   s.r = s.wz + lti_wz_doubles(n, m, a.LDw);
   s.tb = s.r + lti_r_doubles(n, N);  // 16-byte aligned: double2 stores of the T tiles,
   s.cg = s.tb;                       // source of the bulk copies
-  s.tx = s.tb + lti_aux_doubles(n, m, N, a.scan);
+  s.tx = s.tb + lti_aux_doubles(n, m, N, a.scan, (int)blockDim.x >> 5);
   s.tu = s.tx + n;
   return s;
 }
@@ -125,24 +127,24 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   const double* Ab = a.A + b * a.strideA;
   const double* Bb = a.B + b * a.strideB;
   const double* xb = a.x0 + b * n;
-  for (int e = tid; e < n * n; e += kThreads) {
+  for (int e = tid; e < n * n; e += (int)blockDim.x) {
     const double v = Ab[e];
     s.M0[e] = v;
     s.Q[e] = a.Qxx[e];
   }
   // d = 0 of every row, and the zeros before it (causality of the DMMA operands)
-  for (int e = tid; e < n * w; e += kThreads) {
+  for (int e = tid; e < n * w; e += (int)blockDim.x) {
     const int i = e / w, c = e - i * w;
     s.gz[(size_t)e * LD + pad] = (c < m) ? Bb[i * m + c] : xb[i];
   }
   if (pad) {
-    for (int row = warp; row < n * w + n * m; row += kWarps) {
+    for (int row = warp; row < n * w + n * m; row += ((int)blockDim.x >> 5)) {
       double* dst = row < n * w ? s.gz + (size_t)row * LD : s.wz + (size_t)(row - n * w) * a.LDw;
       for (int x = lane; x < pad; x += 32) dst[x] = 0.0;
     }
   }
   // per-instance offsets of the gradient: t = T[:, S] + T[:, :S] @ scalars_b
-  for (int e = tid; e < n + m; e += kThreads) {
+  for (int e = tid; e < n + m; e += (int)blockDim.x) {
     const double* T = (e < n) ? a.Tx + (long)e * (a.S + 1) : a.Tu + (long)(e - n) * (a.S + 1);
     double acc = T[a.S];
 #pragma unroll 4
@@ -168,7 +170,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     const unsigned magic_cnt = pow2 ? 0u : 0xFFFFFFFFu / (unsigned)cnt + 1u;
     const int n_dbl = n * w * cnt;
     const int total = n_dbl + ((have + cnt < N + 1) ? n * n : 0);  // + the next power, if needed
-    for (int e = tid; e < total; e += kThreads) {
+    for (int e = tid; e < total; e += (int)blockDim.x) {
       const double* x;  // left operand: a row of A^have, unit stride
       const double* y;  // right operand, stride ys
       double* out;
@@ -208,7 +210,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   }
 
   // wz[i][j][pad + d] = (Qxx Gam_d)[i][j], d < N (a warp per (i, j) row, lanes along d)
-  for (int ij = warp; ij < n * m; ij += kWarps) {
+  for (int ij = warp; ij < n * m; ij += ((int)blockDim.x >> 5)) {
     const int i = ij / m, j = ij - i * m;
     const double* Qi = s.Q + i * n;
     const double* src = s.gz + (size_t)j * LD + pad;
@@ -221,7 +223,7 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     }
   }
   // r[i][k] = sum_l sym(Qxx)[i][l] f_k[l] - tx[i],  f_k = Gam'_{k+1}[:, m]
-  for (int i = warp; i < n; i += kWarps) {
+  for (int i = warp; i < n; i += ((int)blockDim.x >> 5)) {
     const double txi = s.tx[i];
     const double* f = s.gz + (size_t)m * LD + pad + 1;  // f_k[l] = f[l * w * LD + k]
     for (int k = lane; k < N; k += 32) {
@@ -252,7 +254,7 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
 
   // tiles are sorted by the length of their k-loop and dealt round-robin, the
   // (j, j') blocks innermost: the eight warps get nearly equal work
-  for (int idx = warp; idx < a.n_tiles * mm; idx += kWarps) {
+  for (int idx = warp; idx < a.n_tiles * mm; idx += ((int)blockDim.x >> 5)) {
     const int tt = idx / mm, jj = idx - tt * mm;
     const int2 rc = a.tiles[tt];
     const int j = jj / m, jp = jj - j * m;
@@ -335,7 +337,7 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
 template <int M>
 __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
   const int n = a.n, N = a.N, LD = a.LD, nv = M * a.N;
-  for (int dl0 = 0; dl0 < 2 * N - 1; dl0 += kThreads) {
+  for (int dl0 = 0; dl0 < 2 * N - 1; dl0 += (int)blockDim.x) {
     const int dl = dl0 + threadIdx.x;
     const int delta = dl - (N - 1);
     const bool has = dl < 2 * N - 1;
@@ -382,7 +384,7 @@ __device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* _
   const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int dchunks = (2 * N - 1 + 31) / 32;  // a warp takes 32 diagonals of one block
-  for (int item = warp; item < m * m * dchunks; item += kWarps) {
+  for (int item = warp; item < m * m * dchunks; item += ((int)blockDim.x >> 5)) {
     const int jj = item / dchunks, dc = item - jj * dchunks, j = jj / m, jp = jj - j * m;
     const int dl = dc * 32 + lane;
     const int delta = dl - (N - 1);
@@ -433,7 +435,7 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
   double2* tst = reinterpret_cast<double2*>(tw + g * kScanLd + 2 * t);  // this lane's C slots
   const double* twl = tw + lane;                                         // this lane's diagonal
   const long ga_step = (long)4 * w * LD, wb_step = (long)4 * m * a.LDw;
-  for (int item = warp; item < m * m * dchunks; item += kWarps) {
+  for (int item = warp; item < m * m * dchunks; item += ((int)blockDim.x >> 5)) {
     const int jj = item / dchunks, dc = item - jj * dchunks, j = jj / m, jp = jj - j * m;
     const int d0 = dc * 32 - (N - 1);             // diagonal of lane 0 (delta = c - p)
     const int delta = d0 + lane;
@@ -486,7 +488,7 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
 // ---------------------------------------------------------------------------
 __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ qb) {
   const int n = a.n, m = a.m, N = a.N, LD = a.LD;
-  for (int e = threadIdx.x; e < m * N; e += kThreads) {
+  for (int e = threadIdx.x; e < m * N; e += (int)blockDim.x) {
     const int j = e / N, p = e - j * N;
     const int len = N - p;
     double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;  // four chains hide the DFMA latency
@@ -557,7 +559,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
       __syncthreads();
     }
     const double scale = bulk ? __ldg(arrow) : 1.0;
-    for (int j = warp; j < m; j += kWarps) {
+    for (int j = warp; j < m; j += ((int)blockDim.x >> 5)) {
       const double cuj = __ldg(a.cu + (size_t)grp * m + j);
       for (int y = lane; y < 2 * N; y += 32) {
         double acc = (y == N - 1) ? cuj : 0.0;
@@ -573,7 +575,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
       }
     }
     if (hb) {
-      for (int k = tid; k < N; k += kThreads) {
+      for (int k = tid; k < N; k += (int)blockDim.x) {
         double acc = 0.0;
         if (state) {
 #pragma unroll 4
@@ -591,7 +593,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
       // Long rows: one lane per warp, so the rows in flight stay close together in
       // memory (measured: C4 5.87 -> 5.53 ms with 32 lanes, C5 4.58 -> 4.43 ms with 1).
       const int issue_lanes = (N < 256) ? 32 : 1;
-      for (int k = warp + kWarps * lane; lane < issue_lanes && k < N; k += kWarps * issue_lanes) {
+      for (int k = warp + ((int)blockDim.x >> 5) * lane; lane < issue_lanes && k < N; k += ((int)blockDim.x >> 5) * issue_lanes) {
         const int start = N - 1 - k;
         const double* win = (start & 1) ? cz1 + (start - 1) : cz + start;
         double* row = rows + (size_t)k * nv;
@@ -600,7 +602,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
       bulk_commit();  // every lane commits (an empty group for the idle ones)
       continue;
     }
-    for (int k = warp; k < N; k += kWarps) {
+    for (int k = warp; k < N; k += ((int)blockDim.x >> 5)) {
       const double ak = __ldg(arrow + k);
       double* row = rows + (size_t)k * nv;
       const double* win = cz + (N - 1 - k);  // column c = j N + p reads win[c + j N]
@@ -625,8 +627,11 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
 // One kernel per Hessian mode: the recursion needs neither the DMMA accumulators nor
 // the zero padding, so it is compiled for more resident CTAs per SM (the phases of
 // different instances -- latency-bound prediction, store-bound P / G -- then overlap).
-template <int MODE>
-__global__ void __launch_bounds__(kThreads, MODE == MPCI_LTI_HESSIAN_RECURSION ? MPCI_LTI_MINBLOCKS : (kThreads > 256 ? 1 : 2))
+// WIDE: plans whose shared memory allows one CTA per SM anyway run it with kWideThreads
+// threads (more warps to hide the latency-bound phases; measured at C5: 4.47 -> 4.23 ms).
+template <int MODE, int WIDE>
+__global__ void __launch_bounds__(WIDE ? kWideThreads : kThreads,
+                                  WIDE ? 1 : (MODE == MPCI_LTI_HESSIAN_RECURSION ? MPCI_LTI_MINBLOCKS : 2))
 lti_assemble_kernel(LtiArgs a) {
   extern __shared__ double lti_smem[];
   const Smem s = carve(lti_smem, a);
@@ -668,12 +673,20 @@ lti_assemble_kernel(LtiArgs a) {
 
 }  // namespace
 
+typedef void (*lti_kernel_t)(LtiArgs);
+static lti_kernel_t lti_kernel(int mode, int wide) {
+  if (mode == MPCI_LTI_HESSIAN_DMMA)
+    return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 1> : lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 0>;
+  return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 1>
+              : lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 0>;
+}
+
 static cudaError_t lti_opt_in_smem() {
-  cudaError_t e = cudaFuncSetAttribute(lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  cudaError_t e = cudaSuccess;
+  for (int mode = 0; mode < 2; ++mode)
+    for (int wide = 0; wide < 2 && e == cudaSuccess; ++wide)
+      e = cudaFuncSetAttribute(lti_kernel(mode, wide), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               227 * 1024);
   return e;
 }
 
@@ -684,6 +697,7 @@ struct mpci_lti_plan {
   // per Hessian mode (index = MPCI_LTI_HESSIAN_*): the DMMA operands need kPadL zeros
   // before every generator row, the recursion does not and so fits more CTAs per SM
   int pad[2], LD[2], LDw[2], scan;
+  int threads[2];  // CTA size per mode: kThreads, or kWideThreads when one CTA per SM fits anyway
   size_t smem_bytes[2];
   int blocks_per_sm[2];
 };
@@ -703,12 +717,12 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   size_t smems[2];
   for (int mode = 0; mode < 2; ++mode) {
     LDs[mode] = LDws[mode] = lti_row_len(N, pads[mode]);
-    smems[mode] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], 0);
+    smems[mode] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], 0, kWarps);
   }
   // the band scan of the recursion mode: skewed rows, the warps' T patches, and its
   // unchecked operand loads reach 47 doubles before wz (hessian_scan)
   const int LDg_scan = lti_skew(LDs[1], m + 1), LDw_scan = lti_skew(LDs[1], m);
-  const size_t smem_scan = sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, 1);
+  const size_t smem_scan = sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, 1, kWarps);
   const int scan = smem_scan <= 227 * 1024 &&
                    lti_mats_doubles(n) + lti_gz_doubles(n, m, LDg_scan) >= 48;
   if (scan) {
@@ -767,15 +781,25 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
                    cudaMemcpyHostToDevice);
   if (e == cudaSuccess)  // the largest opt-in size: plans of different sizes share the kernels
     e = lti_opt_in_smem();
-  int per_sm[2] = {0, 0};
-  for (int mode = 0; mode < 2 && e == cudaSuccess; ++mode)
-    if (smems[mode] <= 227 * 1024)
-      e = mode == MPCI_LTI_HESSIAN_DMMA
-              ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-                    &per_sm[mode], lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA>, kThreads, smems[mode])
-              : cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-                    &per_sm[mode], lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION>, kThreads,
-                    smems[mode]);
+  int per_sm[2] = {0, 0}, threads[2] = {kThreads, kThreads};
+  for (int mode = 0; mode < 2 && e == cudaSuccess; ++mode) {
+    if (smems[mode] > 227 * 1024) continue;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm[mode], lti_kernel(mode, 0), kThreads,
+                                                      smems[mode]);
+    if (e != cudaSuccess || per_sm[mode] > 1) continue;
+    // one CTA per SM: give it more warps if its shared memory (larger T-patch area) still fits
+    const int is_scan = mode == MPCI_LTI_HESSIAN_RECURSION && scan;
+    const size_t wide = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], is_scan,
+                                                          kWideThreads / 32);
+    int fit = 0;
+    if (wide <= 227 * 1024)
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, lti_kernel(mode, 1), kWideThreads, wide);
+    if (e == cudaSuccess && fit >= 1) {
+      threads[mode] = kWideThreads;
+      smems[mode] = wide;
+      per_sm[mode] = fit;
+    }
+  }
   if (e != cudaSuccess) {
     int rc = mpci::cuda_fail(e, "lti_plan_create");
     if (p->dev) cudaFree(p->dev);
@@ -795,6 +819,7 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   for (int mode = 0; mode < 2; ++mode) {
     p->pad[mode] = pads[mode];
     p->LD[mode] = LDs[mode];
+    p->threads[mode] = threads[mode];
     p->LDw[mode] = LDws[mode];
     p->smem_bytes[mode] = smems[mode];
     p->blocks_per_sm[mode] = per_sm[mode] < 1 ? 1 : per_sm[mode];
@@ -828,7 +853,7 @@ extern "C" double mpci_lti_hessian_flops(const mpci_lti_plan* p, int mode) {
   return dmmas * n * m * m * 512.0 + 2.0 * n * n * m * N;
 }
 
-extern "C" int mpci_lti_plan_info(const mpci_lti_plan* p, int mode, long info[5]) {
+extern "C" int mpci_lti_plan_info(const mpci_lti_plan* p, int mode, long info[6]) {
   if (!p || !info) return mpci::fail(-3, "lti_plan_info: NULL argument");
   if (mode != MPCI_LTI_HESSIAN_DMMA && mode != MPCI_LTI_HESSIAN_RECURSION)
     return mpci::fail(-1, "lti_plan_info: unknown hessian_mode %d", mode);
@@ -837,6 +862,7 @@ extern "C" int mpci_lti_plan_info(const mpci_lti_plan* p, int mode, long info[5]
   info[2] = mode == MPCI_LTI_HESSIAN_RECURSION ? p->scan : 0;
   info[3] = p->LD[mode];
   info[4] = p->LDw[mode];
+  info[5] = p->threads[mode];
   return 0;
 }
 
@@ -869,12 +895,8 @@ extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long s
   a.sms = sms;
   const long resident = (long)sms * p->blocks_per_sm[mode];
   const unsigned grid = (unsigned)(batch < resident ? batch : resident);
-  if (mode == MPCI_LTI_HESSIAN_DMMA)
-    lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA>
-        <<<grid, kThreads, p->smem_bytes[mode], mpci::as_stream(stream)>>>(a);
-  else
-    lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION>
-        <<<grid, kThreads, p->smem_bytes[mode], mpci::as_stream(stream)>>>(a);
+  lti_kernel(mode, p->threads[mode] == kWideThreads)
+      <<<grid, p->threads[mode], p->smem_bytes[mode], mpci::as_stream(stream)>>>(a);
   MPCI_LAUNCH_CHECK("lti_assemble_kernel");
   return 0;
 }

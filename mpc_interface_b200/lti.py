@@ -100,14 +100,14 @@ class LtiPlan:
         return float(device.lib().mpci_lti_hessian_flops(self.device_plan().handle, mode))
 
     def launch_info(self, mode=HESSIAN_DMMA):
-        """{smem_bytes, ctas_per_sm, scan, ld_gz, ld_wz} of the kernel in ``mode``."""
+        """{smem_bytes, ctas_per_sm, scan, ld_gz, ld_wz, threads} of the kernel in ``mode``."""
         import ctypes
 
         from . import device
 
-        info = (ctypes.c_long * 5)()
+        info = (ctypes.c_long * 6)()
         device.check(device.lib().mpci_lti_plan_info(self.device_plan().handle, mode, info))
-        return dict(zip(("smem_bytes", "ctas_per_sm", "scan", "ld_gz", "ld_wz"), list(info)))
+        return dict(zip(("smem_bytes", "ctas_per_sm", "scan", "ld_gz", "ld_wz", "threads"), list(info)))
 
     def device_plan(self):
         if self._device is None:
