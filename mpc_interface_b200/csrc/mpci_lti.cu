@@ -425,6 +425,8 @@ constexpr int kScanLd = 40;  // 32 diagonals + 8 rows
 // only enables the scan when the layout guarantees it) -- and garbage there only
 // reaches its own row / column of T.  Only the padding of K to a multiple of 4 has to
 // contribute exact zeros.
+// KFULL: n is a multiple of 4, no K padding to mask.
+template <bool KFULL>
 __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
   const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1, nv = a.m * a.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -445,13 +447,14 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
     const bool has = delta <= N - 1;
     const int p_lo = has ? max(0, -delta) : N;
     const unsigned p_rng = has ? (unsigned)(min(N - 1, N - 1 - delta) - p_lo) : 0u;
-    const double quu = (delta == 0) ? a.Quu[j * m + jp] : 0.0;
     int p0 = N - 8 * ((N - 1 - p_first) / 8 + 1);  // rows p0 .. p0+7, bottom band first
     const double* ga = s.gz + (size_t)(t * w + j) * LD + a.pad + (N - 1 - p0 - g);
     const double* wb = s.wz + (size_t)(t * m + jp) * a.LDw + a.pad + (N - 1 - (p0 + d0) - g);
     double* qd = Pb + (size_t)(j * N + p0 + 7) * nv + (size_t)jp * N + (p0 + 7 + delta);
     const long qstep = (long)nv + 1;
-    double carry = 0.0;
+    // the running sum of the main diagonal starts at Quu[j][j']: every entry of that
+    // diagonal then carries the + Quu delta_pc term, no separate add per entry
+    double carry = (delta == 0) ? a.Quu[j * m + jp] : 0.0;
     for (; p0 + 7 >= p_last; p0 -= 8, ga += 8, wb += 8) {
       double acc[5][2];
 #pragma unroll
@@ -459,7 +462,7 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
       const double* gk = ga;
       const double* wk = wb;
       for (int ks = 0; ks < ksteps; ++ks, gk += ga_step, wk += wb_step) {
-        const bool k_ok = 4 * ks + t < n;
+        const bool k_ok = KFULL || 4 * ks + t < n;
         const double av = k_ok ? gk[0] : 0.0;
         double bv[5];
 #pragma unroll
@@ -474,7 +477,7 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
       for (int r = 7; r >= 0; --r) {
         if ((unsigned)(p0 + r - p_lo) <= p_rng) {
           carry += twl[r * (kScanLd + 1)];
-          __stcs(qd, carry + quu);
+          __stcs(qd, carry);
         }
         qd -= qstep;
       }
@@ -656,7 +659,8 @@ lti_assemble_kernel(LtiArgs a) {
     if (a.P) {
       double* Pb = a.P + (size_t)b * nv * nv;
       if (MODE == MPCI_LTI_HESSIAN_DMMA) hessian_dmma(a, s, Pb);
-      else if (a.scan) hessian_scan(a, s, Pb);
+      else if (a.scan && a.n % 4 == 0) hessian_scan<true>(a, s, Pb);
+      else if (a.scan) hessian_scan<false>(a, s, Pb);
       else if (a.m == 1) hessian_recursion<1>(a, s, Pb);
       else if (a.m == 2) hessian_recursion<2>(a, s, Pb);
       else if (a.m == 3) hessian_recursion<3>(a, s, Pb);
