@@ -214,6 +214,15 @@ int mpci_lti_assemble(const mpci_lti_plan* plan, const double* A_dev, long strid
                       const double* scalars_dev, double* P_dev, double* q_dev, double* G_dev,
                       double* h_dev, long batch, int hessian_mode, void* stream);
 
+/* Same with HOST buffers (pinned memory gives full PCIe speed): inputs go to the device
+ * and results come back in chunks of `chunk` instances on two streams.  The plan owns the
+ * device staging buffers (allocated on first use, freed by mpci_lti_plan_destroy).      */
+int mpci_lti_assemble_host(mpci_lti_plan* plan, const double* A_host, long strideA,
+                           const double* B_host, long strideB, const double* x0_host,
+                           const double* scalars_host, double* P_host, double* q_host,
+                           double* G_host, double* h_host, long batch, int hessian_mode,
+                           long chunk);
+
 /* Flops the Hessian phase of one instance executes in `hessian_mode`
  * (for the FP64 roofline; the structural count is SURVEY.md 8(d)).            */
 double mpci_lti_hessian_flops(const mpci_lti_plan* plan, int hessian_mode);

@@ -704,6 +704,11 @@ struct mpci_lti_plan {
   int threads[2];  // CTA size per mode: kThreads, or kWideThreads when one CTA per SM fits anyway
   size_t smem_bytes[2];
   int blocks_per_sm[2];
+  // staging of mpci_lti_assemble_host (two slots), allocated on first use
+  long slot_capacity;
+  double* slot_in[2];   // A | B | x0 | scalars
+  double* slot_out[2];  // P | q | G | h
+  cudaStream_t streams[2];
 };
 
 extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out) {
@@ -834,6 +839,11 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
 
 extern "C" int mpci_lti_plan_destroy(mpci_lti_plan* p) {
   if (!p) return 0;
+  for (int s = 0; s < 2; ++s) {
+    if (p->slot_in[s]) cudaFree(p->slot_in[s]);
+    if (p->slot_out[s]) cudaFree(p->slot_out[s]);
+    if (p->streams[s]) cudaStreamDestroy(p->streams[s]);
+  }
   if (p->dev) cudaFree(p->dev);
   delete p;
   return 0;
@@ -902,5 +912,80 @@ extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long s
   lti_kernel(mode, p->threads[mode] == kWideThreads)
       <<<grid, p->threads[mode], p->smem_bytes[mode], mpci::as_stream(stream)>>>(a);
   MPCI_LAUNCH_CHECK("lti_assemble_kernel");
+  return 0;
+}
+
+// Host buffers: chunks of instances alternate between two slots / streams, so the
+// upload of one chunk and the download of the previous one overlap the kernel.
+extern "C" int mpci_lti_assemble_host(mpci_lti_plan* p, const double* A, long strideA,
+                                      const double* B, long strideB, const double* x0,
+                                      const double* scalars, double* P, double* q, double* G,
+                                      double* h, long batch, int mode, long chunk) {
+  if (!p) return mpci::fail(-3, "lti_assemble_host: NULL plan");
+  if (batch < 0 || chunk < 1) return mpci::fail(-1, "lti_assemble_host: bad batch / chunk");
+  if (batch == 0) return 0;
+  if (!A || !B || !x0 || (p->S > 0 && !scalars))
+    return mpci::fail(-3, "lti_assemble_host: NULL input");
+  const long n = p->n, m = p->m, S = p->S;
+  if ((strideA != 0 && strideA < n * n) || (strideB != 0 && strideB < n * m))
+    return mpci::fail(-4, "lti_assemble_host: instance strides smaller than the matrices");
+  if (chunk > batch) chunk = batch;
+  const long nv = m * p->N, nc = (long)p->n_groups * p->N;
+  const long in_per = n * n + n * m + n + S, out_per = nv * nv + nv + nc * nv + nc;
+  if (p->slot_capacity < chunk) {
+    for (int s = 0; s < 2; ++s) {
+      if (p->slot_in[s]) cudaFree(p->slot_in[s]);
+      if (p->slot_out[s]) cudaFree(p->slot_out[s]);
+      p->slot_in[s] = p->slot_out[s] = nullptr;
+    }
+    p->slot_capacity = 0;
+    for (int s = 0; s < 2; ++s) {
+      MPCI_CUDA(cudaMalloc(&p->slot_in[s], sizeof(double) * in_per * chunk));
+      MPCI_CUDA(cudaMalloc(&p->slot_out[s], sizeof(double) * out_per * chunk));
+      if (!p->streams[s])
+        MPCI_CUDA(cudaStreamCreateWithFlags(&p->streams[s], cudaStreamNonBlocking));
+    }
+    p->slot_capacity = chunk;
+  }
+  int slot = 0;
+  for (long b0 = 0; b0 < batch; b0 += chunk, slot ^= 1) {
+    const long nb = (batch - b0 < chunk) ? batch - b0 : chunk;
+    cudaStream_t st = p->streams[slot];
+    double* d_A = p->slot_in[slot];
+    double* d_B = d_A + n * n * chunk;
+    double* d_x = d_B + n * m * chunk;
+    double* d_s = d_x + n * chunk;
+    double* d_P = p->slot_out[slot];
+    double* d_q = d_P + nv * nv * chunk;
+    double* d_G = d_q + nv * chunk;
+    double* d_h = d_G + nc * nv * chunk;
+    // shared dynamics (stride 0): one matrix per chunk; per-instance: a strided copy
+    if (strideA == 0)
+      MPCI_CUDA(cudaMemcpyAsync(d_A, A, sizeof(double) * n * n, cudaMemcpyHostToDevice, st));
+    else
+      MPCI_CUDA(cudaMemcpy2DAsync(d_A, sizeof(double) * n * n, A + b0 * strideA,
+                                  sizeof(double) * strideA, sizeof(double) * n * n, nb,
+                                  cudaMemcpyHostToDevice, st));
+    if (strideB == 0)
+      MPCI_CUDA(cudaMemcpyAsync(d_B, B, sizeof(double) * n * m, cudaMemcpyHostToDevice, st));
+    else
+      MPCI_CUDA(cudaMemcpy2DAsync(d_B, sizeof(double) * n * m, B + b0 * strideB,
+                                  sizeof(double) * strideB, sizeof(double) * n * m, nb,
+                                  cudaMemcpyHostToDevice, st));
+    MPCI_CUDA(cudaMemcpyAsync(d_x, x0 + b0 * n, sizeof(double) * nb * n, cudaMemcpyHostToDevice, st));
+    if (S)
+      MPCI_CUDA(cudaMemcpyAsync(d_s, scalars + b0 * S, sizeof(double) * nb * S,
+                                cudaMemcpyHostToDevice, st));
+    int rc = mpci_lti_assemble(p, d_A, strideA ? n * n : 0, d_B, strideB ? n * m : 0, d_x,
+                               S ? d_s : nullptr, P ? d_P : nullptr, q ? d_q : nullptr,
+                               G ? d_G : nullptr, h ? d_h : nullptr, nb, mode, st);
+    if (rc) return rc;
+    if (P) MPCI_CUDA(cudaMemcpyAsync(P + b0 * nv * nv, d_P, sizeof(double) * nb * nv * nv, cudaMemcpyDeviceToHost, st));
+    if (q) MPCI_CUDA(cudaMemcpyAsync(q + b0 * nv, d_q, sizeof(double) * nb * nv, cudaMemcpyDeviceToHost, st));
+    if (G) MPCI_CUDA(cudaMemcpyAsync(G + b0 * nc * nv, d_G, sizeof(double) * nb * nc * nv, cudaMemcpyDeviceToHost, st));
+    if (h) MPCI_CUDA(cudaMemcpyAsync(h + b0 * nc, d_h, sizeof(double) * nb * nc, cudaMemcpyDeviceToHost, st));
+  }
+  MPCI_CUDA(cudaStreamSynchronize(p->streams[0]));
+  MPCI_CUDA(cudaStreamSynchronize(p->streams[1]));
   return 0;
 }

@@ -98,6 +98,12 @@ _SIGNATURES = {
     ),
     "mpci_lti_plan_create": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
     "mpci_lti_plan_destroy": (ctypes.c_int, [ctypes.c_void_p]),
+    "mpci_lti_assemble_host": (
+        ctypes.c_int,
+        [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
+         _c_double_p, _c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_long,
+         ctypes.c_int, ctypes.c_long],
+    ),
     "mpci_lti_hessian_flops": (ctypes.c_double, [ctypes.c_void_p, ctypes.c_int]),
     "mpci_lti_plan_info": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
     "mpci_lti_assemble": (

@@ -322,3 +322,43 @@ def assemble(plan, A, B, x0, params=None, out=None, hessian=HESSIAN_DMMA):
         )
     )
     return out
+
+
+def assemble_host(plan, A, B, x0, params=None, hessian=HESSIAN_DMMA, chunk=256, out=None):
+    """Runs ``mpci_lti_assemble_host``: numpy inputs (``A`` [batch,n,n] or [n,n], ``B``
+    likewise, ``x0`` [batch,n]) and HOST results.  ``out`` = (P, q, G, h) pinned CPU
+    tensors to fill (allocated when None); returns that tuple."""
+    import torch
+
+    from . import device
+
+    dp = plan.device_plan()
+    n, m = plan.n, plan.m
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    if x0.ndim != 2 or x0.shape[1] != n:
+        raise ValueError(
+            "matmul: the given vector has {} elements per instance, the formulation "
+            "expects {}".format(x0.shape[-1], n)
+        )
+    batch = x0.shape[0]
+    if A.shape[-2:] != (n, n) or B.shape[-2:] != (n, m):
+        raise ValueError("A must be [..., {0}, {0}] and B [..., {0}, {1}]".format(n, m))
+    for M in (A, B):
+        if M.ndim == 3 and M.shape[0] != batch:
+            raise ValueError("the dynamics hold {} instances, x0 {}".format(M.shape[0], batch))
+    S = len(plan.slots.exprs)
+    scalars = plan.slots.evaluate(params or {}, batch) if S else None
+    if out is None:
+        shapes = ([batch, plan.nv, plan.nv], [batch, plan.nv], [batch, plan.nc, plan.nv], [batch, plan.nc])
+        out = tuple(torch.empty(shape, dtype=torch.float64).pin_memory() for shape in shapes)
+    hp = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(0)  # noqa: E731
+    device.check(
+        device.lib().mpci_lti_assemble_host(
+            dp.handle, hp(A), n * n if A.ndim == 3 else 0, hp(B), n * m if B.ndim == 3 else 0,
+            hp(x0), hp(scalars), *(ctypes.c_void_p(t.data_ptr()) for t in out),
+            batch, int(hessian), int(chunk),
+        )
+    )
+    return out

@@ -145,3 +145,34 @@ def test_lti_launch_info(dev):
     assert rec["ctas_per_sm"] >= dm["ctas_per_sm"] >= 1
     # skewed rows: (rows * LD) mod 16 in {4, 12} for the strided DMMA operand loads
     assert (5 * rec["ld_gz"]) % 16 in (4, 12) and (4 * rec["ld_wz"]) % 16 in (4, 12)
+
+
+@pytest.mark.parametrize("per_instance", [True, False])
+def test_lti_host_buffer_entry_point(dev, per_instance):
+    """mpci_lti_assemble_host (chunks on two streams, ragged last chunk) returns exactly
+    what the device-resident call computes, for per-instance and for shared dynamics."""
+    import torch
+    from mpc_interface_b200 import lti
+
+    g = cases.golden("generic_perinst_small")
+    form, params = _form(g, True)
+    plan = form.lti_plan("plant")
+    reps = 5  # 20 instances, chunk 6 -> chunks of 6, 6, 6, 2
+    A = np.tile(g["A_sys"], [reps, 1, 1]) if per_instance else g["A_sys"][0]
+    B = np.tile(g["B_sys"], [reps, 1, 1]) if per_instance else g["B_sys"][0]
+    x0 = np.tile(g["x0"], [reps, 1])
+    big = {k: np.tile(v, reps) for k, v in params.items()}
+    for mode in (lti.HESSIAN_DMMA, lti.HESSIAN_RECURSION):
+        dev_out = lti.assemble(plan, A, B, x0, big, hessian=mode)
+        P, q, G, h = lti.assemble_host(plan, A, B, x0, big, hessian=mode, chunk=6)
+        assert torch.equal(P, dev_out.P.cpu()) and torch.equal(q, dev_out.q.cpu())
+        assert torch.equal(G, dev_out.G.cpu()) and torch.equal(h, dev_out.h.cpu())
+    null = ctypes_null()
+    assert dev.lib().mpci_lti_assemble_host(plan.device_plan().handle, null, 16, null, 8, null, null,
+                                            null, null, null, null, 4, 0, 2) < 0
+
+
+def ctypes_null():
+    import ctypes
+
+    return ctypes.c_void_p(0)
