@@ -55,11 +55,12 @@ struct LtiArgs {
 };
 
 struct Smem {
-  double *M0, *M1, *Q, *gz, *wz, *r, *tx, *tu, *cg, *tb;
+  double *A, *M0, *M1, *Q, *gz, *wz, *r, *tx, *tu, *cg, *tb;
+  int* next_item;  // work counter of the Hessian scan (warps fetch items as they get free)
 };
 
 // Shared memory of one instance (doubles):
-//   M0, M1, Q      3 n^2  (A^have ping-pong, Qxx)
+//   A, M0, M1, Q   4 n^2  (A for the adjoint recursion of q, A^have ping-pong, Qxx)
 //   gz  [n][m+1][LD]  gz[i][c][pad + d] = (A^d [B | x0])[i][c], d = 0..N: the doubling
 //                     writes straight into it; column c = m is the free response,
 //                     f_k[i] = gz[i][m][pad + 1 + k]
@@ -78,7 +79,7 @@ __host__ __device__ inline size_t lti_aux_doubles(int n, int m, int N, int scan,
   const size_t cg = (size_t)2 * 4 * m * N, tb = scan ? (size_t)warps * 8 * 40 : 0;  // two window sets
   return ((cg > tb ? cg : tb) + 1) & ~(size_t)1;
 }
-__host__ __device__ inline size_t lti_mats_doubles(int n) { return ((size_t)3 * n * n + 1) & ~(size_t)1; }
+__host__ __device__ inline size_t lti_mats_doubles(int n) { return (size_t)4 * n * n; }
 __host__ __device__ inline size_t lti_gz_doubles(int n, int m, int LD) {
   return ((size_t)n * (m + 1) * LD + 1) & ~(size_t)1;
 }
@@ -92,13 +93,14 @@ __host__ __device__ inline int lti_skew(int LD, int rows) {
 __host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD, int LDw, int scan,
                                                    int warps) {
   return lti_mats_doubles(n) + lti_gz_doubles(n, m, LD) + lti_wz_doubles(n, m, LDw) +
-         lti_r_doubles(n, N) + lti_aux_doubles(n, m, N, scan, warps) + n + m;
+         lti_r_doubles(n, N) + lti_aux_doubles(n, m, N, scan, warps) + n + m + 2;
 }
 
 __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
   Smem s;
   const int n = a.n, m = a.m, N = a.N;
-  s.M0 = base;
+  s.A = base;
+  s.M0 = s.A + n * n;
   s.M1 = s.M0 + n * n;
   s.Q = s.M1 + n * n;
   s.gz = base + lti_mats_doubles(n);
@@ -108,6 +110,7 @@ __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
   s.cg = s.tb;                       // source of the bulk copies
   s.tx = s.tb + lti_aux_doubles(n, m, N, a.scan, (int)blockDim.x >> 5);
   s.tu = s.tx + n;
+  s.next_item = reinterpret_cast<int*>(s.tu + m);
   return s;
 }
 
@@ -129,9 +132,11 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   const double* xb = a.x0 + b * n;
   for (int e = tid; e < n * n; e += (int)blockDim.x) {
     const double v = Ab[e];
+    s.A[e] = v;
     s.M0[e] = v;
     s.Q[e] = a.Qxx[e];
   }
+  if (tid == 0) *s.next_item = 0;
   // d = 0 of every row, and the zeros before it (causality of the DMMA operands)
   for (int e = tid; e < n * w; e += (int)blockDim.x) {
     const int i = e / w, c = e - i * w;
@@ -437,7 +442,13 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
   double2* tst = reinterpret_cast<double2*>(tw + g * kScanLd + 2 * t);  // this lane's C slots
   const double* twl = tw + lane;                                         // this lane's diagonal
   const long ga_step = (long)4 * w * LD, wb_step = (long)4 * m * a.LDw;
-  for (int item = warp; item < m * m * dchunks; item += ((int)blockDim.x >> 5)) {
+  // items are fetched from a shared counter: warp 0 joins late (it runs the adjoint
+  // recursion of q first) and the items differ in length
+  for (;;) {
+    int item = 0;
+    if (lane == 0) item = atomicAdd(s.next_item, 1);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= m * m * dchunks) break;
     const int jj = item / dchunks, dc = item - jj * dchunks, j = jj / m, jp = jj - j * m;
     const int d0 = dc * 32 - (N - 1);             // diagonal of lane 0 (delta = c - p)
     const int delta = d0 + lane;
@@ -508,6 +519,44 @@ __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ q
       for (; d < len; ++d) acc0 = fma(gam[d], r[d], acc0);
     }
     qb[e] = ((acc0 + acc1) + (acc2 + acc3)) - s.tu[j];
+  }
+}
+
+// ---------------------------------------------------------------------------
+// phase 4b: q by the adjoint (costate) recursion, one warp
+//   s_p = r_p + A^T s_{p+1},   q[(j,p)] = B[:,j] . s_p - tu[j]
+// which is the same sum  sum_{k>=p} Gam_{k-p}[:,j] . r_k  in O(N n^2) instead of
+// O(N^2 n m) operations.  Lane i carries s[i]; the N steps are sequential but short, and
+// the warp runs them while the other warps are already in the Hessian scan.  s_p
+// overwrites r_p in shared memory (nothing else reads r).  Needs n <= 32.
+// ---------------------------------------------------------------------------
+__device__ void gradient_costate(const LtiArgs& a, const Smem& s, double* __restrict__ qb) {
+  const int n = a.n, m = a.m, N = a.N, w = a.m + 1, LD = a.LD, lane = threadIdx.x & 31;
+  const bool mine = lane < n;
+  double sv = 0.0;  // s_{p+1}[lane]
+  for (int p = N - 1; p >= 0; --p) {
+    double acc0 = mine ? s.r[lane * N + p] : 0.0, acc1 = 0.0;
+    int l = 0;
+    for (; l + 1 < n; l += 2) {
+      const double s0 = __shfl_sync(0xffffffffu, sv, l), s1 = __shfl_sync(0xffffffffu, sv, l + 1);
+      if (mine) {
+        acc0 = fma(s.A[l * n + lane], s0, acc0);
+        acc1 = fma(s.A[(l + 1) * n + lane], s1, acc1);
+      }
+    }
+    if (l < n) {
+      const double s0 = __shfl_sync(0xffffffffu, sv, l);
+      if (mine) acc0 = fma(s.A[l * n + lane], s0, acc0);
+    }
+    sv = acc0 + acc1;
+    if (mine) s.r[lane * N + p] = sv;
+  }
+  __syncwarp();
+  for (int e = lane; e < m * N; e += 32) {
+    const int j = e / N, p = e - j * N;
+    double acc = -s.tu[j];
+    for (int i = 0; i < n; ++i) acc = fma(s.gz[(i * w + j) * LD + a.pad], s.r[i * N + p], acc);
+    qb[e] = acc;
   }
 }
 
@@ -656,6 +705,11 @@ lti_assemble_kernel(LtiArgs a) {
       bulk_wait_read<0>();
       __syncthreads();
     }
+    // scan mode: warp 0 produces q by the adjoint recursion, then joins the scan (short
+    // problems keep the all-threads correlation: their N sequential steps would not hide
+    // under the few scan items)
+    const bool adjoint = MODE == MPCI_LTI_HESSIAN_RECURSION && a.scan && a.n <= 32 && a.m * a.N >= 128;
+    if (adjoint && a.q && threadIdx.x < 32) gradient_costate(a, s, a.q + (size_t)b * nv);
     if (a.P) {
       double* Pb = a.P + (size_t)b * nv * nv;
       if (MODE == MPCI_LTI_HESSIAN_DMMA) hessian_dmma(a, s, Pb);
@@ -667,7 +721,7 @@ lti_assemble_kernel(LtiArgs a) {
       else if (a.m == 4) hessian_recursion<4>(a, s, Pb);
       else hessian_recursion_any(a, s, Pb);
     }
-    if (a.q) gradient(a, s, a.q + (size_t)b * nv);
+    if (a.q && !adjoint) gradient(a, s, a.q + (size_t)b * nv);
     if (limits && !g_first)
       constraint_rows(a, s, a.G ? a.G + (size_t)b * nc * nv : nullptr,
                       a.h ? a.h + (size_t)b * nc : nullptr);
