@@ -41,6 +41,7 @@ struct LtiArgs {
   int LD;   // row length of gz: pad + (N + 1 rounded up to a multiple of 4), plus the
             // skew that keeps the strided DMMA operand loads of the scan conflict-free
   int LDw;  // row length of wz, likewise
+  int per_sm;  // resident CTAs per SM of this launch
   int sms;  // SMs of the device (CTA i shares an SM with i + sms, i + 2 sms, ...)
   int scan; // recursion mode: 1 = DMMA row bands + diagonal scan (needs tb / prev), 0 = plain
   const double *Qxx, *Quu, *Tx, *Tu, *cx, *cu, *arrow, *bound;  // device tables
@@ -696,7 +697,10 @@ lti_assemble_kernel(LtiArgs a) {
     // while its neighbours are in the (issue-bound) Hessian, instead of all of them
     // hitting the same unit in lock-step.
     const bool limits = (a.G || a.h) && a.n_groups;
-    const bool g_first = MODE == MPCI_LTI_HESSIAN_RECURSION && ((blockIdx.x / a.sms) & 1);
+    // (with one CTA per SM the alternation is between neighbouring SMs: half of them stream
+    // constraint rows while the other half computes -- measured 3% at C5)
+    const bool g_first = MODE == MPCI_LTI_HESSIAN_RECURSION &&
+                         (a.per_sm == 1 ? (blockIdx.x & 1) : ((blockIdx.x / a.sms) & 1));
     if (limits && g_first) {
       constraint_rows(a, s, a.G ? a.G + (size_t)b * nc * nv : nullptr,
                       a.h ? a.h + (size_t)b * nc : nullptr);
@@ -961,6 +965,7 @@ extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long s
   MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   MPCI_CUDA(lti_opt_in_smem());  // per device: the plan may be used on another GPU
   a.sms = sms;
+  a.per_sm = p->blocks_per_sm[mode];
   const long resident = (long)sms * p->blocks_per_sm[mode];
   const unsigned grid = (unsigned)(batch < resident ? batch : resident);
   lti_kernel(mode, p->threads[mode] == kWideThreads)
