@@ -38,6 +38,14 @@ class SlotTable:
     def __init__(self):
         self.exprs = []
         self._index = {}
+        self.nonnegative = []  # (expression, description): checked at every evaluate
+
+    def require_nonnegative(self, expr, what):
+        """The reference flips a limit whose extreme is negative
+        (restrictions.py:190-194); the host cannot do that for a per-instance
+        extreme, so every batch is checked instead of silently differing."""
+        if all(expr.key() != e.key() for e, _ in self.nonnegative):
+            self.nonnegative.append((expr, what))
 
     def slot(self, expr):
         key = expr.key()
@@ -59,6 +67,14 @@ class SlotTable:
         out = np.ones([batch, max(1, len(self.exprs))])
         for i, e in enumerate(self.exprs):
             out[:, i] = e.evaluate(values)
+        for e, what in self.nonnegative:
+            v = np.broadcast_to(np.asarray(e.evaluate(values), dtype=np.float64), [batch])
+            if not np.all(v >= 0):
+                raise ValueError(
+                    "{}: the per-instance extreme '{}' is negative for instance {} ({:g}); "
+                    "the reference would flip that limit (restrictions.py:190-194), which "
+                    "needs a numeric extreme".format(what, e, int(np.argmax(~(v >= 0))), float(v[np.argmax(~(v >= 0))]))
+                )
         return out
 
 
@@ -233,6 +249,9 @@ def _limit_poly(form, ops, PM, limit, slots):
                     )
                 for mono, H in picked.terms.items():
                     out.acc(_mono(mono, extra), H, 1.0, rowscale=c[:, 0])
+    for e in np.asarray(limit.extreme, dtype=object).ravel():
+        if is_expr(e):
+            slots.require_nonnegative(e, "limit on '{}'".format(limit.variable))
     bound_parts = []
     for atoms, col in split_array(limit.bound()):
         col = col.reshape([-1, 1])

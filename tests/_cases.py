@@ -152,3 +152,31 @@ def three_yaw_inputs(form, seed, batch, N):
     for k in ("yaw_a", "yaw_b", "yaw_c"):
         params[k] = rng.uniform(-1.0, 1.0, batch)
     return given, params
+
+
+# ------------------------------------------------------------ randomised formulations
+class _OwnAPI:
+    ControlSystem, ExtendedSystem, DomainVariable = ControlSystem, ExtendedSystem, DomainVariable
+    LineCombo, Cost, Box, Constraint = LineCombo, Cost, Box, Constraint
+
+    def __init__(self, backend):
+        self.backend = backend
+
+    def Formulation(self):
+        return Formulation() if self.backend is None else Formulation(backend=self.backend)
+
+
+def random_form(g, seed, backend=None):
+    """Seed ``seed`` of tests/_random_forms.py with every scalar a Param; returns
+    (form, given [B, ng], params, reference (A, h, Q, q) of golden random_forms)."""
+    import _random_forms as rf
+
+    batch = int(g["batch"])
+    vals = rf.random_scalars(seed, batch)
+    form = rf.build(_OwnAPI(backend), seed, {k: Param(k) for k in vals})
+    tag = "s%d_" % seed
+    layout = {k: g[tag + k] for k in ("optim_names", "optim_ranges", "given_names", "given_ranges")}
+    check_layout(form, layout)
+    given = np.repeat(g[tag + "given"][None, :], batch, 0)
+    ref = tuple(g[tag + k] for k in "AhQq")
+    return form, given, vals, ref

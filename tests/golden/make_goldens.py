@@ -40,6 +40,7 @@ from mpc_interface_b200.examples.generic import formulate_generic  # noqa: E402
 
 class RefAPI:
     ControlSystem, ExtendedSystem = ref_dyn.ControlSystem, ref_dyn.ExtendedSystem
+    DomainVariable = ref_dyn.DomainVariable
     Formulation, LineCombo = ref_body.Formulation, ref_comb.LineCombo
     Cost, Box, Constraint = ref_goal.Cost, ref_res.Box, ref_res.Constraint
 
@@ -248,7 +249,31 @@ def generic_per_instance(name, seed, nx, nu, N, n_rows, batch):
          A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs), N=N, **layout(form))
 
 
+def random_forms(name, seeds, batch):
+    """tests/_random_forms.py built by the reference, one formulation per instance."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _random_forms as rf
+
+    out = {"seeds": np.array(seeds), "batch": batch}
+    for seed in seeds:
+        vals = rf.random_scalars(seed, batch)
+        As, hs, Qs, qs = [], [], [], []
+        for b in range(batch):
+            form = rf.build(RefAPI, seed, {k: float(v[b]) for k, v in vals.items()})
+            given = form.arrange_given(rf.given_collector(form, seed))
+            A, h, Q, q = form.generate_all_qp_matrices(given)
+            As.append(A), hs.append(h[:, 0]), Qs.append(Q), qs.append(q[:, 0])
+        tag = "s%d_" % seed
+        out.update({tag + "given": given[:, 0], tag + "A": np.stack(As), tag + "h": np.stack(hs),
+                    tag + "Q": np.stack(Qs), tag + "q": np.stack(qs)})
+        out.update({tag + k: v for k, v in layout(form).items()})
+    save(name, **out)
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["random"]:
+        random_forms("random_forms.npz", list(range(12)), 3)
+        sys.exit(0)
     if sys.argv[1:] == ["yaw"]:
         biped_yaw("biped_n24_yaw.npz", 24, 5, 1011)
         biped_yaw("biped_n100_yaw.npz", 100, 2, 1012)

@@ -255,6 +255,35 @@ def test_more_than_eight_streamed_terms(dev, N, batch):
         cases.assert_qp_close((G[b], h[b], P[b], q[b]), ref)
 
 
+@pytest.mark.parametrize("seed", range(12))
+def test_random_formulations_against_reference(dev, seed):
+    """tests/_random_forms.py through the CUDA path against what the reference
+    produced for the same recipe (golden random_forms, make_goldens.py random):
+    13 P monomials (generic stream kernel), nine per-instance scalars, odd sizes.
+    The CSC hand-off of the same batch is checked against the dense one."""
+    g = cases.golden("random_forms")
+    form, given, params, ref = cases.random_form(g, seed)
+    out = form.generate_all_qp_matrices_batched(given, params)
+    got = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+    cases.assert_qp_close(got, ref)
+    csc = form.generate_all_qp_matrices_batched(given, params, layout="csc")
+    for b in range(given.shape[0]):
+        Pb, Gb = csc.csc(b)
+        assert np.array_equal(Pb.toarray(), got[2][b]) and np.array_equal(Gb.toarray(), got[0][b])
+
+
+def test_negative_per_instance_extreme_is_refused(dev):
+    from mpc_interface_b200 import Constraint, Param
+
+    form = cases.tiny_plant(optim=("u",))
+    form.incorporate_constraint("cap", Constraint("a", Param("e")))
+    form.make_preview_matrices()
+    given = np.zeros([2, form.given_len])
+    values = {"w": np.ones(2), "aim": np.zeros(2)}
+    with pytest.raises(ValueError, match="negative for instance 1"):
+        form.generate_all_qp_matrices_batched(given, dict(values, e=np.array([0.5, -0.1])))
+
+
 def test_reference_test_body_case(dev):
     g = cases.golden("test_body")
     body = cases.body_test_formulation()

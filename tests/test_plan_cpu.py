@@ -215,3 +215,31 @@ def test_more_than_eight_streamed_terms(cpu_extend):
         one = {k: float(v[b]) for k, v in params.items()}
         ref = orc.all_qp_matrices(form, given[b][:, None], one)
         cases.assert_qp_close((out.G[b], out.h[b], out.P[b], out.q[b]), ref)
+
+
+# ------------------------------------------------------------- randomised formulations
+@pytest.mark.parametrize("seed", range(12))
+def test_random_formulations_against_reference(cpu_extend, seed):
+    """tests/_random_forms.py: the reference built each instance with floats
+    (golden random_forms), here one formulation with nine Params -- axes or not,
+    matrix coefficients, nested definitions, a flipped limit, per-row geometry,
+    schedules, L matrices, polygons, crossed costs, mixed optimisation domains."""
+    g = cases.golden("random_forms")
+    form, given, params, ref = cases.random_form(g, seed, NumpyBackend())
+    out = form.generate_all_qp_matrices_batched(given, params)
+    cases.assert_qp_close((out.G, out.h, out.P, out.q), ref)
+
+
+def test_negative_per_instance_extreme_is_refused(cpu_extend):
+    """The reference flips a limit with a negative extreme (restrictions.py:190-194);
+    for a Param extreme the batch is checked and refused instead of differing."""
+    from mpc_interface_b200 import Constraint
+
+    form = cases.tiny_plant(NumpyBackend(), optim=("u",))
+    form.incorporate_constraint("cap", Constraint("a", Param("e")))
+    form.make_preview_matrices()
+    given = np.zeros([2, form.given_len])
+    values = {"w": np.ones(2), "aim": np.zeros(2)}
+    form.generate_all_qp_matrices_batched(given, dict(values, e=np.array([0.5, 0.0])))
+    with pytest.raises(ValueError, match="negative for instance 1"):
+        form.generate_all_qp_matrices_batched(given, dict(values, e=np.array([0.5, -0.1])))
