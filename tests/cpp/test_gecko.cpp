@@ -4,11 +4,15 @@
 // column-major stand-ins with the part of Eigen's interface the routine uses; the
 // expected values are recomputed here with plain loops (test code, not product).
 //
+// It also exercises the two bookkeeping classes of dynamics.hh (check_classes).
+//
 //   g++ -std=c++17 -I include tests/cpp/test_gecko.cpp -L mpc_interface_b200/csrc -lmpci
 //   ./a.out          runs on the GPU      ./a.out --link-only   checks the build only
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <map>
+#include <string>
 #include <vector>
 
 #include "mpci_gecko.hh"
@@ -85,6 +89,68 @@ static int check(const char* name, unsigned N, const MatrixXd& A, const MatrixXd
   return rel <= 1e-10 ? 0 : 1;  // north_star tolerance
 }
 
+// ControlSystem / ExtendedSystem (cpp/include/mpc-interface/dynamics.hh:34-146): the
+// reference has no test for them and leaves from_control_system as a TODO; the expected
+// maps are those of the Python classes (dynamics.py:248-267).
+static int check_classes() {
+  using CS = gecko::tools::ControlSystem<Tensor<3>, Tensor<4>, MatrixXd>;
+  using ES = gecko::tools::ExtendedSystem<Tensor<3>, Tensor<4>, MatrixXd>;
+  MatrixXd A(3, 3), B(3, 1);
+  const double a[3][3] = {{1., 0.1, 0.005}, {0., 1., 0.1}, {0., 0., 1.}};
+  const double b[3] = {0.00016667, 0.005, 0.1};
+  for (int i = 0; i < 3; ++i) {
+    B(i, 0) = b[i];
+    for (int j = 0; j < 3; ++j) A(i, j) = a[i][j];
+  }
+  const std::vector<std::string> inputs = {"CoM_dddot"}, states = {"CoM", "CoM_dot", "CoM_ddot"};
+  const std::vector<std::string> axes = {"_x", "_y"};
+  int bad = 0;
+  CS lip(inputs, states, A, B, axes, CS::Updater(), /*time_variant=*/true);
+  ES ext = ES::from_control_system(lip, "x", 9);
+  auto expect = [&](const std::map<std::string, int>& map, const char* key, int want) {
+    auto it = map.find(key);
+    if (it == map.end() || it->second != want) {
+      std::printf("classes: %s -> %d expected\n", key, want);
+      ++bad;
+    }
+  };
+  expect(ext.domain_ID(), "CoM_dddot_x", 0);
+  expect(ext.domain_ID(), "x0_y", 1);
+  expect(ext.state_ID(), "CoM_ddot_y", 2);
+  expect(ext.domain(), "CoM_dddot_y", 9);
+  expect(ext.domain(), "x0_x", 3);
+  expect(ext.all_variables(), "CoM_dot_x", 9);
+  if (ext.domain_ID().size() != 4 || ext.state_ID().size() != 6 || ext.all_variables().size() != 10 ||
+      ext.horizon() != 9) {
+    std::printf("classes: wrong map sizes\n");
+    ++bad;
+  }
+  // S(0) = A, and a time-variant system follows new matrices: doubling B doubles U
+  Tensor<3> S0 = ext.S();
+  Tensor<4> U0 = ext.U();
+  double worst = 0.0;
+  for (int c = 0; c < 3; ++c)
+    for (int i = 0; i < 3; ++i) worst = std::fmax(worst, std::fabs(S0(0, c, i) - A(i, c)));
+  MatrixXd B2 = B;
+  for (int i = 0; i < 3; ++i) B2(i, 0) = 2.0 * B(i, 0);
+  ext.update(A, B2);
+  Tensor<4> U1 = ext.U();
+  for (std::size_t e = 0; e < U0.v.size(); ++e) worst = std::fmax(worst, std::fabs(U1.v[e] - 2.0 * U0.v[e]));
+  if (worst > 1e-12) {
+    std::printf("classes: S / U wrong by %.3e\n", worst);
+    ++bad;
+  }
+  try {  // misuse: B does not match the names
+    MatrixXd Bw(3, 2);
+    CS wrong(inputs, states, A, Bw, axes);
+    std::printf("classes: shape check did not throw\n");
+    ++bad;
+  } catch (const std::invalid_argument&) {
+  }
+  if (!bad) std::printf("ControlSystem / ExtendedSystem ok\n");
+  return bad;
+}
+
 int main(int argc, char** argv) {
   if (argc > 1 && std::strcmp(argv[1], "--link-only") == 0) {
     std::printf("mpci version %d, devices %d\n", mpci_version(), mpci_device_count());
@@ -118,6 +184,7 @@ int main(int argc, char** argv) {
     ++bad;
   } catch (const std::invalid_argument&) {
   }
+  bad += check_classes();
   std::printf(bad ? "FAILED\n" : "gecko::tools::extend_matrices ok\n");
   return bad;
 }

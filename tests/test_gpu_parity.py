@@ -76,6 +76,9 @@ def test_gecko_cpp_extend_matrices(dev):
     done = _gecko_build.run()
     assert done.returncode == 0, done.stdout + done.stderr
     assert "gecko::tools::extend_matrices ok" in done.stdout
+    # dynamics.hh's ControlSystem / ExtendedSystem incl. the from_control_system the
+    # reference left as a TODO, name -> index maps as in dynamics.py:248-267
+    assert "ControlSystem / ExtendedSystem ok" in done.stdout
 
 
 def test_extend_matrices_errors(dev):
