@@ -1,0 +1,83 @@
+"""Out-of-bounds writes would land in the guard zones placed around every output
+array here (compute-sanitizer is not available on the GPU pool): the outputs of the
+shared-dynamics path and of the per-instance-dynamics path are carved out of one
+buffer filled with a sentinel, also at addresses that are only 8-byte aligned."""
+import numpy as np
+import pytest
+
+import _cases as cases
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    from mpc_interface_b200 import device
+
+    device.require_gpu()
+    return device
+
+SENTINEL = -1.2345e300
+GUARD = 64  # doubles before and after each array
+
+
+class Guarded:
+    """Same attributes as device.QPBatch, arrays inside one guarded buffer."""
+
+    def __init__(self, batch, nv, nc, shift):
+        import torch
+
+        self.batch, self.nv, self.nc = batch, nv, nc
+        sizes = {"P": batch * nv * nv, "q": batch * nv, "G": batch * nc * nv, "h": batch * nc}
+        total = sum(GUARD + n + (n & 1) for n in sizes.values()) + GUARD + 2
+        self.buf = torch.full([total], SENTINEL, dtype=torch.float64, device="cuda")
+        self.spans, pos = {}, shift  # shift = 1: every array starts at an odd double
+        for name, n in sizes.items():
+            pos += GUARD
+            self.spans[name] = (pos, pos + n)
+            pos += n + (n & 1)
+        self.P = self.buf[slice(*self.spans["P"])].view(batch, nv, nv)
+        self.q = self.buf[slice(*self.spans["q"])].view(batch, nv)
+        self.G = self.buf[slice(*self.spans["G"])].view(batch, nc, nv)
+        self.h = self.buf[slice(*self.spans["h"])].view(batch, nc)
+
+    def check(self):
+        import torch
+
+        inside = torch.zeros_like(self.buf, dtype=torch.bool)
+        for a, b in self.spans.values():
+            inside[a:b] = True
+        outside = self.buf[~inside]
+        assert bool((outside == SENTINEL).all()), "a kernel wrote outside its output arrays"
+        assert not bool((self.buf[inside] == SENTINEL).any()), "an output entry was left unwritten"
+
+
+@pytest.mark.parametrize("shift", [0, 1])
+@pytest.mark.parametrize("seed", [0, 2, 5])
+def test_shared_dynamics_outputs_stay_inside(dev, seed, shift):
+    g = cases.golden("random_forms")
+    form, given, params, ref = cases.random_form(g, seed)
+    plan = form._compiled()
+    out = Guarded(given.shape[0], plan.nv, plan.nc, shift)
+    form.generate_all_qp_matrices_batched(given, params, out=out)
+    out.check()
+    got = tuple(x.cpu().numpy() for x in (out.G, out.h, out.P, out.q))
+    cases.assert_qp_close(got, ref)
+
+
+@pytest.mark.parametrize("shift", [0, 1])
+@pytest.mark.parametrize("hessian", ["dmma", "recursion"])
+@pytest.mark.parametrize("name", ["generic_perinst_small", "generic_perinst_odd"])
+def test_per_instance_dynamics_outputs_stay_inside(dev, name, hessian, shift):
+    g = cases.golden(name)
+    form = cases.formulate_generic(g["A_sys"][0], g["B_sys"][0], g["Q_w"], g["R_w"], int(g["N"]), g["rows"],
+                                   refs=[cases.Param("ref%d" % i) for i in range(g["ref"].shape[1])])
+    params = {"ref%d" % i: g["ref"][:, i] for i in range(g["ref"].shape[1])}
+    plan = form.lti_plan("plant")
+    batch = g["x0"].shape[0]
+    out = Guarded(batch, plan.nv, plan.nc, shift)
+    form.generate_all_qp_matrices_batched(g["x0"], params, out=out, hessian=hessian,
+                                          dynamics={"plant": (g["A_sys"], g["B_sys"])})
+    out.check()
+    got = tuple(x.cpu().numpy() for x in (out.G, out.h, out.P, out.q))
+    cases.assert_qp_close(got, (g["A"], g["h"], g["Q"], g["q"]))
