@@ -282,13 +282,16 @@ def run_own(args):
         out = None  # frees the 75.6 GB of outputs (the closures above share this cell)
         torch.cuda.empty_cache()
         lti_lines = run_lti()
+    single = None
+    if rank == 0 and world == 1 and not args.no_lti:
+        single = run_single()
 
     result = None
     if rank == 0:
         result = dict(B=B, world=world, ms=ms, t_P=t_P, t_G=t_G, t_qh=t_qh, nv=nv, ng=ng, nc=nc,
                       clocks=clocks, launches=device.lib().mpci_assemble_launches(handle),
                       n_scalars=scalars_h.shape[1], t_csc=t_csc, csc_bytes=csc_bytes,
-                      nnz=(pP.nnz, pG.nnz), lti=lti_lines, t_shared=t_shared,
+                      nnz=(pP.nnz, pG.nnz), lti=lti_lines, single=single, t_shared=t_shared,
                       shared_terms=shared_terms)
         result["e2e"] = run_e2e(args, form, plan, ops, world)
     elif distributed:
@@ -319,6 +322,17 @@ def run_lti():
                 "fp64_frac": d["fp64_frac_executed"],
                 "flops_per_qp": d["flops_per_qp"]})
     return out
+
+
+def run_single():
+    """scripts/latency.py: ONE instance through the reference's own call
+    (Formulation.generate_all_qp_matrices, NumPy in / NumPy out), wall clock per call."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("latency", os.path.join(ROOT, "scripts", "latency.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return [mod.measure(N, 200) for N in (24, 100)]
 
 
 def run_e2e(args, form, plan, ops, world):
@@ -459,6 +473,11 @@ def main():
                     "instance); reported separately from the headline, which has per-instance omega"}
     if res.get("lti"):
         line["per_instance_dynamics"] = res["lti"]
+    if res.get("single"):
+        line["single_instance_latency"] = {
+            "calls": res["single"],
+            "note": "one instance per call through generate_all_qp_matrices(given) (the reference's own "
+                    "usage, NumPy in / NumPy out), wall clock; oracle_ms_per_call = the CPU port on one core"}
     if not args.no_cpu_baseline and world == 1:
         v, n = cpu_baseline(args.cpu_sample, 1)
         line["cpu_baseline"] = {

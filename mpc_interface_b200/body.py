@@ -321,6 +321,9 @@ class Formulation:
         use, see biped_mpc_loop.py:60)."""
         if not _plan.ordered_limits(self):
             raise ValueError("need at least one array to concatenate")
+        compiled, ops = self._compiled(), self._ops()
+        if not compiled.slots.exprs and hasattr(ops, "assemble_single"):
+            return ops.assemble_single(compiled, self._single(given))
         out = self._run(self._single(given), None)
         return (
             out.G_numpy()[0],

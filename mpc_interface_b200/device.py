@@ -408,6 +408,35 @@ class DeviceBackend:
         )
         return out
 
+    def assemble_single(self, plan, given):
+        """One instance, NumPy in and NumPy out -- the reference's own call pattern
+        (body.py:333-348 once per control tick).  The plan keeps one device buffer
+        [given | P | q | G | h] and its pinned host mirror, so a call is one upload,
+        the three kernels and ONE download; the four arrays returned are fresh copies,
+        as the reference's are."""
+        torch = self.torch
+        dp = self.device_plan(plan)
+        nv, nc, ng = plan.nv, plan.nc, plan.ng
+        ws = getattr(plan, "_single_ws", None)
+        if ws is None:
+            sizes = [ng, nv * nv, nv, nc * nv, nc]
+            starts = np.concatenate([[0], np.cumsum([n + (n & 1) for n in sizes])])  # 16-byte aligned
+            dev = torch.empty([int(starts[-1]) + 2], dtype=torch.float64, device=self.device)
+            host = torch.empty([int(starts[-1]) + 2], dtype=torch.float64).pin_memory()
+            ones = torch.ones([1, max(1, len(plan.slots.exprs))], dtype=torch.float64, device=self.device)
+            ws = plan._single_ws = (dev, host, [int(x) for x in starts], sizes, ones)
+        dev, host, starts, sizes, ones = ws
+        part = [dev[a:a + n] for a, n in zip(starts, sizes)]
+        host[:ng] = torch.from_numpy(np.ascontiguousarray(given, dtype=np.float64).reshape(ng))
+        part[0].copy_(host[:ng], non_blocking=True)
+        check(lib().mpci_assemble(dp.handle, _ptr(ones), _ptr(part[0]), _ptr(part[1]), _ptr(part[2]),
+                                  _ptr(part[3]), _ptr(part[4]), 1, _stream_ptr()))
+        host[starts[1]:].copy_(dev[starts[1]:], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        arr = host.numpy()
+        P, q, G, h = (np.array(arr[a:a + n]) for a, n in zip(starts[1:], sizes[1:]))
+        return G.reshape(nc, nv), h.reshape(nc, 1), P.reshape(nv, nv), q.reshape(nv, 1)
+
     def preview(self, pplan, scalars, given_optim, batch):
         """Rows of a PreviewPlan for a batch: [batch, total rows] (device tensor)."""
         torch = self.torch
