@@ -94,7 +94,7 @@ extern "C" int mpci_plan_create(const mpci_plan_desc* d, mpci_plan** out) {
 
   // Row chunks: at most kQhChunk consecutive rows, never across the q / h border
   // (so a chunk is one contiguous run of q or of h).  Chunks are dealt to the
-  // warps longest-first (greedy balance of the non-zero count).
+  // kQhLists lists longest-first (greedy balance of the non-zero count).
   struct Chunk { int row0, nrows, seg_begin, seg_end; long work; };
   std::vector<Chunk> chunks;
   {
@@ -117,18 +117,18 @@ extern "C" int mpci_plan_create(const mpci_plan_desc* d, mpci_plan** out) {
   for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
   std::stable_sort(order.begin(), order.end(),
                    [&](int x, int y) { return chunks[x].work > chunks[y].work; });
-  std::vector<std::vector<int>> per_warp(mpci::kQhWarps);
-  std::vector<long> load(mpci::kQhWarps, 0);
+  std::vector<std::vector<int>> per_warp(mpci::kQhLists);
+  std::vector<long> load(mpci::kQhLists, 0);
   for (int idx : order) {
     int w = 0;
-    for (int k = 1; k < mpci::kQhWarps; ++k) if (load[k] < load[w]) w = k;
+    for (int k = 1; k < mpci::kQhLists; ++k) if (load[k] < load[w]) w = k;
     per_warp[w].push_back(idx);
     load[w] += chunks[idx].work;
   }
   // per-warp record streams: chunks -> rows -> (row, term) segments -> non-zeros
   std::vector<mpci::QhNz> h_nz;
   std::vector<int> h_chunks, h_nz_ptr(1, 0), h_chunk_ptr(1, 0);
-  for (int w = 0; w < mpci::kQhWarps; ++w) {
+  for (int w = 0; w < mpci::kQhLists; ++w) {
     std::sort(per_warp[w].begin(), per_warp[w].end());
     for (int idx : per_warp[w]) {
       const Chunk& c = chunks[idx];

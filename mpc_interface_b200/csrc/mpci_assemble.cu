@@ -239,11 +239,12 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
   double* tile = tiles + (size_t)warp * kQhInst * kQhTileLd;
   const double2* gl = reinterpret_cast<const double2*>(gs) + lane;
   const double2* cl = reinterpret_cast<const double2*>(cs) + lane;
-  const int e_begin = a.warp_nz_ptr[warp], e_end = a.warp_nz_ptr[warp + 1];
-  int ci = a.warp_chunk_ptr[warp];
+  for (int list = warp + kQhWarps * (int)blockIdx.y; list < kQhLists; list += kQhWarps * (int)gridDim.y) {
+  const int e_begin = a.warp_nz_ptr[list], e_end = a.warp_nz_ptr[list + 1];
+  int ci = a.warp_chunk_ptr[list];
   double acc0 = 0.0, acc1 = 0.0, p0 = 0.0, p1 = 0.0;
   int r = 0;
-  // The warp's record stream comes in batches of 32: one coalesced 16-byte load
+  // The list's record stream comes in batches of 32: one coalesced 16-byte load
   // per lane (the next batch is in flight while this one is consumed), parked in
   // a 512-byte ring and read back as warp-uniform LDS.128.  A ballot marks the
   // records that end a segment, so the runs between them are a branch-free loop.
@@ -302,6 +303,7 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
     }
     __syncwarp();
   }
+  }  // lists of this warp
   }  // groups of instances
 }
 
@@ -328,7 +330,9 @@ int launch_qh(const QhArgs& a, const double* scalars, const double* given, doubl
   const long groups = (batch + kQhInst - 1) / kQhInst;
   const long resident = (long)sms * (per_sm < 1 ? 1 : per_sm);
   const unsigned blocks = (unsigned)(groups < resident ? groups : resident);
-  qh_kernel<<<blocks, kQhWarps * 32, smem, st>>>(a, scalars, given, q, h, batch);
+  int split = 1;  // blocks per group of instances: as many as leave no SM without one
+  while (split < kQhSplit && (long)blocks * split * 2 <= resident) split *= 2;
+  qh_kernel<<<dim3(blocks, split), kQhWarps * 32, smem, st>>>(a, scalars, given, q, h, batch);
   MPCI_LAUNCH_CHECK("qh_kernel");
   return 0;
 }

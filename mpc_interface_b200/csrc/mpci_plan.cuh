@@ -20,6 +20,12 @@ struct StreamArgs {
 // [q; h]: sparse rows, one instance per thread (mpci_assemble.cu)
 constexpr int kQhWarps = 16;  // warps of a block; each owns a list of row chunks
 constexpr int kQhChunk = 4;   // rows per chunk (one 32-byte run per instance)
+// The chunks are dealt to kQhWarps * kQhSplit lists; warp w of a block works through the
+// lists w, w + kQhWarps, ...  A batch too small to give every SM a block is launched with
+// up to kQhSplit blocks per group of instances (gridDim.y), each taking a share of the lists
+// of every warp: one instance then runs on 8 x 16 warps instead of 16.
+constexpr int kQhSplit = 8;
+constexpr int kQhLists = kQhWarps * kQhSplit;
 
 struct QhNz {      // 16 bytes; a warp's records are consecutive, in processing order
   double val;
@@ -35,10 +41,10 @@ constexpr int kQhEndChunk = 0x400;  // ... of a chunk of rows: write the chunk o
 struct QhArgs {
   int nv, ng, nc, n_scalars, n_terms;
   const int* factors;      // dev [n_terms][MPCI_MAX_FACTORS]
-  const QhNz* nz;          // dev: per-warp streams, concatenated
-  const int* warp_nz_ptr;  // dev [kQhWarps + 1]
-  const int2* chunks;      // dev: (first row, rows) in the order the warps meet them
-  const int* warp_chunk_ptr;  // dev [kQhWarps + 1]
+  const QhNz* nz;          // dev: the lists' record streams, concatenated
+  const int* warp_nz_ptr;  // dev [kQhLists + 1]
+  const int2* chunks;      // dev: (first row, rows) in the order the lists meet them
+  const int* warp_chunk_ptr;  // dev [kQhLists + 1]
 };
 
 int launch_stream(const StreamArgs& a, const double* scalars, int n_scalars, double* out,

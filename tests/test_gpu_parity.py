@@ -183,6 +183,30 @@ def test_biped_per_instance_yaw_goldens(dev, name):
     )
 
 
+@pytest.mark.parametrize("batch", [1, 63, 700, 2600, 10000])
+def test_qh_block_splits_over_batch_sizes(dev, batch):
+    """The [q;h] kernel spreads a small batch over up to 8 blocks per group of 64
+    instances (launch_qh: 8 at 1..576 instances, 4 / 2 up to 4736, 1 above): every
+    setting against the oracle, first / middle / last instance."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    N = 24
+    form = cases.formulate_biped(cases.default_configuration(N), omega=Param("omega"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    vals = synthetic.biped_inputs(77, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    q, h = out.q_numpy(), out.h_numpy()
+    assert np.isfinite(q).all() and np.isfinite(h).all()
+    for b in sorted({0, batch // 2, batch - 1}):
+        one = {k: float(v[b]) for k, v in params.items()}
+        ref = orc.all_qp_matrices(form, given[b][:, None], one)
+        assert cases.rel_err(q[b], np.squeeze(ref[3])) <= cases.TOL
+        assert cases.rel_err(h[b], np.squeeze(ref[1])) <= cases.TOL
+
+
 def test_biped_per_instance_geometry_vs_oracle(dev):
     """Rotation + per-instance centre and scale of the support polygon, batch 45
     at N=100 (7 streamed G terms), against the oracle."""
