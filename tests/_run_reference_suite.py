@@ -1,0 +1,63 @@
+"""Runs the reference's OWN unittest files (python/tests/test_*.py, read where they lie
+under /root/reference -- nothing is copied) against THIS package: ``mpc_interface`` is
+aliased to ``mpc_interface_b200`` before they are imported.  Build container only (the
+reference is not on the GPU box); no GPU here, so the two device entry points the host
+classes call are stood in for by the test doubles the CPU suite uses everywhere
+(oracle extend_matrices, NumpyBackend).  Prints "<run> <failures> <errors>".
+
+    python tests/_run_reference_suite.py [/root/reference/python/tests]
+"""
+import importlib
+import importlib.util
+import os
+import sys
+import types
+import unittest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.dont_write_bytecode = True
+sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+
+
+def main(test_dir):
+    import mpc_interface_b200.device as device
+    import mpc_interface_b200.tools as tools
+    from _numpy_backend import NumpyBackend
+    from oracle import qp_oracle
+
+    tools.extend_matrices = qp_oracle.extend_matrices
+    device.DeviceBackend = NumpyBackend
+
+    alias = types.ModuleType("mpc_interface")
+    alias.__path__ = []
+    sys.modules["mpc_interface"] = alias
+    for sub in ("body", "combinations", "dynamics", "goal", "restrictions", "tools"):
+        module = importlib.import_module("mpc_interface_b200." + sub)
+        sys.modules["mpc_interface." + sub] = module
+        setattr(alias, sub, module)
+    # test_dynamics.py imports matplotlib for a plot helper it never calls
+    for name in ("matplotlib", "matplotlib.pyplot", "matplotlib.colors"):
+        if name not in sys.modules:
+            try:
+                importlib.import_module(name)
+            except ImportError:
+                sys.modules[name] = types.ModuleType(name)
+                if "." in name:
+                    setattr(sys.modules["matplotlib"], name.split(".")[1], sys.modules[name])
+
+    os.chdir(test_dir)  # test_dynamics.py opens its pickle by a relative path
+    suite = unittest.TestSuite()
+    for f in sorted(os.listdir(test_dir)):
+        if f.startswith("test_") and f.endswith(".py"):
+            spec = importlib.util.spec_from_file_location("reference_" + f[:-3], os.path.join(test_dir, f))
+            module = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(module)
+            suite.addTests(unittest.defaultTestLoader.loadTestsFromModule(module))
+    result = unittest.TextTestRunner(stream=sys.stderr, verbosity=2).run(suite)
+    print(result.testsRun, len(result.failures), len(result.errors))
+    return 0 if result.wasSuccessful() else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main(sys.argv[1] if len(sys.argv) > 1 else "/root/reference/python/tests"))

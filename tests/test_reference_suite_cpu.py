@@ -1,0 +1,22 @@
+"""The reference's own unittest suite (python/tests/test_*.py, 16 tests: dynamics incl. the
+LIP_matrices pickle, body, goal, restrictions, tools) run against this package with
+``mpc_interface`` aliased to it -- see _run_reference_suite.py.  The files are read where
+they lie; where the reference is absent (the GPU box) the test is skipped, and the same
+assertions are covered by the golden-vector tests."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+REFERENCE_TESTS = "/root/reference/python/tests"
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.mark.skipif(not os.path.isdir(REFERENCE_TESTS), reason="the reference is only in the build container")
+def test_reference_unittests_pass_against_this_package():
+    done = subprocess.run([sys.executable, os.path.join(HERE, "_run_reference_suite.py"), REFERENCE_TESTS],
+                          capture_output=True, text=True, timeout=600)
+    summary = done.stdout.strip().splitlines()[-1] if done.stdout.strip() else ""
+    assert done.returncode == 0 and summary.split()[1:] == ["0", "0"], done.stderr[-3000:]
+    assert int(summary.split()[0]) >= 16
