@@ -55,8 +55,51 @@ def main(test_dir):
             spec.loader.exec_module(module)
             suite.addTests(unittest.defaultTestLoader.loadTestsFromModule(module))
     result = unittest.TextTestRunner(stream=sys.stderr, verbosity=2).run(suite)
+    example = run_example(os.path.join(os.path.dirname(test_dir), "use_examples", "simple_functional_example"))
+    print("example", "ok" if example else "FAILED")
     print(result.testsRun, len(result.failures), len(result.errors))
-    return 0 if result.wasSuccessful() else 1
+    return 0 if result.wasSuccessful() and example else 1
+
+
+def run_example(example_dir):
+    """The reference's example formulation (use_examples/simple_functional_example/
+    biped_formulation.py, unmodified) built on this package's classes: its QP of the
+    default configuration and of the receding-horizon ticks 0, 11, 12, 13 against the
+    golden vectors the reference itself produced (tests/golden/biped_c1, biped_ticks)."""
+    import numpy as np
+
+    sys.path.insert(0, example_dir)
+    import biped_configuration
+    from biped_formulation import formulate_biped
+
+    def close(got, want):
+        worst = 0.0
+        for x, r in zip(got, want):
+            if np.shape(x) != np.shape(r):
+                return False
+            worst = max(worst, float(np.max(np.abs(x - r)) / max(np.max(np.abs(r)), 1e-300)))
+        return worst <= 1e-10
+
+    golden = os.path.join(HERE, "golden")
+    form = formulate_biped(biped_configuration)
+    if not type(form).__module__.startswith("mpc_interface_b200"):
+        return False
+    g = np.load(os.path.join(golden, "biped_c1.npz"))
+    ok = close(form.generate_all_qp_matrices(g["given"]), [g[k] for k in "AhQq"])
+    t = np.load(os.path.join(golden, "biped_ticks.npz"))
+    n = biped_configuration.step_samples
+    step_times = np.array([(i + 1) * n - 1 for i in range(form.domain["Ds_x"])])
+    step_count = 0
+    for tick in range(14):
+        form.update(step_times=step_times, step_count=step_count)
+        if tick in (0, 11, 12, 13):
+            got = form.generate_all_qp_matrices(t["t%d_given" % tick])
+            ok = ok and close(got, [t["t%d_%s" % (tick, k)] for k in "AhQq"])
+        step_times = step_times - 1
+        if step_times[0] == -1:
+            step_times = step_times + n
+            step_count += 1
+    return ok
 
 
 if __name__ == "__main__":

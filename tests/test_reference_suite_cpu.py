@@ -1,7 +1,8 @@
 """The reference's own unittest suite (python/tests/test_*.py, 16 tests: dynamics incl. the
 LIP_matrices pickle, body, goal, restrictions, tools) run against this package with
 ``mpc_interface`` aliased to it -- see _run_reference_suite.py.  The files are read where
-they lie; where the reference is absent (the GPU box) the test is skipped, and the same
+they lie.  The reference's example formulation (biped_formulation.py) is built the same way and
+checked against the goldens, receding-horizon ticks included.  Where the reference is absent (the GPU box) the test is skipped, and the same
 assertions are covered by the golden-vector tests."""
 import os
 import subprocess
@@ -20,3 +21,5 @@ def test_reference_unittests_pass_against_this_package():
     summary = done.stdout.strip().splitlines()[-1] if done.stdout.strip() else ""
     assert done.returncode == 0 and summary.split()[1:] == ["0", "0"], done.stderr[-3000:]
     assert int(summary.split()[0]) >= 16
+    # and the reference's example script (biped_formulation.py) built on this package
+    assert "example ok" in done.stdout
