@@ -19,6 +19,10 @@ import time
 
 import numpy as np
 
+# stdout carries the ONE JSON line of the contract: NCCL's own log lines (its version banner
+# under NCCL_DEBUG=VERSION / INFO) go to stderr unless the caller chose a file for them
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
