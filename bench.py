@@ -19,9 +19,19 @@ import time
 
 import numpy as np
 
-# stdout carries the ONE JSON line of the contract: NCCL's own log lines (its version banner
-# under NCCL_DEBUG=VERSION / INFO) go to stderr unless the caller chose a file for them
+# stdout carries the ONE JSON line of the contract.  Libraries write to file descriptor 1 too
+# (NCCL prints its version banner there under NCCL_DEBUG=VERSION, whatever NCCL_DEBUG_FILE says),
+# so descriptor 1 is pointed at stderr for the whole run and the JSON line goes to a private
+# copy of the original stdout.
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+_RESULT_OUT = os.fdopen(os.dup(1), "w")
+sys.stdout.flush()
+os.dup2(2, 1)
+
+
+def emit(line):
+    _RESULT_OUT.write(json.dumps(line) + "\n")
+    _RESULT_OUT.flush()
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -423,7 +433,7 @@ def main():
         desc = {"value": value, "unit": "QPs/s", "cores": cores, "kind": "port",
                 "sample": "%d instances of the same workload per step over %d processes "
                           "(oracle/qp_oracle.py, 1 BLAS thread each)" % (n, cores)}
-        print(json.dumps({
+        emit(({
             "impl": "reference", "metric": METRIC, "value": value, "unit": "QPs/s",
             "n_gpus": args.gpus, "steps": len(values), "warmup": args.warmup,
             "ms_per_step": 1e3 * n / value, "higher_is_better": True, "scaling": "weak",
@@ -488,7 +498,7 @@ def main():
             "value": v, "unit": "QPs/s", "cores": 1, "kind": "port",
             "sample": "%d instances of the same workload, oracle/qp_oracle.py on 1 core" % n,
             "host_cores": cores}
-    print(json.dumps(line))
+    emit(line)
 
 
 if __name__ == "__main__":
