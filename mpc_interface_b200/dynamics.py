@@ -71,43 +71,46 @@ class DomainVariable(_WithOutputs):
 
     def __init__(self, names, sizes, axes=None, time_variant=False, how_to_update_size=None):
         names = _as_name_list(names, "variable")
-        if not isinstance(sizes, Iterable):
-            sizes = [sizes]
-        if len(names) != len(sizes):
-            raise IndexError("'names' and 'sizes' must have the same amount of elements.")
+        sizes = list(sizes) if isinstance(sizes, Iterable) else [sizes]
+        if len(sizes) != len(names):
+            raise IndexError("one size per name is needed: {} names, {} sizes".format(len(names), len(sizes)))
         self.axes = _as_axes(axes)
-        self.identify_domain(names)
-        self.set_sizes(names, sizes)
-        self.outputs = []
-        self.definitions = {}
-        self.make_definitions()
         self.time_variant = time_variant
         self._size_rule = _pick_rule(how_to_update_size, time_variant)
+        self.outputs, self.definitions = [], {}
+        self.identify_domain(names)
+        self.set_sizes(names, sizes)
+        self.make_definitions()
 
     def identify_domain(self, names):
-        self.domain_ID = {}
-        for axis in self.axes:
-            for index, name in enumerate(names):
-                self.domain_ID[name + axis] = index
+        """``domain_ID[name + axis]`` = position of ``name`` in ``names`` (dynamics.py:71-77)."""
+        self.domain_ID = {name + axis: position
+                          for axis in self.axes for position, name in enumerate(names)}
 
     def set_sizes(self, names, sizes):
-        self.domain = {name: sizes[ID] for name, ID in self.domain_ID.items()}
+        """``domain`` maps every variable to its length; ``all_variables`` is the same dict
+        object, as in the reference (dynamics.py:79-81)."""
+        self.domain = {}
+        for variable, position in self.domain_ID.items():
+            self.domain[variable] = sizes[position]
         self.all_variables = self.domain
+
+    def make_definitions(self):
+        self.definitions.update(
+            (variable, _identity_combo(variable, length)) for variable, length in self.domain.items())
 
     def update_sizes(self, **kargs):
         self._size_rule(self, **kargs)
 
-    def make_definitions(self):
-        for variable, size in self.domain.items():
-            self.definitions[variable] = _identity_combo(variable, size)
-
     def update_definitions(self):
-        for variable, size in self.domain.items():
-            self.definitions[variable].matrices[0] = np.eye(size)
-        for output in self.outputs:
-            self.definitions[output].update(domVar=self)
+        """Identities of the (possibly new) sizes, then the outputs' own rules."""
+        for variable, length in self.domain.items():
+            self.definitions[variable].matrices[0] = np.eye(length)
+        for name in self.outputs:
+            self.definitions[name].update(domVar=self)
 
     def update(self, **kargs):
+        """One tick: sizes first, then everything that depends on them."""
         self.update_sizes(**kargs)
         self.update_definitions()
 
@@ -121,17 +124,8 @@ class ExtendedSystem(_WithOutputs):
 
     _owner_key = "extSyst"
 
-    def __init__(
-        self,
-        input_names,
-        state_names,
-        state_vector_name,
-        S,
-        U,
-        axes=None,
-        time_variant=False,
-        how_to_update_matrices=None,
-    ):
+    def __init__(self, input_names, state_names, state_vector_name, S, U, axes=None,
+                 time_variant=False, how_to_update_matrices=None):
         input_names = _as_name_list(input_names, "input")
         state_names = _as_name_list(state_names, "variable")
         if not isinstance(state_vector_name, str):
@@ -158,49 +152,49 @@ class ExtendedSystem(_WithOutputs):
     def from_cotrol_system(cls, control_system, state_vector_name, horizon_lenght):
         """Extends a ControlSystem over ``horizon_lenght`` samples
         (dynamics.py:216-246; the spelling is the reference's API)."""
-        S, U = use.extend_matrices(horizon_lenght, control_system.A, control_system.B)
-        rule = None
-        if control_system.time_variant:
+        def extend(system):
+            S, U = use.extend_matrices(horizon_lenght, system.A, system.B)
+            return S, U
 
-            def rule(ext_syst, **kargs):
-                source = kargs["control_system"]
-                source.update_matrices(**kargs)
-                S, U = use.extend_matrices(horizon_lenght, source.A, source.B)
-                ext_syst.matrices = U + [S]
+        def follow_the_control_system(extended, **kargs):
+            # the tick hands the one-step system over as ``control_system=``; it refreshes
+            # its own (A, B) first, then the horizon matrices are rebuilt from them
+            system = kargs["control_system"]
+            system.update_matrices(**kargs)
+            S, U = extend(system)
+            extended.matrices = U + [S]
 
-        return cls(
-            control_system.input_names,
-            control_system.state_names,
-            state_vector_name,
-            S,
-            U,
-            control_system.axes,
-            control_system.time_variant,
-            rule,
-        )
+        S, U = extend(control_system)
+        varies = control_system.time_variant
+        return cls(input_names=control_system.input_names, state_names=control_system.state_names,
+                   state_vector_name=state_vector_name, S=S, U=U, axes=control_system.axes,
+                   time_variant=varies,
+                   how_to_update_matrices=follow_the_control_system if varies else None)
 
     def identify_domain(self, input_names, state_names):
-        base_domain = {name: i for i, name in enumerate(input_names)}
-        base_domain[self.state_vector_name + "0"] = len(input_names)
-        self.domain_ID = {}
-        self.state_ID = {}
+        """Positions in ``matrices``: input j at j, the initial state ``<vector>0`` after the
+        inputs; ``state_ID`` numbers the states (dynamics.py:248-258)."""
+        slots = list(input_names) + [self.state_vector_name + "0"]
+        self.domain_ID, self.state_ID = {}, {}
         for axis in self.axes:
-            for name, ID in base_domain.items():
-                self.domain_ID[name + axis] = ID
-            for i, name in enumerate(state_names):
-                self.state_ID[name + axis] = i
+            self.domain_ID.update((name + axis, slot) for slot, name in enumerate(slots))
+            self.state_ID.update((name + axis, row) for row, name in enumerate(state_names))
+
+    def _domain_lengths(self):
+        return {variable: self.matrices[slot].shape[1] for variable, slot in self.domain_ID.items()}
 
     def set_sizes(self):
-        horizon = self.matrices[-1].shape[0]
-        self.domain = {v: self.matrices[ID].shape[1] for v, ID in self.domain_ID.items()}
-        self.all_variables = dict(self.domain)
-        self.all_variables.update({state: horizon for state in self.state_ID})
+        """Domain variables are as long as their matrix has columns (actions of an input,
+        entries of x0); every state spans the horizon (dynamics.py:260-267)."""
+        samples = self.matrices[-1].shape[0]
+        self.domain = self._domain_lengths()
+        self.all_variables = {**self.domain, **dict.fromkeys(self.state_ID, samples)}
 
     def update_sizes(self):
-        if self.time_variant:
-            for variable, ID in self.domain_ID.items():
-                self.domain[variable] = self.matrices[ID].shape[1]
-            self.all_variables.update(self.domain)
+        if not self.time_variant:
+            return
+        self.domain.update(self._domain_lengths())
+        self.all_variables.update(self.domain)
 
     def _same_axis(self, a, b):
         # the reference compares the last two characters (dynamics.py:293)
@@ -222,42 +216,35 @@ class ExtendedSystem(_WithOutputs):
             self.definitions[state] = combo
 
     def update_definitions(self):
-        for variable, size in self.domain.items():
-            self.definitions[variable].matrices[0] = np.eye(size)
-        for state, sID in self.state_ID.items():
+        """Re-slices the state definitions out of the current matrices (in place: other
+        objects hold these LineCombos), then lets the outputs follow."""
+        for variable, length in self.domain.items():
+            self.definitions[variable].matrices[0] = np.eye(length)
+        for state, row in self.state_ID.items():
             combo = self.definitions[state]
-            for k, var in enumerate(combo.variables):
-                combo.matrices[k] = self.matrices[self.domain_ID[var]][..., sID]
-        for output in self.outputs:
-            self.definitions[output].update(extSyst=self)
+            combo.matrices[:] = [self.matrices[self.domain_ID[name]][..., row] for name in combo.variables]
+        for name in self.outputs:
+            self.definitions[name].update(extSyst=self)
 
     def update_matrices(self, **kargs):
         self._matrix_rule(self, **kargs)
 
     def update(self, **kargs):
-        if self.time_variant:
-            self.update_matrices(**kargs)
-            self.update_sizes()
-            self.update_definitions()
+        """One tick of a time-variant system: matrices, sizes, definitions, in that order."""
+        if not self.time_variant:
+            return
+        self.update_matrices(**kargs)
+        self.update_sizes()
+        self.update_definitions()
 
 
 class ControlSystem:
     """One-step system ``x+ = A x + B u`` with named inputs and states."""
 
-    def __init__(
-        self,
-        input_names,
-        state_names,
-        A,
-        B,
-        axes=None,
-        time_variant=False,
-        how_to_update_matrices=None,
-    ):
-        self.state_names = state_names
-        self.input_names = input_names
-        self.A = A
-        self.B = B
+    def __init__(self, input_names, state_names, A, B, axes=None, time_variant=False,
+                 how_to_update_matrices=None):
+        self.input_names, self.state_names = input_names, state_names
+        self.A, self.B = A, B
         self.axes = axes
         self.time_variant = time_variant
         self._matrix_rule = _pick_rule(how_to_update_matrices, time_variant)
@@ -270,20 +257,21 @@ class ControlSystem:
         return use.get_system_matrices(system_name)[2]
 
     @classmethod
-    def from_name(
-        cls, system_name, axes=None, time_variant=False, how_to_update_matrices=None, **kargs
-    ):
-        """A named LIP-family system, discretised exactly (dynamics.py:380-407)."""
-        input_names, state_names = use.get_system_variables(system_name)
-        get_A, get_B, parameters = use.get_system_matrices(system_name)
+    def from_name(cls, system_name, axes=None, time_variant=False, how_to_update_matrices=None,
+                  **kargs):
+        """A named LIP-family system, discretised exactly (dynamics.py:380-407).  ``kargs``
+        are the physical parameters (``tau``, ``omega``); a missing one is a ValueError
+        that lists what the system needs.  The matrix builders stay on the object
+        (``get_A``, ``get_B``) for update rules that re-evaluate them."""
+        builders = use.get_system_matrices(system_name)
         try:
-            A = get_A(**kargs)
-            B = get_B(**kargs)
-        except Exception:
-            raise ValueError("This system formulation requires: " + str(parameters))
-        self = cls(input_names, state_names, A, B, axes, time_variant, how_to_update_matrices)
-        self.get_A = get_A
-        self.get_B = get_B
-        self.parameters = kargs
-        self.system_name = system_name
-        return self
+            A, B = builders[0](**kargs), builders[1](**kargs)
+        except Exception as problem:
+            raise ValueError("the system '{}' takes the parameters {}".format(
+                system_name, builders[2])) from problem
+        inputs, states = use.get_system_variables(system_name)
+        system = cls(inputs, states, A, B, axes=axes, time_variant=time_variant,
+                     how_to_update_matrices=how_to_update_matrices)
+        system.get_A, system.get_B = builders[0], builders[1]
+        system.parameters, system.system_name = kargs, system_name
+        return system

@@ -12,6 +12,7 @@ in the reference, because it fixes the row order of G.
 import numpy as np
 
 from . import tools as use
+from ._shared import axes_list, one_matrix_per_axis, window_length
 from .params import contains_expr, is_expr
 
 
@@ -23,20 +24,12 @@ def _geometry(value, shape, as_float=False):
     return arr.astype(float) if (as_float and arr.dtype != object) else arr
 
 
-def _span(schedule):
-    return (schedule.stop - schedule.start) if schedule else None
-
-
 class Constraint:
-    def __init__(
-        self, variable, extreme, axes=None, arrow=None, center=None, L=None, schedule=None
-    ):
+    def __init__(self, variable, extreme, axes=None, arrow=None, center=None, L=None, schedule=None):
         self.variable = variable
-        self.axes = [""] if axes is None else axes
-        if not isinstance(self.axes, list):
-            raise TypeError("The axes must be a list of string")
+        self.axes = axes_list(axes, empty=False)
         self.axes_len = len(self.axes)
-        self.schedule = range(0) if schedule is None else schedule
+        self.schedule = schedule if schedule is not None else range(0)
         self.L = []
         if L is not None:
             self.arrange_L(L)
@@ -48,75 +41,59 @@ class Constraint:
     # -- sizes -------------------------------------------------------------
     @property
     def m(self):
+        """Rows of the L matrices, None without L."""
         return self.L[0].shape[0] if self.L else None
 
     @property
     def t(self):
-        return _span(self.schedule)
+        """Samples the schedule selects, None without a schedule."""
+        return window_length(self.schedule)
 
     def _geometry_rows(self):
-        return np.array([self.arrow.shape[0], self.center.shape[0], self.extreme.shape[0]])
+        return np.array([part.shape[0] for part in (self.arrow, self.center, self.extreme)])
 
     @property
     def nlines(self):
         """Number of rows this limit produces, None when it follows the size
-        of the constrained variable (restrictions.py:147-162)."""
+        of the constrained variable (restrictions.py:147-162): L decides first, then the
+        schedule, then whichever of arrow / center / extreme has more than one row."""
         if self.L:
             return self.m
         if self.schedule:
             return self.t
-        rows = self._geometry_rows()
-        many = rows[rows != 1]
-        return None if many.size == 0 else many[0]
+        several = [rows for rows in self._geometry_rows() if rows != 1]
+        return several[0] if several else None
 
     # -- set-up ------------------------------------------------------------
     def arrange_L(self, L):
-        """One matrix per axis; needs an up-to-date schedule (restrictions.py:75-90)."""
-        matrices = L if isinstance(L, list) else [L]
-        if len(matrices) == 1:
-            matrices = matrices * self.axes_len
-        elif len(matrices) not in (self.axes_len, 0):
-            self.L = matrices
-            raise IndexError(
-                "'L' must have 0, 1 or len(axes) = {} elements".format(self.axes_len)
-            )
-        self.L = matrices
-        if self.schedule and any(mat.shape[-1] != self.t for mat in matrices):
-            raise ValueError(
-                "arrays in L must have {} columns, which is given by the 'schedule'.".format(
-                    self.t
-                )
-            )
+        """One matrix per axis, checked against the CURRENT schedule
+        (restrictions.py:75-90); on a refusal the limit keeps the L it had."""
+        self.L = one_matrix_per_axis(L, self.axes_len, self.t)
 
     def initialize_geometry(self, arrow, center):
-        if arrow is not None:
-            self.arrow = _geometry(arrow, [-1, self.axes_len])
-        elif self.axes_len == 1:
-            self.arrow = np.ones(self.extreme.shape)
-        else:
-            raise ValueError(
-                "When using multiple axes, some normal direction 'arrow' must be provided"
-            )
-        if center is None:
-            self.center = np.zeros([1, self.axes_len])
-        else:
-            self.center = _geometry(center, [-1, self.axes_len])
+        """Defaults: with one axis the arrow is +1 on every row of ``extreme``; with
+        several axes a direction must be given (ValueError).  The centre defaults to the
+        origin (restrictions.py:92-112)."""
+        k = self.axes_len
+        if arrow is None and k > 1:
+            raise ValueError("a limit over {} axes needs its normal direction 'arrow'".format(k))
+        self.arrow = np.ones(self.extreme.shape) if arrow is None else _geometry(arrow, [-1, k])
+        self.center = np.zeros([1, k]) if center is None else _geometry(center, [-1, k])
 
     def check_geometry(self):
-        rows = self._geometry_rows()
-        many = rows[rows != 1]
-        if many.size and np.any(many != many[0]):
+        """arrow / center / extreme have one row or a common number of rows (ValueError);
+        arrow and center have one column per axis (IndexError) -- restrictions.py:114-133."""
+        counts = self._geometry_rows()
+        several = set(int(c) for c in counts if c != 1)
+        if len(several) > 1:
             raise ValueError(
-                "The number of rows in 'arrow', 'center' and 'extreme' must be equal "
-                "or 1, but they are {} respectively".format(rows)
-            )
+                "'arrow', 'center' and 'extreme' have {} rows: apart from single rows they "
+                "must agree".format(list(counts)))
         if self.axes_len > 1:
-            cols = np.array([self.arrow.shape[1], self.center.shape[1]])
-            if np.any(cols != self.axes_len):
+            widths = [self.arrow.shape[1], self.center.shape[1]]
+            if any(w != self.axes_len for w in widths):
                 raise IndexError(
-                    "'arrow' and 'center' have {} columns but they must have {}, "
-                    "one per axis.".format(cols, self.axes_len)
-                )
+                    "'arrow' / 'center' have {} columns for {} axes".format(widths, self.axes_len))
 
     def normalize(self):
         """Makes every extreme non-negative by flipping the row's arrow
@@ -156,26 +133,30 @@ class Constraint:
         return columns
 
     def bound(self):
-        """``extreme + sum_a arrow_a * center_a``  (restrictions.py:198-199)."""
-        return self.extreme + np.sum(self.arrow * self.center, axis=1).reshape([-1, 1])
+        """Right-hand side in task space: ``extreme + arrow . center`` row by row, a column
+        (restrictions.py:198-199)."""
+        offset = (self.arrow * self.center).sum(axis=1)
+        return self.extreme + offset.reshape([-1, 1])
 
     def update(self, extreme=None, arrow=None, center=None, L=None, schedule=None):
-        self._stamp = getattr(self, "_stamp", 0) + 1  # invalidates compiled plans
+        """Replaces the given fields (restrictions.py:201-219).  The schedule goes first so
+        that a new L is checked against it; new geometry is re-checked, and re-normalised
+        when the extreme or the arrow changed."""
+        self._stamp = getattr(self, "_stamp", 0) + 1  # compiled plans look at this
         if schedule is not None:
             self.schedule = schedule
         if L is not None:
             self.arrange_L(L)
-        if extreme is not None:
-            self.extreme = _geometry(extreme, [-1, 1])
-        if arrow is not None:
-            self.arrow = _geometry(arrow, [-1, self.axes_len])
-        if center is not None:
-            self.center = _geometry(center, [-1, self.axes_len])
-        if extreme is not None or arrow is not None:
+        k = self.axes_len
+        fresh = {"extreme": (extreme, [-1, 1]), "arrow": (arrow, [-1, k]), "center": (center, [-1, k])}
+        changed = [name for name, (value, _) in fresh.items() if value is not None]
+        for name in changed:
+            value, shape = fresh[name]
+            setattr(self, name, _geometry(value, shape))
+        if changed:
             self.check_geometry()
+        if "extreme" in changed or "arrow" in changed:
             self.normalize()
-        elif center is not None:
-            self.check_geometry()
 
     # -- diagnostics (restrictions.py:221-257) -----------------------------
     def SS_to_TS(self, ss_point):
@@ -216,68 +197,65 @@ class Constraint:
 
 
 class Box:
-    """A convex polygon / polyhedron expressed as one Constraint per facet."""
+    """A convex polygon / polyhedron expressed as one Constraint per facet.
+
+    ``ts_*`` describe the box in task space (the space of ``[v_x, v_y, ...]``), ``ss_*`` in
+    state space (consecutive samples of one variable); which of them are filled depends on
+    the constructor used.  The attribute names, ``ss_dimention`` included, are the
+    reference's (restrictions.py:287-311)."""
+
+    # what a box looks like before a constructor has described it
+    _BLANK = dict(ts_orientation=list, ss_orientation=list, schedule=lambda: range(0),
+                  safety_margin=int, ss_dimention=int, ts_dimention=int, axes=lambda: [""],
+                  scale_factor=lambda: np.array([1.0]))
 
     def __init__(self, time_variant=None, how_to_update=None):
         self.constraints = []
-        self.ts_vertices = np.array([])
-        self.ss_vertices = np.array([])
-        self.ts_center = np.array([])
-        self.ts_orientation = []
-        self.ss_center = np.array([])
-        self.ss_orientation = []
-        self.scale_factor = np.array([1.0])
-        self.schedule = range(0)
-        self.safety_margin = 0
-        self.axes = [""]
-        self.ss_dimention = 0
-        self.ts_dimention = 0
+        for name in ("ts_vertices", "ss_vertices", "ts_center", "ss_center"):
+            setattr(self, name, np.array([]))
+        for name, make in self._BLANK.items():
+            setattr(self, name, make())
         self.time_variant = time_variant
-        self._rule = how_to_update if (how_to_update and time_variant) else use.do_not_update
+        self._rule = how_to_update if (time_variant and how_to_update is not None) else use.do_not_update
+
+    def _facets(self, limits, schedule, **description):
+        """Takes over the facet limits and the description of the box they form."""
+        self.constraints.extend(limits)
+        self.axes = self.constraints[0].axes
+        self.schedule = schedule
+        for name, value in description.items():
+            setattr(self, name, value)
+        return self
 
     @classmethod
-    def task_space(
-        cls, variable, vertices, axes=None, L=None, schedule=None, time_variant=None, how_to_update=None
-    ):
-        """Box on the task-space variable ``[v_x, v_y, ...]`` (restrictions.py:313-340)."""
-        box = cls(time_variant, how_to_update)
-        arrows, extremes, center = box_boundaries(vertices)
-        for arrow, extreme in zip(arrows, extremes):
-            box.constraints.append(Constraint(variable, extreme, axes, arrow, center, L, schedule))
+    def task_space(cls, variable, vertices, axes=None, L=None, schedule=None, time_variant=None,
+                   how_to_update=None):
+        """Box around the task-space variable ``[v_x, v_y, ...]``: one limit per facet of the
+        hull of ``vertices`` (one vertex per row), all sharing the centroid as centre
+        (restrictions.py:313-340)."""
+        normals, offsets, centroid = box_boundaries(vertices)
+        limits = [Constraint(variable, offset, axes, normal, centroid, L, schedule)
+                  for normal, offset in zip(normals, offsets)]
         dim = vertices.shape[1]
-        box.ss_dimention = box.ts_dimention = dim
-        box.axes = box.constraints[0].axes
-        box.ts_center = center
-        box.ss_center = np.zeros(center.shape)
-        box.ts_orientation = [np.eye(dim)]
-        box.ss_orientation = [np.eye(dim)]
-        box.ts_vertices = vertices
-        box.schedule = schedule
-        return box
+        return cls(time_variant, how_to_update)._facets(
+            limits, schedule, ts_vertices=vertices, ts_center=centroid,
+            ss_center=np.zeros(centroid.shape), ts_dimention=dim, ss_dimention=dim,
+            ts_orientation=[np.eye(dim)], ss_orientation=[np.eye(dim)])
 
     @classmethod
-    def state_space(
-        cls, variable, vertices, axes=None, schedule=None, time_variant=None, how_to_update=None
-    ):
-        """Box on consecutive samples of one variable: every facet normal is
-        used as an ``L`` row (restrictions.py:342-378)."""
-        box = cls(time_variant, how_to_update)
-        normals, extremes, centroid = box_boundaries(vertices)
-        offsets = np.sum(normals * centroid, axis=1).reshape([-1, 1])
-        for normal, extreme, offset in zip(normals, extremes, offsets):
-            box.constraints.append(
-                Constraint(variable, extreme, axes=axes, center=offset, L=normal, schedule=schedule)
-            )
-        box.ss_dimention = vertices.shape[1]
-        box.ts_dimention = 1
-        box.axes = box.constraints[0].axes
-        box.ss_center = centroid.reshape([-1, 1])
-        box.ts_center = 0
-        box.ss_orientation = [np.eye(box.ss_dimention)]
-        box.ts_orientation = [1]
-        box.ss_vertices = vertices
-        box.schedule = schedule
-        return box
+    def state_space(cls, variable, vertices, axes=None, schedule=None, time_variant=None,
+                    how_to_update=None):
+        """Box in the space of consecutive samples of ONE variable: facet f becomes the
+        scalar limit ``normal_f . v[schedule] < ...`` with the normal as a one-row ``L``
+        and the centroid's projection on it as centre (restrictions.py:342-378)."""
+        normals, offsets, centroid = box_boundaries(vertices)
+        projections = (normals * centroid).sum(axis=1).reshape([-1, 1])
+        limits = [Constraint(variable, offset, axes=axes, center=projection, L=normal, schedule=schedule)
+                  for normal, offset, projection in zip(normals, offsets, projections)]
+        dim = vertices.shape[1]
+        return cls(time_variant, how_to_update)._facets(
+            limits, schedule, ss_vertices=vertices, ss_center=centroid.reshape([-1, 1]), ts_center=0,
+            ss_dimention=dim, ts_dimention=1, ss_orientation=[np.eye(dim)], ts_orientation=[1])
 
     # -- transforms (restrictions.py:380-486) -----------------------------
     def _check_ss_shape(self, value):
