@@ -5,10 +5,14 @@
 // and gecko::tools::extend_matrices (cpp/src/tools.cc:83-144).  One thread
 // block per system keeps the running block [A^(k+1) | A^k B] in shared memory
 // and left-multiplies it by A once per horizon step -- the association order
-// of the reference's recursion (tools.py:23-29) -- writing the COMPACT impulse
-// response (Phi, Gam).  A second, purely streaming kernel expands it into the
-// dense reference layouts S (N,n,n) and U (m,N,N,n): the lower-block-Toeplitz
-// structure is index arithmetic, so that kernel is bound by the HBM write.
+// of the reference's recursion (tools.py:23-29).  The dense reference layouts
+// S (N,n,n) and U (m,N,N,n) are written by the same block: every row of U is a
+// window of a shared-memory array and leaves as one TMA bulk copy
+// (extend_fused_kernel).  The compact impulse response (Phi, Gam) and a streaming
+// expansion of it remain for the plan compiler and for shapes the bulk copies do
+// not fit.
+#include <cstdint>
+
 #include "mpci_common.cuh"
 
 namespace {
@@ -88,6 +92,125 @@ expand_U_kernel(const double* __restrict__ Gam, double* __restrict__ U, long row
   }
 }
 
+// ---------------------------------------------------------------------------
+// The dense layouts in one pass.  Row (j, k) of U -- N*n contiguous doubles --
+// is  [Gam_k[:, j], Gam_{k-1}[:, j], ..., Gam_0[:, j], 0, ..., 0]:  with
+//     Z_j[y*n + i] = Gam_{N-1-y}[i][j]  (y < N),   0  (N <= y < 2N)
+// in shared memory it is the window Z_j[(N-1-k)*n ...] of length N*n, so the block
+// that ran the recursion hands every row to the TMA engine as ONE bulk copy
+// (cp.async.bulk shared -> global); a second copy of Z shifted by one element keeps
+// the source 16-byte aligned when (N-1-k)*n is odd.  S leaves with plain stores while
+// the recursion runs (it is n / (m N) of the bytes).  Needs N*n even and a 16-byte
+// aligned U; other shapes take the three-kernel path above.
+// ---------------------------------------------------------------------------
+constexpr int kFusedThreads = 128;
+
+__device__ __forceinline__ void bulk_row(double* dst, const double* src_smem, unsigned bytes) {
+  const unsigned src = (unsigned)__cvta_generic_to_shared(src_smem);
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n"
+               :: "l"(dst), "r"(src), "r"(bytes) : "memory");
+}
+
+__host__ __device__ inline size_t fused_smem_doubles(int n, int m, int N, bool shifted) {
+  const size_t mats = ((size_t)n * n + 2 * (size_t)n * (n + m) + 1) & ~(size_t)1;
+  return mats + (size_t)m * 2 * N * n * (shifted ? 2 : 1);
+}
+
+__global__ void __launch_bounds__(kFusedThreads)
+extend_fused_kernel(const double* __restrict__ A, const double* __restrict__ B,
+                    double* __restrict__ S, double* __restrict__ U, long batch, int n, int m, int N,
+                    int shifted) {
+  extern __shared__ double sm[];
+  const int w = n + m, tid = threadIdx.x;
+  const int zld = 2 * N * n, row_len = N * n;
+  double* As = sm;
+  double* cur = As + n * n;
+  double* nxt = cur + n * w;
+  double* Z = sm + (((size_t)n * n + 2 * (size_t)n * w + 1) & ~(size_t)1);  // [m][zld]
+  double* Z1 = Z + (size_t)m * zld;                                        // Z1[x] = Z[x + 1]
+  // the zero halves are written once; the recursion only touches [0, N*n)
+  for (int e = tid; e < m * zld; e += blockDim.x) {
+    const int x = e % zld;
+    if (x >= row_len) Z[e] = 0.0;
+    if (shifted && x >= row_len - 1) Z1[e] = 0.0;
+  }
+  for (long b = blockIdx.x; b < batch; b += gridDim.x) {
+    // the rows of the previous system have left Z (bulk groups are per thread)
+    asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+    __syncthreads();
+    const double* Ab = A + b * n * n;
+    const double* Bb = B + b * n * m;
+    for (int e = tid; e < n * n; e += blockDim.x) As[e] = Ab[e];
+    for (int e = tid; e < n * w; e += blockDim.x) {
+      const int i = e / w, c = e - i * w;
+      cur[e] = (c < n) ? Ab[i * n + c] : Bb[i * m + (c - n)];
+    }
+    __syncthreads();
+    double* Sb = S ? S + b * (long)N * n * n : nullptr;
+    for (int k = 0; k < N; ++k) {
+      for (int e = tid; e < n * w; e += blockDim.x) {
+        const int i = e / w, c = e - i * w;
+        const double v = cur[e];
+        if (c < n) {
+          if (Sb) Sb[((long)k * n + c) * n + i] = v;  // S[k][c][i] = (A^(k+1))[i][c]
+        } else {
+          const int x = (c - n) * zld + (N - 1 - k) * n + i;
+          Z[x] = v;
+          if (shifted && ((N - 1 - k) * n + i) > 0) Z1[x - 1] = v;
+        }
+        if (k + 1 < N) {  // next = A @ cur  (tools.py:24-29)
+          double acc = 0.0;
+          for (int l = 0; l < n; ++l) acc += As[i * n + l] * cur[l * w + c];
+          nxt[e] = acc;
+        }
+      }
+      __syncthreads();
+      double* t = cur; cur = nxt; nxt = t;
+    }
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    __syncthreads();
+    double* Ub = U + b * (long)m * N * row_len;
+    for (int r = tid; r < m * N; r += blockDim.x) {
+      const int j = r / N, k = r - j * N;
+      const int start = (N - 1 - k) * n;
+      const double* src = (start & 1) ? Z1 + (size_t)j * zld + (start - 1) : Z + (size_t)j * zld + start;
+      bulk_row(Ub + (long)r * row_len, src, (unsigned)row_len * 8u);
+    }
+    asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+  }
+  asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
+}
+
+// *launched stays false when the shape is not eligible (the caller then takes the
+// three-kernel path); the return value is the usual status.
+int launch_fused(const double* A, const double* B, double* S, double* U, int batch, int n, int m,
+                 int N, cudaStream_t st, bool* launched) {
+  *launched = false;
+  if (!U || ((long)N * n) % 2 != 0 || (reinterpret_cast<uintptr_t>(U) & 15) != 0) return 0;
+  const bool shifted = (n % 2) != 0;
+  const size_t smem = sizeof(double) * fused_smem_doubles(n, m, N, shifted);
+  if (smem > 227 * 1024) return 0;
+  if (smem > 48 * 1024)
+    MPCI_CUDA(cudaFuncSetAttribute(extend_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   (int)smem));
+  int dev = 0, sms = 148, per_sm = 1;
+  MPCI_CUDA(cudaGetDevice(&dev));
+  MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  // small systems: one warp per block, so that up to 32 systems are in flight on an SM
+  // (measured at n=3, m=1: N=100 74 -> 81 %, N=24 36 -> 53 % of the HBM peak); the larger
+  // ones need the threads for the recursion and the row copies (n=12, m=4, N=50: 79 %
+  // with 128 threads, 62 % with 32)
+  const int threads = (n * (n + m) <= 32 && m * N <= 128) ? 32 : kFusedThreads;
+  MPCI_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, extend_fused_kernel, threads, smem));
+  if (per_sm < 1) return 0;
+  const long resident = (long)sms * per_sm;
+  const unsigned blocks = (unsigned)(batch < resident ? batch : resident);
+  extend_fused_kernel<<<blocks, threads, smem, st>>>(A, B, S, U, batch, n, m, N, shifted ? 1 : 0);
+  MPCI_LAUNCH_CHECK("extend_fused_kernel");
+  *launched = true;
+  return 0;
+}
+
 int check_sizes(int batch, int n, int m, int N) {
   if (batch < 0 || n < 1 || m < 1 || N < 1)
     return mpci::fail(-1, "extend_matrices: sizes must be positive (batch=%d n=%d m=%d N=%d)",
@@ -122,6 +245,11 @@ extern "C" int mpci_extend_matrices(const double* A, const double* B, double* S,
   if (!A || !B) return mpci::fail(-3, "extend_matrices: A and B must not be NULL");
   if (batch == 0) return 0;
   cudaStream_t st = mpci::as_stream(stream);
+  {
+    bool launched = false;
+    const int rc = launch_fused(A, B, S, U, batch, n, m, N, st, &launched);
+    if (rc != 0 || launched) return rc;
+  }
   double* scratch = nullptr;
   const size_t phi_elems = (size_t)batch * N * n * n, gam_elems = (size_t)batch * N * n * m;
   MPCI_CUDA(cudaMallocAsync(&scratch, sizeof(double) * (phi_elems + gam_elems), st));

@@ -81,3 +81,38 @@ def test_per_instance_dynamics_outputs_stay_inside(dev, name, hessian, shift):
     out.check()
     got = tuple(x.cpu().numpy() for x in (out.G, out.h, out.P, out.q))
     cases.assert_qp_close(got, (g["A"], g["h"], g["Q"], g["q"]))
+
+
+@pytest.mark.parametrize("n,m,N,batch", [(3, 1, 10, 5), (3, 1, 9, 4), (4, 2, 7, 300), (5, 3, 12, 7), (1, 1, 2, 3)])
+def test_prediction_matrices_stay_inside(dev, n, m, N, batch):
+    """K1 in the dense layouts: fused kernel with TMA row copies (N n even; shifted
+    source for odd n) and the three-kernel path (N n odd), outputs between guard zones,
+    against the oracle."""
+    import ctypes
+
+    import torch
+    from oracle import qp_oracle as orc
+
+    rng = np.random.default_rng(n * 10 + N)
+    A = np.eye(n) + 0.1 * rng.normal(size=[batch, n, n])
+    B = rng.normal(size=[batch, n, m])
+    s_len, u_len = batch * N * n * n, batch * m * N * N * n
+    buf = torch.full([3 * GUARD + s_len + (s_len & 1) + u_len + 2], SENTINEL, dtype=torch.float64, device="cuda")
+    s0 = GUARD
+    u0 = s0 + s_len + (s_len & 1) + GUARD
+    dA, dB = torch.from_numpy(A).cuda(), torch.from_numpy(B).cuda()
+    ptr = lambda t, off=0: ctypes.c_void_p(t.data_ptr() + 8 * off)
+    dev.check(dev.lib().mpci_extend_matrices(ptr(dA), ptr(dB), ptr(buf, s0), ptr(buf, u0), batch, n, m, N,
+                                             ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    torch.cuda.synchronize()
+    host = buf.cpu().numpy()
+    inside = np.zeros(host.shape, dtype=bool)
+    inside[s0:s0 + s_len] = True
+    inside[u0:u0 + u_len] = True
+    assert (host[~inside] == SENTINEL).all() and not (host[inside] == SENTINEL).any()
+    S = host[s0:s0 + s_len].reshape(batch, N, n, n)
+    U = host[u0:u0 + u_len].reshape(batch, m, N, N, n)
+    for b in sorted({0, batch // 2, batch - 1}):
+        So, Uo = orc.extend_matrices(N, A[b], B[b])
+        assert cases.rel_err(S[b], So) < 1e-12 and cases.rel_err(U[b], np.stack(Uo)) < 1e-12
+        assert (U[b][:, np.triu_indices(N, 1)[0], np.triu_indices(N, 1)[1]] == 0.0).all()  # exact zeros
