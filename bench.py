@@ -10,6 +10,7 @@ Prints ONE JSON line (rank 0).  Under torchrun every rank drives its own GPU on
 its own shard of the logical batch; there is no collective on the data path.
 """
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -222,6 +223,9 @@ def run_own(args):
     if rank == 0:
         sampler.start()
     barrier()
+    # the library's own kernel timers: CUDA events around each launch, on the stream it
+    # runs on, inside the timed region (the roofline figure is read from these)
+    device.check(lib.mpci_plan_set_timing(handle, 1))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
@@ -229,6 +233,11 @@ def run_own(args):
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    in_step = (ctypes.c_double * 3)()
+    pieces = ctypes.c_long(0)
+    device.check(lib.mpci_plan_read_timing(handle, ctypes.byref(in_step), ctypes.byref(pieces)))
+    device.check(lib.mpci_plan_set_timing(handle, 0))
+    in_step = [v / args.steps for v in in_step]
     clocks = sampler.stop() if rank == 0 else None
     ms = sharding.max_over_ranks(ms, world, "cuda")
 
@@ -303,7 +312,7 @@ def run_own(args):
     result = None
     if rank == 0:
         result = dict(B=B, world=world, ms=ms, t_P=t_P, t_G=t_G, t_qh=t_qh, nv=nv, ng=ng, nc=nc,
-                      clocks=clocks, launches=device.lib().mpci_assemble_launches(handle),
+                      in_step=in_step, clocks=clocks, launches=device.lib().mpci_assemble_launches(handle),
                       n_scalars=scalars_h.shape[1], t_csc=t_csc, csc_bytes=csc_bytes,
                       nnz=(pP.nnz, pG.nnz), lti=lti_lines, single=single, t_shared=t_shared,
                       shared_terms=shared_terms)
@@ -454,7 +463,9 @@ def main():
     bytes_G = 8.0 * nc * nv * B
     bytes_P = 8.0 * nv * nv * B
     bytes_all = 8.0 * (nv * nv + nv + nc * nv + nc) * B
-    achieved = bytes_G / (res["t_G"] * 1e-3) / 1e9
+    # dominant kernel: average launch duration over the timed region (mpci_plan_read_timing)
+    t_G_step = res["in_step"][1]
+    achieved = bytes_G / (t_G_step * 1e-3) / 1e9
     line = {
         "metric": METRIC, "value": value, "unit": "QPs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": res["ms"] / args.steps, "higher_is_better": True,
@@ -468,15 +479,23 @@ def main():
             "traffic_note": "ncu dram bytes per instance (batch 8192 capture) x this batch",
             "peak_source": peak_kind,
             "algorithmic_bytes_per_launch": bytes_G,
+            "ms_per_launch": t_G_step,
+            "timing": "CUDA events around the launch on its stream, inside the timed region "
+                      "([q;h] runs beside it on a side stream)",
+            "note": "peak = a device copy (read + write); a write-only stream can exceed it",
         },
-        "kernels_ms": {"P_stream": res["t_P"], "G_stream": res["t_G"], "qh": res["t_qh"]},
+        "kernels_ms_in_step": {"P_stream": res["in_step"][0], "G_stream": res["in_step"][1],
+                               "qh_side_stream": res["in_step"][2]},
+        "kernels_ms": {"P_stream": res["t_P"], "G_stream": res["t_G"], "qh": res["t_qh"],
+                       "note": "each kernel launched alone, after the timed region"},
         "csc_layout": {"value": B * world / (res["t_csc"] * 1e-3), "unit": "QPs/s",
                        "ms_per_step": res["t_csc"], "bytes_per_qp": res["csc_bytes"],
                        "nnz_P": res["nnz"][0], "nnz_G": res["nnz"][1],
                        "gbs": res["csc_bytes"] * B / res["t_csc"] / 1e6,
                        "note": "same step writing only the CSC values of P and G (solver "
                                "hand-off layout); not the headline"},
-        "kernels_gbs": {"P_stream": bytes_P / res["t_P"] / 1e6, "G_stream": achieved,
+        "kernels_gbs": {"P_stream": bytes_P / res["t_P"] / 1e6,
+                        "G_stream": bytes_G / res["t_G"] / 1e6,
                         "step_all_outputs": bytes_all / (res["ms"] / args.steps) / 1e6},
     }
     if res.get("t_shared"):

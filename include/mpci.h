@@ -162,6 +162,17 @@ int mpci_assemble_compact_host(mpci_plan* plan, const double* scalars_host,
 /* Number of kernel launches one mpci_assemble call issues for this plan.    */
 int mpci_assemble_launches(const mpci_plan* plan);
 
+/* Kernel timers (measurement only; the reference has no counterpart).  While
+ * on, every mpci_assemble / mpci_assemble_compact call on this plan brackets
+ * its launches with CUDA events on the streams they run on, so that a bench
+ * reads kernel durations from INSIDE its timed region.  set_timing(on) clears
+ * what was collected.  read_timing waits for the recorded events and returns
+ * the summed durations in ms: ms[0] P stream, ms[1] G stream, ms[2] [q;h]
+ * (side stream, concurrent with the other two); *pieces = number of
+ * (call, batch piece) records summed.                                        */
+int mpci_plan_set_timing(mpci_plan* plan, int on);
+int mpci_plan_read_timing(mpci_plan* plan, double ms[3], long* pieces);
+
 /* ---- per-instance dynamics: the condensed LTI problem ---------------------
  * Mode B of DESIGN.md: every instance b has its own x+ = A_b x + B_b u, so the
  * prediction matrices (tools.py:14-33), the Hessian contraction

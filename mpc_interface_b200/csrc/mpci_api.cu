@@ -203,6 +203,7 @@ extern "C" int mpci_plan_destroy(mpci_plan* p) {
   if (p->fork) cudaEventDestroy(p->fork);
   if (p->join) cudaEventDestroy(p->join);
   if (p->dev_tables) cudaFree(p->dev_tables);
+  for (cudaEvent_t e : p->timers) cudaEventDestroy(e);
   delete p;
   return 0;
 }
@@ -210,6 +211,31 @@ extern "C" int mpci_plan_destroy(mpci_plan* p) {
 extern "C" int mpci_assemble_launches(const mpci_plan* p) {
   if (!p) return 0;
   return (p->P.n_elems ? 1 : 0) + (p->G.n_elems ? 1 : 0) + ((p->nv + p->nc) ? 1 : 0);
+}
+
+extern "C" int mpci_plan_set_timing(mpci_plan* p, int on) {
+  if (!p) return mpci::fail(-3, "plan_set_timing: NULL plan");
+  for (cudaEvent_t e : p->timers) cudaEventDestroy(e);
+  p->timers.clear();
+  p->timing = on != 0;
+  return 0;
+}
+
+extern "C" int mpci_plan_read_timing(mpci_plan* p, double ms[3], long* pieces) {
+  if (!p || !ms) return mpci::fail(-3, "plan_read_timing: NULL plan or output");
+  ms[0] = ms[1] = ms[2] = 0.0;
+  const long n = static_cast<long>(p->timers.size() / 6);
+  for (long c = 0; c < n; ++c) {
+    for (int k = 0; k < 3; ++k) {
+      cudaEvent_t a = p->timers[6 * c + 2 * k], b = p->timers[6 * c + 2 * k + 1];
+      MPCI_CUDA(cudaEventSynchronize(b));
+      float t = 0.f;
+      MPCI_CUDA(cudaEventElapsedTime(&t, a, b));
+      ms[k] += t;
+    }
+  }
+  if (pieces) *pieces = n;
+  return 0;
 }
 
 namespace {
@@ -274,11 +300,24 @@ int assemble_with(const mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::St
   for (long b0 = 0; b0 < batch; b0 += piece) {
     const long nb = (batch - b0 < piece) ? batch - b0 : piece;
     const double* s = scalars + b0 * p->n_scalars;
+    cudaEvent_t* ev = nullptr;  // P begin/end, G begin/end, [q;h] begin/end
+    if (p->timing) {
+      const size_t at = p->timers.size();
+      p->timers.resize(at + 6);
+      for (int i = 0; i < 6; ++i) MPCI_CUDA(cudaEventCreate(&p->timers[at + i]));
+      ev = &p->timers[at];
+    }
+    if (ev) MPCI_CUDA(cudaEventRecord(ev[4], qh_stream));
     int rc = mpci::launch_qh(p->Y, s, given ? given + b0 * p->ng : nullptr,
                              q ? q + b0 * p->nv : nullptr, h ? h + b0 * p->nc : nullptr, nb,
                              qh_stream);
+    if (ev) MPCI_CUDA(cudaEventRecord(ev[5], qh_stream));
+    if (ev) MPCI_CUDA(cudaEventRecord(ev[0], st));
     if (!rc && P) rc = mpci::launch_stream(Pa, s, p->n_scalars, P + b0 * Pa.n_elems, nb, st);
+    if (ev) MPCI_CUDA(cudaEventRecord(ev[1], st));
+    if (ev) MPCI_CUDA(cudaEventRecord(ev[2], st));
     if (!rc && G) rc = mpci::launch_stream(Ga, s, p->n_scalars, G + b0 * Ga.n_elems, nb, st);
+    if (ev) MPCI_CUDA(cudaEventRecord(ev[3], st));
     if (rc) return rc;
   }
   if (overlap) {

@@ -71,4 +71,9 @@ struct mpci_plan {
   // (HBM bound) P / G streams: a side stream forked from the caller's stream
   mutable cudaStream_t side;
   mutable cudaEvent_t fork, join;
+  // mpci_plan_set_timing: event pairs around the three launches of every call
+  // (P stream, G stream, [q;h]) so that a bench reads kernel durations measured
+  // INSIDE its timed region; six events per call and piece, in call order
+  mutable bool timing;
+  mutable std::vector<cudaEvent_t> timers;
 };

@@ -81,6 +81,11 @@ _SIGNATURES = {
         [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_long],
     ),
     "mpci_assemble_launches": (ctypes.c_int, [ctypes.c_void_p]),
+    "mpci_plan_set_timing": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "mpci_plan_read_timing": (
+        ctypes.c_int,
+        [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double * 3), ctypes.POINTER(ctypes.c_long)],
+    ),
     "mpci_goal_distance": (
         ctypes.c_int,
         [_c_double_p, _c_double_p, ctypes.c_long, ctypes.c_int, ctypes.c_int, _c_double_p,

@@ -116,3 +116,27 @@ def test_prediction_matrices_stay_inside(dev, n, m, N, batch):
         So, Uo = orc.extend_matrices(N, A[b], B[b])
         assert cases.rel_err(S[b], So) < 1e-12 and cases.rel_err(U[b], np.stack(Uo)) < 1e-12
         assert (U[b][:, np.triu_indices(N, 1)[0], np.triu_indices(N, 1)[1]] == 0.0).all()  # exact zeros
+
+
+def test_kernel_timers_inside_a_call(dev):
+    """mpci_plan_set_timing / mpci_plan_read_timing: one record of three positive
+    durations per call while on, nothing collected while off, results unchanged."""
+    import ctypes
+
+    g = cases.golden("random_forms")
+    form, given, params, ref = cases.random_form(g, 0)
+    plan = form._compiled()
+    handle = form._ops().device_plan(plan).handle
+    lib = dev.lib()
+    ms, pieces = (ctypes.c_double * 3)(), ctypes.c_long(-1)
+    dev.check(lib.mpci_plan_set_timing(handle, 1))
+    for _ in range(3):
+        out = form.generate_all_qp_matrices_batched(given, params)
+    dev.check(lib.mpci_plan_read_timing(handle, ctypes.byref(ms), ctypes.byref(pieces)))
+    assert pieces.value == 3
+    assert all(0.0 <= t < 1e3 for t in ms) and sum(ms) > 0.0
+    dev.check(lib.mpci_plan_set_timing(handle, 0))
+    form.generate_all_qp_matrices_batched(given, params)
+    dev.check(lib.mpci_plan_read_timing(handle, ctypes.byref(ms), ctypes.byref(pieces)))
+    assert pieces.value == 0 and list(ms) == [0.0, 0.0, 0.0]
+    cases.assert_qp_close((out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy()), ref)
