@@ -414,6 +414,22 @@ class Formulation:
             return values
         return values.reshape(batch, len(names), pplan.rows[0]).transpose(1, 2)
 
+    def preview_all_batched(self, given, optim, names=None, params=None):
+        """Batched form of the example loop's ``preview_all`` (biped_mpc_loop.py:62-65):
+        ``{name: CUDA tensor [B, rows]}`` for every definition (or for ``names``),
+        all of them from ONE launch of the sparse-row kernel (the variables may have
+        different numbers of rows)."""
+        names = list(self.definitions) if names is None else list(names)
+        compiled, pplan = self._preview_plan(names)
+        gz, batch = self._given_optim(given, optim)
+        scalars = compiled.slots.evaluate(params or {}, batch)
+        values = self._ops().preview(pplan, scalars, gz, batch)
+        out, at = {}, 0
+        for name, rows in zip(names, pplan.rows):
+            out[name] = values[:, at : at + rows]
+            at += rows
+        return out
+
     def goal_distance_batched(self, given, optim, goal_name, params=None):
         """Batched ``goal_distance`` (body.py:221-229): squared distance to the aim
         of one goal for every instance; a CUDA tensor [B]."""

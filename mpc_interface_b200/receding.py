@@ -65,3 +65,57 @@ class StructureBuckets:
             sub = {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
             out.append((k, idx, form, form.generate_all_qp_matrices_batched(given, sub, layout=layout)))
         return out
+
+
+def count_steps(step_times, step_count, step_samples):
+    """The example loop's ``count_steps`` (biped_mpc_loop.py:41-45) for a batch, integer
+    work on the host: step_times int [B, n_steps], step_count int [B].  Every
+    instance's times go down by one; where the first one reaches -1 the step has
+    been taken: the times move on by ``step_samples`` and the count by one.
+    Returns new arrays (the inputs are not modified)."""
+    times = np.asarray(step_times).astype(np.int64) - 1
+    count = np.asarray(step_count).astype(np.int64).copy()
+    landed = times[:, 0] == -1
+    times[landed] += step_samples
+    count[landed] += 1
+    return times, count
+
+
+def advance_collector(form, given, optim, take, params=None, collector=None):
+    """The example loop's ``update_given_collector`` (biped_mpc_loop.py:81-88) for a batch:
+    the initial state of the next tick is read off the previewed horizon.
+
+    take : {dynamics name: horizon row}; for every state of that ``ExtendedSystem``
+           entry ``state_ID[state]`` of its ``<state_vector_name>0<axis>`` given
+           variable becomes row ``take[...]`` of the state's preview (the example takes
+           row 0 of the LIP states and row 1 of the step positions).
+
+    The previews of all those states come from one kernel launch
+    (``Formulation.preview_all_batched``).  Returns ``{given variable: CUDA tensor
+    [B, size]}``; entries of ``collector`` (``{name: [B, size]}``) that are not
+    produced here -- the bias of the example, which the loop resets itself -- are
+    passed through, moved to the device."""
+    ops = form._ops()
+    states = []
+    for name, row in take.items():
+        dyn = form.dynamics[name]
+        for state, ident in dyn.state_ID.items():
+            if not 0 <= row < dyn.all_variables[state]:
+                raise IndexError("row {} is outside the horizon of {}".format(row, state))
+            states.append((state, dyn.state_vector_name + "0" + state[-2:], ident, row))
+    motion = form.preview_all_batched(given, optim, [s[0] for s in states], params)
+    batch = next(iter(motion.values())).shape[0] if motion else 0
+    out = {}
+    for name, value in (collector or {}).items():
+        out[name] = ops._to_device(value).reshape(batch, -1)
+    fresh = set()
+    for state, variable, ident, row in states:
+        if variable not in fresh:
+            # a copy: the caller's collector is not written to
+            size = form.domain[variable]
+            base = out.get(variable)
+            out[variable] = (ops.torch.zeros([batch, size], dtype=ops.torch.float64, device=ops.device)
+                             if base is None else base.clone())
+            fresh.add(variable)
+        out[variable][:, ident] = motion[state][:, row]
+    return out

@@ -68,3 +68,52 @@ def test_structure_buckets_against_oracle(N):
     # a second tick with the same phases reuses the compiled structures
     buckets.assemble(kargs, vals, params)
     assert len(buckets) == seen
+
+
+def test_preview_all_and_advance_collector():
+    """The rest of the example's tick (biped_mpc_loop.py:62-65, :81-92) for a batch:
+    every definition previewed in one launch, the next initial state read off
+    the horizon (row 0 of the LIP states, row 1 of the step positions), the
+    bias passed through; against the oracle's preview matrices and the loop's
+    own per-instance assignments."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+    from mpc_interface_b200.examples.biped import default_configuration, formulate_biped
+    from mpc_interface_b200.receding import advance_collector
+
+    N, batch = 24, 45
+    form = formulate_biped(default_configuration(N), omega=Param("omega"),
+                           target_vel=[Param("vel_x"), Param("vel_y")])
+    vals = synthetic.biped_inputs(11, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    optim = np.random.default_rng(4).normal(size=[batch, form.optim_len])
+    motion = form.preview_all_batched(given, optim, params=params)
+    assert list(motion) == list(form.definitions)
+    collector = {name: vals[name] for name in form.given_ID}
+    nxt = advance_collector(form, given, optim, {"LIP": 0, "steps": 1}, params, collector)
+    assert set(nxt) == set(form.given_ID)
+    for b in (0, 17, 32, batch - 1):
+        one = {k: float(v[b]) for k, v in params.items()}
+        PM = orc.preview_matrices(form, one)
+        g, z = given[b][:, None], optim[b][:, None]
+        ref = {name: Mg @ g + Mo @ z for name, (Mg, Mo) in PM.items()}
+        for name, value in motion.items():
+            assert tuple(value.shape) == (batch, ref[name].shape[0])
+            assert cases.rel_err(value[b].cpu().numpy(), ref[name][:, 0]) <= cases.TOL, name
+        # update_given_collector, restated on the reference's per-instance arrays
+        want = {name: np.array(vals[name][b], dtype=float).reshape(-1) for name in form.given_ID}
+        for state, ident in form.dynamics["LIP"].state_ID.items():
+            want["x0" + state[-2:]][ident] = ref[state][0, 0]
+        for state, ident in form.dynamics["steps"].state_ID.items():
+            want["s0" + state[-2:]][ident] = ref[state][1, 0]
+        for name in form.given_ID:
+            got = nxt[name][b].cpu().numpy()
+            if name.startswith("n_"):
+                assert np.array_equal(got, want[name])  # passed through untouched
+            else:
+                assert cases.rel_err(got, want[name]) <= cases.TOL, name
+    # the caller's collector is left as it was
+    assert all(np.array_equal(collector[name], vals[name]) for name in collector)
+    with pytest.raises(IndexError):
+        advance_collector(form, given, optim, {"LIP": N}, params)

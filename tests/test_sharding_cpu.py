@@ -81,3 +81,23 @@ def test_two_gloo_ranks_reproduce_the_single_process_batch(tmp_path):
     assert np.isclose(got["sums"][1, 2], whole.P[start:stop].sum(), rtol=1e-12)
     assert np.isclose(got["sums"][:, 3].sum(), whole.G.sum(), rtol=1e-12)
     assert float(got["slowest"]) == 2.0
+
+
+def test_count_steps_batched_follows_the_example_loop():
+    """receding.count_steps against the scalar logic of biped_mpc_loop.py:41-45,
+    for instances at different phases."""
+    from mpc_interface_b200.receding import count_steps
+
+    n, n_steps, batch = 12, 4, 9
+    times = np.stack([np.array([(i + 1) * n - 1 for i in range(n_steps)]) - b for b in range(batch)])
+    count = np.arange(batch)
+    t0, c0 = times.copy(), count.copy()
+    for _ in range(30):
+        new_t, new_c = count_steps(times, count, n)
+        for b in range(batch):
+            st, sc = times[b] - 1, count[b]
+            if st[0] == -1:
+                st, sc = st + n, sc + 1
+            assert np.array_equal(new_t[b], st) and new_c[b] == sc
+        times, count = new_t, new_c
+    assert np.array_equal(t0[0], [(i + 1) * n - 1 for i in range(n_steps)]) and np.array_equal(c0, np.arange(batch))
