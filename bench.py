@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=3072, help="instances of the CPU baseline")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-lti", action="store_true", help="skip the per-instance-dynamics lines")
+    ap.add_argument("--no-numa-bind", action="store_true",
+                    help="leave the rank's CPU affinity / memory policy alone")
     return ap.parse_args()
 
 
@@ -182,6 +184,11 @@ def run_own(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     from mpc_interface_b200 import Param, device, sharding
+
+    # pinned host buffers on the GPU's own NUMA node (matters for the e2e figure at N > 1)
+    props = torch.cuda.get_device_properties(local)
+    numa = (sharding.bind_host_near_gpu(props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+            if not args.no_numa_bind else None)
     from mpc_interface_b200.examples import synthetic
     from mpc_interface_b200.examples.biped import default_configuration, formulate_biped
 
@@ -312,7 +319,7 @@ def run_own(args):
     result = None
     if rank == 0:
         result = dict(B=B, world=world, ms=ms, t_P=t_P, t_G=t_G, t_qh=t_qh, nv=nv, ng=ng, nc=nc,
-                      in_step=in_step, clocks=clocks, launches=device.lib().mpci_assemble_launches(handle),
+                      in_step=in_step, numa=numa, clocks=clocks, launches=device.lib().mpci_assemble_launches(handle),
                       n_scalars=scalars_h.shape[1], t_csc=t_csc, csc_bytes=csc_bytes,
                       nnz=(pP.nnz, pG.nnz), lti=lti_lines, single=single, t_shared=t_shared,
                       shared_terms=shared_terms)
@@ -471,6 +478,7 @@ def main():
         "warmup": args.warmup, "ms_per_step": res["ms"] / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": config, "clocks": res["clocks"], "e2e": res["e2e"],
+        "host_binding_rank0": res["numa"],
         "gpu_launches": res["launches"] * args.steps,
         "roofline": {
             "bound": "hbm", "kernel": "stream_terms_kernel<3,double2> (G stack)",

@@ -81,3 +81,48 @@ def max_over_ranks(value, world, device="cpu"):
     t = torch.tensor([float(value)], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_host_near_gpu(pci_domain, pci_bus, pci_device, sysfs="/sys"):
+    """One process per GPU moves megabytes per QP over its GPU's PCIe link (the
+    host-buffer entry points); with several GPUs the pinned host
+    buffers have to live on the NUMA node the GPU hangs off, otherwise all ranks
+    write through one socket's memory and the inter-socket link.  Call BEFORE
+    allocating pinned memory: restricts this process to the CPUs of the GPU's node
+    that it is allowed to run on (first touch then places its pages there) and sets
+    the memory policy to prefer that node.  Never raises: returns what it did,
+    ``{"numa_node": .., "cpus": .., "mempolicy": ..}`` (node -1 = unknown, nothing done)."""
+    import ctypes
+    import os
+
+    info = {"numa_node": -1, "cpus": 0, "mempolicy": None}
+    try:
+        dev = "{:04x}:{:02x}:{:02x}.0".format(pci_domain, pci_bus, pci_device)
+        with open(os.path.join(sysfs, "bus/pci/devices", dev, "numa_node")) as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return info
+        info["numa_node"] = node
+        with open(os.path.join(sysfs, "devices/system/node/node{}/cpulist".format(node))) as f:
+            local = _parse_cpulist(f.read()) & os.sched_getaffinity(0)
+        if local:
+            os.sched_setaffinity(0, local)
+            info["cpus"] = len(local)
+        # set_mempolicy(MPOL_PREFERRED, {node}): x86-64 syscall 238
+        if os.uname().machine == "x86_64" and node < 64:
+            mask = ctypes.c_ulong(1 << node)
+            libc = ctypes.CDLL(None, use_errno=True)
+            info["mempolicy"] = int(libc.syscall(238, 1, ctypes.byref(mask), ctypes.c_ulong(65)))
+    except (OSError, ValueError):
+        pass
+    return info

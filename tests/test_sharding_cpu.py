@@ -101,3 +101,34 @@ def test_count_steps_batched_follows_the_example_loop():
             assert np.array_equal(new_t[b], st) and new_c[b] == sc
         times, count = new_t, new_c
     assert np.array_equal(t0[0], [(i + 1) * n - 1 for i in range(n_steps)]) and np.array_equal(c0, np.arange(batch))
+
+
+def test_bind_host_near_gpu_on_a_fake_sysfs(tmp_path):
+    """sharding.bind_host_near_gpu: reads the GPU's NUMA node and that node's CPU
+    list from sysfs, keeps the CPUs this process may use; unknown node or missing
+    files leave everything alone.  The binding itself runs in a child process."""
+    import subprocess
+
+    assert sharding._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert sharding.bind_host_near_gpu(0, 0x1B, 0, sysfs=str(tmp_path)) == {
+        "numa_node": -1, "cpus": 0, "mempolicy": None}
+    dev = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("-1\n")
+    assert sharding.bind_host_near_gpu(0, 0x1B, 0, sysfs=str(tmp_path))["numa_node"] == -1
+    allowed = sorted(os.sched_getaffinity(0))
+    keep = allowed[: max(1, len(allowed) // 2)]
+    (dev / "numa_node").write_text("0\n")
+    node = tmp_path / "devices/system/node/node0"
+    node.mkdir(parents=True)
+    (node / "cpulist").write_text(",".join(str(c) for c in keep) + ",4094-4095\n")
+    code = ("import os, sys, json; sys.path.insert(0, {!r}); from mpc_interface_b200 import sharding; "
+            "info = sharding.bind_host_near_gpu(0, 0x1B, 0, sysfs={!r}); "
+            "print(json.dumps([info, sorted(os.sched_getaffinity(0))]))").format(
+                os.path.dirname(os.path.dirname(os.path.abspath(__file__))), str(tmp_path))
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, check=True).stdout
+    import json
+
+    info, bound = json.loads(out.strip().splitlines()[-1])
+    assert info["numa_node"] == 0 and info["cpus"] == len(keep) and bound == keep
+    assert sorted(os.sched_getaffinity(0)) == allowed  # the parent is untouched
