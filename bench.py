@@ -439,13 +439,18 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        sample = cores * 200  # about 2-3 s of work per process and step
+        # exactly K timed steps; a step = a bounded sample of the workload (about 2-3 s of
+        # work per process, less when K is large so that the whole run stays within minutes);
+        # warm-up: every worker process assembles 3 instances before its timed loop
+        steps = max(1, args.steps)
+        sample = cores * (200 if steps <= 10 else max(20, 2000 // steps))
         total_t0 = time.perf_counter()
-        values = []
-        for _ in range(max(1, min(args.steps, 3))):
+        values, seconds = [], 0.0
+        for _ in range(steps):
             v, n = cpu_baseline(sample, cores)
             values.append(v)
-        value = float(np.median(values))
+            seconds += n / v
+        value = n * steps / seconds
         desc = {"value": value, "unit": "QPs/s", "cores": cores, "kind": "port",
                 "sample": "%d instances of the same workload per step over %d processes "
                           "(oracle/qp_oracle.py, 1 BLAS thread each)" % (n, cores)}
