@@ -109,7 +109,9 @@ typedef struct {
 
 typedef struct mpci_plan mpci_plan;
 
-/* Copies the small host tables; keeps the DP/DG/DY device pointers (owned by
+/* A plan handle is used by one host thread at a time (the calls keep per-plan streams,
+ * events and staging slots); different plans may be driven from different threads.
+ * Copies the small host tables; keeps the DP/DG/DY device pointers (owned by
  * the caller, must outlive the plan) and a device copy of the sparse Y rows. */
 int mpci_plan_create(const mpci_plan_desc* desc, mpci_plan** plan_out);
 int mpci_plan_destroy(mpci_plan* plan);
@@ -128,6 +130,19 @@ int mpci_assemble(const mpci_plan* plan, const double* scalars_dev, const double
 int mpci_assemble_host(mpci_plan* plan, const double* scalars_host, const double* given_host,
                        double* P_host, double* q_host, double* G_host, double* h_host,
                        long batch, long chunk);
+
+/* Streaming form for logical batches larger than host memory (BASELINE configs[2..4]:
+ * 1.2 TB / 337 GB of results): the host output arrays hold `ring` chunks of `chunk`
+ * instances and chunk c lands in slot c % ring (instance (c % ring) * chunk of every
+ * array).  `on_chunk` (may be NULL) is called on the calling thread when a chunk is
+ * complete in host memory and before its slot is written again -- the place where the
+ * caller's solver takes the QPs (the reference hands them to the solver one by one,
+ * biped_mpc_loop.py:57-60).  ring >= 2 unless the batch is a single chunk.           */
+typedef void (*mpci_chunk_fn)(void* user, long first_instance, long count, long slot);
+int mpci_assemble_host_stream(mpci_plan* plan, const double* scalars_host,
+                              const double* given_host, double* P_ring, double* q_ring,
+                              double* G_ring, double* h_ring, long batch, long chunk, long ring,
+                              mpci_chunk_fn on_chunk, void* user);
 
 /* ---- after the solve: preview and goal distance ---------------------------
  * Formulation.preview (body.py:209-219), v = Mg given + Mo optim, is the same
@@ -158,6 +173,11 @@ int mpci_assemble_compact(const mpci_plan* plan, const double* scalars_dev,
 int mpci_assemble_compact_host(mpci_plan* plan, const double* scalars_host,
                                const double* given_host, double* Pc_host, double* q_host,
                                double* Gc_host, double* h_host, long batch, long chunk);
+
+int mpci_assemble_compact_host_stream(mpci_plan* plan, const double* scalars_host,
+                                      const double* given_host, double* Pc_ring, double* q_ring,
+                                      double* Gc_ring, double* h_ring, long batch, long chunk,
+                                      long ring, mpci_chunk_fn on_chunk, void* user);
 
 /* Number of kernel launches one mpci_assemble call issues for this plan.    */
 int mpci_assemble_launches(const mpci_plan* plan);
@@ -233,6 +253,13 @@ int mpci_lti_assemble_host(mpci_lti_plan* plan, const double* A_host, long strid
                            const double* scalars_host, double* P_host, double* q_host,
                            double* G_host, double* h_host, long batch, int hessian_mode,
                            long chunk);
+
+/* Streaming form (host rings of `ring` chunks, see mpci_assemble_host_stream).           */
+int mpci_lti_assemble_host_stream(mpci_lti_plan* plan, const double* A_host, long strideA,
+                                  const double* B_host, long strideB, const double* x0_host,
+                                  const double* scalars_host, double* P_ring, double* q_ring,
+                                  double* G_ring, double* h_ring, long batch, int hessian_mode,
+                                  long chunk, long ring, mpci_chunk_fn on_chunk, void* user);
 
 /* Flops the Hessian phase of one instance executes in `hessian_mode`
  * (for the FP64 roofline; the structural count is SURVEY.md 8(d)).            */

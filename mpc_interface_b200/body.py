@@ -202,8 +202,15 @@ class Formulation:
             _plan.ordered_limits(self) if limits is None else limits,
         )
         if key not in self._plans:
+            self._trim_plans()
             self._plans[key] = _plan.compile_plan(self, self._ops(), costs, limits)
         return self._plans[key]
+
+    def _trim_plans(self, keep=32):
+        """Plans (and their device constants) of costs / limits that were passed once and
+        never again do not pile up: the oldest go first (dicts keep insertion order)."""
+        while len(self._plans) >= keep:
+            self._plans.pop(next(iter(self._plans)))
 
     def make_preview_matrices(self):
         """Rebuilds the preview matrices ``PM[var] = (Mg, Mo)`` with
@@ -238,10 +245,13 @@ class Formulation:
     # ------------------------------------------------------------------
     @staticmethod
     def _signature(costs, limits):
-        def stamp(objs):
-            return tuple((id(o), getattr(o, "_stamp", 0)) for o in objs)
-
-        return (stamp(costs), stamp(limits))
+        """Cache key of a compiled plan: the CONTENT of the costs and limits it was built
+        from (plan.cost_token / limit_token).  The reference re-reads the objects on every
+        ``generate_*`` call (body.py:236-302), so a field changed by hand, or a fresh
+        object that happens to reuse the address of a dead one, must never meet a plan
+        compiled from other numbers."""
+        return (tuple(_plan.cost_token(c) for c in costs),
+                tuple(_plan.limit_token(lim) for lim in limits))
 
     def _run(self, given, params, costs=None, limits=None, out=None, layout="dense"):
         """Evaluates a (sub)plan for a batch: given [B, ng], params {name: [B]}."""
@@ -465,5 +475,6 @@ class Formulation:
             list(self.goals.values()), _plan.ordered_limits(self)
         )
         if key not in self._plans:
+            self._trim_plans()
             self._plans[key] = lti.lower(self, name)
         return self._plans[key]

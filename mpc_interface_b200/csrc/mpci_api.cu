@@ -52,12 +52,16 @@ extern "C" int mpci_plan_create(const mpci_plan_desc* d, mpci_plan** out) {
   if (d->nv < 0 || d->ng < 0 || d->nc < 0 || d->n_scalars < 1 || d->n_monomials < 1)
     return mpci::fail(-1, "plan_create: bad sizes nv=%d ng=%d nc=%d scalars=%d monomials=%d",
                       d->nv, d->ng, d->nc, d->n_scalars, d->n_monomials);
+  if (!d->monomials || !d->P_terms || !d->G_terms)
+    return mpci::fail(-3, "plan_create: NULL monomial / term table");
+  if (d->n_Y_terms > mpci::kQhTermMask + 1)  // the records carry the term index in 8 bits
+    return mpci::fail(-7, "plan_create: [q;h] has %d monomials (limit %d)", d->n_Y_terms,
+                      mpci::kQhTermMask + 1);
   for (int i = 0; i < d->n_monomials * MPCI_MAX_FACTORS; ++i)
     if (d->monomials[i] >= d->n_scalars)
       return mpci::fail(-9, "plan_create: monomial factor %d out of %d scalars", d->monomials[i],
                         d->n_scalars);
-  mpci_plan* p = new mpci_plan();
-  std::memset(p, 0, sizeof(*p));
+  mpci_plan* p = new mpci_plan();  // members carry their own zero initialisers
   p->nv = d->nv; p->ng = d->ng; p->nc = d->nc; p->n_scalars = d->n_scalars;
   int rc = fill_stream(p->P, d->n_P_terms, d->P_terms, d->monomials, d->n_monomials, d->DP_dev,
                        (long)d->nv * d->nv, "P");
@@ -125,33 +129,69 @@ extern "C" int mpci_plan_create(const mpci_plan_desc* d, mpci_plan** out) {
     per_warp[w].push_back(idx);
     load[w] += chunks[idx].work;
   }
-  // per-warp record streams: chunks -> rows -> (row, term) segments -> non-zeros
+  // column blocks of [given; 1]: as few passes as the shared memory of one block allows
+  // (ring + row tiles are fixed, every staged column and every monomial costs 528 bytes)
+  const long fixed_bytes = (long)sizeof(mpci::QhNz) * mpci::kQhWarps * 32 +
+                           (long)sizeof(double) * mpci::kQhWarps * 64 * (mpci::kQhChunk + 1);
+  const long col_budget = (227L * 1024 - fixed_bytes) / (66 * (long)sizeof(double)) - d->n_Y_terms;
+  if (col_budget < 1) {
+    delete p;
+    return mpci::fail(-8, "plan_create: %d [q;h] monomials do not fit the kernel's shared memory",
+                      d->n_Y_terms);
+  }
+  const int n_pass = (int)((ngx + col_budget - 1) / col_budget);
+  if (n_pass > mpci::kQhMaxPass) {
+    delete p;
+    return mpci::fail(-8, "plan_create: given_len %d needs %d column passes (limit %d)", d->ng,
+                      n_pass, mpci::kQhMaxPass);
+  }
+  const int cols_per = (ngx + n_pass - 1) / n_pass;
+  for (int k = 0; k <= mpci::kQhMaxPass; ++k) p->Y.pass_col[k] = std::min(k * cols_per, ngx);
+  p->Y.n_pass = n_pass;
+  p->Y.max_cols = cols_per;
+  // per-pass, per-list record streams: chunks -> rows -> (row, term) segments -> the
+  // non-zeros whose column falls into the pass's block.  Pass 0 carries every chunk
+  // (an all-zero row still has to be written); a later pass only the chunks it adds to.
   std::vector<mpci::QhNz> h_nz;
-  std::vector<int> h_chunks, h_nz_ptr(1, 0), h_chunk_ptr(1, 0);
-  for (int w = 0; w < mpci::kQhLists; ++w) {
-    std::sort(per_warp[w].begin(), per_warp[w].end());
-    for (int idx : per_warp[w]) {
-      const Chunk& c = chunks[idx];
-      h_chunks.push_back(c.row0);
-      h_chunks.push_back(c.nrows);
-      int s = c.seg_begin;
-      for (int r = 0; r < c.nrows; ++r) {
-        const size_t row_start = h_nz.size();
-        while (s < c.seg_end && d->Y_segs[4 * s] == c.row0 + r) {
-          const int* g = d->Y_segs + 4 * s;
-          for (int e = g[2]; e < g[3]; ++e)
-            h_nz.push_back(mpci::QhNz{d->Y_val[e], d->Y_col[e] * mpci::kQhColStride, g[1]});
-          h_nz.back().meta |= mpci::kQhEndSeg;
-          ++s;
-        }
-        if (h_nz.size() == row_start)  // an all-zero row still has to be written
-          h_nz.push_back(mpci::QhNz{0.0, 0, mpci::kQhEndSeg});
-        h_nz.back().meta |= mpci::kQhEndRow;
-      }
-      h_nz.back().meta |= mpci::kQhEndChunk;
-    }
+  std::vector<int> h_chunks, h_nz_ptr, h_chunk_ptr;
+  for (int pass = 0; pass < n_pass; ++pass) {
+    const int c_lo = p->Y.pass_col[pass], c_hi = p->Y.pass_col[pass + 1];
     h_nz_ptr.push_back((int)h_nz.size());
     h_chunk_ptr.push_back((int)h_chunks.size() / 2);
+    for (int w = 0; w < mpci::kQhLists; ++w) {
+      if (pass == 0) std::sort(per_warp[w].begin(), per_warp[w].end());
+      for (int idx : per_warp[w]) {
+        const Chunk& c = chunks[idx];
+        if (pass > 0) {  // anything to add in this block of columns?
+          bool any = false;
+          for (int sg = c.seg_begin; sg < c.seg_end && !any; ++sg)
+            for (int e = d->Y_segs[4 * sg + 2]; e < d->Y_segs[4 * sg + 3] && !any; ++e)
+              any = d->Y_col[e] >= c_lo && d->Y_col[e] < c_hi;
+          if (!any) continue;
+        }
+        h_chunks.push_back(c.row0);
+        h_chunks.push_back(c.nrows);
+        int sg = c.seg_begin;
+        for (int r = 0; r < c.nrows; ++r) {
+          const size_t row_start = h_nz.size();
+          while (sg < c.seg_end && d->Y_segs[4 * sg] == c.row0 + r) {
+            const int* g = d->Y_segs + 4 * sg;
+            const size_t seg_start = h_nz.size();
+            for (int e = g[2]; e < g[3]; ++e)
+              if (d->Y_col[e] >= c_lo && d->Y_col[e] < c_hi)
+                h_nz.push_back(mpci::QhNz{d->Y_val[e], (d->Y_col[e] - c_lo) * mpci::kQhColStride, g[1]});
+            if (h_nz.size() > seg_start) h_nz.back().meta |= mpci::kQhEndSeg;
+            ++sg;
+          }
+          if (h_nz.size() == row_start)  // a row without entries here: 0 (written / added)
+            h_nz.push_back(mpci::QhNz{0.0, 0, mpci::kQhEndSeg});
+          h_nz.back().meta |= mpci::kQhEndRow;
+        }
+        h_nz.back().meta |= mpci::kQhEndChunk;
+      }
+      h_nz_ptr.push_back((int)h_nz.size());
+      h_chunk_ptr.push_back((int)h_chunks.size() / 2);
+    }
   }
   std::vector<int> h_factors;
   for (int j = 0; j < d->n_Y_terms; ++j)
@@ -196,7 +236,7 @@ extern "C" int mpci_plan_destroy(mpci_plan* p) {
   for (int s = 0; s < 2; ++s) {
     if (p->slot_in[s]) cudaFree(p->slot_in[s]);
     if (p->slot_out[s]) cudaFree(p->slot_out[s]);
-    if (p->slot_free[s]) cudaEventDestroy(p->slot_free[s]);
+    if (p->slot_done[s]) cudaEventDestroy(p->slot_done[s]);
     if (p->streams[s]) cudaStreamDestroy(p->streams[s]);
   }
   if (p->side) cudaStreamDestroy(p->side);
@@ -331,14 +371,26 @@ int assemble_with(const mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::St
 namespace {
 int assemble_host_with(mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::StreamArgs& Ga,
                        const double* scalars, const double* given, double* P, double* q,
-                       double* G, double* h, long batch, long chunk);
+                       double* G, double* h, long batch, long chunk, long ring,
+                       mpci_chunk_fn on_chunk, void* user);
 }
 
 extern "C" int mpci_assemble_host(mpci_plan* p, const double* scalars, const double* given,
                                   double* P, double* q, double* G, double* h, long batch,
                                   long chunk) {
   if (!p) return mpci::fail(-3, "assemble_host: NULL plan");
-  return assemble_host_with(p, p->P, p->G, scalars, given, P, q, G, h, batch, chunk);
+  return assemble_host_with(p, p->P, p->G, scalars, given, P, q, G, h, batch, chunk, 0, nullptr,
+                            nullptr);
+}
+
+extern "C" int mpci_assemble_host_stream(mpci_plan* p, const double* scalars, const double* given,
+                                         double* P, double* q, double* G, double* h, long batch,
+                                         long chunk, long ring, mpci_chunk_fn on_chunk,
+                                         void* user) {
+  if (!p) return mpci::fail(-3, "assemble_host_stream: NULL plan");
+  if (ring < 1) return mpci::fail(-1, "assemble_host_stream: ring must hold at least one chunk");
+  return assemble_host_with(p, p->P, p->G, scalars, given, P, q, G, h, batch, chunk, ring,
+                            on_chunk, user);
 }
 
 extern "C" int mpci_assemble_compact_host(mpci_plan* p, const double* scalars,
@@ -347,17 +399,41 @@ extern "C" int mpci_assemble_compact_host(mpci_plan* p, const double* scalars,
   if (!p) return mpci::fail(-3, "assemble_compact_host: NULL plan");
   if ((Pc && !p->Pc.consts) || (Gc && !p->Gc.consts))
     return mpci::fail(-3, "assemble_compact_host: mpci_plan_set_compact was not called");
-  return assemble_host_with(p, p->Pc, p->Gc, scalars, given, Pc, q, Gc, h, batch, chunk);
+  return assemble_host_with(p, p->Pc, p->Gc, scalars, given, Pc, q, Gc, h, batch, chunk, 0,
+                            nullptr, nullptr);
+}
+
+extern "C" int mpci_assemble_compact_host_stream(mpci_plan* p, const double* scalars,
+                                                 const double* given, double* Pc, double* q,
+                                                 double* Gc, double* h, long batch, long chunk,
+                                                 long ring, mpci_chunk_fn on_chunk, void* user) {
+  if (!p) return mpci::fail(-3, "assemble_compact_host_stream: NULL plan");
+  if (ring < 1) return mpci::fail(-1, "assemble_compact_host_stream: ring must hold at least one chunk");
+  if ((Pc && !p->Pc.consts) || (Gc && !p->Gc.consts))
+    return mpci::fail(-3, "assemble_compact_host_stream: mpci_plan_set_compact was not called");
+  return assemble_host_with(p, p->Pc, p->Gc, scalars, given, Pc, q, Gc, h, batch, chunk, ring,
+                            on_chunk, user);
 }
 
 namespace {
+// Chunks of instances alternate between two device slots / streams (upload, the three
+// kernels, download), so the copies of one chunk overlap the kernels of the other.
+// ring == 0: the host arrays hold the whole batch (chunk c lands at instance c * chunk);
+// ring >= 1: they hold `ring` chunks and chunk c lands in slot c % ring -- logical batches
+// larger than host memory -- with `on_chunk` called (on this thread) once a chunk is
+// complete in host memory and before its slot is written again.
 int assemble_host_with(mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::StreamArgs& Ga,
                        const double* scalars, const double* given, double* P, double* q,
-                       double* G, double* h, long batch, long chunk) {
+                       double* G, double* h, long batch, long chunk, long ring,
+                       mpci_chunk_fn on_chunk, void* user) {
   if (batch < 0 || chunk < 1) return mpci::fail(-1, "assemble_host: bad batch / chunk");
   if (batch == 0) return 0;
   if (!scalars || (p->ng > 0 && !given)) return mpci::fail(-3, "assemble_host: NULL input");
   if (chunk > batch) chunk = batch;
+  const long n_chunks = (batch + chunk - 1) / chunk;
+  if (ring == 0) ring = n_chunks;
+  if (ring < 2 && n_chunks > 1)
+    return mpci::fail(-1, "assemble_host: a ring of one slot cannot overlap two chunks");
   const long in_per = p->n_scalars + p->ng;
   const long nP = Pa.n_elems, nG = Ga.n_elems;
   const long out_per = nP + p->nv + nG + p->nc;
@@ -372,36 +448,43 @@ int assemble_host_with(mpci_plan* p, const mpci::StreamArgs& Pa, const mpci::Str
       MPCI_CUDA(cudaMalloc(&p->slot_in[s], sizeof(double) * in_per * chunk));
       MPCI_CUDA(cudaMalloc(&p->slot_out[s], sizeof(double) * out_per * chunk));
       if (!p->streams[s]) MPCI_CUDA(cudaStreamCreateWithFlags(&p->streams[s], cudaStreamNonBlocking));
-      if (!p->slot_free[s]) MPCI_CUDA(cudaEventCreateWithFlags(&p->slot_free[s], cudaEventDisableTiming));
+      if (!p->slot_done[s]) MPCI_CUDA(cudaEventCreateWithFlags(&p->slot_done[s], cudaEventDisableTiming));
     }
     p->slot_capacity = chunk;
     p->slot_out_doubles = out_per * chunk;
   }
-  int slot = 0;
-  for (long b0 = 0; b0 < batch; b0 += chunk, slot ^= 1) {
-    const long nb = (batch - b0 < chunk) ? batch - b0 : chunk;
-    cudaStream_t st = p->streams[slot];
-    double* d_s = p->slot_in[slot];
-    double* d_g = d_s + (long)p->n_scalars * chunk;
-    double* d_P = p->slot_out[slot];
-    double* d_q = d_P + nP * chunk;
-    double* d_G = d_q + (long)p->nv * chunk;
-    double* d_h = d_G + nG * chunk;
-    MPCI_CUDA(cudaMemcpyAsync(d_s, scalars + b0 * p->n_scalars, sizeof(double) * nb * p->n_scalars,
-                              cudaMemcpyHostToDevice, st));
-    if (p->ng)
-      MPCI_CUDA(cudaMemcpyAsync(d_g, given + b0 * p->ng, sizeof(double) * nb * p->ng,
+  for (long c = 0; c <= n_chunks; ++c) {
+    if (c < n_chunks) {
+      const int slot = (int)(c & 1);
+      const long b0 = c * chunk, nb = (batch - b0 < chunk) ? batch - b0 : chunk;
+      const long at = (c % ring) * chunk;  // first instance of the host slot
+      cudaStream_t st = p->streams[slot];
+      double* d_s = p->slot_in[slot];
+      double* d_g = d_s + (long)p->n_scalars * chunk;
+      double* d_P = p->slot_out[slot];
+      double* d_q = d_P + nP * chunk;
+      double* d_G = d_q + (long)p->nv * chunk;
+      double* d_h = d_G + nG * chunk;
+      MPCI_CUDA(cudaMemcpyAsync(d_s, scalars + b0 * p->n_scalars, sizeof(double) * nb * p->n_scalars,
                                 cudaMemcpyHostToDevice, st));
-    int rc = assemble_with(p, Pa, Ga, d_s, d_g, P ? d_P : nullptr, q ? d_q : nullptr,
-                           G ? d_G : nullptr, h ? d_h : nullptr, nb, st);
-    if (rc) return rc;
-    if (P) MPCI_CUDA(cudaMemcpyAsync(P + b0 * nP, d_P, sizeof(double) * nb * nP, cudaMemcpyDeviceToHost, st));
-    if (q) MPCI_CUDA(cudaMemcpyAsync(q + b0 * p->nv, d_q, sizeof(double) * nb * p->nv, cudaMemcpyDeviceToHost, st));
-    if (G) MPCI_CUDA(cudaMemcpyAsync(G + b0 * nG, d_G, sizeof(double) * nb * nG, cudaMemcpyDeviceToHost, st));
-    if (h) MPCI_CUDA(cudaMemcpyAsync(h + b0 * p->nc, d_h, sizeof(double) * nb * p->nc, cudaMemcpyDeviceToHost, st));
+      if (p->ng)
+        MPCI_CUDA(cudaMemcpyAsync(d_g, given + b0 * p->ng, sizeof(double) * nb * p->ng,
+                                  cudaMemcpyHostToDevice, st));
+      int rc = assemble_with(p, Pa, Ga, d_s, d_g, P ? d_P : nullptr, q ? d_q : nullptr,
+                             G ? d_G : nullptr, h ? d_h : nullptr, nb, st);
+      if (rc) return rc;
+      if (P) MPCI_CUDA(cudaMemcpyAsync(P + at * nP, d_P, sizeof(double) * nb * nP, cudaMemcpyDeviceToHost, st));
+      if (q) MPCI_CUDA(cudaMemcpyAsync(q + at * p->nv, d_q, sizeof(double) * nb * p->nv, cudaMemcpyDeviceToHost, st));
+      if (G) MPCI_CUDA(cudaMemcpyAsync(G + at * nG, d_G, sizeof(double) * nb * nG, cudaMemcpyDeviceToHost, st));
+      if (h) MPCI_CUDA(cudaMemcpyAsync(h + at * p->nc, d_h, sizeof(double) * nb * p->nc, cudaMemcpyDeviceToHost, st));
+      MPCI_CUDA(cudaEventRecord(p->slot_done[slot], st));
+    }
+    if (c >= 1) {  // chunk c - 1 is complete (chunk c keeps the device busy meanwhile)
+      const long done = c - 1, b0 = done * chunk;
+      MPCI_CUDA(cudaEventSynchronize(p->slot_done[done & 1]));
+      if (on_chunk) on_chunk(user, b0, (batch - b0 < chunk) ? batch - b0 : chunk, done % ring);
+    }
   }
-  MPCI_CUDA(cudaStreamSynchronize(p->streams[0]));
-  MPCI_CUDA(cudaStreamSynchronize(p->streams[1]));
   return 0;
 }
 }  // namespace

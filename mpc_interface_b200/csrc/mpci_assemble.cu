@@ -199,11 +199,10 @@ __global__ void __launch_bounds__(kQhWarps * 32)
 qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict__ given,
           double* __restrict__ q, double* __restrict__ h, long batch) {
   extern __shared__ double sm[];
-  const int ngx = a.ng + 1;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   QhNz* ring = reinterpret_cast<QhNz*>(sm) + warp * 32;                // [kQhWarps][32]
-  double* gs = sm + kQhWarps * 32 * (sizeof(QhNz) / sizeof(double));   // [ngx][33] double2
-  double* cs = gs + (size_t)ngx * 2 * kQhColStride;                                  // [n_terms][33] double2
+  double* gs = sm + kQhWarps * 32 * (sizeof(QhNz) / sizeof(double));   // [max_cols][33] double2
+  double* cs = gs + (size_t)a.max_cols * 2 * kQhColStride;                        // [n_terms][33] double2
   double* tiles = cs + (size_t)a.n_terms * 2 * kQhColStride;              // [kQhWarps][kQhInst][kQhTileLd]
   // persistent: at most one block per SM, so that every block is resident at once
   // and the P / G streams launched beside this kernel can use the other thread slots
@@ -211,16 +210,6 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
   const int group = (int)min((long)kQhInst, batch - b0);
   __syncthreads();  // the previous group is done with gs / cs
 
-  // stage [given; 1]: instance t sits in lane t % 32, half t / 32 of every column
-  for (int t = warp; t < kQhInst; t += kQhWarps) {
-    const double* g = given + (b0 + t) * a.ng;
-    double* dst = gs + (t & 31) * 2 + (t >> 5);
-    for (int k = lane; k < ngx; k += 32) {
-      double v = 0.0;
-      if (t < group) v = (k < a.ng) ? g[k] : 1.0;
-      dst[k * 66] = v;
-    }
-  }
   for (int e = tid; e < a.n_terms * kQhInst; e += blockDim.x) {
     const int j = e / kQhInst, t = e % kQhInst;
     double c = 0.0;
@@ -234,14 +223,32 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
     }
     cs[j * 66 + (t & 31) * 2 + (t >> 5)] = c;
   }
+
+  // one pass per block of columns of [given; 1] (a single pass unless the columns do
+  // not fit in shared memory): pass 0 writes the rows, the later ones add to them
+  for (int pass = 0; pass < a.n_pass; ++pass) {
+  const int c0 = a.pass_col[pass], ncol = a.pass_col[pass + 1] - c0;
+  if (pass) __syncthreads();  // the previous pass is done with gs
+  // stage the columns: instance t sits in lane t % 32, half t / 32 of every column
+  for (int t = warp; t < kQhInst; t += kQhWarps) {
+    const double* g = given + (b0 + t) * a.ng;
+    double* dst = gs + (t & 31) * 2 + (t >> 5);
+    for (int k = lane; k < ncol; k += 32) {
+      double v = 0.0;
+      if (t < group) v = (c0 + k < a.ng) ? g[c0 + k] : 1.0;
+      dst[k * 66] = v;
+    }
+  }
   __syncthreads();
+  const int* nz_ptr = a.warp_nz_ptr + pass * (kQhLists + 1);
+  const int* chunk_ptr = a.warp_chunk_ptr + pass * (kQhLists + 1);
 
   double* tile = tiles + (size_t)warp * kQhInst * kQhTileLd;
   const double2* gl = reinterpret_cast<const double2*>(gs) + lane;
   const double2* cl = reinterpret_cast<const double2*>(cs) + lane;
   for (int list = warp + kQhWarps * (int)blockIdx.y; list < kQhLists; list += kQhWarps * (int)gridDim.y) {
-  const int e_begin = a.warp_nz_ptr[list], e_end = a.warp_nz_ptr[list + 1];
-  int ci = a.warp_chunk_ptr[list];
+  const int e_begin = nz_ptr[list], e_end = nz_ptr[list + 1];
+  int ci = chunk_ptr[list];
   double acc0 = 0.0, acc1 = 0.0, p0 = 0.0, p1 = 0.0;
   int r = 0;
   // The list's record stream comes in batches of 32: one coalesced 16-byte load
@@ -293,7 +300,10 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
 #pragma unroll
             for (int it = 0; it < kQhInst / (32 / kQhChunk); ++it) {
               const int t = it * (32 / kQhChunk) + sub;
-              if (t < group) out[(b0 + t) * stride + row + rr] = tile[t * kQhTileLd + rr];
+              if (t < group) {
+                double* o = out + (b0 + t) * stride + row + rr;
+                *o = pass ? *o + tile[t * kQhTileLd + rr] : tile[t * kQhTileLd + rr];
+              }
             }
           }
         }
@@ -304,11 +314,12 @@ qh_kernel(QhArgs a, const double* __restrict__ scalars, const double* __restrict
     __syncwarp();
   }
   }  // lists of this warp
+  }  // column passes
   }  // groups of instances
 }
 
 size_t qh_smem_bytes(const QhArgs& a) {
-  return sizeof(double) * ((size_t)(a.ng + 1 + a.n_terms) * 66 +
+  return sizeof(double) * ((size_t)(a.max_cols + a.n_terms) * 66 +
                            (size_t)kQhWarps * kQhInst * kQhTileLd) +
          sizeof(QhNz) * kQhWarps * 32;
 }
@@ -319,7 +330,7 @@ int launch_qh(const QhArgs& a, const double* scalars, const double* given, doubl
   if (rows == 0 || batch == 0 || (!q && !h)) return 0;
   const size_t smem = qh_smem_bytes(a);
   if (smem > 227 * 1024)
-    return fail(-8, "assemble: given_len %d too large for the [q;h] kernel", a.ng);
+    return fail(-8, "assemble: %d monomials of [q;h] do not fit the kernel's shared memory", a.n_terms);
   if (smem > 48 * 1024)
     MPCI_CUDA(cudaFuncSetAttribute(qh_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    (int)smem));

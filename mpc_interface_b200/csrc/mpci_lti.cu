@@ -796,6 +796,7 @@ struct mpci_lti_plan {
   double* slot_in[2];   // A | B | x0 | scalars
   double* slot_out[2];  // P | q | G | h
   cudaStream_t streams[2];
+  cudaEvent_t slot_done[2];
 };
 
 extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out) {
@@ -863,8 +864,7 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
     for (int k = 1; k < N; ++k) same = same && d->grp_arrow[(size_t)g * N + k] == d->grp_arrow[(size_t)g * N];
     if (same) flags[g] |= 2;
   }
-  mpci_lti_plan* p = new mpci_lti_plan();
-  std::memset(p, 0, sizeof(*p));
+  mpci_lti_plan* p = new mpci_lti_plan();  // value-initialised: every member zero
   const size_t n_flags = flags.size();
   flags.insert(flags.end(), tile_rc.begin(), tile_rc.end());  // flags | tiles (int2), 8-byte aligned
   if (n_flags % 2) flags.insert(flags.begin() + n_flags, 0);
@@ -930,6 +930,7 @@ extern "C" int mpci_lti_plan_destroy(mpci_lti_plan* p) {
     if (p->slot_in[s]) cudaFree(p->slot_in[s]);
     if (p->slot_out[s]) cudaFree(p->slot_out[s]);
     if (p->streams[s]) cudaStreamDestroy(p->streams[s]);
+    if (p->slot_done[s]) cudaEventDestroy(p->slot_done[s]);
   }
   if (p->dev) cudaFree(p->dev);
   delete p;
@@ -1005,11 +1006,12 @@ extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long s
 
 // Host buffers: chunks of instances alternate between two slots / streams, so the
 // upload of one chunk and the download of the previous one overlap the kernel.
-extern "C" int mpci_lti_assemble_host(mpci_lti_plan* p, const double* A, long strideA,
-                                      const double* B, long strideB, const double* x0,
-                                      const double* scalars, double* P, double* q, double* G,
-                                      double* h, long batch, int mode, long chunk) {
-  if (!p) return mpci::fail(-3, "lti_assemble_host: NULL plan");
+// ring == 0: the host arrays hold the whole batch; ring >= 1: `ring` chunks, chunk c in
+// slot c % ring, `on_chunk` when a chunk is complete (see mpci_assemble_host_stream).
+static int lti_host(mpci_lti_plan* p, const double* A, long strideA, const double* B, long strideB,
+                    const double* x0, const double* scalars, double* P, double* q, double* G,
+                    double* h, long batch, int mode, long chunk, long ring, mpci_chunk_fn on_chunk,
+                    void* user) {
   if (batch < 0 || chunk < 1) return mpci::fail(-1, "lti_assemble_host: bad batch / chunk");
   if (batch == 0) return 0;
   if (!A || !B || !x0 || (p->S > 0 && !scalars))
@@ -1018,6 +1020,10 @@ extern "C" int mpci_lti_assemble_host(mpci_lti_plan* p, const double* A, long st
   if ((strideA != 0 && strideA < n * n) || (strideB != 0 && strideB < n * m))
     return mpci::fail(-4, "lti_assemble_host: instance strides smaller than the matrices");
   if (chunk > batch) chunk = batch;
+  const long n_chunks = (batch + chunk - 1) / chunk;
+  if (ring == 0) ring = n_chunks;
+  if (ring < 2 && n_chunks > 1)
+    return mpci::fail(-1, "lti_assemble_host: a ring of one slot cannot overlap two chunks");
   const long nv = m * p->N, nc = (long)p->n_groups * p->N;
   const long in_per = n * n + n * m + n + S, out_per = nv * nv + nv + nc * nv + nc;
   if (p->slot_capacity < chunk) {
@@ -1032,48 +1038,78 @@ extern "C" int mpci_lti_assemble_host(mpci_lti_plan* p, const double* A, long st
       MPCI_CUDA(cudaMalloc(&p->slot_out[s], sizeof(double) * out_per * chunk));
       if (!p->streams[s])
         MPCI_CUDA(cudaStreamCreateWithFlags(&p->streams[s], cudaStreamNonBlocking));
+      if (!p->slot_done[s])
+        MPCI_CUDA(cudaEventCreateWithFlags(&p->slot_done[s], cudaEventDisableTiming));
     }
     p->slot_capacity = chunk;
   }
-  int slot = 0;
-  for (long b0 = 0; b0 < batch; b0 += chunk, slot ^= 1) {
-    const long nb = (batch - b0 < chunk) ? batch - b0 : chunk;
-    cudaStream_t st = p->streams[slot];
-    double* d_A = p->slot_in[slot];
-    double* d_B = d_A + n * n * chunk;
-    double* d_x = d_B + n * m * chunk;
-    double* d_s = d_x + n * chunk;
-    double* d_P = p->slot_out[slot];
-    double* d_q = d_P + nv * nv * chunk;
-    double* d_G = d_q + nv * chunk;
-    double* d_h = d_G + nc * nv * chunk;
-    // shared dynamics (stride 0): one matrix per chunk; per-instance: a strided copy
-    if (strideA == 0)
-      MPCI_CUDA(cudaMemcpyAsync(d_A, A, sizeof(double) * n * n, cudaMemcpyHostToDevice, st));
-    else
-      MPCI_CUDA(cudaMemcpy2DAsync(d_A, sizeof(double) * n * n, A + b0 * strideA,
-                                  sizeof(double) * strideA, sizeof(double) * n * n, nb,
+  for (long c = 0; c <= n_chunks; ++c) {
+    if (c < n_chunks) {
+      const int slot = (int)(c & 1);
+      const long b0 = c * chunk, nb = (batch - b0 < chunk) ? batch - b0 : chunk;
+      const long at = (c % ring) * chunk;
+      cudaStream_t st = p->streams[slot];
+      double* d_A = p->slot_in[slot];
+      double* d_B = d_A + n * n * chunk;
+      double* d_x = d_B + n * m * chunk;
+      double* d_s = d_x + n * chunk;
+      double* d_P = p->slot_out[slot];
+      double* d_q = d_P + nv * nv * chunk;
+      double* d_G = d_q + nv * chunk;
+      double* d_h = d_G + nc * nv * chunk;
+      // shared dynamics (stride 0): one matrix per chunk; per-instance: a strided copy
+      if (strideA == 0)
+        MPCI_CUDA(cudaMemcpyAsync(d_A, A, sizeof(double) * n * n, cudaMemcpyHostToDevice, st));
+      else
+        MPCI_CUDA(cudaMemcpy2DAsync(d_A, sizeof(double) * n * n, A + b0 * strideA,
+                                    sizeof(double) * strideA, sizeof(double) * n * n, nb,
+                                    cudaMemcpyHostToDevice, st));
+      if (strideB == 0)
+        MPCI_CUDA(cudaMemcpyAsync(d_B, B, sizeof(double) * n * m, cudaMemcpyHostToDevice, st));
+      else
+        MPCI_CUDA(cudaMemcpy2DAsync(d_B, sizeof(double) * n * m, B + b0 * strideB,
+                                    sizeof(double) * strideB, sizeof(double) * n * m, nb,
+                                    cudaMemcpyHostToDevice, st));
+      MPCI_CUDA(cudaMemcpyAsync(d_x, x0 + b0 * n, sizeof(double) * nb * n, cudaMemcpyHostToDevice, st));
+      if (S)
+        MPCI_CUDA(cudaMemcpyAsync(d_s, scalars + b0 * S, sizeof(double) * nb * S,
                                   cudaMemcpyHostToDevice, st));
-    if (strideB == 0)
-      MPCI_CUDA(cudaMemcpyAsync(d_B, B, sizeof(double) * n * m, cudaMemcpyHostToDevice, st));
-    else
-      MPCI_CUDA(cudaMemcpy2DAsync(d_B, sizeof(double) * n * m, B + b0 * strideB,
-                                  sizeof(double) * strideB, sizeof(double) * n * m, nb,
-                                  cudaMemcpyHostToDevice, st));
-    MPCI_CUDA(cudaMemcpyAsync(d_x, x0 + b0 * n, sizeof(double) * nb * n, cudaMemcpyHostToDevice, st));
-    if (S)
-      MPCI_CUDA(cudaMemcpyAsync(d_s, scalars + b0 * S, sizeof(double) * nb * S,
-                                cudaMemcpyHostToDevice, st));
-    int rc = mpci_lti_assemble(p, d_A, strideA ? n * n : 0, d_B, strideB ? n * m : 0, d_x,
-                               S ? d_s : nullptr, P ? d_P : nullptr, q ? d_q : nullptr,
-                               G ? d_G : nullptr, h ? d_h : nullptr, nb, mode, st);
-    if (rc) return rc;
-    if (P) MPCI_CUDA(cudaMemcpyAsync(P + b0 * nv * nv, d_P, sizeof(double) * nb * nv * nv, cudaMemcpyDeviceToHost, st));
-    if (q) MPCI_CUDA(cudaMemcpyAsync(q + b0 * nv, d_q, sizeof(double) * nb * nv, cudaMemcpyDeviceToHost, st));
-    if (G) MPCI_CUDA(cudaMemcpyAsync(G + b0 * nc * nv, d_G, sizeof(double) * nb * nc * nv, cudaMemcpyDeviceToHost, st));
-    if (h) MPCI_CUDA(cudaMemcpyAsync(h + b0 * nc, d_h, sizeof(double) * nb * nc, cudaMemcpyDeviceToHost, st));
+      int rc = mpci_lti_assemble(p, d_A, strideA ? n * n : 0, d_B, strideB ? n * m : 0, d_x,
+                                 S ? d_s : nullptr, P ? d_P : nullptr, q ? d_q : nullptr,
+                                 G ? d_G : nullptr, h ? d_h : nullptr, nb, mode, st);
+      if (rc) return rc;
+      if (P) MPCI_CUDA(cudaMemcpyAsync(P + at * nv * nv, d_P, sizeof(double) * nb * nv * nv, cudaMemcpyDeviceToHost, st));
+      if (q) MPCI_CUDA(cudaMemcpyAsync(q + at * nv, d_q, sizeof(double) * nb * nv, cudaMemcpyDeviceToHost, st));
+      if (G) MPCI_CUDA(cudaMemcpyAsync(G + at * nc * nv, d_G, sizeof(double) * nb * nc * nv, cudaMemcpyDeviceToHost, st));
+      if (h) MPCI_CUDA(cudaMemcpyAsync(h + at * nc, d_h, sizeof(double) * nb * nc, cudaMemcpyDeviceToHost, st));
+      MPCI_CUDA(cudaEventRecord(p->slot_done[slot], st));
+    }
+    if (c >= 1) {
+      const long done = c - 1, b0 = done * chunk;
+      MPCI_CUDA(cudaEventSynchronize(p->slot_done[done & 1]));
+      if (on_chunk) on_chunk(user, b0, (batch - b0 < chunk) ? batch - b0 : chunk, done % ring);
+    }
   }
-  MPCI_CUDA(cudaStreamSynchronize(p->streams[0]));
-  MPCI_CUDA(cudaStreamSynchronize(p->streams[1]));
   return 0;
+}
+
+extern "C" int mpci_lti_assemble_host(mpci_lti_plan* p, const double* A, long strideA,
+                                      const double* B, long strideB, const double* x0,
+                                      const double* scalars, double* P, double* q, double* G,
+                                      double* h, long batch, int mode, long chunk) {
+  if (!p) return mpci::fail(-3, "lti_assemble_host: NULL plan");
+  return lti_host(p, A, strideA, B, strideB, x0, scalars, P, q, G, h, batch, mode, chunk, 0,
+                  nullptr, nullptr);
+}
+
+extern "C" int mpci_lti_assemble_host_stream(mpci_lti_plan* p, const double* A, long strideA,
+                                             const double* B, long strideB, const double* x0,
+                                             const double* scalars, double* P, double* q,
+                                             double* G, double* h, long batch, int mode,
+                                             long chunk, long ring, mpci_chunk_fn on_chunk,
+                                             void* user) {
+  if (!p) return mpci::fail(-3, "lti_assemble_host_stream: NULL plan");
+  if (ring < 1) return mpci::fail(-1, "lti_assemble_host_stream: ring must hold at least one chunk");
+  return lti_host(p, A, strideA, B, strideB, x0, scalars, P, q, G, h, batch, mode, chunk, ring,
+                  on_chunk, user);
 }

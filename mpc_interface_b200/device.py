@@ -44,6 +44,9 @@ class PlanDesc(ctypes.Structure):
     ]
 
 
+# mpci_chunk_fn: void (*)(void* user, long first_instance, long count, long slot)
+ChunkFn = ctypes.CFUNCTYPE(None, ctypes.c_void_p, ctypes.c_long, ctypes.c_long, ctypes.c_long)
+
 _SIGNATURES = {
     "mpci_version": (ctypes.c_int, []),
     "mpci_last_error": (ctypes.c_char_p, []),
@@ -80,6 +83,14 @@ _SIGNATURES = {
         ctypes.c_int,
         [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long, ctypes.c_long],
     ),
+    "mpci_assemble_host_stream": (
+        ctypes.c_int,
+        [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long] * 3 + [ChunkFn, ctypes.c_void_p],
+    ),
+    "mpci_assemble_compact_host_stream": (
+        ctypes.c_int,
+        [ctypes.c_void_p] + [_c_double_p] * 6 + [ctypes.c_long] * 3 + [ChunkFn, ctypes.c_void_p],
+    ),
     "mpci_assemble_launches": (ctypes.c_int, [ctypes.c_void_p]),
     "mpci_plan_set_timing": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "mpci_plan_read_timing": (
@@ -108,6 +119,12 @@ _SIGNATURES = {
         [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
          _c_double_p, _c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_long,
          ctypes.c_int, ctypes.c_long],
+    ),
+    "mpci_lti_assemble_host_stream": (
+        ctypes.c_int,
+        [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
+         _c_double_p, _c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_long,
+         ctypes.c_int, ctypes.c_long, ctypes.c_long, ChunkFn, ctypes.c_void_p],
     ),
     "mpci_lti_hessian_flops": (ctypes.c_double, [ctypes.c_void_p, ctypes.c_int]),
     "mpci_lti_plan_info": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
@@ -525,10 +542,29 @@ class DeviceBackend:
     def assemble_host(self, plan, scalars, given, P, q, G, h, batch, chunk):
         """Host (ideally pinned) numpy / CPU-tensor buffers in and out."""
         dp = self.device_plan(plan)
-
-        def p(x):
-            if x is None:
-                return ctypes.c_void_p(0)
-            return ctypes.c_void_p(x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
-
+        p = _host_ptr
         check(lib().mpci_assemble_host(dp.handle, p(scalars), p(given), p(P), p(q), p(G), p(h), batch, chunk))
+
+    def assemble_host_stream(self, plan, scalars, given, P, q, G, h, batch, chunk, ring,
+                             on_chunk=None, layout="dense"):
+        """Logical batches larger than host memory: ``P, q, G, h`` hold ``ring`` chunks of
+        ``chunk`` instances, chunk c lands in slot ``c % ring`` and
+        ``on_chunk(first_instance, count, slot)`` is called when it is complete in host
+        memory, before the slot is written again (mpci_assemble_host_stream).
+        ``layout="csc"``: ``P`` / ``G`` take the CSC values (compact())."""
+        dp = self.device_plan(plan)
+        p = _host_ptr
+        callback = ChunkFn(lambda _user, first, count, slot: on_chunk(first, count, slot)) \
+            if on_chunk is not None else ChunkFn(0)
+        fn = lib().mpci_assemble_host_stream
+        if layout != "dense":
+            self.compact(plan, layout == "csc_upper")
+            fn = lib().mpci_assemble_compact_host_stream
+        check(fn(dp.handle, p(scalars), p(given), p(P), p(q), p(G), p(h), batch, chunk, ring,
+                 callback, None))
+
+
+def _host_ptr(x):
+    if x is None:
+        return ctypes.c_void_p(0)
+    return ctypes.c_void_p(x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)

@@ -362,3 +362,39 @@ def assemble_host(plan, A, B, x0, params=None, hessian=HESSIAN_DMMA, chunk=256, 
         )
     )
     return out
+
+
+def assemble_host_stream(plan, A, B, x0, out, ring, params=None, hessian=HESSIAN_RECURSION, chunk=256,
+                         on_chunk=None):
+    """Runs ``mpci_lti_assemble_host_stream`` -- logical batches larger than host memory.
+    ``out`` = (P, q, G, h) pinned CPU tensors holding ``ring`` chunks of ``chunk``
+    instances; chunk c lands in slot ``c % ring`` and ``on_chunk(first, count, slot)`` is
+    called when it is complete, before the slot is written again."""
+    from . import device
+
+    dp = plan.device_plan()
+    n, m = plan.n, plan.m
+    A = np.ascontiguousarray(A, dtype=np.float64)
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    if x0.ndim != 2 or x0.shape[1] != n:
+        raise ValueError(
+            "matmul: the given vector has {} elements per instance, the formulation "
+            "expects {}".format(x0.shape[-1], n)
+        )
+    batch = x0.shape[0]
+    if A.shape[-2:] != (n, n) or B.shape[-2:] != (n, m):
+        raise ValueError("A must be [..., {0}, {0}] and B [..., {0}, {1}]".format(n, m))
+    S = len(plan.slots.exprs)
+    scalars = plan.slots.evaluate(params or {}, batch) if S else None
+    hp = lambda a: ctypes.c_void_p(a.ctypes.data) if a is not None else ctypes.c_void_p(0)  # noqa: E731
+    callback = device.ChunkFn(lambda _u, first, count, slot: on_chunk(first, count, slot)) \
+        if on_chunk is not None else device.ChunkFn(0)
+    device.check(
+        device.lib().mpci_lti_assemble_host_stream(
+            dp.handle, hp(A), n * n if A.ndim == 3 else 0, hp(B), n * m if B.ndim == 3 else 0,
+            hp(x0), hp(scalars), *(ctypes.c_void_p(t.data_ptr()) for t in out),
+            batch, int(hessian), int(chunk), int(ring), callback, None,
+        )
+    )
+    return out

@@ -32,6 +32,36 @@ MAX_FACTORS = 4  # factors per monomial the kernels accept (mpci.h: MPCI_MAX_FAC
 MAX_TERMS = 32  # monomials per streamed array (mpci.h: MPCI_MAX_TERMS; fast path up to 8)
 
 
+def _array_token(x):
+    """Hashable content of an array of numbers and / or Param expressions."""
+    arr = np.asarray(x)
+    if arr.dtype == object:
+        return ("o", arr.shape, tuple(e.key() if is_expr(e) else float(e) for e in arr.ravel()))
+    arr = np.ascontiguousarray(arr)
+    return (arr.shape, arr.dtype.str, arr.tobytes())
+
+
+def _schedule_token(schedule):
+    if isinstance(schedule, range):
+        return (schedule.start, schedule.stop, schedule.step)
+    return tuple(schedule) if schedule is not None else None
+
+
+def cost_token(cost):
+    """Everything of a Cost that generate_qp_cost reads (body.py:266-302)."""
+    return ("cost", cost.variable, cost.cross, tuple(cost.axes), _array_token(cost.weight),
+            _array_token(cost.aim), _array_token(cost.cross_aim),
+            tuple(_array_token(m) for m in cost.L), tuple(_array_token(m) for m in cost.cross_L),
+            _schedule_token(cost.schedule))
+
+
+def limit_token(limit):
+    """Everything of a Constraint that generate_qp_constraint reads (body.py:236-264)."""
+    return ("limit", limit.variable, tuple(limit.axes), _array_token(limit.arrow),
+            _array_token(limit.center), _array_token(limit.extreme),
+            tuple(_array_token(m) for m in limit.L), _schedule_token(limit.schedule))
+
+
 class SlotTable:
     """Distinct per-instance scalar expressions, in order of first use."""
 
@@ -226,6 +256,13 @@ def _limit_poly(form, ops, PM, limit, slots):
     nlines = limit.nlines
     c_rows = rows if nlines is None else int(nlines)
     schedule = range(rows) if not limit.schedule else limit.schedule
+    if limit.schedule and not limit.L and len(schedule) != c_rows:
+        # nlines is stop - start (restrictions.py:152-153); a stepped range selects fewer
+        # rows and the reference fails in the broadcast of body.py:258-259
+        raise ValueError(
+            "operands could not be broadcast together: the schedule {} selects {} rows "
+            "but the limit counts {} lines (stop - start)".format(limit.schedule, len(schedule), c_rows)
+        )
     out = Poly(ops, c_rows, width)
     multipliers = limit.matrices()
     for a, axis in enumerate(limit.axes):

@@ -1,11 +1,15 @@
-"""Runs the reference's OWN unittest files (python/tests/test_*.py, read where they lie
-under /root/reference -- nothing is copied) against THIS package: ``mpc_interface`` is
-aliased to ``mpc_interface_b200`` before they are imported.  Build container only (the
-reference is not on the GPU box); no GPU here, so the two device entry points the host
-classes call are stood in for by the test doubles the CPU suite uses everywhere
-(oracle extend_matrices, NumpyBackend).  Prints "<run> <failures> <errors>".
+"""Runs the reference's OWN unittest files (python/tests/test_*.py, read where they lie --
+/root/reference in the build container, the staged oracle/_ref on the GPU box) against
+THIS package: ``mpc_interface`` is aliased to ``mpc_interface_b200`` before they are
+imported.  Prints "<run> <failures> <errors>".
 
-    python tests/_run_reference_suite.py [/root/reference/python/tests]
+    python tests/_run_reference_suite.py [--device] [<reference>/python/tests]
+
+Without ``--device`` (no GPU: the build container) the two device entry points the host
+classes call are stood in for by the test doubles the CPU suite uses everywhere (oracle
+extend_matrices, NumpyBackend).  With ``--device`` nothing is replaced: every matrix the
+reference's tests look at comes out of libmpci.so on the GPU (K1, the plan compiler's
+DMMA products, the streaming kernels).
 """
 import importlib
 import importlib.util
@@ -20,14 +24,18 @@ sys.path.insert(0, os.path.dirname(HERE))
 sys.path.insert(0, HERE)
 
 
-def main(test_dir):
+def main(test_dir, on_device=False):
     import mpc_interface_b200.device as device
     import mpc_interface_b200.tools as tools
-    from _numpy_backend import NumpyBackend
-    from oracle import qp_oracle
 
-    tools.extend_matrices = qp_oracle.extend_matrices
-    device.DeviceBackend = NumpyBackend
+    if on_device:
+        device.require_gpu()
+    else:
+        from _numpy_backend import NumpyBackend
+        from oracle import qp_oracle
+
+        tools.extend_matrices = qp_oracle.extend_matrices
+        device.DeviceBackend = NumpyBackend
 
     alias = types.ModuleType("mpc_interface")
     alias.__path__ = []
@@ -46,6 +54,7 @@ def main(test_dir):
                 if "." in name:
                     setattr(sys.modules["matplotlib"], name.split(".")[1], sys.modules[name])
 
+    test_dir = os.path.abspath(test_dir)
     os.chdir(test_dir)  # test_dynamics.py opens its pickle by a relative path
     suite = unittest.TestSuite()
     for f in sorted(os.listdir(test_dir)):
@@ -57,6 +66,9 @@ def main(test_dir):
     result = unittest.TextTestRunner(stream=sys.stderr, verbosity=2).run(suite)
     example = run_example(os.path.join(os.path.dirname(test_dir), "use_examples", "simple_functional_example"))
     print("example", "ok" if example else "FAILED")
+    if on_device:  # proof that the kernels ran: the library is loaded and saw a device
+        print("backend", "libmpci" if device._lib is not None and device.lib().mpci_device_count() > 0
+              else "MISSING")
     print(result.testsRun, len(result.failures), len(result.errors))
     return 0 if result.wasSuccessful() and example else 1
 
@@ -103,4 +115,5 @@ def run_example(example_dir):
 
 
 if __name__ == "__main__":
-    sys.exit(main(sys.argv[1] if len(sys.argv) > 1 else "/root/reference/python/tests"))
+    argv = [a for a in sys.argv[1:] if a != "--device"]
+    sys.exit(main(argv[0] if argv else "/root/reference/python/tests", "--device" in sys.argv[1:]))

@@ -11,8 +11,25 @@ import pytest
 
 import _cases as cases
 from oracle import qp_oracle as orc
+from oracle import reference
 
 pytestmark = pytest.mark.gpu
+SAMPLES = 64  # SURVEY.md 8(c) "Parity metric": >= 64 sampled instances per config
+
+
+class _BipedExpect:
+    """Expected (A, h, Q, q) of sampled biped instances: the unmodified reference where
+    its staged copy is present (the GPU box: oracle/_ref), else the NumPy port."""
+
+    def __init__(self, form, N):
+        self.form = form
+        self.ref_form = reference.biped_form(N) if reference.available() else None
+
+    def __call__(self, vals, given, b):
+        if self.ref_form is not None:
+            return reference.biped_instance(self.ref_form, vals, b)
+        one = {k: float(vals[k][b]) for k in ("omega", "vel_x", "vel_y")}
+        return orc.all_qp_matrices(self.form, given[b][:, None], one)
 
 
 @pytest.fixture(scope="module")
@@ -65,12 +82,15 @@ def test_c2_full_batch_65536(biped100):
     params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
     out = form.generate_all_qp_matrices_batched(given, params)
     assert out.P.shape == (B, 218, 218) and out.G.shape == (B, 440, 218)
-    # sampled instances against the oracle (first / last of the batch and of 32-instance groups)
-    for b in (0, 31, 32, 40000, B - 33, B - 1):
-        one = {k: float(v[b]) for k, v in params.items()}
-        ref = orc.all_qp_matrices(form, given[b][:, None], one)
+    # sampled instances against the reference: first / last of the batch and of 32-instance
+    # groups, the rest spread over the batch
+    expect = _BipedExpect(form, 100)
+    picks = sorted(set([0, 31, 32, 40000, B - 33, B - 1]) |
+                   set(int(x) for x in np.random.default_rng(5).integers(0, B, SAMPLES - 6)))
+    assert len(picks) >= SAMPLES - 2
+    for b in picks:
         got = tuple(x[b].cpu().numpy() for x in (out.G, out.h, out.P, out.q))
-        cases.assert_qp_close(got, ref)
+        cases.assert_qp_close(got, expect(vals, given, b))
     # P and G depend on omega only: equal omega -> bitwise equal matrices
     assert torch.equal(out.P[: B // 2], out.P[B // 2:]) and torch.equal(out.G[: B // 2], out.G[B // 2:])
     # the 36 stepping-area rows do not depend on any per-instance value (probe8)
@@ -105,6 +125,7 @@ def test_c3_logical_batch_1048576_through_a_ring(biped100):
     rng_chunks = [0, 1, 15, 31]  # checksums are verified on these chunks, all chunks are assembled
     sums = torch.zeros(4, dtype=torch.float64, device="cuda")
     expect = np.zeros(4)
+    reference_of = _BipedExpect(form, 100)
     for c in range(total // chunk):
         vals = synthetic.biped_inputs(1003 + c, chunk, 100)  # chunk c of the logical batch
         given = synthetic.pack_given(form.given_ID, form.given_len, vals, chunk)
@@ -115,24 +136,27 @@ def test_c3_logical_batch_1048576_through_a_ring(biped100):
             coef = _monomial_values(plan, plan.slots.evaluate(params, chunk))
             sq, sh, sP, sG = _expected_sums(plan, coef, given)
             expect += np.array([sq.sum(), sh.sum(), sP, sG])
-            b = chunk - 1
-            ref = orc.all_qp_matrices(form, given[b][:, None], {k: float(v[b]) for k, v in params.items()})
-            cases.assert_qp_close(tuple(x[b].cpu().numpy() for x in (out.G, out.h, out.P, out.q)), ref)
+            for b in [chunk - 1] + [int(x) for x in np.random.default_rng(c).integers(0, chunk, SAMPLES // 4 - 1)]:
+                cases.assert_qp_close(tuple(x[b].cpu().numpy() for x in (out.G, out.h, out.P, out.q)),
+                                      reference_of(vals, given, b))
     assert _close(sums.cpu().numpy(), expect)
     del ring
     torch.cuda.empty_cache()
 
 
 @pytest.mark.parametrize("nx,nu,N,n_rows,total,chunk,seed,hessian,samples", [
-    (12, 4, 50, 4, 262144, 16384, 1004, "recursion", (0, 16383)),   # configs[3]
-    (12, 4, 50, 4, 32768, 16384, 1004, "dmma", (5,)),               # same shape, tensor-core Hessian
-    (6, 2, 400, 2, 16384, 1024, 1005, "dmma", (1023,)),             # configs[4]
+    (12, 4, 50, 4, 262144, 16384, 1004, "recursion", 32),   # configs[3]: 2 x 32 samples
+    (12, 4, 50, 4, 32768, 16384, 1004, "dmma", 32),         # same shape, tensor-core Hessian
+    (6, 2, 400, 2, 16384, 1024, 1005, "dmma", 2),           # configs[4]: 2 x 2 samples (0.7 s each)
+    (6, 2, 400, 2, 2048, 1024, 1005, "recursion", 2),       # same shape, displacement recursion
 ])
 def test_generic_full_batches_per_instance_plants(monkeypatch, nx, nu, N, n_rows, total, chunk, seed,
                                                    hessian, samples):
     """configs[3] / configs[4] with one plant per instance (mode B), streamed
-    through a ring of two slots; samples of the first and last chunk against the
-    oracle, P symmetric, the input-box rows independent of the plant."""
+    through a ring of two slots; ``samples`` instances of the first and of the last chunk
+    (their first / last instance and random ones) against the unmodified reference (the
+    NumPy port where oracle/_ref is absent), P symmetric, the input-box rows independent
+    of the plant."""
     import torch
     import mpc_interface_b200.tools as tools
     from _numpy_backend import NumpyBackend
@@ -159,11 +183,21 @@ def test_generic_full_batches_per_instance_plants(monkeypatch, nx, nu, N, n_rows
             assert sym <= 1e-11 * out.P.abs().amax().item()
             box = out.G[:, n_rows * N:]  # the 2 m N input-box rows: +-1 on the diagonal, plant-free
             assert bool((box == box[0]).all()) and float(box.abs().sum(dim=(1, 2)).max()) == 2 * nu * N
-            for b in samples:
+            picks = [0, chunk - 1]
+            for x in np.random.default_rng(c).permutation(chunk):
+                if len(picks) < samples and int(x) not in picks:
+                    picks.append(int(x))
+            for b in picks:
                 checked.append((c, b, A[b], B[b], vals["x0"][b], vals["ref"][b],
                                 tuple(x[b].cpu().numpy() for x in (out.G, out.h, out.P, out.q))))
     del ring
     torch.cuda.empty_cache()
+    assert len(checked) == 2 * samples
+    if reference.available():
+        plants = reference.GenericPlants(A0[0], B0[0], Q, R, N, rows)
+        for c, b, Ab, Bb, x0, ref_b, got in checked:
+            cases.assert_qp_close(got, plants.instance(Ab, Bb, ref_b, x0))
+        return
     monkeypatch.setattr(tools, "extend_matrices", orc.extend_matrices)
     for c, b, Ab, Bb, x0, ref_b, got in checked:
         ref_form = cases.formulate_generic(Ab, Bb, Q, R, N, rows, refs=list(ref_b), backend=NumpyBackend())

@@ -243,3 +243,40 @@ def test_negative_per_instance_extreme_is_refused(cpu_extend):
     form.generate_all_qp_matrices_batched(given, dict(values, e=np.array([0.5, 0.0])))
     with pytest.raises(ValueError, match="negative for instance 1"):
         form.generate_all_qp_matrices_batched(given, dict(values, e=np.array([0.5, -0.1])))
+
+
+def test_plan_cache_is_keyed_on_content(cpu_extend):
+    """Regression (round-1 advisor finding): plans were cached under (id(obj), stamp); a
+    fresh Constraint reusing the address of a dead one got the stale plan, and a field
+    changed by hand (no .update()) was ignored.  The reference re-reads the objects on
+    every generate_* call (body.py:236-302)."""
+    from mpc_interface_b200 import Constraint
+
+    form = cases.tiny_plant(backend=NumpyBackend(), optim=("u",))
+    given = np.zeros([form.given_len, 1])
+    seen = []
+    for extreme in (1.0, 2.0, 3.0):  # temporaries: CPython hands out the same id again
+        A, h = form.generate_qp_constraint(Constraint("b", extreme), given)
+        seen.append(float(h[0, 0]))
+    assert seen == [1.0, 2.0, 3.0]
+    # direct attribute mutation, no update()
+    limit = form.constraints["lim"][0]
+    _, h0 = form.generate_qp_constraint(limit, given)
+    limit.extreme = limit.extreme * 2
+    _, h1 = form.generate_qp_constraint(limit, given)
+    assert np.allclose(h1, 2 * h0) and float(h0[0, 0]) == 3.0
+    cost = form.goals["g2"]
+    Q0, _ = form.generate_qp_cost(cost, given)
+    cost.weight = 10 * cost.weight
+    Q1, _ = form.generate_qp_cost(cost, given)
+    assert np.allclose(Q1, 10 * Q0) and np.abs(Q0).max() > 0
+    _, h_all = form.generate_all_qp_constraints(given)
+    assert float(h_all[0, 0]) == 6.0  # the full plan sees the mutated limit as well
+    # equal content -> one plan; the cache does not grow without bound
+    n_before = len(form._plans)
+    for _ in range(5):
+        form.generate_qp_constraint(Constraint("b", 7.0), given)
+    assert len(form._plans) == n_before + 1
+    for k in range(50):
+        form.generate_qp_constraint(Constraint("b", 10.0 + k), given)
+    assert len(form._plans) <= 32
