@@ -36,6 +36,33 @@ def assert_qp_close(got, ref, tol=TOL):
         assert err <= tol, "{}: relative error {:.3e} > {:.1e}".format(name, err, tol)
 
 
+def digest(A, h, Q, q, seed, rows=8):
+    """Small fingerprint of one large QP for the committed goldens (a C5 instance is
+    20 MB): h and q in full, ``rows`` sampled rows of A and of Q, and the products of A
+    and Q with a seeded random vector -- every entry of both matrices enters those with
+    its own random weight, so a wrong entry anywhere moves them."""
+    rng = np.random.default_rng(seed)
+    rA = np.sort(rng.choice(A.shape[0], min(rows, A.shape[0]), replace=False))
+    rQ = np.sort(rng.choice(Q.shape[0], min(rows, Q.shape[0]), replace=False))
+    v = rng.normal(size=A.shape[1])
+    return {"h": np.ravel(h), "q": np.ravel(q), "A_idx": rA, "A_rows": A[rA], "Q_idx": rQ,
+            "Q_rows": Q[rQ], "A_v": A @ v, "Q_v": Q @ v, "Qt_v": Q.T @ v,
+            "shape": np.array([A.shape[0], A.shape[1]])}
+
+
+def assert_digest_close(got, g, prefix, seed, tol=TOL):
+    """got = (A, h, Q, q) of one instance against the digest stored under ``prefix``."""
+    A, h, Q, q = (np.asarray(x, dtype=float) for x in got)
+    assert tuple(g[prefix + "shape"]) == A.shape and Q.shape == (A.shape[1], A.shape[1])
+    mine = digest(A, h, Q, q, seed, rows=len(g[prefix + "A_idx"]))
+    for key, value in mine.items():
+        if key.endswith("idx") or key == "shape":
+            assert np.array_equal(value, g[prefix + key]), key
+        else:
+            err = rel_err(value, g[prefix + key])
+            assert err <= tol, "{}{}: relative error {:.3e} > {:.1e}".format(prefix, key, err, tol)
+
+
 def check_layout(form, g):
     for kind in ("optim", "given"):
         ids = getattr(form, kind + "_ID")

@@ -249,6 +249,46 @@ def generic_per_instance(name, seed, nx, nu, N, n_rows, batch):
          A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs), N=N, **layout(form))
 
 
+def _digests(out, tag, qp, seed):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _cases
+
+    A, h, Q, q = qp
+    out.update({tag + k: v for k, v in _cases.digest(A, h, Q, q, seed).items()})
+
+
+def biped_long(name, horizons, seed):
+    """Long horizons (given_len = 8 + 2N = 408 / 808): one instance each with its own
+    omega and aims; stored as digests (tests/_cases.py: digest) because A is 12 MB at
+    N = 400."""
+    out = {"horizons": np.array(horizons), "seed": seed}
+    for N in horizons:
+        form = formulate_biped(biped_conf(N))
+        vals = synthetic.biped_inputs(seed + N, 1, N)
+        given = synthetic.pack_given(form.given_ID, form.given_len, vals, 1)
+        set_omega(form, vals["omega"][0])
+        form.goals["track vel_x"].update(aim=vals["vel_x"][0])
+        form.goals["track vel_y"].update(aim=vals["vel_y"][0])
+        _digests(out, "n%d_" % N, form.generate_all_qp_matrices(given[0][:, None]), seed + N)
+        out.update({"n%d_%s" % (N, k): v for k, v in layout(form).items()})
+    save(name, **out)
+
+
+def generic_per_instance_digest(name, seed, nx, nu, N, n_rows, batch):
+    """Per-instance plants at the BASELINE shapes C4 / C5, stored as digests."""
+    _, _, Q, R = synthetic.generic_system(seed, nx, nu)
+    A, B = synthetic.generic_plants(seed, batch, nx, nu)
+    rows = np.random.default_rng(seed + 1).normal(size=[n_rows, nx])
+    vals = synthetic.generic_inputs(seed, batch, nx)
+    out = dict(seed=seed, A_sys=A, B_sys=B, Q_w=Q, R_w=R, rows=rows, x0=vals["x0"], ref=vals["ref"], N=N)
+    for b in range(batch):
+        form = formulate_generic(A[b], B[b], Q, R, N, rows, refs=list(vals["ref"][b]), api=RefAPI)
+        given = form.arrange_given({"x0": vals["x0"][b][:, None]})
+        _digests(out, "i%d_" % b, form.generate_all_qp_matrices(given), seed + b)
+    out.update(layout(form))
+    save(name, **out)
+
+
 def random_forms(name, seeds, batch):
     """tests/_random_forms.py built by the reference, one formulation per instance."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -277,6 +317,11 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["yaw"]:
         biped_yaw("biped_n24_yaw.npz", 24, 5, 1011)
         biped_yaw("biped_n100_yaw.npz", 100, 2, 1012)
+        sys.exit(0)
+    if sys.argv[1:] == ["big"]:
+        biped_long("biped_long_digest.npz", [200, 400], 1020)
+        generic_per_instance_digest("generic_c4_perinst_digest.npz", 1004, 12, 4, 50, 4, 8)
+        generic_per_instance_digest("generic_c5_perinst_digest.npz", 1005, 6, 2, 400, 2, 4)
         sys.exit(0)
     if sys.argv[1:] == ["per_instance"]:
         generic_per_instance("generic_perinst_small.npz", 31, 4, 2, 10, 2, 4)

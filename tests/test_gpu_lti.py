@@ -177,3 +177,19 @@ def ctypes_null():
     import ctypes
 
     return ctypes.c_void_p(0)
+
+
+@pytest.mark.parametrize("hessian", ["dmma", "recursion"])
+@pytest.mark.parametrize("name", ["generic_c4_perinst_digest", "generic_c5_perinst_digest"])
+def test_lti_at_the_baseline_shapes_against_reference_digests(dev, name, hessian):
+    """BASELINE configs[3] / configs[4] shapes with one plant per instance (8 plants at
+    nx=12, nu=4, N=50; 4 at nx=6, nu=2, N=400), both Hessian modes, against digests of the
+    matrices the unmodified reference produced (make_goldens.py big)."""
+    g = cases.golden(name)
+    form, params = _form(g, True)
+    cases.check_layout(form, g)
+    out = form.generate_all_qp_matrices_batched(
+        g["x0"], params, dynamics={"plant": (g["A_sys"], g["B_sys"])}, hessian=hessian)
+    got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+    for b in range(g["x0"].shape[0]):
+        cases.assert_digest_close(tuple(x[b] for x in got), g, "i%d_" % b, int(g["seed"]) + b)

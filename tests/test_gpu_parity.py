@@ -455,13 +455,14 @@ def test_csc_hand_off_layout(dev, name):
     assert torch.equal(hq, out.q.cpu()) and torch.equal(hh, out.h.cpu())
 
 
-def test_preview_and_goal_distance_batched(dev):
+@pytest.mark.parametrize("N", [24, 100])
+def test_preview_and_goal_distance_batched(dev, N):
     """Formulation.preview / goal_distance (body.py:209-234)
     for a batch with per-instance omega, against the oracle's preview matrices."""
     from mpc_interface_b200 import Param
     from mpc_interface_b200.examples import synthetic
 
-    N, batch = 24, 70
+    batch = 70
     form = cases.formulate_biped(
         cases.default_configuration(N), omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")])
     vals = synthetic.biped_inputs(9, batch, N)
@@ -499,3 +500,35 @@ def test_preview_and_goal_distance_batched(dev):
     single = cases.formulate_biped(cases.default_configuration(N))
     v = single.preview(given[0][:, None], optim[0][:, None], "CoM", ["_x", "_y"])
     assert v.shape == (N, 2)
+
+
+@pytest.mark.parametrize("N", [200, 400])
+def test_biped_long_horizons_in_mode_a(dev, N):
+    """given_len = 8 + 2N = 408 / 808: [given; 1] no longer fits the shared memory of the
+    [q; h] kernel in one piece (round 1 refused it above ~340); the columns are staged in
+    passes.  Against digests written by the unmodified reference (make_goldens.py big),
+    and the same instance inside a batch of 70 (more than one group of 64)."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    g = cases.golden("biped_long_digest")
+    seed = int(g["seed"]) + N
+    form = cases.formulate_biped(cases.default_configuration(N), omega=Param("omega"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    cases.check_layout(form, {k: g["n%d_%s" % (N, k)] for k in
+                              ("optim_names", "optim_ranges", "given_names", "given_ranges")})
+    one = synthetic.biped_inputs(seed, 1, N)
+    batch = 70
+    vals = synthetic.biped_inputs(seed + 1, batch, N)
+    for k in vals:  # the golden instance sits at positions 3 and 66
+        vals[k][3] = one[k][0]
+        vals[k][66] = one[k][0]
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    assert form.given_len == 8 + 2 * N
+    out = form.generate_all_qp_matrices_batched(given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")})
+    for b in (3, 66):
+        got = tuple(x[b].cpu().numpy() for x in (out.G, out.h, out.P, out.q))
+        cases.assert_digest_close(got, g, "n%d_" % N, seed)
+    other = tuple(x[5].cpu().numpy() for x in (out.G, out.h, out.P, out.q))
+    params5 = {k: float(vals[k][5]) for k in ("omega", "vel_x", "vel_y")}
+    cases.assert_qp_close(other, orc.all_qp_matrices(form, given[5][:, None], params5))

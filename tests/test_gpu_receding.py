@@ -70,8 +70,11 @@ def test_structure_buckets_against_oracle(N):
     assert len(buckets) == seen
 
 
-def test_preview_all_and_advance_collector():
-    """The rest of the example's tick (biped_mpc_loop.py:62-65, :81-92) for a batch:
+@pytest.mark.parametrize("N", [24, 100])
+def test_preview_all_and_advance_collector(N):
+    """N = 100 is the size the bench runs at: [given; optim; 1] has 427 columns, which
+    the sparse-row kernel stages in two column passes (round-1 advisor finding).
+    The rest of the example's tick (biped_mpc_loop.py:62-65, :81-92) for a batch:
     every definition previewed in one launch, the next initial state read off
     the horizon (row 0 of the LIP states, row 1 of the step positions), the
     bias passed through; against the oracle's preview matrices and the loop's
@@ -81,7 +84,7 @@ def test_preview_all_and_advance_collector():
     from mpc_interface_b200.examples.biped import default_configuration, formulate_biped
     from mpc_interface_b200.receding import advance_collector
 
-    N, batch = 24, 45
+    batch = 45
     form = formulate_biped(default_configuration(N), omega=Param("omega"),
                            target_vel=[Param("vel_x"), Param("vel_y")])
     vals = synthetic.biped_inputs(11, batch, N)

@@ -82,3 +82,63 @@ def test_generic(cpu_extend, name):
         one = {k: float(v[b]) for k, v in params.items()}
         got = orc.all_qp_matrices(form, given[b][:, None], one)
         cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]), 1e-12)
+
+
+def test_port_against_digests_at_the_baseline_shapes(cpu_extend):
+    """The port at the C4 shape with per-instance plants and the host mirror + plan
+    compiler at a long biped horizon, against digests of reference output."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+
+    g = cases.golden("generic_c4_perinst_digest")
+    for b in (0, 7):
+        form = cases.formulate_generic(g["A_sys"][b], g["B_sys"][b], g["Q_w"], g["R_w"], int(g["N"]),
+                                       g["rows"], refs=list(g["ref"][b]), backend=NumpyBackend())
+        got = orc.all_qp_matrices(form, g["x0"][b][:, None])
+        cases.assert_digest_close(got, g, "i%d_" % b, int(g["seed"]) + b, 1e-12)
+    g = cases.golden("biped_long_digest")
+    N, seed = 200, int(g["seed"]) + 200
+    form = cases.formulate_biped(cases.default_configuration(N), omega=Param("omega"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")], backend=NumpyBackend())
+    vals = synthetic.biped_inputs(seed, 1, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, 1)
+    out = form.generate_all_qp_matrices_batched(given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")})
+    cases.assert_digest_close((out.G[0], out.h[0], out.P[0], out.q[0]), g, "n200_", seed, 1e-12)
+
+
+def test_live_reference_pins_the_port_and_the_generic_recipes():
+    """Where a reference tree is present: the port equals the unmodified reference on fresh
+    random instances (not only on the stored goldens), and the two ways of driving the
+    reference for per-instance plants (fresh formulation / re-incorporated dynamics) give
+    the same bits."""
+    from oracle import reference
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+    import mpc_interface_b200.tools as tools
+
+    if not reference.available():
+        pytest.skip("no reference tree here")
+    old, tools.extend_matrices = tools.extend_matrices, orc.extend_matrices
+    try:
+        N, B = 24, 5
+        form = cases.formulate_biped(cases.default_configuration(N), omega=Param("omega"),
+                                     target_vel=[Param("vel_x"), Param("vel_y")], backend=NumpyBackend())
+        vals = synthetic.biped_inputs(77, B, N)
+        given = synthetic.pack_given(form.given_ID, form.given_len, vals, B)
+        ref_form = reference.biped_form(N)
+        for b in range(B):
+            one = {k: float(vals[k][b]) for k in ("omega", "vel_x", "vel_y")}
+            cases.assert_qp_close(orc.all_qp_matrices(form, given[b][:, None], one),
+                                  reference.biped_instance(ref_form, vals, b), 1e-13)
+    finally:
+        tools.extend_matrices = old
+    nx, nu, H = 4, 2, 9
+    _, _, Q, R = synthetic.generic_system(5, nx, nu)
+    A, Bm = synthetic.generic_plants(5, 3, nx, nu)
+    v = synthetic.generic_inputs(5, 3, nx)
+    rows = np.random.default_rng(6).normal(size=[2, nx])
+    plants = reference.GenericPlants(A[0], Bm[0], Q, R, H, rows)
+    for b in range(3):
+        fresh = reference.generic_instance(A[b], Bm[b], Q, R, H, rows, v["ref"][b], v["x0"][b])
+        again = plants.instance(A[b], Bm[b], v["ref"][b], v["x0"][b])
+        assert all(np.array_equal(x, y) for x, y in zip(fresh, again))
