@@ -1,6 +1,8 @@
 // Measured ceilings of one B200 for the roofline denominators of this repo (one JSON line):
-//   hbm_fill_gbs   write-only stream: a plain double2 fill of 8 GiB (16-byte streaming
-//                  stores, one pass, no reads) -- what the P / G streams are up against
+//   hbm_fill_gbs   write-only stream: 8 GiB of 16-byte streaming stores, one pass, no reads --
+//                  what the P / G streams are up against; the best of a grid-stride fill, a
+//                  fill that walks 32 rows per thread (the stores of stream_terms_kernel
+//                  without its arithmetic) and cudaMemsetAsync
 //   hbm_copy_gbs   read + write bytes of a double2 copy of 4 GiB -> 4 GiB (the quantity
 //                  MEASURED_PEAKS.json reports from a torch copy)
 //   fp64_dmma_tflops / fp64_dfma_tflops   register-resident DMMA.8x8x4 / DFMA loops
@@ -21,6 +23,19 @@ __global__ void fill_kernel(double2* __restrict__ out, long n_vec, double v) {
   const long stride = (long)gridDim.x * blockDim.x;
   const double2 val = make_double2(v, -v);
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec; i += stride) __stcs(out + i, val);
+}
+
+// one 16-byte store per thread, consecutive threads on consecutive vectors; ROWS rows of
+// `pitch` vectors per thread (the access pattern of stream_terms_kernel: a thread walks
+// down a column of a [rows][pitch] array, a warp covers 512 contiguous bytes per row)
+template <int ROWS>
+__global__ void fill_rows_kernel(double2* __restrict__ out, long pitch, double v) {
+  const long col = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= pitch) return;
+  double2* dst = out + (long)blockIdx.y * ROWS * pitch + col;
+  const double2 val = make_double2(v, -v);
+#pragma unroll 4
+  for (int r = 0; r < ROWS; ++r) { __stcs(dst, val); dst += pitch; }
 }
 
 __global__ void copy_kernel(const double2* __restrict__ in, double2* __restrict__ out, long n_vec) {
@@ -66,7 +81,7 @@ int main(int argc, char** argv) {
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-  double fill = 0, copy = 0, dmma = 0, dfma = 0, d2h = 0;
+  double fill = 0, fill_rows = 0, fill_memset = 0, copy = 0, dmma = 0, dfma = 0, d2h = 0;
 
   if (!d2h_only) {
     const long bytes = 8L << 30, n_vec = bytes / 16;
@@ -80,6 +95,23 @@ int main(int argc, char** argv) {
         float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
         if (rep && bytes / ms / 1e6 > fill) fill = bytes / ms / 1e6;
       }
+    // the same bytes as [rows][pitch] with 32 rows per thread (pitch = 1 MiB of vectors)
+    for (int rep = 0; rep < 11; ++rep) {
+      const long pitch = 65536;
+      dim3 grid((unsigned)(pitch / 256), (unsigned)(n_vec / pitch / 32));
+      CK(cudaEventRecord(e0));
+      fill_rows_kernel<32><<<grid, 256>>>(buf, pitch, 1.0 + rep);
+      CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+      float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+      if (rep && bytes / ms / 1e6 > fill_rows) fill_rows = bytes / ms / 1e6;
+    }
+    for (int rep = 0; rep < 11; ++rep) {
+      CK(cudaEventRecord(e0));
+      CK(cudaMemsetAsync(buf, rep, bytes, 0));
+      CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+      float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+      if (rep && bytes / ms / 1e6 > fill_memset) fill_memset = bytes / ms / 1e6;
+    }
     for (int blocks_per_sm : {4, 8, 16})
       for (int rep = 0; rep < 11; ++rep) {
         CK(cudaEventRecord(e0));
@@ -124,8 +156,11 @@ int main(int argc, char** argv) {
     if (d2h_only) d2h = sum / reps;  // sustained mean when several GPUs copy at once
     CK(cudaFreeHost(host)); CK(cudaFree(dev));
   }
-  printf("{\"sms\": %d, \"hbm_fill_gbs\": %.1f, \"hbm_copy_gbs\": %.1f, \"fp64_dmma_tflops\": %.2f, "
+  const double fill_best = fill > fill_rows ? (fill > fill_memset ? fill : fill_memset)
+                                            : (fill_rows > fill_memset ? fill_rows : fill_memset);
+  printf("{\"sms\": %d, \"hbm_fill_gbs\": %.1f, \"fill_grid_stride_gbs\": %.1f, \"fill_rows_gbs\": %.1f, "
+         "\"fill_memset_gbs\": %.1f, \"hbm_copy_gbs\": %.1f, \"fp64_dmma_tflops\": %.2f, "
          "\"fp64_dfma_tflops\": %.2f, \"d2h_pinned_gbs\": %.2f, \"d2h_only\": %d}\n",
-         sms, fill, copy, dmma, dfma, d2h, d2h_only);
+         sms, fill_best, fill, fill_rows, fill_memset, copy, dmma, dfma, d2h, d2h_only);
   return 0;
 }

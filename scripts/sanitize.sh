@@ -9,7 +9,7 @@ LTI="python scripts/bench_lti.py --config small --batch 48 --reps 1"
 for tool in memcheck racecheck; do
   for what in smoke lti; do
     if [ $what = smoke ]; then CMD=$SMOKE; else CMD=$LTI; fi
-    timeout 900 compute-sanitizer --tool $tool --print-limit 20 $CMD > gpurun_out/sanitizer_${tool}_${what}.log 2>&1
+    timeout 400 compute-sanitizer --tool $tool --print-limit 20 $CMD > gpurun_out/sanitizer_${tool}_${what}.log 2>&1
     echo "$tool $what exit $?"; grep -E "ERROR SUMMARY|RACECHECK SUMMARY|smoke ok" gpurun_out/sanitizer_${tool}_${what}.log | tail -3
   done
 done
