@@ -223,6 +223,11 @@ typedef struct {
   const double* grp_cu;    /* [n_groups][m]                                   */
   const double* grp_arrow; /* [n_groups][N]                                   */
   const double* grp_bound; /* [n_groups][N]                                   */
+  /* rows of every group: horizon samples grp_k0[g] .. grp_k0[g] + grp_rows[g] - 1 (a
+   * limit's `schedule`, body.py:246; restrictions.py:147-162).  NULL = all N samples.
+   * nc = sum of grp_rows; the tables above stay [n_groups][N], indexed by the sample. */
+  const int* grp_k0;       /* [n_groups] or NULL                              */
+  const int* grp_rows;     /* [n_groups] or NULL                              */
 } mpci_lti_desc;
 
 typedef struct mpci_lti_plan mpci_lti_plan;
@@ -244,6 +249,39 @@ int mpci_lti_assemble(const mpci_lti_plan* plan, const double* A_dev, long strid
                       const double* B_dev, long strideB, const double* x0_dev,
                       const double* scalars_dev, double* P_dev, double* q_dev, double* G_dev,
                       double* h_dev, long batch, int hessian_mode, void* stream);
+
+/* Per-instance tables: cost weights, form coefficients or bounds that differ between the
+ * instances (a `Param` inside a LineCombo / Cost / Constraint of a formulation lowered to
+ * this path: e.g. the LIP's CoP  b = CoM - CoM_ddot / omega_b^2  with one omega per robot).
+ * Every non-NULL pointer replaces the plan's table of the same name for this call; its
+ * instance stride is the table size (Qxx [batch][n][n], Quu [batch][m][m], tx [batch][n]
+ * and tu [batch][m] -- the offsets of the gradient, replacing Tx / Tu x scalars --,
+ * cx [batch][n_groups][n], cu [batch][n_groups][m], bound [batch][n_groups][N]).
+ * Device pointers.  The plan must have been created with n_scalars = 0 when tx / tu are
+ * given, and with non-zero grp_cx entries wherever an instance's cx may be non-zero.      */
+typedef struct {
+  const double* Qxx;
+  const double* Quu;
+  const double* tx;
+  const double* tu;
+  const double* cx;
+  const double* cu;
+  const double* bound;
+} mpci_lti_tables;
+int mpci_lti_assemble_ex(const mpci_lti_plan* plan, const double* A_dev, long strideA,
+                         const double* B_dev, long strideB, const double* x0_dev,
+                         const double* scalars_dev, const mpci_lti_tables* per_instance,
+                         double* P_dev, double* q_dev, double* G_dev, double* h_dev, long batch,
+                         int hessian_mode, void* stream);
+
+/* Closed forms of the reference's named LIP systems (tools.get_system_matrices,
+ * python/mpc_interface/tools.py:240-285: A = exp(G tau), B = int_0^tau exp(G t) dt h, there
+ * by SymPy) for a batch with one sampling period and one pendulum frequency per instance:
+ * system 0 "J->CCC", 1 "P->CC", 2 "P->X", 3 "dP->CCC", 4 "dP->CCP".
+ * tau_dev / omega_dev [batch] (stride 0 = one value for the batch; omega may be NULL for
+ * system 0); A_dev [batch][n][n], B_dev [batch][n][1], n = 3, 2, 1, 3, 3.                  */
+int mpci_named_system(int system, const double* tau_dev, long stride_tau, const double* omega_dev,
+                      long stride_omega, double* A_dev, double* B_dev, long batch, void* stream);
 
 /* Same with HOST buffers (pinned memory gives full PCIe speed): inputs go to the device
  * and results come back in chunks of `chunk` instances on two streams.  The plan owns the

@@ -276,25 +276,21 @@ class Formulation:
         return given.reshape([1, self.given_len])
 
     def preview(self, given, optim, variable, axes=None):
-        """Value of a variable along the horizon (body.py:209-219)."""
-        if axes is None:
-            Mg, Mo = self.PM[variable]
-            return Mg @ given + Mo @ optim
-        columns = []
-        for axis in axes:
-            Mg, Mo = self.PM[variable + axis]
-            columns.append(Mg @ given + Mo @ optim)
-        return np.hstack(columns)
+        """Value of a variable along the horizon (body.py:209-219): ``Mg @ given + Mo @ optim``
+        -- a batch of one through the device preview plan (the sparse-row kernel), returned
+        like the reference's: a column [rows, 1] (``axes`` None) or [rows, len(axes)]."""
+        given = np.asarray(given, dtype=np.float64).reshape(1, self.given_len)
+        optim = np.asarray(optim, dtype=np.float64).reshape(1, self.optim_len)
+        values = self.preview_batched(given, optim, variable, axes)
+        values = values.cpu().numpy()[0]
+        return values.reshape(-1, 1) if axes is None else values
 
     def goal_distance(self, given, optim, goal_name):
-        """Squared distance to the aim of one goal (body.py:221-229)."""
-        goal = self.goals[goal_name]
-        value = 0
-        for i, axis in enumerate(goal.axes):
-            Mg, Mo = self.PM[goal.variable + axis]
-            gap = Mg @ given + Mo @ optim - goal.aim[:, i]
-            value += gap.T @ gap
-        return float(value)
+        """Squared distance to the aim of one goal (body.py:221-229), a batch of one through
+        ``goal_distance_batched`` (preview rows + the reduction kernel)."""
+        given = np.asarray(given, dtype=np.float64).reshape(1, self.given_len)
+        optim = np.asarray(optim, dtype=np.float64).reshape(1, self.optim_len)
+        return float(self.goal_distance_batched(given, optim, goal_name).cpu().numpy()[0])
 
     def full_goal_distance(self, given, optim):
         return sum(self.goal_distance(given, optim, name) for name in self.goals)
@@ -361,6 +357,10 @@ class Formulation:
                    built with (the formulation then only fixes the structure);
                    everything, prediction matrices included, is computed per
                    instance by the fused kernel of csrc/mpci_lti.cu (lti.py).
+                   ``{name: (system_name, tau, omega)}`` builds the plants of a named
+                   LIP system on the GPU from one sampling period / pendulum
+                   frequency per instance (``ControlSystem.from_name``,
+                   dynamics.py:380-407, for a whole batch).
         hessian  : with ``dynamics``: "dmma" (dense contraction on the FP64 tensor
                    cores) or "recursion" (displacement recursion, O(N^2) flops)
 
@@ -380,9 +380,13 @@ class Formulation:
 
         if len(dynamics) != 1:
             raise NotImplementedError("exactly one dynamics can vary per instance")
-        (name, (A, B)), = dynamics.items()
+        (name, spec), = dynamics.items()
         if name not in self.dynamics:
             raise KeyError("no dynamics named '{}' was incorporated".format(name))
+        if isinstance(spec[0], str):
+            A, B = lti.named_system_batched(spec[0], *spec[1:])
+        else:
+            A, B = spec
         modes = {"dmma": lti.HESSIAN_DMMA, "recursion": lti.HESSIAN_RECURSION}
         if hessian not in modes:
             raise ValueError("hessian must be 'dmma' or 'recursion'")
@@ -424,7 +428,7 @@ class Formulation:
             return values
         return values.reshape(batch, len(names), pplan.rows[0]).transpose(1, 2)
 
-    def preview_all_batched(self, given, optim, names=None, params=None):
+    def preview_all_batched(self, given, optim, names=None, params=None, scalars=None):
         """Batched form of the example loop's ``preview_all`` (biped_mpc_loop.py:62-65):
         ``{name: CUDA tensor [B, rows]}`` for every definition (or for ``names``),
         all of them from ONE launch of the sparse-row kernel (the variables may have
@@ -432,7 +436,8 @@ class Formulation:
         names = list(self.definitions) if names is None else list(names)
         compiled, pplan = self._preview_plan(names)
         gz, batch = self._given_optim(given, optim)
-        scalars = compiled.slots.evaluate(params or {}, batch)
+        if scalars is None:  # else: a CUDA tensor [B, n_slots] evaluated by the caller
+            scalars = compiled.slots.evaluate(params or {}, batch)
         values = self._ops().preview(pplan, scalars, gz, batch)
         out, at = {}, 0
         for name, rows in zip(names, pplan.rows):

@@ -43,9 +43,20 @@ struct LtiArgs {
   int LDw;  // row length of wz, likewise
   int per_sm;  // resident CTAs per SM of this launch
   int sms;  // SMs of the device (CTA i shares an SM with i + sms, i + 2 sms, ...)
-  int scan; // recursion mode: 1 = DMMA row bands + diagonal scan (needs tb / prev), 0 = plain
+  int scan; // recursion mode: 1 = DMMA row bands + diagonal scan (needs tb / prev), 0 = plain,
+            // 2 = whole rows per warp (short horizons, hessian_rows)
+  int ldp;  // scan == 2: row length (doubles) of a warp's T patch
+  int scan_warps;  // scan == 2: warps that own a T patch (the others do not take Hessian items)
+  int aux;  // doubles of the aux region (row windows of the constraint phase / T patches)
   const double *Qxx, *Quu, *Tx, *Tu, *cx, *cu, *arrow, *bound;  // device tables
+  // instance strides of the tables (doubles; 0 = one table for the batch): per-instance
+  // cost weights / form coefficients / bounds (mpci_lti_assemble_ex)
+  long sQ, sR, sTx, sTu, scx, scu, sbd;
   const int* grp_state;  // bit 0: the group has a non-zero cx; bit 1: one arrow for all rows
+  const int* grp_k0;     // first horizon sample of the group's rows (a limit's schedule)
+  const int* grp_cnt;    // number of rows of the group
+  const int* grp_row0;   // first row of the group in G / h
+  int nc;                // rows of G / h: sum of grp_cnt
   const int2* tiles;     // DMMA warp tiles (row tile, column tile) of one (j, j') block, longest first
   int n_tiles;
   const double *A, *B, *x0, *scalars;
@@ -56,7 +67,7 @@ struct LtiArgs {
 };
 
 struct Smem {
-  double *A, *M0, *M1, *Q, *gz, *wz, *r, *tx, *tu, *cg, *tb;
+  double *A, *M0, *M1, *Q, *R, *gz, *wz, *r, *tx, *tu, *cg, *tb;
   int* next_item;  // work counter of the Hessian scan (warps fetch items as they get free)
 };
 
@@ -76,11 +87,21 @@ __host__ __device__ inline size_t lti_wz_doubles(int n, int m, int LDw) {
 __host__ __device__ inline size_t lti_r_doubles(int n, int N) { return ((size_t)n * N + 1) & ~(size_t)1; }
 // aux: the constraint phase's row windows and group tables (cg) and, in the scan, the
 // warps' T patches (tb) share one region -- the two phases never run at the same time
-__host__ __device__ inline size_t lti_aux_doubles(int n, int m, int N, int scan, int warps) {
-  const size_t cg = (size_t)2 * 4 * m * N, tb = scan ? (size_t)warps * 8 * 40 : 0;  // two window sets
-  return ((cg > tb ? cg : tb) + 1) & ~(size_t)1;
+__host__ __device__ inline size_t lti_aux_doubles(int m, int N, size_t patches) {
+  const size_t cg = (size_t)2 * 4 * m * N;  // two window sets; `patches` = doubles of the T patches
+  return ((cg > patches ? cg : patches) + 1) & ~(size_t)1;
 }
-__host__ __device__ inline size_t lti_mats_doubles(int n) { return (size_t)4 * n * n; }
+// hessian_rows: a T patch is 8 rows of ldp doubles, ldp = 8 * ceil(N / 8) bumped to 8 (mod 16)
+// so that the double2 stores of the DMMA fragments (rows g, g+1 per quarter-warp) do not
+// collide on a bank
+__host__ __device__ inline int lti_rows_ldp(int N) {
+  int x = (N + 7) / 8 * 8;
+  while (x % 16 != 8) x += 8;
+  return x;
+}
+__host__ __device__ inline size_t lti_mats_doubles(int n, int m) {  // A, M0, M1, Qxx | Quu
+  return (size_t)4 * n * n + (((size_t)m * m + 1) & ~(size_t)1);
+}
 __host__ __device__ inline size_t lti_gz_doubles(int n, int m, int LD) {
   return ((size_t)n * (m + 1) * LD + 1) & ~(size_t)1;
 }
@@ -91,10 +112,9 @@ __host__ __device__ inline int lti_skew(int LD, int rows) {
     if ((rows * x) % 16 == 4 || (rows * x) % 16 == 12) return x;
   return LD;
 }
-__host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD, int LDw, int scan,
-                                                   int warps) {
-  return lti_mats_doubles(n) + lti_gz_doubles(n, m, LD) + lti_wz_doubles(n, m, LDw) +
-         lti_r_doubles(n, N) + lti_aux_doubles(n, m, N, scan, warps) + n + m + 2;
+__host__ __device__ inline size_t lti_smem_doubles(int n, int m, int N, int LD, int LDw, size_t aux) {
+  return lti_mats_doubles(n, m) + lti_gz_doubles(n, m, LD) + lti_wz_doubles(n, m, LDw) +
+         lti_r_doubles(n, N) + aux + n + m + 2;
 }
 
 __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
@@ -104,12 +124,13 @@ __device__ __forceinline__ Smem carve(double* base, const LtiArgs& a) {
   s.M0 = s.A + n * n;
   s.M1 = s.M0 + n * n;
   s.Q = s.M1 + n * n;
-  s.gz = base + lti_mats_doubles(n);
+  s.R = s.Q + n * n;
+  s.gz = base + lti_mats_doubles(n, m);
   s.wz = s.gz + lti_gz_doubles(n, m, a.LD);
   s.r = s.wz + lti_wz_doubles(n, m, a.LDw);
   s.tb = s.r + lti_r_doubles(n, N);  // 16-byte aligned: double2 stores of the T tiles,
   s.cg = s.tb;                       // source of the bulk copies
-  s.tx = s.tb + lti_aux_doubles(n, m, N, a.scan, (int)blockDim.x >> 5);
+  s.tx = s.tb + a.aux;
   s.tu = s.tx + n;
   s.next_item = reinterpret_cast<int*>(s.tu + m);
   return s;
@@ -164,8 +185,9 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     const double v = Ab[e];
     s.A[e] = v;
     s.M0[e] = v;
-    s.Q[e] = a.Qxx[e];
+    s.Q[e] = a.Qxx[b * a.sQ + e];
   }
+  for (int e = tid; e < m * m; e += (int)blockDim.x) s.R[e] = a.Quu[b * a.sR + e];
   if (tid == 0) *s.next_item = 0;
   // d = 0 of every row, and the zeros before it (causality of the DMMA operands)
   for (int e = tid; e < n * w; e += (int)blockDim.x) {
@@ -180,7 +202,8 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   }
   // per-instance offsets of the gradient: t = T[:, S] + T[:, :S] @ scalars_b
   for (int e = tid; e < n + m; e += (int)blockDim.x) {
-    const double* T = (e < n) ? a.Tx + (long)e * (a.S + 1) : a.Tu + (long)(e - n) * (a.S + 1);
+    const double* T = (e < n) ? a.Tx + b * a.sTx + (long)e * (a.S + 1)
+                              : a.Tu + b * a.sTu + (long)(e - n) * (a.S + 1);
     double acc = T[a.S];
 #pragma unroll 4
     for (int k = 0; k < a.S; ++k) acc = fma(T[k], a.scalars[b * a.S + k], acc);
@@ -321,7 +344,7 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
       }
     }
     // epilogue: + Quu[j][j'] on the diagonal of the block, store
-    const double ruu = a.Quu[j * m + jp];
+    const double ruu = s.R[j * m + jp];
 #pragma unroll
     for (int x = 0; x < TM; ++x) {
       const int p = p0 + 8 * x + g;
@@ -391,7 +414,7 @@ __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __res
 #pragma unroll
         for (int y = 0; y < M; ++y)
           __stcs(dst + (size_t)x * N * nv + y * N,
-                 delta == 0 ? acc[x][y] + a.Quu[x * M + y] : acc[x][y]);
+                 delta == 0 ? acc[x][y] + s.R[x * M + y] : acc[x][y]);
     }
   }
 }
@@ -410,7 +433,7 @@ __device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* _
     const int p_lo = has ? max(0, -delta) : N;
     const int w_hi = __reduce_max_sync(0xffffffffu, p_hi);
     const int w_lo = __reduce_min_sync(0xffffffffu, p_lo);
-    const double ruu = (delta == 0) ? a.Quu[j * m + jp] : 0.0;
+    const double ruu = (delta == 0) ? s.R[j * m + jp] : 0.0;
     double acc = 0.0;
     for (int p = w_hi; p >= w_lo; --p) {
       if (p > p_hi || p < p_lo) continue;
@@ -477,7 +500,7 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
     const long qstep = (long)nv + 1;
     // the running sum of the main diagonal starts at Quu[j][j']: every entry of that
     // diagonal then carries the + Quu delta_pc term, no separate add per entry
-    double carry = (delta == 0) ? a.Quu[j * m + jp] : 0.0;
+    double carry = (delta == 0) ? s.R[j * m + jp] : 0.0;
     for (; p0 + 7 >= p_last; p0 -= 8, ga += 8, wb += 8) {
       double acc[5][2];
 #pragma unroll
@@ -506,6 +529,130 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
       }
       __syncwarp();
     }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// phase 3d: the displacement recursion for short horizons (N <= 60)
+// The band scan above gives a lane one DIAGONAL; at N = 50 its 8 x 40 patches are 41-57 %
+// full (2N - 1 = 99 diagonals in chunks of 32, triangles at both ends) and the warp spends
+// its issue slots on empty slots.  Here a warp owns a whole (j, j') block and a lane two
+// adjacent COLUMNS (2 lane, 2 lane + 1) of it: the band's T patch is 8 rows x N columns --
+// every slot is used -- and per row of the block the lane does one LDS.128, one shuffle
+// (column 2 lane + 2 of the row below lives in lane + 1), two DADDs and one 16-byte store:
+//   P[p][c] = T[p][c] + P[p+1][c+1],   T[p][c] = Gam_{N-1-p}[:,j] . W_{N-1-c}[:,j']
+// The + Quu[j][j'] of the main diagonal enters as the virtual entry P[N][N] = Quu.  Only
+// the first a.scan_warps warps own a patch (shared memory is what limits the CTAs per SM);
+// the last warp runs the adjoint recursion of q meanwhile.  Operand loads of rows p < 0
+// and columns >= N are not bounds-checked: they stay inside the CTA's shared memory and
+// only reach T entries nobody reads (as in hessian_scan).
+// ---------------------------------------------------------------------------
+// NT column tiles (8 x 8 each) of the band's T patch: K = n in steps of 4, operands straight
+// from the Toeplitz generators (one LDS each), results parked in the warp's patch
+template <bool KFULL, int NT>
+__device__ __forceinline__ void rows_tiles(const double* gk, const double* wk, long ga_step, long wb_step,
+                                           int n, int t, double2* dst) {
+  double acc[NT][2];
+#pragma unroll
+  for (int y = 0; y < NT; ++y) acc[y][0] = acc[y][1] = 0.0;
+  for (int ks = 0; ks < (n >> 2); ++ks, gk += ga_step, wk += wb_step) {
+    const double av = gk[0];
+    double bv[NT];
+#pragma unroll
+    for (int y = 0; y < NT; ++y) bv[y] = wk[-8 * y];
+#pragma unroll
+    for (int y = 0; y < NT; ++y) dmma8x8x4(acc[y][0], acc[y][1], av, bv[y]);
+  }
+  if (!KFULL) {  // the last, partial step of K: states past n contribute exact zeros
+    const bool k_ok = (n & ~3) + t < n;
+    const double av = k_ok ? gk[0] : 0.0;
+    double bv[NT];
+#pragma unroll
+    for (int y = 0; y < NT; ++y) bv[y] = k_ok ? wk[-8 * y] : 0.0;
+#pragma unroll
+    for (int y = 0; y < NT; ++y) dmma8x8x4(acc[y][0], acc[y][1], av, bv[y]);
+  }
+#pragma unroll
+  for (int y = 0; y < NT; ++y) dst[4 * y] = make_double2(acc[y][0], acc[y][1]);
+}
+
+template <bool KFULL, int CT>
+__device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1, LDP = a.ldp;
+  const long nv = (long)a.m * a.N;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (warp >= a.scan_warps) return;
+  const int g = lane >> 2, t = lane & 3;
+  double* tw = s.tb + (size_t)warp * 8 * LDP;
+  double2* tst = reinterpret_cast<double2*>(tw + g * LDP + 2 * t);  // this lane's C slots of tile 0
+  const double* trow = tw + 2 * lane;                                 // this lane's two columns
+  const long ga_step = (long)4 * w * LD, wb_step = (long)4 * m * a.LDw;
+  const int col = 2 * lane;
+  const bool act0 = col < N, act1 = col + 1 < N;
+  const bool vec = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0);
+  constexpr int T0 = CT < 4 ? CT : 4, T1 = CT - T0;  // two groups of tiles (register budget)
+
+  // one row of the block: the lane's two entries from the patch row, the carries of the
+  // row below (column 2 lane + 2 lives in lane + 1), a 16-byte store.  Lanes past the
+  // block read nothing and keep their carries at zero.
+  auto row_step = [&](const double* trow_r, double& c0, double& c1, double* dst) {
+    double2 tv = make_double2(0.0, 0.0);
+    if (act0) tv = *reinterpret_cast<const double2*>(trow_r);
+    if (!act1) tv.y = 0.0;
+    const double up = __shfl_down_sync(0xffffffffu, c0, 1);
+    const double n0 = tv.x + c1, n1 = tv.y + up;
+    c0 = n0;
+    c1 = n1;
+    if (vec) {
+      if (act0) __stcs(reinterpret_cast<double2*>(dst), make_double2(n0, n1));
+    } else {
+      if (act0) __stcs(dst, n0);
+      if (act1) __stcs(dst + 1, n1);
+    }
+  };
+
+  for (;;) {
+    int item = 0;
+    if (lane == 0) item = atomicAdd(s.next_item, 1);
+    item = __shfl_sync(0xffffffffu, item, 0);
+    if (item >= m * m) break;
+    const int j = item / m, jp = item - j * m;
+    const double ruu = s.R[j * m + jp];
+    // carries = row p + 1 of the block in columns 2 lane, 2 lane + 1; the virtual P[N][N] = Quu
+    double c0 = (col == N) ? ruu : 0.0, c1 = (col + 1 == N) ? ruu : 0.0;
+    const double* ga = s.gz + (size_t)(t * w + j) * LD + a.pad + (7 - g);           // band p0 = N - 8
+    const double* wb = s.wz + (size_t)(t * m + jp) * a.LDw + a.pad + (N - 1 - g);
+    double* dst = Pb + (size_t)(j * N + N - 1) * nv + (size_t)jp * N + col;        // row N - 1
+    int p0 = N - 8;
+    for (; p0 >= 0; p0 -= 8, ga += 8) {  // full bands: rows p0 .. p0 + 7, bottom band first
+      rows_tiles<KFULL, T0>(ga, wb, ga_step, wb_step, n, t, tst);
+      if (T1 > 0) rows_tiles<KFULL, (T1 > 0 ? T1 : 1)>(ga, wb - 32, ga_step, wb_step, n, t, tst + 16);
+      __syncwarp();
+#pragma unroll
+      for (int r = 7; r >= 0; --r, dst -= nv) row_step(trow + r * LDP, c0, c1, dst);
+      __syncwarp();
+    }
+    if (p0 > -8) {  // the top band overhangs row 0: rows 0 .. p0 + 7
+      rows_tiles<KFULL, T0>(ga, wb, ga_step, wb_step, n, t, tst);
+      if (T1 > 0) rows_tiles<KFULL, (T1 > 0 ? T1 : 1)>(ga, wb - 32, ga_step, wb_step, n, t, tst + 16);
+      __syncwarp();
+      for (int r = 7; r >= -p0; --r, dst -= nv) row_step(trow + r * LDP, c0, c1, dst);
+      __syncwarp();
+    }
+  }
+}
+
+template <bool KFULL>
+__device__ void hessian_rows_any(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
+  switch ((a.N + 7) >> 3) {  // column tiles of a block (N <= 60)
+    case 1: return hessian_rows<KFULL, 1>(a, s, Pb);
+    case 2: return hessian_rows<KFULL, 2>(a, s, Pb);
+    case 3: return hessian_rows<KFULL, 3>(a, s, Pb);
+    case 4: return hessian_rows<KFULL, 4>(a, s, Pb);
+    case 5: return hessian_rows<KFULL, 5>(a, s, Pb);
+    case 6: return hessian_rows<KFULL, 6>(a, s, Pb);
+    case 7: return hessian_rows<KFULL, 7>(a, s, Pb);
+    default: return hessian_rows<KFULL, 8>(a, s, Pb);
   }
 }
 
@@ -598,18 +745,21 @@ __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wa
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 
 // windows and h entries of one group, by the threads tid = 0 .. nthreads-1
-__device__ __forceinline__ void group_windows(const LtiArgs& a, const Smem& s, int grp, double* cz,
+__device__ __forceinline__ void group_windows(const LtiArgs& a, const Smem& s, long b, int grp, double* cz,
                                               double* cz1, bool bulk, double* __restrict__ hb, int tid,
                                               int nthreads, unsigned magic_2N) {
   const int n = a.n, m = a.m, N = a.N, czld = 2 * N;
   const int gstride = (m + 1) * a.LD;
   const bool state = (a.grp_state[grp] & 1) != 0;
   const double* arrow = a.arrow + (size_t)grp * N;
-  const double* cx = a.cx + (size_t)grp * n;  // warp-uniform global reads (L1 hits)
-  const double scale = bulk ? __ldg(arrow) : 1.0;
+  const double* cx = a.cx + b * a.scx + (size_t)grp * n;  // warp-uniform global reads (L1 hits)
+  const double* cu = a.cu + b * a.scu + (size_t)grp * m;
+  const double* bound = a.bound + b * a.sbd + (size_t)grp * N;
+  const int k0 = a.grp_k0[grp], k1 = k0 + a.grp_cnt[grp];
+  const double scale = bulk ? __ldg(arrow + k0) : 1.0;
   for (int e = tid; e < m * 2 * N; e += nthreads) {  // y fastest
     const int j = magic_div(e, magic_2N), y = e - j * 2 * N;
-    double acc = (y == N - 1) ? __ldg(a.cu + (size_t)grp * m + j) : 0.0;
+    double acc = (y == N - 1) ? __ldg(cu + j) : 0.0;
     if (state && y < N) {
       const double* src = s.gz + j * a.LD + a.pad + (N - 1 - y);
 #pragma unroll 4
@@ -622,13 +772,14 @@ __device__ __forceinline__ void group_windows(const LtiArgs& a, const Smem& s, i
   }
   if (hb) {
     const double* fk = s.gz + m * a.LD + a.pad + 1;  // f_k[i] = fk[i (m+1) LD + k]
-    for (int k = tid; k < N; k += nthreads) {
+    double* hg = hb + a.grp_row0[grp] - k0;  // row of sample k: grp_row0 + (k - k0)
+    for (int k = k0 + tid; k < k1; k += nthreads) {
       double acc = 0.0;
       if (state) {
 #pragma unroll 4
         for (int i = 0; i < n; ++i) acc = fma(__ldg(cx + i), fk[i * gstride + k], acc);
       }
-      hb[(size_t)grp * N + k] = a.bound[(size_t)grp * N + k] - __ldg(arrow + k) * acc;
+      hg[k] = __ldg(bound + k) - __ldg(arrow + k) * acc;
     }
   }
 }
@@ -640,9 +791,10 @@ __device__ __forceinline__ void group_rows_by_warps(const LtiArgs& a, int grp, c
                                                     int nwarps, int lane) {
   const int m = a.m, N = a.N, nv = a.m * a.N;
   const double* arrow = a.arrow + (size_t)grp * N;
-  for (int k = warp; k < N; k += nwarps) {
+  const int k0 = a.grp_k0[grp], k1 = k0 + a.grp_cnt[grp];
+  for (int k = k0 + warp; k < k1; k += nwarps) {
     const double ak = __ldg(arrow + k);
-    double* row = rows + (size_t)k * nv;
+    double* row = rows + (size_t)(k - k0) * nv;
     const double* win = cz + (N - 1 - k);  // column c = j N + p reads win[c + j N]
     if (aligned) {
       for (int c = 2 * lane; c < nv; c += 64) {  // c and c+1 share j because N is even
@@ -660,7 +812,7 @@ __device__ __forceinline__ void group_rows_by_warps(const LtiArgs& a, int grp, c
   }
 }
 
-__device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restrict__ Gb,
+__device__ void constraint_rows(const LtiArgs& a, const Smem& s, long b, double* __restrict__ Gb,
                                 double* __restrict__ hb) {
   const int m = a.m, N = a.N, nv = a.m * a.N, tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5, nwarps = (int)blockDim.x >> 5;
@@ -681,21 +833,22 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, double* __restr
       bulk_wait_read<1>();
       __syncthreads();
     }
-    group_windows(a, s, grp, cz, cz1, bulk, hb, tid, (int)blockDim.x, magic_2N);
+    group_windows(a, s, b, grp, cz, cz1, bulk, hb, tid, (int)blockDim.x, magic_2N);
     fence_async_smem();  // the windows must be visible to the async proxy
     __syncthreads();
     if (!Gb) continue;
-    double* rows = Gb + (size_t)grp * N * nv;
+    double* rows = Gb + (size_t)a.grp_row0[grp] * nv;
+    const int k0 = a.grp_k0[grp], k1 = k0 + a.grp_cnt[grp];
     if (bulk) {
       // Short rows (< 2 kB per copy): every lane issues, the cost is the issue itself
       // (a single issuing warp per CTA fed through named barriers was measured at C4:
       // G, h 3.0 -> 4.3 ms).  Long rows: one lane per warp, so the rows in flight stay
       // close together in memory (C4 5.87 -> 5.53 ms with 32 lanes, C5 4.58 -> 4.43 ms with 1).
       const int issue_lanes = (N < 256) ? 32 : 1;
-      for (int k = warp + nwarps * lane; lane < issue_lanes && k < N; k += nwarps * issue_lanes) {
+      for (int k = k0 + warp + nwarps * lane; lane < issue_lanes && k < k1; k += nwarps * issue_lanes) {
         const int start = N - 1 - k;
         const double* win = (start & 1) ? cz1 + (start - 1) : cz + start;
-        double* row = rows + (size_t)k * nv;
+        double* row = rows + (size_t)(k - k0) * nv;
         for (int j = 0; j < m; ++j) bulk_store(row + j * N, win + j * czld, (unsigned)N * 8u);
       }
       bulk_commit();  // every lane commits (an empty group for the idle ones)
@@ -717,7 +870,7 @@ __global__ void __launch_bounds__(WIDE ? kWideThreads : kThreads,
 lti_assemble_kernel(LtiArgs a) {
   extern __shared__ double lti_smem[];
   const Smem s = carve(lti_smem, a);
-  const size_t nv = (size_t)a.m * a.N, nc = (size_t)a.n_groups * a.N;
+  const size_t nv = (size_t)a.m * a.N, nc = (size_t)a.nc;
   for (long b = blockIdx.x; b < a.batch; b += gridDim.x) {
     __syncthreads();  // the previous instance is done with shared memory
     build_prediction(a, s, b);
@@ -731,7 +884,7 @@ lti_assemble_kernel(LtiArgs a) {
     const bool g_first = MODE == MPCI_LTI_HESSIAN_RECURSION &&
                          (a.per_sm == 1 ? (blockIdx.x & 1) : ((blockIdx.x / a.sms) & 1));
     if (limits && g_first) {
-      constraint_rows(a, s, a.G ? a.G + (size_t)b * nc * nv : nullptr,
+      constraint_rows(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
                       a.h ? a.h + (size_t)b * nc : nullptr);
     }
     if (a.P && a.scan && limits) {  // aux: the windows must have been read before the T patches
@@ -742,10 +895,14 @@ lti_assemble_kernel(LtiArgs a) {
     // problems keep the all-threads correlation: their N sequential steps would not hide
     // under the few scan items)
     const bool adjoint = MODE == MPCI_LTI_HESSIAN_RECURSION && a.scan && a.n <= 32 && a.m * a.N >= 128;
-    if (adjoint && a.q && threadIdx.x < 32) gradient_costate(a, s, a.q + (size_t)b * nv);
+    // (rows mode: the last warp, which owns no T patch, runs it beside the Hessian warps)
+    const int adjoint_warp = (a.scan == 2 && a.scan_warps < ((int)blockDim.x >> 5)) ? ((int)blockDim.x >> 5) - 1 : 0;
+    if (adjoint && a.q && (threadIdx.x >> 5) == adjoint_warp) gradient_costate(a, s, a.q + (size_t)b * nv);
     if (a.P) {
       double* Pb = a.P + (size_t)b * nv * nv;
       if (MODE == MPCI_LTI_HESSIAN_DMMA) hessian_dmma(a, s, Pb);
+      else if (a.scan == 2 && a.n % 4 == 0) hessian_rows_any<true>(a, s, Pb);
+      else if (a.scan == 2) hessian_rows_any<false>(a, s, Pb);
       else if (a.scan && a.n % 4 == 0) hessian_scan<true>(a, s, Pb);
       else if (a.scan) hessian_scan<false>(a, s, Pb);
       else if (a.m == 1) hessian_recursion<1>(a, s, Pb);
@@ -756,13 +913,66 @@ lti_assemble_kernel(LtiArgs a) {
     }
     if (a.q && !adjoint) gradient(a, s, a.q + (size_t)b * nv);
     if (limits && !g_first)
-      constraint_rows(a, s, a.G ? a.G + (size_t)b * nc * nv : nullptr,
+      constraint_rows(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
                       a.h ? a.h + (size_t)b * nc : nullptr);
   }
   bulk_wait_all();  // bulk stores of the last rows
 }
 
 }  // namespace
+
+// ---------------------------------------------------------------------------
+// Closed forms of the named LIP systems (the reference derives them
+// with SymPy, tools.py:240-285 / :328-358): one thread per instance.
+// ---------------------------------------------------------------------------
+namespace {
+__global__ void named_system_kernel(int system, const double* __restrict__ tau, long st,
+                                    const double* __restrict__ omega, long sw, double* __restrict__ A,
+                                    double* __restrict__ B, long batch) {
+  const long b = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  const double T = tau[b * st];
+  const double w = omega ? omega[b * sw] : 0.0;
+  const double c = cosh(w * T), s = sinh(w * T);
+  if (system == 0) {  // J->CCC: jerk -> CoM, CoM_dot, CoM_ddot
+    double* a = A + b * 9;
+    a[0] = 1.0; a[1] = T; a[2] = T * T / 2; a[3] = 0.0; a[4] = 1.0; a[5] = T; a[6] = 0.0; a[7] = 0.0; a[8] = 1.0;
+    B[b * 3] = T * T * T / 6; B[b * 3 + 1] = T * T / 2; B[b * 3 + 2] = T;
+  } else if (system == 1) {  // P->CC: CoP -> CoM, CoM_dot
+    double* a = A + b * 4;
+    a[0] = c; a[1] = s / w; a[2] = w * s; a[3] = c;
+    B[b * 2] = 1.0 - c; B[b * 2 + 1] = -w * s;
+  } else if (system == 2) {  // P->X: CoP -> DCM
+    A[b] = exp(w * T);
+    B[b] = 1.0 - exp(w * T);
+  } else if (system == 3) {  // dP->CCC: CoP rate -> CoM, CoM_dot, CoM_ddot
+    double* a = A + b * 9;
+    a[0] = 1.0; a[1] = s / w; a[2] = (c - 1.0) / (w * w);
+    a[3] = 0.0; a[4] = c; a[5] = s / w;
+    a[6] = 0.0; a[7] = w * s; a[8] = c;
+    B[b * 3] = T - s / w; B[b * 3 + 1] = 1.0 - c; B[b * 3 + 2] = -w * s;
+  } else {  // dP->CCP: CoP rate -> CoM, CoM_dot, CoP
+    double* a = A + b * 9;
+    a[0] = c; a[1] = s / w; a[2] = 1.0 - c;
+    a[3] = w * s; a[4] = c; a[5] = -w * s;
+    a[6] = 0.0; a[7] = 0.0; a[8] = 1.0;
+    B[b * 3] = T - s / w; B[b * 3 + 1] = 1.0 - c; B[b * 3 + 2] = T;
+  }
+}
+}  // namespace
+
+extern "C" int mpci_named_system(int system, const double* tau, long stride_tau, const double* omega,
+                                 long stride_omega, double* A, double* B, long batch, void* stream) {
+  if (system < 0 || system > 4) return mpci::fail(-1, "named_system: unknown system %d", system);
+  if (batch < 0) return mpci::fail(-1, "named_system: negative batch");
+  if (batch == 0) return 0;
+  if (!tau || !A || !B || (system != 0 && !omega))
+    return mpci::fail(-3, "named_system: NULL argument");
+  named_system_kernel<<<(unsigned)((batch + 127) / 128), 128, 0, mpci::as_stream(stream)>>>(
+      system, tau, stride_tau, omega, stride_omega, A, B, batch);
+  MPCI_LAUNCH_CHECK("named_system_kernel");
+  return 0;
+}
 
 typedef void (*lti_kernel_t)(LtiArgs);
 static lti_kernel_t lti_kernel(int mode, int wide) {
@@ -782,12 +992,13 @@ static cudaError_t lti_opt_in_smem() {
 }
 
 struct mpci_lti_plan {
-  int n, m, N, S, n_groups;
+  int n, m, N, S, n_groups, nc;
   void* dev;  // one allocation holding every table
   LtiArgs args;  // table pointers and sizes filled in, per-call fields zero
   // per Hessian mode (index = MPCI_LTI_HESSIAN_*): the DMMA operands need kPadL zeros
   // before every generator row, the recursion does not and so fits more CTAs per SM
-  int pad[2], LD[2], LDw[2], scan;
+  int pad[2], LD[2], LDw[2], scan;  // scan: 0 plain, 1 band scan, 2 whole rows (N <= 64)
+  int aux[2], ldp, scan_warps;
   int threads[2];  // CTA size per mode: kThreads, or kWideThreads when one CTA per SM fits anyway
   size_t smem_bytes[2];
   int blocks_per_sm[2];
@@ -811,21 +1022,47 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   const int n = d->n, m = d->m, N = d->N, S = d->n_scalars, G = d->n_groups;
   const int pads[2] = {kPadL, 0};
   int LDs[2], LDws[2];
-  size_t smems[2];
+  size_t smems[2], auxs[2];
   for (int mode = 0; mode < 2; ++mode) {
     LDs[mode] = LDws[mode] = lti_row_len(N, pads[mode]);
-    smems[mode] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], 0, kWarps);
+    auxs[mode] = lti_aux_doubles(m, N, 0);
+    smems[mode] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], auxs[mode]);
   }
-  // the band scan of the recursion mode: skewed rows, the warps' T patches, and its
-  // unchecked operand loads reach 47 doubles before wz (hessian_scan)
+  // The DMMA scans of the recursion mode: skewed rows, the warps' T patches, and their
+  // unchecked operand loads reach 47 doubles before wz (hessian_scan / hessian_rows).
+  //   N <= 60: whole rows per warp (scan = 2); as many warps own a patch as fit without
+  //            costing a resident CTA (registers allow three CTAs per SM at most)
+  //   else:    32 diagonals per warp in bands of 8 rows (scan = 1)
   const int LDg_scan = lti_skew(LDs[1], m + 1), LDw_scan = lti_skew(LDs[1], m);
-  const size_t smem_scan = sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, 1, kWarps);
-  const int scan = smem_scan <= 227 * 1024 &&
-                   lti_mats_doubles(n) + lti_gz_doubles(n, m, LDg_scan) >= 48;
-  if (scan) {
-    smems[MPCI_LTI_HESSIAN_RECURSION] = smem_scan;
-    LDs[1] = LDg_scan;
-    LDws[1] = LDw_scan;
+  int scan = 0, ldp = 0, scan_warps = 0;
+  if (lti_mats_doubles(n, m) + lti_gz_doubles(n, m, LDg_scan) >= 48) {
+    auto bytes_with = [&](size_t patches) {
+      return sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, lti_aux_doubles(m, N, patches));
+    };
+    if (N <= 60) {  // (lane 31 must neither own a column nor hold the virtual P[N][N])
+      ldp = lti_rows_ldp(N);
+      const size_t patch = (size_t)8 * ldp;
+      auto ctas = [&](int sw) {
+        const size_t bytes = bytes_with(sw * patch);
+        return bytes > 227 * 1024 ? 0 : std::min(MPCI_LTI_MINBLOCKS, (int)(233472 / (bytes + 1024)));
+      };
+      const int target = ctas(4);
+      if (target >= 1) {
+        scan = 2;
+        scan_warps = 4;
+        while (scan_warps < kWarps && ctas(scan_warps + 1) >= target) ++scan_warps;
+        auxs[1] = lti_aux_doubles(m, N, scan_warps * patch);
+      }
+    }
+    if (!scan && bytes_with((size_t)kWarps * 8 * 40) <= 227 * 1024) {
+      scan = 1;
+      auxs[1] = lti_aux_doubles(m, N, (size_t)kWarps * 8 * 40);
+    }
+    if (scan) {
+      LDs[1] = LDg_scan;
+      LDws[1] = LDw_scan;
+      smems[1] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[1], LDws[1], auxs[1]);
+    }
   }
   if (smems[MPCI_LTI_HESSIAN_RECURSION] > 227 * 1024)
     return mpci::fail(-8, "lti_plan_create: n=%d m=%d N=%d needs %zu bytes of shared memory "
@@ -856,13 +1093,25 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
           tile_rc.push_back(rt);
           tile_rc.push_back(ct);
         }
-  std::vector<int> flags(G > 0 ? G : 1, 0);
+  // int tables: flags | k0 | rows | row0 (G entries each, at least one), then the DMMA tiles
+  const int Gs = G > 0 ? G : 1;
+  std::vector<int> flags(4 * (size_t)Gs, 0);
+  int nc = 0;
   for (int g = 0; g < G; ++g) {
+    const int k0 = d->grp_k0 ? d->grp_k0[g] : 0, cnt = d->grp_rows ? d->grp_rows[g] : N;
+    if (k0 < 0 || cnt < 0 || k0 + cnt > N)
+      return mpci::fail(-1, "lti_plan_create: group %d has rows %d .. %d outside the horizon %d", g, k0,
+                        k0 + cnt - 1, N);
     for (int i = 0; i < n; ++i)
       if (d->grp_cx[(size_t)g * n + i] != 0.0) flags[g] |= 1;
     bool same = true;  // one arrow for all rows: the rows can be written as bulk copies
-    for (int k = 1; k < N; ++k) same = same && d->grp_arrow[(size_t)g * N + k] == d->grp_arrow[(size_t)g * N];
+    for (int k = k0 + 1; k < k0 + cnt; ++k)
+      same = same && d->grp_arrow[(size_t)g * N + k] == d->grp_arrow[(size_t)g * N + k0];
     if (same) flags[g] |= 2;
+    flags[Gs + g] = k0;
+    flags[2 * Gs + g] = cnt;
+    flags[3 * Gs + g] = nc;
+    nc += cnt;
   }
   mpci_lti_plan* p = new mpci_lti_plan();  // value-initialised: every member zero
   const size_t n_flags = flags.size();
@@ -884,15 +1133,17 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
                                                       smems[mode]);
     if (e != cudaSuccess || per_sm[mode] > 1) continue;
     // one CTA per SM: give it more warps if its shared memory (larger T-patch area) still fits
-    const int is_scan = mode == MPCI_LTI_HESSIAN_RECURSION && scan;
-    const size_t wide = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], is_scan,
-                                                          kWideThreads / 32);
+    size_t aux_wide = auxs[mode];  // the band scan keeps one T patch per warp
+    if (mode == MPCI_LTI_HESSIAN_RECURSION && scan == 1)
+      aux_wide = lti_aux_doubles(m, N, (size_t)(kWideThreads / 32) * 8 * 40);
+    const size_t wide = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], aux_wide);
     int fit = 0;
     if (wide <= 227 * 1024)
       e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, lti_kernel(mode, 1), kWideThreads, wide);
     if (e == cudaSuccess && fit >= 1) {
       threads[mode] = kWideThreads;
       smems[mode] = wide;
+      auxs[mode] = aux_wide;
       per_sm[mode] = fit;
     }
   }
@@ -903,16 +1154,22 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
     return rc;
   }
   const double* base = static_cast<const double*>(p->dev);
-  p->n = n; p->m = m; p->N = N; p->S = S; p->n_groups = G;
+  p->n = n; p->m = m; p->N = N; p->S = S; p->n_groups = G; p->nc = nc;
   LtiArgs& a = p->args;
-  a.n = n; a.m = m; a.N = N; a.S = S; a.n_groups = G;
+  a.n = n; a.m = m; a.N = N; a.S = S; a.n_groups = G; a.nc = nc;
   a.Qxx = base + oQ; a.Quu = base + oR; a.Tx = base + oTx; a.Tu = base + oTu;
   a.cx = base + ocx; a.cu = base + ocu; a.arrow = base + oar; a.bound = base + obd;
   a.grp_state = reinterpret_cast<const int*>(static_cast<const char*>(p->dev) + bytes_d);
+  a.grp_k0 = a.grp_state + Gs;
+  a.grp_cnt = a.grp_state + 2 * Gs;
+  a.grp_row0 = a.grp_state + 3 * Gs;
   a.tiles = reinterpret_cast<const int2*>(a.grp_state + tiles_off);
   a.n_tiles = (int)tile_rc.size() / 2;
   p->scan = scan;
+  p->ldp = ldp;
+  p->scan_warps = scan_warps;
   for (int mode = 0; mode < 2; ++mode) {
+    p->aux[mode] = (int)auxs[mode];
     p->pad[mode] = pads[mode];
     p->LD[mode] = LDs[mode];
     p->threads[mode] = threads[mode];
@@ -968,10 +1225,32 @@ extern "C" int mpci_lti_plan_info(const mpci_lti_plan* p, int mode, long info[6]
   return 0;
 }
 
+static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, const double* B,
+                      long strideB, const double* x0, const double* scalars,
+                      const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
+                      long batch, int mode, void* stream);
+
 extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long strideA,
                                  const double* B, long strideB, const double* x0,
                                  const double* scalars, double* P, double* q, double* G,
                                  double* h, long batch, int mode, void* stream) {
+  return lti_launch(p, A, strideA, B, strideB, x0, scalars, nullptr, P, q, G, h, batch, mode, stream);
+}
+
+extern "C" int mpci_lti_assemble_ex(const mpci_lti_plan* p, const double* A, long strideA,
+                                    const double* B, long strideB, const double* x0,
+                                    const double* scalars, const mpci_lti_tables* tab, double* P,
+                                    double* q, double* G, double* h, long batch, int mode,
+                                    void* stream) {
+  if (p && tab && (tab->tx || tab->tu) && p->S != 0)
+    return mpci::fail(-1, "lti_assemble_ex: per-instance tx / tu need a plan with n_scalars = 0");
+  return lti_launch(p, A, strideA, B, strideB, x0, scalars, tab, P, q, G, h, batch, mode, stream);
+}
+
+static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, const double* B,
+                      long strideB, const double* x0, const double* scalars,
+                      const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
+                      long batch, int mode, void* stream) {
   if (!p) return mpci::fail(-3, "lti_assemble: NULL plan");
   if (batch < 0) return mpci::fail(-1, "lti_assemble: negative batch");
   if (batch == 0) return 0;
@@ -988,8 +1267,20 @@ extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long s
   LtiArgs a = p->args;
   a.pad = p->pad[mode]; a.LD = p->LD[mode]; a.LDw = p->LDw[mode];
   a.scan = (mode == MPCI_LTI_HESSIAN_RECURSION) ? p->scan : 0;
+  a.aux = p->aux[mode]; a.ldp = p->ldp; a.scan_warps = p->scan_warps;
   a.A = A; a.B = B; a.x0 = x0; a.scalars = scalars; a.strideA = strideA; a.strideB = strideB;
   a.P = P; a.q = q; a.G = G; a.h = h; a.batch = batch; a.hessian_mode = mode;
+  a.sQ = a.sR = a.sTx = a.sTu = a.scx = a.scu = a.sbd = 0;
+  if (tab) {  // per-instance tables replace the plan's
+    const long n = p->n, m = p->m, Gn = p->n_groups, N = p->N;
+    if (tab->Qxx) { a.Qxx = tab->Qxx; a.sQ = n * n; }
+    if (tab->Quu) { a.Quu = tab->Quu; a.sR = m * m; }
+    if (tab->tx) { a.Tx = tab->tx; a.sTx = n; }
+    if (tab->tu) { a.Tu = tab->tu; a.sTu = m; }
+    if (tab->cx) { a.cx = tab->cx; a.scx = Gn * n; }
+    if (tab->cu) { a.cu = tab->cu; a.scu = Gn * m; }
+    if (tab->bound) { a.bound = tab->bound; a.sbd = Gn * N; }
+  }
   int dev = 0, sms = 148;
   MPCI_CUDA(cudaGetDevice(&dev));
   MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -1024,7 +1315,7 @@ static int lti_host(mpci_lti_plan* p, const double* A, long strideA, const doubl
   if (ring == 0) ring = n_chunks;
   if (ring < 2 && n_chunks > 1)
     return mpci::fail(-1, "lti_assemble_host: a ring of one slot cannot overlap two chunks");
-  const long nv = m * p->N, nc = (long)p->n_groups * p->N;
+  const long nv = m * p->N, nc = p->nc;
   const long in_per = n * n + n * m + n + S, out_per = nv * nv + nv + nc * nv + nc;
   if (p->slot_capacity < chunk) {
     for (int s = 0; s < 2; ++s) {

@@ -126,6 +126,18 @@ _SIGNATURES = {
          _c_double_p, _c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_long,
          ctypes.c_int, ctypes.c_long, ctypes.c_long, ChunkFn, ctypes.c_void_p],
     ),
+    "mpci_lti_assemble_ex": (
+        ctypes.c_int,
+        [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
+         _c_double_p, ctypes.c_void_p]
+        + [_c_double_p] * 4
+        + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p],
+    ),
+    "mpci_named_system": (
+        ctypes.c_int,
+        [ctypes.c_int, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
+         _c_double_p, ctypes.c_long, ctypes.c_void_p],
+    ),
     "mpci_lti_hessian_flops": (ctypes.c_double, [ctypes.c_void_p, ctypes.c_int]),
     "mpci_lti_plan_info": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]),
     "mpci_lti_assemble": (

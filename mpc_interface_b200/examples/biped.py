@@ -161,3 +161,20 @@ def structure_key(horizon_lenght):
         return (tuple(int(t) for t in inside), int(step_count) % 2)
 
     return key
+
+
+def structure_keys(horizon_lenght, step_times, step_count):
+    """``structure_key`` for a whole batch at once: step_times int [B, n_steps] (ascending
+    per row), step_count int [B] -> int64 [B, n_steps + 1] key rows for
+    ``receding.StructureBuckets.group_keys``: the step times inside the preview window
+    (the others masked to -1) and the parity of the step count.  Two instances get equal
+    rows exactly when ``structure_key`` gives them equal keys."""
+    times = np.asarray(step_times).astype(np.int64)
+    inside = (times >= 0) & (times < horizon_lenght - 1)
+    # the inside times left-aligned (sorted, the masked ones last), so that a row depends on
+    # the SET of inside times alone, as the tuple of structure_key does
+    big = np.iinfo(np.int64).max
+    rows = np.sort(np.where(inside, times, big), axis=1)
+    rows = np.where(rows == big, -1, rows)
+    parity = (np.asarray(step_count).astype(np.int64) % 2).reshape(-1, 1)
+    return np.concatenate([rows, parity], axis=1)

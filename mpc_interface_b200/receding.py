@@ -47,6 +47,66 @@ class StructureBuckets:
             groups[k][1].append(b)
         return {k: (kargs, np.asarray(idx, dtype=np.int64)) for k, (kargs, idx) in groups.items()}
 
+    @staticmethod
+    def group_keys(keys):
+        """Vectorised grouping: ``keys`` int64 [B, K], one structural key row per instance
+        (e.g. ``biped.structure_keys``).  Returns ``[(key tuple, int64 indices)]`` ordered by
+        first appearance, the indices of a group ascending -- integer work only
+        (``np.unique`` over the rows), no Python loop over the instances."""
+        keys = np.ascontiguousarray(keys, dtype=np.int64)
+        if keys.ndim != 2:
+            raise ValueError("keys must be [B, K]")
+        if keys.shape[0] == 0:
+            return []
+        uniq, first, inverse = np.unique(keys, axis=0, return_index=True, return_inverse=True)
+        inverse = inverse.reshape(-1)
+        order = np.argsort(inverse, kind="stable")
+        bounds = np.cumsum(np.bincount(inverse, minlength=len(uniq)))[:-1]
+        members = np.split(order, bounds)
+        by_appearance = np.argsort(first, kind="stable")
+        return [(tuple(int(x) for x in uniq[u]), members[u]) for u in by_appearance]
+
+    def assemble_device(self, keys, kargs_of, collector, scalars=None, params=None, outs=None):
+        """One tick for a batch whose inputs live on the GPU (a receding-horizon stream: the
+        collector of tick t+1 is produced on the device by ``advance_collector``).
+
+        keys      : int64 [B, K] structural key rows (``group_keys``)
+        kargs_of  : ``kargs_of(b)`` -> the update arguments of instance b; called once per
+                    structure that has not been seen before (for its representative)
+        collector : {given variable: CUDA tensor [B, size]}
+        params    : {name: array [B]} per-instance ``Param`` values (host), evaluated per
+                    structure; or ``scalars``: a CUDA tensor [B, n_slots] already evaluated
+                    in the slot order the structures share (``slots_of``)
+        outs      : optional dict reused across ticks: {(key, count): QPBatch} ring slots
+
+        Returns ``[(key, indices (CUDA int64 tensor), formulation, QPBatch)]``; the rows of a
+        bucket's inputs are gathered on the device (no host copy of ``given``)."""
+        out = []
+        for key, idx in self.group_keys(keys):
+            if key not in self._forms:
+                form = self._factory()
+                form.update(**kargs_of(int(idx[0])))
+                self._forms[key] = form
+            form = self._forms[key]
+            ops = form._ops()
+            torch = ops.torch
+            index = torch.from_numpy(idx).to(ops.device)
+            given = torch.cat([collector[v].reshape(collector[v].shape[0], -1).index_select(0, index)
+                               for v in form.given_variables], dim=1) if form.given_variables else \
+                torch.zeros([len(idx), 0], dtype=torch.float64, device=ops.device)
+            compiled = form._compiled()
+            if scalars is not None:
+                scal = scalars.index_select(0, index)
+            else:
+                sub = {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
+                scal = compiled.slots.evaluate(sub, len(idx))
+            slot = None if outs is None else outs.get((key, len(idx)))
+            qp = ops.assemble(compiled, scal, given, len(idx), slot)
+            if outs is not None:
+                outs[(key, len(idx))] = qp
+            out.append((key, index, form, qp))
+        return out
+
     def assemble(self, instance_kargs, collector, params=None, layout="dense"):
         """One tick for a batch.
 
@@ -81,7 +141,7 @@ def count_steps(step_times, step_count, step_samples):
     return times, count
 
 
-def advance_collector(form, given, optim, take, params=None, collector=None):
+def advance_collector(form, given, optim, take, params=None, collector=None, scalars=None):
     """The example loop's ``update_given_collector`` (biped_mpc_loop.py:81-88) for a batch:
     the initial state of the next tick is read off the previewed horizon.
 
@@ -103,7 +163,7 @@ def advance_collector(form, given, optim, take, params=None, collector=None):
             if not 0 <= row < dyn.all_variables[state]:
                 raise IndexError("row {} is outside the horizon of {}".format(row, state))
             states.append((state, dyn.state_vector_name + "0" + state[-2:], ident, row))
-    motion = form.preview_all_batched(given, optim, [s[0] for s in states], params)
+    motion = form.preview_all_batched(given, optim, [s[0] for s in states], params, scalars=scalars)
     batch = next(iter(motion.values())).shape[0] if motion else 0
     out = {}
     for name, value in (collector or {}).items():

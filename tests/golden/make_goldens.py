@@ -289,6 +289,32 @@ def generic_per_instance_digest(name, seed, nx, nu, N, n_rows, batch):
     save(name, **out)
 
 
+def lip_per_instance(name, N, batch, seed):
+    """examples/lip.py on the reference's classes, one formulation per instance: its own
+    pendulum frequency and sampling period enter the PLANT
+    (ControlSystem.from_name("dP->CCC", tau=..., omega=...), tools.py:253-280) and the
+    definitions b, DCM."""
+    from mpc_interface_b200.examples import lip
+
+    api = types.SimpleNamespace(ControlSystem=ref_dyn.ControlSystem, ExtendedSystem=ref_dyn.ExtendedSystem,
+                                Formulation=ref_body.Formulation, LineCombo=ref_comb.LineCombo,
+                                Cost=ref_goal.Cost, Box=ref_res.Box,
+                                make_simetric_vertices=ref_tools.make_simetric_vertices)
+    vals = lip.lip_inputs(seed, batch)
+    conf = lip.default_configuration(N)
+    As, hs, Qs, qs, Asys, Bsys = [], [], [], [], [], []
+    for b in range(batch):
+        form = lip.formulate_lip(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                 target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        given = form.arrange_given({"x0_x": vals["x0_x"][b][:, None], "x0_y": vals["x0_y"][b][:, None]})
+        A, h, Q, q = form.generate_all_qp_matrices(given)
+        As.append(A), hs.append(h[:, 0]), Qs.append(Q), qs.append(q[:, 0])
+        system = ref_dyn.ControlSystem.from_name("dP->CCC", tau=float(vals["tau"][b]), omega=float(vals["omega"][b]))
+        Asys.append(np.array(system.A, dtype=float)), Bsys.append(np.array(system.B, dtype=float))
+    save(name, seed=seed, N=N, A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs),
+         A_sys=np.stack(Asys), B_sys=np.stack(Bsys), **vals, **layout(form))
+
+
 def random_forms(name, seeds, batch):
     """tests/_random_forms.py built by the reference, one formulation per instance."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -317,6 +343,10 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["yaw"]:
         biped_yaw("biped_n24_yaw.npz", 24, 5, 1011)
         biped_yaw("biped_n100_yaw.npz", 100, 2, 1012)
+        sys.exit(0)
+    if sys.argv[1:] == ["lip"]:
+        lip_per_instance("lip_perinst.npz", 40, 6, 1030)
+        lip_per_instance("lip_perinst_n9.npz", 9, 3, 1031)
         sys.exit(0)
     if sys.argv[1:] == ["big"]:
         biped_long("biped_long_digest.npz", [200, 400], 1020)

@@ -80,3 +80,27 @@ def test_cpp_header_builds_and_links(lib):
     if lib.mpci_device_count() == 0:  # no CPU fallback behind the C++ face either
         failed = _gecko_build.run()
         assert failed.returncode != 0 and "extend_matrices" in (failed.stdout + failed.stderr)
+
+
+def test_plan_desc_of_the_documentation_matches_the_header():
+    """The PlanDesc printed in INTEGRATION.md, the one in device.py and mpci_plan_desc of
+    include/mpci.h list the same fields in the same order with the same C types."""
+    from mpc_interface_b200 import device
+
+    header = open(os.path.join(ROOT, "include", "mpci.h")).read()
+    body = re.search(r"typedef struct \{(.*?)\} mpci_plan_desc;", header, flags=re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    fields = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        ctype, names = decl.rsplit(" ", 1)[0], decl
+        pointer = "*" in decl
+        for name in re.sub(r"^(const\s+)?(int|double)\s*\*?\s*", "", names).split(","):
+            fields.append((name.strip().lstrip("*"), "p" if pointer else "i"))
+    own = [(n, "p" if t is ctypes.c_void_p else "i") for n, t in device.PlanDesc._fields_]
+    assert own == fields
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    block = re.search(r"class PlanDesc\(ctypes.Structure\):.*?_fields_ = \[(.*?)\]\n", doc, flags=re.S).group(1)
+    assert re.findall(r'\("(\w+)", (\w)\)', block) == fields

@@ -193,3 +193,87 @@ def test_lti_at_the_baseline_shapes_against_reference_digests(dev, name, hessian
     got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
     for b in range(g["x0"].shape[0]):
         cases.assert_digest_close(tuple(x[b] for x in got), g, "i%d_" % b, int(g["seed"]) + b)
+
+
+@pytest.mark.parametrize("hessian", ["dmma", "recursion"])
+@pytest.mark.parametrize("name", ["lip_perinst", "lip_perinst_n9"])
+def test_lip_named_system_per_instance_omega_and_tau(dev, name, hessian):
+    """The LIP with CoP-rate input on two axes, one pendulum frequency AND one sampling period
+    per instance: the plants come from the device-side closed forms of "dP->CCC"
+    (mpci_named_system), the definitions b / DCM carry Param coefficients (per-instance
+    tables, mpci_lti_assemble_ex), the terminal DCM box is a scheduled limit.  Golden: the
+    reference formulated every instance with ControlSystem.from_name("dP->CCC", tau_b,
+    omega_b) (make_goldens.py lip).  ONE batched call."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import lip
+
+    g = cases.golden(name)
+    conf = lip.default_configuration(int(g["N"]))
+    form = lip.formulate_lip(conf, omega=Param("omega"), tau=Param("tau"),
+                             target_vel=[Param("vel_x"), Param("vel_y")])
+    cases.check_layout(form, g)
+    params = {k: g[k] for k in ("omega", "vel_x", "vel_y")}
+    given = np.hstack([g["x0_x"], g["x0_y"]])
+    out = form.generate_all_qp_matrices_batched(
+        given, params, dynamics={"LIP": ("dP->CCC", g["tau"], g["omega"])}, hessian=hessian)
+    got = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+    cases.assert_qp_close(got, (g["A"], g["h"], g["Q"], g["q"]))
+    N = int(g["N"])
+    assert np.all(got[2][:, :N, N:] == 0.0)  # the axes do not couple: exact zeros, as in the reference
+
+
+def test_named_systems_on_device_match_the_sympy_lambdas(dev):
+    """mpci_named_system against tools.get_system_matrices (SymPy exp / integrate,
+    tools.py:240-285) for every named system and a batch of (tau, omega)."""
+    from mpc_interface_b200 import lti
+    from mpc_interface_b200 import tools as use
+
+    rng = np.random.default_rng(3)
+    tau, omega = rng.uniform(0.05, 0.2, 9), rng.uniform(2.5, 4.0, 9)
+    for name in ("J->CCC", "P->CC", "P->X", "dP->CCC", "dP->CCP"):
+        A, B = lti.named_system_batched(name, tau, omega)
+        get_A, get_B, _ = use.get_system_matrices(name)
+        for b in range(9):
+            refA = np.array(get_A(tau=tau[b], omega=omega[b]), dtype=float)
+            refB = np.array(get_B(tau=tau[b], omega=omega[b]), dtype=float)
+            assert cases.rel_err(A[b].cpu().numpy(), refA) <= 1e-13, name
+            assert cases.rel_err(B[b].cpu().numpy(), refB.reshape(B[b].shape)) <= 1e-13, name
+    A1, _ = lti.named_system_batched("J->CCC", 0.1, None, batch=4)  # shared tau, no omega
+    assert tuple(A1.shape) == (4, 3, 3) and float(A1[3, 0, 1]) == 0.1
+
+
+@pytest.mark.parametrize("hessian", ["dmma", "recursion"])
+def test_permuted_inputs_scheduled_limit_and_param_weight(dev, monkeypatch, hessian):
+    """Optimisation variables in another order than the plant inputs, a limit on a window of
+    the horizon, a per-instance cost weight and a per-instance bound: against the oracle."""
+    import mpc_interface_b200.tools as tools
+    from _numpy_backend import NumpyBackend
+    from mpc_interface_b200 import Constraint, Cost, Param
+
+    g = cases.golden("generic_small")
+
+    def build(backend, refs, weight, extreme):
+        form = cases.formulate_generic(g["A_sys"], g["B_sys"], g["Q_w"], g["R_w"], int(g["N"]), g["rows"],
+                                       refs=refs, backend=backend)
+        form.incorporate_constraint("late", Constraint("z2", extreme, schedule=range(3, 7)))
+        form.incorporate_goal("extra", Cost("z1", weight, aim=[0.25]))
+        form.identify_qp_domain(["u1", "u0"])
+        form.make_preview_matrices()
+        return form
+
+    nx, batch = 4, g["x0"].shape[0]
+    form = build(None, [Param("ref%d" % i) for i in range(nx)], Param("w"), Param("lim"))
+    params = {"ref%d" % i: g["ref"][:, i] for i in range(nx)}
+    params["w"] = np.array([0.5, 2.0, 3.5])[:batch]
+    params["lim"] = np.array([1.0, 1.5, 0.2])[:batch]
+    out = form.generate_all_qp_matrices_batched(
+        g["x0"], params, dynamics={"plant": (g["A_sys"], g["B_sys"])}, hessian=hessian)
+    got = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+    monkeypatch.setattr(tools, "extend_matrices", orc.extend_matrices)
+    for b in range(batch):
+        ref_form = build(NumpyBackend(), list(g["ref"][b]), float(params["w"][b]), float(params["lim"][b]))
+        ref = orc.all_qp_matrices(ref_form, g["x0"][b][:, None])
+        cases.assert_qp_close(tuple(x[b] for x in got), ref)
+    with pytest.raises(ValueError):  # a negative per-instance extreme would be flipped by the reference
+        form.generate_all_qp_matrices_batched(
+            g["x0"], dict(params, lim=-params["lim"]), dynamics={"plant": (g["A_sys"], g["B_sys"])})

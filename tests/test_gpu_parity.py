@@ -498,8 +498,18 @@ def test_preview_and_goal_distance_batched(dev, N):
         assert abs(total[b] - ref_total) <= cases.TOL * max(1.0, abs(ref_total))
     # one instance through the reference-named single-instance calls
     single = cases.formulate_biped(cases.default_configuration(N))
-    v = single.preview(given[0][:, None], optim[0][:, None], "CoM", ["_x", "_y"])
+    g, z = given[0][:, None], optim[0][:, None]
+    v = single.preview(g, z, "CoM", ["_x", "_y"])
     assert v.shape == (N, 2)
+    PM = orc.preview_matrices(single)
+    want = np.hstack([PM["CoM" + a][0] @ g + PM["CoM" + a][1] @ z for a in ("_x", "_y")])
+    assert cases.rel_err(v, want) <= cases.TOL
+    col = single.preview(g, z, "DCM_y")
+    assert col.shape == (N, 1) and cases.rel_err(col, PM["DCM_y"][0] @ g + PM["DCM_y"][1] @ z) <= cases.TOL
+    gap = PM["CoM_dot_x"][0] @ g + PM["CoM_dot_x"][1] @ z - single.goals["track vel_x"].aim[:, 0]
+    d = single.goal_distance(g, z, "track vel_x")
+    assert abs(d - float(gap.T @ gap)) <= cases.TOL * max(1.0, float(gap.T @ gap))
+    assert single.full_goal_distance(g, z) >= d
 
 
 @pytest.mark.parametrize("N", [200, 400])
@@ -532,3 +542,21 @@ def test_biped_long_horizons_in_mode_a(dev, N):
     other = tuple(x[5].cpu().numpy() for x in (out.G, out.h, out.P, out.q))
     params5 = {k: float(vals[k][5]) for k in ("omega", "vel_x", "vel_y")}
     cases.assert_qp_close(other, orc.all_qp_matrices(form, given[5][:, None], params5))
+
+
+def test_integration_snippet_runs(dev):
+    """the ctypes call sequence a maintainer would write (a
+    hand-made mpci_plan_desc, mpci_plan_create, mpci_assemble_host) is executed as it is
+    printed there, asserts included."""
+    import os
+    import re
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "INTEGRATION.md")).read()
+    block = re.search(r"<!-- snippet:plan -->\n```python\n(.*?)\n```", text, flags=re.S).group(1)
+    here = os.getcwd()
+    os.chdir(root)  # the snippet loads the library by its path inside the repo
+    try:
+        exec(compile(block, "INTEGRATION.md:snippet:plan", "exec"), {"__name__": "snippet"})
+    finally:
+        os.chdir(here)

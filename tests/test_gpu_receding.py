@@ -120,3 +120,47 @@ def test_preview_all_and_advance_collector(N):
     assert all(np.array_equal(collector[name], vals[name]) for name in collector)
     with pytest.raises(IndexError):
         advance_collector(form, given, optim, {"LIP": N}, params)
+
+
+def test_device_tick_equals_the_per_instance_grouping():
+    """StructureBuckets.assemble_device (np.unique grouping, inputs gathered on the GPU,
+    output slots reused across ticks) gives bit-identical matrices to assemble()."""
+    import torch
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import synthetic
+    from mpc_interface_b200.examples.biped import (default_configuration, formulate_biped,
+                                                   structure_key, structure_keys)
+    from mpc_interface_b200.receding import StructureBuckets
+
+    N, batch = 24, 333
+    conf = default_configuration(N)
+
+    def factory():
+        return formulate_biped(conf, omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")])
+
+    n_steps = factory().domain["Ds_x"]
+    ticks = _tick_sequence(30, conf.step_samples, n_steps)
+    phase = np.random.default_rng(1).integers(0, len(ticks), size=batch)
+    times = np.stack([ticks[t][0] for t in phase])
+    count = np.array([ticks[t][1] for t in phase])
+    kargs = [dict(step_times=times[b], step_count=count[b]) for b in range(batch)]
+    vals = synthetic.biped_inputs(5, batch, N)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    a = StructureBuckets(factory, structure_key(N))
+    want = a.assemble(kargs, vals, params)
+    b = StructureBuckets(factory, structure_key(N))
+    collector = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in vals.items()
+                 if k not in params}
+    outs = {}
+    got = b.assemble_device(structure_keys(N, times, count), lambda i: kargs[i], collector,
+                            params=params, outs=outs)
+    assert len(got) == len(want) and len(outs) == len(got)
+    for (_, idx_w, _, qp_w), (_, idx_g, _, qp_g) in zip(want, got):
+        assert np.array_equal(idx_w, idx_g.cpu().numpy())
+        for x, y in ((qp_w.P, qp_g.P), (qp_w.q, qp_g.q), (qp_w.G, qp_g.G), (qp_w.h, qp_g.h)):
+            assert torch.equal(x, y)
+    # a second tick reuses plans and output slots
+    slots = {k: v.P.data_ptr() for k, v in outs.items()}
+    again = b.assemble_device(structure_keys(N, times, count), lambda i: kargs[i], collector,
+                              params=params, outs=outs)
+    assert {k: v.P.data_ptr() for k, v in outs.items()} == slots and len(again) == len(got)

@@ -99,3 +99,41 @@ def test_per_instance_plants_against_the_live_reference(nx, nu, N, n_rows, count
                 cases.assert_qp_close(tuple(x[b] for x in got[mode]), ref)
             except AssertionError as e:
                 raise AssertionError("seed {} instance {} ({}): {}".format(fresh, b, mode, e))
+
+
+def test_lip_with_per_instance_plants_against_the_live_reference():
+    """examples/lip.py, 32 fresh instances: every one its own omega, tau (so its own
+    "dP->CCC" plant), initial state and velocity target; the reference formulates each
+    instance from scratch with its own classes, the GPU does the batch in one call."""
+    import types
+
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import lip
+
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                Formulation=ref.Formulation, LineCombo=ref.LineCombo, Cost=ref.Cost,
+                                Box=ref.Box, make_simetric_vertices=ref.tools.make_simetric_vertices)
+    N, B = 50, 32
+    seed = int.from_bytes(os.urandom(4), "little")
+    vals = lip.lip_inputs(seed, B)
+    conf = lip.default_configuration(N)
+    form = lip.formulate_lip(conf, omega=Param("omega"), tau=Param("tau"),
+                             target_vel=[Param("vel_x"), Param("vel_y")])
+    given = np.hstack([vals["x0_x"], vals["x0_y"]])
+    got = {}
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")},
+            dynamics={"LIP": ("dP->CCC", vals["tau"], vals["omega"])}, hessian=mode)
+        got[mode] = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+    for b in range(B):
+        one = lip.formulate_lip(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        g = one.arrange_given({"x0_x": vals["x0_x"][b][:, None], "x0_y": vals["x0_y"][b][:, None]})
+        want = one.generate_all_qp_matrices(g)
+        for mode in got:
+            try:
+                cases.assert_qp_close(tuple(x[b] for x in got[mode]), want)
+            except AssertionError as e:
+                raise AssertionError("seed {} instance {} ({}): {}".format(seed, b, mode, e))

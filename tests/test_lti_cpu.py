@@ -80,3 +80,81 @@ def test_lowering_input_forms_and_derived_definitions(cpu_extend):
     got = _lti_numpy.evaluate(plan, g["A_sys"], g["B_sys"], g["x0"][0], scalars)
     ref = orc.all_qp_matrices(form, g["x0"][0][:, None], values)
     cases.assert_qp_close(got, ref)
+
+
+def _lip(g, cpu_extend):
+    from mpc_interface_b200.examples import lip
+
+    conf = lip.default_configuration(int(g["N"]))
+    form = lip.formulate_lip(conf, omega=Param("omega"), tau=Param("tau"),
+                             target_vel=[Param("vel_x"), Param("vel_y")], backend=NumpyBackend())
+    return form
+
+
+@pytest.mark.parametrize("name", ["lip_perinst", "lip_perinst_n9"])
+def test_lip_two_axes_param_coefficients_terminal_schedule(cpu_extend, name):
+    """Mode B widened (round 2): the plant on two axes (block-diagonal lowering), Param
+    coefficients in the definitions (b = CoM - CoM_ddot / omega^2, DCM = CoM + CoM_dot /
+    omega), multi-axis box facets, a scheduled terminal limit, multi-axis costs -- against
+    the reference, which formulated every instance with its own
+    ControlSystem.from_name("dP->CCC", tau_b, omega_b)."""
+    g = cases.golden(name)
+    form = _lip(g, cpu_extend)
+    cases.check_layout(form, g)
+    plan = form.lti_plan("LIP")
+    N = int(g["N"])
+    assert plan.per_instance and (plan.n, plan.m, plan.n0, plan.m0) == (6, 2, 3, 1)
+    assert (plan.nv, plan.nc) == (2 * N, 4 * N + 4) and plan.limit_rows == [N] * 4 + [1] * 4
+    batch = g["A"].shape[0]
+    params = {k: g[k] for k in ("omega", "tau", "vel_x", "vel_y")}
+    assert sorted(plan.parameter_names()) == ["omega", "vel_x", "vel_y"]  # tau lives in the plant
+    tables = plan.instance_tables(params, batch)
+    given = np.hstack([g["x0_x"], g["x0_y"]])
+    for b in range(batch):
+        one = {k: v[b] for k, v in tables.items()}
+        got = _lti_numpy.evaluate(plan, g["A_sys"][b], g["B_sys"][b], given[b], None, one)
+        cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
+    # the cross blocks of P between the axes are exact zeros, as in the reference
+    assert np.all(g["Q"][0][:N, N:] == 0.0) and np.all(got[2][:N, N:] == 0.0)
+
+
+def test_named_systems_closed_forms_match_sympy():
+    """the closed forms the device kernel evaluates (restated here in
+    NumPy, the kernel itself is checked on the GPU) against the SymPy-derived lambdas of
+    tools.get_system_matrices for every named system."""
+    from mpc_interface_b200 import tools as use
+
+    T, w = 0.1, 3.3445
+    c, s = np.cosh(w * T), np.sinh(w * T)
+    closed = {
+        "J->CCC": ([[1, T, T * T / 2], [0, 1, T], [0, 0, 1]], [T**3 / 6, T * T / 2, T]),
+        "P->CC": ([[c, s / w], [w * s, c]], [1 - c, -w * s]),
+        "P->X": ([[np.exp(w * T)]], [1 - np.exp(w * T)]),
+        "dP->CCC": ([[1, s / w, (c - 1) / w**2], [0, c, s / w], [0, w * s, c]], [T - s / w, 1 - c, -w * s]),
+        "dP->CCP": ([[c, s / w, 1 - c], [w * s, c, -w * s], [0, 0, 1]], [T - s / w, 1 - c, T]),
+    }
+    for name, (A, B) in closed.items():
+        get_A, get_B, _ = use.get_system_matrices(name)
+        assert np.allclose(np.array(get_A(tau=T, omega=w), dtype=float), np.array(A, dtype=float), rtol=1e-13, atol=1e-15), name
+        assert np.allclose(np.array(get_B(tau=T, omega=w), dtype=float).ravel(), np.array(B, dtype=float), rtol=1e-13, atol=1e-15), name
+
+
+def test_lowering_permuted_inputs_and_scheduled_limit(cpu_extend):
+    """The optimisation variables in another order than the plant's inputs, and a limit on
+    a window of the horizon."""
+    g = cases.golden("generic_small")
+    form = _formulation(g, cpu_extend, False)
+    form.incorporate_constraint("late", Constraint("z2", 1.5, schedule=range(3, 7)))
+    form.identify_qp_domain(["u1", "u0"])
+    form.make_preview_matrices()
+    plan = form.lti_plan("plant")
+    assert plan.inputs == [(0, 1), (0, 0)] and 4 in plan.limit_rows and plan.nc == sum(plan.limit_rows)
+    from oracle import qp_oracle as orc
+
+    names = [repr(e) for e in plan.slots.exprs]
+    values = {"ref%d" % i: float(g["ref"][0, i]) for i in range(4)}
+    scalars = np.array([values[nm] for nm in names])
+    got = _lti_numpy.evaluate(plan, g["A_sys"], g["B_sys"], g["x0"][0], scalars)
+    ref = orc.all_qp_matrices(form, g["x0"][0][:, None], values)
+    cases.assert_qp_close(got, ref)
+    assert got[0].shape[0] == ref[0].shape[0]

@@ -132,3 +132,24 @@ def test_bind_host_near_gpu_on_a_fake_sysfs(tmp_path):
     info, bound = json.loads(out.strip().splitlines()[-1])
     assert info["numa_node"] == 0 and info["cpus"] == len(keep) and bound == keep
     assert sorted(os.sched_getaffinity(0)) == allowed  # the parent is untouched
+
+
+def test_structure_keys_group_like_the_per_instance_key():
+    """receding.StructureBuckets.group_keys (np.unique over integer key rows) forms the same
+    buckets, in the same order, as the per-instance Python loop over structure_key."""
+    from mpc_interface_b200.examples.biped import structure_key, structure_keys
+    from mpc_interface_b200.receding import StructureBuckets
+
+    rng = np.random.default_rng(0)
+    B, N = 3000, 100
+    first = rng.integers(0, 12, B)
+    count = rng.integers(0, 50, B)
+    times = first[:, None] + 12 * np.arange(9)[None, :]
+    groups = StructureBuckets.group_keys(structure_keys(N, times, count))
+    key = structure_key(N)
+    loop = {}
+    for b in range(B):
+        loop.setdefault(key(step_times=times[b], step_count=count[b]), []).append(b)
+    assert len(groups) == len(loop) == 24  # 12 phases x 2 feet
+    assert [list(idx) for _, idx in groups] == list(loop.values())
+    assert StructureBuckets.group_keys(np.zeros([0, 3], dtype=np.int64)) == []
