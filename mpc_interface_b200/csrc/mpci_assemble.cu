@@ -81,28 +81,34 @@ stream_terms_kernel(StreamArgs args, const double* __restrict__ scalars, int n_s
 }
 
 // More than 8 monomials (e.g. several boxes turned by different per-instance angles):
-// the constants do not fit the register file, so every output vector re-reads its K
-// constant vectors through L1 / L2 (read-only path).  Same grid, same store pattern;
-// slower by the extra on-chip traffic, not by extra HBM bytes.
+// the constants do not fit the register file next to 32 instances, so the thread works on
+// eight instances at a time -- eight accumulators, every constant vector fetched once
+// per eight outputs through the read-only path (L1 / L2), the eight coefficients of a
+// term as two warp-uniform 32-byte shared-memory reads.  Same grid, same store pattern,
+// no extra HBM bytes.
+constexpr int kGenericSub = 8;
 template <typename VecT>
 __global__ void __launch_bounds__(kStreamThreads)
 stream_terms_generic(StreamArgs args, const double* __restrict__ scalars, int n_scalars,
                      double* __restrict__ out, long batch) {
   constexpr int V = sizeof(VecT) / sizeof(double);
-  __shared__ double coef[kStreamGroup][MPCI_MAX_TERMS];
+  __shared__ __align__(16) double coef[MPCI_MAX_TERMS][kStreamGroup];  // [term][instance]
   const int K = args.n_terms;
   const long b0 = (long)blockIdx.y * kStreamGroup;
   const int group = (int)min((long)kStreamGroup, batch - b0);
-  for (int e = threadIdx.x; e < group * K; e += blockDim.x) {
-    const int t = e / K, k = e - t * K;
-    const double* s = scalars + (b0 + t) * n_scalars;
-    double c = 1.0;
+  for (int e = threadIdx.x; e < kStreamGroup * K; e += blockDim.x) {
+    const int k = e / kStreamGroup, t = e - k * kStreamGroup;
+    double c = 0.0;  // instances past the batch: zero coefficients, nothing stored
+    if (t < group) {
+      const double* s = scalars + (b0 + t) * n_scalars;
+      c = 1.0;
 #pragma unroll
-    for (int f = 0; f < MPCI_MAX_FACTORS; ++f) {
-      const int idx = args.factors[k][f];
-      if (idx >= 0) c *= s[idx];
+      for (int f = 0; f < MPCI_MAX_FACTORS; ++f) {
+        const int idx = args.factors[k][f];
+        if (idx >= 0) c *= s[idx];
+      }
     }
-    coef[t][k] = c;
+    coef[k][t] = c;
   }
   __syncthreads();
   const long n_vec = args.n_elems / V;
@@ -110,21 +116,31 @@ stream_terms_generic(StreamArgs args, const double* __restrict__ scalars, int n_
   if (v >= n_vec) return;
   const VecT* src = reinterpret_cast<const VecT*>(args.consts) + v;
   VecT* dst = reinterpret_cast<VecT*>(out + b0 * args.n_elems) + v;
-  for (int t = 0; t < group; ++t) {
-    VecT r;
-    if constexpr (V == 2) {
-      r.x = r.y = 0.0;
-      for (int k = 0; k < K; ++k) {
-        const VecT d = __ldg(src + (long)k * n_vec);
-        r.x = fma(coef[t][k], d.x, r.x);
-        r.y = fma(coef[t][k], d.y, r.y);
-      }
-    } else {
-      r = 0.0;
-      for (int k = 0; k < K; ++k) r = fma(coef[t][k], __ldg(src + (long)k * n_vec), r);
+  for (int t0 = 0; t0 < group; t0 += kGenericSub, dst += kGenericSub * n_vec) {
+    VecT acc[kGenericSub];
+#pragma unroll
+    for (int i = 0; i < kGenericSub; ++i) {
+      if constexpr (V == 2) acc[i].x = acc[i].y = 0.0;
+      else acc[i] = 0.0;
     }
-    __stcs(dst, r);
-    dst += n_vec;
+    for (int k = 0; k < K; ++k) {
+      const VecT d = __ldg(src + (long)k * n_vec);
+      const double4 ca = *reinterpret_cast<const double4*>(&coef[k][t0]);
+      const double4 cb = *reinterpret_cast<const double4*>(&coef[k][t0 + 4]);
+      const double c[kGenericSub] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
+#pragma unroll
+      for (int i = 0; i < kGenericSub; ++i) {
+        if constexpr (V == 2) {
+          acc[i].x = fma(c[i], d.x, acc[i].x);
+          acc[i].y = fma(c[i], d.y, acc[i].y);
+        } else {
+          acc[i] = fma(c[i], d, acc[i]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kGenericSub; ++i)
+      if (t0 + i < group) __stcs(dst + (long)i * n_vec, acc[i]);
   }
 }
 

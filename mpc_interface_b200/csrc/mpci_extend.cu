@@ -115,38 +115,24 @@ __host__ __device__ inline size_t fused_smem_doubles(int n, int m, int N, bool s
   const size_t mats = ((size_t)n * n + 2 * (size_t)n * (n + m) + 1) & ~(size_t)1;
   return mats + (size_t)m * 2 * N * n * (shifted ? 2 : 1);
 }
-// Short rows (N*n*8 < 2 kB, e.g. the biped's default horizon N = 24: 576-byte rows): the
-// copy engine takes one copy per ~19 cycles whatever its size (profiles/r01_tma_rate.txt),
-// so row-sized copies cap the rate.  There the block keeps a dense image of U[j] --
-// [N][N*n], zeros above the diagonal written once -- scatters every Gam_k into its N - k
-// places while the recursion runs, and hands the image over in pieces of up to 8 kB.
-__host__ __device__ inline size_t dense_smem_doubles(int n, int m, int N) {
-  const size_t mats = ((size_t)n * n + 2 * (size_t)n * (n + m) + 1) & ~(size_t)1;
-  return mats + (size_t)m * N * N * n;
-}
 
 __global__ void __launch_bounds__(kFusedThreads)
 extend_fused_kernel(const double* __restrict__ A, const double* __restrict__ B,
                     double* __restrict__ S, double* __restrict__ U, long batch, int n, int m, int N,
-                    int shifted, int dense) {
+                    int shifted) {
   extern __shared__ double sm[];
   const int w = n + m, tid = threadIdx.x;
-  const int zld = dense ? N * N * n : 2 * N * n, row_len = N * n;
+  const int zld = 2 * N * n, row_len = N * n;
   double* As = sm;
   double* cur = As + n * n;
   double* nxt = cur + n * w;
   double* Z = sm + (((size_t)n * n + 2 * (size_t)n * w + 1) & ~(size_t)1);  // [m][zld]
   double* Z1 = Z + (size_t)m * zld;                                        // Z1[x] = Z[x + 1]
-  // the zeros are written once: the recursion only touches [0, N*n) of Z (the lower
-  // triangle of the dense image)
-  if (dense) {
-    for (int e = tid; e < m * zld; e += blockDim.x) Z[e] = 0.0;
-  } else {
-    for (int e = tid; e < m * zld; e += blockDim.x) {
-      const int x = e % zld;
-      if (x >= row_len) Z[e] = 0.0;
-      if (shifted && x >= row_len - 1) Z1[e] = 0.0;
-    }
+  // the zero halves are written once; the recursion only touches [0, N*n)
+  for (int e = tid; e < m * zld; e += blockDim.x) {
+    const int x = e % zld;
+    if (x >= row_len) Z[e] = 0.0;
+    if (shifted && x >= row_len - 1) Z1[e] = 0.0;
   }
   for (long b = blockIdx.x; b < batch; b += gridDim.x) {
     // the rows of the previous system have left Z (bulk groups are per thread)
@@ -167,10 +153,6 @@ extend_fused_kernel(const double* __restrict__ A, const double* __restrict__ B,
         const double v = cur[e];
         if (c < n) {
           if (Sb) Sb[((long)k * n + c) * n + i] = v;  // S[k][c][i] = (A^(k+1))[i][c]
-        } else if (dense) {
-          // Gam_k[i][j] = U[j][k'][k' - k][i] for every k' >= k
-          double* img = Z + (size_t)(c - n) * zld + i;
-          for (int kk = k; kk < N; ++kk) img[((size_t)kk * N + (kk - k)) * n] = v;
         } else {
           const int x = (c - n) * zld + (N - 1 - k) * n + i;
           Z[x] = v;
@@ -188,11 +170,6 @@ extend_fused_kernel(const double* __restrict__ A, const double* __restrict__ B,
     asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
     __syncthreads();
     double* Ub = U + b * (long)m * N * row_len;
-    if (dense) {  // the images of all inputs are one contiguous block: pieces of <= 8 kB
-      const long total = (long)m * zld, piece = 1024;
-      for (long at = (long)tid * piece; at < total; at += (long)blockDim.x * piece)
-        bulk_row(Ub + at, Z + at, (unsigned)((total - at < piece ? total - at : piece) * 8));
-    } else
     for (int r = tid; r < m * N; r += blockDim.x) {
       const int j = r / N, k = r - j * N;
       const int start = (N - 1 - k) * n;
@@ -210,9 +187,8 @@ int launch_fused(const double* A, const double* B, double* S, double* U, int bat
                  int N, cudaStream_t st, bool* launched) {
   *launched = false;
   if (!U || ((long)N * n) % 2 != 0 || (reinterpret_cast<uintptr_t>(U) & 15) != 0) return 0;
-  const bool dense = (long)N * n * 8 < 2048 && sizeof(double) * dense_smem_doubles(n, m, N) <= 56 * 1024;
-  const bool shifted = !dense && (n % 2) != 0;
-  const size_t smem = sizeof(double) * (dense ? dense_smem_doubles(n, m, N) : fused_smem_doubles(n, m, N, shifted));
+  const bool shifted = (n % 2) != 0;
+  const size_t smem = sizeof(double) * fused_smem_doubles(n, m, N, shifted);
   if (smem > 227 * 1024) return 0;
   if (smem > 48 * 1024)
     MPCI_CUDA(cudaFuncSetAttribute(extend_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -229,8 +205,7 @@ int launch_fused(const double* A, const double* B, double* S, double* U, int bat
   if (per_sm < 1) return 0;
   const long resident = (long)sms * per_sm;
   const unsigned blocks = (unsigned)(batch < resident ? batch : resident);
-  extend_fused_kernel<<<blocks, threads, smem, st>>>(A, B, S, U, batch, n, m, N, shifted ? 1 : 0,
-                                                     dense ? 1 : 0);
+  extend_fused_kernel<<<blocks, threads, smem, st>>>(A, B, S, U, batch, n, m, N, shifted ? 1 : 0);
   MPCI_LAUNCH_CHECK("extend_fused_kernel");
   *launched = true;
   return 0;

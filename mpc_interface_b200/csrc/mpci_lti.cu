@@ -95,7 +95,7 @@ __host__ __device__ inline size_t lti_aux_doubles(int m, int N, size_t patches) 
 // so that the double2 stores of the DMMA fragments (rows g, g+1 per quarter-warp) do not
 // collide on a bank
 __host__ __device__ inline int lti_rows_ldp(int N) {
-  int x = (N + 7) / 8 * 8;
+  int x = (N + 2 + 7) / 8 * 8;  // whole 8 x 8 tiles, at least two (zero) columns past the block
   while (x % 16 != 8) x += 8;
   return x;
 }
@@ -145,23 +145,30 @@ __device__ __forceinline__ void dmma8x8x4(double& d0, double& d1, double a, doub
 
 // One 8x8 tile of D = X Y on the FP64 tensor cores: X is n x n, row-major in shared
 // memory (SYM: its symmetric part), Y(l, x) = Y[l * ys + x].  Lane (g, t) gets
-// D[i0 + g][x0 + 2t] and D[i0 + g][x0 + 2t + 1].  No branches: indices past n are clamped
-// and the X operand is zeroed there, so rows i >= n come out as zeros; columns whose Y
-// entries are not valid data yet give garbage in THAT column only -- the caller does not
-// store them.
-template <bool SYM>
+// D[i0 + g][x0 + 2t] and D[i0 + g][x0 + 2t + 1].  Row g of D depends on row g of X only,
+// so rows i >= n are simply read from row n - 1 (in bounds) and come out as garbage the
+// caller does not store; likewise columns whose Y entries are not valid data yet.  Only
+// the padding of K to a multiple of 4 must contribute exact zeros (KFULL: there is none).
+template <bool SYM, bool KFULL>
 __device__ __forceinline__ void small_tile(const double* X, int n, const double* Y, int ys, int i0,
                                            int x0, int g, int t, double& d0, double& d1) {
   d0 = d1 = 0.0;
-  const int i = i0 + g, ic = min(i, n - 1);
-  const double* Xi = X + ic * n;
-  const double* Xt = X + ic;  // column ic, for the transposed read of SYM
-  const double* Yg = Y + x0 + g;
-  for (int l = t; l < n + t; l += 4) {  // the same trip count on every lane
-    const int lc = min(l, n - 1);
-    double av = SYM ? 0.5 * (Xi[lc] + Xt[lc * n]) : Xi[lc];
-    const double bv = Yg[lc * ys];
-    if (i >= n || l >= n) av = 0.0;
+  const int ic = min(i0 + g, n - 1);
+  const double* Xi = X + ic * n + t;
+  const double* Xt = X + ic + t * n;  // column ic, for the transposed read of SYM
+  const double* Yg = Y + x0 + g + t * ys;
+  const int full = n >> 2;
+  for (int ks = 0; ks < full; ++ks, Xi += 4, Xt += 4 * n, Yg += 4 * ys) {
+    const double av = SYM ? 0.5 * (Xi[0] + Xt[0]) : Xi[0];
+    dmma8x8x4(d0, d1, av, Yg[0]);
+  }
+  if (!KFULL) {
+    const bool k_ok = 4 * full + t < n;
+    double av = 0.0, bv = 0.0;
+    if (k_ok) {
+      av = SYM ? 0.5 * (Xi[0] + Xt[0]) : Xi[0];
+      bv = Yg[0];
+    }
     dmma8x8x4(d0, d1, av, bv);
   }
 }
@@ -175,6 +182,7 @@ __device__ __forceinline__ int magic_div(int e, unsigned magic) {
 // ---------------------------------------------------------------------------
 // phase 1 + 2: prediction data of instance b
 // ---------------------------------------------------------------------------
+template <bool KFULL>
 __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
   const int n = a.n, m = a.m, N = a.N, w = a.m + 1, LD = a.LD, pad = a.pad, tid = threadIdx.x;
   const int lane = tid & 31, warp = tid >> 5;
@@ -232,14 +240,14 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
       if (idx < n_dbl) {
         const int rc = magic_div(idx, magic_dt), dt = idx - rc * n_dt;
         const int it = magic_div(rc, magic_w), c = rc - it * w;
-        small_tile<false>(M0, n, s.gz + c * LD + pad, wLD, it * 8, dt * 8, g, t, d0, d1);
+        small_tile<false, KFULL>(M0, n, s.gz + c * LD + pad, wLD, it * 8, dt * 8, g, t, d0, d1);
         const int i = it * 8 + g, x = dt * 8 + 2 * t;
         double* o = s.gz + (i * w + c) * LD + pad + have + x;
         if (i < n && x < cnt) o[0] = d0;
         if (i < n && x + 1 < cnt) o[1] = d1;
       } else {
         const int e = idx - n_dbl, it = magic_div(e, magic_it), ct = e - it * it_n;
-        small_tile<false>(M0, n, M0, n, it * 8, ct * 8, g, t, d0, d1);
+        small_tile<false, KFULL>(M0, n, M0, n, it * 8, ct * 8, g, t, d0, d1);
         const int i = it * 8 + g, x = ct * 8 + 2 * t;
         if (i < n && x < n) M1[i * n + x] = d0;
         if (i < n && x + 1 < n) M1[i * n + x + 1] = d1;
@@ -260,14 +268,14 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
     if (idx < n_wz) {
       const int rc = magic_div(idx, magic_dt), dt = idx - rc * n_dt;
       const int it = magic_div(rc, magic_m), j = rc - it * m;
-      small_tile<false>(s.Q, n, s.gz + j * LD + pad, wLD, it * 8, dt * 8, g, t, d0, d1);
+      small_tile<false, KFULL>(s.Q, n, s.gz + j * LD + pad, wLD, it * 8, dt * 8, g, t, d0, d1);
       const int i = it * 8 + g, x = dt * 8 + 2 * t;
       double* o = s.wz + (i * m + j) * a.LDw + pad + x;
       if (i < n && x < N) o[0] = d0;
       if (i < n && x + 1 < N) o[1] = d1;
     } else {
       const int e = idx - n_wz, it = magic_div(e, magic_dt), dt = e - it * n_dt;
-      small_tile<true>(s.Q, n, s.gz + m * LD + pad + 1, wLD, it * 8, dt * 8, g, t, d0, d1);
+      small_tile<true, KFULL>(s.Q, n, s.gz + m * LD + pad + 1, wLD, it * 8, dt * 8, g, t, d0, d1);
       const int i = it * 8 + g, x = dt * 8 + 2 * t;
       const double txi = s.tx[min(i, n - 1)];
       if (i < n && x < N) s.r[i * N + x] = d0 - txi;
@@ -548,68 +556,61 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
 // only reach T entries nobody reads (as in hessian_scan).
 // ---------------------------------------------------------------------------
 // NT column tiles (8 x 8 each) of the band's T patch: K = n in steps of 4, operands straight
-// from the Toeplitz generators (one LDS each), results parked in the warp's patch
-template <bool KFULL, int NT>
+// from the Toeplitz generators (one LDS each), results parked in the warp's patch.
+// MASKED: the group's last two tiles may reach past column N - 1; there the lanes whose
+// column does not exist (ok0 / ok1 false) feed zeros, so those patch columns hold exact
+// zeros (the row scan relies on that).
+template <bool KFULL, int NT, bool MASKED>
 __device__ __forceinline__ void rows_tiles(const double* gk, const double* wk, long ga_step, long wb_step,
-                                           int n, int t, double2* dst) {
+                                           int n, int t, double2* dst, bool ok0, bool ok1) {
   double acc[NT][2];
 #pragma unroll
   for (int y = 0; y < NT; ++y) acc[y][0] = acc[y][1] = 0.0;
-  for (int ks = 0; ks < (n >> 2); ++ks, gk += ga_step, wk += wb_step) {
-    const double av = gk[0];
-    double bv[NT];
-#pragma unroll
-    for (int y = 0; y < NT; ++y) bv[y] = wk[-8 * y];
-#pragma unroll
-    for (int y = 0; y < NT; ++y) dmma8x8x4(acc[y][0], acc[y][1], av, bv[y]);
-  }
-  if (!KFULL) {  // the last, partial step of K: states past n contribute exact zeros
-    const bool k_ok = (n & ~3) + t < n;
+  auto step = [&](bool k_ok) {
     const double av = k_ok ? gk[0] : 0.0;
     double bv[NT];
 #pragma unroll
     for (int y = 0; y < NT; ++y) bv[y] = k_ok ? wk[-8 * y] : 0.0;
+    if (MASKED) {
+      if (NT >= 2 && !ok0) bv[NT >= 2 ? NT - 2 : 0] = 0.0;
+      if (!ok1) bv[NT - 1] = 0.0;
+    }
 #pragma unroll
     for (int y = 0; y < NT; ++y) dmma8x8x4(acc[y][0], acc[y][1], av, bv[y]);
-  }
+  };
+  for (int ks = 0; ks < (n >> 2); ++ks, gk += ga_step, wk += wb_step) step(true);
+  if (!KFULL) step((n & ~3) + t < n);  // the last, partial step of K
 #pragma unroll
   for (int y = 0; y < NT; ++y) dst[4 * y] = make_double2(acc[y][0], acc[y][1]);
 }
 
+__device__ __forceinline__ double2 lds128(unsigned addr) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];\n" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+  return v;
+}
+
+// CT column tiles: 8 CT - 2 >= N, so the patch keeps two zero columns after the block
 template <bool KFULL, int CT>
 __device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
-  const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1, LDP = a.ldp;
+  constexpr int LDP = (8 * CT) % 16 == 8 ? 8 * CT : 8 * CT + 8;  // = lti_rows_ldp
+  constexpr int T0 = CT > 4 ? CT / 2 : CT, T1 = CT - T0;          // two groups (register budget)
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1;
   const long nv = (long)a.m * a.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (warp >= a.scan_warps) return;
   const int g = lane >> 2, t = lane & 3;
   double* tw = s.tb + (size_t)warp * 8 * LDP;
   double2* tst = reinterpret_cast<double2*>(tw + g * LDP + 2 * t);  // this lane's C slots of tile 0
-  const double* trow = tw + 2 * lane;                                 // this lane's two columns
   const long ga_step = (long)4 * w * LD, wb_step = (long)4 * m * a.LDw;
   const int col = 2 * lane;
   const bool act0 = col < N, act1 = col + 1 < N;
+  // the lane's two columns; lanes past the tiles read the tiles' last two columns, which
+  // are zero (8 CT - 2 >= N)
+  const unsigned trow = (unsigned)__cvta_generic_to_shared(tw) + 8u * (unsigned)min(col, 8 * CT - 2);
   const bool vec = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0);
-  constexpr int T0 = CT < 4 ? CT : 4, T1 = CT - T0;  // two groups of tiles (register budget)
-
-  // one row of the block: the lane's two entries from the patch row, the carries of the
-  // row below (column 2 lane + 2 lives in lane + 1), a 16-byte store.  Lanes past the
-  // block read nothing and keep their carries at zero.
-  auto row_step = [&](const double* trow_r, double& c0, double& c1, double* dst) {
-    double2 tv = make_double2(0.0, 0.0);
-    if (act0) tv = *reinterpret_cast<const double2*>(trow_r);
-    if (!act1) tv.y = 0.0;
-    const double up = __shfl_down_sync(0xffffffffu, c0, 1);
-    const double n0 = tv.x + c1, n1 = tv.y + up;
-    c0 = n0;
-    c1 = n1;
-    if (vec) {
-      if (act0) __stcs(reinterpret_cast<double2*>(dst), make_double2(n0, n1));
-    } else {
-      if (act0) __stcs(dst, n0);
-      if (act1) __stcs(dst + 1, n1);
-    }
-  };
+  // columns of the last two tiles that exist
+  const bool ok0 = 8 * (CT - 2) + g < N, ok1 = 8 * (CT - 1) + g < N;
 
   for (;;) {
     int item = 0;
@@ -623,20 +624,40 @@ __device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict
     const double* ga = s.gz + (size_t)(t * w + j) * LD + a.pad + (7 - g);           // band p0 = N - 8
     const double* wb = s.wz + (size_t)(t * m + jp) * a.LDw + a.pad + (N - 1 - g);
     double* dst = Pb + (size_t)(j * N + N - 1) * nv + (size_t)jp * N + col;        // row N - 1
-    int p0 = N - 8;
-    for (; p0 >= 0; p0 -= 8, ga += 8) {  // full bands: rows p0 .. p0 + 7, bottom band first
-      rows_tiles<KFULL, T0>(ga, wb, ga_step, wb_step, n, t, tst);
-      if (T1 > 0) rows_tiles<KFULL, (T1 > 0 ? T1 : 1)>(ga, wb - 32, ga_step, wb_step, n, t, tst + 16);
+    for (int p0 = N - 8; p0 > -8; p0 -= 8, ga += 8) {  // rows p0 .. p0 + 7, bottom band first
+      if (T1 > 0) {
+        rows_tiles<KFULL, T0, false>(ga, wb, ga_step, wb_step, n, t, tst, true, true);
+        rows_tiles<KFULL, (T1 > 0 ? T1 : 1), true>(ga, wb - 8 * T0, ga_step, wb_step, n, t, tst + 4 * T0, ok0, ok1);
+      } else {
+        rows_tiles<KFULL, T0, true>(ga, wb, ga_step, wb_step, n, t, tst, ok0, ok1);
+      }
       __syncwarp();
+      // one row of the block per step: the lane's two entries of the patch row plus the
+      // carries of the row below (column 2 lane + 2 lives in lane + 1), one 16-byte store
+      const int r_min = p0 < 0 ? -p0 : 0;  // the top band overhangs row 0
+      if (vec && r_min == 0) {
 #pragma unroll
-      for (int r = 7; r >= 0; --r, dst -= nv) row_step(trow + r * LDP, c0, c1, dst);
-      __syncwarp();
-    }
-    if (p0 > -8) {  // the top band overhangs row 0: rows 0 .. p0 + 7
-      rows_tiles<KFULL, T0>(ga, wb, ga_step, wb_step, n, t, tst);
-      if (T1 > 0) rows_tiles<KFULL, (T1 > 0 ? T1 : 1)>(ga, wb - 32, ga_step, wb_step, n, t, tst + 16);
-      __syncwarp();
-      for (int r = 7; r >= -p0; --r, dst -= nv) row_step(trow + r * LDP, c0, c1, dst);
+        for (int r = 7; r >= 0; --r, dst -= nv) {
+          const double2 tv = lds128(trow + 8u * (unsigned)(r * LDP));
+          const double up = __shfl_down_sync(0xffffffffu, c0, 1);
+          c0 = tv.x + c1;
+          c1 = tv.y + up;
+          if (act0) __stcs(reinterpret_cast<double2*>(dst), make_double2(c0, c1));
+        }
+      } else {
+        for (int r = 7; r >= r_min; --r, dst -= nv) {
+          const double2 tv = lds128(trow + 8u * (unsigned)(r * LDP));
+          const double up = __shfl_down_sync(0xffffffffu, c0, 1);
+          c0 = tv.x + c1;
+          c1 = tv.y + up;
+          if (vec) {
+            if (act0) __stcs(reinterpret_cast<double2*>(dst), make_double2(c0, c1));
+          } else {
+            if (act0) __stcs(dst, c0);
+            if (act1) __stcs(dst + 1, c1);
+          }
+        }
+      }
       __syncwarp();
     }
   }
@@ -644,7 +665,7 @@ __device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict
 
 template <bool KFULL>
 __device__ void hessian_rows_any(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
-  switch ((a.N + 7) >> 3) {  // column tiles of a block (N <= 60)
+  switch ((a.N + 2 + 7) >> 3) {  // column tiles: two zero columns follow the block (N <= 60)
     case 1: return hessian_rows<KFULL, 1>(a, s, Pb);
     case 2: return hessian_rows<KFULL, 2>(a, s, Pb);
     case 3: return hessian_rows<KFULL, 3>(a, s, Pb);
@@ -784,6 +805,34 @@ __device__ __forceinline__ void group_windows(const LtiArgs& a, const Smem& s, l
   }
 }
 
+// A group without a state part (cx = 0: input boxes and the like) whose arrow is the same on
+// every row: row k is  scale * cu[j]  at column j N + k and zero elsewhere, i.e. the window
+// L[N-1-k .. N-1-k + m N) of ONE line  L[y] = scale * cu[j] at y = N - 1 + j N  -- a single
+// bulk copy of the whole row (m N doubles) instead of one per input block, and no window
+// arithmetic at all.  L1 is the copy shifted by one element (16-byte aligned sources).
+__device__ __forceinline__ void group_line(const LtiArgs& a, long b, int grp, double* L, double* L1,
+                                           double* __restrict__ hb, int tid, int nthreads) {
+  const int m = a.m, N = a.N, len = (m + 1) * N;
+  const double* arrow = a.arrow + (size_t)grp * N;
+  const double* cu = a.cu + b * a.scu + (size_t)grp * m;
+  const double* bound = a.bound + b * a.sbd + (size_t)grp * N;
+  const int k0 = a.grp_k0[grp], k1 = k0 + a.grp_cnt[grp];
+  const double scale = __ldg(arrow + k0);
+  for (int y = tid; y < len; y += nthreads) {
+    double v = 0.0, v1 = 0.0;  // L[y], L[y + 1]
+    for (int j = 0; j < m; ++j) {
+      if (y == N - 1 + j * N) v = scale * __ldg(cu + j);
+      if (y + 1 == N - 1 + j * N) v1 = scale * __ldg(cu + j);
+    }
+    L[y] = v;
+    L1[y] = v1;
+  }
+  if (hb) {
+    double* hg = hb + a.grp_row0[grp] - k0;
+    for (int k = k0 + tid; k < k1; k += nthreads) hg[k] = __ldg(bound + k);
+  }
+}
+
 // rows of a group whose arrow changes from row to row (or that are not 16-byte aligned):
 // warps warp0, warp0 + nwarps, ... scale and store the windows themselves
 __device__ __forceinline__ void group_rows_by_warps(const LtiArgs& a, int grp, const double* cz,
@@ -833,12 +882,27 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, long b, double*
       bulk_wait_read<1>();
       __syncthreads();
     }
-    group_windows(a, s, b, grp, cz, cz1, bulk, hb, tid, (int)blockDim.x, magic_2N);
+    const bool line = bulk && !(a.grp_state[grp] & 1) && m <= 8;  // no state part: one copy per row
+    if (line) group_line(a, b, grp, cz, cz + (((m + 1) * N + 1) & ~1), hb, tid, (int)blockDim.x);
+    else group_windows(a, s, b, grp, cz, cz1, bulk, hb, tid, (int)blockDim.x, magic_2N);
     fence_async_smem();  // the windows must be visible to the async proxy
     __syncthreads();
     if (!Gb) continue;
     double* rows = Gb + (size_t)a.grp_row0[grp] * nv;
     const int k0 = a.grp_k0[grp], k1 = k0 + a.grp_cnt[grp];
+    if (line) {
+      const double* L = cz;
+      const double* L1 = cz + (((m + 1) * N + 1) & ~1);
+      // copies of 800 bytes and more go out fastest from one lane per warp, shorter ones
+      // from all lanes (profiles/r01_tma_rate.txt)
+      const int issue_lanes = (nv < 100) ? 32 : 1;
+      for (int k = k0 + warp + nwarps * lane; lane < issue_lanes && k < k1; k += nwarps * issue_lanes) {
+        const int start = N - 1 - k;
+        bulk_store(rows + (size_t)(k - k0) * nv, (start & 1) ? L1 + (start - 1) : L + start, (unsigned)nv * 8u);
+      }
+      bulk_commit();
+      continue;
+    }
     if (bulk) {
       // Short rows (< 2 kB per copy): every lane issues, the cost is the issue itself
       // (a single issuing warp per CTA fed through named barriers was measured at C4:
@@ -873,7 +937,8 @@ lti_assemble_kernel(LtiArgs a) {
   const size_t nv = (size_t)a.m * a.N, nc = (size_t)a.nc;
   for (long b = blockIdx.x; b < a.batch; b += gridDim.x) {
     __syncthreads();  // the previous instance is done with shared memory
-    build_prediction(a, s, b);
+    if (a.n % 4 == 0) build_prediction<true>(a, s, b);
+    else build_prediction<false>(a, s, b);
     // P, q and G only read the prediction data, so their order is free: every other
     // resident CTA of an SM starts with the (store-bound, TMA-driven) constraint rows
     // while its neighbours are in the (issue-bound) Hessian, instead of all of them

@@ -68,10 +68,13 @@ def receding_tick(batch=65536, N=100):
     torch.cuda.synchronize()
     cold = time.perf_counter() - t0
     n_struct = len(done)
-    # one plan compile alone (a structure not seen yet: another parity / window)
-    t0 = time.perf_counter()
+    # one plan compile alone: Formulation.update to the structure of instance 0 on a fresh
+    # formulation (the set-up of the formulation itself -- SymPy discretisation, qhull -- is
+    # not part of a tick and is left out)
     form = factory()
-    form.update(step_times=times[0] + 1000, step_count=1)  # no step inside the window
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    form.update(**kargs_of(0))
     torch.cuda.synchronize()
     compile_ms = (time.perf_counter() - t0) * 1e3
     # all scalars of the batch evaluated once (the structures share the slot order)
@@ -88,6 +91,16 @@ def receding_tick(batch=65536, N=100):
     for _ in range(2):
         assemble_tick()
     torch.cuda.synchronize()
+    if os.environ.get("MPCI_PROFILE_TICK"):
+        import cProfile
+        import pstats
+
+        prof = cProfile.Profile()
+        prof.enable()
+        assemble_tick()
+        torch.cuda.synchronize()
+        prof.disable()
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("cumulative").print_stats(35)
     reps = 5
     t0 = time.perf_counter()
     for _ in range(reps):
@@ -190,7 +203,9 @@ def run():
         try:
             out[name] = fn()
         except Exception as e:  # an extra must never cost the headline line
-            out[name] = {"error": "%s: %s" % (type(e).__name__, e)}
+            import traceback
+
+            out[name] = {"error": "%s: %s" % (type(e).__name__, e), "where": traceback.format_exc()[-600:]}
     return out
 
 

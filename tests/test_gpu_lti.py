@@ -141,7 +141,8 @@ def test_lti_launch_info(dev):
     form, params, _ = cases.generic_batched(g)
     plan = form.lti_plan("plant")
     dm, rec = plan.launch_info(lti.HESSIAN_DMMA), plan.launch_info(lti.HESSIAN_RECURSION)
-    assert dm["scan"] == 0 and rec["scan"] == 1
+    # N = 50: whole rows of a block per warp (scan 2); long horizons keep the band scan (1)
+    assert dm["scan"] == 0 and rec["scan"] == 2
     assert rec["smem_bytes"] < dm["smem_bytes"] <= 227 * 1024
     assert rec["ctas_per_sm"] >= dm["ctas_per_sm"] >= 1
     # skewed rows: (rows * LD) mod 16 in {4, 12} for the strided DMMA operand loads
