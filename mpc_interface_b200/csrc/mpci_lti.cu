@@ -321,34 +321,48 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
         sub_span[x][y] = N - max(p0 + 8 * x, q0 + 8 * y);
       }
 
-    // steps in which every sub-tile is inside its span run without predicates
+    // K runs over (step of four samples, state): the steps outermost, so that what depends
+    // on the step -- which sub-tiles are still inside their span -- is decided once per
+    // step and not once per step and state (short horizons: the spans are a dozen steps)
     const int full = max(0, N - max(p0 + 8 * (TM - 1), q0 + 8 * (TN - 1))) & ~3;
-    for (int i = 0; i < n; ++i) {
-      const double* ga = s.gz + (size_t)(i * (m + 1) + j) * LD + kPadL + (N - 1 - t - p0 - g);
-      const double* wb = s.wz + (size_t)(i * m + jp) * a.LDw + kPadL + (N - 1 - t - q0 - g);
+    const double* ga0 = s.gz + (size_t)j * LD + kPadL + (N - 1 - t - p0 - g);
+    const double* wb0 = s.wz + (size_t)jp * a.LDw + kPadL + (N - 1 - t - q0 - g);
+    const long gi = (long)(m + 1) * LD, wi = (long)m * a.LDw;
+    for (int s0 = 0; s0 < full; s0 += 4) {  // every sub-tile inside its span: no predicates
+      const double* ga = ga0 - s0;
+      const double* wb = wb0 - s0;
 #pragma unroll 2
-      for (int s0 = 0; s0 < full; s0 += 4) {
+      for (int i = 0; i < n; ++i, ga += gi, wb += wi) {
         double av[TM], bv[TN];
 #pragma unroll
-        for (int x = 0; x < TM; ++x) av[x] = ga[-s0 - 8 * x];
+        for (int x = 0; x < TM; ++x) av[x] = ga[-8 * x];
 #pragma unroll
-        for (int y = 0; y < TN; ++y) bv[y] = wb[-s0 - 8 * y];
+        for (int y = 0; y < TN; ++y) bv[y] = wb[-8 * y];
 #pragma unroll
         for (int x = 0; x < TM; ++x)
 #pragma unroll
           for (int y = 0; y < TN; ++y) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
       }
-      for (int s0 = full; s0 < span; s0 += 4) {  // the triangular tail of the tile
+    }
+    for (int s0 = full; s0 < span; s0 += 4) {  // the triangular tail of the tile
+      bool on[TM][TN];
+#pragma unroll
+      for (int x = 0; x < TM; ++x)
+#pragma unroll
+        for (int y = 0; y < TN; ++y) on[x][y] = s0 < sub_span[x][y];
+      const double* ga = ga0 - s0;
+      const double* wb = wb0 - s0;
+      for (int i = 0; i < n; ++i, ga += gi, wb += wi) {
         double av[TM], bv[TN];
 #pragma unroll
-        for (int x = 0; x < TM; ++x) av[x] = ga[-s0 - 8 * x];
+        for (int x = 0; x < TM; ++x) av[x] = ga[-8 * x];
 #pragma unroll
-        for (int y = 0; y < TN; ++y) bv[y] = wb[-s0 - 8 * y];
+        for (int y = 0; y < TN; ++y) bv[y] = wb[-8 * y];
 #pragma unroll
         for (int x = 0; x < TM; ++x)
 #pragma unroll
           for (int y = 0; y < TN; ++y)
-            if (s0 < sub_span[x][y]) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
+            if (on[x][y]) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
       }
     }
     // epilogue: + Quu[j][j'] on the diagonal of the block, store

@@ -169,12 +169,25 @@ def structure_keys(horizon_lenght, step_times, step_count):
     ``receding.StructureBuckets.group_keys``: the step times inside the preview window
     (the others masked to -1) and the parity of the step count.  Two instances get equal
     rows exactly when ``structure_key`` gives them equal keys."""
+    if hasattr(step_times, "is_cuda"):  # CUDA tensors in, a CUDA tensor out (same rows)
+        import torch
+
+        times = step_times.to(torch.int64)
+        inside = (times >= 0) & (times < horizon_lenght - 1)
+        big = torch.iinfo(torch.int64).max
+        rows = torch.where(inside, times, torch.full_like(times, big))
+        rows = torch.sort(rows, dim=1).values
+        rows = torch.where(rows == big, torch.full_like(rows, -1), rows)
+        parity = (torch.as_tensor(step_count, device=times.device).to(torch.int64) % 2).reshape(-1, 1)
+        return torch.cat([rows, parity], dim=1)
     times = np.asarray(step_times).astype(np.int64)
     inside = (times >= 0) & (times < horizon_lenght - 1)
     # the inside times left-aligned (sorted, the masked ones last), so that a row depends on
     # the SET of inside times alone, as the tuple of structure_key does
     big = np.iinfo(np.int64).max
-    rows = np.sort(np.where(inside, times, big), axis=1)
+    rows = np.where(inside, times, big)
+    if rows.shape[1] > 1 and not np.all(rows[:, :-1] <= rows[:, 1:]):
+        rows = np.sort(rows, axis=1)  # (ascending step times: already in place)
     rows = np.where(rows == big, -1, rows)
     parity = (np.asarray(step_count).astype(np.int64) % 2).reshape(-1, 1)
     return np.concatenate([rows, parity], axis=1)

@@ -332,34 +332,30 @@ class Box:
 
 
 def box_boundaries(vertices):
-    """Outward unit normals, offsets and centroid of the convex hull of
-    ``vertices`` (one vertex per row)  (restrictions.py:492-531).  Facets are
-    listed in qhull's simplex order."""
-    import scipy.spatial as sp
+    """Facet normals (unit length), facet offsets from the centroid and the centroid of the
+    convex hull of ``vertices`` (one vertex per row) -- what restrictions.py:492-531 hands to
+    ``Box``.  The facets come in qhull's simplex order, because that order becomes the row
+    order of G; the normal of a facet is the 90-degree turn of its edge (2-D) or the cross
+    product of two of its edges (3-D), as qhull lists the vertices, and is NOT re-oriented
+    here: ``Constraint.normalize`` flips a limit whose offset comes out negative."""
+    import scipy.spatial
 
-    vertices = vertices.astype("float64")
-    count, dim = vertices.shape
-    center = vertices.sum(axis=0) / count
-    if dim == 1:
-        simplices = np.array([[0], [1]])
-        arrows = np.ones([2, 1])
-    elif dim == 2:
-        simplices = sp.ConvexHull(vertices).simplices
-        edge = vertices[simplices[:, 0]] - vertices[simplices[:, 1]]
-        arrows = np.column_stack([edge[:, 1], -edge[:, 0]])
-    elif dim == 3:
-        simplices = sp.ConvexHull(vertices).simplices
-        e0 = vertices[simplices[:, 0]] - vertices[simplices[:, 2]]
-        e1 = vertices[simplices[:, 1]] - vertices[simplices[:, 2]]
-        arrows = np.column_stack(
-            [
-                e0[:, 1] * e1[:, 2] - e0[:, 2] * e1[:, 1],
-                e0[:, 2] * e1[:, 0] - e0[:, 0] * e1[:, 2],
-                e0[:, 0] * e1[:, 1] - e0[:, 1] * e1[:, 0],
-            ]
-        )
-    for i in range(arrows.shape[0]):
-        arrows[i] = arrows[i] / np.linalg.norm(arrows[i])
-    anchor = vertices[simplices[:, 0]]
-    extremes = np.sum(arrows * (anchor - center), axis=1).reshape([-1, 1])
-    return arrows, extremes, center
+    points = np.asarray(vertices, dtype="float64")
+    dim = points.shape[1]
+    centroid = points.sum(axis=0) / points.shape[0]
+    if dim == 1:  # a segment: its two ends, both with the normal +1
+        facets = np.array([[0], [1]])
+        normals = np.ones([2, 1])
+    elif dim in (2, 3):
+        facets = scipy.spatial.ConvexHull(points).simplices
+        corner = points[facets]  # [facet, vertex of the facet, coordinate]
+        if dim == 2:
+            quarter_turn = np.array([[0.0, -1.0], [1.0, 0.0]])  # (x, y) -> (y, -x)
+            normals = (corner[:, 0] - corner[:, 1]) @ quarter_turn
+        else:
+            normals = np.cross(corner[:, 0] - corner[:, 2], corner[:, 1] - corner[:, 2])
+    else:
+        raise ValueError("boxes are built in 1, 2 or 3 dimensions, not {}".format(dim))
+    normals = normals / np.linalg.norm(normals, axis=1, keepdims=True)
+    offsets = ((points[facets[:, 0]] - centroid) * normals).sum(axis=1, keepdims=True)
+    return normals, offsets, centroid

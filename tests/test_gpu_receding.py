@@ -159,6 +159,15 @@ def test_device_tick_equals_the_per_instance_grouping():
         assert np.array_equal(idx_w, idx_g.cpu().numpy())
         for x, y in ((qp_w.P, qp_g.P), (qp_w.q, qp_g.q), (qp_w.G, qp_g.G), (qp_w.h, qp_g.h)):
             assert torch.equal(x, y)
+    # key rows computed and grouped on the device: the same buckets (ordered by key there)
+    dev_keys = structure_keys(N, torch.from_numpy(times).cuda(), torch.from_numpy(count).cuda())
+    assert np.array_equal(dev_keys.cpu().numpy(), structure_keys(N, times, count))
+    on_dev = b.assemble_device(dev_keys, lambda i: kargs[i], collector, params=params)
+    by_key = {k: (idx, qp) for k, idx, _, qp in got}
+    assert len(on_dev) == len(got)
+    for k, idx, _, qp in on_dev:
+        assert np.array_equal(idx.cpu().numpy(), by_key[k][0].cpu().numpy())
+        assert torch.equal(qp.P, by_key[k][1].P) and torch.equal(qp.h, by_key[k][1].h)
     # a second tick reuses plans and output slots
     slots = {k: v.P.data_ptr() for k, v in outs.items()}
     again = b.assemble_device(structure_keys(N, times, count), lambda i: kargs[i], collector,
