@@ -16,6 +16,7 @@
 //   5. G,h -- generated row by row, 16-byte coalesced stores
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -293,6 +294,24 @@ __device__ void build_prediction(const LtiArgs& a, const Smem& s, long b) {
 // 11 consecutive words per warp, so there are no bank conflicts; the zero
 // padding before d = 0 encodes causality (k >= p) without a branch.
 // ---------------------------------------------------------------------------
+// the XX x YY live sub-tiles of a warp tile, one step of four samples, all the states
+template <int XX, int YY>
+__device__ __forceinline__ void dmma_states(double (&acc)[TM][TN][2], const double* ga, const double* wb,
+                                            int n, long gi, long wi) {
+#pragma unroll 2
+  for (int i = 0; i < n; ++i, ga += gi, wb += wi) {
+    double av[XX], bv[YY];
+#pragma unroll
+    for (int x = 0; x < XX; ++x) av[x] = ga[-8 * x];
+#pragma unroll
+    for (int y = 0; y < YY; ++y) bv[y] = wb[-8 * y];
+#pragma unroll
+    for (int x = 0; x < XX; ++x)
+#pragma unroll
+      for (int y = 0; y < YY; ++y) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
+  }
+}
+
 __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
   const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -311,58 +330,35 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
     // it passes max(p, p') of the 8x8 sub-tile: below that every product has a
     // factor with d < 0 (block-triangular skipping, per sub-tile)
     const int span = N - max(p0, q0);
-    int sub_span[TM][TN];
     double acc[TM][TN][2];
 #pragma unroll
     for (int x = 0; x < TM; ++x)
 #pragma unroll
-      for (int y = 0; y < TN; ++y) {
-        acc[x][y][0] = acc[x][y][1] = 0.0;
-        sub_span[x][y] = N - max(p0 + 8 * x, q0 + 8 * y);
-      }
+      for (int y = 0; y < TN; ++y) acc[x][y][0] = acc[x][y][1] = 0.0;
 
-    // K runs over (step of four samples, state): the steps outermost, so that what depends
-    // on the step -- which sub-tiles are still inside their span -- is decided once per
-    // step and not once per step and state (short horizons: the spans are a dozen steps)
-    const int full = max(0, N - max(p0 + 8 * (TM - 1), q0 + 8 * (TN - 1))) & ~3;
+    // K runs over (step of four samples, state), the steps outermost.  Which sub-tiles are
+    // still inside their span depends on the step only, and they always form a rectangle
+    // XX x YY of the warp tile (sub-tile (x, y) is live while s0 < N - max(p0 + 8x, q0 + 8y)):
+    // the step picks the loop over the states that issues exactly those DMMAs -- none is
+    // issued predicated-off (at N = 50 the spans are a dozen steps and most of them are in
+    // the triangular tail: predicated-off DMMAs kept the tensor pipe 89 % busy at 55 % use)
     const double* ga0 = s.gz + (size_t)j * LD + kPadL + (N - 1 - t - p0 - g);
     const double* wb0 = s.wz + (size_t)jp * a.LDw + kPadL + (N - 1 - t - q0 - g);
     const long gi = (long)(m + 1) * LD, wi = (long)m * a.LDw;
-    for (int s0 = 0; s0 < full; s0 += 4) {  // every sub-tile inside its span: no predicates
+    for (int s0 = 0; s0 < span; s0 += 4) {
+      const int XX = min(TM, (N - s0 - p0 + 7) >> 3), YY = min(TN, (N - s0 - q0 + 7) >> 3);
       const double* ga = ga0 - s0;
       const double* wb = wb0 - s0;
-#pragma unroll 2
-      for (int i = 0; i < n; ++i, ga += gi, wb += wi) {
-        double av[TM], bv[TN];
-#pragma unroll
-        for (int x = 0; x < TM; ++x) av[x] = ga[-8 * x];
-#pragma unroll
-        for (int y = 0; y < TN; ++y) bv[y] = wb[-8 * y];
-#pragma unroll
-        for (int x = 0; x < TM; ++x)
-#pragma unroll
-          for (int y = 0; y < TN; ++y) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
-      }
-    }
-    for (int s0 = full; s0 < span; s0 += 4) {  // the triangular tail of the tile
-      bool on[TM][TN];
-#pragma unroll
-      for (int x = 0; x < TM; ++x)
-#pragma unroll
-        for (int y = 0; y < TN; ++y) on[x][y] = s0 < sub_span[x][y];
-      const double* ga = ga0 - s0;
-      const double* wb = wb0 - s0;
-      for (int i = 0; i < n; ++i, ga += gi, wb += wi) {
-        double av[TM], bv[TN];
-#pragma unroll
-        for (int x = 0; x < TM; ++x) av[x] = ga[-8 * x];
-#pragma unroll
-        for (int y = 0; y < TN; ++y) bv[y] = wb[-8 * y];
-#pragma unroll
-        for (int x = 0; x < TM; ++x)
-#pragma unroll
-          for (int y = 0; y < TN; ++y)
-            if (on[x][y]) dmma8x8x4(acc[x][y][0], acc[x][y][1], av[x], bv[y]);
+      switch (XX * 8 + YY) {
+        case 2 * 8 + 4: dmma_states<2, 4>(acc, ga, wb, n, gi, wi); break;
+        case 2 * 8 + 3: dmma_states<2, 3>(acc, ga, wb, n, gi, wi); break;
+        case 2 * 8 + 2: dmma_states<2, 2>(acc, ga, wb, n, gi, wi); break;
+        case 2 * 8 + 1: dmma_states<2, 1>(acc, ga, wb, n, gi, wi); break;
+        case 1 * 8 + 4: dmma_states<1, 4>(acc, ga, wb, n, gi, wi); break;
+        case 1 * 8 + 3: dmma_states<1, 3>(acc, ga, wb, n, gi, wi); break;
+        case 1 * 8 + 2: dmma_states<1, 2>(acc, ga, wb, n, gi, wi); break;
+        case 1 * 8 + 1: dmma_states<1, 1>(acc, ga, wb, n, gi, wi); break;
+        default: break;
       }
     }
     // epilogue: + Quu[j][j'] on the diagonal of the block, store
@@ -960,8 +956,11 @@ lti_assemble_kernel(LtiArgs a) {
     const bool limits = (a.G || a.h) && a.n_groups;
     // (with one CTA per SM the alternation is between neighbouring SMs: half of them stream
     // constraint rows while the other half computes -- measured 3% at C5)
+    // (three resident CTAs: two of them start with the rows -- measured at C4, 16,384 instances:
+    // 4.17 ms with one of three, 4.06 with two, 4.7-4.8 with none or all; scripts/gpu_lti_sweep.sh)
+    const int slot = a.per_sm == 1 ? (int)blockIdx.x : (int)(blockIdx.x / a.sms);  // resident slot
     const bool g_first = MODE == MPCI_LTI_HESSIAN_RECURSION &&
-                         (a.per_sm == 1 ? (blockIdx.x & 1) : ((blockIdx.x / a.sms) & 1));
+                         (a.per_sm == 3 ? (slot % 3 != 0) : (slot & 1));
     if (limits && g_first) {
       constraint_rows(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
                       a.h ? a.h + (size_t)b * nc : nullptr);

@@ -22,18 +22,17 @@ CONFIGS = {"c2 (LIP, n=3, m=1, N=100)": (3, 1, 100, 32768),
            "c1 (LIP, n=3, m=1, N=24)": (3, 1, 24, 262144)}
 
 
-def main():
+def run(reps=5):
+    """One line (dict) per configuration; needs a CUDA device."""
     import torch
     from mpc_interface_b200 import device
 
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--reps", type=int, default=5)
-    args = ap.parse_args()
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     # MEASURED_PEAKS.json (driver-written); the fallback is the B200_PROFILING.md figure
     peak = json.load(open(path))["hbm_gbs"] if os.path.exists(path) else 6650.0
     lib = device.lib()
     stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    lines = []
     for name, (n, m, N, batch) in CONFIGS.items():
         rng = np.random.default_rng(n * 100 + N)
         A = torch.from_numpy(np.eye(n) + 0.05 * rng.normal(size=[batch, n, n])).cuda()
@@ -48,16 +47,25 @@ def main():
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(args.reps):
+        for _ in range(reps):
             call()
         e1.record()
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / args.reps
+        ms = e0.elapsed_time(e1) / reps
         nbytes = 8.0 * batch * (N * n * n + m * N * N * n)
-        print(json.dumps({"config": name, "batch": batch, "ms": ms, "systems_per_s": batch / ms * 1e3,
-                          "bytes_per_system": nbytes / batch, "gbs": nbytes / ms / 1e6,
-                          "hbm_peak_gbs": peak, "frac": nbytes / ms / 1e6 / peak}), flush=True)
+        lines.append({"config": name, "batch": batch, "ms": ms, "systems_per_s": batch / ms * 1e3,
+                      "bytes_per_system": nbytes / batch, "gbs": nbytes / ms / 1e6,
+                      "hbm_peak_gbs": peak, "frac": nbytes / ms / 1e6 / peak})
         del S, U
+    return lines
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=5)
+    args = ap.parse_args()
+    for line in run(args.reps):
+        print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":

@@ -201,9 +201,21 @@ def generic_stream(batch=8192, N=100):
     return lines
 
 
+def k1_extend():
+    """scripts/bench_extend.py: K1 alone (batched extend_matrices, S and U in the reference's
+    layouts) at the sizes of C2 / C4 / C5 / C1."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("bench_extend", os.path.join(ROOT, "scripts", "bench_extend.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.run(3)
+
+
 def run():
     out = {}
-    for name, fn in (("receding_tick", receding_tick), ("generic_stream", generic_stream)):
+    for name, fn in (("receding_tick", receding_tick), ("generic_stream", generic_stream),
+                     ("k1_extend_matrices", k1_extend)):
         try:
             out[name] = fn()
         except Exception as e:  # an extra must never cost the headline line
