@@ -560,3 +560,42 @@ def test_integration_snippet_runs(dev):
         exec(compile(block, "INTEGRATION.md:snippet:plan", "exec"), {"__name__": "snippet"})
     finally:
         os.chdir(here)
+
+
+def test_large_and_small_batches_give_the_same_q_and_h(dev):
+    """[q; h] of a large batch (one persistent block per SM, every warp on its own lists) and
+    of a small one (several blocks share a group of instances); N = 200 adds a second pass
+    over the columns of [given; 1] to both.  Same instances -> bitwise the same q and h.
+    Only q and h are requested, so the 43 GB of P and G are not allocated."""
+    import ctypes
+
+    import torch
+    from mpc_interface_b200 import Param, device
+    from mpc_interface_b200.examples import synthetic
+
+    N, small, large = 200, 70, 9600
+    form = cases.formulate_biped(cases.default_configuration(N), omega=Param("omega"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    plan, ops = form._compiled(), form._ops()
+    vals = synthetic.biped_inputs(77, large, N)
+    given = torch.from_numpy(synthetic.pack_given(form.given_ID, form.given_len, vals, large)).cuda()
+    scal = torch.from_numpy(plan.slots.evaluate({k: vals[k] for k in ("omega", "vel_x", "vel_y")}, large)).cuda()
+    handle = ops.device_plan(plan).handle
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def qh(batch):
+        q = torch.full([batch, plan.nv], float("nan"), dtype=torch.float64, device="cuda")
+        h = torch.full([batch, plan.nc], float("nan"), dtype=torch.float64, device="cuda")
+        device.check(device.lib().mpci_assemble(handle, scal.data_ptr(), given.data_ptr(), None,
+                                                q.data_ptr(), None, h.data_ptr(), batch, stream))
+        return q, h
+
+    q_small, h_small = qh(small)
+    q_large, h_large = qh(large)
+    assert torch.equal(q_large[:small], q_small) and torch.equal(h_large[:small], h_small)
+    assert bool(torch.isfinite(q_large).all()) and bool(torch.isfinite(h_large).all())
+    b = large - 1  # and the last instance against the oracle
+    one = {k: float(vals[k][b]) for k in ("omega", "vel_x", "vel_y")}
+    ref = orc.all_qp_matrices(form, given[b].cpu().numpy()[:, None], one)
+    assert cases.rel_err(h_large[b].cpu().numpy(), ref[1][:, 0]) <= cases.TOL
+    assert cases.rel_err(q_large[b].cpu().numpy(), ref[3][:, 0]) <= cases.TOL
