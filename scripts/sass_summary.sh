@@ -15,4 +15,4 @@ cuobjdump -sass $LIB | awk '
   /STG\.E\.EF\.128/ { st128++ } /STG\.E\.EF\.64/ { st64++ } /LDS\.128/ { lds128++ } /SHFL/ { shfl++ }
   END { print name " | " n " | " dmma " | " ublk " | " flush " | " st128 " | " st64 " | " lds128 " | " shfl }' | c++filt | sed 's/(anonymous namespace):://g'
 echo "# excerpt: the DMMA loop of hessian_rows / hessian_scan in lti_assemble_kernel<1, 0> (first 12 DMMA lines with context)"
-cuobjdump -sass -fun '_ZN44_GLOBAL__N__14dcf290_11_mpci_lti_cu_d46b294319lti_assemble_kernelILi1ELi0EEEvNS_7LtiArgsE' $LIB 2>/dev/null | grep -E "DMMA|UBLKCP|STG.E.EF" | head -16
+cuobjdump -sass $LIB | awk '/Function :/ {f = ($0 ~ /lti_assemble_kernelILi1ELi0/)} f' | grep -E "DMMA|UBLKCP|STG.E.EF|LDS.128|SHFL.DOWN" | head -24
