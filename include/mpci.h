@@ -274,6 +274,68 @@ int mpci_lti_assemble_ex(const mpci_lti_plan* plan, const double* A_dev, long st
                          double* P_dev, double* q_dev, double* G_dev, double* h_dev, long batch,
                          int hessian_mode, void* stream);
 
+/* ---- per-instance plant INSIDE a larger formulation --------------------------------
+ * The biped of the reference's example (biped_formulation.py:23-191) with one plant per
+ * instance: besides the plant's inputs the QP has auxiliary optimisation variables z (the
+ * footstep displacements Ds of the shared `steps` system s = F s0 + E Ds, tools.py:79-101)
+ * and besides x0 it has auxiliary given variables (s0, the bias n); costs and limits are
+ * written on signals   f_k = cx . x_{k+1} + cu . u_k + Mz[k,:] z + Mg[k,:] given + const
+ * (`(b+n-s)`, `(DCM-s)`: LineCombos with the matrix coefficient of biped_formulation.py:57,63
+ * folded into Mz / Mg on the host).  Everything that involves only the plant is written by
+ * the fused kernel at its place in the larger matrices (the embedded layout below); the
+ * blocks that involve z or the auxiliary givens are written by a second kernel
+ * (csrc/mpci_couple.cu) from per-instance signals and formulation constants:
+ *   P[u,z] = sum_c w_c T_c^T Mz_c  (and its transpose),   P[z,z] = sum_c w_c Mz_c^T Mz_c
+ *   q[u]  += sum_c w_c T_c^T e_c,   q[z] = sum_c w_c Mz_c^T (fr_c + e_c)
+ *   G[r,z] = Gz[r,z],   h[r] (+)= Hg[r,:] . [given; 1]
+ * with T_c the Toeplitz operator of cost c's signal (rows k, columns (j,p): cx . Gam_{k-p}[:,j]
+ * + cu[j] [p == k]), fr_c[k] = cx . A^{k+1} x0 and e_c = E_c [given; 1] (body.py:236-302 for
+ * such a formulation).  All pointers are host pointers, copied at creation.               */
+typedef struct {
+  int nv_total;            /* variables of the QP (row length of P and G)                  */
+  int nc_total;            /* rows of G / h                                                */
+  const int* var_off;      /* [m] column of sample 0 of input j (its N samples contiguous) */
+  const int* grp_row0;     /* [n_groups] first row of every group of the mpci_lti_desc     */
+  int nz;                  /* auxiliary optimisation variables                             */
+  const int* z_col;        /* [nz] their columns                                           */
+  int given_len;           /* doubles per instance of `given_dev` (0: no auxiliary givens) */
+  int n_costs;             /* costs whose signal involves z or the auxiliary givens        */
+  const double* cost_cx;   /* [n_costs][n]   plant part of the signal                      */
+  const double* cost_cu;   /* [n_costs][m]                                                 */
+  const double* cost_w;    /* [n_costs]                                                    */
+  const double* cost_MzT;  /* [n_costs][nz][N]  (Mz transposed)                            */
+  const int* cost_e_ptr;   /* CSR over the rows (c, k): e_c[k] = sum val * [given; 1][col] */
+  const int* cost_e_col;   /*   [n_costs * N + 1], [nnz], [nnz]                            */
+  const double* cost_e_val;
+  const double* Pzz;       /* [nz][nz]                                                     */
+  const double* Gz;        /* [nc_total][nz]                                               */
+  const int* h_ptr;        /* CSR over the rows of h: [nc_total + 1], [nnz], [nnz]         */
+  const int* h_col;
+  const double* h_val;
+  const int* row_kind;     /* [nc_total] 0: a row of a plant group (the CSR part is ADDED  */
+                           /* to h); 1: a row without plant part (h = the CSR part, the    */
+                           /* plant's columns of G are zeroed)                             */
+} mpci_lti_embed;
+
+/* A plan whose outputs have the embedded layout (P [nv_total][nv_total], q [nv_total],
+ * G [nc_total][nv_total], h [nc_total] per instance).  Runs through
+ * mpci_lti_assemble_coupled only.                                                         */
+int mpci_lti_plan_create_embedded(const mpci_lti_desc* desc, const mpci_lti_embed* embed,
+                                  mpci_lti_plan** plan_out);
+
+/* As mpci_lti_assemble_ex, plus: given_dev [batch][given_len] (the formulation's whole given
+ * vector; x0_dev stays the plant's initial state in the kernel's order), and optional
+ * per-instance signal tables of the coupled costs, cost_cx_dev [batch][n_costs][n] /
+ * cost_cu_dev [batch][n_costs][m] (NULL = the plan's).  Two launches on `stream`: the fused
+ * per-instance kernel, then the coupling kernel.                                           */
+int mpci_lti_assemble_coupled(const mpci_lti_plan* plan, const double* A_dev, long strideA,
+                              const double* B_dev, long strideB, const double* x0_dev,
+                              const double* given_dev, const double* scalars_dev,
+                              const mpci_lti_tables* per_instance, const double* cost_cx_dev,
+                              const double* cost_cu_dev, double* P_dev, double* q_dev,
+                              double* G_dev, double* h_dev, long batch, int hessian_mode,
+                              void* stream);
+
 /* Closed forms of the reference's named LIP systems (tools.get_system_matrices,
  * python/mpc_interface/tools.py:240-285: A = exp(G tau), B = int_0^tau exp(G t) dt h, there
  * by SymPy) for a batch with one sampling period and one pendulum frequency per instance:

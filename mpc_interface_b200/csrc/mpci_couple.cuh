@@ -1,0 +1,22 @@
+// The coupling stage of an embedded per-instance plan (include/mpci.h: mpci_lti_embed):
+// everything of P, q, G, h that involves the auxiliary optimisation variables or the
+// auxiliary given variables.  Implemented in mpci_couple.cu, owned by an mpci_lti_plan.
+#pragma once
+#include "mpci_common.cuh"
+
+namespace mpci {
+
+struct CouplePlan;
+
+// n, m, N: the plant as the fused kernel sees it.  Copies every table of `e` to the device.
+int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out);
+void couple_destroy(CouplePlan* p);
+
+// Runs after the fused kernel on the same stream (it adds to the q and h that kernel wrote).
+// cost_cx / cost_cu: per-instance signal tables [batch][n_costs][n] / [batch][n_costs][m],
+// or nullptr for the plan's.  Any output may be nullptr.
+int couple_launch(const CouplePlan* p, const double* A, long strideA, const double* B, long strideB,
+                  const double* x0, const double* given, const double* cost_cx, const double* cost_cu,
+                  double* P, double* q, double* G, double* h, long batch, cudaStream_t stream);
+
+}  // namespace mpci

@@ -21,6 +21,7 @@
 #include <vector>
 
 #include "mpci_common.cuh"
+#include "mpci_couple.cuh"
 
 namespace {
 
@@ -65,7 +66,25 @@ struct LtiArgs {
   double *P, *q, *G, *h;
   long batch;
   int hessian_mode;
+  // embedded layout (EMB kernels only): the plant's inputs are SOME of the QP's variables
+  // and its limits SOME of the rows -- input j's samples live at columns voff[j] .. + N of
+  // rows of ldv doubles, group g's rows start at grp_row0[g] of nct rows per instance
+  int ldv, nct;
+  int emb_even;  // ldv and every voff[j] even: 16-byte stores / bulk copies stay aligned
+  const int* voff;
 };
+
+// Where the kernel's variables live in the QP.  EMB = false: the plant's inputs ARE the
+// variables (row length m N, input j at column j N) -- the arithmetic of the plain kernels.
+// (int there, as the plain kernels always computed it; long in the embedded layout)
+template <bool EMB> __device__ __forceinline__ auto row_len(const LtiArgs& a) {
+  if constexpr (EMB) return (long)a.ldv;
+  else return a.m * a.N;
+}
+template <bool EMB> __device__ __forceinline__ auto var_off(const LtiArgs& a, int j) {
+  if constexpr (EMB) return (long)a.voff[j];
+  else return j * a.N;
+}
 
 struct Smem {
   double *A, *M0, *M1, *Q, *R, *gz, *wz, *r, *tx, *tu, *cg, *tb;
@@ -312,12 +331,14 @@ __device__ __forceinline__ void dmma_states(double (&acc)[TM][TN][2], const doub
   }
 }
 
+template <bool EMB>
 __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
-  const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD;
+  const auto nv = row_len<EMB>(a);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int mm = m * m;
-  const bool vec_ok = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0);
+  const bool vec_ok = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0) && (!EMB || a.emb_even);
 
   // tiles are sorted by the length of their k-loop and dealt round-robin, the
   // (j, j') blocks innermost: the eight warps get nearly equal work
@@ -367,7 +388,7 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
     for (int x = 0; x < TM; ++x) {
       const int p = p0 + 8 * x + g;
       if (p >= N) continue;
-      double* row = Pb + (size_t)(j * N + p) * nv + (size_t)jp * N;
+      double* row = Pb + (size_t)(var_off<EMB>(a, j) + p) * nv + (size_t)var_off<EMB>(a, jp);
 #pragma unroll
       for (int y = 0; y < TN; ++y) {
         const int c = q0 + 8 * y + 2 * t;
@@ -392,9 +413,10 @@ __device__ void hessian_dmma(const LtiArgs& a, const Smem& s, double* __restrict
 // A thread owns one diagonal delta = p' - p of all m x m blocks and walks the
 // rows from p = N-1 up to 0, so that a warp writes consecutive p' of one row.
 // ---------------------------------------------------------------------------
-template <int M>
+template <int M, bool EMB>
 __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
-  const int n = a.n, N = a.N, LD = a.LD, nv = M * a.N;
+  const int n = a.n, N = a.N, LD = a.LD;
+  const auto nv = row_len<EMB>(a);
   for (int dl0 = 0; dl0 < 2 * N - 1; dl0 += (int)blockDim.x) {
     const int dl = dl0 + threadIdx.x;
     const int delta = dl - (N - 1);
@@ -431,15 +453,17 @@ __device__ void hessian_recursion(const LtiArgs& a, const Smem& s, double* __res
       for (int x = 0; x < M; ++x)
 #pragma unroll
         for (int y = 0; y < M; ++y)
-          __stcs(dst + (size_t)x * N * nv + y * N,
+          __stcs(dst + (size_t)var_off<EMB>(a, x) * nv + var_off<EMB>(a, y),
                  delta == 0 ? acc[x][y] + s.R[x * M + y] : acc[x][y]);
     }
   }
 }
 
 // general m: one (j, j') block at a time
+template <bool EMB>
 __device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
-  const int n = a.n, m = a.m, N = a.N, LD = a.LD, nv = a.m * a.N;
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD;
+  const auto nv = row_len<EMB>(a);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int dchunks = (2 * N - 1 + 31) / 32;  // a warp takes 32 diagonals of one block
   for (int item = warp; item < m * m * dchunks; item += ((int)blockDim.x >> 5)) {
@@ -459,7 +483,7 @@ __device__ void hessian_recursion_any(const LtiArgs& a, const Smem& s, double* _
       for (int i = 0; i < n; ++i)
         acc = fma(s.gz[(size_t)(i * (m + 1) + j) * LD + a.pad + (N - 1 - p)],
                   s.wz[(size_t)(i * m + jp) * a.LDw + a.pad + (N - 1 - c)], acc);
-      __stcs(Pb + (size_t)(j * N + p) * nv + (size_t)jp * N + c, acc + ruu);
+      __stcs(Pb + (size_t)(var_off<EMB>(a, j) + p) * nv + (size_t)var_off<EMB>(a, jp) + c, acc + ruu);
     }
   }
 }
@@ -484,9 +508,10 @@ constexpr int kScanLd = 40;  // 32 diagonals + 8 rows
 // reaches its own row / column of T.  Only the padding of K to a multiple of 4 has to
 // contribute exact zeros.
 // KFULL: n is a multiple of 4, no K padding to mask.
-template <bool KFULL>
+template <bool KFULL, bool EMB>
 __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
-  const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1, nv = a.m * a.N;
+  const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1;
+  const auto nv = row_len<EMB>(a);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int ksteps = (n + 3) / 4;
@@ -514,7 +539,7 @@ __device__ void hessian_scan(const LtiArgs& a, const Smem& s, double* __restrict
     int p0 = N - 8 * ((N - 1 - p_first) / 8 + 1);  // rows p0 .. p0+7, bottom band first
     const double* ga = s.gz + (size_t)(t * w + j) * LD + a.pad + (N - 1 - p0 - g);
     const double* wb = s.wz + (size_t)(t * m + jp) * a.LDw + a.pad + (N - 1 - (p0 + d0) - g);
-    double* qd = Pb + (size_t)(j * N + p0 + 7) * nv + (size_t)jp * N + (p0 + 7 + delta);
+    double* qd = Pb + (size_t)(var_off<EMB>(a, j) + p0 + 7) * nv + (size_t)var_off<EMB>(a, jp) + (p0 + 7 + delta);
     const long qstep = (long)nv + 1;
     // the running sum of the main diagonal starts at Quu[j][j']: every entry of that
     // diagonal then carries the + Quu delta_pc term, no separate add per entry
@@ -601,12 +626,12 @@ __device__ __forceinline__ double2 lds128(unsigned addr) {
 }
 
 // CT column tiles: 8 CT - 2 >= N, so the patch keeps two zero columns after the block
-template <bool KFULL, int CT>
+template <bool KFULL, int CT, bool EMB>
 __device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
   constexpr int LDP = (8 * CT) % 16 == 8 ? 8 * CT : 8 * CT + 8;  // = lti_rows_ldp
   constexpr int T0 = CT > 4 ? CT / 2 : CT, T1 = CT - T0;          // two groups (register budget)
   const int n = a.n, m = a.m, N = a.N, LD = a.LD, w = a.m + 1;
-  const long nv = (long)a.m * a.N;
+  const long nv = row_len<EMB>(a);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (warp >= a.scan_warps) return;
   const int g = lane >> 2, t = lane & 3;
@@ -618,7 +643,7 @@ __device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict
   // the lane's two columns; lanes past the tiles read the tiles' last two columns, which
   // are zero (8 CT - 2 >= N)
   const unsigned trow = (unsigned)__cvta_generic_to_shared(tw) + 8u * (unsigned)min(col, 8 * CT - 2);
-  const bool vec = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0);
+  const bool vec = (N % 2 == 0) && ((reinterpret_cast<uintptr_t>(Pb) & 15) == 0) && (!EMB || a.emb_even);
   // columns of the last two tiles that exist
   const bool ok0 = 8 * (CT - 2) + g < N, ok1 = 8 * (CT - 1) + g < N;
 
@@ -633,7 +658,7 @@ __device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict
     double c0 = (col == N) ? ruu : 0.0, c1 = (col + 1 == N) ? ruu : 0.0;
     const double* ga = s.gz + (size_t)(t * w + j) * LD + a.pad + (7 - g);           // band p0 = N - 8
     const double* wb = s.wz + (size_t)(t * m + jp) * a.LDw + a.pad + (N - 1 - g);
-    double* dst = Pb + (size_t)(j * N + N - 1) * nv + (size_t)jp * N + col;        // row N - 1
+    double* dst = Pb + (size_t)(var_off<EMB>(a, j) + N - 1) * nv + (size_t)var_off<EMB>(a, jp) + col;  // row N - 1
     for (int p0 = N - 8; p0 > -8; p0 -= 8, ga += 8) {  // rows p0 .. p0 + 7, bottom band first
       if (T1 > 0) {
         rows_tiles<KFULL, T0, false>(ga, wb, ga_step, wb_step, n, t, tst, true, true);
@@ -673,23 +698,24 @@ __device__ void hessian_rows(const LtiArgs& a, const Smem& s, double* __restrict
   }
 }
 
-template <bool KFULL>
+template <bool KFULL, bool EMB>
 __device__ void hessian_rows_any(const LtiArgs& a, const Smem& s, double* __restrict__ Pb) {
   switch ((a.N + 2 + 7) >> 3) {  // column tiles: two zero columns follow the block (N <= 60)
-    case 1: return hessian_rows<KFULL, 1>(a, s, Pb);
-    case 2: return hessian_rows<KFULL, 2>(a, s, Pb);
-    case 3: return hessian_rows<KFULL, 3>(a, s, Pb);
-    case 4: return hessian_rows<KFULL, 4>(a, s, Pb);
-    case 5: return hessian_rows<KFULL, 5>(a, s, Pb);
-    case 6: return hessian_rows<KFULL, 6>(a, s, Pb);
-    case 7: return hessian_rows<KFULL, 7>(a, s, Pb);
-    default: return hessian_rows<KFULL, 8>(a, s, Pb);
+    case 1: return hessian_rows<KFULL, 1, EMB>(a, s, Pb);
+    case 2: return hessian_rows<KFULL, 2, EMB>(a, s, Pb);
+    case 3: return hessian_rows<KFULL, 3, EMB>(a, s, Pb);
+    case 4: return hessian_rows<KFULL, 4, EMB>(a, s, Pb);
+    case 5: return hessian_rows<KFULL, 5, EMB>(a, s, Pb);
+    case 6: return hessian_rows<KFULL, 6, EMB>(a, s, Pb);
+    case 7: return hessian_rows<KFULL, 7, EMB>(a, s, Pb);
+    default: return hessian_rows<KFULL, 8, EMB>(a, s, Pb);
   }
 }
 
 // ---------------------------------------------------------------------------
 // phase 4: q[(j,p)] = sum_{d>=0} Gam_d[:,j] . r_{p+d} - tu[j]
 // ---------------------------------------------------------------------------
+template <bool EMB>
 __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ qb) {
   const int n = a.n, m = a.m, N = a.N, LD = a.LD;
   for (int e = threadIdx.x; e < m * N; e += (int)blockDim.x) {
@@ -708,7 +734,7 @@ __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ q
       }
       for (; d < len; ++d) acc0 = fma(gam[d], r[d], acc0);
     }
-    qb[e] = ((acc0 + acc1) + (acc2 + acc3)) - s.tu[j];
+    qb[EMB ? var_off<EMB>(a, j) + p : (long)e] = ((acc0 + acc1) + (acc2 + acc3)) - s.tu[j];
   }
 }
 
@@ -720,6 +746,7 @@ __device__ void gradient(const LtiArgs& a, const Smem& s, double* __restrict__ q
 // the warp runs them while the other warps are already in the Hessian scan.  s_p
 // overwrites r_p in shared memory (nothing else reads r).  Needs n <= 32.
 // ---------------------------------------------------------------------------
+template <bool EMB>
 __device__ void gradient_costate(const LtiArgs& a, const Smem& s, double* __restrict__ qb) {
   const int n = a.n, m = a.m, N = a.N, w = a.m + 1, LD = a.LD, lane = threadIdx.x & 31;
   const bool mine = lane < n;
@@ -746,7 +773,7 @@ __device__ void gradient_costate(const LtiArgs& a, const Smem& s, double* __rest
     const int j = e / N, p = e - j * N;
     double acc = -s.tu[j];
     for (int i = 0; i < n; ++i) acc = fma(s.gz[(i * w + j) * LD + a.pad], s.r[i * N + p], acc);
-    qb[e] = acc;
+    qb[EMB ? var_off<EMB>(a, j) + p : (long)e] = acc;
   }
 }
 
@@ -845,16 +872,36 @@ __device__ __forceinline__ void group_line(const LtiArgs& a, long b, int grp, do
 
 // rows of a group whose arrow changes from row to row (or that are not 16-byte aligned):
 // warps warp0, warp0 + nwarps, ... scale and store the windows themselves
+// N scaled doubles to dst (8-byte aligned, either parity) by one warp: 16-byte stores over the
+// aligned middle, single ones at an odd head / tail
+__device__ __forceinline__ void warp_store_scaled(double* __restrict__ dst, const double* src, int N,
+                                                  double ak, int lane) {
+  const int head = (int)((reinterpret_cast<uintptr_t>(dst) >> 3) & 1);
+  if (head && lane == 0) __stcs(dst, ak * src[0]);
+  const int pairs = (N - head) >> 1;
+  for (int i = lane; i < pairs; i += 32) {
+    const int c = head + 2 * i;
+    __stcs(reinterpret_cast<double2*>(dst + c), make_double2(ak * src[c], ak * src[c + 1]));
+  }
+  if (((N - head) & 1) && lane == 31) __stcs(dst + N - 1, ak * src[N - 1]);
+}
+
+template <bool EMB>
 __device__ __forceinline__ void group_rows_by_warps(const LtiArgs& a, int grp, const double* cz,
                                                     double* __restrict__ rows, bool aligned, int warp,
                                                     int nwarps, int lane) {
-  const int m = a.m, N = a.N, nv = a.m * a.N;
+  const int m = a.m, N = a.N;
+  const auto nv = row_len<EMB>(a);
   const double* arrow = a.arrow + (size_t)grp * N;
   const int k0 = a.grp_k0[grp], k1 = k0 + a.grp_cnt[grp];
   for (int k = k0 + warp; k < k1; k += nwarps) {
     const double ak = __ldg(arrow + k);
     double* row = rows + (size_t)(k - k0) * nv;
     const double* win = cz + (N - 1 - k);  // column c = j N + p reads win[c + j N]
+    if (EMB) {  // block j at its own column offset, whatever its parity
+      for (int j = 0; j < m; ++j) warp_store_scaled(row + var_off<EMB>(a, j), win + 2 * j * N, N, ak, lane);
+      continue;
+    }
     if (aligned) {
       for (int c = 2 * lane; c < nv; c += 64) {  // c and c+1 share j because N is even
         int off = c;
@@ -871,12 +918,15 @@ __device__ __forceinline__ void group_rows_by_warps(const LtiArgs& a, int grp, c
   }
 }
 
+template <bool EMB>
 __device__ void constraint_rows(const LtiArgs& a, const Smem& s, long b, double* __restrict__ Gb,
                                 double* __restrict__ hb) {
-  const int m = a.m, N = a.N, nv = a.m * a.N, tid = threadIdx.x;
+  const int m = a.m, N = a.N, tid = threadIdx.x;
+  const auto nv = row_len<EMB>(a);
   const int lane = tid & 31, warp = tid >> 5, nwarps = (int)blockDim.x >> 5;
   const int czld = 2 * N, set_doubles = 4 * m * N;  // one set of windows: cz | cz1
-  const bool aligned = (N % 2 == 0) && Gb && ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0);
+  const bool aligned = (N % 2 == 0) && Gb && ((reinterpret_cast<uintptr_t>(Gb) & 15) == 0) &&
+                       (!EMB || a.emb_even);
   const unsigned magic_2N = magic_of(2 * N);
   // Two sets of windows alternate, so the TMA engine drains the rows of one group while
   // the next group's windows are built (a third set was measured: no gain); whatever the
@@ -892,7 +942,7 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, long b, double*
       bulk_wait_read<1>();
       __syncthreads();
     }
-    const bool line = bulk && !(a.grp_state[grp] & 1) && m <= 8;  // no state part: one copy per row
+    const bool line = !EMB && bulk && !(a.grp_state[grp] & 1) && m <= 8;  // no state part: one copy per row
     if (line) group_line(a, b, grp, cz, cz + (((m + 1) * N + 1) & ~1), hb, tid, (int)blockDim.x);
     else group_windows(a, s, b, grp, cz, cz1, bulk, hb, tid, (int)blockDim.x, magic_2N);
     fence_async_smem();  // the windows must be visible to the async proxy
@@ -923,12 +973,12 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, long b, double*
         const int start = N - 1 - k;
         const double* win = (start & 1) ? cz1 + (start - 1) : cz + start;
         double* row = rows + (size_t)(k - k0) * nv;
-        for (int j = 0; j < m; ++j) bulk_store(row + j * N, win + j * czld, (unsigned)N * 8u);
+        for (int j = 0; j < m; ++j) bulk_store(row + var_off<EMB>(a, j), win + j * czld, (unsigned)N * 8u);
       }
       bulk_commit();  // every lane commits (an empty group for the idle ones)
       continue;
     }
-    group_rows_by_warps(a, grp, cz, rows, aligned, warp, nwarps, lane);
+    group_rows_by_warps<EMB>(a, grp, cz, rows, aligned, warp, nwarps, lane);
     bulk_commit();  // keeps the group count in step with the bulk groups
   }
 }
@@ -938,13 +988,15 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, long b, double*
 // different instances -- latency-bound prediction, store-bound P / G -- then overlap).
 // WIDE: plans whose shared memory allows one CTA per SM anyway run it with kWideThreads
 // threads (more warps to hide the latency-bound phases; measured at C5: 4.47 -> 4.23 ms).
-template <int MODE, int WIDE>
+// EMB: the embedded layout (LtiArgs::ldv / voff / nct) -- separate instantiations, so the
+// plain kernels keep their code.
+template <int MODE, int WIDE, bool EMB>
 __global__ void __launch_bounds__(WIDE ? kWideThreads : kThreads,
                                   WIDE ? 1 : (MODE == MPCI_LTI_HESSIAN_RECURSION ? MPCI_LTI_MINBLOCKS : 2))
 lti_assemble_kernel(LtiArgs a) {
   extern __shared__ double lti_smem[];
   const Smem s = carve(lti_smem, a);
-  const size_t nv = (size_t)a.m * a.N, nc = (size_t)a.nc;
+  const size_t nv = EMB ? (size_t)a.ldv : (size_t)a.m * a.N, nc = EMB ? (size_t)a.nct : (size_t)a.nc;
   for (long b = blockIdx.x; b < a.batch; b += gridDim.x) {
     __syncthreads();  // the previous instance is done with shared memory
     if (a.n % 4 == 0) build_prediction<true>(a, s, b);
@@ -962,8 +1014,8 @@ lti_assemble_kernel(LtiArgs a) {
     const bool g_first = MODE == MPCI_LTI_HESSIAN_RECURSION &&
                          (a.per_sm == 3 ? (slot % 3 != 0) : (slot & 1));
     if (limits && g_first) {
-      constraint_rows(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
-                      a.h ? a.h + (size_t)b * nc : nullptr);
+      constraint_rows<EMB>(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
+                           a.h ? a.h + (size_t)b * nc : nullptr);
     }
     if (a.P && a.scan && limits) {  // aux: the windows must have been read before the T patches
       bulk_wait_read<0>();
@@ -975,24 +1027,24 @@ lti_assemble_kernel(LtiArgs a) {
     const bool adjoint = MODE == MPCI_LTI_HESSIAN_RECURSION && a.scan && a.n <= 32 && a.m * a.N >= 128;
     // (rows mode: the last warp, which owns no T patch, runs it beside the Hessian warps)
     const int adjoint_warp = (a.scan == 2 && a.scan_warps < ((int)blockDim.x >> 5)) ? ((int)blockDim.x >> 5) - 1 : 0;
-    if (adjoint && a.q && (threadIdx.x >> 5) == adjoint_warp) gradient_costate(a, s, a.q + (size_t)b * nv);
+    if (adjoint && a.q && (threadIdx.x >> 5) == adjoint_warp) gradient_costate<EMB>(a, s, a.q + (size_t)b * nv);
     if (a.P) {
       double* Pb = a.P + (size_t)b * nv * nv;
-      if (MODE == MPCI_LTI_HESSIAN_DMMA) hessian_dmma(a, s, Pb);
-      else if (a.scan == 2 && a.n % 4 == 0) hessian_rows_any<true>(a, s, Pb);
-      else if (a.scan == 2) hessian_rows_any<false>(a, s, Pb);
-      else if (a.scan && a.n % 4 == 0) hessian_scan<true>(a, s, Pb);
-      else if (a.scan) hessian_scan<false>(a, s, Pb);
-      else if (a.m == 1) hessian_recursion<1>(a, s, Pb);
-      else if (a.m == 2) hessian_recursion<2>(a, s, Pb);
-      else if (a.m == 3) hessian_recursion<3>(a, s, Pb);
-      else if (a.m == 4) hessian_recursion<4>(a, s, Pb);
-      else hessian_recursion_any(a, s, Pb);
+      if (MODE == MPCI_LTI_HESSIAN_DMMA) hessian_dmma<EMB>(a, s, Pb);
+      else if (a.scan == 2 && a.n % 4 == 0) hessian_rows_any<true, EMB>(a, s, Pb);
+      else if (a.scan == 2) hessian_rows_any<false, EMB>(a, s, Pb);
+      else if (a.scan && a.n % 4 == 0) hessian_scan<true, EMB>(a, s, Pb);
+      else if (a.scan) hessian_scan<false, EMB>(a, s, Pb);
+      else if (a.m == 1) hessian_recursion<1, EMB>(a, s, Pb);
+      else if (a.m == 2) hessian_recursion<2, EMB>(a, s, Pb);
+      else if (a.m == 3) hessian_recursion<3, EMB>(a, s, Pb);
+      else if (a.m == 4) hessian_recursion<4, EMB>(a, s, Pb);
+      else hessian_recursion_any<EMB>(a, s, Pb);
     }
-    if (a.q && !adjoint) gradient(a, s, a.q + (size_t)b * nv);
+    if (a.q && !adjoint) gradient<EMB>(a, s, a.q + (size_t)b * nv);
     if (limits && !g_first)
-      constraint_rows(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
-                      a.h ? a.h + (size_t)b * nc : nullptr);
+      constraint_rows<EMB>(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
+                           a.h ? a.h + (size_t)b * nc : nullptr);
   }
   bulk_wait_all();  // bulk stores of the last rows
 }
@@ -1053,19 +1105,28 @@ extern "C" int mpci_named_system(int system, const double* tau, long stride_tau,
 }
 
 typedef void (*lti_kernel_t)(LtiArgs);
-static lti_kernel_t lti_kernel(int mode, int wide) {
+static lti_kernel_t lti_kernel(int mode, int wide, int emb = 0) {
+  if (emb) {
+    if (mode == MPCI_LTI_HESSIAN_DMMA)
+      return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 1, true>
+                  : lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 0, true>;
+    return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 1, true>
+                : lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 0, true>;
+  }
   if (mode == MPCI_LTI_HESSIAN_DMMA)
-    return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 1> : lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 0>;
-  return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 1>
-              : lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 0>;
+    return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 1, false>
+                : lti_assemble_kernel<MPCI_LTI_HESSIAN_DMMA, 0, false>;
+  return wide ? lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 1, false>
+              : lti_assemble_kernel<MPCI_LTI_HESSIAN_RECURSION, 0, false>;
 }
 
 static cudaError_t lti_opt_in_smem() {
   cudaError_t e = cudaSuccess;
-  for (int mode = 0; mode < 2; ++mode)
-    for (int wide = 0; wide < 2 && e == cudaSuccess; ++wide)
-      e = cudaFuncSetAttribute(lti_kernel(mode, wide), cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               227 * 1024);
+  for (int emb = 0; emb < 2; ++emb)
+    for (int mode = 0; mode < 2; ++mode)
+      for (int wide = 0; wide < 2 && e == cudaSuccess; ++wide)
+        e = cudaFuncSetAttribute(lti_kernel(mode, wide, emb), cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 227 * 1024);
   return e;
 }
 
@@ -1086,9 +1147,24 @@ struct mpci_lti_plan {
   double* slot_out[2];  // P | q | G | h
   cudaStream_t streams[2];
   cudaEvent_t slot_done[2];
+  // embedded layout (mpci_lti_plan_create_embedded): total sizes and the coupling stage
+  int embedded, nvt, nct;
+  mpci::CouplePlan* couple;
 };
 
+static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mpci_lti_plan** out);
+
 extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out) {
+  return lti_plan_create(d, nullptr, out);
+}
+
+extern "C" int mpci_lti_plan_create_embedded(const mpci_lti_desc* d, const mpci_lti_embed* emb,
+                                             mpci_lti_plan** out) {
+  if (!emb) return mpci::fail(-3, "lti_plan_create_embedded: NULL embed");
+  return lti_plan_create(d, emb, out);
+}
+
+static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mpci_lti_plan** out) {
   if (!d || !out) return mpci::fail(-3, "lti_plan_create: NULL argument");
   *out = nullptr;
   if (d->n < 1 || d->m < 1 || d->N < 1 || d->n_scalars < 0 || d->n_groups < 0)
@@ -1189,9 +1265,26 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
     flags[Gs + g] = k0;
     flags[2 * Gs + g] = cnt;
     flags[3 * Gs + g] = nc;
+    if (emb) {  // the group's rows inside the larger G / h
+      if (!emb->grp_row0) return mpci::fail(-3, "lti_plan_create_embedded: NULL grp_row0");
+      const int r0 = emb->grp_row0[g];
+      if (r0 < 0 || r0 + cnt > emb->nc_total)
+        return mpci::fail(-1, "lti_plan_create_embedded: group %d at rows %d .. %d of %d", g, r0,
+                          r0 + cnt - 1, emb->nc_total);
+      flags[3 * Gs + g] = r0;
+    }
     nc += cnt;
   }
+  mpci::CouplePlan* couple = nullptr;
+  if (emb) {
+    const int rc = mpci::couple_create(n, m, N, emb, &couple);  // validates the layout as well
+    if (rc) return rc;
+  }
   mpci_lti_plan* p = new mpci_lti_plan();  // value-initialised: every member zero
+  p->couple = couple;
+  if (emb) {  // voff goes in front of the group tables' tail: flags | voff(m) | tiles
+    flags.insert(flags.end(), emb->var_off, emb->var_off + m);
+  }
   const size_t n_flags = flags.size();
   flags.insert(flags.end(), tile_rc.begin(), tile_rc.end());  // flags | tiles (int2), 8-byte aligned
   if (n_flags % 2) flags.insert(flags.begin() + n_flags, 0);
@@ -1228,6 +1321,7 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   if (e != cudaSuccess) {
     int rc = mpci::cuda_fail(e, "lti_plan_create");
     if (p->dev) cudaFree(p->dev);
+    mpci::couple_destroy(p->couple);
     delete p;
     return rc;
   }
@@ -1243,6 +1337,16 @@ extern "C" int mpci_lti_plan_create(const mpci_lti_desc* d, mpci_lti_plan** out)
   a.grp_row0 = a.grp_state + 3 * Gs;
   a.tiles = reinterpret_cast<const int2*>(a.grp_state + tiles_off);
   a.n_tiles = (int)tile_rc.size() / 2;
+  if (emb) {
+    p->embedded = 1;
+    p->nvt = emb->nv_total;
+    p->nct = emb->nc_total;
+    a.ldv = emb->nv_total;
+    a.nct = emb->nc_total;
+    a.voff = a.grp_state + 4 * Gs;
+    a.emb_even = (emb->nv_total % 2 == 0);
+    for (int j = 0; j < m; ++j) a.emb_even = a.emb_even && (emb->var_off[j] % 2 == 0);
+  }
   p->scan = scan;
   p->ldp = ldp;
   p->scan_warps = scan_warps;
@@ -1268,6 +1372,7 @@ extern "C" int mpci_lti_plan_destroy(mpci_lti_plan* p) {
     if (p->slot_done[s]) cudaEventDestroy(p->slot_done[s]);
   }
   if (p->dev) cudaFree(p->dev);
+  mpci::couple_destroy(p->couple);
   delete p;
   return 0;
 }
@@ -1306,7 +1411,7 @@ extern "C" int mpci_lti_plan_info(const mpci_lti_plan* p, int mode, long info[6]
 static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, const double* B,
                       long strideB, const double* x0, const double* scalars,
                       const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
-                      long batch, int mode, void* stream);
+                      long batch, int mode, void* stream, bool coupled = false);
 
 extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long strideA,
                                  const double* B, long strideB, const double* x0,
@@ -1325,11 +1430,30 @@ extern "C" int mpci_lti_assemble_ex(const mpci_lti_plan* p, const double* A, lon
   return lti_launch(p, A, strideA, B, strideB, x0, scalars, tab, P, q, G, h, batch, mode, stream);
 }
 
+extern "C" int mpci_lti_assemble_coupled(const mpci_lti_plan* p, const double* A, long strideA,
+                                         const double* B, long strideB, const double* x0,
+                                         const double* given, const double* scalars,
+                                         const mpci_lti_tables* tab, const double* cost_cx,
+                                         const double* cost_cu, double* P, double* q, double* G,
+                                         double* h, long batch, int mode, void* stream) {
+  if (!p) return mpci::fail(-3, "lti_assemble_coupled: NULL plan");
+  if (!p->embedded)
+    return mpci::fail(-1, "lti_assemble_coupled: the plan was not created by mpci_lti_plan_create_embedded");
+  if (tab && (tab->tx || tab->tu) && p->S != 0)
+    return mpci::fail(-1, "lti_assemble_coupled: per-instance tx / tu need a plan with n_scalars = 0");
+  int rc = lti_launch(p, A, strideA, B, strideB, x0, scalars, tab, P, q, G, h, batch, mode, stream, true);
+  if (rc) return rc;
+  return mpci::couple_launch(p->couple, A, strideA, B, strideB, x0, given, cost_cx, cost_cu, P, q, G, h,
+                             batch, mpci::as_stream(stream));
+}
+
 static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, const double* B,
                       long strideB, const double* x0, const double* scalars,
                       const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
-                      long batch, int mode, void* stream) {
+                      long batch, int mode, void* stream, bool coupled) {
   if (!p) return mpci::fail(-3, "lti_assemble: NULL plan");
+  if (p->embedded && !coupled)
+    return mpci::fail(-1, "lti_assemble: a plan with the embedded layout runs through mpci_lti_assemble_coupled");
   if (batch < 0) return mpci::fail(-1, "lti_assemble: negative batch");
   if (batch == 0) return 0;
   if (!A || !B || !x0) return mpci::fail(-3, "lti_assemble: NULL A, B or x0");
@@ -1367,7 +1491,7 @@ static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, con
   a.per_sm = p->blocks_per_sm[mode];
   const long resident = (long)sms * a.per_sm;
   const unsigned grid = (unsigned)(batch < resident ? batch : resident);
-  lti_kernel(mode, p->threads[mode] == kWideThreads)
+  lti_kernel(mode, p->threads[mode] == kWideThreads, p->embedded)
       <<<grid, p->threads[mode], p->smem_bytes[mode], mpci::as_stream(stream)>>>(a);
   MPCI_LAUNCH_CHECK("lti_assemble_kernel");
   return 0;
@@ -1382,6 +1506,8 @@ static int lti_host(mpci_lti_plan* p, const double* A, long strideA, const doubl
                     double* h, long batch, int mode, long chunk, long ring, mpci_chunk_fn on_chunk,
                     void* user) {
   if (batch < 0 || chunk < 1) return mpci::fail(-1, "lti_assemble_host: bad batch / chunk");
+  if (p->embedded)
+    return mpci::fail(-1, "lti_assemble_host: plans with the embedded layout have no host-buffer entry point");
   if (batch == 0) return 0;
   if (!A || !B || !x0 || (p->S > 0 && !scalars))
     return mpci::fail(-3, "lti_assemble_host: NULL input");

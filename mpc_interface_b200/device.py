@@ -133,6 +133,15 @@ _SIGNATURES = {
         + [_c_double_p] * 4
         + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p],
     ),
+    "mpci_lti_plan_create_embedded": (
+        ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "mpci_lti_assemble_coupled": (
+        ctypes.c_int,
+        [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
+         _c_double_p, _c_double_p, ctypes.c_void_p, _c_double_p, _c_double_p]
+        + [_c_double_p] * 4
+        + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p],
+    ),
     "mpci_named_system": (
         ctypes.c_int,
         [ctypes.c_int, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,

@@ -6,6 +6,14 @@ with biped_configuration.py:11-52), written against this package.  ``omega``
 may be a float (one instance, as in the reference) or a ``Param`` so that the
 pendulum frequency differs between the instances of a batch; the velocity aims
 may be ``Param``s as well.
+
+``conf.system`` may also be "dP->CCC" (tools.py:253-280: the same states CoM, CoM_dot,
+CoM_ddot driven by the CoP rate): that plant depends on the pendulum frequency, so a batch
+with one ``omega`` / ``tau`` per instance needs one plant per instance --
+``generate_all_qp_matrices_batched(..., dynamics={"LIP": ("dP->CCC", tau_b, omega_b)})``,
+with ``Param``s for ``omega`` / ``tau`` here (``nominal`` numbers then build the structure).
+``api=`` a namespace of the reference's own classes builds the identical formulation with
+them (the oracle of the parity tests).
 """
 from types import SimpleNamespace
 
@@ -16,10 +24,17 @@ from ..body import Formulation
 from ..combinations import LineCombo
 from ..dynamics import ControlSystem, DomainVariable, ExtendedSystem
 from ..goal import Cost
+from ..params import is_expr
 from ..restrictions import Box
 
 AXES = ["_x", "_y"]
 OPTIM = ["CoM_dddot_x", "Ds_x", "CoM_dddot_y", "Ds_y"]
+
+
+def _own_api():
+    return SimpleNamespace(ControlSystem=ControlSystem, ExtendedSystem=ExtendedSystem,
+                           DomainVariable=DomainVariable, Formulation=Formulation, LineCombo=LineCombo,
+                           Cost=Cost, Box=Box, tools=now)
 
 
 def default_configuration(horizon_lenght=None):
@@ -53,15 +68,23 @@ def default_configuration(horizon_lenght=None):
     return c
 
 
-def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=True, yaw=None):
+def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=True, yaw=None,
+                    tau=None, nominal=None, api=None):
     """Builds the Formulation.  ``omega`` / ``target_vel`` default to the
     configuration's numbers; pass ``Param``s to make them per-instance.
     ``yaw`` (float or ``Param``) turns the support polygon and the terminal box
     by that angle with ``Box.rotate_in_TS`` (restrictions.py:437-457): the feet of
-    every instance of a batch may point somewhere else."""
+    every instance of a batch may point somewhere else.
+    ``tau``: the sampling period of the plant (default ``conf.mpc_period``; a ``Param`` for a
+    per-instance plant -- ``nominal = (tau, omega)`` numbers then build the structure)."""
+    now, ExtendedSystem, ControlSystem, DomainVariable, LineCombo, Box, Cost, Formulation = (
+        lambda a: (a.tools, a.ExtendedSystem, a.ControlSystem, a.DomainVariable, a.LineCombo, a.Box,
+                   a.Cost, a.Formulation))(_own_api() if api is None else api)
     w = conf.omega if omega is None else omega
+    period = conf.mpc_period if tau is None else tau
     vel = conf.target_vel if target_vel is None else target_vel
     N = conf.horizon_lenght
+    tau_n, omega_n = nominal if nominal is not None else (conf.mpc_period, conf.omega)
 
     # footsteps: s = 1*s0 + E*Ds with a 0/1 step-indicator matrix
     steps = ExtendedSystem(
@@ -77,15 +100,17 @@ def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=Tru
     steps.define_output("stamps", {"s0": 1, "Ds": 1}, time_variant=True, how_to_update=now.adapt_size)
 
     # centre of mass
-    lip = ControlSystem.from_name(conf.system, AXES, tau=conf.mpc_period, omega=conf.omega)
+    lip = ControlSystem.from_name(conf.system, AXES, tau=tau_n if is_expr(period) else period,
+                                  omega=omega_n if is_expr(w) else (conf.omega if omega is None else w))
     lip_ext = ExtendedSystem.from_cotrol_system(lip, "x", N)
+    drive = lip.input_names[0]  # "CoM_dddot" (J->CCC) or "cCoP_dot" (dP->CCC)
 
     # non-linearity bias, one sample per horizon step
     bias = DomainVariable("n", N, AXES)
 
     shift = np.diag(np.ones([N - 1]), 1)  # n enters one sample later
     extra = {}
-    if conf.system == "J->CCC":
+    if conf.system in ("J->CCC", "dP->CCC"):  # both carry CoM, CoM_dot, CoM_ddot
         for ax in AXES:
             extra["b" + ax] = LineCombo({"CoM" + ax: 1, "CoM_ddot" + ax: -1 / w**2})
             extra["(b+n-s)" + ax] = LineCombo({"b" + ax: 1, "n" + ax: shift, "s" + ax: -1})
@@ -117,13 +142,13 @@ def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=Tru
     goals = {
         "relax ankles x": Cost("(b+n-s)", weights["relax ankles"], aim=[0], axes=["_x"]),
         "relax ankles y": Cost("(b+n-s)", weights["relax ankles"], aim=[0], axes=["_y"]),
-        "minimize jerk": Cost("CoM_dddot", weights["minimize jerk"], aim=[0, 0], axes=AXES),
+        "minimize jerk": Cost(drive, weights["minimize jerk"], aim=[0, 0], axes=AXES),
         "track vel_x": Cost("CoM_dot", weights["track velocity"], aim=vel[0], axes=["_x"]),
         "track vel_y": Cost("CoM_dot", weights["track velocity"], aim=vel[1], axes=["_y"]),
         "terminal_cost": Cost("(DCM-s)", weights["terminal"], aim=[0, 0], axes=AXES, schedule=last),
     }
 
-    form = Formulation(backend=backend)
+    form = Formulation() if (api is not None or backend is None) else Formulation(backend=backend)
     form.incorporate_dynamics("steps", steps)
     form.incorporate_dynamics("LIP", lip_ext)
     form.incorporate_dynamics("bias", bias)
@@ -133,7 +158,7 @@ def formulate_biped(conf, omega=None, target_vel=None, backend=None, preview=Tru
     form.incorporate_box("stepping area", stepping_area)
     form.incorporate_box("support_polygon", support_polygon)
     form.incorporate_box("terminal_Constraint", terminal_constraint)
-    form.identify_qp_domain(list(OPTIM))
+    form.identify_qp_domain([drive + "_x", "Ds_x", drive + "_y", "Ds_y"])
     if preview:  # builds the device plan; False leaves a host-only description
         form.make_preview_matrices()
 

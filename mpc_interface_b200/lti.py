@@ -74,22 +74,94 @@ class LtiTables(ctypes.Structure):
     _fields_ = [(name, ctypes.c_void_p) for name in ("Qxx", "Quu", "tx", "tu", "cx", "cu", "bound")]
 
 
+class LtiEmbed(ctypes.Structure):
+    """mpci_lti_embed of include/mpci.h (host pointers)"""
+
+    _fields_ = [
+        ("nv_total", ctypes.c_int),
+        ("nc_total", ctypes.c_int),
+        ("var_off", ctypes.c_void_p),
+        ("grp_row0", ctypes.c_void_p),
+        ("nz", ctypes.c_int),
+        ("z_col", ctypes.c_void_p),
+        ("given_len", ctypes.c_int),
+        ("n_costs", ctypes.c_int),
+        ("cost_cx", ctypes.c_void_p),
+        ("cost_cu", ctypes.c_void_p),
+        ("cost_w", ctypes.c_void_p),
+        ("cost_MzT", ctypes.c_void_p),
+        ("cost_e_ptr", ctypes.c_void_p),
+        ("cost_e_col", ctypes.c_void_p),
+        ("cost_e_val", ctypes.c_void_p),
+        ("Pzz", ctypes.c_void_p),
+        ("Gz", ctypes.c_void_p),
+        ("h_ptr", ctypes.c_void_p),
+        ("h_col", ctypes.c_void_p),
+        ("h_val", ctypes.c_void_p),
+        ("row_kind", ctypes.c_void_p),
+    ]
+
+
 # ---------------------------------------------------------------------------
 # point-wise linear forms with (possibly per-instance) scalar coefficients
 # ---------------------------------------------------------------------------
 class _Form:
     """``sum_i cx[i] * state_i + sum_j cu[j] * input_j`` as sparse maps index -> coefficient
-    (a float or a ``Param`` expression)."""
+    (a float or a ``Param`` expression), plus an auxiliary part ``Mz @ z + Mg @ given`` over
+    the optimisation variables that are not plant inputs and the given variables that are not
+    the plant's initial state (dense numeric [rows, nz] / [rows, given_len], or None).
+    ``rows``: samples of the signal (None: not fixed yet; a plant part means the horizon)."""
 
-    def __init__(self, cx=None, cu=None):
+    def __init__(self, cx=None, cu=None, rows=None, Mz=None, Mg=None):
         self.cx, self.cu = dict(cx or {}), dict(cu or {})
+        self.rows, self.Mz, self.Mg = rows, Mz, Mg
 
     def add(self, other, coef):
+        """self += coef * other, ``coef`` a float or a ``Param`` expression (the latter on a
+        form without auxiliary part only)."""
+        if other.has_aux() and is_expr(coef):
+            _unsupported("a Param coefficient on a variable outside the plant")
+        self._fit_rows(other.rows)
         for mine, theirs in ((self.cx, other.cx), (self.cu, other.cu)):
             for idx, c in theirs.items():
                 term = coef * c
                 mine[idx] = mine[idx] + term if idx in mine else term
+        for name in ("Mz", "Mg"):
+            theirs = getattr(other, name)
+            if theirs is not None:
+                mine = getattr(self, name)
+                setattr(self, name, coef * theirs if mine is None else mine + coef * theirs)
         return self
+
+    def add_matrix(self, other, matrix, where):
+        """self += matrix @ other for a numeric [rows, other.rows] coefficient (the shifted
+        bias of biped_formulation.py:57,63); ``other`` must not have a plant part."""
+        if other.cx or other.cu:
+            _unsupported("a matrix coefficient on a plant variable in the definition '{}'".format(where))
+        if other.rows is not None and matrix.shape[1] != other.rows:
+            raise ValueError("matmul: a [{}x{}] coefficient on a variable of {} samples in '{}'".format(
+                matrix.shape[0], matrix.shape[1], other.rows, where))
+        self._fit_rows(matrix.shape[0])
+        for name in ("Mz", "Mg"):
+            theirs = getattr(other, name)
+            if theirs is not None:
+                mine = getattr(self, name)
+                setattr(self, name, matrix @ theirs if mine is None else mine + matrix @ theirs)
+        return self
+
+    def _fit_rows(self, rows):
+        if rows is None:
+            return
+        if self.rows is not None and self.rows != rows:
+            raise ValueError("operands could not be broadcast together with shapes ({},) ({},)".format(
+                self.rows, rows))
+        self.rows = rows
+
+    def has_aux(self):
+        return any(M is not None and np.any(M) for M in (self.Mz, self.Mg))
+
+    def has_plant(self):
+        return self.touches_states() or self.touches_inputs()
 
     def symbolic(self):
         return any(is_expr(c) for c in list(self.cx.values()) + list(self.cu.values()))
@@ -136,6 +208,12 @@ class LtiPlan:
         self.blocks, self.inputs = [0], [(0, j) for j in range(m)]
         self.per_instance = False  # any Param in weights / forms / bounds
         self._device = None
+        # embedded layout: the QP has variables / givens / rows outside the plant (lower())
+        self.embedded = False
+        self.nz, self.z_col, self.var_off, self.x0_index = 0, [], None, None
+        self.group_row0 = []  # first row of every plant group in G / h
+        self.coupled = []     # costs on signals with an auxiliary part: (w, form, Mz [N,nz], E [N,ng+1])
+        self.Pzz = self.Gz = self.Hg = self.row_kind = None
 
     # ---- numeric tables -----------------------------------------------------
     def _cost_tables(self, params, batch):
@@ -206,6 +284,43 @@ class LtiPlan:
         return dict(Qxx=np.ascontiguousarray(Qxx[0]), Quu=np.ascontiguousarray(Quu[0]), Tx=Tx, Tu=Tu,
                     grp_cx=np.ascontiguousarray(cx[0]), grp_cu=np.ascontiguousarray(cu[0]),
                     grp_arrow=arrow, grp_bound=np.ascontiguousarray(bound[0]), grp_k0=k0, grp_rows=cnt)
+
+    def embed_tables(self):
+        """The constant tables of mpci_lti_embed (include/mpci.h) for an embedded plan."""
+        n, m, N, nz, nC = self.n, self.m, self.N, self.nz, len(self.coupled)
+        i32 = lambda x: np.ascontiguousarray(x, dtype=np.int32)  # noqa: E731
+        f64 = lambda x: np.ascontiguousarray(x, dtype=np.float64)  # noqa: E731
+
+        def csr(dense):  # rows of a dense [R, ng + 1] map, exact zeros dropped
+            ptr, col, val = [0], [], []
+            for row in dense:
+                nzc = np.nonzero(row)[0]
+                col += list(nzc)
+                val += list(row[nzc])
+                ptr.append(len(col))
+            return i32(ptr), i32(col), f64(val)
+
+        cx, cu = np.zeros([nC, n]), np.zeros([nC, m])
+        if not self.per_instance:
+            for c, (_w, fv, _Mz, _E) in enumerate(self.coupled):
+                cx[c], cu[c] = _dense(fv.cx, n, {}, 1)[0], _dense(fv.cu, m, {}, 1)[0]
+        e_ptr, e_col, e_val = csr(np.vstack([E for *_r, E in self.coupled]) if nC else np.zeros([0, self.ng + 1]))
+        h_ptr, h_col, h_val = csr(self.Hg)
+        MzT = np.stack([Mz.T for _w, _f, Mz, _E in self.coupled]) if nC else np.zeros([0, nz, N])
+        return dict(var_off=i32(self.var_off), grp_row0=i32(self.group_row0), z_col=i32(self.z_col),
+                    cost_cx=f64(cx), cost_cu=f64(cu), cost_w=f64([w for w, *_r in self.coupled]),
+                    cost_MzT=f64(MzT), cost_e_ptr=e_ptr, cost_e_col=e_col, cost_e_val=e_val,
+                    Pzz=f64(self.Pzz), Gz=f64(self.Gz), h_ptr=h_ptr, h_col=h_col, h_val=h_val,
+                    row_kind=i32(self.row_kind))
+
+    def coupled_tables(self, params, batch):
+        """Per-instance signal tables of the coupled costs: cost_cx [B, nC, n], cost_cu [B, nC, m]."""
+        nC = len(self.coupled)
+        cx, cu = np.zeros([batch, nC, self.n]), np.zeros([batch, nC, self.m])
+        for c, (_w, fv, _Mz, _E) in enumerate(self.coupled):
+            cx[:, c] = _dense(fv.cx, self.n, params, batch)
+            cu[:, c] = _dense(fv.cu, self.m, params, batch)
+        return cx, cu
 
     def instance_tables(self, params, batch):
         """Per-instance tables of a plan with ``Param`` coefficients: ``{name: [B, ...]}``
@@ -308,7 +423,19 @@ class _DeviceLtiPlan:
             t["grp_bound"].ctypes.data, t["grp_k0"].ctypes.data, t["grp_rows"].ctypes.data,
         )
         handle = ctypes.c_void_p()
-        device.check(device.lib().mpci_lti_plan_create(ctypes.byref(desc), ctypes.byref(handle)))
+        if plan.embedded:
+            e = plan.embed_tables()
+            self._keep_embed = e
+            at = lambda k: e[k].ctypes.data  # noqa: E731
+            embed = LtiEmbed(
+                plan.nv, plan.nc, at("var_off"), at("grp_row0"), plan.nz, at("z_col"), plan.ng,
+                len(plan.coupled), at("cost_cx"), at("cost_cu"), at("cost_w"), at("cost_MzT"),
+                at("cost_e_ptr"), at("cost_e_col"), at("cost_e_val"), at("Pzz"), at("Gz"),
+                at("h_ptr"), at("h_col"), at("h_val"), at("row_kind"))
+            device.check(device.lib().mpci_lti_plan_create_embedded(
+                ctypes.byref(desc), ctypes.byref(embed), ctypes.byref(handle)))
+        else:
+            device.check(device.lib().mpci_lti_plan_create(ctypes.byref(desc), ctypes.byref(handle)))
         self.handle = handle
         self._lib = device.lib()
 
@@ -355,40 +482,75 @@ def _plant_layout(form, plant_name):
         if ident < n_inputs and (name.endswith(first) or first == ""):
             base_inputs[ident] = name[: len(name) - len(first)] if first else name
     n0, m0 = len(base_states), n_inputs
-    # state blocks follow the order of the given variables, inputs the optimisation order
-    given = list(form.given_variables)
-    if sorted(given) != sorted(x0_base + ax for ax in axes):
-        _unsupported("given variables other than the plant's initial states")
+    # state blocks follow the order of the given variables, inputs the optimisation order;
+    # whatever else is given / optimised is auxiliary (another dynamics' variables, a bias)
+    x0_names = [x0_base + ax for ax in axes]
+    given = [g for g in form.given_variables if g in x0_names]
+    if sorted(given) != sorted(x0_names):
+        _unsupported("a plant whose initial states are not all given")
     blocks = [axes.index(g[len(x0_base):]) for g in given]  # block -> axis index
     block_of_axis = {axis: blk for blk, axis in enumerate(blocks)}
     wanted = {inp + ax: (block_of_axis[a], j) for a, ax in enumerate(axes) for j, inp in enumerate(base_inputs)}
-    optim = list(form.optim_variables)
+    optim = [v for v in form.optim_variables if v in wanted]
     if sorted(optim) != sorted(wanted):
-        _unsupported("an optimisation domain other than the plant inputs")
+        _unsupported("a plant whose inputs are not all optimisation variables")
     inputs = [wanted[v] for v in optim]  # kernel input k -> (block, plant input j)
     return plant, axes, base_states, base_inputs, x0_base, n0, m0, blocks, inputs, block_of_axis
+
+
+def _aux_layout(form, layout):
+    """The variables outside the plant: ``(z_of, nz, z_col)`` -- auxiliary optimisation
+    variable -> its range of z indices, their number and their columns in the QP -- and the
+    set of auxiliary given variables (their columns are ``form.given_ID``)."""
+    plant, axes, base_states, base_inputs, x0_base = layout[:5]
+    plant_inputs = set(inp + ax for ax in axes for inp in base_inputs)
+    z_of, z_col = {}, []
+    for v in form.optim_variables:
+        if v not in plant_inputs:
+            ids = form.optim_ID[v]
+            z_of[v] = range(len(z_col), len(z_col) + len(ids))
+            z_col += list(ids)
+    x0_names = set(x0_base + ax for ax in axes)
+    aux_given = [g for g in form.given_variables if g not in x0_names]
+    return z_of, len(z_col), z_col, aux_given
 
 
 def _linear_forms(form, plant_name, layout):
     """{definition name: _Form} for every point-wise linear form."""
     plant, axes, base_states, base_inputs, x0_base, n0, m0, blocks, inputs, block_of_axis = layout
+    z_of, nz, _z_col, aux_given = _aux_layout(form, layout)
+    N = plant.matrices[-1].shape[0]
     forms = {}
     for a, ax in enumerate(axes):
         for i, name in enumerate(base_states):
-            forms[name + ax] = _Form(cx={block_of_axis[a] * n0 + i: 1.0})
-    for k, name in enumerate(form.optim_variables):
-        forms[name] = _Form(cu={k: 1.0})
+            forms[name + ax] = _Form(cx={block_of_axis[a] * n0 + i: 1.0}, rows=N)
+    k = 0
+    for name in form.optim_variables:
+        if name in z_of:  # an auxiliary optimisation variable: its own slots of z
+            sel = np.zeros([len(z_of[name]), nz])
+            sel[np.arange(len(z_of[name])), list(z_of[name])] = 1.0
+            forms[name] = _Form(rows=sel.shape[0], Mz=sel)
+        else:
+            forms[name] = _Form(cu={k: 1.0}, rows=N)
+            k += 1
+    for name in aux_given:
+        ids = form.given_ID[name]
+        sel = np.zeros([len(ids), form.given_len])
+        sel[np.arange(len(ids)), list(ids)] = 1.0
+        forms[name] = _Form(rows=sel.shape[0], Mg=sel)
     skip = set(x0_base + ax for ax in axes)
     for name, combo in form.definitions.items():
         if name in forms or name in skip:
             continue
-        if name in form.of:
-            _unsupported("a second dynamics ('{}')".format(form.of[name]))
         out = _Form()
         for var, coef in combo.items():
             if var not in forms:
                 _unsupported("the definition '{}' (depends on '{}')".format(name, var))
-            out.add(forms[var], _scalar(coef, name))
+            kind, value = _plan._scalar_kind(coef)
+            if kind == "mat":  # blocks of another dynamics (tools.py:79-101), shifted biases
+                out.add_matrix(forms[var], value if value.ndim == 2 else value.reshape([value.shape[0], -1]), name)
+            else:
+                out.add(forms[var], value)
         forms[name] = out
     return forms
 
@@ -408,6 +570,7 @@ def lower(form, plant_name):
     structure, and the reference's own exceptions for malformed objects)."""
     layout = _plant_layout(form, plant_name)
     plant, axes, base_states, base_inputs, x0_base, n0, m0, blocks, inputs, block_of_axis = layout
+    z_of, nz, z_col, aux_given = _aux_layout(form, layout)
     forms = _linear_forms(form, plant_name, layout)
     n, m = n0 * len(axes), len(inputs)
     N = plant.matrices[-1].shape[0]
@@ -415,21 +578,40 @@ def lower(form, plant_name):
     plan.n0, plan.m0, plan.blocks, plan.inputs = n0, m0, blocks, inputs
     plan.optim_ID = dict(form.optim_ID)
     plan.given_ID = dict(form.given_ID)
+    plan.embedded = bool(nz or aux_given)
+    if plan.embedded:
+        plan.nv, plan.ng, plan.nz, plan.z_col = form.optim_len, form.given_len, nz, list(z_col)
+        plant_optim = [v for v in form.optim_variables if v not in z_of]
+        for v in plant_optim:
+            if len(form.optim_ID[v]) != N:
+                _unsupported("a plant input with {} actions over {} samples".format(len(form.optim_ID[v]), N))
+        plan.var_off = [form.optim_ID[v].start for v in plant_optim]
+        plan.x0_index = [i for blk in blocks for i in form.given_ID[x0_base + axes[blk]]]
+
+    def form_of(name, what):
+        if name not in forms:
+            _unsupported("{} on '{}'".format(what, name))
+        if isinstance(forms[name], Exception):
+            raise forms[name]
+        return forms[name]
 
     # ---- limits, in the reference's stacking order (body.py:306-318) -------
+    Gz_rows, Hg_rows, kinds = [], [], []
     for limit in _plan.ordered_limits(form):
         if limit.L:
             _unsupported("a limit with L")
-        k0, cnt = 0, N
+        names = [limit.variable + ax for ax in limit.axes]
+        members = [form_of(nm, "a limit") for nm in names]
+        on_plant = any(f.has_plant() for f in members) or not plan.embedded
+        rows = N if on_plant else members[0].rows
+        if rows is None:
+            _unsupported("a limit on '{}' (no samples)".format(names[0]))
+        k0, cnt = 0, rows
         if limit.schedule:
             sched = limit.schedule
-            if not isinstance(sched, range) or sched.step != 1 or sched.start < 0 or sched.stop > N:
+            if not isinstance(sched, range) or sched.step != 1 or sched.start < 0 or sched.stop > rows:
                 _unsupported("a limit whose schedule is not a contiguous range inside the horizon")
             k0, cnt = sched.start, len(sched)
-        names = [limit.variable + ax for ax in limit.axes]
-        for nm in names:
-            if nm not in forms:
-                _unsupported("a limit on '{}'".format(nm))
         arrow = np.asarray(limit.arrow)
         if arrow.dtype == object:
             _unsupported("a per-instance arrow (a limit turned by a Param)")
@@ -439,21 +621,21 @@ def lower(form, plant_name):
             raise ValueError(
                 "operands could not be broadcast together with shapes ({},1) ({},{})".format(
                     int(nlines), cnt, plan.nv))
-        rows_form, rows_arrow = _Form(), np.ones([N])
+        rows_form, rows_arrow = _Form(), np.ones([rows])
         if len(names) == 1:
-            rows_form.add(forms[names[0]], 1.0)
+            rows_form.add(members[0], 1.0)
             column = arrow[:, 0]
-            rows_arrow = np.zeros([N])
+            rows_arrow = np.zeros([rows])
             rows_arrow[k0:k0 + cnt] = np.broadcast_to(column, [cnt]) if column.shape[0] == 1 else column
         else:
             if arrow.shape[0] != 1:
                 _unsupported("a limit over several axes whose arrow changes from row to row")
-            for a, nm in enumerate(names):  # one facet: the axes' forms weighted by the normal
-                rows_form.add(forms[nm], float(arrow[0, a]))
+            for a, f in enumerate(members):  # one facet: the axes' forms weighted by the normal
+                rows_form.add(f, float(arrow[0, a]))
         # bound = extreme + sum_a arrow_a * center_a   (restrictions.py:198-199), rows k0..
         parts = []
         for coef, col in _bound_parts(limit, cnt):
-            full = np.zeros([N])
+            full = np.zeros([rows])
             full[k0:k0 + cnt] = col
             parts.append((coef, full))
         for e in np.asarray(limit.extreme, dtype=object).ravel():
@@ -461,26 +643,61 @@ def lower(form, plant_name):
                 plan.slots.require_nonnegative(e, "limit on '{}'".format(limit.variable))
         plan.row_offsets.append(plan.nc)
         plan.limit_rows.append(cnt)
+        if plan.embedded:  # the rows' part over z and over the auxiliary givens (+ constant)
+            Mz = rows_form.Mz if rows_form.Mz is not None else np.zeros([rows, nz])
+            Mg = rows_form.Mg if rows_form.Mg is not None else np.zeros([rows, form.given_len])
+            Gz_rows.append((rows_arrow[:, None] * Mz)[k0:k0 + cnt])
+            Hg = np.zeros([cnt, form.given_len + 1])
+            Hg[:, :-1] = -(rows_arrow[:, None] * Mg)[k0:k0 + cnt]
+            if not on_plant:
+                if any(is_expr(coef) for coef, _ in parts):
+                    _unsupported("a per-instance bound on a limit outside the plant")
+                for coef, col in parts:
+                    Hg[:, -1] += float(coef) * col[k0:k0 + cnt]
+            Hg_rows.append(Hg)
+            kinds += [0 if on_plant else 1] * cnt
+        if on_plant:
+            plan.group_row0.append(plan.nc)
+            plan.groups.append((rows_form, rows_arrow, parts, k0, cnt))
         plan.nc += cnt
-        plan.groups.append((rows_form, rows_arrow, parts, k0, cnt))
 
     # ---- costs, in dict order (body.py:322-329) -----------------------------
+    Pzz = np.zeros([nz, nz])
     for cost in form.goals.values():
-        if cost.L or cost.cross_L or cost.schedule:
-            _unsupported("a cost with L or a schedule")
         if isinstance(cost.weight, np.ndarray) and cost.weight.ndim:
             raise TypeError("a cost weight must be a scalar")
         w = cost.weight if is_expr(cost.weight) else float(cost.weight)
+        if not is_expr(w) and w == 0.0 and (plan.embedded or cost.L or cost.cross_L or cost.schedule):
+            continue  # adds exact zeros (the biped's terminal cost, biped_configuration.py:49)
+        if cost.L or cost.cross_L or cost.schedule:
+            _unsupported("a cost with L or a schedule")
         for a, ax in enumerate(cost.axes):
             vname, cname = cost.variable + ax, cost.cross + ax
-            if vname not in forms or cname not in forms:
-                _unsupported("a cost on '{}'".format(vname))
-            fv, fc = forms[vname], forms[cname]
+            fv, fc = form_of(vname, "a cost"), form_of(cname, "a cost")
             if (fv.touches_states() and fc.touches_inputs()) or (fv.touches_inputs() and fc.touches_states()):
                 _unsupported("a cost that couples states and inputs")
             aim = _single(np.asarray(cost.aim, dtype=object)[:, a], "an aim")
             caim = _single(np.asarray(cost.cross_aim, dtype=object)[:, a], "an aim")
-            plan.cost_terms.append((w, fv, fc, aim, caim))
+            if fv.has_aux() or fc.has_aux():
+                if fv is not fc:
+                    _unsupported("a crossed cost on variables outside the plant")
+                if is_expr(w) or is_expr(aim):
+                    _unsupported("a per-instance weight or aim of a cost on variables outside the plant")
+                if fv.rows != N:
+                    _unsupported("a cost on '{}' ({} samples, the horizon has {})".format(vname, fv.rows, N))
+                Mz = fv.Mz if fv.Mz is not None else np.zeros([N, nz])
+                Mg = fv.Mg if fv.Mg is not None else np.zeros([N, form.given_len])
+                E = np.zeros([N, form.given_len + 1])  # e = Mg given - aim
+                E[:, :-1], E[:, -1] = Mg, -float(aim)
+                plan.coupled.append((w, fv, Mz, E))
+                Pzz += w * (Mz.T @ Mz)  # body.py:292 with Vo = Co = [T | Mz]
+            if fv.has_plant() or fc.has_plant() or not plan.embedded:
+                plan.cost_terms.append((w, fv, fc, aim, caim))
+    if plan.embedded:
+        plan.Pzz = Pzz
+        plan.Gz = np.vstack(Gz_rows) if Gz_rows else np.zeros([0, nz])
+        plan.Hg = np.vstack(Hg_rows) if Hg_rows else np.zeros([0, form.given_len + 1])
+        plan.row_kind = np.array(kinds, dtype=np.int32)
 
     plan.per_instance = (
         any(is_expr(w) or fv.symbolic() or fc.symbolic() for w, fv, fc, _, _ in plan.cost_terms)
@@ -565,15 +782,18 @@ def assemble(plan, A, B, x0, params=None, out=None, hessian=HESSIAN_DMMA):
     def to_dev(x):
         if torch.is_tensor(x):
             return x.to(device=dev, dtype=torch.float64).contiguous()
-        return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float64)).to(dev)
+        return torch.from_numpy(np.require(x, dtype=np.float64, requirements=["C", "W"])).to(dev)
 
     A, B, x0 = to_dev(A), to_dev(B), to_dev(x0)
     n, m, n0, m0 = plan.n, plan.m, plan.n0, plan.m0
-    if x0.dim() != 2 or x0.shape[1] != n:
+    if x0.dim() != 2 or x0.shape[1] != plan.ng:
         raise ValueError(
             "matmul: the given vector has {} elements per instance, the formulation "
-            "expects {}".format(x0.shape[-1], n)
+            "expects {}".format(x0.shape[-1], plan.ng)
         )
+    given = x0
+    if plan.embedded:  # the plant's initial state, in the kernel's block order
+        x0 = given[:, torch.as_tensor(plan.x0_index, device=dev)].contiguous()
     batch = x0.shape[0]
     if tuple(A.shape[-2:]) != (n0, n0) or tuple(B.shape[-2:]) != (n0, m0):
         raise ValueError("A must be [..., {0}, {0}] and B [..., {0}, {1}]".format(n0, m0))
@@ -590,6 +810,30 @@ def assemble(plan, A, B, x0, params=None, out=None, hessian=HESSIAN_DMMA):
         raise ValueError("the output batch does not match the plan")
     stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     ptr = device._ptr
+    if plan.embedded:
+        missing = [nm for nm in plan.parameter_names() if nm not in (params or {})]
+        if missing:
+            raise KeyError("no value given for the parameter '{}'".format(missing[0]))
+        keep, tables, scalars, ccx, ccu = {}, None, None, None, None
+        if plan.per_instance:
+            keep = {k: to_dev(v) for k, v in plan.instance_tables(params, batch).items()}
+            tables = LtiTables(*(keep[k].data_ptr() for k in ("Qxx", "Quu", "tx", "tu", "cx", "cu", "bound")))
+            if plan.coupled:
+                ccx, ccu = (to_dev(t) for t in plan.coupled_tables(params, batch))
+                keep["ccx"], keep["ccu"] = ccx, ccu
+        elif len(plan.slots.exprs):
+            scalars = to_dev(plan.slots.evaluate(params or {}, batch))
+            keep["scalars"] = scalars
+        device.check(
+            device.lib().mpci_lti_assemble_coupled(
+                dp.handle, ptr(A), strideA, ptr(B), strideB, ptr(x0), ptr(given), ptr(scalars),
+                ctypes.byref(tables) if tables is not None else None, ptr(ccx), ptr(ccu),
+                ptr(out.P), ptr(out.q), ptr(out.G), ptr(out.h), batch, int(hessian), stream,
+            )
+        )
+        keep["x0"] = x0
+        out._keep = keep  # the launches are asynchronous: the tables live as long as the result
+        return out
     if plan.per_instance:
         missing = [nm for nm in plan.parameter_names() if nm not in (params or {})]
         if missing:

@@ -49,3 +49,55 @@ def evaluate(plan, A, B, x0, scalars, instance=None):
     G = np.vstack(Gs) if Gs else np.zeros([0, nv])
     h = np.concatenate(hs) if hs else np.zeros([0])
     return G, h, P, q
+
+
+def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None):
+    """An embedded plan (variables / givens / rows outside the plant, lti.lower): what the
+    fused kernel writes at its place in the larger matrices plus what the coupling kernel
+    (csrc/mpci_couple.cu) adds, from the plan's tables.  ``given`` [given_len];
+    ``coupled`` = (cost_cx [nC, n], cost_cu [nC, m]) of this instance for a per-instance plan."""
+    given = np.asarray(given, dtype=np.float64)
+    x0 = given[plan.x0_index]
+    Gc, hc, Pc, qc = evaluate(plan, A, B, x0, scalars, instance)
+    n, m, N, nv, nc = plan.n, plan.m, plan.N, plan.nv, plan.nc
+    cols = np.concatenate([np.arange(o, o + N) for o in plan.var_off])
+    z = np.array(plan.z_col, dtype=int)
+    P, q = np.zeros([nv, nv]), np.zeros([nv])
+    G, h = np.zeros([nc, nv]), np.zeros([nc])
+    P[np.ix_(cols, cols)], q[cols] = Pc, qc
+    at = 0
+    for g, (_form, _arrow, _parts, _k0, cnt) in enumerate(plan.groups):
+        rows = plan.group_row0[g] + np.arange(cnt)
+        G[np.ix_(rows, cols)] = Gc[at:at + cnt]
+        h[rows] = hc[at:at + cnt]
+        at += cnt
+    g1 = np.append(given, 1.0)
+    G[:, z] = plan.Gz
+    extra = plan.Hg @ g1
+    h = np.where(plan.row_kind == 1, extra, h + extra)
+    P[np.ix_(z, z)] = plan.Pzz
+    Ae, Be = plan.expand_numpy(A, B)
+    Gam = [Be]
+    for _ in range(N - 1):
+        Gam.append(Ae @ Gam[-1])
+    f, x = [], x0
+    for _ in range(N):
+        x = Ae @ x
+        f.append(x)
+    tab = plan.embed_tables()
+    for c, (w, _fv, Mz, E) in enumerate(plan.coupled):
+        cx = tab["cost_cx"][c] if coupled is None else coupled[0][c]
+        cu = tab["cost_cu"][c] if coupled is None else coupled[1][c]
+        T = np.zeros([N, m, N])
+        for k in range(N):
+            for p in range(k + 1):
+                T[k, :, p] = cx @ Gam[k - p]
+            T[k, :, k] += cu
+        T = T.reshape([N, m * N])
+        fr = np.array([cx @ f[k] for k in range(N)])
+        ee = E @ g1
+        P[np.ix_(cols, z)] += w * T.T @ Mz
+        P[np.ix_(z, cols)] += w * Mz.T @ T
+        q[cols] += w * T.T @ ee
+        q[z] += w * Mz.T @ (fr + ee)
+    return G, h, P, q

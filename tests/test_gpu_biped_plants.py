@@ -1,0 +1,127 @@
+"""The walking biped with ONE PLANT PER INSTANCE, on the GPU, against
+the unmodified reference.
+
+``formulate_biped`` with ``conf.system = "dP->CCC"``: the plant (CoP rate -> CoM, CoM_dot,
+CoM_ddot, python/mpc_interface/tools.py:253-280) depends on every robot's pendulum frequency
+and sampling period, so nothing of the prediction can be shared.  The QP keeps the whole
+structure of the reference's example (biped_formulation.py:23-191): footstep variables Ds of
+the shared ``steps`` system, the bias ``n`` entering one sample late through a matrix
+coefficient, the support-polygon box on ``(b+n-s)``, the stepping area on ``Ds`` alone, the
+terminal box on ``(DCM-s)``.  One ``generate_all_qp_matrices_batched(..., dynamics=...)`` call
+assembles the batch (fused per-instance kernel in the embedded layout + the coupling kernel);
+the reference formulates every instance from scratch with its own classes.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import _cases as cases
+from oracle import reference
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")]
+
+
+def _inputs(seed, batch, N):
+    from mpc_interface_b200.examples import synthetic
+
+    vals = synthetic.biped_inputs(seed, batch, N)
+    vals["tau"] = np.random.default_rng(seed + 5).uniform(0.08, 0.12, batch)
+    return vals
+
+
+def _conf(N, system):
+    from mpc_interface_b200.examples import biped
+
+    conf = biped.default_configuration(N)
+    conf.system = system
+    return conf
+
+
+def _reference_instance(conf, vals, b, tick=None):
+    from mpc_interface_b200.examples import biped
+
+    one = biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])],
+                                api=reference.load())
+    if tick is not None:
+        one.update(**tick)
+    collector = {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}
+    return one, one.generate_all_qp_matrices(one.arrange_given(collector))
+
+
+@pytest.mark.parametrize("system,N,batch", [("dP->CCC", 24, 16), ("dP->CCC", 100, 12), ("J->CCC", 100, 6),
+                                            ("dP->CCC", 37, 8)])
+def test_biped_with_per_instance_plants_against_the_live_reference(system, N, batch):
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    seed = int.from_bytes(os.urandom(4), "little")
+    vals = _inputs(seed, batch, N)
+    conf = _conf(N, system)
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    got = {}
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, params, dynamics={"LIP": (system, vals["tau"], vals["omega"])}, hessian=mode)
+        got[mode] = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+    for b in range(batch):
+        one, want = _reference_instance(conf, vals, b)
+        if b == 0:
+            assert list(one.optim_ID.items()) == list(form.optim_ID.items()), "integer layout"
+            assert list(one.given_ID.items()) == list(form.given_ID.items())
+        for mode in got:
+            try:
+                cases.assert_qp_close(tuple(x[b] for x in got[mode]), want)
+            except AssertionError as e:
+                raise AssertionError("seed {} instance {} ({}): {}".format(seed, b, mode, e))
+
+
+def test_biped_plants_follow_the_walking_cycle():
+    """Ticks of the receding horizon (biped_formulation.py:156-187): the step matrix E, the
+    number of Ds variables and the stepping-area centres change with the phase; every tick is
+    lowered again and must match the reference updated the same way."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    N, batch, system = 30, 4, "dP->CCC"
+    seed = int.from_bytes(os.urandom(4), "little")
+    conf = _conf(N, system)
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    sizes = set()
+    for tick in (dict(step_times=np.array([5, 17, 29]), step_count=1),
+                 dict(step_times=np.array([0, 12, 24]), step_count=2),
+                 dict(step_times=np.array([11, 23]), step_count=3)):
+        form.update(**tick)
+        vals = _inputs(seed, batch, N)
+        given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+        out = form.generate_all_qp_matrices_batched(
+            given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")},
+            dynamics={"LIP": (system, vals["tau"], vals["omega"])}, hessian="recursion")
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        sizes.add(got[0].shape[1:])
+        for b in range(batch):
+            one, want = _reference_instance(conf, vals, b, tick)
+            assert list(one.optim_ID.items()) == list(form.optim_ID.items())
+            try:
+                cases.assert_qp_close(tuple(x[b] for x in got), want)
+            except AssertionError as e:
+                raise AssertionError("seed {} tick {} instance {}: {}".format(seed, tick, b, e))
+    assert len(sizes) > 1, "the ticks were meant to change the QP's size"
+
+
+def test_embedded_plan_refuses_the_plain_entry_points():
+    from mpc_interface_b200 import Param, device, lti
+    from mpc_interface_b200.examples import biped
+
+    form = biped.formulate_biped(_conf(24, "dP->CCC"), omega=Param("omega"), tau=Param("tau"))
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and plan.nz == 2 * form.dynamics["steps"].domain["Ds_x"]
+    with pytest.raises(ValueError, match="mpci_lti_assemble_coupled"):
+        device.check(device.lib().mpci_lti_assemble(plan.device_plan().handle, None, 0, None, 0, None, None,
+                                                    None, None, None, None, 1, lti.HESSIAN_RECURSION, None))
