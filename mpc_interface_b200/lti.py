@@ -173,19 +173,70 @@ class _Form:
         return any(is_expr(c) or c != 0.0 for c in self.cu.values())
 
 
-def _value(coef, params, batch):
-    """A coefficient for the whole batch: float, or [B] for a ``Param`` expression."""
-    if is_expr(coef):
-        return np.broadcast_to(np.asarray(coef.evaluate(params), dtype=np.float64), [batch])
-    return float(coef)
+class _Host:
+    """Array namespace of the table builders on the host (NumPy)."""
+
+    @staticmethod
+    def zeros(shape):
+        return np.zeros(shape)
+
+    @staticmethod
+    def const(array):
+        return np.asarray(array, dtype=np.float64)
+
+    @staticmethod
+    def full(a, batch):
+        return np.ascontiguousarray(np.broadcast_to(a, (batch,) + tuple(a.shape[1:])))
+
+    @staticmethod
+    def params(values, batch):
+        return {k: np.broadcast_to(np.asarray(v, dtype=np.float64), [batch]) for k, v in (values or {}).items()}
 
 
-def _dense(mapping, size, params, batch):
+class _Device:
+    """The same on the GPU (torch tensors): the per-instance tables of a large batch are built
+    where the kernel reads them -- a few dozen elementwise launches instead of NumPy temporaries
+    of the batch and an upload from pageable memory."""
+
+    def __init__(self, dev):
+        import torch
+
+        self.torch, self.dev = torch, dev
+
+    def zeros(self, shape):
+        return self.torch.zeros(list(shape), dtype=self.torch.float64, device=self.dev)
+
+    def const(self, array):
+        return self.torch.from_numpy(np.require(array, dtype=np.float64, requirements=["C", "W"])).to(self.dev)
+
+    def full(self, a, batch):
+        return a.expand(batch, *a.shape[1:]).contiguous()
+
+    def params(self, values, batch):
+        out = {}
+        for k, v in (values or {}).items():
+            t = v if self.torch.is_tensor(v) else self.torch.from_numpy(
+                np.require(np.asarray(v, dtype=np.float64).reshape([-1]), requirements=["C", "W"]))
+            out[k] = t.to(device=self.dev, dtype=self.torch.float64).reshape(-1).expand(batch)
+        return out
+
+
+def _value(coef, params):
+    """A coefficient for the whole batch: float, or [B] (array / tensor) for a ``Param`` expression."""
+    return coef.evaluate(params) if is_expr(coef) else float(coef)
+
+
+def _col(v, trailing):
+    """A per-instance value shaped to broadcast against [B, ...] with ``trailing`` more axes."""
+    return v.reshape([-1] + [1] * trailing) if hasattr(v, "reshape") else v
+
+
+def _dense(mapping, size, params, batch, xp=_Host):
     """[B, size] (or [1, size] when nothing in it is per-instance)."""
     rows = batch if any(is_expr(c) for c in mapping.values()) else 1
-    out = np.zeros([rows, size])
+    out = xp.zeros([rows, size])
     for idx, c in mapping.items():
-        out[:, idx] += _value(c, params, batch) if is_expr(c) else float(c)
+        out[:, idx] += _value(c, params)
     return out
 
 
@@ -207,6 +258,7 @@ class LtiPlan:
         self.n0, self.m0 = n, m
         self.blocks, self.inputs = [0], [(0, j) for j in range(m)]
         self.per_instance = False  # any Param in weights / forms / bounds
+        self.varying = set()       # ... and which of the kernel's tables they reach
         self._device = None
         # embedded layout: the QP has variables / givens / rows outside the plant (lower())
         self.embedded = False
@@ -216,58 +268,93 @@ class LtiPlan:
         self.Pzz = self.Gz = self.Hg = self.row_kind = None
 
     # ---- numeric tables -----------------------------------------------------
-    def _cost_tables(self, params, batch):
+    def _cost_tables(self, params, batch, xp=_Host):
         """Qxx [R, n, n], Quu [R, m, m], and the aim parts; R = batch when per-instance."""
         n, m = self.n, self.m
-        Qxx, Quu = np.zeros([1, n, n]), np.zeros([1, m, m])
+        Qxx, Quu = xp.zeros([1, n, n]), xp.zeros([1, m, m])
         for w, fv, fc, _aim, _caim in self.cost_terms:
-            wv = np.reshape(_value(w, params, batch), [-1, 1, 1])
-            cvx, ccx = _dense(fv.cx, n, params, batch), _dense(fc.cx, n, params, batch)
-            cvu, ccu = _dense(fv.cu, m, params, batch), _dense(fc.cu, m, params, batch)
+            wv = _col(_value(w, params), 2)
+            cvx, ccx = _dense(fv.cx, n, params, batch, xp), _dense(fc.cx, n, params, batch, xp)
+            cvu, ccu = _dense(fv.cu, m, params, batch, xp), _dense(fc.cu, m, params, batch, xp)
             Qxx = Qxx + wv * cvx[:, :, None] * ccx[:, None, :]  # Q += w Vo^T Co   (body.py:292)
             Quu = Quu + wv * cvu[:, :, None] * ccu[:, None, :]
         return Qxx, Quu
 
-    def _offsets(self, params, batch):
+    def _offsets(self, params, batch, xp=_Host):
         """tx [R, n], tu [R, m]: (w/2)(cv * caim + cc * aim) summed over the costs
         (body.py:293-300), every factor evaluated per instance."""
         n, m = self.n, self.m
-        tx, tu = np.zeros([1, n]), np.zeros([1, m])
+        tx, tu = xp.zeros([1, n]), xp.zeros([1, m])
         for w, fv, fc, aim, caim in self.cost_terms:
-            half = np.reshape(_value(w, params, batch), [-1, 1]) / 2
+            half = _col(_value(w, params), 1) / 2
             for form, target in ((fv, caim), (fc, aim)):
-                a = np.reshape(_value(target, params, batch), [-1, 1])
-                tx = tx + half * a * _dense(form.cx, n, params, batch)
-                tu = tu + half * a * _dense(form.cu, m, params, batch)
+                a = _col(_value(target, params), 1)
+                tx = tx + half * a * _dense(form.cx, n, params, batch, xp)
+                tu = tu + half * a * _dense(form.cu, m, params, batch, xp)
         return tx, tu
 
-    def _group_tables(self, params, batch):
+    def _group_tables(self, params, batch, xp=_Host, which=("cx", "cu", "bound")):
         G, n, m, N = len(self.groups), self.n, self.m, self.N
-        rows = batch if self.per_instance else 1
-        cx, cu = np.zeros([rows, G, n]), np.zeros([rows, G, m])
-        bound = np.zeros([rows, G, N])
+        rows = {k: batch if (self.per_instance and k in self.varying) else 1 for k in ("cx", "cu", "bound")}
+        cx = xp.zeros([rows["cx"], G, n]) if "cx" in which else None
+        cu = xp.zeros([rows["cu"], G, m]) if "cu" in which else None
+        bound = xp.zeros([rows["bound"], G, N]) if "bound" in which else None
         for g, (form, _arrow, parts, _k0, _cnt) in enumerate(self.groups):
-            cx[:, g] = _dense(form.cx, n, params, batch)
-            cu[:, g] = _dense(form.cu, m, params, batch)
-            for coef, col in parts:
-                bound[:, g] += np.reshape(_value(coef, params, batch), [-1, 1]) * col[None, :]
+            if cx is not None:
+                cx[:, g] = _dense(form.cx, n, params, batch, xp)
+            if cu is not None:
+                cu[:, g] = _dense(form.cu, m, params, batch, xp)
+            for coef, col in (parts if bound is not None else ()):
+                bound[:, g] += _col(_value(coef, params), 1) * xp.const(col)[None, :]
         return cx, cu, bound
 
+    def _find_varying(self):
+        """Which tables differ between the instances of a per-instance plan: only those travel
+        per instance (mpci_lti_tables), the others stay formulation constants of the plan."""
+        v = set()
+        for w, fv, fc, _aim, _caim in self.cost_terms:
+            sym_x = any(is_expr(c) for f in (fv, fc) for c in f.cx.values())
+            sym_u = any(is_expr(c) for f in (fv, fc) for c in f.cu.values())
+            if (is_expr(w) or sym_x) and (fv.cx and fc.cx):
+                v.add("Qxx")
+            if (is_expr(w) or sym_u) and (fv.cu and fc.cu):
+                v.add("Quu")
+        for form, _arrow, parts, _k0, _cnt in self.groups:
+            if any(is_expr(c) for c in form.cx.values()):
+                v.add("cx")
+            if any(is_expr(c) for c in form.cu.values()):
+                v.add("cu")
+            if any(is_expr(coef) for coef, _ in parts):
+                v.add("bound")
+        return v
+
     def tables(self):
-        """Constant tables for ``mpci_lti_plan_create``.  A per-instance plan gets
-        placeholders whose only job is the structure: ones wherever a form may touch a
-        state (the kernel skips the state part of limits whose ``cx`` is all zero)."""
+        """Constant tables for ``mpci_lti_plan_create``.  In a per-instance plan the tables
+        that vary get placeholders whose only job is the structure: ones wherever a form may
+        touch a state (the kernel skips the state part of limits whose ``cx`` is all zero)."""
         G, n, m, N, S = len(self.groups), self.n, self.m, self.N, len(self.slots.exprs)
         arrow = np.array([g[1] for g in self.groups], dtype=np.float64).reshape([G, N])
         k0 = np.array([g[3] for g in self.groups], dtype=np.int32).reshape([G])
         cnt = np.array([g[4] for g in self.groups], dtype=np.int32).reshape([G])
         if self.per_instance:
-            cx = np.zeros([G, n])
-            for g, (form, *_rest) in enumerate(self.groups):
-                for idx, c in form.cx.items():
-                    cx[g, idx] = 1.0 if (is_expr(c) or c != 0.0) else 0.0
-            return dict(Qxx=np.zeros([n, n]), Quu=np.zeros([m, m]), Tx=np.zeros([n, 1]), Tu=np.zeros([m, 1]),
-                        grp_cx=cx, grp_cu=np.zeros([G, m]), grp_arrow=arrow, grp_bound=np.zeros([G, N]),
+            fixed = [k for k in ("cx", "cu", "bound") if k not in self.varying]
+            cx, cu, bound = self._group_tables({}, 1, which=fixed)
+            if cx is None:
+                cx = np.zeros([1, G, n])
+                for g, (form, *_rest) in enumerate(self.groups):
+                    for idx, c in form.cx.items():
+                        cx[0, g, idx] = 1.0 if (is_expr(c) or c != 0.0) else 0.0
+            cu = np.zeros([1, G, m]) if cu is None else cu
+            bound = np.zeros([1, G, N]) if bound is None else bound
+            Qxx, Quu = np.zeros([1, n, n]), np.zeros([1, m, m])
+            if "Qxx" not in self.varying or "Quu" not in self.varying:
+                # (a table that does not vary has no Param in it: any values do for the others)
+                Qc, Rc = self._cost_tables({k: 1.0 for k in self.parameter_names()}, 1)
+                Qxx = Qc if "Qxx" not in self.varying else Qxx
+                Quu = Rc if "Quu" not in self.varying else Quu
+            c = np.ascontiguousarray
+            return dict(Qxx=c(Qxx[0]), Quu=c(Quu[0]), Tx=np.zeros([n, 1]), Tu=np.zeros([m, 1]),
+                        grp_cx=c(cx[0]), grp_cu=c(cu[0]), grp_arrow=arrow, grp_bound=c(bound[0]),
                         grp_k0=k0, grp_rows=cnt)
         Qxx, Quu = self._cost_tables({}, 1)
         cx, cu, bound = self._group_tables({}, 1)
@@ -313,32 +400,48 @@ class LtiPlan:
                     Pzz=f64(self.Pzz), Gz=f64(self.Gz), h_ptr=h_ptr, h_col=h_col, h_val=h_val,
                     row_kind=i32(self.row_kind))
 
-    def coupled_tables(self, params, batch):
-        """Per-instance signal tables of the coupled costs: cost_cx [B, nC, n], cost_cu [B, nC, m]."""
+    def coupled_tables(self, params, batch, dev=None):
+        """Per-instance signal tables of the coupled costs: cost_cx [B, nC, n], cost_cu [B, nC, m]
+        (NumPy, or CUDA tensors when ``dev`` is given)."""
+        xp = _Host if dev is None else _Device(dev)
+        params = xp.params(params, batch)
         nC = len(self.coupled)
-        cx, cu = np.zeros([batch, nC, self.n]), np.zeros([batch, nC, self.m])
+        cx, cu = xp.zeros([batch, nC, self.n]), xp.zeros([batch, nC, self.m])
         for c, (_w, fv, _Mz, _E) in enumerate(self.coupled):
-            cx[:, c] = _dense(fv.cx, self.n, params, batch)
-            cu[:, c] = _dense(fv.cu, self.m, params, batch)
+            cx[:, c] = _dense(fv.cx, self.n, params, batch, xp)
+            cu[:, c] = _dense(fv.cu, self.m, params, batch, xp)
         return cx, cu
 
-    def instance_tables(self, params, batch):
-        """Per-instance tables of a plan with ``Param`` coefficients: ``{name: [B, ...]}``
-        for mpci_lti_tables (float64, C order)."""
+    def instance_tables(self, params, batch, dev=None):
+        """Per-instance tables of a plan with ``Param`` coefficients: ``{name: [B, ...]}`` for
+        mpci_lti_tables (float64, C order) -- ``tx`` / ``tu`` and whichever of ``Qxx``, ``Quu``,
+        ``cx``, ``cu``, ``bound`` vary (``self.varying``).  NumPy arrays, or CUDA tensors built
+        on the device when ``dev`` is given."""
+        xp = _Host if dev is None else _Device(dev)
+        params = xp.params(params, batch)
         for e, what in self.slots.nonnegative:
-            v = np.broadcast_to(np.asarray(e.evaluate(params), dtype=np.float64), [batch])
-            if not np.all(v >= 0):
+            v = e.evaluate(params)
+            if not bool((v >= 0).all()):
+                v = np.asarray(v.cpu() if hasattr(v, "cpu") else v)
                 bad = int(np.argmax(~(v >= 0)))
                 raise ValueError(
                     "{}: the per-instance extreme '{}' is negative for instance {} ({:g}); the "
                     "reference would flip that limit (restrictions.py:190-194), which needs a "
                     "numeric extreme".format(what, e, bad, float(v[bad])))
-        Qxx, Quu = self._cost_tables(params, batch)
-        tx, tu = self._offsets(params, batch)
-        cx, cu, bound = self._group_tables(params, batch)
-        full = lambda a: np.ascontiguousarray(np.broadcast_to(a, (batch,) + a.shape[1:]))  # noqa: E731
-        return dict(Qxx=full(Qxx), Quu=full(Quu), tx=full(tx), tu=full(tu), cx=full(cx), cu=full(cu),
-                    bound=full(bound))
+        out = {}
+        if "Qxx" in self.varying or "Quu" in self.varying:
+            Qxx, Quu = self._cost_tables(params, batch, xp)
+            if "Qxx" in self.varying:
+                out["Qxx"] = Qxx
+            if "Quu" in self.varying:
+                out["Quu"] = Quu
+        out["tx"], out["tu"] = self._offsets(params, batch, xp)
+        moving = [k for k in ("cx", "cu", "bound") if k in self.varying]
+        if moving:
+            for k, t in zip(("cx", "cu", "bound"), self._group_tables(params, batch, xp, which=moving)):
+                if t is not None:
+                    out[k] = t
+        return {k: xp.full(a, batch) for k, a in out.items()}
 
     def parameter_names(self):
         names = []
@@ -543,15 +646,20 @@ def _linear_forms(form, plant_name, layout):
         if name in forms or name in skip:
             continue
         out = _Form()
-        for var, coef in combo.items():
-            if var not in forms:
-                _unsupported("the definition '{}' (depends on '{}')".format(name, var))
-            kind, value = _plan._scalar_kind(coef)
-            if kind == "mat":  # blocks of another dynamics (tools.py:79-101), shifted biases
-                out.add_matrix(forms[var], value if value.ndim == 2 else value.reshape([value.shape[0], -1]), name)
-            else:
-                out.add(forms[var], value)
-        forms[name] = out
+        try:
+            for var, coef in combo.items():
+                if var not in forms:
+                    _unsupported("the definition '{}' (depends on '{}')".format(name, var))
+                if isinstance(forms[var], Exception):
+                    raise forms[var]
+                kind, value = _plan._scalar_kind(coef)
+                if kind == "mat":  # blocks of another dynamics (tools.py:79-101), shifted biases
+                    out.add_matrix(forms[var], value if value.ndim == 2 else value.reshape([value.shape[0], -1]), name)
+                else:
+                    out.add(forms[var], value)
+            forms[name] = out
+        except (NotImplementedError, ValueError, TypeError) as problem:
+            forms[name] = problem  # raised when a cost or a limit asks for this variable
     return forms
 
 
@@ -702,6 +810,7 @@ def lower(form, plant_name):
     plan.per_instance = (
         any(is_expr(w) or fv.symbolic() or fc.symbolic() for w, fv, fc, _, _ in plan.cost_terms)
         or any(f.symbolic() or any(is_expr(c) for c, _ in parts) for f, _, parts, _, _ in plan.groups))
+    plan.varying = plan._find_varying() if plan.per_instance else set()
     if not plan.per_instance:
         for _, _, _, aim, caim in plan.cost_terms:  # fix the slot order (first use, as before)
             for target in (caim, aim):
@@ -767,97 +876,101 @@ def named_system_batched(name, tau, omega=None, batch=None):
     return A, B
 
 
+def _lti_tables(tensors):
+    """mpci_lti_tables of the per-instance CUDA tensors present in ``tensors`` (NULL = the plan's)."""
+    return LtiTables(*(tensors[k].data_ptr() if k in tensors else None
+                       for k in ("Qxx", "Quu", "tx", "tu", "cx", "cu", "bound")))
+
+
+class LtiJob:
+    """The device-resident inputs of one batch for a lowered plan: the expanded plants, the
+    given vectors, the scalar slots or per-instance tables (evaluated on the GPU) -- everything
+    ``launch`` hands to ``mpci_lti_assemble`` / ``_ex`` / ``_coupled``.  Building the job and
+    launching it are separate so that a receding-horizon loop (or a benchmark) can launch the
+    same inputs again without re-evaluating the tables."""
+
+    def __init__(self, plan, A, B, x0, params=None):
+        import torch
+
+        self.plan = plan
+        self.handle = plan.device_plan().handle
+        dev = self.dev = torch.device("cuda", torch.cuda.current_device())
+
+        def to_dev(x):
+            if torch.is_tensor(x):
+                return x.to(device=dev, dtype=torch.float64).contiguous()
+            return torch.from_numpy(np.require(x, dtype=np.float64, requirements=["C", "W"])).to(dev)
+
+        A, B, x0 = to_dev(A), to_dev(B), to_dev(x0)
+        n, m, n0, m0 = plan.n, plan.m, plan.n0, plan.m0
+        if x0.dim() != 2 or x0.shape[1] != plan.ng:
+            raise ValueError(
+                "matmul: the given vector has {} elements per instance, the formulation "
+                "expects {}".format(x0.shape[-1], plan.ng)
+            )
+        self.given = x0
+        if plan.embedded:  # the plant's initial state, in the kernel's block order
+            x0 = x0[:, torch.as_tensor(plan.x0_index, device=dev)].contiguous()
+        self.x0 = x0
+        batch = self.batch = x0.shape[0]
+        if tuple(A.shape[-2:]) != (n0, n0) or tuple(B.shape[-2:]) != (n0, m0):
+            raise ValueError("A must be [..., {0}, {0}] and B [..., {0}, {1}]".format(n0, m0))
+        for M in (A, B):
+            if M.dim() == 3 and M.shape[0] != batch:
+                raise ValueError("the dynamics hold {} instances, x0 {}".format(M.shape[0], batch))
+        A, B = plan.expand_device(A, B)
+        self.A, self.B = A.contiguous(), B.contiguous()
+        self.strideA = n * n if A.dim() == 3 else 0
+        self.strideB = n * m if B.dim() == 3 else 0
+        self.tables = self.scalars = self.ccx = self.ccu = None
+        if plan.per_instance or plan.embedded:
+            missing = [nm for nm in plan.parameter_names() if nm not in (params or {})]
+            if missing:
+                raise KeyError("no value given for the parameter '{}'".format(missing[0]))
+        if plan.per_instance:
+            self.tensors = plan.instance_tables(params, batch, dev)
+            self.tables = _lti_tables(self.tensors)
+            if plan.coupled:
+                self.ccx, self.ccu = plan.coupled_tables(params, batch, dev)
+        elif len(plan.slots.exprs):
+            self.scalars = to_dev(plan.slots.evaluate(params or {}, batch))
+
+    def launch(self, out=None, hessian=HESSIAN_DMMA, parts="PqGh"):
+        """One assembly of the batch into ``out`` (a ``QPBatch``, allocated when None) on the
+        current stream; ``parts`` picks the outputs (the others are not computed)."""
+        import torch
+
+        from . import device
+
+        plan, batch = self.plan, self.batch
+        if out is None:
+            out = device.QPBatch(batch, plan.nv, plan.nc, self.dev)
+        elif (out.batch, out.nv, out.nc) != (batch, plan.nv, plan.nc):
+            raise ValueError("the output batch does not match the plan")
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        ptr = device._ptr
+        outs = [ptr(t) if tag in parts else None for tag, t in zip("PqGh", (out.P, out.q, out.G, out.h))]
+        tables = ctypes.byref(self.tables) if self.tables is not None else None
+        head = (self.handle, ptr(self.A), self.strideA, ptr(self.B), self.strideB, ptr(self.x0))
+        lib = device.lib()
+        if plan.embedded:
+            rc = lib.mpci_lti_assemble_coupled(*head, ptr(self.given), ptr(self.scalars), tables,
+                                               ptr(self.ccx), ptr(self.ccu), *outs, batch, int(hessian), stream)
+        elif plan.per_instance:
+            rc = lib.mpci_lti_assemble_ex(*head, None, tables, *outs, batch, int(hessian), stream)
+        else:
+            rc = lib.mpci_lti_assemble(*head, ptr(self.scalars), *outs, batch, int(hessian), stream)
+        device.check(rc)
+        out._keep = self  # the launches are asynchronous: the inputs live as long as the result
+        return out
+
+
 def assemble(plan, A, B, x0, params=None, out=None, hessian=HESSIAN_DMMA):
     """Runs ``mpci_lti_assemble`` (``mpci_lti_assemble_ex`` for a plan with per-instance
-    tables).  ``A`` [batch, n0, n0] or [n0, n0] (shared), ``B`` likewise -- the plant of ONE
-    axis -- and ``x0`` [batch, given_len] in the formulation's given order: numpy arrays or
-    CUDA tensors (float64)."""
-    import torch
-
-    from . import device
-
-    dp = plan.device_plan()
-    dev = torch.device("cuda", torch.cuda.current_device())
-
-    def to_dev(x):
-        if torch.is_tensor(x):
-            return x.to(device=dev, dtype=torch.float64).contiguous()
-        return torch.from_numpy(np.require(x, dtype=np.float64, requirements=["C", "W"])).to(dev)
-
-    A, B, x0 = to_dev(A), to_dev(B), to_dev(x0)
-    n, m, n0, m0 = plan.n, plan.m, plan.n0, plan.m0
-    if x0.dim() != 2 or x0.shape[1] != plan.ng:
-        raise ValueError(
-            "matmul: the given vector has {} elements per instance, the formulation "
-            "expects {}".format(x0.shape[-1], plan.ng)
-        )
-    given = x0
-    if plan.embedded:  # the plant's initial state, in the kernel's block order
-        x0 = given[:, torch.as_tensor(plan.x0_index, device=dev)].contiguous()
-    batch = x0.shape[0]
-    if tuple(A.shape[-2:]) != (n0, n0) or tuple(B.shape[-2:]) != (n0, m0):
-        raise ValueError("A must be [..., {0}, {0}] and B [..., {0}, {1}]".format(n0, m0))
-    for M in (A, B):
-        if M.dim() == 3 and M.shape[0] != batch:
-            raise ValueError("the dynamics hold {} instances, x0 {}".format(M.shape[0], batch))
-    A, B = plan.expand_device(A, B)
-    A, B = A.contiguous(), B.contiguous()
-    strideA = n * n if A.dim() == 3 else 0
-    strideB = n * m if B.dim() == 3 else 0
-    if out is None:
-        out = device.QPBatch(batch, plan.nv, plan.nc, dev)
-    elif (out.batch, out.nv, out.nc) != (batch, plan.nv, plan.nc):
-        raise ValueError("the output batch does not match the plan")
-    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    ptr = device._ptr
-    if plan.embedded:
-        missing = [nm for nm in plan.parameter_names() if nm not in (params or {})]
-        if missing:
-            raise KeyError("no value given for the parameter '{}'".format(missing[0]))
-        keep, tables, scalars, ccx, ccu = {}, None, None, None, None
-        if plan.per_instance:
-            keep = {k: to_dev(v) for k, v in plan.instance_tables(params, batch).items()}
-            tables = LtiTables(*(keep[k].data_ptr() for k in ("Qxx", "Quu", "tx", "tu", "cx", "cu", "bound")))
-            if plan.coupled:
-                ccx, ccu = (to_dev(t) for t in plan.coupled_tables(params, batch))
-                keep["ccx"], keep["ccu"] = ccx, ccu
-        elif len(plan.slots.exprs):
-            scalars = to_dev(plan.slots.evaluate(params or {}, batch))
-            keep["scalars"] = scalars
-        device.check(
-            device.lib().mpci_lti_assemble_coupled(
-                dp.handle, ptr(A), strideA, ptr(B), strideB, ptr(x0), ptr(given), ptr(scalars),
-                ctypes.byref(tables) if tables is not None else None, ptr(ccx), ptr(ccu),
-                ptr(out.P), ptr(out.q), ptr(out.G), ptr(out.h), batch, int(hessian), stream,
-            )
-        )
-        keep["x0"] = x0
-        out._keep = keep  # the launches are asynchronous: the tables live as long as the result
-        return out
-    if plan.per_instance:
-        missing = [nm for nm in plan.parameter_names() if nm not in (params or {})]
-        if missing:
-            raise KeyError("no value given for the parameter '{}'".format(missing[0]))
-        host = plan.instance_tables(params, batch)
-        keep = {k: to_dev(v) for k, v in host.items()}
-        tables = LtiTables(*(keep[k].data_ptr() for k in ("Qxx", "Quu", "tx", "tu", "cx", "cu", "bound")))
-        device.check(
-            device.lib().mpci_lti_assemble_ex(
-                dp.handle, ptr(A), strideA, ptr(B), strideB, ptr(x0), None, ctypes.byref(tables),
-                ptr(out.P), ptr(out.q), ptr(out.G), ptr(out.h), batch, int(hessian), stream,
-            )
-        )
-        out._keep = keep  # the launch is asynchronous: the tables live as long as the result
-        return out
-    S = len(plan.slots.exprs)
-    scalars = to_dev(plan.slots.evaluate(params or {}, batch)) if S else None
-    device.check(
-        device.lib().mpci_lti_assemble(
-            dp.handle, ptr(A), strideA, ptr(B), strideB, ptr(x0), ptr(scalars),
-            ptr(out.P), ptr(out.q), ptr(out.G), ptr(out.h), batch, int(hessian), stream,
-        )
-    )
-    return out
+    tables, ``mpci_lti_assemble_coupled`` for an embedded one).  ``A`` [batch, n0, n0] or
+    [n0, n0] (shared), ``B`` likewise -- the plant of ONE axis -- and ``x0`` [batch, given_len]
+    in the formulation's given order: numpy arrays or CUDA tensors (float64)."""
+    return LtiJob(plan, A, B, x0, params).launch(out, hessian)
 
 
 def _host_inputs(plan, A, B, x0, params):

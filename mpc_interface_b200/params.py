@@ -69,12 +69,9 @@ class Expr:
             return v[0] ** v[1]
         if self.op == "neg":
             return -v[0]
-        if self.op == "sqrt":
-            return np.sqrt(v[0])
-        if self.op == "cos":
-            return np.cos(v[0])
-        if self.op == "sin":
-            return np.sin(v[0])
+        if self.op in ("sqrt", "cos", "sin"):  # ndarray / float, or a tensor (its own method)
+            own = getattr(v[0], self.op, None)
+            return own() if callable(own) else getattr(np, self.op)(v[0])
         raise ValueError("unknown operation " + self.op)
 
     # -- polynomial form ---------------------------------------------------

@@ -2,7 +2,7 @@
 # One iteration on the embedded per-instance path (biped with one plant per instance):
 # parity against the live reference, the plain per-instance tests, timings.
 mkdir -p gpurun_out
-python -m pytest tests/test_gpu_biped_plants.py -q -x > gpurun_out/pytest_biped_plants.log 2>&1; echo "pytest biped plants exit $?"; tail -25 gpurun_out/pytest_biped_plants.log
+[[ " $* " == *" notests "* ]] || python -m pytest tests/test_gpu_biped_plants.py -q -x > gpurun_out/pytest_biped_plants.log 2>&1; echo "pytest biped plants exit $?"; tail -25 gpurun_out/pytest_biped_plants.log
 if [[ " $* " == *" lti "* ]]; then
   python -m pytest tests/test_gpu_lti.py tests/test_gpu_reference_live.py tests/test_gpu_guards.py -q -k "lti or plants or guard or lip or named or permuted" > gpurun_out/pytest_lti.log 2>&1; echo "pytest lti exit $?"; tail -5 gpurun_out/pytest_lti.log
   python scripts/bench_lti.py --config ${CFG:-all} > gpurun_out/bench_lti.jsonl 2> gpurun_out/bench_lti.err; echo "bench_lti exit $?"

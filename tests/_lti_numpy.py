@@ -24,9 +24,11 @@ def evaluate(plan, A, B, x0, scalars, instance=None):
         s1 = np.append(scalars, 1.0)
         tx, tu = t["Tx"] @ s1, t["Tu"] @ s1
         Qxx, Quu, cxs, cus, bounds = t["Qxx"], t["Quu"], t["grp_cx"], t["grp_cu"], t["grp_bound"]
-    else:
-        tx, tu, Qxx, Quu = instance["tx"], instance["tu"], instance["Qxx"], instance["Quu"]
-        cxs, cus, bounds = instance["cx"], instance["cu"], instance["bound"]
+    else:  # whatever does not vary between the instances stays in the plan's tables
+        tx, tu = instance["tx"], instance["tu"]
+        Qxx, Quu = instance.get("Qxx", t["Qxx"]), instance.get("Quu", t["Quu"])
+        cxs, cus = instance.get("cx", t["grp_cx"]), instance.get("cu", t["grp_cu"])
+        bounds = instance.get("bound", t["grp_bound"])
     Qs = 0.5 * (Qxx + Qxx.T)
     # dense Toeplitz operator: rows (k, i), columns (j, p)
     T = np.zeros([N, n, m, N])

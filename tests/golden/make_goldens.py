@@ -315,6 +315,38 @@ def lip_per_instance(name, N, batch, seed):
          A_sys=np.stack(Asys), B_sys=np.stack(Bsys), **vals, **layout(form))
 
 
+def biped_plants(name, N, batch, seed, system="dP->CCC", tick=None):
+    """examples/biped.py (the structure of biped_formulation.py:23-191: steps system, bias
+    through its matrix coefficient, three boxes) with ONE PLANT PER INSTANCE -- its own
+    pendulum frequency and sampling period in ControlSystem.from_name(system, tau_b, omega_b)
+    -- formulated per instance on the reference's classes; ``tick`` = kargs of
+    Formulation.update (another phase of the walking cycle)."""
+    from mpc_interface_b200.examples import biped
+
+    api = types.SimpleNamespace(ControlSystem=ref_dyn.ControlSystem, ExtendedSystem=ref_dyn.ExtendedSystem,
+                                DomainVariable=ref_dyn.DomainVariable, Formulation=ref_body.Formulation,
+                                LineCombo=ref_comb.LineCombo, Cost=ref_goal.Cost, Box=ref_res.Box,
+                                tools=ref_tools)
+    vals = synthetic.biped_inputs(seed, batch, N)
+    vals["tau"] = np.random.default_rng(seed + 5).uniform(0.08, 0.12, batch)
+    conf = biped.default_configuration(N)
+    conf.system = system
+    As, hs, Qs, qs, Asys, Bsys = [], [], [], [], [], []
+    for b in range(batch):
+        form = biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                     target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        if tick is not None:
+            form.update(**tick)
+        collector = {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in form.given_ID}
+        A, h, Q, q = form.generate_all_qp_matrices(form.arrange_given(collector))
+        As.append(A), hs.append(h[:, 0]), Qs.append(Q), qs.append(q[:, 0])
+        system_b = ref_dyn.ControlSystem.from_name(system, tau=float(vals["tau"][b]), omega=float(vals["omega"][b]))
+        Asys.append(np.array(system_b.A, dtype=float)), Bsys.append(np.array(system_b.B, dtype=float))
+    extra = {} if tick is None else {"tick_" + k: np.asarray(v) for k, v in tick.items()}
+    save(name, seed=seed, N=N, A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs), q=np.stack(qs),
+         A_sys=np.stack(Asys), B_sys=np.stack(Bsys), **vals, **extra, **layout(form))
+
+
 def random_forms(name, seeds, batch):
     """tests/_random_forms.py built by the reference, one formulation per instance."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -347,6 +379,12 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["lip"]:
         lip_per_instance("lip_perinst.npz", 40, 6, 1030)
         lip_per_instance("lip_perinst_n9.npz", 9, 3, 1031)
+        sys.exit(0)
+    if sys.argv[1:] == ["biped_plants"]:
+        biped_plants("biped_plants_n24.npz", 24, 4, 1040)
+        biped_plants("biped_plants_n30_tick.npz", 30, 3, 1041,
+                     tick=dict(step_times=np.array([5, 17, 29]), step_count=1))
+        biped_plants("biped_plants_jccc_n16.npz", 16, 2, 1042, system="J->CCC")
         sys.exit(0)
     if sys.argv[1:] == ["big"]:
         biped_long("biped_long_digest.npz", [200, 400], 1020)

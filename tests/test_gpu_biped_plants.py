@@ -125,3 +125,29 @@ def test_embedded_plan_refuses_the_plain_entry_points():
     with pytest.raises(ValueError, match="mpci_lti_assemble_coupled"):
         device.check(device.lib().mpci_lti_assemble(plan.device_plan().handle, None, 0, None, 0, None, None,
                                                     None, None, None, None, 1, lti.HESSIAN_RECURSION, None))
+
+
+@pytest.mark.parametrize("name,system", [("biped_plants_n24", "dP->CCC"), ("biped_plants_n30_tick", "dP->CCC"),
+                                         ("biped_plants_jccc_n16", "J->CCC")])
+def test_biped_with_per_instance_plants_against_the_committed_golden(name, system):
+    """The same against the reference's output stored under tests/golden (written by
+    make_goldens.py biped_plants), explicit (A_b, B_b) instead of a named system."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    g = cases.golden(name)
+    conf = _conf(int(g["N"]), system)
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    if "tick_step_times" in g:
+        form.update(step_times=g["tick_step_times"], step_count=int(g["tick_step_count"]))
+    cases.check_layout(form, g)
+    batch = g["A"].shape[0]
+    given = synthetic.pack_given(form.given_ID, form.given_len, {k: g[k] for k in form.given_ID}, batch)
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, {k: g[k] for k in ("omega", "vel_x", "vel_y")},
+            dynamics={"LIP": (g["A_sys"], g["B_sys"])}, hessian=mode)
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        for b in range(batch):
+            cases.assert_qp_close(tuple(x[b] for x in got), (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))

@@ -158,3 +158,87 @@ def test_lowering_permuted_inputs_and_scheduled_limit(cpu_extend):
     ref = orc.all_qp_matrices(form, g["x0"][0][:, None], values)
     cases.assert_qp_close(got, ref)
     assert got[0].shape[0] == ref[0].shape[0]
+
+
+# ---------------------------------------------------------------------------
+# the walking biped with one plant per instance (embedded layout + coupling stage)
+# ---------------------------------------------------------------------------
+def _biped_plants(g, system):
+    from mpc_interface_b200.examples import biped
+
+    conf = biped.default_configuration(int(g["N"]))
+    conf.system = system
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")], backend=NumpyBackend())
+    if "tick_step_times" in g:
+        form.update(step_times=g["tick_step_times"], step_count=int(g["tick_step_count"]))
+    return form
+
+
+@pytest.mark.parametrize("name,system", [("biped_plants_n24", "dP->CCC"), ("biped_plants_n30_tick", "dP->CCC"),
+                                         ("biped_plants_jccc_n16", "J->CCC")])
+def test_biped_with_per_instance_plants_lowering(cpu_extend, name, system):
+    """the biped's whole structure (steps system, bias through a matrix
+    coefficient, boxes on (b+n-s), Ds and (DCM-s)) lowered around a per-instance plant; the
+    tables of lti.lower -- fused-kernel part in the embedded layout plus the coupling stage,
+    both restated in NumPy (tests/_lti_numpy.py) -- against the reference, which formulated
+    every instance with its own ControlSystem.from_name(system, tau_b, omega_b)."""
+    from mpc_interface_b200.examples import synthetic
+
+    g = cases.golden(name)
+    form = _biped_plants(g, system)
+    cases.check_layout(form, g)
+    plan = form.lti_plan("LIP")
+    N, batch = int(g["N"]), g["A"].shape[0]
+    k = form.domain["Ds_x"]
+    assert plan.embedded and plan.per_instance and (plan.n, plan.m, plan.nz) == (6, 2, 2 * k)
+    assert (plan.nv, plan.nc) == g["A"].shape[:0:-1] == (2 * N + 2 * k, 4 * k + 4 * N + 4)
+    assert plan.var_off == [0, N + k] and plan.z_col == list(range(N, N + k)) + list(range(2 * N + k, 2 * N + 2 * k))
+    assert plan.varying == {"Qxx", "cx"}  # omega reaches the CoP definitions only
+    assert list(plan.row_kind[:4 * k]) == [1] * (4 * k) and not plan.row_kind[4 * k:].any()
+    params = {key: g[key] for key in ("omega", "tau", "vel_x", "vel_y")}
+    assert sorted(plan.parameter_names()) == ["omega", "vel_x", "vel_y"]  # tau lives in the plant
+    tables = plan.instance_tables(params, batch)
+    ccx, ccu = plan.coupled_tables(params, batch)
+    given = synthetic.pack_given(form.given_ID, form.given_len, {key: g[key] for key in form.given_ID}, batch)
+    for b in range(batch):
+        one = {key: v[b] for key, v in tables.items()}
+        got = _lti_numpy.evaluate_embedded(plan, g["A_sys"][b], g["B_sys"][b], given[b], None, one, (ccx[b], ccu[b]))
+        cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
+
+
+def test_per_instance_tables_built_with_torch_equal_the_numpy_ones(cpu_extend):
+    """The GPU path evaluates the Param expressions on torch tensors (lti._Device); on the CPU
+    device the same code must give the NumPy tables bit for bit."""
+    import torch
+
+    g = cases.golden("biped_plants_n24")
+    plan = _biped_plants(g, "dP->CCC").lti_plan("LIP")
+    batch = g["A"].shape[0]
+    params = {key: g[key] for key in ("omega", "tau", "vel_x", "vel_y")}
+    host = plan.instance_tables(params, batch)
+    there = plan.instance_tables(params, batch, torch.device("cpu"))
+    assert sorted(host) == sorted(there) == ["Qxx", "cx", "tu", "tx"]
+    for key in host:
+        assert np.array_equal(host[key], there[key].numpy()), key
+    for a, b in zip(plan.coupled_tables(params, batch), plan.coupled_tables(params, batch, torch.device("cpu"))):
+        assert np.array_equal(a, b.numpy())
+
+
+def test_embedded_lowering_refuses_what_the_coupling_stage_cannot_do(cpu_extend):
+    from mpc_interface_b200.examples import biped
+
+    conf = biped.default_configuration(16)
+    form = biped.formulate_biped(conf, backend=NumpyBackend())
+    form.incorporate_goal("steps", Cost("(c-s)", Param("w_steps"), aim=[0, 0], axes=["_x", "_y"]))
+    with pytest.raises(NotImplementedError, match="per-instance weight"):
+        form.lti_plan("LIP")
+    form = biped.formulate_biped(conf, backend=NumpyBackend())
+    form.incorporate_goal("crossed", Cost("(c-s)", 1.0, cross="CoM", axes=["_x"]))
+    with pytest.raises(NotImplementedError, match="crossed"):
+        form.lti_plan("LIP")
+    form = biped.formulate_biped(conf, backend=NumpyBackend())
+    form.incorporate_definition("odd_x", LineCombo({"CoM_x": np.eye(16), "s_x": 1.0}))
+    form.incorporate_goal("odd", Cost("odd", 1.0, axes=["_x"]))
+    with pytest.raises(NotImplementedError, match="matrix coefficient"):
+        form.lti_plan("LIP")
