@@ -58,6 +58,23 @@ int mpci_extend_compact(const double* A_dev, const double* B_dev, double* Phi_de
 int mpci_extend_matrices_host(const double* A_host, const double* B_host, double* S_host,
                               double* U_host, int batch, int n, int m, int N);
 
+/* K1 without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments and results as
+ * mpci_extend_matrices, by its three-kernel path, with the intermediate (Phi, Gam) in a
+ * static device array of MPCI_EXTEND_STATIC_MAX_DOUBLES doubles (4 MiB, held by every GPU
+ * that loads the library until the process exits):
+ *     batch * N * n * (n [if S] + m [if U])  <=  MPCI_EXTEND_STATIC_MAX_DOUBLES,
+ * larger problems are refused with code -8 and a message that names both numbers.  Calls
+ * neither cudaMalloc nor cudaFree nor any other allocating routine; the caller passes every
+ * input and output.  All calls on one GPU share the array: two calls that overlap on that GPU (other
+ * streams, other host threads) race -- serialise them.  Nothing in the array needs clearing
+ * between calls (every element read was written by the same call).                         */
+#define MPCI_EXTEND_STATIC_MAX_DOUBLES 524288
+int mpci_extend_matrices_static(const double* A_dev, const double* B_dev, double* S_dev,
+                                double* U_dev, int batch, int n, int m, int N, void* stream);
+long mpci_extend_static_capacity(void); /* MPCI_EXTEND_STATIC_MAX_DOUBLES of the loaded library */
+
 /* ---- dense building blocks used while a plan is built -------------------
  * The NumPy dots of body.py:184-191 (definitions), :254-255 (L-type limits)
  * and :279-292 (cost products) for the constant coefficient matrices.

@@ -12,6 +12,7 @@
 // expansion of it remain for the plan compiler and for shapes the bulk copies do
 // not fit.
 #include <cstdint>
+#include <mutex>
 
 #include "mpci_common.cuh"
 
@@ -300,4 +301,73 @@ extern "C" int mpci_extend_matrices_host(const double* A, const double* B, doubl
     rc = mpci::cuda_fail(e, "cudaMemcpy D2H U");
   cudaFree(dA); cudaFree(dB); cudaFree(dS); cudaFree(dU);
   return rc;
+}
+
+// ---------------------------------------------------------------------------
+// K1 without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The three-kernel path above -- compact recursion into
+// (Phi, Gam), then the two expansions -- with (Phi, Gam) in a file-scope device array instead
+// of a cudaMallocAsync'd buffer.  Every GPU that loads the library holds the array until the
+// process exits; every call on a device shares it, so calls that overlap on that GPU race.
+// Nothing in it has to start at zero: the recursion writes every element the expansions read.
+// ---------------------------------------------------------------------------
+namespace {
+
+constexpr size_t kStaticScratchDoubles = MPCI_EXTEND_STATIC_MAX_DOUBLES;  // 4 MiB
+static __device__ __align__(256) double extend_static_scratch[kStaticScratchDoubles];
+
+constexpr int kMaxDevices = 64;
+std::mutex static_scratch_lock;
+double* static_scratch_addr[kMaxDevices];  // device address of the array, per device (set-up once)
+
+// The array's name is a host-side stand-in here, not a device address: the kernels get what
+// cudaGetSymbolAddress returns for the CURRENT device.
+int static_scratch(double** out) {
+  int dev = 0;
+  MPCI_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return mpci::fail(-2, "extend_matrices_static: device %d out of range", dev);
+  std::lock_guard<std::mutex> hold(static_scratch_lock);
+  if (!static_scratch_addr[dev]) {
+    double* ptr = nullptr;
+    MPCI_CUDA(cudaGetSymbolAddress((void**)&ptr, extend_static_scratch));
+    static_scratch_addr[dev] = ptr;
+  }
+  *out = static_scratch_addr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" long mpci_extend_static_capacity(void) { return (long)kStaticScratchDoubles; }
+
+extern "C" int mpci_extend_matrices_static(const double* A, const double* B, double* S, double* U,
+                                           int batch, int n, int m, int N, void* stream) {
+  if (int rc = check_sizes(batch, n, m, N)) return rc;
+  if (!A || !B) return mpci::fail(-3, "extend_matrices_static: A and B must not be NULL");
+  if (batch == 0) return 0;
+  const size_t phi_elems = S ? (size_t)batch * N * n * n : 0, gam_elems = U ? (size_t)batch * N * n * m : 0;
+  if (phi_elems + gam_elems > kStaticScratchDoubles)
+    return mpci::fail(-8, "extend_matrices_static: batch=%d n=%d m=%d N=%d needs %zu doubles of scratch, the "
+                      "static array holds %zu (use mpci_extend_matrices, or split the batch)", batch, n, m,
+                      N, phi_elems + gam_elems, kStaticScratchDoubles);
+  double* scratch = nullptr;
+  if (int rc = static_scratch(&scratch)) return rc;
+  cudaStream_t st = mpci::as_stream(stream);
+  double* Phi = scratch;
+  double* Gam = scratch + phi_elems;
+  if (int rc = launch_compact(A, B, S ? Phi : nullptr, U ? Gam : nullptr, batch, n, m, N, st)) return rc;
+  if (S) {
+    const long total = (long)phi_elems;
+    const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+    expand_S_kernel<<<blocks, 256, 0, st>>>(Phi, S, total, n);
+    MPCI_LAUNCH_CHECK("expand_S_kernel");
+  }
+  if (U) {
+    const long rows = (long)batch * m * N;
+    const int blocks = (int)(rows < 148L * 16 ? rows : 148L * 16);
+    expand_U_kernel<<<blocks, 256, 0, st>>>(Gam, U, rows, n, m, N);
+    MPCI_LAUNCH_CHECK("expand_U_kernel");
+  }
+  return 0;
 }

@@ -142,6 +142,12 @@ _SIGNATURES = {
         + [_c_double_p] * 4
         + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p],
     ),
+    "mpci_extend_matrices_static": (
+        ctypes.c_int,
+        [_c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+         ctypes.c_int, ctypes.c_void_p],
+    ),
+    "mpci_extend_static_capacity": (ctypes.c_long, []),
     "mpci_named_system": (
         ctypes.c_int,
         [ctypes.c_int, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
