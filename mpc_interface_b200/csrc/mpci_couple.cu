@@ -25,11 +25,14 @@ constexpr int kThreads = 256;
 
 struct CoupleArgs {
   int n, m, N, nz, nC, glen, nvt, nct, n_aux_rows;
+
   const int *voff, *zcol;
   const double *ccx, *ccu;  // [nC][n], [nC][m] (+ instance strides)
   long sccx, sccu;
   const double *cw, *MzT;   // [nC], [nC][nz][N]
   const unsigned char* act; // [nC][nz]: column z of Mz_c is not identically zero
+  const int *d_ptr, *d_tau; // CSR over (c, z) of the column differences Mz[tau] - Mz[tau-1]
+  const double* d_val;
   const int *e_ptr, *e_col;
   const double* e_val;
   const double *Pzz, *Gz;
@@ -42,10 +45,10 @@ struct CoupleArgs {
   long batch;
 };
 
-// shared memory (doubles): Mp, Mq [n][n] | V [N+1][n][m+1] | hs [nC][m][N] | eps, ee [nC][N]
+// shared memory (doubles): Mp, Mq [n][n] | V [N+1][n][m+1] | hs, Hs [nC][m][N] | eps, ee [nC][N]
 // | W [nz][m N] | gv [glen + 1] ; then ints: colmap [nvt] | hsact [nC m]
 __host__ __device__ inline size_t couple_doubles(int n, int m, int N, int nz, int nC, int glen) {
-  return (size_t)2 * n * n + (size_t)(N + 1) * n * (m + 1) + (size_t)nC * m * N + (size_t)2 * nC * N +
+  return (size_t)2 * n * n + (size_t)(N + 1) * n * (m + 1) + (size_t)2 * nC * m * N + (size_t)2 * nC * N +
          (size_t)nz * m * N + (size_t)glen + 1;
 }
 
@@ -57,7 +60,8 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
   double* Mq = Mp + n * n;
   double* V = Mq + n * n;                 // V[d][i][c]
   double* hs = V + (size_t)(N + 1) * n * w;  // hs[c][j][d]
-  double* eps = hs + (size_t)nC * nu;     // fr + e
+  double* Hs = hs + (size_t)nC * nu;      // running sums of hs
+  double* eps = Hs + (size_t)nC * nu;     // fr + e
   double* ee = eps + (size_t)nC * N;      // e
   double* W = ee + (size_t)nC * N;        // W[z][j N + p]
   double* gv = W + (size_t)nz * nu;       // [given; 1]
@@ -131,23 +135,35 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
     }
     __syncthreads();
     // ---- 3. W = P[u,z]^T ------------------------------------------------------------------
-    for (int e = tid; e < nz * nu; e += nthr) {
-      const int z = e / nu, r = e - z * nu, j = r / N, p = r - j * N;
-      double acc = 0.0;
-      for (int c = 0; c < nC; ++c) {
-        if (!a.act[c * nz + z] || !hsact[c * m + j]) continue;
-        const double* h_ = hs + (size_t)c * nu + j * N;
-        const double* mz = a.MzT + ((size_t)c * nz + z) * N + p;
-        double s0 = 0.0, s1 = 0.0;
-        int t = 0;
-        for (; t + 1 < N - p; t += 2) {
-          s0 = fma(h_[t], __ldg(mz + t), s0);
-          s1 = fma(h_[t + 1], __ldg(mz + t + 1), s1);
-        }
-        if (t < N - p) s0 = fma(h_[t], __ldg(mz + t), s0);
-        acc = fma(a.cw[c], s0 + s1, acc);
+    // W[z][(j,p)] = sum_c w_c sum_{k >= p} hs_c[j][k-p] Mz_c[k][z].  The columns of Mz are
+    // stored as their differences d[tau] = Mz[tau] - Mz[tau-1] (CSR; a footstep's column is a
+    // unit step: ONE entry), so with the running sums Hs[i] = hs[0] + .. + hs[i]
+    //   sum_{k>=p} hs[k-p] Mz[k] = sum_tau d[tau] (Hs[N-1-p] - Hs[max(tau,p)-p-1])
+    // costs one term per difference instead of N - p products (a dense column: the same).
+    if (a.P) {
+      for (int e = tid; e < nC * m; e += nthr) {  // running sums of every (cost, input) signal
+        double* hrow = Hs + (size_t)e * N;
+        const double* src = hs + (size_t)e * N;
+        double run = 0.0;
+        for (int t = 0; t < N; ++t) { run += src[t]; hrow[t] = run; }
       }
-      W[e] = acc;
+      __syncthreads();
+      for (int e = tid; e < nz * nu; e += nthr) {
+        const int z = e / nu, r = e - z * nu, j = r / N, p = r - j * N;
+        double acc = 0.0;
+        for (int c = 0; c < nC; ++c) {
+          if (!hsact[c * m + j]) continue;
+          const double* H = Hs + (size_t)(c * m + j) * N;
+          const double top = H[N - 1 - p];
+          double sum = 0.0;
+          for (int x = a.d_ptr[c * nz + z]; x < a.d_ptr[c * nz + z + 1]; ++x) {
+            const int lo = max(a.d_tau[x], p) - p - 1;
+            sum = fma(a.d_val[x], lo >= 0 ? top - H[lo] : top, sum);
+          }
+          acc = fma(a.cw[c], sum, acc);
+        }
+        W[e] = acc;
+      }
     }
     __syncthreads();
     // ---- 4. outputs ---------------------------------------------------------------------------
@@ -194,14 +210,14 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
       }
     }
     if (a.G) {
+      // rows without a plant part, whole rows (the fused kernel writes the rows of its groups,
+      // the auxiliary variables' columns included): zeros under the plant's inputs, constants
+      // under the auxiliary variables
       double* Gb = a.G + (size_t)b * a.nct * a.nvt;
-      for (int e = tid; e < a.nct * nz; e += nthr) {
-        const int r = e / nz, z = e - r * nz;
-        __stcs(Gb + (size_t)r * a.nvt + a.zcol[z], __ldg(a.Gz + e));
-      }
-      for (int e = tid; e < a.n_aux_rows * nu; e += nthr) {
-        const int i = e / nu, r = e - i * nu;
-        __stcs(Gb + (size_t)a.aux_rows[i] * a.nvt + a.voff[r / N] + r % N, 0.0);
+      for (int e = tid; e < a.n_aux_rows * a.nvt; e += nthr) {
+        const int i = e / a.nvt, col = e - i * a.nvt, what = colmap[col], r = a.aux_rows[i];
+        if (what == INT32_MIN) continue;
+        __stcs(Gb + (size_t)r * a.nvt + col, what >= 0 ? 0.0 : __ldg(a.Gz + r * nz + (-1 - what)));
       }
     }
     if (a.h) {
@@ -265,10 +281,22 @@ int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out
   for (int r = 0; r < nct; ++r)
     if (e->row_kind[r]) aux_rows.push_back(r);
   std::vector<unsigned char> act((size_t)std::max(1, nC * nz), 0);
+  std::vector<int> d_ptr(1, 0), d_tau;
+  std::vector<double> d_val;
   for (int c = 0; c < nC; ++c)
-    for (int z = 0; z < nz; ++z)
-      for (int k = 0; k < N; ++k)
-        if (e->cost_MzT[((size_t)c * nz + z) * N + k] != 0.0) act[(size_t)c * nz + z] = 1;
+    for (int z = 0; z < nz; ++z) {
+      const double* col = e->cost_MzT + ((size_t)c * nz + z) * N;
+      double before = 0.0;
+      for (int k = 0; k < N; ++k) {
+        if (col[k] != 0.0) act[(size_t)c * nz + z] = 1;
+        if (col[k] != before) {
+          d_tau.push_back(k);
+          d_val.push_back(col[k] - before);
+        }
+        before = col[k];
+      }
+      d_ptr.push_back((int)d_tau.size());
+    }
 
   // one allocation: doubles first, then ints, then bytes
   std::vector<double> dbl;
@@ -277,6 +305,7 @@ int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out
   auto pushi = [&](const int* p, size_t count) { const size_t o = ints.size(); if (count) ints.insert(ints.end(), p, p + count); return o; };
   const size_t o_ccx = pushd(e->cost_cx, (size_t)nC * n), o_ccu = pushd(e->cost_cu, (size_t)nC * m);
   const size_t o_cw = pushd(e->cost_w, nC), o_mz = pushd(e->cost_MzT, (size_t)nC * nz * N);
+  const size_t o_dv = pushd(d_val.data(), d_val.size());
   const size_t o_ev = pushd(e->cost_e_val, e_nnz), o_pzz = pushd(e->Pzz, (size_t)nz * nz);
   const size_t o_gz = pushd(e->Gz, (size_t)nct * nz), o_hv = pushd(e->h_val, h_nnz);
   const size_t o_voff = pushi(e->var_off, m), o_zcol = pushi(e->z_col, nz);
@@ -286,6 +315,7 @@ int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out
   const size_t o_hptr = nct ? pushi(e->h_ptr, (size_t)nct + 1) : pushi(&zero, 1);
   const size_t o_hcol = pushi(e->h_col, h_nnz), o_kind = pushi(e->row_kind, nct);
   const size_t o_aux = pushi(aux_rows.data(), aux_rows.size());
+  const size_t o_dp = pushi(d_ptr.data(), d_ptr.size()), o_dt = pushi(d_tau.data(), d_tau.size());
   const size_t bytes_d = dbl.size() * sizeof(double), bytes_i = ints.size() * sizeof(int);
 
   CouplePlan* p = new CouplePlan();
@@ -320,10 +350,17 @@ int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out
   a.voff = i + o_voff; a.zcol = i + o_zcol; a.e_ptr = i + o_eptr; a.e_col = i + o_ecol;
   a.h_ptr = i + o_hptr; a.h_col = i + o_hcol; a.row_kind = i + o_kind; a.aux_rows = i + o_aux;
   a.act = reinterpret_cast<const unsigned char*>(base + bytes_d + bytes_i);
+  a.d_ptr = i + o_dp; a.d_tau = i + o_dt; a.d_val = d + o_dv;
   p->smem_bytes = smem;
   p->blocks_per_sm = per_sm < 1 ? 1 : per_sm;
   *out = p;
   return 0;
+}
+
+void couple_limit_tables(const CouplePlan* p, const double** Gz, const int** z_col, int* nz) {
+  *Gz = p->args.Gz;
+  *z_col = p->args.zcol;
+  *nz = p->args.nz;
 }
 
 void couple_destroy(CouplePlan* p) {

@@ -12,6 +12,10 @@ struct CouplePlan;
 int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out);
 void couple_destroy(CouplePlan* p);
 
+// Device tables the fused kernel reads in the embedded layout: Gz [nc_total][nz] (the rows'
+// entries in the auxiliary variables' columns, formulation constants) and z_col [nz].
+void couple_limit_tables(const CouplePlan* p, const double** Gz, const int** z_col, int* nz);
+
 // Runs after the fused kernel on the same stream (it adds to the q and h that kernel wrote).
 // cost_cx / cost_cu: per-instance signal tables [batch][n_costs][n] / [batch][n_costs][m],
 // or nullptr for the plan's.  Any output may be nullptr.

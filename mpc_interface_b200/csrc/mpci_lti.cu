@@ -72,6 +72,11 @@ struct LtiArgs {
   int ldv, nct;
   int emb_even;  // ldv and every voff[j] even: 16-byte stores / bulk copies stay aligned
   const int* voff;
+  // the rows' constant entries under the auxiliary variables (mpci_lti_embed::Gz, z_col): written
+  // with the rows, so that every 32-byte sector of G is complete when it leaves the L2
+  const double* Gz;
+  const int* zcol;
+  int nz;
 };
 
 // Where the kernel's variables live in the QP.  EMB = false: the plant's inputs ARE the
@@ -983,6 +988,150 @@ __device__ void constraint_rows(const LtiArgs& a, const Smem& s, long b, double*
   }
 }
 
+// ---------------------------------------------------------------------------
+// phase 5, embedded layout.  The biped-sized problems that run here (N = 100, n = 6, m = 2,
+// 1 MB per instance) are latency-bound, not store-bound, so this version removes the round
+// trips of the generic one: the instance's cx / cu (staged in shared memory with the plant,
+// one DRAM round trip for everything) and the group tables (staged once per CTA) are read
+// from shared memory; groups of a row or two (the terminal box: 4 groups of ONE row) are
+// written entry by entry without windows, fences or barriers.
+// ---------------------------------------------------------------------------
+constexpr int kShortRows = 2;
+
+struct EmbStage {
+  const double *cx, *cu;  // [G][n], [G][m] of this instance (shared memory)
+  const int* tab;         // state | k0 | cnt | row0, Gs entries each (shared memory)
+  int Gs;
+  unsigned magic_2N;
+};
+__host__ __device__ inline size_t lti_emb_doubles(int n, int m, int G) {
+  const size_t Gs = G > 0 ? G : 1;
+  return (((size_t)G * (n + m) + (4 * Gs + 1) / 2) + 1) & ~(size_t)1;
+}
+
+__device__ void constraint_rows_emb(const LtiArgs& a, const Smem& s, const EmbStage& st, long b,
+                                    double* __restrict__ Gb, double* __restrict__ hb) {
+  const int n = a.n, m = a.m, N = a.N, tid = threadIdx.x, nthr = (int)blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
+  const long nv = a.ldv;
+  const int czld = 2 * N, set_doubles = 4 * m * N, gstride = (m + 1) * a.LD, nu = m * N;
+  const int *g_state = st.tab, *g_k0 = st.tab + st.Gs, *g_cnt = st.tab + 2 * st.Gs, *g_row0 = st.tab + 3 * st.Gs;
+  const bool can_bulk = Gb != nullptr && N >= 4;
+  const double* fk = s.gz + m * a.LD + a.pad + 1;  // f_k[i] = fk[i (m+1) LD + k]
+  bulk_wait_read<0>();  // whatever the previous instance left in flight has read the windows
+  __syncthreads();
+
+  // groups of one or two rows: entry by entry
+  for (int grp = 0; grp < a.n_groups; ++grp) {
+    const int cnt = g_cnt[grp];
+    if (cnt > kShortRows) continue;
+    const int k0 = g_k0[grp], row0 = g_row0[grp];
+    const bool state = (g_state[grp] & 1) != 0;
+    const double* cx = st.cx + grp * n;
+    const double* cu = st.cu + grp * m;
+    const double* arrow = a.arrow + (size_t)grp * N;
+    if (Gb) {
+      for (int e = tid; e < cnt * nu; e += nthr) {
+        const int kk = e / nu, r = e - kk * nu, j = r / N, p = r - j * N, k = k0 + kk;
+        double acc = (p == k) ? cu[j] : 0.0;
+        if (state && p <= k) {
+          const double* src = s.gz + j * a.LD + a.pad + (k - p);
+#pragma unroll 4
+          for (int i = 0; i < n; ++i) acc = fma(cx[i], src[i * gstride], acc);
+        }
+        __stcs(Gb + (size_t)(row0 + kk) * nv + a.voff[j] + p, __ldg(arrow + k) * acc);
+      }
+      for (int e = tid; e < cnt * a.nz; e += nthr) {
+        const int kk = e / a.nz, z = e - kk * a.nz;
+        __stcs(Gb + (size_t)(row0 + kk) * nv + a.zcol[z], __ldg(a.Gz + (size_t)(row0 + kk) * a.nz + z));
+      }
+    }
+    if (hb && tid < cnt) {
+      const int k = k0 + tid;
+      double acc = 0.0;
+      if (state)
+        for (int i = 0; i < n; ++i) acc = fma(cx[i], fk[i * gstride + k], acc);
+      hb[row0 + tid] = __ldg(a.bound + b * a.sbd + (size_t)grp * N + k) - __ldg(arrow + k) * acc;
+    }
+  }
+
+  int it = 0;  // window sets alternate over the groups that use them
+  for (int grp = 0; grp < a.n_groups; ++grp) {
+    const int cnt = g_cnt[grp];
+    if (cnt <= kShortRows) continue;
+    const int k0 = g_k0[grp], k1 = k0 + cnt, row0 = g_row0[grp];
+    const bool state = (g_state[grp] & 1) != 0;
+    const bool bulk = can_bulk && (g_state[grp] & 2);  // bit 1: one arrow for all rows
+    double* cz = s.cg + (it & 1) * set_doubles;  // [m][2N]
+    double* cz1 = cz + m * czld;                 // cz1[j][y] = cz[j][y + 1]
+    if (it >= 2) {  // the copies of two groups ago have read this set
+      bulk_wait_read<1>();
+      __syncthreads();
+    }
+    ++it;
+    const double* cx = st.cx + grp * n;
+    const double* cu = st.cu + grp * m;
+    const double* arrow = a.arrow + (size_t)grp * N;
+    const double scale = bulk ? __ldg(arrow + k0) : 1.0;
+    for (int e = tid; e < m * 2 * N; e += nthr) {  // y fastest
+      const int j = magic_div(e, st.magic_2N), y = e - j * 2 * N;
+      double acc = (y == N - 1) ? cu[j] : 0.0;
+      if (state && y < N) {
+        const double* src = s.gz + j * a.LD + a.pad + (N - 1 - y);
+#pragma unroll 6
+        for (int i = 0; i < n; ++i) acc = fma(cx[i], src[i * gstride], acc);
+      }
+      acc *= scale;
+      cz[j * czld + y] = acc;
+      if (y > 0) cz1[j * czld + y - 1] = acc;
+      if (y == 2 * N - 1) cz1[j * czld + y] = 0.0;
+    }
+    if (hb) {
+      const double* bound = a.bound + b * a.sbd + (size_t)grp * N;
+      double* hg = hb + row0 - k0;  // row of sample k: row0 + (k - k0)
+      for (int k = k0 + tid; k < k1; k += nthr) {
+        double acc = 0.0;
+        if (state) {
+#pragma unroll 6
+          for (int i = 0; i < n; ++i) acc = fma(cx[i], fk[i * gstride + k], acc);
+        }
+        hg[k] = __ldg(bound + k) - __ldg(arrow + k) * acc;
+      }
+    }
+    fence_async_smem();  // the windows must be visible to the async proxy
+    __syncthreads();
+    if (!Gb) continue;
+    double* rows = Gb + (size_t)row0 * nv;
+    if (bulk) {
+      // A block may start at an odd column (the biped's y block comes after N + 9 columns of
+      // x): the bulk copy takes the 16-byte aligned middle of the block -- from the copy of
+      // the window whose parity matches -- and the lane stores the odd head / tail itself.
+      const int issue_lanes = (N < 256) ? 32 : 1;
+      for (int k = k0 + warp + nwarps * lane; lane < issue_lanes && k < k1; k += nwarps * issue_lanes) {
+        const int start = N - 1 - k;
+        double* row = rows + (size_t)(k - k0) * nv;
+        for (int j = 0; j < m; ++j) {
+          double* dst = row + a.voff[j];
+          const int head = (int)((reinterpret_cast<uintptr_t>(dst) >> 3) & 1);
+          const int len = (N - head) & ~1, src0 = start + head;
+          const double* wj = cz + j * czld;
+          bulk_store(dst + head, (src0 & 1) ? cz1 + j * czld + (src0 - 1) : wj + src0, (unsigned)len * 8u);
+          if (head) __stcs(dst, wj[start]);
+          if (head + len < N) __stcs(dst + N - 1, wj[start + N - 1]);
+        }
+      }
+    } else {
+      group_rows_by_warps<true>(a, grp, cz, rows, false, warp, nwarps, lane);
+    }
+    bulk_commit();  // every thread, every group: keeps the group counts in step
+    // the rows' entries under the auxiliary variables (constants of the formulation)
+    for (int e = tid; e < cnt * a.nz; e += nthr) {
+      const int kk = e / a.nz, z = e - kk * a.nz;
+      __stcs(rows + (size_t)kk * nv + a.zcol[z], __ldg(a.Gz + (size_t)(row0 + kk) * a.nz + z));
+    }
+  }
+}
+
 // One kernel per Hessian mode: the recursion needs neither the DMMA accumulators nor
 // the zero padding, so it is compiled for more resident CTAs per SM (the phases of
 // different instances -- latency-bound prediction, store-bound P / G -- then overlap).
@@ -997,8 +1146,28 @@ lti_assemble_kernel(LtiArgs a) {
   extern __shared__ double lti_smem[];
   const Smem s = carve(lti_smem, a);
   const size_t nv = EMB ? (size_t)a.ldv : (size_t)a.m * a.N, nc = EMB ? (size_t)a.nct : (size_t)a.nc;
+  [[maybe_unused]] EmbStage stage;
+  if constexpr (EMB) {  // group tables: once per CTA (visible after the first barrier below)
+    const int Gs = a.n_groups > 0 ? a.n_groups : 1;
+    double* ecx = s.tu + a.m + 2;
+    double* ecu = ecx + a.n_groups * a.n;
+    int* etab = reinterpret_cast<int*>(ecu + a.n_groups * a.m);
+    for (int e = threadIdx.x; e < 4 * Gs; e += (int)blockDim.x) etab[e] = a.grp_state[e];
+    stage.cx = ecx; stage.cu = ecu; stage.tab = etab; stage.Gs = Gs;
+    stage.magic_2N = magic_of(2 * a.N);
+  }
+  auto limit_rows = [&](double* Gb, double* hb, long b) {
+    if constexpr (EMB) constraint_rows_emb(a, s, stage, b, Gb, hb);
+    else constraint_rows<false>(a, s, b, Gb, hb);
+  };
   for (long b = blockIdx.x; b < a.batch; b += gridDim.x) {
     __syncthreads();  // the previous instance is done with shared memory
+    if constexpr (EMB) {  // this instance's limit forms, fetched together with the plant
+      double* ecx = const_cast<double*>(stage.cx);
+      double* ecu = const_cast<double*>(stage.cu);
+      for (int e = threadIdx.x; e < a.n_groups * a.n; e += (int)blockDim.x) ecx[e] = a.cx[b * a.scx + e];
+      for (int e = threadIdx.x; e < a.n_groups * a.m; e += (int)blockDim.x) ecu[e] = a.cu[b * a.scu + e];
+    }
     if (a.n % 4 == 0) build_prediction<true>(a, s, b);
     else build_prediction<false>(a, s, b);
     // P, q and G only read the prediction data, so their order is free: every other
@@ -1014,8 +1183,7 @@ lti_assemble_kernel(LtiArgs a) {
     const bool g_first = MODE == MPCI_LTI_HESSIAN_RECURSION &&
                          (a.per_sm == 3 ? (slot % 3 != 0) : (slot & 1));
     if (limits && g_first) {
-      constraint_rows<EMB>(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
-                           a.h ? a.h + (size_t)b * nc : nullptr);
+      limit_rows(a.G ? a.G + (size_t)b * nc * nv : nullptr, a.h ? a.h + (size_t)b * nc : nullptr, b);
     }
     if (a.P && a.scan && limits) {  // aux: the windows must have been read before the T patches
       bulk_wait_read<0>();
@@ -1043,8 +1211,7 @@ lti_assemble_kernel(LtiArgs a) {
     }
     if (a.q && !adjoint) gradient<EMB>(a, s, a.q + (size_t)b * nv);
     if (limits && !g_first)
-      constraint_rows<EMB>(a, s, b, a.G ? a.G + (size_t)b * nc * nv : nullptr,
-                           a.h ? a.h + (size_t)b * nc : nullptr);
+      limit_rows(a.G ? a.G + (size_t)b * nc * nv : nullptr, a.h ? a.h + (size_t)b * nc : nullptr, b);
   }
   bulk_wait_all();  // bulk stores of the last rows
 }
@@ -1218,6 +1385,8 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
       smems[1] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[1], LDws[1], auxs[1]);
     }
   }
+  const size_t emb_bytes = emb ? sizeof(double) * lti_emb_doubles(n, m, G) : 0;  // staged limit tables
+  for (int mode = 0; mode < 2; ++mode) smems[mode] += emb_bytes;
   if (smems[MPCI_LTI_HESSIAN_RECURSION] > 227 * 1024)
     return mpci::fail(-8, "lti_plan_create: n=%d m=%d N=%d needs %zu bytes of shared memory "
                       "(limit 232448)", n, m, N, smems[MPCI_LTI_HESSIAN_RECURSION]);
@@ -1300,17 +1469,17 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
   int per_sm[2] = {0, 0}, threads[2] = {kThreads, kThreads};
   for (int mode = 0; mode < 2 && e == cudaSuccess; ++mode) {
     if (smems[mode] > 227 * 1024) continue;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm[mode], lti_kernel(mode, 0), kThreads,
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm[mode], lti_kernel(mode, 0, emb ? 1 : 0), kThreads,
                                                       smems[mode]);
     if (e != cudaSuccess || per_sm[mode] > 1) continue;
     // one CTA per SM: give it more warps if its shared memory (larger T-patch area) still fits
     size_t aux_wide = auxs[mode];  // the band scan keeps one T patch per warp
     if (mode == MPCI_LTI_HESSIAN_RECURSION && scan == 1)
       aux_wide = lti_aux_doubles(m, N, (size_t)(kWideThreads / 32) * 8 * 40);
-    const size_t wide = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], aux_wide);
+    const size_t wide = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], aux_wide) + emb_bytes;
     int fit = 0;
     if (wide <= 227 * 1024)
-      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, lti_kernel(mode, 1), kWideThreads, wide);
+      e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, lti_kernel(mode, 1, emb ? 1 : 0), kWideThreads, wide);
     if (e == cudaSuccess && fit >= 1) {
       threads[mode] = kWideThreads;
       smems[mode] = wide;
@@ -1344,6 +1513,7 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
     a.ldv = emb->nv_total;
     a.nct = emb->nc_total;
     a.voff = a.grp_state + 4 * Gs;
+    mpci::couple_limit_tables(p->couple, &a.Gz, &a.zcol, &a.nz);
     a.emb_even = (emb->nv_total % 2 == 0);
     for (int j = 0; j < m; ++j) a.emb_even = a.emb_even && (emb->var_off[j] % 2 == 0);
   }

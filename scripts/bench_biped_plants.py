@@ -16,6 +16,9 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
 
+PARTS = tuple(os.environ.get("PARTS", "P q Gh").split(" "))  # outputs timed alone ("-" = none: prediction only)
+
+
 def run(batch=16384, horizon=100, steps=10, warmup=3, system="dP->CCC"):
     import torch
 
@@ -63,7 +66,7 @@ def run(batch=16384, horizon=100, steps=10, warmup=3, system="dP->CCC"):
         line[mode] = {"ms": ms, "ms_min": ms_min, "qps": batch / ms * 1e3,
                       "hbm_gbs_all": bytes_per_qp * batch / ms / 1e6,
                       "parts_ms": {parts: timed(lambda: job.launch(out, code, parts))[0]
-                                   for parts in ("P", "q", "Gh")},
+                                   for parts in PARTS},
                       "launch": plan.launch_info(code)}
     line["with_job_build_ms"] = timed(lambda: lti.assemble(plan, A, B, given, params, out, lti.HESSIAN_RECURSION))[0]
     return line

@@ -9,6 +9,7 @@
   plan_compile_ms   Formulation.update + plan compile of ONE new structure (cold)
   generic_stream    stream_terms_generic (9-32 monomials) at 10 and 32 G terms
   k1_small_horizon  K1 at N = 24 (short rows)
+  biped_per_instance_plants   the biped at N = 100 with one plant per instance (embedded layout)
 
     python scripts/bench_extras.py
 """
@@ -212,10 +213,27 @@ def k1_extend():
     return mod.run(3)
 
 
+def biped_plants(batch=16384, N=100):
+    """The walking biped with one dP->CCC plant per instance (per-instance omega and tau): the
+    fused per-instance kernel in the embedded layout + the coupling kernel (scripts/
+    bench_biped_plants.py); recursion mode is the headline, DMMA mode beside it."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("bench_biped_plants", os.path.join(ROOT, "scripts", "bench_biped_plants.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    line = mod.run(batch=batch, horizon=N, steps=5)
+    keep = {k: line[k] for k in ("workload", "nv", "nc", "nz", "bytes_per_qp", "flush", "job_build_ms")}
+    for mode in ("recursion", "dmma"):
+        keep[mode] = {k: line[mode][k] for k in ("ms", "qps", "hbm_gbs_all", "parts_ms")}
+    keep["launches_per_call"] = 2
+    return keep
+
+
 def run():
     out = {}
     for name, fn in (("receding_tick", receding_tick), ("generic_stream", generic_stream),
-                     ("k1_extend_matrices", k1_extend)):
+                     ("k1_extend_matrices", k1_extend), ("biped_per_instance_plants", biped_plants)):
         try:
             out[name] = fn()
         except Exception as e:  # an extra must never cost the headline line

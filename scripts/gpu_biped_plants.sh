@@ -14,3 +14,20 @@ for l in open('gpurun_out/bench_lti.jsonl'):
 PY
 fi
 if [ -f scripts/bench_biped_plants.py ]; then python scripts/bench_biped_plants.py > gpurun_out/bench_biped_plants.json 2> gpurun_out/bench_biped_plants.err; echo "bench biped plants exit $?"; cat gpurun_out/bench_biped_plants.json; tail -3 gpurun_out/bench_biped_plants.err; fi
+if [[ " $* " == *" prof "* ]]; then
+  # launch list of the two kernels; bench_biped_plants launches, per mode, [all, P, q, Gh] x (3 + steps)
+  ncu --metrics gpu__time_duration.sum --clock-control none -k regex:lti_ -c 400 --csv --log-file gpurun_out/launches_biped_plants.csv python scripts/bench_biped_plants.py --steps 2 > gpurun_out/ncu_biped_plants.log 2>&1
+  python - <<'PY'
+import csv, collections
+rows = [r for r in csv.reader(open('gpurun_out/launches_biped_plants.csv')) if len(r) > 5]
+head = rows[0]; ki, vi = head.index('Kernel Name'), head.index('Metric Value')
+seq = collections.OrderedDict()
+for r in rows[1:]:
+    try: v = float(r[vi].replace(',', ''))
+    except ValueError: continue
+    seq.setdefault(r[ki][:60], []).append(v / 1e6)
+for k, v in seq.items():
+    per = 5
+    print(k, len(v), "launches;", "ms per block of %d:" % per, [round(sum(v[i:i + per]) / len(v[i:i + per]), 3) for i in range(0, len(v), per)])
+PY
+fi

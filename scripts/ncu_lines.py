@@ -23,3 +23,6 @@ total_s = sum(v[2] for v in lines.values())
 print("total instructions %d, samples %d" % (total_i, total_s))
 for no, (src, inst, samp) in sorted(lines.items(), key=lambda kv: -kv[1][1])[:top]:
     print("%5d %6.2f%% inst %6.2f%% stall | %s" % (no, 100.0 * inst / total_i, 100.0 * samp / max(1, total_s), src.strip()[:110]))
+print("-- by stall samples")
+for no, (src, inst, samp) in sorted(lines.items(), key=lambda kv: -kv[1][2])[:top]:
+    print("%5d %6.2f%% inst %6.2f%% stall | %s" % (no, 100.0 * inst / total_i, 100.0 * samp / max(1, total_s), src.strip()[:110]))
