@@ -104,3 +104,55 @@ def test_plan_desc_of_the_documentation_matches_the_header():
     doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
     block = re.search(r"class PlanDesc\(ctypes.Structure\):.*?_fields_ = \[(.*?)\]\n", doc, flags=re.S).group(1)
     assert re.findall(r'\("(\w+)", (\w)\)', block) == fields
+
+
+def _header_fields(struct_name):
+    header = open(os.path.join(ROOT, "include", "mpci.h")).read()
+    end = header.index("} %s;" % struct_name)
+    body = header[header.rindex("typedef struct {", 0, end) + len("typedef struct {"):end]
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    fields = []
+    for decl in body.split(";"):
+        decl = decl.strip()
+        if not decl:
+            continue
+        pointer = "*" in decl
+        for name in re.sub(r"^(const\s+)?(int|double)\s*\*?\s*", "", decl).split(","):
+            fields.append((name.strip().lstrip("*").strip(), "p" if pointer else "i"))
+    return fields
+
+
+@pytest.mark.parametrize("struct_name,mirror", [("mpci_lti_desc", "LtiDesc"), ("mpci_lti_tables", "LtiTables"),
+                                                ("mpci_lti_embed", "LtiEmbed")])
+def test_lti_structs_of_the_binding_match_the_header(struct_name, mirror):
+    """The ctypes mirrors in lti.py list the fields of include/mpci.h in the same order with
+    the same kinds (int / pointer): a field added on one side only would shift every later one."""
+    from mpc_interface_b200 import lti
+
+    own = [(n, "p" if t is ctypes.c_void_p else "i") for n, t in getattr(lti, mirror)._fields_]
+    assert own == _header_fields(struct_name)
+
+
+def test_embedded_plan_validation_needs_no_gpu(lib):
+    """mpci_lti_plan_create_embedded refuses NULL / overlapping layouts before any CUDA call."""
+    import numpy as np
+    from mpc_interface_b200 import lti
+
+    assert lib.mpci_lti_plan_create_embedded(None, None, None) < 0
+    n, m, N = 2, 1, 4
+    z = lambda *shape: np.zeros(shape)  # noqa: E731
+    t = dict(Qxx=z(n, n), Quu=z(m, m), Tx=z(n, 1), Tu=z(m, 1))
+    desc = lti.LtiDesc(n, m, N, 0, 0, t["Qxx"].ctypes.data, t["Quu"].ctypes.data, t["Tx"].ctypes.data,
+                       t["Tu"].ctypes.data, None, None, None, None, None, None)
+    voff, zcol = np.array([0], dtype=np.int32), np.array([2], dtype=np.int32)  # z inside the input block
+    pzz, hptr, kind = z(1, 1), np.zeros(1, dtype=np.int32), np.zeros(0, dtype=np.int32)
+    embed = lti.LtiEmbed(N + 1, 0, voff.ctypes.data, None, 1, zcol.ctypes.data, 0, 0, None, None, None, None,
+                         None, None, None, pzz.ctypes.data, None, hptr.ctypes.data, None, None, kind.ctypes.data)
+    handle = ctypes.c_void_p()
+    rc = lib.mpci_lti_plan_create_embedded(ctypes.byref(desc), ctypes.byref(embed), ctypes.byref(handle))
+    assert rc < 0 and b"not a free column" in lib.mpci_last_error()
+    rc = lib.mpci_lti_assemble_coupled(None, None, 0, None, 0, None, None, None, None, None, None, None, None,
+                                       None, None, 1, 1, None)
+    assert rc < 0 and b"NULL plan" in lib.mpci_last_error()
+    assert lib.mpci_extend_matrices_static(None, None, None, None, 1, 0, 1, 5, None) < 0
+    assert lib.mpci_extend_static_capacity() == 524288
