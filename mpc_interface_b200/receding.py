@@ -128,39 +128,75 @@ class StructureBuckets:
 
         Returns ``[(key, indices (CUDA int64 tensor), formulation, QPBatch)]``; the rows of a
         bucket's inputs are gathered on the device (no host copy of ``given``)."""
-        out = []
         on_device = hasattr(keys, "is_cuda") and keys.is_cuda
         rows, order, bounds = self._partition_device(keys) if on_device else self._partition(keys)
-        order_dev = order if on_device else None
+        groups = []
         for g in range(len(rows)):
             key = tuple(int(x) for x in rows[g])
-            count = int(bounds[g + 1] - bounds[g])
             if key not in self._forms:
                 form = self._factory()
                 form.update(**kargs_of(int(order[int(bounds[g])])))
                 self._forms[key] = form
-            form = self._forms[key]
-            ops = form._ops()
-            torch = ops.torch
-            if order_dev is None:  # ONE upload of the permutation; a bucket's indices are a slice
-                order_dev = torch.from_numpy(order).to(ops.device)
-            index = order_dev[int(bounds[g]):int(bounds[g + 1])]
-            given = torch.cat([collector[v].reshape(collector[v].shape[0], -1).index_select(0, index)
-                               for v in form.given_variables], dim=1) if form.given_variables else \
-                torch.zeros([count, 0], dtype=torch.float64, device=ops.device)
+            groups.append((key, self._forms[key], int(bounds[g]), int(bounds[g + 1])))
+        if not groups:
+            return []
+        ops = groups[0][1]._ops()
+        torch = ops.torch
+        # ONE upload of the permutation; a bucket's indices are a slice of it
+        order_dev = order if on_device else torch.from_numpy(order).to(ops.device)
+        # The permutation sorts the batch by structure.  When the structures agree on the layout
+        # of the given vector (the biped's do: only the optimisation side is ragged) the inputs
+        # are gathered ONCE for the whole batch and a bucket's rows are a contiguous slice.
+        first = groups[0][1]
+        shared = all(list(f.given_ID.items()) == list(first.given_ID.items()) for _, f, _, _ in groups)
+        given_all = scal_all = None
+        if shared and first.given_variables:
+            given_all = torch.cat([collector[v].reshape(collector[v].shape[0], -1).index_select(0, order_dev)
+                                   for v in first.given_variables], dim=1)
+        if scalars is not None:
+            scal_all = scalars.index_select(0, order_dev)
+        # The buckets are independent: their launches go round-robin over a few streams, so that
+        # the tail of one bucket's kernels overlaps the head of the next one's.
+        main = torch.cuda.current_stream()
+        streams = self._streams(torch, ops.device) if len(groups) > 1 else [main]
+        ready = torch.cuda.Event()
+        ready.record(main)
+        out = []
+        for g, (key, form, b0, b1) in enumerate(groups):
+            count = b1 - b0
+            index = order_dev[b0:b1]
             compiled = form._compiled()
-            if scalars is not None:
-                scal = scalars.index_select(0, index)
-            else:
-                idx = index.cpu().numpy() if on_device else order[int(bounds[g]):int(bounds[g + 1])]
-                sub = {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
-                scal = compiled.slots.evaluate(sub, count)
-            slot = None if outs is None else outs.get((key, count))
-            qp = ops.assemble(compiled, scal, given, count, slot)
+            side = streams[g % len(streams)]
+            if side is not main and g < len(streams):
+                side.wait_event(ready)
+            with torch.cuda.stream(side):
+                if given_all is not None:
+                    given = given_all[b0:b1]
+                elif form.given_variables:
+                    given = torch.cat([collector[v].reshape(collector[v].shape[0], -1).index_select(0, index)
+                                       for v in form.given_variables], dim=1)
+                else:
+                    given = torch.zeros([count, 0], dtype=torch.float64, device=ops.device)
+                if scal_all is not None:
+                    scal = scal_all[b0:b1]
+                else:
+                    idx = index.cpu().numpy() if on_device else order[b0:b1]
+                    sub = {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
+                    scal = compiled.slots.evaluate(sub, count)
+                slot = None if outs is None else outs.get((key, count))
+                qp = ops.assemble(compiled, scal, given, count, slot)
             if outs is not None:
                 outs[(key, count)] = qp
             out.append((key, index, form, qp))
+        for side in streams:
+            if side is not main:
+                main.wait_stream(side)
         return out
+
+    def _streams(self, torch, device, count=4):
+        if getattr(self, "_side_streams", None) is None:
+            self._side_streams = [torch.cuda.Stream(device=device) for _ in range(count)]
+        return self._side_streams
 
     def assemble(self, instance_kargs, collector, params=None, layout="dense"):
         """One tick for a batch.
