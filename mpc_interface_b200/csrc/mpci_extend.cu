@@ -182,12 +182,120 @@ extend_fused_kernel(const double* __restrict__ A, const double* __restrict__ B,
   asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
 }
 
+// ---------------------------------------------------------------------------
+// Small systems (the LIP: n = 3, m = 1).  At the reference's default horizon N = 24 the rows
+// are 576 bytes and the TMA engine takes a bulk copy every ~20 ns whatever its size: 3.5 TB/s
+// (0.53 of the copy peak, profiles/r01_tma_rate.txt).  Measured here: 4.74 TB/s (0.72) at
+// N = 24 and 5.7 TB/s (0.87, from 5.3 with bulk rows) at N = 100; taken whenever eight systems
+// fit a block's shared memory.  (The same plain stores in the block-per-system kernel gave
+// nothing at n = 12, m = 4, N = 50 or n = 6, m = 2, N = 400: 4.95 / 5.28 against 5.19 / 5.35 TB/s.)
+// Here a WARP owns a system -- no block-wide barrier anywhere: one lane per element of the
+// running block [A^(k+1) | A^k B] (n (n + m) <= 32), S collected in shared memory, and both
+// outputs leave as flat streams of 16-byte stores (U[j] is N rows of N n doubles, each a window
+// of Z_j; the rows are contiguous in memory, so the warp walks the whole of U[j] 512 bytes at
+// a time).
+// ---------------------------------------------------------------------------
+constexpr int kSmallWarps = 8;
+constexpr int kSmallMaxN = 5;  // n (n + m) <= 32 with m >= 1
+
+__host__ __device__ inline size_t small_warp_doubles(int n, int m, int N) {
+  return (size_t)m * 2 * N * n + (((size_t)N * n * n + 1) & ~(size_t)1);
+}
+
+#ifndef MPCI_SMALL_MINBLOCKS
+#define MPCI_SMALL_MINBLOCKS 4
+#endif
+__global__ void __launch_bounds__(32 * kSmallWarps, MPCI_SMALL_MINBLOCKS)
+extend_small_kernel(const double* __restrict__ A, const double* __restrict__ B, double* __restrict__ S,
+                    double* __restrict__ U, long batch, int n, int m, int N) {
+  extern __shared__ double sm[];
+  const int w = n + m, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int zld = 2 * N * n, row_len = N * n;
+  double* Z = sm + (size_t)warp * small_warp_doubles(n, m, N);  // [m][zld]
+  double* Sb = Z + (size_t)m * zld;                             // [N][n][n]
+  for (int e = lane; e < m * zld; e += 32)
+    if (e % zld >= row_len) Z[e] = 0.0;  // the zero halves, once
+  const int i = lane / w, c = lane - i * w;  // this lane's element of the running block
+  const bool mine = lane < n * w;
+  for (long b = (long)blockIdx.x * kSmallWarps + warp; b < batch; b += (long)gridDim.x * kSmallWarps) {
+    __syncwarp();  // the previous system has left shared memory
+    const double* Ab = A + b * n * n;
+    const double* Bb = B + b * n * m;
+    // the running block lives in registers, one element per lane: row i of A beside it, the
+    // column of the block through shuffles (n <= 5 here) -- the recursion touches shared memory
+    // only to park its results
+    double arow[kSmallMaxN];
+#pragma unroll
+    for (int l = 0; l < kSmallMaxN; ++l) arow[l] = (mine && l < n) ? Ab[i * n + l] : 0.0;
+    double v = mine ? ((c < n) ? Ab[i * n + c] : Bb[i * m + (c - n)]) : 0.0;
+    const int col = mine ? c : 0;
+    for (int k = 0; k < N; ++k) {
+      if (mine) {
+        if (c < n) Sb[(k * n + c) * n + i] = v;                   // S[k][c][i] = (A^(k+1))[i][c]
+        else Z[(c - n) * zld + (N - 1 - k) * n + i] = v;
+      }
+      double acc = 0.0;  // next = A @ cur  (tools.py:24-29; the last one is not used)
+#pragma unroll
+      for (int l = 0; l < kSmallMaxN; ++l) {
+        const double below = __shfl_sync(0xffffffffu, v, l * w + col);
+        if (l < n) acc += arow[l] * below;
+      }
+      v = acc;
+    }
+    __syncwarp();
+    if (S) {
+      double* Sg = S + b * (long)N * n * n;  // N n n doubles; 16-byte aligned when N n n is even
+      const int total = N * n * n;
+      if ((total & 1) == 0 && (reinterpret_cast<uintptr_t>(S) & 15) == 0) {
+        for (int e = 2 * lane; e < total; e += 64)
+          __stcs(reinterpret_cast<double2*>(Sg + e), make_double2(Sb[e], Sb[e + 1]));
+      } else {
+        for (int e = lane; e < total; e += 32) __stcs(Sg + e, Sb[e]);
+      }
+    }
+    for (int j = 0; j < m; ++j) {  // U[j]: flat index f = k row_len + e  <-  Z_j[(N-1-k) n + e]
+      double* Ug = U + (b * m + j) * (long)N * row_len;
+      const double* Zj = Z + (size_t)j * zld;
+      int e = 2 * lane, k = 0;
+      while (e >= row_len) { e -= row_len; ++k; }
+      for (; k < N;) {
+        const double* src = Zj + (N - 1 - k) * n + e;
+        __stcs(reinterpret_cast<double2*>(Ug + (long)k * row_len + e), make_double2(src[0], src[1]));
+        e += 64;
+        while (e >= row_len) { e -= row_len; ++k; }
+      }
+    }
+  }
+}
+
 // *launched stays false when the shape is not eligible (the caller then takes the
 // three-kernel path); the return value is the usual status.
 int launch_fused(const double* A, const double* B, double* S, double* U, int batch, int n, int m,
                  int N, cudaStream_t st, bool* launched) {
   *launched = false;
   if (!U || ((long)N * n) % 2 != 0 || (reinterpret_cast<uintptr_t>(U) & 15) != 0) return 0;
+  if (n * (n + m) <= 32) {  // small systems whose data fits eight to a block: a warp per system, plain stores
+    const size_t bytes = sizeof(double) * small_warp_doubles(n, m, N) * kSmallWarps;
+    if (bytes <= 96 * 1024) {
+      if (bytes > 48 * 1024)
+        MPCI_CUDA(cudaFuncSetAttribute(extend_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+      int dev = 0, sms = 148, per_sm = 1;
+      MPCI_CUDA(cudaGetDevice(&dev));
+      MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      MPCI_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, extend_small_kernel, 32 * kSmallWarps, bytes));
+#ifdef MPCI_SMALL_PER_SM
+      if (per_sm > MPCI_SMALL_PER_SM) per_sm = MPCI_SMALL_PER_SM;
+#endif
+      if (per_sm >= 1) {
+        const long want = ((long)batch + kSmallWarps - 1) / kSmallWarps, resident = (long)sms * per_sm;
+        extend_small_kernel<<<(unsigned)(want < resident ? want : resident), 32 * kSmallWarps, bytes, st>>>(
+            A, B, S, U, batch, n, m, N);
+        MPCI_LAUNCH_CHECK("extend_small_kernel");
+        *launched = true;
+        return 0;
+      }
+    }
+  }
   const bool shifted = (n % 2) != 0;
   const size_t smem = sizeof(double) * fused_smem_doubles(n, m, N, shifted);
   if (smem > 227 * 1024) return 0;

@@ -599,3 +599,44 @@ def test_large_and_small_batches_give_the_same_q_and_h(dev):
     ref = orc.all_qp_matrices(form, given[b].cpu().numpy()[:, None], one)
     assert cases.rel_err(h_large[b].cpu().numpy(), ref[1][:, 0]) <= cases.TOL
     assert cases.rel_err(q_large[b].cpu().numpy(), ref[3][:, 0]) <= cases.TOL
+
+
+@pytest.mark.parametrize("batch,n,m,N", [(1000, 3, 1, 24), (7, 3, 1, 24), (1, 2, 1, 10), (513, 4, 2, 8),
+                                         (260, 3, 1, 30), (33, 5, 1, 20), (64, 1, 1, 6)])
+def test_k1_short_rows_warp_per_system(batch, n, m, N):
+    """extend_small_kernel (a warp per system, plain 16-byte stores; rows shorter than 1 kB)
+    against the three-kernel path (mpci_extend_matrices_static: another implementation of
+    tools.py:14-33) bit for bit, and against NumPy powers on a few entries."""
+    import ctypes
+
+    import torch
+
+    from mpc_interface_b200 import device
+
+    rng = np.random.default_rng(batch + N)
+    A = np.eye(n) + 0.1 * rng.normal(size=[batch, n, n])
+    B = rng.normal(size=[batch, n, m])
+    dA, dB = torch.from_numpy(A).cuda(), torch.from_numpy(B).cuda()
+    got = {}
+    for entry in ("mpci_extend_matrices", "mpci_extend_matrices_static"):
+        S = torch.full([batch, N, n, n], float("nan"), dtype=torch.float64, device="cuda")
+        U = torch.full([batch, m, N, N, n], float("nan"), dtype=torch.float64, device="cuda")
+        stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        device.check(getattr(device.lib(), entry)(device._ptr(dA), device._ptr(dB), device._ptr(S),
+                                                  device._ptr(U), batch, n, m, N, stream))
+        torch.cuda.synchronize()
+        got[entry] = (S.cpu().numpy(), U.cpu().numpy())
+    S, U = got["mpci_extend_matrices"]
+    assert np.array_equal(S, got["mpci_extend_matrices_static"][0])
+    assert np.array_equal(U, got["mpci_extend_matrices_static"][1])
+    b = batch - 1
+    k, p = N - 1, 1
+    assert np.allclose(S[b, k], np.linalg.matrix_power(A[b], k + 1).T, rtol=1e-12, atol=1e-13)
+    assert np.allclose(U[b, m - 1, k, p], (np.linalg.matrix_power(A[b], k - p) @ B[b])[:, m - 1], rtol=1e-12, atol=1e-13)
+    assert np.all(U[b, 0, 2, 3:] == 0.0)
+    # S alone / U alone
+    Sx = torch.full([batch, N, n, n], float("nan"), dtype=torch.float64, device="cuda")
+    device.check(device.lib().mpci_extend_matrices(device._ptr(dA), device._ptr(dB), device._ptr(Sx), None,
+                                                   batch, n, m, N, None))
+    torch.cuda.synchronize()
+    assert np.array_equal(Sx.cpu().numpy(), S)
