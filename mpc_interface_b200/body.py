@@ -445,6 +445,22 @@ class Formulation:
             at += rows
         return out
 
+    def preview_rows_batched(self, given, optim, picks, params=None, scalars=None, out=None):
+        """Single samples of several variables for a batch: ``picks = [(name, row), ...]`` ->
+        CUDA tensor [B, len(picks)], column k = row ``row_k`` of ``name_k`` (``preview``,
+        body.py:209-219, restricted to the rows the receding-horizon loop reads,
+        biped_mpc_loop.py:81-88).  One launch of the sparse-row kernel over exactly those rows."""
+        picks = [(str(name), int(row)) for name, row in picks]
+        compiled = self._compiled()
+        cache = compiled.__dict__.setdefault("_previews", {})
+        key = ("rows",) + tuple(picks)
+        if key not in cache:
+            cache[key] = _plan.PreviewPlan(compiled, self._ops(), [n for n, _ in picks], [[r] for _, r in picks])
+        gz, batch = self._given_optim(given, optim)
+        if scalars is None:
+            scalars = compiled.slots.evaluate(params or {}, batch)
+        return self._ops().preview(cache[key], scalars, gz, batch, out=out)
+
     def goal_distance_batched(self, given, optim, goal_name, params=None):
         """Batched ``goal_distance`` (body.py:221-229): squared distance to the aim
         of one goal for every instance; a CUDA tensor [B]."""

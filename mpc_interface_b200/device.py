@@ -486,12 +486,15 @@ class DeviceBackend:
         P, q, G, h = (np.array(arr[a:a + n]) for a, n in zip(starts[1:], sizes[1:]))
         return G.reshape(nc, nv), h.reshape(nc, 1), P.reshape(nv, nv), q.reshape(nv, 1)
 
-    def preview(self, pplan, scalars, given_optim, batch):
-        """Rows of a PreviewPlan for a batch: [batch, total rows] (device tensor)."""
+    def preview(self, pplan, scalars, given_optim, batch, out=None):
+        """Rows of a PreviewPlan for a batch: [batch, total rows] (device tensor; written
+        into ``out`` when given -- a contiguous [batch, total rows] CUDA tensor)."""
         torch = self.torch
         dp = self.device_plan(pplan)
         scalars = self._to_device(scalars)
-        values = torch.empty([batch, pplan.nv], dtype=torch.float64, device=self.device)
+        if out is not None and (tuple(out.shape) != (batch, pplan.nv) or not out.is_contiguous()):
+            raise ValueError("out must be a contiguous [{}, {}] tensor".format(batch, pplan.nv))
+        values = torch.empty([batch, pplan.nv], dtype=torch.float64, device=self.device) if out is None else out
         null = ctypes.c_void_p(0)
         check(lib().mpci_assemble(dp.handle, _ptr(scalars), _ptr(given_optim), null, _ptr(values),
                                   null, null, batch, _stream_ptr()))

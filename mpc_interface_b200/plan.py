@@ -407,11 +407,17 @@ class PreviewPlan:
     ``value = sum_m c_m(s_b) * D_m @ [given_b; optim_b; 1]`` (Formulation.preview,
     body.py:209-219).  Shares the scalar slots of the assembly plan it is cut from."""
 
-    def __init__(self, compiled, ops, names):
+    def __init__(self, compiled, ops, names, picks=None):
+        """``picks``: per name, the rows of that variable to keep (a list), or None for all --
+        the receding-horizon loop needs ONE sample of every state (biped_mpc_loop.py:81-88)."""
         polys = [compiled.PM[name] for name in names]
         width = compiled.ng + compiled.nv
         self.names = list(names)
-        self.rows = [p.rows for p in polys]
+        picks = [None] * len(polys) if picks is None else list(picks)
+        for p, rows in zip(polys, picks):
+            if rows is not None and not all(0 <= r < p.rows for r in rows):
+                raise IndexError("a picked row is outside the variable's {} rows".format(p.rows))
+        self.rows = [p.rows if rows is None else len(rows) for p, rows in zip(polys, picks)]
         self.nv, self.ng, self.nc = sum(self.rows), width, 0  # the kernel's view of the sizes
         self.slots = compiled.slots
         monos = []
@@ -428,10 +434,11 @@ class PreviewPlan:
         self.DP = self.DG = None
         DY = np.zeros([len(monos), self.nv, width + 1])
         row0 = 0
-        for p in polys:
+        for p, rows, count in zip(polys, picks, self.rows):
             for mono, H in p.terms.items():
-                DY[monos.index(mono), row0 : row0 + p.rows, :width] = ops.download(H)
-            row0 += p.rows
+                block = ops.download(H)
+                DY[monos.index(mono), row0 : row0 + count, :width] = block if rows is None else block[list(rows)]
+            row0 += count
         self.DY = DY
         self.Y_segs, self.Y_val, self.Y_col = _scan_qh_rows(DY)
 

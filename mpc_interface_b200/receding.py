@@ -191,6 +191,89 @@ class StructureBuckets:
         for side in streams:
             if side is not main:
                 main.wait_stream(side)
+        # what advance_device needs again: the batch in structure order
+        self._last = dict(order=order_dev, given=given_all, scalars=scal_all,
+                          bounds=[(b0, b1) for _, _, b0, b1 in groups], done=out)
+        return out
+
+    def advance_device(self, done, optims, take, collector, scalars=None, params=None):
+        """The example loop's ``update_given_collector`` (biped_mpc_loop.py:81-88) for the whole
+        batch of the last ``assemble_device`` tick: the initial states of the next tick are
+        single samples of the previewed states.
+
+        done      : what ``assemble_device`` returned
+        optims    : per bucket of ``done``, the optimum [count, optim_len] (CUDA tensors, rows in
+                    the bucket's order -- the order of its QPBatch)
+        take      : {dynamics name: horizon row} as in ``advance_collector``
+        collector : {given variable: CUDA tensor [B, size]}, batch order
+
+        Per bucket ONE launch over exactly the rows that are read (``preview_rows_batched``: 8
+        rows for the biped instead of the 800 of the full previews), on the inputs the tick
+        gathered in structure order; the results go back to batch order with one
+        ``index_copy_`` per given variable.  Returns the new collector (fresh tensors; entries
+        that are not produced here are copied through)."""
+        last = getattr(self, "_last", None)
+        if last is None or last["done"] is not done or last["given"] is None:
+            return self._advance_by_bucket(done, optims, take, collector, scalars, params)
+        ops = done[0][2]._ops()
+        torch = ops.torch
+        order, given_all, scal_all = last["order"], last["given"], last["scalars"]
+        if scal_all is None and scalars is not None:
+            scal_all = scalars.index_select(0, order)
+        batch = given_all.shape[0]
+        first = done[0][2]
+        picks = _state_picks(first, take)
+        sampled = torch.empty([batch, len(picks)], dtype=torch.float64, device=ops.device)
+        main = torch.cuda.current_stream()
+        streams = self._streams(torch, ops.device) if len(done) > 1 else [main]
+        ready = torch.cuda.Event()
+        ready.record(main)
+        for g, ((key, index, form, _qp), (b0, b1)) in enumerate(zip(done, last["bounds"])):
+            side = streams[g % len(streams)]
+            if side is not main and g < len(streams):
+                side.wait_event(ready)
+            with torch.cuda.stream(side):
+                if scal_all is not None:
+                    scal, sub = scal_all[b0:b1], None
+                else:
+                    idx = index.cpu().numpy()
+                    scal, sub = None, {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
+                form.preview_rows_batched(given_all[b0:b1], optims[g], [(s_, r) for s_, _, _, r in picks],
+                                          params=sub, scalars=scal, out=sampled[b0:b1])
+        for side in streams:
+            if side is not main:
+                main.wait_stream(side)
+        out = {name: ops._to_device(value).reshape(batch, -1).clone() for name, value in collector.items()}
+        by_variable = {}
+        for k, (_state, variable, ident, _row) in enumerate(picks):
+            by_variable.setdefault(variable, []).append((ident, k))
+        for variable, pairs in by_variable.items():
+            ids = first.given_ID[variable]
+            fresh = given_all[:, ids.start:ids.stop].clone()  # structure order
+            fresh[:, [i for i, _ in pairs]] = sampled[:, [k for _, k in pairs]]
+            if variable not in out:
+                out[variable] = torch.empty_like(fresh)
+            out[variable].index_copy_(0, order, fresh)
+        return out
+
+    def _advance_by_bucket(self, done, optims, take, collector, scalars, params):
+        """``advance_device`` without the sorted inputs of the tick: one ``advance_collector``
+        per bucket, scattered back."""
+        ops = done[0][2]._ops()
+        torch = ops.torch
+        batch = sum(int(index.shape[0]) for _, index, _, _ in done)
+        out = {name: ops._to_device(value).reshape(batch, -1).clone() for name, value in collector.items()}
+        for (key, index, form, _qp), optim in zip(done, optims):
+            given = torch.cat([out[v].index_select(0, index) for v in form.given_variables], dim=1)
+            sub = scalars.index_select(0, index) if scalars is not None else None
+            sub_params = None if sub is not None else {k: np.asarray(v)[index.cpu().numpy()]
+                                                       for k, v in (params or {}).items()}
+            moved = advance_collector(form, given, optim, take, sub_params,
+                                      {k: v.index_select(0, index) for k, v in out.items()}, scalars=sub)
+            for name, value in moved.items():
+                if name not in out:
+                    out[name] = torch.zeros([batch, value.shape[1]], dtype=torch.float64, device=ops.device)
+                out[name].index_copy_(0, index, value)
         return out
 
     def _streams(self, torch, device, count=4):
@@ -216,6 +299,18 @@ class StructureBuckets:
             sub = {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
             out.append((k, idx, form, form.generate_all_qp_matrices_batched(given, sub, layout=layout)))
         return out
+
+
+def _state_picks(form, take):
+    """[(state, given variable, entry of that variable, horizon row)] for ``take``."""
+    picks = []
+    for name, row in take.items():
+        dyn = form.dynamics[name]
+        for state, ident in dyn.state_ID.items():
+            if not 0 <= row < dyn.all_variables[state]:
+                raise IndexError("row {} is outside the horizon of {}".format(row, state))
+            picks.append((state, dyn.state_vector_name + "0" + state[-2:], ident, row))
+    return picks
 
 
 def count_steps(step_times, step_count, step_samples):

@@ -114,17 +114,16 @@ def receding_tick(batch=65536, N=100):
     dev_ms = _events(torch, assemble_tick, 3)
 
     # the rest of the loop (no solve: the optimum is stood in for by zeros)
+    done = assemble_tick()  # (advance_device works on the inputs of the LAST tick)
+    torch.cuda.synchronize()
+    optims = [torch.zeros([index.shape[0], form.optim_len], dtype=torch.float64, device="cuda")
+              for _, index, form, _ in done]
+
     def rest():
-        for key, index, form, qp in done:
-            n = index.shape[0]
-            given = torch.cat([collector[v].index_select(0, index) for v in form.given_variables], dim=1)
-            optim = torch.zeros([n, form.optim_len], dtype=torch.float64, device="cuda")
-            sub = scalars.index_select(0, index) if scalars is not None else None
-            sub_params = None if sub is not None else {k: v[index.cpu().numpy()] for k, v in params.items()}
-            sub_collector = {k: v.index_select(0, index) for k, v in collector.items()}
-            receding.advance_collector(form, given, optim, {"LIP": 0, "steps": 1}, sub_params, sub_collector,
-                                       scalars=sub)
+        moved = buckets.advance_device(done, optims, {"LIP": 0, "steps": 1}, collector, scalars=scalars,
+                                       params=None if scalars is not None else params)
         receding.count_steps(times, count, conf.step_samples)
+        return moved
 
     rest()
     torch.cuda.synchronize()
@@ -146,7 +145,8 @@ def receding_tick(batch=65536, N=100):
             "note": "warm tick = structure keys + grouping on the device (torch.unique over packed key "
                     "rows) + per structure: device gather of the given rows, "
                     "mpci_assemble into a reused slot (all 65,536 instances, 24 structures); "
-                    "rest_of_loop = preview of the states + advance_collector per structure + count_steps "
+                    "rest_of_loop = StructureBuckets.advance_device (per structure one launch over the 8 sampled "
+                    "state rows on the tick's sorted inputs, one scatter per given variable) + count_steps "
                     "(biped_mpc_loop.py:41-45, 62-65, 81-92), the solve itself left out"}
 
 

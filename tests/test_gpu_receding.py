@@ -173,3 +173,59 @@ def test_device_tick_equals_the_per_instance_grouping():
     again = b.assemble_device(structure_keys(N, times, count), lambda i: kargs[i], collector,
                               params=params, outs=outs)
     assert {k: v.P.data_ptr() for k, v in outs.items()} == slots and len(again) == len(got)
+
+
+@pytest.mark.parametrize("N,batch", [(24, 333), (100, 97)])
+def test_advance_device_equals_advance_collector_per_bucket(N, batch):
+    """StructureBuckets.advance_device (one launch per bucket over the 8 sampled rows, on the
+    inputs the tick gathered in structure order, one scatter per variable) against
+    advance_collector bucket by bucket (full previews) -- and so against the oracle's preview
+    matrices, which test_preview_all_and_advance_collector pins."""
+    import torch
+    from mpc_interface_b200 import Param, receding
+    from mpc_interface_b200.examples import synthetic
+    from mpc_interface_b200.examples.biped import default_configuration, formulate_biped, structure_key, structure_keys
+
+    conf = default_configuration(N)
+
+    def factory():
+        return formulate_biped(conf, omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")])
+
+    n_steps = factory().domain["Ds_x"]
+    ticks = _tick_sequence(3 * conf.step_samples, conf.step_samples, n_steps)
+    phase = np.random.default_rng(2).integers(0, len(ticks), size=batch)
+    times = np.stack([ticks[t][0] for t in phase])
+    count = np.array([ticks[t][1] for t in phase])
+    vals = synthetic.biped_inputs(6, batch, N)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    collector = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in vals.items() if k not in params}
+    buckets = receding.StructureBuckets(factory, structure_key(N))
+    keys = structure_keys(N, times, count)
+    done = buckets.assemble_device(keys, lambda i: dict(step_times=times[i], step_count=count[i]), collector,
+                                   params=params)
+    plan0 = done[0][2]._compiled()
+    scalars = torch.from_numpy(plan0.slots.evaluate(params, batch)).cuda()
+    done = buckets.assemble_device(keys, None, collector, scalars=scalars)  # warm, shared scalar slots
+    rng = np.random.default_rng(3)
+    optims = [torch.from_numpy(rng.normal(size=[int(idx.shape[0]), form.optim_len]) * 0.1).cuda()
+              for _, idx, form, _ in done]
+    take = {"LIP": 0, "steps": 1}
+    got = buckets.advance_device(done, optims, take, collector, scalars=scalars)
+    want = buckets._advance_by_bucket(done, optims, take, collector, scalars, None)
+    assert sorted(got) == sorted(want) == sorted(collector)
+    moved = 0
+    for name in want:
+        a, b = got[name].cpu().numpy(), want[name].cpu().numpy()
+        assert a.shape == b.shape
+        assert np.abs(a - b).max() <= cases.TOL * max(1.0, np.abs(b).max()), name
+        moved += int(np.any(b != collector[name].cpu().numpy().reshape(b.shape)))
+        assert got[name].data_ptr() != collector[name].data_ptr()  # fresh tensors
+    assert moved >= 4  # x0_x, x0_y, s0_x, s0_y changed; the bias passes through
+    assert np.array_equal(got["n_x"].cpu().numpy(), vals["n_x"])
+    # a stale `done` (not the last tick's) takes the per-bucket route and agrees as well
+    stale = list(done)
+    again = buckets.advance_device(stale, optims, take, collector, scalars=scalars)
+    for name in want:
+        assert torch.allclose(again[name], want[name], rtol=0, atol=1e-12)
+    with pytest.raises(IndexError):
+        buckets.advance_device(done, optims, {"LIP": N}, collector, scalars=scalars)
