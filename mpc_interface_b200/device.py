@@ -209,7 +209,10 @@ def _torch():
 
 
 def _stream_ptr():
-    return ctypes.c_void_p(_torch().cuda.current_stream().cuda_stream)
+    # (torch._C._cuda_getCurrentRawStream: what torch.cuda.current_stream() wraps, without
+    # building a Stream object -- a plan compile asks ~200 times)
+    torch = _torch()
+    return ctypes.c_void_p(torch._C._cuda_getCurrentRawStream(torch.cuda.current_device()))
 
 
 def _ptr(tensor):
@@ -368,6 +371,20 @@ class DeviceBackend:
         return H.cpu().numpy()
 
     download3 = download
+
+    def scan_rows(self, DY):
+        """plan._scan_qh_rows on the device: the sparse rows (segs, val, col) of the stacked
+        constants DY [K, rows, cols] -- which entries are non-zero is found where they live,
+        only those (about 1 % for the biped) are downloaded."""
+        from . import plan as _plan
+
+        by_row = DY.permute(1, 0, 2)  # entries ordered by (row, term, column)
+        mask = by_row != 0
+        where = mask.nonzero()
+        val = by_row[mask].cpu().numpy().astype(np.float64)
+        col = where[:, 2].to(self.torch.int32).cpu().numpy()
+        counts = mask.sum(dim=2).cpu().numpy()
+        return _plan._segments(counts, DY.shape[0]), val, col
 
     def rows(self, H, index):
         index = list(index)

@@ -380,6 +380,17 @@ def _cost_into(form, ops, PM, slots, cost, Pacc, Yacc):
                 )
 
 
+def _segments(counts, K):
+    """(row, term, nz_begin, nz_end) of the non-empty (row, term) pairs; counts int [rows, K]."""
+    rows = counts.shape[0]
+    flat = counts.reshape(-1)
+    ends = np.cumsum(flat)
+    begins = ends - flat
+    keep = flat > 0
+    rr, tt = np.divmod(np.arange(rows * K), K)
+    return np.stack([rr[keep], tt[keep], begins[keep], ends[keep]], axis=1).astype(np.int32).reshape([-1, 4])
+
+
 def _scan_qh_rows(DY):
     """Sparse rows of the stacked DY constants for the [q; h] kernel.
 
@@ -560,7 +571,9 @@ def compile_plan(form, ops, costs=None, limits=None):
     plan.G_terms, plan.DG = finish(Gacc, "G")
     plan.Y_terms, plan.DY = finish(Yacc, "Y")
     plan.monomials = [m for m, _ in sorted(table.items(), key=lambda kv: kv[1])]
-    plan.Y_segs, plan.Y_val, plan.Y_col = _scan_qh_rows(ops.download3(plan.DY))
+    # (structural scan where the constants live: only the non-zeros come back to the host)
+    plan.Y_segs, plan.Y_val, plan.Y_col = (ops.scan_rows(plan.DY) if hasattr(ops, "scan_rows")
+                                           else _scan_qh_rows(ops.download3(plan.DY)))
 
     plan.nv, plan.ng, plan.nc = nv, ng, nc
     plan.slots = slots
