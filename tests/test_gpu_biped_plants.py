@@ -151,3 +151,46 @@ def test_biped_with_per_instance_plants_against_the_committed_golden(name, syste
         got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
         for b in range(batch):
             cases.assert_qp_close(tuple(x[b] for x in got), (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
+
+
+def test_biped_plants_large_batch_properties_and_samples():
+    """8,192 robots at N = 100 in one call (9.4 GB of matrices): instances with equal inputs get
+    bitwise equal matrices wherever they sit in the batch (the persistent CTAs walk the batch
+    in strides), P is symmetric, the rows of the stepping area do not depend on the instance,
+    and sampled instances match the live reference."""
+    import torch
+
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    N, batch, system = 100, 8192, "dP->CCC"
+    seed = int.from_bytes(os.urandom(4), "little")
+    vals = _inputs(seed, batch, N)
+    twins = [(0, 4097), (17, 8191), (1000, 1001)]
+    for a, b in twins:
+        for k in vals:
+            vals[k][b] = vals[k][a]
+    conf = _conf(N, system)
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    out = form.generate_all_qp_matrices_batched(
+        given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")},
+        dynamics={"LIP": (system, vals["tau"], vals["omega"])}, hessian="recursion")
+    torch.cuda.synchronize()
+    for a, b in twins:
+        for x in (out.P, out.q, out.G, out.h):
+            assert torch.equal(x[a], x[b]), "seed {} twins {} {}".format(seed, a, b)
+    asym = (out.P - out.P.transpose(1, 2)).abs().amax()
+    assert float(asym) <= 1e-10 * float(out.P.abs().amax())
+    k = form.domain["Ds_x"]
+    area = out.G[:, :4 * k, :]  # the stepping area: constants of the formulation
+    assert torch.equal(area, area[:1].expand_as(area))
+    assert bool(torch.isfinite(out.h).all()) and bool(torch.isfinite(out.q).all())
+    for b in (0, 4097, 2048, 8191):
+        one, want = _reference_instance(conf, vals, b)
+        got = tuple(x[b].cpu().numpy() for x in (out.G, out.h, out.P, out.q))
+        try:
+            cases.assert_qp_close(got, want)
+        except AssertionError as e:
+            raise AssertionError("seed {} instance {}: {}".format(seed, b, e))
