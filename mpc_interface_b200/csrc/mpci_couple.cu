@@ -1,15 +1,16 @@
 // Coupling stage of an embedded per-instance plan (include/mpci.h: mpci_lti_embed).
 //
 // The fused kernel of mpci_lti.cu writes everything of one instance's QP that involves only
-// the plant.  What involves the auxiliary optimisation variables z (the biped's footstep
-// displacements Ds) or the auxiliary given variables (s0, the bias n) is written here, one
-// CTA per instance:
+// the plant, ALL of P (the blocks that involve the auxiliary variables included: it has the
+// prediction in shared memory and writes whole 32-byte sectors while the rows are in the L2)
+// and the rows of G that have a plant part.  What is left of q, G, h -- the parts that involve
+// the auxiliary optimisation variables z (the biped's footstep displacements Ds) or the
+// auxiliary given variables (s0, the bias n) -- is written here, one CTA per instance:
 //   1. V_d = A^d [B | x0], d = 0..N, by prefix doubling (plain FP64 FMAs: n <= a dozen)
 //   2. per coupled cost c: hs_c[j][d] = cx_c . Gam_d[:,j] (+ cu_c[j] at d = 0),
 //      fr_c[k] = cx_c . A^{k+1} x0,  e_c = E_c [given; 1]
-//   3. W[z][(j,p)] = sum_c w_c sum_{k>=p} hs_c[j][k-p] Mz_c[k][z]       (= P[u,z]^T)
-//   4. P[z,:], P[:,z], q[z], q[u] +=, G[:,z], the plant columns of rows without a plant part,
-//      h (+)= Hg [given; 1]
+//   3. q[z] = sum_c w_c Mz_c[:,z] . (fr_c + e_c),  q[u] += sum_c w_c T_c^T e_c,  the rows of G
+//      without a plant part (whole rows),  h (+)= Hg [given; 1]
 // Reference: generate_qp_cost / generate_qp_constraint (python/mpc_interface/body.py:236-302)
 // on preview matrices whose optimisation block is [T_c | Mz_c] and whose given block is
 // [S_c | Mg_c] (make_preview_matrices, body.py:149-193).
@@ -41,15 +42,15 @@ struct CoupleArgs {
   const int *row_kind, *aux_rows;
   const double *A, *B, *x0, *given;
   long sA, sB;
-  double *P, *q, *G, *h;
+  double *q, *G, *h;
   long batch;
 };
 
-// shared memory (doubles): Mp, Mq [n][n] | V [N+1][n][m+1] | hs, Hs [nC][m][N] | eps, ee [nC][N]
-// | W [nz][m N] | gv [glen + 1] ; then ints: colmap [nvt] | hsact [nC m]
+// shared memory (doubles): Mp, Mq [n][n] | V [N+1][n][m+1] | hs [nC][m][N] | eps, ee [nC][N]
+// | gv [glen + 1] ; then ints: colmap [nvt] | hsact [nC m]
 __host__ __device__ inline size_t couple_doubles(int n, int m, int N, int nz, int nC, int glen) {
-  return (size_t)2 * n * n + (size_t)(N + 1) * n * (m + 1) + (size_t)2 * nC * m * N + (size_t)2 * nC * N +
-         (size_t)nz * m * N + (size_t)glen + 1;
+  return (size_t)2 * n * n + (size_t)(N + 1) * n * (m + 1) + (size_t)nC * m * N + (size_t)2 * nC * N +
+         (size_t)glen + 1;
 }
 
 __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
@@ -60,11 +61,9 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
   double* Mq = Mp + n * n;
   double* V = Mq + n * n;                 // V[d][i][c]
   double* hs = V + (size_t)(N + 1) * n * w;  // hs[c][j][d]
-  double* Hs = hs + (size_t)nC * nu;      // running sums of hs
-  double* eps = Hs + (size_t)nC * nu;     // fr + e
+  double* eps = hs + (size_t)nC * nu;     // fr + e
   double* ee = eps + (size_t)nC * N;      // e
-  double* W = ee + (size_t)nC * N;        // W[z][j N + p]
-  double* gv = W + (size_t)nz * nu;       // [given; 1]
+  double* gv = ee + (size_t)nC * N;       // [given; 1]
   int* colmap = reinterpret_cast<int*>(gv + a.glen + 1);
   int* hsact = colmap + a.nvt;
 
@@ -134,52 +133,7 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
       }
     }
     __syncthreads();
-    // ---- 3. W = P[u,z]^T ------------------------------------------------------------------
-    // W[z][(j,p)] = sum_c w_c sum_{k >= p} hs_c[j][k-p] Mz_c[k][z].  The columns of Mz are
-    // stored as their differences d[tau] = Mz[tau] - Mz[tau-1] (CSR; a footstep's column is a
-    // unit step: ONE entry), so with the running sums Hs[i] = hs[0] + .. + hs[i]
-    //   sum_{k>=p} hs[k-p] Mz[k] = sum_tau d[tau] (Hs[N-1-p] - Hs[max(tau,p)-p-1])
-    // costs one term per difference instead of N - p products (a dense column: the same).
-    if (a.P) {
-      for (int e = tid; e < nC * m; e += nthr) {  // running sums of every (cost, input) signal
-        double* hrow = Hs + (size_t)e * N;
-        const double* src = hs + (size_t)e * N;
-        double run = 0.0;
-        for (int t = 0; t < N; ++t) { run += src[t]; hrow[t] = run; }
-      }
-      __syncthreads();
-      for (int e = tid; e < nz * nu; e += nthr) {
-        const int z = e / nu, r = e - z * nu, j = r / N, p = r - j * N;
-        double acc = 0.0;
-        for (int c = 0; c < nC; ++c) {
-          if (!hsact[c * m + j]) continue;
-          const double* H = Hs + (size_t)(c * m + j) * N;
-          const double top = H[N - 1 - p];
-          double sum = 0.0;
-          for (int x = a.d_ptr[c * nz + z]; x < a.d_ptr[c * nz + z + 1]; ++x) {
-            const int lo = max(a.d_tau[x], p) - p - 1;
-            sum = fma(a.d_val[x], lo >= 0 ? top - H[lo] : top, sum);
-          }
-          acc = fma(a.cw[c], sum, acc);
-        }
-        W[e] = acc;
-      }
-    }
-    __syncthreads();
     // ---- 4. outputs ---------------------------------------------------------------------------
-    if (a.P) {
-      double* Pb = a.P + (size_t)b * a.nvt * a.nvt;
-      for (int e = tid; e < nz * a.nvt; e += nthr) {  // the rows of z: whole rows, coalesced
-        const int z = e / a.nvt, col = e - z * a.nvt, what = colmap[col];
-        if (what == INT32_MIN) continue;
-        __stcs(Pb + (size_t)a.zcol[z] * a.nvt + col,
-               what >= 0 ? W[(size_t)z * nu + what] : __ldg(a.Pzz + z * nz + (-1 - what)));
-      }
-      for (int e = tid; e < nu * nz; e += nthr) {  // the columns of z in the plant's rows
-        const int r = e / nz, z = e - r * nz, j = r / N, p = r - j * N;
-        __stcs(Pb + (size_t)(a.voff[j] + p) * a.nvt + a.zcol[z], W[(size_t)z * nu + r]);
-      }
-    }
     if (a.q) {
       double* qb = a.q + (size_t)b * a.nvt;
       for (int z = warp; z < nz; z += nwarps) {  // q[z] = sum_c w_c Mz_c[:,z] . (fr_c + e_c)
@@ -357,10 +311,11 @@ int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out
   return 0;
 }
 
-void couple_limit_tables(const CouplePlan* p, const double** Gz, const int** z_col, int* nz) {
-  *Gz = p->args.Gz;
-  *z_col = p->args.zcol;
-  *nz = p->args.nz;
+void couple_share(const CouplePlan* p, CoupleShare* out) {
+  const CoupleArgs& a = p->args;
+  out->Gz = a.Gz; out->Pzz = a.Pzz; out->cost_cx = a.ccx; out->cost_cu = a.ccu; out->cost_w = a.cw;
+  out->d_val = a.d_val; out->z_col = a.zcol; out->d_ptr = a.d_ptr; out->d_tau = a.d_tau;
+  out->nz = a.nz; out->n_costs = a.nC;
 }
 
 void couple_destroy(CouplePlan* p) {
@@ -371,15 +326,15 @@ void couple_destroy(CouplePlan* p) {
 
 int couple_launch(const CouplePlan* p, const double* A, long strideA, const double* B, long strideB,
                   const double* x0, const double* given, const double* cost_cx, const double* cost_cu,
-                  double* P, double* q, double* G, double* h, long batch, cudaStream_t stream) {
-  if (batch == 0) return 0;
+                  double* q, double* G, double* h, long batch, cudaStream_t stream) {
+  if (batch == 0 || (!q && !G && !h)) return 0;
   CoupleArgs a = p->args;
   if (a.glen && !given) return fail(-3, "lti_assemble_coupled: NULL given");
   a.A = A; a.B = B; a.x0 = x0; a.given = given; a.sA = strideA; a.sB = strideB;
   a.sccx = a.sccu = 0;
   if (cost_cx) { a.ccx = cost_cx; a.sccx = (long)a.nC * a.n; }
   if (cost_cu) { a.ccu = cost_cu; a.sccu = (long)a.nC * a.m; }
-  a.P = P; a.q = q; a.G = G; a.h = h; a.batch = batch;
+  a.q = q; a.G = G; a.h = h; a.batch = batch;
   int dev = 0, sms = 148;
   MPCI_CUDA(cudaGetDevice(&dev));
   MPCI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

@@ -12,15 +12,23 @@ struct CouplePlan;
 int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out);
 void couple_destroy(CouplePlan* p);
 
-// Device tables the fused kernel reads in the embedded layout: Gz [nc_total][nz] (the rows'
-// entries in the auxiliary variables' columns, formulation constants) and z_col [nz].
-void couple_limit_tables(const CouplePlan* p, const double** Gz, const int** z_col, int* nz);
+// Device tables the fused kernel reads in the embedded layout (formulation constants): Gz
+// [nc_total][nz] (the rows' entries under the auxiliary variables' columns), z_col [nz], and what
+// it needs for the blocks of P that involve the auxiliary variables -- the coupled costs' plant
+// forms cost_cx [nC][n] / cost_cu [nC][m] and weights, the columns of their Mz as CSR differences
+// (d_ptr over (cost, z); d_tau, d_val), Pzz [nz][nz].
+struct CoupleShare {
+  const double *Gz, *Pzz, *cost_cx, *cost_cu, *cost_w, *d_val;
+  const int *z_col, *d_ptr, *d_tau;
+  int nz, n_costs;
+};
+void couple_share(const CouplePlan* p, CoupleShare* out);
 
-// Runs after the fused kernel on the same stream (it adds to the q and h that kernel wrote).
-// cost_cx / cost_cu: per-instance signal tables [batch][n_costs][n] / [batch][n_costs][m],
-// or nullptr for the plan's.  Any output may be nullptr.
+// Runs after the fused kernel on the same stream (it adds to the q and h that kernel wrote; all
+// of P is the fused kernel's).  cost_cx / cost_cu: per-instance signal tables
+// [batch][n_costs][n] / [batch][n_costs][m], or nullptr for the plan's.  Any output may be nullptr.
 int couple_launch(const CouplePlan* p, const double* A, long strideA, const double* B, long strideB,
                   const double* x0, const double* given, const double* cost_cx, const double* cost_cu,
-                  double* P, double* q, double* G, double* h, long batch, cudaStream_t stream);
+                  double* q, double* G, double* h, long batch, cudaStream_t stream);
 
 }  // namespace mpci

@@ -77,6 +77,13 @@ struct LtiArgs {
   const double* Gz;
   const int* zcol;
   int nz;
+  // the blocks of P that involve the auxiliary variables (coupled_hessian_emb): the coupled
+  // costs' plant forms (instance strides sccx / sccu, 0 = the plan's), weights, the columns of
+  // their Mz as CSR differences over (cost, z), and the constant block Pzz
+  int nC;
+  const double *ccx, *ccu, *ccw, *d_val, *Pzz;
+  long sccx, sccu;
+  const int *d_ptr, *d_tau;
 };
 
 // Where the kernel's variables live in the QP.  EMB = false: the plant's inputs ARE the
@@ -1132,6 +1139,88 @@ __device__ void constraint_rows_emb(const LtiArgs& a, const Smem& s, const EmbSt
   }
 }
 
+// ---------------------------------------------------------------------------
+// phase 3e, embedded layout: the blocks of P that involve the auxiliary variables z.
+//   P[u,z] = sum_c w_c T_c^T Mz_c  (and its transpose P[z,u]),   P[z,z] = Pzz
+// with T_c the Toeplitz operator of cost c's plant signal hs_c[j][d] = cx_c . Gam_d[:,j]
+// (+ cu_c[j] at d = 0).  The columns of Mz are stored as their differences d[tau] = Mz[tau] -
+// Mz[tau-1] (CSR; a footstep's column is a unit step: ONE entry), so with the running sums
+// Hs[i] = hs[0] + .. + hs[i]
+//   sum_{k>=p} hs[k-p] Mz[k][z] = sum_tau d[tau] (Hs[N-1-p] - Hs[max(tau,p)-p-1]):
+// one term per difference instead of N - p products.  Written here, next to the plant blocks
+// of the same rows, so that every 32-byte sector of P is complete when it leaves the L2 (a
+// second kernel filling the 72-byte gaps later cost a DRAM read-modify-write per gap).
+// hs / Hs live in the aux region (free between the Hessian scan and the constraint rows).
+// ---------------------------------------------------------------------------
+__device__ void coupled_hessian_emb(const LtiArgs& a, const Smem& s, long b, double* __restrict__ Pb) {
+  const int n = a.n, m = a.m, N = a.N, nz = a.nz, nC = a.nC, nu = a.m * a.N;
+  const int tid = threadIdx.x, nthr = (int)blockDim.x, gstride = (m + 1) * a.LD;
+  const long nv = a.ldv;
+  double* hs = s.cg;                  // [nC][m][N]
+  double* Hs = hs + (size_t)nC * nu;  // running sums
+  bulk_wait_read<0>();  // (row windows of this CTA still being read by the TMA engine)
+  __syncthreads();      // the T patches / windows in aux are done with
+  for (int e = tid; e < nC * nu; e += nthr) {
+    const int c = e / nu, r = e - c * nu, j = r / N, d = r - j * N;
+    const double* cx = a.ccx + b * a.sccx + (size_t)c * n;
+    double acc = (d == 0) ? a.ccu[b * a.sccu + (size_t)c * m + j] : 0.0;
+    const double* src = s.gz + j * a.LD + a.pad + d;
+    for (int i = 0; i < n; ++i) acc = fma(__ldg(cx + i), src[i * gstride], acc);
+    hs[e] = acc;
+  }
+  __syncthreads();
+  {  // running sums of every (cost, input) signal: a warp per signal, shuffle scan in chunks of 32
+    const int lane = tid & 31, warp = tid >> 5, nwarps = nthr >> 5;
+    for (int e = warp; e < nC * m; e += nwarps) {
+      const double* src = hs + (size_t)e * N;
+      double* dst = Hs + (size_t)e * N;
+      double carry = 0.0;
+      for (int t0 = 0; t0 < N; t0 += 32) {
+        double v = (t0 + lane < N) ? src[t0 + lane] : 0.0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const double up = __shfl_up_sync(0xffffffffu, v, o);
+          if (lane >= o) v += up;
+        }
+        v += carry;
+        if (t0 + lane < N) dst[t0 + lane] = v;
+        carry = __shfl_sync(0xffffffffu, v, 31);
+      }
+    }
+  }
+  __syncthreads();
+  auto entry = [&](int z, int j, int p) {
+    double acc = 0.0;
+    for (int c = 0; c < nC; ++c) {
+      const double* H = Hs + (size_t)(c * m + j) * N;
+      const double top = H[N - 1 - p];
+      double sum = 0.0;
+      for (int x = a.d_ptr[c * nz + z]; x < a.d_ptr[c * nz + z + 1]; ++x) {
+        const int lo = max(a.d_tau[x], p) - p - 1;
+        sum = fma(a.d_val[x], lo >= 0 ? top - H[lo] : top, sum);
+      }
+      acc = fma(a.ccw[c], sum, acc);
+    }
+    return acc;
+  };
+  // the rows of z (consecutive p: coalesced), then the columns of z in the plant's rows with z
+  // fastest (the auxiliary columns come in runs: 72-byte pieces instead of single doubles);
+  // the entry is cheap enough to be computed once per store
+  for (int e = tid; e < nz * nu; e += nthr) {
+    const int z = e / nu, r = e - z * nu, j = r / N, p = r - j * N;
+    __stcs(Pb + (long)a.zcol[z] * nv + a.voff[j] + p, entry(z, j, p));
+  }
+  for (int e = tid; e < nz * nu; e += nthr) {
+    const int r = e / nz, z = e - r * nz, j = r / N, p = r - j * N;
+    __stcs(Pb + (long)(a.voff[j] + p) * nv + a.zcol[z], entry(z, j, p));
+  }
+  for (int e = tid; e < nz * nz; e += nthr) {
+    const int z = e / nz, y = e - z * nz;
+    __stcs(Pb + (long)a.zcol[z] * nv + a.zcol[y], __ldg(a.Pzz + e));
+  }
+  __syncthreads();  // aux is free again
+}
+
 // One kernel per Hessian mode: the recursion needs neither the DMMA accumulators nor
 // the zero padding, so it is compiled for more resident CTAs per SM (the phases of
 // different instances -- latency-bound prediction, store-bound P / G -- then overlap).
@@ -1208,6 +1297,9 @@ lti_assemble_kernel(LtiArgs a) {
       else if (a.m == 3) hessian_recursion<3, EMB>(a, s, Pb);
       else if (a.m == 4) hessian_recursion<4, EMB>(a, s, Pb);
       else hessian_recursion_any<EMB>(a, s, Pb);
+      if constexpr (EMB) {
+        if (a.nz > 0) coupled_hessian_emb(a, s, b, Pb);
+      }
     }
     if (a.q && !adjoint) gradient<EMB>(a, s, a.q + (size_t)b * nv);
     if (limits && !g_first)
@@ -1513,7 +1605,12 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
     a.ldv = emb->nv_total;
     a.nct = emb->nc_total;
     a.voff = a.grp_state + 4 * Gs;
-    mpci::couple_limit_tables(p->couple, &a.Gz, &a.zcol, &a.nz);
+    mpci::CoupleShare sh;
+    mpci::couple_share(p->couple, &sh);
+    a.Gz = sh.Gz; a.zcol = sh.z_col; a.nz = sh.nz;
+    a.nC = sh.n_costs; a.ccx = sh.cost_cx; a.ccu = sh.cost_cu; a.ccw = sh.cost_w;
+    a.d_ptr = sh.d_ptr; a.d_tau = sh.d_tau; a.d_val = sh.d_val; a.Pzz = sh.Pzz;
+    a.sccx = a.sccu = 0;
     a.emb_even = (emb->nv_total % 2 == 0);
     for (int j = 0; j < m; ++j) a.emb_even = a.emb_even && (emb->var_off[j] % 2 == 0);
   }
@@ -1529,6 +1626,13 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
     p->smem_bytes[mode] = smems[mode];
     p->blocks_per_sm[mode] = per_sm[mode] < 1 ? 1 : per_sm[mode];
   }
+  if (emb)  // coupled_hessian_emb keeps 2 n_costs m N doubles in the aux region
+    for (int mode = 0; mode < 2; ++mode)
+      if ((size_t)2 * a.nC * m * N > (size_t)p->aux[mode]) {
+        mpci_lti_plan_destroy(p);
+        return mpci::fail(-8, "lti_plan_create_embedded: %d coupled costs need %zu doubles of work space, the "
+                          "plan has %d", a.nC, (size_t)2 * a.nC * m * N, p->aux[mode]);
+      }
   *out = p;
   return 0;
 }
@@ -1581,7 +1685,8 @@ extern "C" int mpci_lti_plan_info(const mpci_lti_plan* p, int mode, long info[6]
 static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, const double* B,
                       long strideB, const double* x0, const double* scalars,
                       const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
-                      long batch, int mode, void* stream, bool coupled = false);
+                      long batch, int mode, void* stream, bool coupled = false,
+                      const double* cost_cx = nullptr, const double* cost_cu = nullptr);
 
 extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long strideA,
                                  const double* B, long strideB, const double* x0,
@@ -1611,16 +1716,18 @@ extern "C" int mpci_lti_assemble_coupled(const mpci_lti_plan* p, const double* A
     return mpci::fail(-1, "lti_assemble_coupled: the plan was not created by mpci_lti_plan_create_embedded");
   if (tab && (tab->tx || tab->tu) && p->S != 0)
     return mpci::fail(-1, "lti_assemble_coupled: per-instance tx / tu need a plan with n_scalars = 0");
-  int rc = lti_launch(p, A, strideA, B, strideB, x0, scalars, tab, P, q, G, h, batch, mode, stream, true);
+  int rc = lti_launch(p, A, strideA, B, strideB, x0, scalars, tab, P, q, G, h, batch, mode, stream, true,
+                      cost_cx, cost_cu);
   if (rc) return rc;
-  return mpci::couple_launch(p->couple, A, strideA, B, strideB, x0, given, cost_cx, cost_cu, P, q, G, h,
+  return mpci::couple_launch(p->couple, A, strideA, B, strideB, x0, given, cost_cx, cost_cu, q, G, h,
                              batch, mpci::as_stream(stream));
 }
 
 static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, const double* B,
                       long strideB, const double* x0, const double* scalars,
                       const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
-                      long batch, int mode, void* stream, bool coupled) {
+                      long batch, int mode, void* stream, bool coupled, const double* cost_cx,
+                      const double* cost_cu) {
   if (!p) return mpci::fail(-3, "lti_assemble: NULL plan");
   if (p->embedded && !coupled)
     return mpci::fail(-1, "lti_assemble: a plan with the embedded layout runs through mpci_lti_assemble_coupled");
@@ -1643,6 +1750,8 @@ static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, con
   a.A = A; a.B = B; a.x0 = x0; a.scalars = scalars; a.strideA = strideA; a.strideB = strideB;
   a.P = P; a.q = q; a.G = G; a.h = h; a.batch = batch; a.hessian_mode = mode;
   a.sQ = a.sR = a.sTx = a.sTu = a.scx = a.scu = a.sbd = 0;
+  if (cost_cx) { a.ccx = cost_cx; a.sccx = (long)a.nC * p->n; }
+  if (cost_cu) { a.ccu = cost_cu; a.sccu = (long)a.nC * p->m; }
   if (tab) {  // per-instance tables replace the plan's
     const long n = p->n, m = p->m, Gn = p->n_groups, N = p->N;
     if (tab->Qxx) { a.Qxx = tab->Qxx; a.sQ = n * n; }
