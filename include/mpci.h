@@ -300,8 +300,9 @@ int mpci_lti_assemble_ex(const mpci_lti_plan* plan, const double* A_dev, long st
  * (`(b+n-s)`, `(DCM-s)`: LineCombos with the matrix coefficient of biped_formulation.py:57,63
  * folded into Mz / Mg on the host).  Everything that involves only the plant is written by
  * the fused kernel at its place in the larger matrices (the embedded layout below); the
- * blocks that involve z or the auxiliary givens are written by a second kernel
- * (csrc/mpci_couple.cu) from per-instance signals and formulation constants:
+ * blocks that involve z or the auxiliary givens come from per-instance signals and formulation
+ * constants -- those of P in a phase of the fused kernel, those of q, G, h in a second kernel
+ * (csrc/mpci_couple.cu):
  *   P[u,z] = sum_c w_c T_c^T Mz_c  (and its transpose),   P[z,z] = sum_c w_c Mz_c^T Mz_c
  *   q[u]  += sum_c w_c T_c^T e_c,   q[z] = sum_c w_c Mz_c^T (fr_c + e_c)
  *   G[r,z] = Gz[r,z],   h[r] (+)= Hg[r,:] . [given; 1]
