@@ -191,6 +191,19 @@ int mpci_assemble_compact_host(mpci_plan* plan, const double* scalars_host,
                                const double* given_host, double* Pc_host, double* q_host,
                                double* Gc_host, double* h_host, long batch, long chunk);
 
+/* Box bounds for solvers that take lb <= z <= ub beside G z <= h (qpsolvers' `lb`, `ub`; the
+ * reference's example passes everything as rows of A, biped_mpc_loop.py:57-60).  The rows of G
+ * that bound ONE variable with a coefficient that does not depend on the instance (the stepping
+ * area and every `Box` / `Constraint` on an optimisation variable itself, restrictions.py:175-199)
+ * are found once per plan on the host; per instance only h differs:
+ *   for x in col_ptr[c] .. col_ptr[c+1]:  a = coef[x], v = h[b][row[x]] / a;
+ *        a > 0: ub[b][c] = min(ub, v)      a < 0: lb[b][c] = max(lb, v)
+ * h_dev [batch][ld_h]; col_ptr_dev [nv+1], row_dev / coef_dev [col_ptr[nv]] (device);
+ * lb_dev / ub_dev [batch][nv], -inf / +inf where a variable has no such row.                */
+int mpci_box_bounds(const double* h_dev, long ld_h, int nv, const int* col_ptr_dev,
+                    const int* row_dev, const double* coef_dev, double* lb_dev, double* ub_dev,
+                    long batch, void* stream);
+
 int mpci_assemble_compact_host_stream(mpci_plan* plan, const double* scalars_host,
                                       const double* given_host, double* Pc_ring, double* q_ring,
                                       double* Gc_ring, double* h_ring, long batch, long chunk,

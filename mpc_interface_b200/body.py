@@ -461,6 +461,22 @@ class Formulation:
             scalars = compiled.slots.evaluate(params or {}, batch)
         return self._ops().preview(cache[key], scalars, gz, batch, out=out)
 
+    def box_rows(self):
+        """``plan.BoxRows`` of the compiled formulation (cached with the plan)."""
+        compiled = self._compiled()
+        if "_box_rows" not in compiled.__dict__:
+            compiled._box_rows = _plan.BoxRows(compiled, self._ops())
+        return compiled._box_rows
+
+    def box_bounds_batched(self, qp):
+        """``(lb, ub, rest)`` for a batch assembled by ``generate_all_qp_matrices_batched``
+        (dense or CSC layout): CUDA tensors ``lb, ub [B, nv]`` (-inf / +inf where a variable
+        has no bound row) from the rows of G that bound one variable each, and ``rest``, the
+        int32 indices of the rows that remain general constraints -- ``G[:, rest] z <= h[:, rest]``
+        with ``lb <= z <= ub`` is the same feasible set as ``G z <= h``."""
+        box = self.box_rows()
+        return self._ops().box_bounds(box, qp.h, self.optim_len) + (box.rest,)
+
     def goal_distance_batched(self, given, optim, goal_name, params=None):
         """Batched ``goal_distance`` (body.py:221-229): squared distance to the aim
         of one goal for every instance; a CUDA tensor [B]."""

@@ -4,6 +4,8 @@
 //   * mpci_axpy2d -- dst += alpha * rowscale * src with row broadcasting
 // They stand where the reference calls NumPy dots: body.py:184-191 (derived
 // definitions), :254-255 (limits with L) and :279-292 (V^T C cost products).
+#include <cmath>
+
 #include "mpci_common.cuh"
 
 namespace {
@@ -139,6 +141,40 @@ extern "C" int mpci_goal_distance(const double* V, const double* aim, long aim_s
   goal_distance_kernel<<<(unsigned)((batch + 7) / 8), 256, 0, mpci::as_stream(stream)>>>(
       V, aim, aim_stride, rows, n_axes, out, batch);
   MPCI_LAUNCH_CHECK("goal_distance_kernel");
+  return 0;
+}
+
+namespace {
+// lb / ub of the variables from the rows of G that bound ONE variable with a coefficient that
+// is the same for every instance: thread (b, c) walks the rows of column c.
+__global__ void __launch_bounds__(256)
+box_bounds_kernel(const double* __restrict__ h, long ld_h, int nv, const int* __restrict__ col_ptr,
+                  const int* __restrict__ row, const double* __restrict__ coef,
+                  double* __restrict__ lb, double* __restrict__ ub, long batch) {
+  const long e = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= batch * nv) return;
+  const long b = e / nv;
+  const int c = (int)(e - b * nv);
+  double lo = -INFINITY, hi = INFINITY;
+  for (int x = col_ptr[c]; x < col_ptr[c + 1]; ++x) {
+    const double a = coef[x], v = h[b * ld_h + row[x]] / a;  // a z_c <= h
+    if (a > 0.0) hi = fmin(hi, v);
+    else lo = fmax(lo, v);
+  }
+  lb[e] = lo;
+  ub[e] = hi;
+}
+}  // namespace
+
+extern "C" int mpci_box_bounds(const double* h, long ld_h, int nv, const int* col_ptr, const int* row,
+                               const double* coef, double* lb, double* ub, long batch, void* stream) {
+  if (nv < 0 || batch < 0 || ld_h < 0) return mpci::fail(-1, "box_bounds: negative size");
+  if (batch == 0 || nv == 0) return 0;
+  if (!h || !col_ptr || !lb || !ub) return mpci::fail(-3, "box_bounds: NULL pointer");
+  const long total = batch * nv;
+  box_bounds_kernel<<<(unsigned)((total + 255) / 256), 256, 0, mpci::as_stream(stream)>>>(
+      h, ld_h, nv, col_ptr, row, coef, lb, ub, batch);
+  MPCI_LAUNCH_CHECK("box_bounds_kernel");
   return 0;
 }
 

@@ -102,6 +102,11 @@ _SIGNATURES = {
         [_c_double_p, _c_double_p, ctypes.c_long, ctypes.c_int, ctypes.c_int, _c_double_p,
          ctypes.c_long, ctypes.c_void_p],
     ),
+    "mpci_box_bounds": (
+        ctypes.c_int,
+        [_c_double_p, ctypes.c_long, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, _c_double_p,
+         _c_double_p, _c_double_p, ctypes.c_long, ctypes.c_void_p],
+    ),
     "mpci_plan_set_compact": (
         ctypes.c_int, [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long]),
     "mpci_assemble_compact": (
@@ -516,6 +521,22 @@ class DeviceBackend:
         check(lib().mpci_assemble(dp.handle, _ptr(scalars), _ptr(given_optim), null, _ptr(values),
                                   null, null, batch, _stream_ptr()))
         return values
+
+    def box_bounds(self, box, h, nv):
+        """mpci_box_bounds for a ``plan.BoxRows`` and the h of a batch ([B, nc] CUDA tensor)."""
+        torch = self.torch
+        if box._device is None:
+            box._device = (torch.from_numpy(box.col_ptr).to(self.device), torch.from_numpy(box.row).to(self.device),
+                           torch.from_numpy(box.coef).to(self.device))
+        col_ptr, row, coef = box._device
+        batch = h.shape[0]
+        h = h.contiguous()
+        lb = torch.empty([batch, nv], dtype=torch.float64, device=self.device)
+        ub = torch.empty([batch, nv], dtype=torch.float64, device=self.device)
+        check(lib().mpci_box_bounds(_ptr(h), h.shape[1], nv, ctypes.c_void_p(col_ptr.data_ptr()),
+                                    ctypes.c_void_p(row.data_ptr()), _ptr(coef), _ptr(lb), _ptr(ub), batch,
+                                    _stream_ptr()))
+        return lb, ub
 
     def goal_distance(self, values, aims, rows, n_axes):
         """values [batch, n_axes * rows], aims [batch, n_axes] or [1, n_axes] -> [batch]."""

@@ -494,6 +494,44 @@ def csc_patterns(plan, ops, upper_P=False):
     return pP, pG, cP, cG
 
 
+class BoxRows:
+    """The rows of G that bound ONE optimisation variable with a coefficient that does not
+    depend on the instance -- ``a * z_c <= h_r`` -- for solvers that take ``lb <= z <= ub``
+    beside ``G z <= h`` (qpsolvers' ``lb`` / ``ub``).  Structural, like
+    the CSC patterns: a row qualifies when, over ALL constant matrices of the plan, it has one
+    non-zero column, and that entry lives in the constant term only.
+
+    rows   : int32, the qualifying rows of G (ascending)
+    rest   : int32, the other rows (what stays in ``G z <= h``)
+    col_ptr, row, coef : CSR over the variables: variable c is bounded by the rows
+             ``row[col_ptr[c]:col_ptr[c+1]]`` with the coefficients ``coef[...]``"""
+
+    def __init__(self, plan, ops):
+        nc, nv = plan.nc, plan.nv
+        self.rows = np.zeros([0], dtype=np.int32)
+        rows, cols, coefs = [], [], []
+        if plan.DG is not None and nc:
+            DG = ops.download3(plan.DG)  # [K, nc, nv]
+            const = [t for t, mono in enumerate(plan.G_terms) if plan.monomials[mono] == ()]
+            mask = DG != 0.0
+            single = mask.any(axis=0).sum(axis=1) == 1
+            varying = np.zeros([nc], dtype=bool)
+            for t in range(DG.shape[0]):
+                if t not in const:
+                    varying |= mask[t].any(axis=1)
+            for r in np.nonzero(single & ~varying)[0]:
+                c = int(np.nonzero(mask[:, r, :].any(axis=0))[0][0])
+                rows.append(int(r)), cols.append(c), coefs.append(float(sum(DG[t, r, c] for t in const)))
+        order = np.argsort(np.asarray(cols, dtype=np.int64), kind="stable")
+        self.rows = np.asarray(rows, dtype=np.int32)
+        self.rest = np.setdiff1d(np.arange(nc, dtype=np.int32), self.rows).astype(np.int32)
+        self.row = self.rows[order].astype(np.int32)
+        self.coef = np.asarray(coefs, dtype=np.float64)[order]
+        counts = np.bincount(np.asarray(cols, dtype=np.int64), minlength=nv) if cols else np.zeros([nv], dtype=np.int64)
+        self.col_ptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+        self._device = None
+
+
 def compile_plan(form, ops, costs=None, limits=None):
     """Builds the AffinePlan of ``form`` with backend ``ops``.
 

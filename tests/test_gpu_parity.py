@@ -640,3 +640,41 @@ def test_k1_short_rows_warp_per_system(batch, n, m, N):
                                                    batch, n, m, N, None))
     torch.cuda.synchronize()
     assert np.array_equal(Sx.cpu().numpy(), S)
+
+
+@pytest.mark.parametrize("name,layout", [("biped_n24_batch", "dense"), ("biped_n100_batch", "csc")])
+def test_box_bounds_batched_against_the_reference_matrices(name, layout):
+    """lb / ub extraction: for every instance the bounds equal what the
+    single-entry rows of the REFERENCE's A and h say, and the remaining rows are the
+    reference's other rows -- together the same feasible set as A z <= h."""
+    from mpc_interface_b200 import Param
+
+    g = cases.golden(name)
+    N, batch = int(g["N"]), g["A"].shape[0]
+    form = cases.formulate_biped(cases.default_configuration(N), omega=Param("omega"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    qp = form.generate_all_qp_matrices_batched(g["given"], {k: g[k] for k in ("omega", "vel_x", "vel_y")},
+                                               layout=layout)
+    lb, ub, rest = form.box_bounds_batched(qp)
+    lb, ub = lb.cpu().numpy(), ub.cpu().numpy()
+    nv = form.optim_len
+    assert lb.shape == ub.shape == (batch, nv)
+    for b in range(batch):
+        A, h = g["A"][b], g["h"][b]
+        want_lb, want_ub, general = np.full(nv, -np.inf), np.full(nv, np.inf), []
+        for r in range(A.shape[0]):
+            nz = np.nonzero(A[r])[0]
+            if len(nz) == 1 and r < 4 * form.domain["Ds_x"]:
+                v = h[r] / A[r, nz[0]]
+                if A[r, nz[0]] > 0:
+                    want_ub[nz[0]] = min(want_ub[nz[0]], v)
+                else:
+                    want_lb[nz[0]] = max(want_lb[nz[0]], v)
+            else:
+                general.append(r)
+        assert list(rest) == general
+        finite = np.isfinite(want_lb)
+        assert np.array_equal(np.isfinite(lb[b]), finite) and np.array_equal(np.isfinite(ub[b]), np.isfinite(want_ub))
+        assert np.abs(lb[b][finite] - want_lb[finite]).max() <= cases.TOL * np.abs(want_lb[finite]).max()
+        assert np.abs(ub[b][finite] - want_ub[finite]).max() <= cases.TOL * np.abs(want_ub[finite]).max()
+        assert np.all(lb[b][finite] <= ub[b][finite])

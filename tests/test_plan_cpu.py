@@ -280,3 +280,23 @@ def test_plan_cache_is_keyed_on_content(cpu_extend):
     for k in range(50):
         form.generate_qp_constraint(Constraint("b", 10.0 + k), given)
     assert len(form._plans) <= 32
+
+
+def test_box_rows_of_the_biped_are_the_stepping_area(cpu_extend):
+    """plan.BoxRows (lb / ub extraction): at the biped the rows that bound
+    one variable with an instance-independent coefficient are exactly the stepping area's
+    (Box on Ds itself: 4 rows per step); the support polygon and the terminal box mix
+    variables and carry omega."""
+    from mpc_interface_b200 import Param, plan as _plan
+
+    g = cases.golden("biped_n24_batch")
+    form = cases.formulate_biped(cases.default_configuration(24), omega=Param("omega"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")], backend=NumpyBackend())
+    box = _plan.BoxRows(form._compiled(), form._ops())
+    k = form.domain["Ds_x"]
+    assert list(box.rows) == list(range(4 * k)) and list(box.rest) == list(range(4 * k, form._compiled().nc))
+    A = g["A"][0]  # the reference's G: those rows have ONE non-zero, the value BoxRows reports
+    for r, c, a in zip(box.row, np.repeat(np.arange(form.optim_len), np.diff(box.col_ptr)), box.coef):
+        assert np.count_nonzero(A[r]) == 1 and A[r, c] == a
+    assert box.col_ptr[-1] == 4 * k and set(np.nonzero(np.diff(box.col_ptr))[0]) == \
+        set(form.optim_ID["Ds_x"]) | set(form.optim_ID["Ds_y"])
