@@ -194,3 +194,45 @@ def test_biped_plants_large_batch_properties_and_samples():
             cases.assert_qp_close(got, want)
         except AssertionError as e:
             raise AssertionError("seed {} instance {}: {}".format(seed, b, e))
+
+
+def test_embedded_plan_without_auxiliary_variables():
+    """Edge of the embedded layout: the footsteps GIVEN instead of optimised (nz = 0: no
+    auxiliary columns, only auxiliary givens -- s0, Ds, the bias); the stepping area then has
+    no optimisation part at all (zero rows of G, h from the given steps)."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    N, batch, system = 24, 5, "dP->CCC"
+    seed = int.from_bytes(os.urandom(4), "little")
+    vals = _inputs(seed, batch, N)
+    conf = _conf(N, system)
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    drive = ["cCoP_dot_x", "cCoP_dot_y"]
+    form.identify_qp_domain(drive)
+    form.make_preview_matrices()
+    rng = np.random.default_rng(seed)
+    for ax in ("_x", "_y"):
+        vals["Ds" + ax] = rng.normal(size=[batch, form.domain["Ds" + ax]]) * 0.05
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and plan.nz == 0 and plan.nv == 2 * N
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")},
+            dynamics={"LIP": (system, vals["tau"], vals["omega"])}, hessian=mode)
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        for b in range(batch):
+            one = biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                        target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])],
+                                        api=reference.load())
+            one.identify_qp_domain(drive)
+            one.make_preview_matrices()
+            assert list(one.given_ID.items()) == list(form.given_ID.items())
+            want = one.generate_all_qp_matrices(one.arrange_given(
+                {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
+            try:
+                cases.assert_qp_close(tuple(x[b] for x in got), want)
+            except AssertionError as e:
+                raise AssertionError("seed {} instance {} ({}): {}".format(seed, b, mode, e))
