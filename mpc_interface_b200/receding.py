@@ -112,7 +112,8 @@ class StructureBuckets:
         return [(tuple(int(x) for x in rows[g]), order[bounds[g]:bounds[g + 1]])
                 for g in range(len(rows))]
 
-    def assemble_device(self, keys, kargs_of, collector, scalars=None, params=None, outs=None):
+    def assemble_device(self, keys, kargs_of, collector, scalars=None, params=None, outs=None,
+                        dynamics=None, hessian="recursion"):
         """One tick for a batch whose inputs live on the GPU (a receding-horizon stream: the
         collector of tick t+1 is produced on the device by ``advance_collector``).
 
@@ -125,6 +126,11 @@ class StructureBuckets:
                     structure; or ``scalars``: a CUDA tensor [B, n_slots] already evaluated
                     in the slot order the structures share (``slots_of``)
         outs      : optional dict reused across ticks: {(key, count): QPBatch} ring slots
+        dynamics  : ``{name: (A [B, n, n], B [B, n, m])}`` CUDA tensors (or numpy): one plant per
+                    robot for the dynamics ``name`` (``generate_all_qp_matrices_batched(...,
+                    dynamics=...)`` per bucket: fused per-instance kernel, embedded layout when
+                    the structure has other variables); ``params`` then holds the per-instance
+                    ``Param`` values ([B] arrays or CUDA tensors), ``hessian`` picks the mode
 
         Returns ``[(key, indices (CUDA int64 tensor), formulation, QPBatch)]``; the rows of a
         bucket's inputs are gathered on the device (no host copy of ``given``)."""
@@ -155,6 +161,19 @@ class StructureBuckets:
                                    for v in first.given_variables], dim=1)
         if scalars is not None:
             scal_all = scalars.index_select(0, order_dev)
+        plant = None
+        if dynamics is not None:
+            from . import lti
+
+            if len(dynamics) != 1:
+                raise NotImplementedError("exactly one dynamics can vary per instance")
+            (plant_name, (A_b, B_b)), = dynamics.items()
+            to_dev = lambda x: x if torch.is_tensor(x) else torch.from_numpy(  # noqa: E731
+                np.require(x, dtype=np.float64, requirements=["C", "W"])).to(ops.device)
+            plant = (plant_name, to_dev(A_b).index_select(0, order_dev), to_dev(B_b).index_select(0, order_dev),
+                     {k: to_dev(np.asarray(v) if not torch.is_tensor(v) else v).reshape(-1).index_select(0, order_dev)
+                      for k, v in (params or {}).items()},
+                     {"dmma": lti.HESSIAN_DMMA, "recursion": lti.HESSIAN_RECURSION}[hessian])
         # The buckets are independent: their launches go round-robin over a few streams, so that
         # the tail of one bucket's kernels overlaps the head of the next one's.
         main = torch.cuda.current_stream()
@@ -165,7 +184,6 @@ class StructureBuckets:
         for g, (key, form, b0, b1) in enumerate(groups):
             count = b1 - b0
             index = order_dev[b0:b1]
-            compiled = form._compiled()
             side = streams[g % len(streams)]
             if side is not main and g < len(streams):
                 side.wait_event(ready)
@@ -177,14 +195,21 @@ class StructureBuckets:
                                        for v in form.given_variables], dim=1)
                 else:
                     given = torch.zeros([count, 0], dtype=torch.float64, device=ops.device)
-                if scal_all is not None:
-                    scal = scal_all[b0:b1]
-                else:
-                    idx = index.cpu().numpy() if on_device else order[b0:b1]
-                    sub = {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
-                    scal = compiled.slots.evaluate(sub, count)
                 slot = None if outs is None else outs.get((key, count))
-                qp = ops.assemble(compiled, scal, given, count, slot)
+                if plant is not None:  # one plant per robot: the bucket through the fused kernel
+                    plant_name, A_all, B_all, par_all, mode = plant
+                    job = lti.LtiJob(form.lti_plan(plant_name), A_all[b0:b1], B_all[b0:b1], given,
+                                     {k: v[b0:b1] for k, v in par_all.items()})
+                    qp = job.launch(slot, mode)
+                else:
+                    compiled = form._compiled()
+                    if scal_all is not None:
+                        scal = scal_all[b0:b1]
+                    else:
+                        idx = index.cpu().numpy() if on_device else order[b0:b1]
+                        sub = {name: np.asarray(v)[idx] for name, v in (params or {}).items()}
+                        scal = compiled.slots.evaluate(sub, count)
+                    qp = ops.assemble(compiled, scal, given, count, slot)
             if outs is not None:
                 outs[(key, count)] = qp
             out.append((key, index, form, qp))

@@ -236,3 +236,52 @@ def test_embedded_plan_without_auxiliary_variables():
                 cases.assert_qp_close(tuple(x[b] for x in got), want)
             except AssertionError as e:
                 raise AssertionError("seed {} instance {} ({}): {}".format(seed, b, mode, e))
+
+
+def test_receding_tick_with_per_instance_plants():
+    """StructureBuckets.assemble_device(..., dynamics=...): robots at different walking phases
+    (different QP sizes) AND with one plant each -- every bucket through the fused per-instance
+    kernel; bitwise the matrices of a direct batched call on the bucket's instances, and the
+    live reference on a sample."""
+    import torch
+
+    from mpc_interface_b200 import Param, lti, receding
+    from mpc_interface_b200.examples import biped, synthetic
+
+    N, batch, system = 30, 61, "dP->CCC"
+    seed = int.from_bytes(os.urandom(4), "little")
+    conf = _conf(N, system)
+
+    def factory():
+        return biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                     target_vel=[Param("vel_x"), Param("vel_y")])
+
+    rng = np.random.default_rng(seed)
+    ticks = [dict(step_times=np.array([5, 17, 29]), step_count=1), dict(step_times=np.array([0, 12, 24]), step_count=2),
+             dict(step_times=np.array([11, 23, 35]), step_count=3)]
+    phase = rng.integers(0, len(ticks), size=batch)
+    times = np.stack([ticks[t]["step_times"] for t in phase])
+    count = np.array([ticks[t]["step_count"] for t in phase])
+    vals = _inputs(seed, batch, N)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    collector = {k: torch.from_numpy(np.ascontiguousarray(vals[k])).cuda()
+                 for k in ("s0_x", "s0_y", "x0_x", "x0_y", "n_x", "n_y")}
+    A, B = lti.named_system_batched(system, vals["tau"], vals["omega"])
+    buckets = receding.StructureBuckets(factory, biped.structure_key(N))
+    done = buckets.assemble_device(biped.structure_keys(N, times, count),
+                                   lambda i: dict(step_times=times[i], step_count=int(count[i])), collector,
+                                   params=params, dynamics={"LIP": (A, B)})
+    assert len(done) == len(set(phase)) and len({(qp.nv, qp.nc) for *_x, qp in done}) > 1
+    seen = 0
+    for key, index, form, qp in done:
+        idx = index.cpu().numpy()
+        seen += len(idx)
+        given = synthetic.pack_given(form.given_ID, form.given_len, {k: vals[k][idx] for k in form.given_ID}, len(idx))
+        direct = form.generate_all_qp_matrices_batched(given, {k: v[idx] for k, v in params.items()},
+                                                       dynamics={"LIP": (A[index], B[index])}, hessian="recursion")
+        for x, y in ((qp.P, direct.P), (qp.q, direct.q), (qp.G, direct.G), (qp.h, direct.h)):
+            assert torch.equal(x, y)
+        b = int(idx[0])
+        _one, want = _reference_instance(conf, vals, b, dict(step_times=times[b], step_count=int(count[b])))
+        cases.assert_qp_close(tuple(x[0].cpu().numpy() for x in (qp.G, qp.h, qp.P, qp.q)), want)
+    assert seen == batch
