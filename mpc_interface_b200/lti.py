@@ -800,7 +800,9 @@ def lower(form, plant_name):
                 plan.coupled.append((w, fv, Mz, E))
                 Pzz += w * (Mz.T @ Mz)  # body.py:292 with Vo = Co = [T | Mz]
             if fv.has_plant() or fc.has_plant() or not plan.embedded:
-                plan.cost_terms.append((w, fv, fc, aim, caim))
+                # (a coupled cost's aim is carried by E alone: the plant part must not subtract it again)
+                coupled_here = fv.has_aux() or fc.has_aux()
+                plan.cost_terms.append((w, fv, fc, 0.0 if coupled_here else aim, 0.0 if coupled_here else caim))
     if plan.embedded:
         plan.Pzz = Pzz
         plan.Gz = np.vstack(Gz_rows) if Gz_rows else np.zeros([0, nz])

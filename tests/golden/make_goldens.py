@@ -347,6 +347,33 @@ def biped_plants(name, N, batch, seed, system="dP->CCC", tick=None):
          A_sys=np.stack(Asys), B_sys=np.stack(Bsys), **vals, **extra, **layout(form))
 
 
+def soft_lip_plants(name, N, batch, seed, order):
+    """examples/soft_lip.py (slack variable, late disturbance, a cost with a non-zero aim over
+    a plant part and an auxiliary part, row-wise arrows) with one dP->CCC plant per instance,
+    every instance formulated on the reference's classes."""
+    from mpc_interface_b200.examples import soft_lip
+
+    api = types.SimpleNamespace(ControlSystem=ref_dyn.ControlSystem, ExtendedSystem=ref_dyn.ExtendedSystem,
+                                DomainVariable=ref_dyn.DomainVariable, Formulation=ref_body.Formulation,
+                                LineCombo=ref_comb.LineCombo, Cost=ref_goal.Cost, Constraint=ref_res.Constraint)
+    rng = np.random.default_rng(seed)
+    vals = {"x0_x": rng.normal(size=[batch, 3]) * [0.03, 0.1, 0.2], "d_x": rng.normal(size=[batch, N]) * 0.01,
+            "omega": np.sqrt(9.81 / rng.uniform(0.75, 1.0, batch)), "tau": rng.uniform(0.08, 0.12, batch),
+            "vel": rng.uniform(0.0, 0.4, batch)}
+    As, hs, Qs, qs, Asys, Bsys = [], [], [], [], [], []
+    for b in range(batch):
+        form = soft_lip.formulate_soft_lip(N, float(vals["omega"][b]), float(vals["tau"][b]),
+                                           float(vals["vel"][b]), order=order, api=api)
+        collector = {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in form.given_ID}
+        A, h, Q, q = form.generate_all_qp_matrices(form.arrange_given(collector))
+        As.append(A), hs.append(h[:, 0]), Qs.append(Q), qs.append(q[:, 0])
+        system_b = ref_dyn.ControlSystem.from_name("dP->CCC", ["_x"], tau=float(vals["tau"][b]),
+                                                   omega=float(vals["omega"][b]))
+        Asys.append(np.array(system_b.A, dtype=float)), Bsys.append(np.array(system_b.B, dtype=float))
+    save(name, seed=seed, N=N, order=np.array(order), A=np.stack(As), h=np.stack(hs), Q=np.stack(Qs),
+         q=np.stack(qs), A_sys=np.stack(Asys), B_sys=np.stack(Bsys), **vals, **layout(form))
+
+
 def random_forms(name, seeds, batch):
     """tests/_random_forms.py built by the reference, one formulation per instance."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -385,6 +412,10 @@ if __name__ == "__main__":
         biped_plants("biped_plants_n30_tick.npz", 30, 3, 1041,
                      tick=dict(step_times=np.array([5, 17, 29]), step_count=1))
         biped_plants("biped_plants_jccc_n16.npz", 16, 2, 1042, system="J->CCC")
+        sys.exit(0)
+    if sys.argv[1:] == ["soft_lip"]:
+        soft_lip_plants("soft_lip_n12.npz", 12, 3, 1050, ("cCoP_dot_x", "e_x"))
+        soft_lip_plants("soft_lip_n17_slack_first.npz", 17, 2, 1051, ("e_x", "cCoP_dot_x"))
         sys.exit(0)
     if sys.argv[1:] == ["big"]:
         biped_long("biped_long_digest.npz", [200, 400], 1020)

@@ -1,0 +1,83 @@
+"""The embedded per-instance path on a formulation that is NOT the biped: a soft-constrained LIP.
+
+Plant dP->CCC on one axis with one (tau_b, omega_b) per instance; next to it an OPTIMISED slack
+``e`` (DomainVariable, N samples), a GIVEN disturbance ``d`` entering one sample late (matrix
+coefficient), the signal ``soft = b + S d - e`` with ``b = CoM - CoM_ddot / omega_b^2``; costs on
+the slack alone, on ``soft`` and on the CoM velocity (per-instance aim); limits on ``soft`` with
+one arrow, with an arrow per row (the rows leave through the warps, not the bulk copies), on the
+slack alone (rows without a plant part) and a scheduled one.  Every instance is formulated
+from scratch by the unmodified reference.
+"""
+import os
+import types
+
+import numpy as np
+import pytest
+
+import _cases as cases
+from oracle import reference
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", ["soft_lip_n12", "soft_lip_n17_slack_first"])
+def test_soft_constrained_lip_goldens(name):
+    """The committed vectors (tests/golden/make_goldens.py soft_lip: every instance formulated by
+    the reference with its own plant), both Hessian variants."""
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import soft_lip, synthetic
+
+    g = cases.golden(name)
+    N, batch, order = int(g["N"]), g["A"].shape[0], tuple(str(x) for x in g["order"])
+    form = soft_lip.formulate_soft_lip(N, Param("omega"), Param("tau"), Param("vel"), order=order)
+    cases.check_layout(form, g)
+    given = synthetic.pack_given(form.given_ID, form.given_len, {key: g[key] for key in form.given_ID}, batch)
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, {"omega": g["omega"], "vel": g["vel"]},
+            dynamics={"LIP": ("dP->CCC", g["tau"], g["omega"])}, hessian=mode)
+        got = tuple(x.cpu().numpy() for x in (out.G, out.h, out.P, out.q))
+        for b in range(batch):
+            cases.assert_qp_close(tuple(x[b] for x in got), (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
+
+
+@pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
+@pytest.mark.parametrize("N,order", [(20, ("cCoP_dot_x", "e_x")), (33, ("e_x", "cCoP_dot_x")),
+                                     (70, ("cCoP_dot_x", "e_x"))])
+def test_soft_constrained_lip_against_the_live_reference(N, order):
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import soft_lip
+
+    batch = 6
+    seed = int.from_bytes(os.urandom(4), "little")
+    rng = np.random.default_rng(seed)
+    vals = {"x0_x": rng.normal(size=[batch, 3]) * [0.03, 0.1, 0.2], "d_x": rng.normal(size=[batch, N]) * 0.01,
+            "omega": np.sqrt(9.81 / rng.uniform(0.75, 1.0, batch)), "tau": rng.uniform(0.08, 0.12, batch) * min(1.0, 35.0 / N),  # (same preview time: A^N stays ~1e5)
+            "vel": rng.uniform(0.0, 0.4, batch)}
+    form = soft_lip.formulate_soft_lip(N, Param("omega"), Param("tau"), Param("vel"), order=order)
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and plan.nz == N and plan.nv == 2 * N
+    given = np.zeros([batch, form.given_len])
+    for name, ids in form.given_ID.items():
+        given[:, ids.start:ids.stop] = vals[name]
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                DomainVariable=ref.DomainVariable, Formulation=ref.Formulation,
+                                LineCombo=ref.LineCombo, Cost=ref.Cost, Constraint=ref.Constraint)
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, {"omega": vals["omega"], "vel": vals["vel"]},
+            dynamics={"LIP": ("dP->CCC", vals["tau"], vals["omega"])}, hessian=mode)
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        for b in range(batch):
+            one = soft_lip.formulate_soft_lip(N, float(vals["omega"][b]), float(vals["tau"][b]), float(vals["vel"][b]),
+                                              order=order, api=api)
+            if b == 0:
+                assert list(one.optim_ID.items()) == list(form.optim_ID.items())
+                assert list(one.given_ID.items()) == list(form.given_ID.items())
+            want = one.generate_all_qp_matrices(one.arrange_given(
+                {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
+            try:
+                cases.assert_qp_close(tuple(x[b] for x in got), want)
+            except AssertionError as e:
+                raise AssertionError("seed {} N {} instance {} ({}): {}".format(seed, N, b, mode, e))

@@ -207,6 +207,34 @@ def test_biped_with_per_instance_plants_lowering(cpu_extend, name, system):
         cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
 
 
+@pytest.mark.parametrize("name", ["soft_lip_n12", "soft_lip_n17_slack_first"])
+def test_soft_constrained_lip_lowering(cpu_extend, name):
+    """The embedded layout away from the biped (examples/soft_lip.py): an optimised slack, a
+    disturbance through a shift matrix, a cost with a NON-ZERO aim whose signal has a plant part
+    and an auxiliary part (its aim must reach q[u] and q[z] once each), row-wise arrows, rows
+    of the slack alone; the plant's input first or second in the QP."""
+    from mpc_interface_b200.examples import soft_lip, synthetic
+
+    g = cases.golden(name)
+    N, batch, order = int(g["N"]), g["A"].shape[0], tuple(str(x) for x in g["order"])
+    form = soft_lip.formulate_soft_lip(N, Param("omega"), Param("tau"), Param("vel"), order=order,
+                                       backend=NumpyBackend())
+    cases.check_layout(form, g)
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and plan.per_instance and (plan.n, plan.m, plan.nz, plan.nv) == (3, 1, N, 2 * N)
+    first = order[0] == "cCoP_dot_x"
+    assert plan.var_off == [0 if first else N] and plan.z_col == list(range(N, 2 * N) if first else range(N))
+    assert len(plan.coupled) == 2 and plan.varying == {"Qxx", "cx"}
+    params = {key: g[key] for key in ("omega", "vel")}
+    tables = plan.instance_tables(params, batch)
+    ccx, ccu = plan.coupled_tables(params, batch)
+    given = synthetic.pack_given(form.given_ID, form.given_len, {key: g[key] for key in form.given_ID}, batch)
+    for b in range(batch):
+        one = {key: v[b] for key, v in tables.items()}
+        got = _lti_numpy.evaluate_embedded(plan, g["A_sys"][b], g["B_sys"][b], given[b], None, one, (ccx[b], ccu[b]))
+        cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
+
+
 def test_per_instance_tables_built_with_torch_equal_the_numpy_ones(cpu_extend):
     """The GPU path evaluates the Param expressions on torch tensors (lti._Device); on the CPU
     device the same code must give the NumPy tables bit for bit."""
