@@ -791,12 +791,17 @@ def lower(form, plant_name):
                     _unsupported("a crossed cost on variables outside the plant")
                 if is_expr(w) or is_expr(aim):
                     _unsupported("a per-instance weight or aim of a cost on variables outside the plant")
-                if fv.rows != N:
-                    _unsupported("a cost on '{}' ({} samples, the horizon has {})".format(vname, fv.rows, N))
-                Mz = fv.Mz if fv.Mz is not None else np.zeros([N, nz])
-                Mg = fv.Mg if fv.Mg is not None else np.zeros([N, form.given_len])
+                rows = fv.rows
+                if rows != N and (fv.has_plant() or rows > N):
+                    _unsupported("a cost on '{}' ({} samples, the horizon has {})".format(vname, rows, N))
+                # (a signal of fewer samples, e.g. the footsteps: the missing rows are exact zeros)
+                Mz, Mg = np.zeros([N, nz]), np.zeros([N, form.given_len])
+                if fv.Mz is not None:
+                    Mz[:rows] = fv.Mz
+                if fv.Mg is not None:
+                    Mg[:rows] = fv.Mg
                 E = np.zeros([N, form.given_len + 1])  # e = Mg given - aim
-                E[:, :-1], E[:, -1] = Mg, -float(aim)
+                E[:, :-1], E[:rows, -1] = Mg, -float(aim)
                 plan.coupled.append((w, fv, Mz, E))
                 Pzz += w * (Mz.T @ Mz)  # body.py:292 with Vo = Co = [T | Mz]
             if fv.has_plant() or fc.has_plant() or not plan.embedded:

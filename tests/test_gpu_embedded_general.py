@@ -81,3 +81,42 @@ def test_soft_constrained_lip_against_the_live_reference(N, order):
                 cases.assert_qp_close(tuple(x[b] for x in got), want)
             except AssertionError as e:
                 raise AssertionError("seed {} N {} instance {} ({}): {}".format(seed, N, b, mode, e))
+
+
+@pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
+@pytest.mark.parametrize("seed", range(300, 324))
+def test_random_embedded_formulations_against_the_live_reference(seed):
+    """tests/_embedded_forms.py through the kernels: random structures around a per-instance plant
+    (four named plants, one or two axes, slack / footsteps / disturbance, costs with aims and on
+    signals shorter than the horizon, facets, row-wise arrows, centres, schedules, any variable
+    order), both Hessian variants, every instance checked against the unmodified reference."""
+    import _embedded_forms as forms
+    from mpc_interface_b200 import Param
+
+    spec = forms.draw(seed)
+    form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"))
+    plan = form.lti_plan("LIP")
+    assert plan.embedded
+    batch = 5
+    vals = forms.inputs(spec, form, batch, seed + 1000)
+    given = np.zeros([batch, form.given_len])
+    for name, ids in form.given_ID.items():
+        given[:, ids.start:ids.stop] = vals[name]
+    params = {key: vals[key] for key in plan.parameter_names()}
+    api = forms.reference_api(reference.load())
+    wants = []
+    for b in range(batch):
+        one = forms.build(spec, api, *(float(vals[key][b]) for key in ("omega", "tau", "vel", "gain")))
+        assert list(one.optim_ID.items()) == list(form.optim_ID.items())
+        wants.append(one.generate_all_qp_matrices(one.arrange_given(
+            {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID})))
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, params, dynamics={"LIP": (spec["system"], vals["tau"], vals["omega"])}, hessian=mode)
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        for b in range(batch):
+            try:
+                cases.assert_qp_close(tuple(x[b] for x in got), wants[b])
+            except AssertionError as e:
+                raise AssertionError("seed {} instance {} ({}; {} {} N {}): {}".format(
+                    seed, b, mode, spec["system"], spec["axes"], spec["N"], e))

@@ -235,6 +235,47 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
         cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
 
 
+@pytest.mark.parametrize("seed", range(200, 212))
+def test_random_embedded_formulations_lowering(cpu_extend, seed):
+    """tests/_embedded_forms.py: random structures around a per-instance plant (four named
+    plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
+    with aims and on signals shorter than the horizon, facets, row-wise arrows, centres,
+    schedules, any variable order), lowered and evaluated by the NumPy restatement of the
+    kernels' arithmetic, against the unmodified reference formulating every instance itself."""
+    import _embedded_forms as forms
+    from oracle import reference
+
+    if not reference.available():
+        pytest.skip("oracle/_ref is not staged")
+    from mpc_interface_b200 import dynamics
+
+    spec = forms.draw(seed)
+    form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
+                       backend=NumpyBackend())
+    plan = form.lti_plan("LIP")
+    assert plan.embedded
+    batch = 2
+    vals = forms.inputs(spec, form, batch, seed + 1000)
+    given = np.zeros([batch, form.given_len])
+    for name, ids in form.given_ID.items():
+        given[:, ids.start:ids.stop] = vals[name]
+    params = {key: vals[key] for key in plan.parameter_names()}
+    tables = plan.instance_tables(params, batch)
+    ccx, ccu = plan.coupled_tables(params, batch)
+    api = forms.reference_api(reference.load())
+    for b in range(batch):
+        one = forms.build(spec, api, *(float(vals[key][b]) for key in ("omega", "tau", "vel", "gain")))
+        assert list(one.optim_ID.items()) == list(form.optim_ID.items())
+        assert list(one.given_ID.items()) == list(form.given_ID.items())
+        want = one.generate_all_qp_matrices(one.arrange_given(
+            {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
+        plant = dynamics.ControlSystem.from_name(spec["system"], ["_x"], tau=float(vals["tau"][b]),
+                                                 omega=float(vals["omega"][b]))
+        got = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], None,
+                                           {key: v[b] for key, v in tables.items()}, (ccx[b], ccu[b]))
+        cases.assert_qp_close(got, want)
+
+
 def test_per_instance_tables_built_with_torch_equal_the_numpy_ones(cpu_extend):
     """The GPU path evaluates the Param expressions on torch tensors (lti._Device); on the CPU
     device the same code must give the NumPy tables bit for bit."""
