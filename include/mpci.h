@@ -367,6 +367,51 @@ int mpci_lti_assemble_coupled(const mpci_lti_plan* plan, const double* A_dev, lo
                               double* G_dev, double* h_dev, long batch, int hessian_mode,
                               void* stream);
 
+/* ---- costs with a `schedule` on the per-instance path ---------------------------------
+ * A Cost whose `schedule` picks some samples of the horizon (goal.py:46-60; the rows `sigma`
+ * of body.py:273-283 -- a terminal cost is schedule = range(N - 1, N)) has no time-invariant
+ * stage weight, so it is not part of the fused kernel's Hessian: this stage ADDS it to the P
+ * and q that mpci_lti_assemble / _ex / _coupled wrote, on the same stream:
+ *   P += sum_t w_t sum_{k in sigma_t} v_{t,k} c_{t,k}^T                         (body.py:292)
+ *   q += sum_t w_t / 2 sum_k ( v_{t,k} (fc_{t,k} - caim_t) + c_{t,k} (fv_{t,k} - aim_t) )
+ *                                                                               (body.py:293-300)
+ * v_{t,k} [nv] = row k of the preview matrix of the term's variable over the optimisation
+ * variables (plant columns (j, p <= k): cx . A^{k-p} B[:,j] + cu[j] [p == k]; auxiliary columns:
+ * Mz[k,:]), fv_{t,k} = cx . A^{k+1} x0 + Mg[k,:] . given its given part; c / fc the same for the
+ * crossed variable (equal to v / fv for a plain cost).  Mz / Mg hold one row per SCHEDULED
+ * sample, in the order of row_k.  All pointers of the description are host pointers, copied
+ * at creation.                                                                              */
+typedef struct {
+  int n, m, N;            /* the plant, as mpci_lti_desc                                     */
+  int nv;                 /* variables of the QP: row length of P (m * N in the plain layout) */
+  const int* var_off;     /* [m] column of sample 0 of input j; NULL = j * N                  */
+  int nz;                 /* auxiliary optimisation variables (0: none)                       */
+  const int* z_col;       /* [nz] their columns                                               */
+  int given_len;          /* doubles per instance of given_dev (0: no auxiliary givens)       */
+  int n_terms;
+  const int* row_ptr;     /* [n_terms + 1] the samples of term t: row_k[row_ptr[t] ..]        */
+  const int* row_k;       /* [row_ptr[n_terms]] horizon samples, 0 <= k < N                   */
+  const double* v_Mz;     /* [row_ptr[n_terms]][nz] or NULL (= zeros)                         */
+  const double* v_Mg;     /* [row_ptr[n_terms]][given_len] or NULL                            */
+  const double* c_Mz;     /* the crossed variable's; NULL = the variable's own                */
+  const double* c_Mg;
+} mpci_lti_sched_desc;
+
+typedef struct mpci_lti_sched mpci_lti_sched;
+
+int mpci_lti_sched_create(const mpci_lti_sched_desc* desc, mpci_lti_sched** out);
+int mpci_lti_sched_destroy(mpci_lti_sched* sched);
+
+/* terms_dev: per term (w, aim, caim, v_cx [n], v_cu [m], c_cx [n], c_cu [m]) = 3 + 2n + 2m
+ * doubles, [batch][n_terms][3 + 2n + 2m] (stride_terms = n_terms * (3 + 2n + 2m)) or one set
+ * for the batch (stride_terms = 0).  A, B, x0 as mpci_lti_assemble; given_dev [batch][given_len]
+ * or NULL.  P_dev [batch][nv][nv] / q_dev [batch][nv] may be NULL.
+ * One CTA per instance; read-modify-write of P (the one pass over P this stage costs).        */
+int mpci_lti_sched_add(const mpci_lti_sched* sched, const double* A_dev, long strideA,
+                       const double* B_dev, long strideB, const double* x0_dev,
+                       const double* given_dev, const double* terms_dev, long stride_terms,
+                       double* P_dev, double* q_dev, long batch, void* stream);
+
 /* Closed forms of the reference's named LIP systems (tools.get_system_matrices,
  * python/mpc_interface/tools.py:240-285: A = exp(G tau), B = int_0^tau exp(G t) dt h, there
  * by SymPy) for a batch with one sampling period and one pendulum frequency per instance:

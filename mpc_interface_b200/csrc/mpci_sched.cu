@@ -1,0 +1,295 @@
+// Costs with a `schedule` on the per-instance path (include/mpci.h: mpci_lti_sched_desc).
+//
+// The fused kernel of mpci_lti.cu builds P from ONE stage weight (its Hessian variants all rest
+// on  P[p,p'] = sum_k Gam_{k-p}^T Qxx Gam_{k-p'}  with the same Qxx at every sample).  A cost that
+// acts on some samples only (goal.py:46-60 `schedule`; the rows sigma of body.py:273-283 -- the
+// terminal cost of an MPC is schedule = range(N - 1, N)) is a sum of a few outer products
+// instead, and is ADDED here to the P and q the assembly wrote, one CTA per instance:
+//   1. W_d = A^d B (d < K) and xs_k = A^{k+1} x0 (k < K), K = 1 + the last scheduled sample, by the
+//      recursion of extend_matrices (tools.py:23-29: u_k = A u_{k-1}, s_k = A s_{k-1})
+//   2. per scheduled row r = (term t, sample k), a chunk of rows at a time in shared memory:
+//      v_r [nv] = row k of the variable's preview matrix over the optimisation variables,
+//      c_r the crossed variable's, and the given parts fv_r, fc_r
+//   3. P[i][j] += sum_r w_r v_r[i] c_r[j]                                        (body.py:292)
+//      q[i]    += sum_r w_r / 2 (v_r[i] (fc_r - caim_r) + c_r[i] (fv_r - aim_r))  (body.py:293-300)
+// P is read and written once per chunk of rows: a terminal cost costs one more pass over P.
+#include <algorithm>
+#include <vector>
+
+#include "mpci_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr size_t kRowBudget = 64 * 1024;    // bytes of shared memory for the chunk of rows ...
+constexpr size_t kSmemLimit = 200 * 1024;   // ... unless one row pair needs more
+
+struct SchedArgs {
+  int n, m, N, nv, nz, glen, T, R, K, chunk;
+  const int *voff, *zcol, *row_term, *row_k;
+  const double *vMz, *vMg, *cMz, *cMg;
+  const double *A, *B, *x0, *given, *terms;
+  long sA, sB, sT;
+  double *P, *q;
+  long batch;
+};
+
+// shared memory (doubles): A [n][n] | W [K][n][m] | X [K][n] | V, C [chunk][nv] | epsV, epsC, w [chunk]
+__host__ __device__ inline size_t fixed_doubles(int n, int m, int K) {
+  return (size_t)n * n + (size_t)K * n * m + (size_t)K * n;
+}
+
+__global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
+  extern __shared__ double sched_smem[];
+  const int n = a.n, m = a.m, nv = a.nv, K = a.K, tl = 3 + 2 * a.n + 2 * a.m;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = (int)blockDim.x, nwarps = nthr >> 5;
+  double* As = sched_smem;
+  double* W = As + n * n;
+  double* X = W + (size_t)K * n * m;
+  double* V = X + (size_t)K * n;
+  double* C = V + (size_t)a.chunk * nv;
+  double* epsV = C + (size_t)a.chunk * nv;
+  double* epsC = epsV + a.chunk;
+  double* wr = epsC + a.chunk;
+
+  for (long b = blockIdx.x; b < a.batch; b += gridDim.x) {
+    const double* Ab = a.A + b * a.sA;
+    const double* Bb = a.B + b * a.sB;
+    const double* xb = a.x0 + b * (long)n;
+    const double* gb = a.given ? a.given + b * (long)a.glen : nullptr;
+    const double* tb = a.terms + b * a.sT;
+    __syncthreads();  // (the previous instance's rows are still being read)
+    for (int e = tid; e < n * n; e += nthr) As[e] = Ab[e];
+    for (int e = tid; e < n * m; e += nthr) W[e] = Bb[e];
+    __syncthreads();
+    if (tid < n) {  // xs_0 = A x0
+      double acc = 0.0;
+      for (int i = 0; i < n; ++i) acc = fma(As[tid * n + i], xb[i], acc);
+      X[tid] = acc;
+    }
+    __syncthreads();
+    for (int d = 1; d < K; ++d) {  // W_d = A W_{d-1},  xs_d = A xs_{d-1}
+      const double* Wp = W + (size_t)(d - 1) * n * m;
+      const double* Xp = X + (size_t)(d - 1) * n;
+      for (int e = tid; e < n * m + n; e += nthr) {
+        double acc = 0.0;
+        if (e < n * m) {
+          const int i = e / m, j = e - i * m;
+          for (int l = 0; l < n; ++l) acc = fma(As[i * n + l], Wp[l * m + j], acc);
+          W[(size_t)d * n * m + e] = acc;
+        } else {
+          const int i = e - n * m;
+          for (int l = 0; l < n; ++l) acc = fma(As[i * n + l], Xp[l], acc);
+          X[(size_t)d * n + i] = acc;
+        }
+      }
+      __syncthreads();
+    }
+
+    for (int r0 = 0; r0 < a.R; r0 += a.chunk) {
+      const int rows = min(a.chunk, a.R - r0);
+      __syncthreads();
+      for (int e = tid; e < rows * nv; e += nthr) V[e] = 0.0, C[e] = 0.0;
+      __syncthreads();
+      for (int rr = warp; rr < rows; rr += nwarps) {  // a warp per row
+        const int r = r0 + rr, t = a.row_term[r], k = a.row_k[r];
+        const double* tt = tb + (long)t * tl;
+        const double *vcx = tt + 3, *vcu = vcx + n, *ccx = vcu + m, *ccu = ccx + n;
+        double* Vr = V + (size_t)rr * nv;
+        double* Cr = C + (size_t)rr * nv;
+        for (int e = lane; e < m * (k + 1); e += 32) {
+          const int j = e / (k + 1), p = e - j * (k + 1);
+          const double* Wd = W + (size_t)(k - p) * n * m + j;
+          double av = p == k ? vcu[j] : 0.0, ac = p == k ? ccu[j] : 0.0;
+          for (int i = 0; i < n; ++i) {
+            const double wv = Wd[i * m];
+            av = fma(vcx[i], wv, av);
+            ac = fma(ccx[i], wv, ac);
+          }
+          Vr[a.voff[j] + p] = av;
+          Cr[a.voff[j] + p] = ac;
+        }
+        const double* cMz = a.cMz ? a.cMz : a.vMz;
+        for (int i = lane; i < a.nz; i += 32) {
+          if (a.vMz) Vr[a.zcol[i]] = a.vMz[(size_t)r * a.nz + i];
+          if (cMz) Cr[a.zcol[i]] = cMz[(size_t)r * a.nz + i];
+        }
+        // the given parts: cx . A^{k+1} x0 + Mg[r,:] . given
+        const double* cMg = a.cMg ? a.cMg : a.vMg;
+        double fv = 0.0, fc = 0.0;
+        for (int i = lane; i < n; i += 32) {
+          const double xk = X[(size_t)k * n + i];
+          fv = fma(vcx[i], xk, fv);
+          fc = fma(ccx[i], xk, fc);
+        }
+        if (gb) {
+          for (int g = lane; g < a.glen; g += 32) {
+            const double gv = gb[g];
+            if (a.vMg) fv = fma(a.vMg[(size_t)r * a.glen + g], gv, fv);
+            if (cMg) fc = fma(cMg[(size_t)r * a.glen + g], gv, fc);
+          }
+        }
+        for (int o = 16; o; o >>= 1) {
+          fv += __shfl_xor_sync(0xffffffffu, fv, o);
+          fc += __shfl_xor_sync(0xffffffffu, fc, o);
+        }
+        if (lane == 0) {
+          const double w = tt[0];
+          wr[rr] = w;
+          epsV[rr] = 0.5 * w * (fv - tt[1]);
+          epsC[rr] = 0.5 * w * (fc - tt[2]);
+        }
+      }
+      __syncthreads();
+      if (a.P) {
+        double* Pb = a.P + b * (long)nv * nv;
+        for (long e = tid; e < (long)nv * nv; e += nthr) {
+          const int i = (int)(e / nv), j = (int)(e - (long)i * nv);
+          double acc = 0.0;
+          for (int rr = 0; rr < rows; ++rr) acc = fma(wr[rr] * V[(size_t)rr * nv + i], C[(size_t)rr * nv + j], acc);
+          Pb[e] += acc;
+        }
+      }
+      if (a.q) {
+        double* qb = a.q + b * (long)nv;
+        for (int i = tid; i < nv; i += nthr) {
+          double acc = 0.0;
+          for (int rr = 0; rr < rows; ++rr)
+            acc += V[(size_t)rr * nv + i] * epsC[rr] + C[(size_t)rr * nv + i] * epsV[rr];
+          qb[i] += acc;
+        }
+      }
+    }
+  }
+}
+
+template <typename T>
+int upload(T** dst, const T* src, size_t count) {
+  *dst = nullptr;
+  if (!src || !count) return 0;
+  MPCI_CUDA(cudaMalloc(dst, count * sizeof(T)));
+  MPCI_CUDA(cudaMemcpy(*dst, src, count * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+}  // namespace
+
+struct mpci_lti_sched {
+  int n = 0, m = 0, N = 0, nv = 0, nz = 0, glen = 0, T = 0, R = 0, K = 0, chunk = 0, device = 0;
+  size_t smem = 0;
+  int *voff = nullptr, *zcol = nullptr, *row_term = nullptr, *row_k = nullptr;
+  double *vMz = nullptr, *vMg = nullptr, *cMz = nullptr, *cMg = nullptr;
+};
+
+extern "C" int mpci_lti_sched_destroy(mpci_lti_sched* s) {
+  if (!s) return 0;
+  cudaFree(s->voff), cudaFree(s->zcol), cudaFree(s->row_term), cudaFree(s->row_k);
+  cudaFree(s->vMz), cudaFree(s->vMg), cudaFree(s->cMz), cudaFree(s->cMg);
+  delete s;
+  return 0;
+}
+
+extern "C" int mpci_lti_sched_create(const mpci_lti_sched_desc* d, mpci_lti_sched** out) {
+  using mpci::fail;
+  if (!d || !out) return fail(-1, "mpci_lti_sched_create: null argument");
+  *out = nullptr;
+  if (d->n <= 0 || d->m <= 0 || d->N <= 0 || d->nv <= 0 || d->nz < 0 || d->given_len < 0 || d->n_terms <= 0)
+    return fail(-2, "mpci_lti_sched_create: bad sizes (n %d, m %d, N %d, nv %d, nz %d, given_len %d, terms %d)",
+                d->n, d->m, d->N, d->nv, d->nz, d->given_len, d->n_terms);
+  if (!d->row_ptr || !d->row_k) return fail(-1, "mpci_lti_sched_create: row_ptr / row_k missing");
+  if (d->nz > 0 && !d->z_col) return fail(-1, "mpci_lti_sched_create: z_col missing");
+  if (d->row_ptr[0] != 0) return fail(-2, "mpci_lti_sched_create: row_ptr[0] must be 0");
+  const int R = d->row_ptr[d->n_terms];
+  if (R <= 0) return fail(-2, "mpci_lti_sched_create: no scheduled rows");
+  std::vector<int> row_term(R), voff(d->m);
+  int K = 0;
+  for (int t = 0; t < d->n_terms; ++t) {
+    if (d->row_ptr[t + 1] < d->row_ptr[t]) return fail(-2, "mpci_lti_sched_create: row_ptr decreases at term %d", t);
+    for (int r = d->row_ptr[t]; r < d->row_ptr[t + 1]; ++r) {
+      if (d->row_k[r] < 0 || d->row_k[r] >= d->N)
+        return fail(-3, "mpci_lti_sched_create: term %d schedules sample %d outside the horizon of %d", t,
+                    d->row_k[r], d->N);
+      row_term[r] = t;
+      K = std::max(K, d->row_k[r] + 1);
+    }
+  }
+  for (int j = 0; j < d->m; ++j) {
+    voff[j] = d->var_off ? d->var_off[j] : j * d->N;
+    if (voff[j] < 0 || voff[j] + d->N > d->nv)
+      return fail(-3, "mpci_lti_sched_create: input %d at columns %d..%d of %d", j, voff[j], voff[j] + d->N, d->nv);
+  }
+  for (int i = 0; i < d->nz; ++i) {
+    if (d->z_col[i] < 0 || d->z_col[i] >= d->nv)
+      return fail(-3, "mpci_lti_sched_create: auxiliary variable %d at column %d of %d", i, d->z_col[i], d->nv);
+    for (int j = 0; j < d->m; ++j)
+      if (d->z_col[i] >= voff[j] && d->z_col[i] < voff[j] + d->N)
+        return fail(-3, "mpci_lti_sched_create: auxiliary variable %d at column %d, inside input %d's samples", i,
+                    d->z_col[i], j);
+  }
+  if ((d->c_Mz && !d->v_Mz) || (d->c_Mg && !d->v_Mg))
+    return fail(-2, "mpci_lti_sched_create: a crossed auxiliary table needs the variable's own");
+
+  auto* s = new mpci_lti_sched;
+  s->n = d->n, s->m = d->m, s->N = d->N, s->nv = d->nv, s->nz = d->nz, s->glen = d->given_len;
+  s->T = d->n_terms, s->R = R, s->K = K;
+  const size_t fixed = fixed_doubles(d->n, d->m, K) * sizeof(double);
+  const size_t per_row = ((size_t)2 * d->nv + 3) * sizeof(double);
+  size_t chunk = std::max<size_t>(1, kRowBudget / per_row);
+  chunk = std::min<size_t>(chunk, (size_t)R);
+  if (fixed + per_row > kSmemLimit) {
+    delete s;
+    return fail(-4, "mpci_lti_sched_create: %zu bytes of shared memory needed (n %d, m %d, %d samples, nv %d), "
+                "%zu available", fixed + per_row, d->n, d->m, K, d->nv, kSmemLimit);
+  }
+  while (fixed + chunk * per_row > kSmemLimit) --chunk;
+  s->chunk = (int)chunk;
+  s->smem = fixed + chunk * per_row;
+  cudaGetDevice(&s->device);
+  int rc = 0;
+  if (!rc) rc = upload(&s->voff, voff.data(), (size_t)d->m);
+  if (!rc) rc = upload(&s->zcol, d->z_col, (size_t)d->nz);
+  if (!rc) rc = upload(&s->row_term, row_term.data(), (size_t)R);
+  if (!rc) rc = upload(&s->row_k, d->row_k, (size_t)R);
+  if (!rc) rc = upload(&s->vMz, d->v_Mz, (size_t)R * d->nz);
+  if (!rc) rc = upload(&s->vMg, d->v_Mg, (size_t)R * d->given_len);
+  if (!rc) rc = upload(&s->cMz, d->c_Mz, (size_t)R * d->nz);
+  if (!rc) rc = upload(&s->cMg, d->c_Mg, (size_t)R * d->given_len);
+  if (!rc && s->smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(lti_sched_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)kSmemLimit);
+    if (e != cudaSuccess) rc = mpci::cuda_fail(e, "cudaFuncSetAttribute(lti_sched_kernel)");
+  }
+  if (rc) {
+    mpci_lti_sched_destroy(s);
+    return rc;
+  }
+  *out = s;
+  return 0;
+}
+
+extern "C" int mpci_lti_sched_add(const mpci_lti_sched* s, const double* A, long strideA, const double* B,
+                                  long strideB, const double* x0, const double* given, const double* terms,
+                                  long stride_terms, double* P, double* q, long batch, void* stream) {
+  using mpci::fail;
+  if (!s || !A || !B || !x0 || !terms) return fail(-1, "mpci_lti_sched_add: null argument");
+  if (batch < 0) return fail(-2, "mpci_lti_sched_add: negative batch");
+  if (s->vMg && !given) return fail(-1, "mpci_lti_sched_add: the scheduled costs read `given`, which is NULL");
+  const long tl = (long)s->T * (3 + 2 * s->n + 2 * s->m);
+  if (stride_terms != 0 && stride_terms != tl)
+    return fail(-2, "mpci_lti_sched_add: stride_terms %ld (0 or %ld expected)", stride_terms, tl);
+  if (batch == 0 || (!P && !q)) return 0;
+  SchedArgs a{};
+  a.n = s->n, a.m = s->m, a.N = s->N, a.nv = s->nv, a.nz = s->nz, a.glen = s->glen, a.T = s->T, a.R = s->R;
+  a.K = s->K, a.chunk = s->chunk;
+  a.voff = s->voff, a.zcol = s->zcol, a.row_term = s->row_term, a.row_k = s->row_k;
+  a.vMz = s->vMz, a.vMg = s->vMg, a.cMz = s->cMz, a.cMg = s->cMg;
+  a.A = A, a.B = B, a.x0 = x0, a.given = given, a.terms = terms;
+  a.sA = strideA, a.sB = strideB, a.sT = stride_terms;
+  a.P = P, a.q = q, a.batch = batch;
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
+  const long grid = std::min<long>(batch, (long)sms * 8);
+  lti_sched_kernel<<<(unsigned)grid, kThreads, s->smem, mpci::as_stream(stream)>>>(a);
+  MPCI_LAUNCH_CHECK("lti_sched_kernel");
+  return 0;
+}

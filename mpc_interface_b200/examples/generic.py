@@ -18,12 +18,14 @@ class _Own:
 
 
 def formulate_generic(A, B, Q, R, horizon, rows, refs=None, u_box=(-1.0, 2.0), row_bound=5.0,
-                      backend=None, api=None):
+                      backend=None, api=None, terminal=None):
     """``rows``: [n_rows, nx] coefficients of the linear state constraints
     ``c' x_k <= row_bound``; ``refs``: per-state aims (numbers or Params).
     ``api`` is any namespace with the formulation classes (default: this
     package) -- the golden-vector script passes the reference's own classes so
-    both sides are built by the same recipe."""
+    both sides are built by the same recipe.  ``terminal``: [nx, nx] weight of the terminal
+    cost ``(x_N - ref)' Qf (x_N - ref)``, the same crossed costs on the last sample only
+    (``schedule=range(horizon - 1, horizon)``, goal.py:46-60)."""
     api = _Own if api is None else api
     ControlSystem, ExtendedSystem = api.ControlSystem, api.ExtendedSystem
     LineCombo, Cost, Box, Constraint = api.LineCombo, api.Cost, api.Box, api.Constraint
@@ -46,6 +48,17 @@ def formulate_generic(A, B, Q, R, horizon, rows, refs=None, u_box=(-1.0, 2.0), r
             else:
                 cost = Cost(states[i], Q[i, j], aim=[refs[i]], cross=states[j], cross_aim=[refs[j]])
             form.incorporate_goal("Q_%d_%d" % (i, j), cost)
+    last = range(horizon - 1, horizon)
+    for i in range(nx if terminal is not None else 0):
+        for j in range(nx):
+            if terminal[i, j] == 0.0:
+                continue
+            if i == j:
+                cost = Cost(states[i], terminal[i, i], aim=[refs[i]], schedule=last)
+            else:
+                cost = Cost(states[i], terminal[i, j], aim=[refs[i]], cross=states[j], cross_aim=[refs[j]],
+                            schedule=last)
+            form.incorporate_goal("Qf_%d_%d" % (i, j), cost)
     for i in range(nu):
         for j in range(nu):
             if R[i, j] == 0.0:

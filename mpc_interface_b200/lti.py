@@ -19,9 +19,10 @@ no slower fallback):
     inputs / such definitions (a point-wise linear form).  The coefficient may be a
     ``Param`` expression: the LIP's centre of pressure ``b = CoM - CoM_ddot / omega_b^2``
     with one pendulum frequency per instance (biped_formulation.py:62);
-  * costs: scalar weight (number or ``Param``), no ``L`` / ``schedule``, aims that are
-    numbers or ``Param`` expressions, optional ``cross``, one or several axes; a cost
-    may not mix states and inputs;
+  * costs: scalar weight (number or ``Param``), no ``L``, aims that are numbers or ``Param``
+    expressions, optional ``cross``, one or several axes; a cost over the whole horizon may
+    not mix states and inputs; a cost with a ``schedule`` (a terminal cost: ``range(N - 1, N)``;
+    any list of samples) is added to P and q by a second stage (csrc/mpci_sched.cu);
   * limits: no ``L``; ``schedule`` a contiguous ``range`` (the terminal constraint of the
     biped, biped_formulation.py:97-102); one axis with ``arrow`` / ``center`` / ``extreme``
     of one row or one row per sample, or several axes with a single-row ``arrow`` (a facet
@@ -44,6 +45,28 @@ HESSIAN_DMMA = 0
 HESSIAN_RECURSION = 1
 
 NAMED_SYSTEMS = {"J->CCC": (0, 3), "P->CC": (1, 2), "P->X": (2, 1), "dP->CCC": (3, 3), "dP->CCP": (4, 3)}
+
+
+class LtiSchedDesc(ctypes.Structure):
+    """mpci_lti_sched_desc of include/mpci.h"""
+
+    _fields_ = [
+        ("n", ctypes.c_int),
+        ("m", ctypes.c_int),
+        ("N", ctypes.c_int),
+        ("nv", ctypes.c_int),
+        ("var_off", ctypes.c_void_p),
+        ("nz", ctypes.c_int),
+        ("z_col", ctypes.c_void_p),
+        ("given_len", ctypes.c_int),
+        ("n_terms", ctypes.c_int),
+        ("row_ptr", ctypes.c_void_p),
+        ("row_k", ctypes.c_void_p),
+        ("v_Mz", ctypes.c_void_p),
+        ("v_Mg", ctypes.c_void_p),
+        ("c_Mz", ctypes.c_void_p),
+        ("c_Mg", ctypes.c_void_p),
+    ]
 
 
 class LtiDesc(ctypes.Structure):
@@ -266,6 +289,10 @@ class LtiPlan:
         self.group_row0 = []  # first row of every plant group in G / h
         self.coupled = []     # costs on signals with an auxiliary part: (w, form, Mz [N,nz], E [N,ng+1])
         self.Pzz = self.Gz = self.Hg = self.row_kind = None
+        # costs with a schedule (the stage of csrc/mpci_sched.cu, added to P and q afterwards):
+        # (weight, form, cross form, aim, cross aim, samples [list of k])
+        self.sched_terms = []
+        self._sched = None
 
     # ---- numeric tables -----------------------------------------------------
     def _cost_tables(self, params, batch, xp=_Host):
@@ -460,7 +487,70 @@ class LtiPlan:
         for form, _arrow, parts, _k0, _cnt in self.groups:
             out += [c for c in list(form.cx.values()) + list(form.cu.values()) if is_expr(c)]
             out += [coef for coef, _ in parts if is_expr(coef)]
+        for w, fv, fc, aim, caim, _rows in self.sched_terms:
+            out += [x for x in (w, aim, caim) if is_expr(x)]
+            for form in (fv, fc):
+                out += [c for c in list(form.cx.values()) + list(form.cu.values()) if is_expr(c)]
         return out
+
+    # ---- costs with a schedule ---------------------------------------------------
+    def sched_tables(self, params, batch, dev=None):
+        """terms [R, T, 3 + 2n + 2m] of mpci_lti_sched_add -- per term (w, aim, caim, v_cx, v_cu,
+        c_cx, c_cu); R = batch when anything in them is per-instance, else 1."""
+        xp = _Host if dev is None else _Device(dev)
+        params = xp.params(params, batch)
+        n, m, T = self.n, self.m, len(self.sched_terms)
+        symbolic = any(is_expr(x) for x in self._sched_exprs())
+        out = xp.zeros([batch if symbolic else 1, T, 3 + 2 * n + 2 * m])
+        for t, (w, fv, fc, aim, caim, _rows) in enumerate(self.sched_terms):
+            for col, x in enumerate((w, aim, caim)):
+                out[:, t, col] = _value(x, params)
+            out[:, t, 3:3 + n] = _dense(fv.cx, n, params, batch, xp)
+            out[:, t, 3 + n:3 + n + m] = _dense(fv.cu, m, params, batch, xp)
+            out[:, t, 3 + n + m:3 + 2 * n + m] = _dense(fc.cx, n, params, batch, xp)
+            out[:, t, 3 + 2 * n + m:] = _dense(fc.cu, m, params, batch, xp)
+        return out
+
+    def _sched_exprs(self):
+        out = []
+        for w, fv, fc, aim, caim, _rows in self.sched_terms:
+            out += [w, aim, caim]
+            for form in (fv, fc):
+                out += list(form.cx.values()) + list(form.cu.values())
+        return out
+
+    def sched_desc_tables(self):
+        """The constant tables of mpci_lti_sched_desc (include/mpci.h)."""
+        i32 = lambda x: np.ascontiguousarray(x, dtype=np.int32)  # noqa: E731
+        nz, ng = self.nz, (self.ng if self.embedded else 0)
+        ptr, rows = [0], []
+        for *_r, samples in self.sched_terms:
+            rows += list(samples)
+            ptr.append(len(rows))
+
+        def stack(which, attr, width):
+            if not width or not any(getattr(term[which], attr) is not None for term in self.sched_terms):
+                return None
+            blocks = []
+            for term in self.sched_terms:
+                M = getattr(term[which], attr)
+                blocks.append(np.zeros([len(term[5]), width]) if M is None else np.asarray(M)[list(term[5])])
+            return np.ascontiguousarray(np.vstack(blocks), dtype=np.float64)
+
+        crossed = any(fv is not fc for _w, fv, fc, *_r in self.sched_terms)
+        t = dict(row_ptr=i32(ptr), row_k=i32(rows), v_Mz=stack(1, "Mz", nz), v_Mg=stack(1, "Mg", ng),
+                 c_Mz=stack(2, "Mz", nz) if crossed else None, c_Mg=stack(2, "Mg", ng) if crossed else None,
+                 var_off=i32(self.var_off) if self.embedded else None,
+                 z_col=i32(self.z_col) if nz else None)
+        for own, cross in (("v_Mz", "c_Mz"), ("v_Mg", "c_Mg")):  # (the C side wants the own table beside a crossed one)
+            if t[cross] is not None and t[own] is None:
+                t[own] = np.zeros_like(t[cross])
+        return t
+
+    def device_sched(self):
+        if self._sched is None:
+            self._sched = _DeviceLtiSched(self)
+        return self._sched
 
     # ---- the plant as the kernel sees it --------------------------------------
     def expand_numpy(self, A, B):
@@ -546,6 +636,29 @@ class _DeviceLtiPlan:
         handle, self.handle = getattr(self, "handle", None), None
         if handle:
             self._lib.mpci_lti_plan_destroy(handle)
+
+
+class _DeviceLtiSched:
+    """mpci_lti_sched of a plan with scheduled costs."""
+
+    def __init__(self, plan):
+        from . import device
+
+        device.require_gpu()
+        t = self._keep = plan.sched_desc_tables()
+        at = lambda k: t[k].ctypes.data if t[k] is not None else None  # noqa: E731
+        desc = LtiSchedDesc(plan.n, plan.m, plan.N, plan.nv, at("var_off"), plan.nz, at("z_col"),
+                            plan.ng if plan.embedded else 0, len(plan.sched_terms), at("row_ptr"), at("row_k"),
+                            at("v_Mz"), at("v_Mg"), at("c_Mz"), at("c_Mg"))
+        handle = ctypes.c_void_p()
+        device.check(device.lib().mpci_lti_sched_create(ctypes.byref(desc), ctypes.byref(handle)))
+        self.handle = handle
+        self._lib = device.lib()
+
+    def __del__(self):
+        handle, self.handle = getattr(self, "handle", None), None
+        if handle:
+            self._lib.mpci_lti_sched_destroy(handle)
 
 
 # ---------------------------------------------------------------------------
@@ -777,11 +890,23 @@ def lower(form, plant_name):
         w = cost.weight if is_expr(cost.weight) else float(cost.weight)
         if not is_expr(w) and w == 0.0 and (plan.embedded or cost.L or cost.cross_L or cost.schedule):
             continue  # adds exact zeros (the biped's terminal cost, biped_configuration.py:49)
-        if cost.L or cost.cross_L or cost.schedule:
-            _unsupported("a cost with L or a schedule")
+        if cost.L or cost.cross_L:
+            _unsupported("a cost with L")
         for a, ax in enumerate(cost.axes):
             vname, cname = cost.variable + ax, cost.cross + ax
             fv, fc = form_of(vname, "a cost"), form_of(cname, "a cost")
+            if cost.schedule:  # some samples only: no stage weight, added by the stage of mpci_sched.cu
+                rows = N if (fv.has_plant() or fc.has_plant() or not plan.embedded) else fv.rows
+                if rows is None or rows > N or (fc.rows is not None and not fc.has_plant() and fc.rows < rows):
+                    _unsupported("a scheduled cost on '{}' ({} samples, the horizon has {})".format(vname, rows, N))
+                samples = [int(k) for k in cost.schedule]
+                if any(k < 0 or k >= rows for k in samples):
+                    raise IndexError("index {} is out of bounds for axis 0 with size {}".format(
+                        next(k for k in samples if k < 0 or k >= rows), rows))
+                aim = _single(np.asarray(cost.aim, dtype=object)[:, a], "an aim")
+                caim = _single(np.asarray(cost.cross_aim, dtype=object)[:, a], "an aim")
+                plan.sched_terms.append((w, fv, fc, aim, caim, samples))
+                continue
             if (fv.touches_states() and fc.touches_inputs()) or (fv.touches_inputs() and fc.touches_states()):
                 _unsupported("a cost that couples states and inputs")
             aim = _single(np.asarray(cost.aim, dtype=object)[:, a], "an aim")
@@ -930,7 +1055,7 @@ class LtiJob:
         self.strideA = n * n if A.dim() == 3 else 0
         self.strideB = n * m if B.dim() == 3 else 0
         self.tables = self.scalars = self.ccx = self.ccu = None
-        if plan.per_instance or plan.embedded:
+        if plan.per_instance or plan.embedded or plan.sched_terms:
             missing = [nm for nm in plan.parameter_names() if nm not in (params or {})]
             if missing:
                 raise KeyError("no value given for the parameter '{}'".format(missing[0]))
@@ -941,6 +1066,10 @@ class LtiJob:
                 self.ccx, self.ccu = plan.coupled_tables(params, batch, dev)
         elif len(plan.slots.exprs):
             self.scalars = to_dev(plan.slots.evaluate(params or {}, batch))
+        self.sched_terms = None
+        if plan.sched_terms:
+            self.sched = plan.device_sched()
+            self.sched_terms = plan.sched_tables(params, batch, dev).contiguous()
 
     def launch(self, out=None, hessian=HESSIAN_DMMA, parts="PqGh"):
         """One assembly of the batch into ``out`` (a ``QPBatch``, allocated when None) on the
@@ -968,6 +1097,12 @@ class LtiJob:
         else:
             rc = lib.mpci_lti_assemble(*head, ptr(self.scalars), *outs, batch, int(hessian), stream)
         device.check(rc)
+        if self.sched_terms is not None and (outs[0] is not None or outs[1] is not None):
+            terms = self.sched_terms
+            stride = terms.shape[1] * terms.shape[2] if terms.shape[0] == batch and batch > 1 else 0
+            device.check(lib.mpci_lti_sched_add(
+                self.sched.handle, ptr(self.A), self.strideA, ptr(self.B), self.strideB, ptr(self.x0),
+                ptr(self.given) if plan.embedded else None, ptr(terms), stride, outs[0], outs[1], batch, stream))
         out._keep = self  # the launches are asynchronous: the inputs live as long as the result
         return out
 
@@ -984,6 +1119,8 @@ def _host_inputs(plan, A, B, x0, params):
     n, m, n0, m0 = plan.n, plan.m, plan.n0, plan.m0
     if plan.per_instance:
         _unsupported("Param coefficients through the host-buffer entry points")
+    if plan.sched_terms:
+        _unsupported("costs with a schedule through the host-buffer entry points")
     A = np.asarray(A, dtype=np.float64)
     B = np.asarray(B, dtype=np.float64)
     x0 = np.ascontiguousarray(x0, dtype=np.float64)

@@ -22,8 +22,9 @@ INPUT = {"dP->CCC": "cCoP_dot", "J->CCC": "CoM_dddot", "dP->CCP": "cCoP_dot", "P
 OMEGA_COEFS = ("inv", "neg_inv2", "times", "num")
 
 
-def draw(seed):
-    """The structure as plain data (a dict of lists and numbers)."""
+def draw(seed, scheduled=False):
+    """The structure as plain data (a dict of lists and numbers).  ``scheduled``: some of the
+    costs act on a few samples only (goal.py `schedule`)."""
     rng = np.random.default_rng(seed)
     system = SYSTEMS[rng.integers(len(SYSTEMS))]
     axes = ["_x", "_y"] if rng.random() < 0.4 else ["_x"]
@@ -75,9 +76,23 @@ def draw(seed):
                       "weight_param": bool(per_instance and rng.random() < 0.3),
                       "aim": [float(rng.uniform(-0.3, 0.3)) if rng.random() < 0.7 else 0.0 for _ in axes],
                       "aim_param": bool(per_instance)})
+    for c in costs:  # some of them on a few samples only (a terminal cost, a window, scattered samples)
+        c["schedule"] = None
+        rows = spec["steps_U"].shape[1] if c["var"] == "Ds" else N
+        if scheduled and rng.random() < 0.45:
+            kind = rng.random()
+            if kind < 0.4:
+                c["schedule"] = (rows - 1, rows, 1)
+            elif kind < 0.8:
+                a0 = int(rng.integers(0, rows))
+                c["schedule"] = (a0, int(rng.integers(a0 + 1, rows + 1)), 1)
+            else:
+                c["schedule"] = (int(rng.integers(0, min(3, rows))), rows, int(rng.integers(2, 4)))
+            if c["var"] not in ("e", "d", "s", "Ds", "side") and rng.random() < 0.5:
+                c["weight_param"] = c["aim_param"] = True  # (allowed on any signal with a plant part)
     if not any(c["var"] == INPUT[system] for c in costs):
         costs.append({"name": "effort", "var": INPUT[system], "weight": 0.01, "weight_param": False,
-                      "aim": [0.0 for _ in axes], "aim_param": False})
+                      "aim": [0.0 for _ in axes], "aim_param": False, "schedule": None})
     spec["costs"] = costs
 
     limits = []
@@ -152,7 +167,8 @@ def build(spec, api, omega, tau, vel, gain, nominal=(0.1, 3.3), backend=None):
     for c in spec["costs"]:
         weight = c["weight"] * gain if c["weight_param"] else c["weight"]
         aim = [a + vel if c["aim_param"] else a for a in c["aim"]]
-        form.incorporate_goal(c["name"], api.Cost(c["var"], weight, aim=aim, axes=axes))
+        kargs = {"schedule": range(*c["schedule"])} if c.get("schedule") else {}
+        form.incorporate_goal(c["name"], api.Cost(c["var"], weight, aim=aim, axes=axes, **kargs))
     for lim in spec["limits"]:
         extreme = lim["extreme"] + vel if lim["extreme_param"] else lim["extreme"]
         kargs = {"axes": lim["axes"], "arrow": np.array(lim["arrow"])}

@@ -103,3 +103,46 @@ def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None):
         q[cols] += w * T.T @ ee
         q[z] += w * Mz.T @ (fr + ee)
     return G, h, P, q
+
+
+def add_scheduled(plan, A, B, given, terms, P, q):
+    """What the stage of csrc/mpci_sched.cu adds for the plan's scheduled costs (include/mpci.h:
+    mpci_lti_sched_desc): ``terms`` [T, 3 + 2n + 2m] of this instance (``plan.sched_tables``
+    row), ``given`` the formulation's given vector (the plant's x0 alone in the plain layout).
+    Returns (P, q) with the terms added."""
+    n, m, N, nv = plan.n, plan.m, plan.N, plan.nv
+    given = np.asarray(given, dtype=np.float64)
+    x0 = given[plan.x0_index] if plan.embedded else given
+    Ae, Be = plan.expand_numpy(A, B)
+    W, xs, x = [Be], [], x0
+    for _ in range(N - 1):
+        W.append(Ae @ W[-1])
+    for _ in range(N):
+        x = Ae @ x
+        xs.append(x)
+    voff = plan.var_off if plan.embedded else [j * N for j in range(m)]
+    tab = plan.sched_desc_tables()
+    P, q = P.copy(), q.copy()
+    r = 0
+    for t, (_w, _fv, _fc, _aim, _caim, samples) in enumerate(plan.sched_terms):
+        w, aim, caim = terms[t, :3]
+        vcx, vcu = terms[t, 3:3 + n], terms[t, 3 + n:3 + n + m]
+        ccx, ccu = terms[t, 3 + n + m:3 + 2 * n + m], terms[t, 3 + 2 * n + m:]
+        for k in samples:
+            rows = []
+            for cx, cu, Mz, Mg in ((vcx, vcu, tab["v_Mz"], tab["v_Mg"]),
+                                   (ccx, ccu, tab["c_Mz"] if tab["c_Mz"] is not None else tab["v_Mz"],
+                                    tab["c_Mg"] if tab["c_Mg"] is not None else tab["v_Mg"])):
+                v = np.zeros([nv])
+                for j in range(m):
+                    for p in range(k + 1):
+                        v[voff[j] + p] = cx @ W[k - p][:, j] + (cu[j] if p == k else 0.0)
+                if Mz is not None:
+                    v[np.array(plan.z_col, dtype=int)] = Mz[r]
+                free = cx @ xs[k] + (Mg[r] @ given if Mg is not None else 0.0)
+                rows.append((v, free))
+            (v, fv), (c, fc) = rows
+            P += w * np.outer(v, c)
+            q += w / 2 * (v * (fc - caim) + c * (fv - aim))
+            r += 1
+    return P, q

@@ -123,7 +123,8 @@ def _header_fields(struct_name):
 
 
 @pytest.mark.parametrize("struct_name,mirror", [("mpci_lti_desc", "LtiDesc"), ("mpci_lti_tables", "LtiTables"),
-                                                ("mpci_lti_embed", "LtiEmbed")])
+                                                ("mpci_lti_embed", "LtiEmbed"),
+                                                ("mpci_lti_sched_desc", "LtiSchedDesc")])
 def test_lti_structs_of_the_binding_match_the_header(struct_name, mirror):
     """The ctypes mirrors in lti.py list the fields of include/mpci.h in the same order with
     the same kinds (int / pointer): a field added on one side only would shift every later one."""
@@ -156,3 +157,29 @@ def test_embedded_plan_validation_needs_no_gpu(lib):
     assert rc < 0 and b"NULL plan" in lib.mpci_last_error()
     assert lib.mpci_extend_matrices_static(None, None, None, None, 1, 0, 1, 5, None) < 0
     assert lib.mpci_extend_static_capacity() == 524288
+
+
+def test_scheduled_cost_stage_validation_needs_no_gpu(lib):
+    """mpci_lti_sched_create / _add refuse malformed descriptions before any CUDA call."""
+    import numpy as np
+    from mpc_interface_b200 import lti
+
+    handle = ctypes.c_void_p()
+    assert lib.mpci_lti_sched_create(None, ctypes.byref(handle)) < 0
+    i32 = lambda *v: np.array(v, dtype=np.int32)  # noqa: E731
+    ptr, rows, zcol = i32(0, 2), i32(1, 4), i32(2)
+
+    def create(n=2, m=1, N=4, nv=5, nz=0, zc=None, rp=ptr, rk=rows, terms=1):
+        desc = lti.LtiSchedDesc(n, m, N, nv, None, nz, zc, 0, terms, rp.ctypes.data, rk.ctypes.data,
+                                None, None, None, None)
+        return lib.mpci_lti_sched_create(ctypes.byref(desc), ctypes.byref(handle))
+
+    assert create() < 0 and b"outside the horizon" in lib.mpci_last_error()  # sample 4 of 4
+    assert create(nv=3, rk=i32(1, 3)) < 0 and b"columns" in lib.mpci_last_error()  # the input does not fit
+    assert create(nz=1, zc=zcol.ctypes.data, rk=i32(1, 3)) < 0 and b"inside input" in lib.mpci_last_error()
+    assert create(terms=0) < 0 and b"bad sizes" in lib.mpci_last_error()
+    assert create(rp=i32(0, 0), rk=i32(1, 3)) < 0 and b"no scheduled rows" in lib.mpci_last_error()
+    assert not handle.value
+    rc = lib.mpci_lti_sched_add(None, None, 0, None, 0, None, None, None, 0, None, None, 1, None)
+    assert rc < 0 and b"null argument" in lib.mpci_last_error()
+    assert lib.mpci_lti_sched_destroy(None) == 0

@@ -43,8 +43,12 @@ def test_lowering_matches_reference(cpu_extend, name, per_instance):
 def test_lowering_refuses_unsupported(cpu_extend):
     g = cases.golden("generic_small")
     form = _formulation(g, cpu_extend, False)
-    form.incorporate_goal("sched", Cost("z0", 1.0, schedule=range(2, 4)))
+    form.incorporate_goal("weighted rows", Cost("z0", 1.0, L=np.eye(int(g["N"]))))
     with pytest.raises(NotImplementedError):
+        form.lti_plan("plant")
+    form = _formulation(g, cpu_extend, False)
+    form.incorporate_goal("sched", Cost("z0", 1.0, schedule=range(2, int(g["N"]) + 1)))
+    with pytest.raises(IndexError):  # (the reference's fancy index fails the same way, body.py:283)
         form.lti_plan("plant")
     form = _formulation(g, cpu_extend, False)
     form.incorporate_definition("mix", LineCombo({"z0": 1.0, "u0": 2.0}))
@@ -235,13 +239,15 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
         cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
 
 
-@pytest.mark.parametrize("seed", range(200, 212))
-def test_random_embedded_formulations_lowering(cpu_extend, seed):
+@pytest.mark.parametrize("seed,scheduled", [(s, False) for s in range(200, 212)] + [(s, True) for s in range(220, 232)])
+def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled):
     """tests/_embedded_forms.py: random structures around a per-instance plant (four named
     plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
     with aims and on signals shorter than the horizon, facets, row-wise arrows, centres,
     schedules, any variable order), lowered and evaluated by the NumPy restatement of the
-    kernels' arithmetic, against the unmodified reference formulating every instance itself."""
+    kernels' arithmetic, against the unmodified reference formulating every instance itself.
+    ``scheduled``: some costs act on a few samples only (terminal, a window, every 2nd / 3rd
+    sample; per-instance weights and aims) -- the stage of csrc/mpci_sched.cu."""
     import _embedded_forms as forms
     from oracle import reference
 
@@ -249,11 +255,12 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed):
         pytest.skip("oracle/_ref is not staged")
     from mpc_interface_b200 import dynamics
 
-    spec = forms.draw(seed)
+    spec = forms.draw(seed, scheduled)
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
                        backend=NumpyBackend())
     plan = form.lti_plan("LIP")
     assert plan.embedded
+    assert len(plan.sched_terms) == sum(len(spec["axes"]) for c in spec["costs"] if c["schedule"])
     batch = 2
     vals = forms.inputs(spec, form, batch, seed + 1000)
     given = np.zeros([batch, form.given_len])
@@ -273,7 +280,62 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed):
                                                  omega=float(vals["omega"][b]))
         got = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], None,
                                            {key: v[b] for key, v in tables.items()}, (ccx[b], ccu[b]))
+        if plan.sched_terms:
+            terms = plan.sched_tables(params, batch)
+            got = got[:2] + _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b],
+                                                     terms[b if terms.shape[0] > 1 else 0], got[2], got[3])
         cases.assert_qp_close(got, want)
+
+
+@pytest.mark.parametrize("per_instance", [False, True])
+def test_generic_mpc_with_a_terminal_cost_lowering(cpu_extend, per_instance):
+    """The textbook terminal cost (x_N - ref)' Qf (x_N - ref) on the generic per-instance MPC:
+    nx^2 crossed costs with schedule = range(N - 1, N) (examples/generic.py), in the plain layout;
+    with ``Param`` references and, in the per-instance variant, a ``Param`` weight on one more
+    scheduled cost.  Against the oracle's restatement of body.py:266-302."""
+    from oracle import qp_oracle
+
+    rng = np.random.default_rng(77)
+    nx, nu, N, batch = 4, 2, 9, 3
+    A = np.eye(nx) + 0.1 * rng.normal(size=[batch, nx, nx])
+    B = 0.3 * rng.normal(size=[batch, nx, nu])
+    M = rng.normal(size=[nx, nx])
+    Q, R, Qf = M @ M.T / nx + np.eye(nx), np.eye(nu), 3.0 * (M.T @ M) / nx + np.eye(nx)
+    refs = [Param("ref%d" % i) for i in range(nx)]
+    form = cases.formulate_generic(A[0], B[0], Q, R, N, rng.normal(size=[2, nx]), refs=refs,
+                                   backend=NumpyBackend(), terminal=Qf)
+    if per_instance:
+        form.incorporate_goal("window", Cost("z1", Param("gain"), aim=[Param("ref0") * 2], schedule=range(2, 7, 2)))
+    plan = form.lti_plan("plant")
+    assert not plan.embedded and len(plan.sched_terms) == nx * nx + (1 if per_instance else 0)
+    x0 = rng.normal(size=[batch, nx])
+    params = {"ref%d" % i: rng.normal(size=batch) for i in range(nx)}
+    params["gain"] = rng.uniform(0.5, 2.0, batch)
+    names = [repr(e) for e in plan.slots.exprs]
+    terms = plan.sched_tables(params, batch)
+    assert terms.shape[0] == batch
+    for b in range(batch):
+        one = {k: float(v[b]) for k, v in params.items()}
+        scalars = np.array([one[nm] for nm in names])
+        G, h, P, q = _lti_numpy.evaluate(plan, A[b], B[b], x0[b], scalars)
+        P, q = _lti_numpy.add_scheduled(plan, A[b], B[b], x0[b], terms[b], P, q)
+        single = cases.formulate_generic(A[b], B[b], Q, R, N, form_rows(form), refs=refs,
+                                         backend=NumpyBackend(), terminal=Qf)
+        if per_instance:
+            single.incorporate_goal("window", Cost("z1", Param("gain"), aim=[Param("ref0") * 2], schedule=range(2, 7, 2)))
+        want = qp_oracle.all_qp_matrices(single, x0[b][:, None], one)
+        cases.assert_qp_close((G, h, P, q), want)
+
+
+def form_rows(form):
+    """The linear rows a generic formulation was built with (its ``lin<r>`` definitions)."""
+    rows = []
+    r = 0
+    while "lin%d" % r in form.definitions:
+        combo = form.definitions["lin%d" % r]
+        rows.append([float(combo.matrices[i]) for i in range(len(combo.variables))])
+        r += 1
+    return np.array(rows)
 
 
 def test_per_instance_tables_built_with_torch_equal_the_numpy_ones(cpu_extend):
