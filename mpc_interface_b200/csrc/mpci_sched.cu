@@ -5,8 +5,8 @@
 // acts on some samples only (goal.py:46-60 `schedule`; the rows sigma of body.py:273-283 -- the
 // terminal cost of an MPC is schedule = range(N - 1, N)) is a sum of a few outer products
 // instead, and is ADDED here to the P and q the assembly wrote, one CTA per instance:
-//   1. W_d = A^d B (d < K) and xs_k = A^{k+1} x0 (k < K), K = 1 + the last scheduled sample, by the
-//      recursion of extend_matrices (tools.py:23-29: u_k = A u_{k-1}, s_k = A s_{k-1})
+//   1. V_d = A^d [B | x0] (d <= K, K = 1 + the last scheduled sample) by prefix doubling, as the
+//      coupling kernel does (what extend_matrices builds by recursion, tools.py:23-29)
 //   2. per scheduled row r = (term t, sample k), a chunk of rows at a time in shared memory:
 //      v_r [nv] = row k of the variable's preview matrix over the optimisation variables,
 //      c_r the crossed variable's, and the given parts fv_r, fc_r
@@ -34,23 +34,45 @@ struct SchedArgs {
   long batch;
 };
 
-// shared memory (doubles): A [n][n] | W [K][n][m] | X [K][n] | V, C [chunk][nv] | epsV, epsC, w [chunk]
+// shared memory (doubles): Mp, Mq [n][n] | S [K + 1][n][m + 1] | V, C [chunk][nv] | epsV, epsC [chunk]
 __host__ __device__ inline size_t fixed_doubles(int n, int m, int K) {
-  return (size_t)n * n + (size_t)K * n * m + (size_t)K * n;
+  const size_t d = (size_t)2 * n * n + (size_t)(K + 1) * n * (m + 1);
+  return (d + 1) & ~(size_t)1;  // (the rows are read 16 bytes at a time)
+}
+
+// P[i .. i + ROWS)[2 j, 2 j + 1] += sum_r (w v_r)[i ..] c_r[2 j ..]: ROWS 16-byte loads in flight per lane
+template <int ROWS>
+__device__ __forceinline__ void update_rows(double* __restrict__ Pb, const double* V, const double* C, int nv,
+                                            int rows, int i, int lane) {
+  const int half = nv >> 1;
+  for (int j = lane; j < half; j += 32) {
+    double2 p[ROWS];
+#pragma unroll
+    for (int u = 0; u < ROWS; ++u) p[u] = reinterpret_cast<const double2*>(Pb + (long)(i + u) * nv)[j];
+    for (int rr = 0; rr < rows; ++rr) {
+      const double2 c = reinterpret_cast<const double2*>(C + (size_t)rr * nv)[j];
+#pragma unroll
+      for (int u = 0; u < ROWS; ++u) {
+        const double v = V[(size_t)rr * nv + i + u];
+        p[u].x = fma(v, c.x, p[u].x), p[u].y = fma(v, c.y, p[u].y);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < ROWS; ++u) reinterpret_cast<double2*>(Pb + (long)(i + u) * nv)[j] = p[u];
+  }
 }
 
 __global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
   extern __shared__ double sched_smem[];
-  const int n = a.n, m = a.m, nv = a.nv, K = a.K, tl = 3 + 2 * a.n + 2 * a.m;
+  const int n = a.n, m = a.m, nv = a.nv, K = a.K, tl = 3 + 2 * a.n + 2 * a.m, w1 = a.m + 1, slab = a.n * w1;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = (int)blockDim.x, nwarps = nthr >> 5;
-  double* As = sched_smem;
-  double* W = As + n * n;
-  double* X = W + (size_t)K * n * m;
-  double* V = X + (size_t)K * n;
+  double* Mp = sched_smem;
+  double* Mq = Mp + n * n;
+  double* S = Mq + n * n;  // S[d][i][c]: c < m: (A^d B)[i][c];  c == m: (A^d x0)[i]
+  double* V = sched_smem + fixed_doubles(n, m, K);
   double* C = V + (size_t)a.chunk * nv;
   double* epsV = C + (size_t)a.chunk * nv;
   double* epsC = epsV + a.chunk;
-  double* wr = epsC + a.chunk;
 
   for (long b = blockIdx.x; b < a.batch; b += gridDim.x) {
     const double* Ab = a.A + b * a.sA;
@@ -59,66 +81,73 @@ __global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
     const double* gb = a.given ? a.given + b * (long)a.glen : nullptr;
     const double* tb = a.terms + b * a.sT;
     __syncthreads();  // (the previous instance's rows are still being read)
-    for (int e = tid; e < n * n; e += nthr) As[e] = Ab[e];
-    for (int e = tid; e < n * m; e += nthr) W[e] = Bb[e];
-    __syncthreads();
-    if (tid < n) {  // xs_0 = A x0
-      double acc = 0.0;
-      for (int i = 0; i < n; ++i) acc = fma(As[tid * n + i], xb[i], acc);
-      X[tid] = acc;
+    for (int e = tid; e < n * n; e += nthr) Mp[e] = Ab[e];
+    for (int e = tid; e < slab; e += nthr) {
+      const int i = e / w1, c = e - i * w1;
+      S[e] = (c < m) ? Bb[i * m + c] : xb[i];
     }
     __syncthreads();
-    for (int d = 1; d < K; ++d) {  // W_d = A W_{d-1},  xs_d = A xs_{d-1}
-      const double* Wp = W + (size_t)(d - 1) * n * m;
-      const double* Xp = X + (size_t)(d - 1) * n;
-      for (int e = tid; e < n * m + n; e += nthr) {
+    double* P0 = Mp;
+    double* P1 = Mq;
+    for (int have = 1; have < K + 1;) {  // S[have .. have + cnt) = A^have S[0 .. cnt)
+      const int cnt = min(have, K + 1 - have);
+      for (int e = tid; e < cnt * slab; e += nthr) {
+        const int d = e / slab, r = e - d * slab, i = r / w1, c = r - i * w1;
+        const double* src = S + (size_t)d * slab + c;
         double acc = 0.0;
-        if (e < n * m) {
-          const int i = e / m, j = e - i * m;
-          for (int l = 0; l < n; ++l) acc = fma(As[i * n + l], Wp[l * m + j], acc);
-          W[(size_t)d * n * m + e] = acc;
-        } else {
-          const int i = e - n * m;
-          for (int l = 0; l < n; ++l) acc = fma(As[i * n + l], Xp[l], acc);
-          X[(size_t)d * n + i] = acc;
+        for (int l = 0; l < n; ++l) acc = fma(P0[i * n + l], src[l * w1], acc);
+        S[(size_t)(have + d) * slab + r] = acc;
+      }
+      if (have + cnt < K + 1) {
+        for (int e = tid; e < n * n; e += nthr) {
+          const int i = e / n, c = e - i * n;
+          double acc = 0.0;
+          for (int l = 0; l < n; ++l) acc = fma(P0[i * n + l], P0[l * n + c], acc);
+          P1[e] = acc;
         }
       }
       __syncthreads();
+      double* t = P0; P0 = P1; P1 = t;
+      have += cnt;
     }
 
     for (int r0 = 0; r0 < a.R; r0 += a.chunk) {
       const int rows = min(a.chunk, a.R - r0);
-      __syncthreads();
+      if (r0) __syncthreads();
       for (int e = tid; e < rows * nv; e += nthr) V[e] = 0.0, C[e] = 0.0;
       __syncthreads();
-      for (int rr = warp; rr < rows; rr += nwarps) {  // a warp per row
+      for (int rr = warp; rr < rows; rr += nwarps) {  // a warp per row; V is kept scaled by the weight
         const int r = r0 + rr, t = a.row_term[r], k = a.row_k[r];
         const double* tt = tb + (long)t * tl;
         const double *vcx = tt + 3, *vcu = vcx + n, *ccx = vcu + m, *ccu = ccx + n;
+        const double w = tt[0];
         double* Vr = V + (size_t)rr * nv;
         double* Cr = C + (size_t)rr * nv;
-        for (int e = lane; e < m * (k + 1); e += 32) {
-          const int j = e / (k + 1), p = e - j * (k + 1);
-          const double* Wd = W + (size_t)(k - p) * n * m + j;
-          double av = p == k ? vcu[j] : 0.0, ac = p == k ? ccu[j] : 0.0;
-          for (int i = 0; i < n; ++i) {
-            const double wv = Wd[i * m];
-            av = fma(vcx[i], wv, av);
-            ac = fma(ccx[i], wv, ac);
+        for (int j = 0; j < m; ++j) {
+          double* Vj = Vr + a.voff[j];
+          double* Cj = Cr + a.voff[j];
+          for (int p = lane; p <= k; p += 32) {
+            const double* Wd = S + (size_t)(k - p) * slab + j;
+            double av = p == k ? vcu[j] : 0.0, ac = p == k ? ccu[j] : 0.0;
+            for (int i = 0; i < n; ++i) {
+              const double wv = Wd[i * w1];
+              av = fma(vcx[i], wv, av);
+              ac = fma(ccx[i], wv, ac);
+            }
+            Vj[p] = w * av;
+            Cj[p] = ac;
           }
-          Vr[a.voff[j] + p] = av;
-          Cr[a.voff[j] + p] = ac;
         }
         const double* cMz = a.cMz ? a.cMz : a.vMz;
         for (int i = lane; i < a.nz; i += 32) {
-          if (a.vMz) Vr[a.zcol[i]] = a.vMz[(size_t)r * a.nz + i];
+          if (a.vMz) Vr[a.zcol[i]] = w * a.vMz[(size_t)r * a.nz + i];
           if (cMz) Cr[a.zcol[i]] = cMz[(size_t)r * a.nz + i];
         }
         // the given parts: cx . A^{k+1} x0 + Mg[r,:] . given
         const double* cMg = a.cMg ? a.cMg : a.vMg;
         double fv = 0.0, fc = 0.0;
         for (int i = lane; i < n; i += 32) {
-          const double xk = X[(size_t)k * n + i];
+          const double xk = S[(size_t)(k + 1) * slab + i * w1 + m];
           fv = fma(vcx[i], xk, fv);
           fc = fma(ccx[i], xk, fc);
         }
@@ -134,20 +163,30 @@ __global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
           fc += __shfl_xor_sync(0xffffffffu, fc, o);
         }
         if (lane == 0) {
-          const double w = tt[0];
-          wr[rr] = w;
-          epsV[rr] = 0.5 * w * (fv - tt[1]);
-          epsC[rr] = 0.5 * w * (fc - tt[2]);
+          epsV[rr] = 0.5 * w * (fv - tt[1]);  // times c_r
+          epsC[rr] = 0.5 * (fc - tt[2]);      // times w v_r
         }
       }
       __syncthreads();
       if (a.P) {
         double* Pb = a.P + b * (long)nv * nv;
-        for (long e = tid; e < (long)nv * nv; e += nthr) {
-          const int i = (int)(e / nv), j = (int)(e - (long)i * nv);
-          double acc = 0.0;
-          for (int rr = 0; rr < rows; ++rr) acc = fma(wr[rr] * V[(size_t)rr * nv + i], C[(size_t)rr * nv + j], acc);
-          Pb[e] += acc;
+        if ((nv & 1) == 0 && (reinterpret_cast<size_t>(Pb) & 15) == 0) {
+          // four rows of P per warp pass, 16 bytes per lane and row
+          for (int i = 4 * warp; i < nv; i += 4 * nwarps) {
+            if (i + 4 <= nv)
+              update_rows<4>(Pb, V, C, nv, rows, i, lane);
+            else
+              update_rows<2>(Pb, V, C, nv, rows, i, lane);
+          }
+        } else {
+          for (int i = warp; i < nv; i += nwarps) {
+            double* Pi = Pb + (long)i * nv;
+            for (int j = lane; j < nv; j += 32) {
+              double acc = Pi[j];
+              for (int rr = 0; rr < rows; ++rr) acc = fma(V[(size_t)rr * nv + i], C[(size_t)rr * nv + j], acc);
+              Pi[j] = acc;
+            }
+          }
         }
       }
       if (a.q) {
@@ -233,7 +272,7 @@ extern "C" int mpci_lti_sched_create(const mpci_lti_sched_desc* d, mpci_lti_sche
   s->n = d->n, s->m = d->m, s->N = d->N, s->nv = d->nv, s->nz = d->nz, s->glen = d->given_len;
   s->T = d->n_terms, s->R = R, s->K = K;
   const size_t fixed = fixed_doubles(d->n, d->m, K) * sizeof(double);
-  const size_t per_row = ((size_t)2 * d->nv + 3) * sizeof(double);
+  const size_t per_row = ((size_t)2 * d->nv + 2) * sizeof(double);
   size_t chunk = std::max<size_t>(1, kRowBudget / per_row);
   chunk = std::min<size_t>(chunk, (size_t)R);
   if (fixed + per_row > kSmemLimit) {

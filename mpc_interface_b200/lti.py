@@ -494,21 +494,64 @@ class LtiPlan:
         return out
 
     # ---- costs with a schedule ---------------------------------------------------
+    def sched_layout(self):
+        """The stage's terms: one per scheduled cost and axis, except that costs on plant
+        STATES alone which share their samples -- the nx^2 crossed costs of a dense terminal weight
+        (x_N - r)' Qf (x_N - r) -- are merged into n terms per group: with Qk = sum_t w_t cx_t cc_t^T
+        and tx = sum_t w_t / 2 (cx_t caim_t + cc_t aim_t), the group adds T_k^T Qk T_k to P and
+        T_k^T ((Qk + Qk^T) / 2 x_k - tx) to q, which are n outer products per sample (term a: the
+        variable's form e_a, the cross form Qk[a, :], weight 1, aims (0, 2 tx[a])) instead of one
+        per cost.  Entries: ("one", index into sched_terms) / ("merged", [indices], a)."""
+        groups, layout = {}, []
+        for i, (_w, fv, fc, _aim, _caim, samples) in enumerate(self.sched_terms):
+            states_only = not (fv.touches_inputs() or fc.touches_inputs() or fv.has_aux() or fc.has_aux())
+            if states_only:
+                groups.setdefault(tuple(samples), []).append(i)
+            else:
+                layout.append(("one", i))
+        for members in groups.values():
+            if len(members) > self.n:
+                layout += [("merged", members, a) for a in range(self.n)]
+            else:
+                layout += [("one", i) for i in members]
+        return layout
+
     def sched_tables(self, params, batch, dev=None):
-        """terms [R, T, 3 + 2n + 2m] of mpci_lti_sched_add -- per term (w, aim, caim, v_cx, v_cu,
-        c_cx, c_cu); R = batch when anything in them is per-instance, else 1."""
+        """terms [R, T, 3 + 2n + 2m] of mpci_lti_sched_add -- per term of ``sched_layout`` (w, aim,
+        caim, v_cx, v_cu, c_cx, c_cu); R = batch when anything in them is per-instance, else 1."""
         xp = _Host if dev is None else _Device(dev)
         params = xp.params(params, batch)
-        n, m, T = self.n, self.m, len(self.sched_terms)
+        n, m = self.n, self.m
+        layout = self.sched_layout()
         symbolic = any(is_expr(x) for x in self._sched_exprs())
-        out = xp.zeros([batch if symbolic else 1, T, 3 + 2 * n + 2 * m])
-        for t, (w, fv, fc, aim, caim, _rows) in enumerate(self.sched_terms):
-            for col, x in enumerate((w, aim, caim)):
-                out[:, t, col] = _value(x, params)
-            out[:, t, 3:3 + n] = _dense(fv.cx, n, params, batch, xp)
-            out[:, t, 3 + n:3 + n + m] = _dense(fv.cu, m, params, batch, xp)
-            out[:, t, 3 + n + m:3 + 2 * n + m] = _dense(fc.cx, n, params, batch, xp)
-            out[:, t, 3 + 2 * n + m:] = _dense(fc.cu, m, params, batch, xp)
+        out = xp.zeros([batch if symbolic else 1, len(layout), 3 + 2 * n + 2 * m])
+        merged = {}
+        for t, entry in enumerate(layout):
+            if entry[0] == "one":
+                w, fv, fc, aim, caim, _rows = self.sched_terms[entry[1]]
+                for col, x in enumerate((w, aim, caim)):
+                    out[:, t, col] = _value(x, params)
+                out[:, t, 3:3 + n] = _dense(fv.cx, n, params, batch, xp)
+                out[:, t, 3 + n:3 + n + m] = _dense(fv.cu, m, params, batch, xp)
+                out[:, t, 3 + n + m:3 + 2 * n + m] = _dense(fc.cx, n, params, batch, xp)
+                out[:, t, 3 + 2 * n + m:] = _dense(fc.cu, m, params, batch, xp)
+                continue
+            _kind, members, a = entry
+            key = tuple(members)
+            if key not in merged:
+                Qk, tx = xp.zeros([1, n, n]), xp.zeros([1, n])
+                for i in members:
+                    w, fv, fc, aim, caim, _rows = self.sched_terms[i]
+                    wv = _value(w, params)
+                    cv, cc = _dense(fv.cx, n, params, batch, xp), _dense(fc.cx, n, params, batch, xp)
+                    Qk = Qk + _col(wv, 2) * cv[:, :, None] * cc[:, None, :]
+                    tx = tx + _col(wv, 1) / 2 * (_col(_value(caim, params), 1) * cv + _col(_value(aim, params), 1) * cc)
+                merged[key] = (Qk, tx)
+            Qk, tx = merged[key]
+            out[:, t, 0] = 1.0
+            out[:, t, 2] = 2.0 * tx[:, a]
+            out[:, t, 3 + a] = 1.0
+            out[:, t, 3 + n + m:3 + 2 * n + m] = Qk[:, a, :]
         return out
 
     def _sched_exprs(self):
@@ -520,24 +563,28 @@ class LtiPlan:
         return out
 
     def sched_desc_tables(self):
-        """The constant tables of mpci_lti_sched_desc (include/mpci.h)."""
+        """The constant tables of mpci_lti_sched_desc (include/mpci.h), terms as ``sched_layout``."""
         i32 = lambda x: np.ascontiguousarray(x, dtype=np.int32)  # noqa: E731
         nz, ng = self.nz, (self.ng if self.embedded else 0)
+        layout = self.sched_layout()
         ptr, rows = [0], []
-        for *_r, samples in self.sched_terms:
-            rows += list(samples)
+        for entry in layout:
+            rows += list(self.sched_terms[entry[1] if entry[0] == "one" else entry[1][0]][5])
             ptr.append(len(rows))
 
         def stack(which, attr, width):
-            if not width or not any(getattr(term[which], attr) is not None for term in self.sched_terms):
+            singles = [self.sched_terms[e[1]] for e in layout if e[0] == "one"]
+            if not width or not any(getattr(term[which], attr) is not None for term in singles):
                 return None
             blocks = []
-            for term in self.sched_terms:
-                M = getattr(term[which], attr)
-                blocks.append(np.zeros([len(term[5]), width]) if M is None else np.asarray(M)[list(term[5])])
+            for t, entry in enumerate(layout):
+                count = ptr[t + 1] - ptr[t]
+                term = self.sched_terms[entry[1]] if entry[0] == "one" else None
+                M = getattr(term[which], attr) if term is not None else None
+                blocks.append(np.zeros([count, width]) if M is None else np.asarray(M)[list(term[5])])
             return np.ascontiguousarray(np.vstack(blocks), dtype=np.float64)
 
-        crossed = any(fv is not fc for _w, fv, fc, *_r in self.sched_terms)
+        crossed = any(e[0] == "one" and self.sched_terms[e[1]][1] is not self.sched_terms[e[1]][2] for e in layout)
         t = dict(row_ptr=i32(ptr), row_k=i32(rows), v_Mz=stack(1, "Mz", nz), v_Mg=stack(1, "Mg", ng),
                  c_Mz=stack(2, "Mz", nz) if crossed else None, c_Mg=stack(2, "Mg", ng) if crossed else None,
                  var_off=i32(self.var_off) if self.embedded else None,
@@ -648,7 +695,7 @@ class _DeviceLtiSched:
         t = self._keep = plan.sched_desc_tables()
         at = lambda k: t[k].ctypes.data if t[k] is not None else None  # noqa: E731
         desc = LtiSchedDesc(plan.n, plan.m, plan.N, plan.nv, at("var_off"), plan.nz, at("z_col"),
-                            plan.ng if plan.embedded else 0, len(plan.sched_terms), at("row_ptr"), at("row_k"),
+                            plan.ng if plan.embedded else 0, len(t["row_ptr"]) - 1, at("row_ptr"), at("row_k"),
                             at("v_Mz"), at("v_Mg"), at("c_Mz"), at("c_Mg"))
         handle = ctypes.c_void_p()
         device.check(device.lib().mpci_lti_sched_create(ctypes.byref(desc), ctypes.byref(handle)))

@@ -107,8 +107,8 @@ def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None):
 
 def add_scheduled(plan, A, B, given, terms, P, q):
     """What the stage of csrc/mpci_sched.cu adds for the plan's scheduled costs (include/mpci.h:
-    mpci_lti_sched_desc): ``terms`` [T, 3 + 2n + 2m] of this instance (``plan.sched_tables``
-    row), ``given`` the formulation's given vector (the plant's x0 alone in the plain layout).
+    mpci_lti_sched_desc), from the tables the stage gets: ``terms`` [T, 3 + 2n + 2m] of this
+    instance (``plan.sched_tables`` row) and ``plan.sched_desc_tables``, ``given`` the formulation's given vector (the plant's x0 alone in the plain layout).
     Returns (P, q) with the terms added."""
     n, m, N, nv = plan.n, plan.m, plan.N, plan.nv
     given = np.asarray(given, dtype=np.float64)
@@ -123,12 +123,12 @@ def add_scheduled(plan, A, B, given, terms, P, q):
     voff = plan.var_off if plan.embedded else [j * N for j in range(m)]
     tab = plan.sched_desc_tables()
     P, q = P.copy(), q.copy()
-    r = 0
-    for t, (_w, _fv, _fc, _aim, _caim, samples) in enumerate(plan.sched_terms):
+    for t in range(len(tab["row_ptr"]) - 1):
         w, aim, caim = terms[t, :3]
         vcx, vcu = terms[t, 3:3 + n], terms[t, 3 + n:3 + n + m]
         ccx, ccu = terms[t, 3 + n + m:3 + 2 * n + m], terms[t, 3 + 2 * n + m:]
-        for k in samples:
+        for r in range(tab["row_ptr"][t], tab["row_ptr"][t + 1]):
+            k = int(tab["row_k"][r])
             rows = []
             for cx, cu, Mz, Mg in ((vcx, vcu, tab["v_Mz"], tab["v_Mg"]),
                                    (ccx, ccu, tab["c_Mz"] if tab["c_Mz"] is not None else tab["v_Mz"],
@@ -144,5 +144,4 @@ def add_scheduled(plan, A, B, given, terms, P, q):
             (v, fv), (c, fc) = rows
             P += w * np.outer(v, c)
             q += w / 2 * (v * (fc - caim) + c * (fv - aim))
-            r += 1
     return P, q

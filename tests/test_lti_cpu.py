@@ -308,6 +308,9 @@ def test_generic_mpc_with_a_terminal_cost_lowering(cpu_extend, per_instance):
         form.incorporate_goal("window", Cost("z1", Param("gain"), aim=[Param("ref0") * 2], schedule=range(2, 7, 2)))
     plan = form.lti_plan("plant")
     assert not plan.embedded and len(plan.sched_terms) == nx * nx + (1 if per_instance else 0)
+    # the nx^2 crossed costs share their sample: nx merged terms (T_N' Qf T_N), the window stays one
+    assert [e[0] for e in plan.sched_layout()].count("merged") == nx
+    assert len(plan.sched_layout()) == nx + (1 if per_instance else 0)
     x0 = rng.normal(size=[batch, nx])
     params = {"ref%d" % i: rng.normal(size=batch) for i in range(nx)}
     params["gain"] = rng.uniform(0.5, 2.0, batch)
