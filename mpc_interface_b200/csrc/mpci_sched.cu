@@ -52,9 +52,10 @@ __device__ __forceinline__ void update_rows(double* __restrict__ Pb, const doubl
     for (int rr = 0; rr < rows; ++rr) {
       const double2 c = reinterpret_cast<const double2*>(C + (size_t)rr * nv)[j];
 #pragma unroll
-      for (int u = 0; u < ROWS; ++u) {
-        const double v = V[(size_t)rr * nv + i + u];
-        p[u].x = fma(v, c.x, p[u].x), p[u].y = fma(v, c.y, p[u].y);
+      for (int u = 0; u < ROWS; u += 2) {  // (i is even and so is nv: 16-byte broadcasts)
+        const double2 v = *reinterpret_cast<const double2*>(V + (size_t)rr * nv + i + u);
+        p[u].x = fma(v.x, c.x, p[u].x), p[u].y = fma(v.x, c.y, p[u].y);
+        p[u + 1].x = fma(v.y, c.x, p[u + 1].x), p[u + 1].y = fma(v.y, c.y, p[u + 1].y);
       }
     }
 #pragma unroll
