@@ -20,9 +20,10 @@ no slower fallback):
     ``Param`` expression: the LIP's centre of pressure ``b = CoM - CoM_ddot / omega_b^2``
     with one pendulum frequency per instance (biped_formulation.py:62);
   * costs: scalar weight (number or ``Param``), no ``L``, aims that are numbers or ``Param``
-    expressions, optional ``cross``, one or several axes; a cost over the whole horizon may
-    not mix states and inputs; a cost with a ``schedule`` (a terminal cost: ``range(N - 1, N)``;
-    any list of samples) is added to P and q by a second stage (csrc/mpci_sched.cu);
+    expressions, optional ``cross``, one or several axes; a cost with a ``schedule`` (a terminal
+    cost: ``range(N - 1, N)``; any list of samples) is added to P and q by a second stage
+    (csrc/mpci_sched.cu), and so is -- row by row over the whole horizon -- a cost that couples
+    states and inputs;
   * limits: no ``L``; ``schedule`` a contiguous ``range`` (the terminal constraint of the
     biped, biped_formulation.py:97-102); one axis with ``arrow`` / ``center`` / ``extreme``
     of one row or one row per sample, or several axes with a single-row ``arrow`` (a facet
@@ -589,9 +590,11 @@ class LtiPlan:
                  c_Mz=stack(2, "Mz", nz) if crossed else None, c_Mg=stack(2, "Mg", ng) if crossed else None,
                  var_off=i32(self.var_off) if self.embedded else None,
                  z_col=i32(self.z_col) if nz else None)
-        for own, cross in (("v_Mz", "c_Mz"), ("v_Mg", "c_Mg")):  # (the C side wants the own table beside a crossed one)
-            if t[cross] is not None and t[own] is None:
+        for own, cross in (("v_Mz", "c_Mz"), ("v_Mg", "c_Mg")):
+            if t[cross] is not None and t[own] is None:  # (the C side wants the own table beside a crossed one)
                 t[own] = np.zeros_like(t[cross])
+            if crossed and t[own] is not None and t[cross] is None:  # (NULL would mean "the variable's own")
+                t[cross] = np.zeros_like(t[own])
         return t
 
     def device_sched(self):
@@ -942,27 +945,26 @@ def lower(form, plant_name):
         for a, ax in enumerate(cost.axes):
             vname, cname = cost.variable + ax, cost.cross + ax
             fv, fc = form_of(vname, "a cost"), form_of(cname, "a cost")
-            if cost.schedule:  # some samples only: no stage weight, added by the stage of mpci_sched.cu
+            aim = _single(np.asarray(cost.aim, dtype=object)[:, a], "an aim")
+            caim = _single(np.asarray(cost.cross_aim, dtype=object)[:, a], "an aim")
+            # What the fused kernel's stage weights (and the coupling stage's constant tables) cannot
+            # express goes through the general stage of mpci_sched.cu, row by row: a schedule; a cost
+            # that couples states and inputs (no Qxu block in T' Qxx T + Quu x I); a crossed cost or a
+            # per-instance weight / aim on a signal with a part outside the plant.
+            mixes = (fv.touches_states() and fc.touches_inputs()) or (fv.touches_inputs() and fc.touches_states())
+            outside = fv.has_aux() or fc.has_aux()
+            general = mixes or (outside and (fv is not fc or is_expr(w) or is_expr(aim) or is_expr(caim)))
+            if cost.schedule or general:
                 rows = N if (fv.has_plant() or fc.has_plant() or not plan.embedded) else fv.rows
                 if rows is None or rows > N or (fc.rows is not None and not fc.has_plant() and fc.rows < rows):
-                    _unsupported("a scheduled cost on '{}' ({} samples, the horizon has {})".format(vname, rows, N))
-                samples = [int(k) for k in cost.schedule]
+                    _unsupported("a cost on '{}' ({} samples, the horizon has {})".format(vname, rows, N))
+                samples = [int(k) for k in cost.schedule] if cost.schedule else list(range(rows))
                 if any(k < 0 or k >= rows for k in samples):
                     raise IndexError("index {} is out of bounds for axis 0 with size {}".format(
                         next(k for k in samples if k < 0 or k >= rows), rows))
-                aim = _single(np.asarray(cost.aim, dtype=object)[:, a], "an aim")
-                caim = _single(np.asarray(cost.cross_aim, dtype=object)[:, a], "an aim")
                 plan.sched_terms.append((w, fv, fc, aim, caim, samples))
                 continue
-            if (fv.touches_states() and fc.touches_inputs()) or (fv.touches_inputs() and fc.touches_states()):
-                _unsupported("a cost that couples states and inputs")
-            aim = _single(np.asarray(cost.aim, dtype=object)[:, a], "an aim")
-            caim = _single(np.asarray(cost.cross_aim, dtype=object)[:, a], "an aim")
-            if fv.has_aux() or fc.has_aux():
-                if fv is not fc:
-                    _unsupported("a crossed cost on variables outside the plant")
-                if is_expr(w) or is_expr(aim):
-                    _unsupported("a per-instance weight or aim of a cost on variables outside the plant")
+            if outside:
                 rows = fv.rows
                 if rows != N and (fv.has_plant() or rows > N):
                     _unsupported("a cost on '{}' ({} samples, the horizon has {})".format(vname, rows, N))

@@ -22,9 +22,12 @@ INPUT = {"dP->CCC": "cCoP_dot", "J->CCC": "CoM_dddot", "dP->CCP": "cCoP_dot", "P
 OMEGA_COEFS = ("inv", "neg_inv2", "times", "num")
 
 
-def draw(seed, scheduled=False):
+def draw(seed, scheduled=False, general=False):
     """The structure as plain data (a dict of lists and numbers).  ``scheduled``: some of the
-    costs act on a few samples only (goal.py `schedule`)."""
+    costs act on a few samples only (goal.py `schedule`).  ``general``: also costs that the stage
+    weights of the fused kernel cannot express -- crossed costs between any two signals, per-instance
+    weights and aims on signals with a part outside the plant, a definition that mixes states and
+    the input."""
     rng = np.random.default_rng(seed)
     system = SYSTEMS[rng.integers(len(SYSTEMS))]
     axes = ["_x", "_y"] if rng.random() < 0.4 else ["_x"]
@@ -64,6 +67,8 @@ def draw(seed, scheduled=False):
         defs.append(("side", aux_terms()))
     if rng.random() < 0.5:
         defs.append(("mix2", [("mix", "num", float(rng.uniform(0.5, 2.0)))] + plant_terms(1)))
+    if general and rng.random() < 0.7:
+        defs.append(("ux", plant_terms(1) + [(INPUT[system], "num", float(rng.uniform(-0.5, 0.5)))]))
     spec["defs"] = defs
     names = plant_vars + [d[0] for d in defs] + aux_vars + (["Ds"] if has_s else [])
     inside = set(plant_vars + ["u1"])
@@ -90,9 +95,18 @@ def draw(seed, scheduled=False):
                 c["schedule"] = (int(rng.integers(0, min(3, rows))), rows, int(rng.integers(2, 4)))
             if c["var"] not in ("e", "d", "s", "Ds", "side") and rng.random() < 0.5:
                 c["weight_param"] = c["aim_param"] = True  # (allowed on any signal with a plant part)
+    for c in costs:
+        c["cross"] = None
+        if general and c["var"] != "Ds":
+            if rng.random() < 0.4:
+                others = [v for v in names if v not in ("Ds", c["var"])]
+                c["cross"] = str(others[rng.integers(len(others))])
+                c["cross_aim"] = [float(rng.uniform(-0.2, 0.2)) for _ in axes]
+            if rng.random() < 0.4:
+                c["weight_param"] = c["aim_param"] = True
     if not any(c["var"] == INPUT[system] for c in costs):
         costs.append({"name": "effort", "var": INPUT[system], "weight": 0.01, "weight_param": False,
-                      "aim": [0.0 for _ in axes], "aim_param": False, "schedule": None})
+                      "aim": [0.0 for _ in axes], "aim_param": False, "schedule": None, "cross": None})
     spec["costs"] = costs
 
     limits = []
@@ -168,6 +182,8 @@ def build(spec, api, omega, tau, vel, gain, nominal=(0.1, 3.3), backend=None):
         weight = c["weight"] * gain if c["weight_param"] else c["weight"]
         aim = [a + vel if c["aim_param"] else a for a in c["aim"]]
         kargs = {"schedule": range(*c["schedule"])} if c.get("schedule") else {}
+        if c.get("cross"):
+            kargs.update(cross=c["cross"], cross_aim=[x + vel if c["aim_param"] else x for x in c["cross_aim"]])
         form.incorporate_goal(c["name"], api.Cost(c["var"], weight, aim=aim, axes=axes, **kargs))
     for lim in spec["limits"]:
         extreme = lim["extreme"] + vel if lim["extreme_param"] else lim["extreme"]

@@ -142,3 +142,45 @@ def test_biped_with_per_instance_plants_and_a_terminal_cost(system, N, batch):
         got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
         for b in range(batch):
             cases.assert_qp_close(tuple(x[b] for x in got), wants[b])
+
+
+def test_costs_beyond_the_stage_weights_on_generic_plants(monkeypatch):
+    """A cost that couples states and inputs (a LineCombo of a state and an input: no Qxu block in
+    T' Qxx T + Quu x I) and a crossed state x input cost are lowered to whole-horizon terms of the
+    scheduled-cost stage -- N rows each, several chunks of shared memory -- instead of being refused."""
+    import mpc_interface_b200.tools as tools
+    from _numpy_backend import NumpyBackend
+    from mpc_interface_b200 import Cost, LineCombo, Param
+    from mpc_interface_b200.examples import synthetic
+
+    nx, nu, N, batch = 5, 2, 120, 7
+    _, _, Q, R = synthetic.generic_system(61, nx, nu)
+    A, B = synthetic.generic_plants(61, batch, nx, nu)
+    A = np.eye(nx) + 0.2 * (A - np.eye(nx))  # (N = 120: keep A^N moderate)
+    rows = np.random.default_rng(62).normal(size=[2, nx])
+    vals = synthetic.generic_inputs(61, batch, nx)
+    gain = np.random.default_rng(63).uniform(0.5, 2.0, batch)
+
+    def build(b, refs, weight, backend=None):
+        f = cases.formulate_generic(A[b], B[b], Q, R, N, rows, refs=refs, backend=backend)
+        f.incorporate_definition("mix", LineCombo({"z0": 1.0, "u1": 2.0, "z3": -0.5}))
+        f.incorporate_goal("mixed", Cost("mix", weight, aim=[refs[1]]))
+        f.incorporate_goal("state x input", Cost("z2", 0.3, aim=[0.1], cross="u0", cross_aim=[refs[0]]))
+        f.make_preview_matrices()
+        return f
+
+    form = build(0, [Param("ref%d" % i) for i in range(nx)], Param("gain"))
+    plan = form.lti_plan("plant")
+    assert [t[5] for t in plan.sched_terms] == [list(range(N))] * 2
+    params = {"ref%d" % i: vals["ref"][:, i] for i in range(nx)}
+    params["gain"] = gain
+    outs = {}
+    for mode in ("dmma", "recursion"):
+        out = form.generate_all_qp_matrices_batched(vals["x0"], params, dynamics={"plant": (A, B)}, hessian=mode)
+        outs[mode] = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+    monkeypatch.setattr(tools, "extend_matrices", orc.extend_matrices)
+    for b in (0, 3, batch - 1):
+        ref_form = build(b, [float(x) for x in vals["ref"][b]], float(gain[b]), backend=NumpyBackend())
+        ref = orc.all_qp_matrices(ref_form, vals["x0"][b][:, None])
+        for mode in outs:
+            cases.assert_qp_close([x[b] for x in outs[mode]], ref)

@@ -51,11 +51,6 @@ def test_lowering_refuses_unsupported(cpu_extend):
     with pytest.raises(IndexError):  # (the reference's fancy index fails the same way, body.py:283)
         form.lti_plan("plant")
     form = _formulation(g, cpu_extend, False)
-    form.incorporate_definition("mix", LineCombo({"z0": 1.0, "u0": 2.0}))
-    form.incorporate_goal("mixed", Cost("mix", 1.0))
-    with pytest.raises(NotImplementedError):
-        form.lti_plan("plant")
-    form = _formulation(g, cpu_extend, False)
     form.incorporate_constraint("L", Constraint("z1", 3.0, L=np.eye(int(g["N"]))))
     with pytest.raises(NotImplementedError):
         form.lti_plan("plant")
@@ -239,15 +234,18 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
         cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
 
 
-@pytest.mark.parametrize("seed,scheduled", [(s, False) for s in range(200, 212)] + [(s, True) for s in range(220, 232)])
-def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled):
+@pytest.mark.parametrize("seed,scheduled,general", [(s, False, False) for s in range(200, 212)]
+                         + [(s, True, False) for s in range(220, 232)] + [(s, True, True) for s in range(240, 256)])
+def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, general):
     """tests/_embedded_forms.py: random structures around a per-instance plant (four named
     plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
     with aims and on signals shorter than the horizon, facets, row-wise arrows, centres,
     schedules, any variable order), lowered and evaluated by the NumPy restatement of the
     kernels' arithmetic, against the unmodified reference formulating every instance itself.
     ``scheduled``: some costs act on a few samples only (terminal, a window, every 2nd / 3rd
-    sample; per-instance weights and aims) -- the stage of csrc/mpci_sched.cu."""
+    sample; per-instance weights and aims) -- the stage of csrc/mpci_sched.cu.  ``general``: also
+    crossed costs between any two signals, per-instance weights / aims on signals with a part outside
+    the plant and a definition that mixes states and the input (whole-horizon terms of that stage)."""
     import _embedded_forms as forms
     from oracle import reference
 
@@ -255,12 +253,13 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled):
         pytest.skip("oracle/_ref is not staged")
     from mpc_interface_b200 import dynamics
 
-    spec = forms.draw(seed, scheduled)
+    spec = forms.draw(seed, scheduled, general)
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
                        backend=NumpyBackend())
     plan = form.lti_plan("LIP")
     assert plan.embedded
-    assert len(plan.sched_terms) == sum(len(spec["axes"]) for c in spec["costs"] if c["schedule"])
+    if not general:
+        assert len(plan.sched_terms) == sum(len(spec["axes"]) for c in spec["costs"] if c["schedule"])
     batch = 2
     vals = forms.inputs(spec, form, batch, seed + 1000)
     given = np.zeros([batch, form.given_len])
@@ -364,15 +363,54 @@ def test_embedded_lowering_refuses_what_the_coupling_stage_cannot_do(cpu_extend)
 
     conf = biped.default_configuration(16)
     form = biped.formulate_biped(conf, backend=NumpyBackend())
-    form.incorporate_goal("steps", Cost("(c-s)", Param("w_steps"), aim=[0, 0], axes=["_x", "_y"]))
-    with pytest.raises(NotImplementedError, match="per-instance weight"):
-        form.lti_plan("LIP")
-    form = biped.formulate_biped(conf, backend=NumpyBackend())
-    form.incorporate_goal("crossed", Cost("(c-s)", 1.0, cross="CoM", axes=["_x"]))
-    with pytest.raises(NotImplementedError, match="crossed"):
-        form.lti_plan("LIP")
-    form = biped.formulate_biped(conf, backend=NumpyBackend())
     form.incorporate_definition("odd_x", LineCombo({"CoM_x": np.eye(16), "s_x": 1.0}))
     form.incorporate_goal("odd", Cost("odd", 1.0, axes=["_x"]))
     with pytest.raises(NotImplementedError, match="matrix coefficient"):
         form.lti_plan("LIP")
+
+
+def test_costs_beyond_the_stage_weights_take_the_general_stage(cpu_extend):
+    """What T' Qxx T + Quu x I and the coupling stage's constant tables cannot express is lowered
+    to whole-horizon terms of the scheduled-cost stage instead of being refused: a cost that
+    couples states and inputs (generic plant), a per-instance weight and aim on a signal with a
+    footstep part and a crossed cost on it (biped).  Against the oracle's body.py:266-302."""
+    from mpc_interface_b200.examples import biped, synthetic
+    from oracle import qp_oracle
+
+    g = cases.golden("generic_small")
+    form = _formulation(g, cpu_extend, False)
+    form.incorporate_definition("mix", LineCombo({"z0": 1.0, "u0": 2.0}))
+    form.incorporate_goal("mixed", Cost("mix", 1.5, aim=[Param("ref0")]))
+    form.make_preview_matrices()
+    plan = form.lti_plan("plant")
+    N = int(g["N"])
+    assert len(plan.sched_terms) == 1 and plan.sched_terms[0][5] == list(range(N))
+    names = [repr(e) for e in plan.slots.exprs]
+    batch = g["x0"].shape[0]
+    params = {"ref%d" % i: g["ref"][:, i] for i in range(g["ref"].shape[1])}
+    terms = plan.sched_tables(params, batch)
+    for b in range(batch):
+        one = {k: float(v[b]) for k, v in params.items()}
+        G, h, P, q = _lti_numpy.evaluate(plan, g["A_sys"], g["B_sys"], g["x0"][b], np.array([one[nm] for nm in names]))
+        P, q = _lti_numpy.add_scheduled(plan, g["A_sys"], g["B_sys"], g["x0"][b], terms[b if terms.shape[0] > 1 else 0], P, q)
+        cases.assert_qp_close((G, h, P, q), qp_oracle.all_qp_matrices(form, g["x0"][b][:, None], one))
+
+    N, batch = 16, 3
+    conf = biped.default_configuration(N)
+    form = biped.formulate_biped(conf, backend=NumpyBackend())
+    form.incorporate_goal("steps", Cost("(c-s)", Param("w_steps"), aim=[Param("lead"), 0], axes=["_x", "_y"]))
+    form.incorporate_goal("crossed", Cost("(c-s)", 0.7, aim=[0.05], cross="CoM", cross_aim=[0.1], axes=["_x"]))
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and len(plan.sched_terms) == 3 and not plan.per_instance
+    vals = synthetic.biped_inputs(5, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {"w_steps": np.array([0.5, 1.0, 2.0]), "lead": np.array([0.0, 0.1, -0.2])}
+    terms = plan.sched_tables(params, batch)
+    assert terms.shape[0] == batch
+    from mpc_interface_b200 import dynamics
+    plant = dynamics.ControlSystem.from_name(conf.system, ["_x"], tau=conf.mpc_period, omega=conf.omega)
+    for b in range(batch):
+        one = {k: float(v[b]) for k, v in params.items()}
+        got = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], np.zeros([0]))
+        P, q = _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b], terms[b], got[2], got[3])
+        cases.assert_qp_close((got[0], got[1], P, q), qp_oracle.all_qp_matrices(form, given[b][:, None], one))
