@@ -1199,6 +1199,8 @@ def assemble_host(plan, A, B, x0, params=None, hessian=HESSIAN_DMMA, chunk=256, 
 
     from . import device
 
+    if plan.per_instance or plan.sched_terms or plan.embedded:
+        return _assemble_host_chunks(plan, A, B, x0, params, hessian, chunk, out)
     dp = plan.device_plan()
     n, m = plan.n, plan.m
     A, B, x0, scalars, batch = _host_inputs(plan, A, B, x0, params)
@@ -1214,6 +1216,59 @@ def assemble_host(plan, A, B, x0, params=None, hessian=HESSIAN_DMMA, chunk=256, 
         )
     )
     return out
+
+
+def _assemble_host_chunks(plan, A, B, x0, params, hessian, chunk, out):
+    """HOST results for the plans ``mpci_lti_assemble_host`` does not take (per-instance tables,
+    an embedded layout, scheduled costs): chunks of instances through ``LtiJob`` on two streams
+    with two device slots -- chunk c's four device-to-host copies (into pinned memory) run behind
+    chunk c + 1's kernels.  ``x0`` [batch, given_len] in the formulation's given order."""
+    import torch
+
+    from . import device
+
+    device.require_gpu()
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    if x0.ndim != 2:
+        raise ValueError("the given vectors must be [batch, {}]".format(plan.ng))
+    batch = x0.shape[0]
+    if not torch.is_tensor(A):
+        A = np.asarray(A, dtype=np.float64)
+    if not torch.is_tensor(B):
+        B = np.asarray(B, dtype=np.float64)
+    if out is None:
+        shapes = ([batch, plan.nv, plan.nv], [batch, plan.nv], [batch, plan.nc, plan.nv], [batch, plan.nc])
+        out = tuple(torch.empty(shape, dtype=torch.float64).pin_memory() for shape in shapes)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    chunk = max(1, min(int(chunk), batch))
+    slots = [device.QPBatch(chunk, plan.nv, plan.nc, dev) for _ in range(2 if batch > chunk else 1)]
+    streams = [torch.cuda.Stream(device=dev) for _ in slots]
+    part = lambda v, lo, hi: v[lo:hi] if (hasattr(v, "__len__") and len(v) == batch) else v  # noqa: E731
+    jobs = []
+    for c, lo in enumerate(range(0, batch, chunk)):
+        hi = min(lo + chunk, batch)
+        slot, stream = slots[c % len(slots)], streams[c % len(slots)]
+        view = slot if hi - lo == chunk else _slot_view(slot, hi - lo)
+        with torch.cuda.stream(stream):
+            job = LtiJob(plan, part(A, lo, hi) if A.ndim == 3 else A, part(B, lo, hi) if B.ndim == 3 else B,
+                         x0[lo:hi], {k: part(v, lo, hi) for k, v in (params or {}).items()})
+            job.launch(view, hessian)
+            for host, devt in zip(out, (view.P, view.q, view.G, view.h)):
+                host[lo:hi].copy_(devt, non_blocking=True)
+        jobs.append(job)  # (inputs stay alive until the streams are drained)
+    for stream in streams:
+        stream.synchronize()
+    return out
+
+
+def _slot_view(slot, count):
+    """The first ``count`` instances of a device slot as a QPBatch."""
+    from . import device
+
+    view = device.QPBatch.__new__(device.QPBatch)
+    view.batch, view.nv, view.nc = count, slot.nv, slot.nc
+    view.P, view.q, view.G, view.h = slot.P[:count], slot.q[:count], slot.G[:count], slot.h[:count]
+    return view
 
 
 def assemble_host_stream(plan, A, B, x0, out, ring, params=None, hessian=HESSIAN_RECURSION, chunk=256,

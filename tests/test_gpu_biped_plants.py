@@ -285,3 +285,29 @@ def test_receding_tick_with_per_instance_plants():
         _one, want = _reference_instance(conf, vals, b, dict(step_times=times[b], step_count=int(count[b])))
         cases.assert_qp_close(tuple(x[0].cpu().numpy() for x in (qp.G, qp.h, qp.P, qp.q)), want)
     assert seen == batch
+
+
+def test_biped_plants_host_results():
+    """``lti.assemble_host`` on an embedded plan with per-instance tables: chunks of instances
+    through the two kernels on two streams, results in pinned host memory, bit-identical with
+    the device-resident call (ragged last chunk; the named plants as CUDA tensors)."""
+    import torch
+
+    from mpc_interface_b200 import Param, lti
+    from mpc_interface_b200.examples import biped, synthetic
+
+    N, batch = 24, 11
+    conf = biped.default_configuration(N)
+    conf.system = "dP->CCC"
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    vals = synthetic.biped_inputs(31, batch, N)
+    vals["tau"] = np.random.default_rng(2).uniform(0.08, 0.12, batch)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    plan = form.lti_plan("LIP")
+    A, B = lti.named_system_batched("dP->CCC", vals["tau"], vals["omega"])
+    want = lti.assemble(plan, A, B, given, params, hessian=lti.HESSIAN_RECURSION)
+    host = lti.assemble_host(plan, A, B, given, params, hessian=lti.HESSIAN_RECURSION, chunk=4)
+    for got, ref in zip(host, (want.P, want.q, want.G, want.h)):
+        assert got.is_pinned() and torch.equal(got, ref.cpu())

@@ -70,7 +70,8 @@ def test_generic_mpc_with_a_terminal_cost(monkeypatch, nx, nu, N, batch, window)
 
 def test_scheduled_costs_partial_outputs_and_refusals():
     """``parts``: the stage adds to the outputs that were asked for and leaves the others alone;
-    the host-buffer entry points refuse such a plan (no silent omission of the terminal cost)."""
+    ``assemble_host`` returns the same in host memory; the ring entry point refuses such a plan (no
+    silent omission of the terminal cost)."""
     import torch
 
     from mpc_interface_b200 import Param, device, lti
@@ -99,8 +100,12 @@ def test_scheduled_costs_partial_outputs_and_refusals():
                 assert torch.equal(got, want), (parts, tag)
             else:
                 assert bool((got == -7.0).all()), (parts, tag)
+    # HOST results: chunks through the same two launches (6 instances, chunks of 4 + 2)
+    host = lti.assemble_host(plan, A, B, vals["x0"], params, chunk=4)
+    for got, want in zip(host, (full.P, full.q, full.G, full.h)):
+        assert torch.equal(got, want.cpu())
     with pytest.raises(NotImplementedError, match="schedule"):
-        lti.assemble_host(plan, A, B, vals["x0"], params)
+        lti.assemble_host_stream(plan, A, B, vals["x0"], host, 1, params)
     with pytest.raises(KeyError, match="ref1"):
         lti.LtiJob(plan, A, B, vals["x0"], {"ref0": vals["ref"][:, 0]})
 
