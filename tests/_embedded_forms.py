@@ -22,12 +22,14 @@ INPUT = {"dP->CCC": "cCoP_dot", "J->CCC": "CoM_dddot", "dP->CCP": "cCoP_dot", "P
 OMEGA_COEFS = ("inv", "neg_inv2", "times", "num")
 
 
-def draw(seed, scheduled=False, general=False):
+def draw(seed, scheduled=False, general=False, with_L=False):
     """The structure as plain data (a dict of lists and numbers).  ``scheduled``: some of the
     costs act on a few samples only (goal.py `schedule`).  ``general``: also costs that the stage
     weights of the fused kernel cannot express -- crossed costs between any two signals, per-instance
     weights and aims on signals with a part outside the plant, a definition that mixes states and
-    the input."""
+    the input.  ``with_L``: some uncrossed costs and some limits combine their samples through a
+    matrix ``L`` (goal.py:88-104, restrictions.py:75-90) -- mode A only, the per-instance path
+    refuses ``L``."""
     rng = np.random.default_rng(seed)
     system = SYSTEMS[rng.integers(len(SYSTEMS))]
     axes = ["_x", "_y"] if rng.random() < 0.4 else ["_x"]
@@ -135,6 +137,23 @@ def draw(seed, scheduled=False, general=False):
     optim += ["e" + ax for ax in axes] if has_e else []
     optim += ["Ds" + ax for ax in axes] if has_s else []
     spec["order"] = [optim[i] for i in rng.permutation(len(optim))]
+    if with_L:
+        def samples_of(var, schedule):
+            rows = spec["steps_U"].shape[1] if var == "Ds" else N
+            return rows if schedule is None else len(range(*schedule))
+
+        for c in costs:
+            c["L"] = None
+            stepped = c["schedule"] is not None and c["schedule"][2] != 1  # (L counts stop - start columns)
+            if c["cross"] is None and not stepped and rng.random() < 0.5:
+                c["L"] = rng.normal(size=[int(rng.integers(1, 5)), samples_of(c["var"], c["schedule"])])
+        for lim in limits:
+            lim["L"] = None
+            if rng.random() < 0.5:
+                schedule = None if lim["schedule"] is None else lim["schedule"] + (1,)
+                lines = int(rng.integers(1, 5))
+                lim["L"] = rng.normal(size=[lines, samples_of(lim["var"], schedule)])
+                lim["arrow"] = np.array(lim["arrow"])[:1]  # (one arrow for all lines)
     return spec
 
 
@@ -182,6 +201,8 @@ def build(spec, api, omega, tau, vel, gain, nominal=(0.1, 3.3), backend=None):
         weight = c["weight"] * gain if c["weight_param"] else c["weight"]
         aim = [a + vel if c["aim_param"] else a for a in c["aim"]]
         kargs = {"schedule": range(*c["schedule"])} if c.get("schedule") else {}
+        if c.get("L") is not None:
+            kargs["L"] = [np.array(c["L"]) for _ in axes]
         if c.get("cross"):
             kargs.update(cross=c["cross"], cross_aim=[x + vel if c["aim_param"] else x for x in c["cross_aim"]])
         form.incorporate_goal(c["name"], api.Cost(c["var"], weight, aim=aim, axes=axes, **kargs))
@@ -192,6 +213,8 @@ def build(spec, api, omega, tau, vel, gain, nominal=(0.1, 3.3), backend=None):
             kargs["schedule"] = range(*lim["schedule"])
         if lim["center"] is not None:
             kargs["center"] = np.array(lim["center"])
+        if lim.get("L") is not None:
+            kargs["L"] = [np.array(lim["L"]) for _ in lim["axes"]]
         form.incorporate_constraint(lim["name"], [api.Constraint(lim["var"], extreme, **kargs)])
     form.identify_qp_domain(list(spec["order"]))
     form.make_preview_matrices()

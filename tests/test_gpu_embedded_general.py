@@ -125,3 +125,37 @@ def test_random_embedded_formulations_against_the_live_reference(seed, scheduled
             except AssertionError as e:
                 raise AssertionError("seed {} instance {} ({}; {} {} N {}): {}".format(
                     seed, b, mode, spec["system"], spec["axes"], spec["N"], e))
+
+
+@pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
+@pytest.mark.parametrize("seed", range(600, 632))
+def test_random_formulations_with_a_shared_plant_against_the_live_reference(seed):
+    """The same random structures through MODE A (the headline path: shared plant, affine plan,
+    `stream_terms` / `qh` kernels): omega and tau are numbers, the per-instance parameters are the
+    aims / bounds (`vel`) and the weights (`gain`); scheduled, crossed and state-input costs and
+    costs / limits with a matrix ``L`` over their samples included -- mode A takes them all.  Every
+    instance against the unmodified reference."""
+    import _embedded_forms as forms
+    from mpc_interface_b200 import Param
+
+    spec = forms.draw(seed, scheduled=True, general=True, with_L=True)
+    omega, tau = 3.4, 0.1 * min(1.0, 30.0 / spec["N"])
+    form = forms.build(spec, forms.own_api(), omega, tau, Param("vel"), Param("gain"))
+    batch = 5
+    vals = forms.inputs(spec, form, batch, seed + 1000)
+    given = np.zeros([batch, form.given_len])
+    for name, ids in form.given_ID.items():
+        given[:, ids.start:ids.stop] = vals[name]
+    out = form.generate_all_qp_matrices_batched(given, {"vel": vals["vel"], "gain": vals["gain"]})
+    got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+    api = forms.reference_api(reference.load())
+    for b in range(batch):
+        one = forms.build(spec, api, omega, tau, float(vals["vel"][b]), float(vals["gain"][b]))
+        assert list(one.optim_ID.items()) == list(form.optim_ID.items())
+        want = one.generate_all_qp_matrices(one.arrange_given(
+            {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
+        try:
+            cases.assert_qp_close(tuple(x[b] for x in got), want)
+        except AssertionError as e:
+            raise AssertionError("seed {} instance {} ({} {} N {}): {}".format(
+                seed, b, spec["system"], spec["axes"], spec["N"], e))

@@ -230,6 +230,35 @@ def test_random_formulations_against_reference(cpu_extend, seed):
     cases.assert_qp_close((out.G, out.h, out.P, out.q), ref)
 
 
+@pytest.mark.parametrize("seed", range(640, 652))
+def test_random_structures_around_a_shared_plant_against_the_live_reference(cpu_extend, seed):
+    """tests/_embedded_forms.py in mode A (the compiled affine plan, evaluated by the NumPy
+    backend): named plants, slack / footsteps / disturbance, scheduled, crossed and state-input
+    costs, ``L`` on costs and limits; per-instance aims / bounds and weights.  Every instance
+    formulated by the unmodified reference."""
+    import _embedded_forms as forms
+    from mpc_interface_b200 import Param
+    from oracle import reference
+
+    if not reference.available():
+        pytest.skip("oracle/_ref is not staged")
+    spec = forms.draw(seed, scheduled=True, general=True, with_L=True)
+    omega, tau = 3.4, 0.1 * min(1.0, 30.0 / spec["N"])
+    form = forms.build(spec, forms.own_api(), omega, tau, Param("vel"), Param("gain"), backend=NumpyBackend())
+    batch = 3
+    vals = forms.inputs(spec, form, batch, seed + 1000)
+    given = np.zeros([batch, form.given_len])
+    for name, ids in form.given_ID.items():
+        given[:, ids.start:ids.stop] = vals[name]
+    out = form.generate_all_qp_matrices_batched(given, {"vel": vals["vel"], "gain": vals["gain"]})
+    api = forms.reference_api(reference.load())
+    for b in range(batch):
+        one = forms.build(spec, api, omega, tau, float(vals["vel"][b]), float(vals["gain"][b]))
+        want = one.generate_all_qp_matrices(one.arrange_given(
+            {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
+        cases.assert_qp_close((out.G[b], out.h[b], out.P[b], out.q[b]), want)
+
+
 def test_negative_per_instance_extreme_is_refused(cpu_extend):
     """The reference flips a limit with a negative extreme (restrictions.py:190-194);
     for a Param extreme the batch is checked and refused instead of differing."""
