@@ -146,7 +146,11 @@ def test_random_formulations_with_a_shared_plant_against_the_live_reference(seed
     given = np.zeros([batch, form.given_len])
     for name, ids in form.given_ID.items():
         given[:, ids.start:ids.stop] = vals[name]
-    out = form.generate_all_qp_matrices_batched(given, {"vel": vals["vel"], "gain": vals["gain"]})
+    import scipy.sparse as sp
+
+    params = {"vel": vals["vel"], "gain": vals["gain"]}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    compact = form.generate_all_qp_matrices_batched(given, params, layout="csc")  # the solver hand-off
     got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
     api = forms.reference_api(reference.load())
     for b in range(batch):
@@ -156,6 +160,10 @@ def test_random_formulations_with_a_shared_plant_against_the_live_reference(seed
             {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
         try:
             cases.assert_qp_close(tuple(x[b] for x in got), want)
+            for mine, dense in zip(compact.csc(b), (want[2], want[0])):  # biped_mpc_loop.py:57-58
+                ref = sp.csc_matrix(dense)
+                assert np.array_equal(mine.indptr, ref.indptr) and np.array_equal(mine.indices, ref.indices)
+                assert cases.rel_err(mine.data, ref.data) <= cases.TOL
         except AssertionError as e:
             raise AssertionError("seed {} instance {} ({} {} N {}): {}".format(
                 seed, b, spec["system"], spec["axes"], spec["N"], e))
