@@ -152,10 +152,20 @@ def test_random_formulations_with_a_shared_plant_against_the_live_reference(seed
     out = form.generate_all_qp_matrices_batched(given, params)
     compact = form.generate_all_qp_matrices_batched(given, params, layout="csc")  # the solver hand-off
     got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+    # the step after a solve (body.py:209-234): every definition previewed from ONE launch, the goals' distances
+    optim = np.random.default_rng(seed + 7).normal(size=[batch, form.optim_len]) * 0.1
+    previews = {k: v.cpu().numpy() for k, v in form.preview_all_batched(given, optim, params=params).items()}
+    distance = form.full_goal_distance_batched(given, optim, params=params).cpu().numpy()
     api = forms.reference_api(reference.load())
     for b in range(batch):
         one = forms.build(spec, api, omega, tau, float(vals["vel"][b]), float(vals["gain"][b]))
         assert list(one.optim_ID.items()) == list(form.optim_ID.items())
+        g_b = one.arrange_given({name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID})
+        for name in one.definitions:
+            want_v = one.preview(g_b, optim[b][:, None], name)[:, 0]
+            assert cases.rel_err(previews[name][b], want_v) <= cases.TOL, (seed, b, name)
+        want_d = one.full_goal_distance(g_b, optim[b][:, None])
+        assert abs(distance[b] - want_d) <= cases.TOL * max(1.0, abs(want_d)), (seed, b)
         want = one.generate_all_qp_matrices(one.arrange_given(
             {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
         try:
