@@ -367,6 +367,26 @@ int mpci_lti_assemble_coupled(const mpci_lti_plan* plan, const double* A_dev, lo
                               double* G_dev, double* h_dev, long batch, int hessian_mode,
                               void* stream);
 
+/* mpci_lti_assemble_coupled with every per-instance table of the coupled costs: besides the signal
+ * tables, one WEIGHT per instance and cost (cost_w [batch][n_costs], replacing the plan's cost_w --
+ * the caller then also passes Pzz [batch][nz][nz] = sum_c w_c Mz_c^T Mz_c for its weights) and one
+ * AIM per instance and cost (cost_aim [batch][n_costs], subtracted from every sample of e_c on top
+ * of the constant column of the plan's cost_e map).  Any pointer may be NULL (= the plan's / zero). */
+typedef struct {
+  const double* cost_cx;   /* [batch][n_costs][n] */
+  const double* cost_cu;   /* [batch][n_costs][m] */
+  const double* cost_w;    /* [batch][n_costs]    */
+  const double* cost_aim;  /* [batch][n_costs]    */
+  const double* Pzz;       /* [batch][nz][nz]     */
+} mpci_lti_coupled_tables;
+int mpci_lti_assemble_coupled_ex(const mpci_lti_plan* plan, const double* A_dev, long strideA,
+                                 const double* B_dev, long strideB, const double* x0_dev,
+                                 const double* given_dev, const double* scalars_dev,
+                                 const mpci_lti_tables* per_instance,
+                                 const mpci_lti_coupled_tables* coupled, double* P_dev, double* q_dev,
+                                 double* G_dev, double* h_dev, long batch, int hessian_mode,
+                                 void* stream);
+
 /* ---- costs with a `schedule` on the per-instance path ---------------------------------
  * A Cost whose `schedule` picks some samples of the horizon (goal.py:46-60; the rows `sigma`
  * of body.py:273-283 -- a terminal cost is schedule = range(N - 1, N)) has no time-invariant

@@ -29,7 +29,8 @@ struct CoupleArgs {
 
   const int *voff, *zcol;
   const double *ccx, *ccu;  // [nC][n], [nC][m] (+ instance strides)
-  long sccx, sccu;
+  long sccx, sccu, scw;     // (scw: stride of the per-instance weights and aims, 0 = the plan's / none)
+  const double* caim;       // [batch][nC] per-instance aims, or nullptr
   const double *cw, *MzT;   // [nC], [nC][nz][N]
   const unsigned char* act; // [nC][nz]: column z of Mz_c is not identically zero
   const int *d_ptr, *d_tau; // CSR over (c, z) of the column differences Mz[tau] - Mz[tau-1]
@@ -128,6 +129,7 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
         double acc = 0.0;
         for (int z = a.e_ptr[c * N + d]; z < a.e_ptr[c * N + d + 1]; ++z)
           acc = fma(a.e_val[z], gv[a.e_col[z]], acc);
+        if (a.caim) acc -= a.caim[b * (long)nC + c];
         ee[c * N + d] = acc;
         eps[c * N + d] = fr + acc;
       }
@@ -143,7 +145,7 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
           const double* mz = a.MzT + ((size_t)c * nz + z) * N;
           double s = 0.0;
           for (int k = lane; k < N; k += 32) s = fma(__ldg(mz + k), eps[c * N + k], s);
-          acc = fma(a.cw[c], s, acc);
+          acc = fma(a.cw[b * a.scw + c], s, acc);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -158,7 +160,7 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
           const double* ev = ee + c * N + p;
           double s = 0.0;
           for (int t = 0; t < N - p; ++t) s = fma(h_[t], ev[t], s);
-          acc = fma(a.cw[c], s, acc);
+          acc = fma(a.cw[b * a.scw + c], s, acc);
         }
         qb[a.voff[j] + p] += acc;
       }
@@ -325,15 +327,18 @@ void couple_destroy(CouplePlan* p) {
 }
 
 int couple_launch(const CouplePlan* p, const double* A, long strideA, const double* B, long strideB,
-                  const double* x0, const double* given, const double* cost_cx, const double* cost_cu,
+                  const double* x0, const double* given, const mpci_lti_coupled_tables* ct,
                   double* q, double* G, double* h, long batch, cudaStream_t stream) {
   if (batch == 0 || (!q && !G && !h)) return 0;
   CoupleArgs a = p->args;
   if (a.glen && !given) return fail(-3, "lti_assemble_coupled: NULL given");
   a.A = A; a.B = B; a.x0 = x0; a.given = given; a.sA = strideA; a.sB = strideB;
-  a.sccx = a.sccu = 0;
-  if (cost_cx) { a.ccx = cost_cx; a.sccx = (long)a.nC * a.n; }
-  if (cost_cu) { a.ccu = cost_cu; a.sccu = (long)a.nC * a.m; }
+  a.sccx = a.sccu = a.scw = 0;
+  a.caim = nullptr;
+  if (ct && ct->cost_cx) { a.ccx = ct->cost_cx; a.sccx = (long)a.nC * a.n; }
+  if (ct && ct->cost_cu) { a.ccu = ct->cost_cu; a.sccu = (long)a.nC * a.m; }
+  if (ct && ct->cost_w) { a.cw = ct->cost_w; a.scw = a.nC; }
+  if (ct && ct->cost_aim) a.caim = ct->cost_aim;
   a.q = q; a.G = G; a.h = h; a.batch = batch;
   int dev = 0, sms = 148;
   MPCI_CUDA(cudaGetDevice(&dev));

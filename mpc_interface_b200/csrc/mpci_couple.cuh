@@ -25,10 +25,10 @@ struct CoupleShare {
 void couple_share(const CouplePlan* p, CoupleShare* out);
 
 // Runs after the fused kernel on the same stream (it adds to the q and h that kernel wrote; all
-// of P is the fused kernel's).  cost_cx / cost_cu: per-instance signal tables
-// [batch][n_costs][n] / [batch][n_costs][m], or nullptr for the plan's.  Any output may be nullptr.
+// of P is the fused kernel's).  ct: per-instance tables of the coupled costs (signal forms, weights,
+// aims; include/mpci.h), nullptr or NULL members for the plan's.  Any output may be nullptr.
 int couple_launch(const CouplePlan* p, const double* A, long strideA, const double* B, long strideB,
-                  const double* x0, const double* given, const double* cost_cx, const double* cost_cu,
+                  const double* x0, const double* given, const mpci_lti_coupled_tables* ct,
                   double* q, double* G, double* h, long batch, cudaStream_t stream);
 
 }  // namespace mpci

@@ -82,7 +82,7 @@ struct LtiArgs {
   // their Mz as CSR differences over (cost, z), and the constant block Pzz
   int nC;
   const double *ccx, *ccu, *ccw, *d_val, *Pzz;
-  long sccx, sccu;
+  long sccx, sccu, sccw, sPzz;  // (instance strides, 0 = the plan's table)
   const int *d_ptr, *d_tau;
 };
 
@@ -1199,7 +1199,7 @@ __device__ void coupled_hessian_emb(const LtiArgs& a, const Smem& s, long b, dou
         const int lo = max(a.d_tau[x], p) - p - 1;
         sum = fma(a.d_val[x], lo >= 0 ? top - H[lo] : top, sum);
       }
-      acc = fma(a.ccw[c], sum, acc);
+      acc = fma(a.ccw[b * a.sccw + c], sum, acc);
     }
     return acc;
   };
@@ -1216,7 +1216,7 @@ __device__ void coupled_hessian_emb(const LtiArgs& a, const Smem& s, long b, dou
   }
   for (int e = tid; e < nz * nz; e += nthr) {
     const int z = e / nz, y = e - z * nz;
-    __stcs(Pb + (long)a.zcol[z] * nv + a.zcol[y], __ldg(a.Pzz + e));
+    __stcs(Pb + (long)a.zcol[z] * nv + a.zcol[y], __ldg(a.Pzz + b * a.sPzz + e));
   }
   __syncthreads();  // aux is free again
 }
@@ -1433,12 +1433,14 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
       (d->n_groups && (!d->grp_cx || !d->grp_cu || !d->grp_arrow || !d->grp_bound)))
     return mpci::fail(-3, "lti_plan_create: NULL table");
   const int n = d->n, m = d->m, N = d->N, S = d->n_scalars, G = d->n_groups;
+  // (coupled_hessian_emb keeps 2 n_costs m N doubles in the aux region)
+  const size_t aux_floor = emb ? (size_t)2 * (emb->n_costs > 0 ? emb->n_costs : 0) * m * N : 0;
   const int pads[2] = {kPadL, 0};
   int LDs[2], LDws[2];
   size_t smems[2], auxs[2];
   for (int mode = 0; mode < 2; ++mode) {
     LDs[mode] = LDws[mode] = lti_row_len(N, pads[mode]);
-    auxs[mode] = lti_aux_doubles(m, N, 0);
+    auxs[mode] = lti_aux_doubles(m, N, std::max<size_t>(0, aux_floor));
     smems[mode] = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], auxs[mode]);
   }
   // The DMMA scans of the recursion mode: skewed rows, the warps' T patches, and their
@@ -1450,7 +1452,7 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
   int scan = 0, ldp = 0, scan_warps = 0;
   if (lti_mats_doubles(n, m) + lti_gz_doubles(n, m, LDg_scan) >= 48) {
     auto bytes_with = [&](size_t patches) {
-      return sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, lti_aux_doubles(m, N, patches));
+      return sizeof(double) * lti_smem_doubles(n, m, N, LDg_scan, LDw_scan, lti_aux_doubles(m, N, std::max<size_t>(patches, aux_floor)));
     };
     if (N <= 60) {  // (lane 31 must neither own a column nor hold the virtual P[N][N])
       ldp = lti_rows_ldp(N);
@@ -1464,12 +1466,12 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
         scan = 2;
         scan_warps = 4;
         while (scan_warps < kWarps && ctas(scan_warps + 1) >= target) ++scan_warps;
-        auxs[1] = lti_aux_doubles(m, N, scan_warps * patch);
+        auxs[1] = lti_aux_doubles(m, N, std::max<size_t>(scan_warps * patch, aux_floor));
       }
     }
     if (!scan && bytes_with((size_t)kWarps * 8 * 40) <= 227 * 1024) {
       scan = 1;
-      auxs[1] = lti_aux_doubles(m, N, (size_t)kWarps * 8 * 40);
+      auxs[1] = lti_aux_doubles(m, N, std::max<size_t>((size_t)kWarps * 8 * 40, aux_floor));
     }
     if (scan) {
       LDs[1] = LDg_scan;
@@ -1567,7 +1569,7 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
     // one CTA per SM: give it more warps if its shared memory (larger T-patch area) still fits
     size_t aux_wide = auxs[mode];  // the band scan keeps one T patch per warp
     if (mode == MPCI_LTI_HESSIAN_RECURSION && scan == 1)
-      aux_wide = lti_aux_doubles(m, N, (size_t)(kWideThreads / 32) * 8 * 40);
+      aux_wide = lti_aux_doubles(m, N, std::max<size_t>((size_t)(kWideThreads / 32) * 8 * 40, aux_floor));
     const size_t wide = sizeof(double) * lti_smem_doubles(n, m, N, LDs[mode], LDws[mode], aux_wide) + emb_bytes;
     int fit = 0;
     if (wide <= 227 * 1024)
@@ -1610,7 +1612,7 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
     a.Gz = sh.Gz; a.zcol = sh.z_col; a.nz = sh.nz;
     a.nC = sh.n_costs; a.ccx = sh.cost_cx; a.ccu = sh.cost_cu; a.ccw = sh.cost_w;
     a.d_ptr = sh.d_ptr; a.d_tau = sh.d_tau; a.d_val = sh.d_val; a.Pzz = sh.Pzz;
-    a.sccx = a.sccu = 0;
+    a.sccx = a.sccu = a.sccw = a.sPzz = 0;
     a.emb_even = (emb->nv_total % 2 == 0);
     for (int j = 0; j < m; ++j) a.emb_even = a.emb_even && (emb->var_off[j] % 2 == 0);
   }
@@ -1686,7 +1688,7 @@ static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, con
                       long strideB, const double* x0, const double* scalars,
                       const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
                       long batch, int mode, void* stream, bool coupled = false,
-                      const double* cost_cx = nullptr, const double* cost_cu = nullptr);
+                      const mpci_lti_coupled_tables* ct = nullptr);
 
 extern "C" int mpci_lti_assemble(const mpci_lti_plan* p, const double* A, long strideA,
                                  const double* B, long strideB, const double* x0,
@@ -1711,23 +1713,41 @@ extern "C" int mpci_lti_assemble_coupled(const mpci_lti_plan* p, const double* A
                                          const mpci_lti_tables* tab, const double* cost_cx,
                                          const double* cost_cu, double* P, double* q, double* G,
                                          double* h, long batch, int mode, void* stream) {
+  mpci_lti_coupled_tables ct{};
+  ct.cost_cx = cost_cx;
+  ct.cost_cu = cost_cu;
+  return mpci_lti_assemble_coupled_ex(p, A, strideA, B, strideB, x0, given, scalars, tab, &ct, P, q, G, h, batch,
+                                      mode, stream);
+}
+
+extern "C" int mpci_lti_assemble_coupled_ex(const mpci_lti_plan* p, const double* A, long strideA,
+                                            const double* B, long strideB, const double* x0,
+                                            const double* given, const double* scalars,
+                                            const mpci_lti_tables* tab, const mpci_lti_coupled_tables* ct,
+                                            double* P, double* q, double* G, double* h, long batch,
+                                            int mode, void* stream) {
   if (!p) return mpci::fail(-3, "lti_assemble_coupled: NULL plan");
   if (!p->embedded)
     return mpci::fail(-1, "lti_assemble_coupled: the plan was not created by mpci_lti_plan_create_embedded");
   if (tab && (tab->tx || tab->tu) && p->S != 0)
     return mpci::fail(-1, "lti_assemble_coupled: per-instance tx / tu need a plan with n_scalars = 0");
-  int rc = lti_launch(p, A, strideA, B, strideB, x0, scalars, tab, P, q, G, h, batch, mode, stream, true,
-                      cost_cx, cost_cu);
+  if (ct && ct->cost_w && !ct->Pzz) {
+    mpci::CoupleShare sh;
+    mpci::couple_share(p->couple, &sh);
+    if (sh.nz > 0)
+      return mpci::fail(-1, "lti_assemble_coupled: per-instance cost_w needs the per-instance Pzz of those weights");
+  }
+  int rc = lti_launch(p, A, strideA, B, strideB, x0, scalars, tab, P, q, G, h, batch, mode, stream, true, ct);
   if (rc) return rc;
-  return mpci::couple_launch(p->couple, A, strideA, B, strideB, x0, given, cost_cx, cost_cu, q, G, h,
-                             batch, mpci::as_stream(stream));
+  return mpci::couple_launch(p->couple, A, strideA, B, strideB, x0, given, ct, q, G, h, batch,
+                             mpci::as_stream(stream));
 }
 
 static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, const double* B,
                       long strideB, const double* x0, const double* scalars,
                       const mpci_lti_tables* tab, double* P, double* q, double* G, double* h,
-                      long batch, int mode, void* stream, bool coupled, const double* cost_cx,
-                      const double* cost_cu) {
+                      long batch, int mode, void* stream, bool coupled,
+                      const mpci_lti_coupled_tables* ct) {
   if (!p) return mpci::fail(-3, "lti_assemble: NULL plan");
   if (p->embedded && !coupled)
     return mpci::fail(-1, "lti_assemble: a plan with the embedded layout runs through mpci_lti_assemble_coupled");
@@ -1750,8 +1770,10 @@ static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, con
   a.A = A; a.B = B; a.x0 = x0; a.scalars = scalars; a.strideA = strideA; a.strideB = strideB;
   a.P = P; a.q = q; a.G = G; a.h = h; a.batch = batch; a.hessian_mode = mode;
   a.sQ = a.sR = a.sTx = a.sTu = a.scx = a.scu = a.sbd = 0;
-  if (cost_cx) { a.ccx = cost_cx; a.sccx = (long)a.nC * p->n; }
-  if (cost_cu) { a.ccu = cost_cu; a.sccu = (long)a.nC * p->m; }
+  if (ct && ct->cost_cx) { a.ccx = ct->cost_cx; a.sccx = (long)a.nC * p->n; }
+  if (ct && ct->cost_cu) { a.ccu = ct->cost_cu; a.sccu = (long)a.nC * p->m; }
+  if (ct && ct->cost_w) { a.ccw = ct->cost_w; a.sccw = a.nC; }
+  if (ct && ct->Pzz) { a.Pzz = ct->Pzz; a.sPzz = (long)a.nz * a.nz; }
   if (tab) {  // per-instance tables replace the plan's
     const long n = p->n, m = p->m, Gn = p->n_groups, N = p->N;
     if (tab->Qxx) { a.Qxx = tab->Qxx; a.sQ = n * n; }

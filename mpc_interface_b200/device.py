@@ -147,6 +147,13 @@ _SIGNATURES = {
         + [_c_double_p] * 4
         + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p],
     ),
+    "mpci_lti_assemble_coupled_ex": (
+        ctypes.c_int,
+        [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
+         _c_double_p, _c_double_p, ctypes.c_void_p, ctypes.c_void_p]
+        + [_c_double_p] * 4
+        + [ctypes.c_long, ctypes.c_int, ctypes.c_void_p],
+    ),
     "mpci_lti_sched_create": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
     "mpci_lti_sched_destroy": (ctypes.c_int, [ctypes.c_void_p]),
     "mpci_lti_sched_add": (

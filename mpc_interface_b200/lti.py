@@ -48,6 +48,12 @@ HESSIAN_RECURSION = 1
 NAMED_SYSTEMS = {"J->CCC": (0, 3), "P->CC": (1, 2), "P->X": (2, 1), "dP->CCC": (3, 3), "dP->CCP": (4, 3)}
 
 
+class LtiCoupledTables(ctypes.Structure):
+    """mpci_lti_coupled_tables of include/mpci.h"""
+
+    _fields_ = [(name, ctypes.c_void_p) for name in ("cost_cx", "cost_cu", "cost_w", "cost_aim", "Pzz")]
+
+
 class LtiSchedDesc(ctypes.Structure):
     """mpci_lti_sched_desc of include/mpci.h"""
 
@@ -290,6 +296,8 @@ class LtiPlan:
         self.group_row0 = []  # first row of every plant group in G / h
         self.coupled = []     # costs on signals with an auxiliary part: (w, form, Mz [N,nz], E [N,ng+1])
         self.Pzz = self.Gz = self.Hg = self.row_kind = None
+        self.coupled_aims = []  # per coupled cost: its aim when that is a Param expression, else None
+        self.Pzz_terms = []     # (Param weight, Mz' Mz) of the coupled costs with a per-instance weight
         # costs with a schedule (the stage of csrc/mpci_sched.cu, added to P and q afterwards):
         # (weight, form, cross form, aim, cross aim, samples [list of k])
         self.sched_terms = []
@@ -423,7 +431,7 @@ class LtiPlan:
         h_ptr, h_col, h_val = csr(self.Hg)
         MzT = np.stack([Mz.T for _w, _f, Mz, _E in self.coupled]) if nC else np.zeros([0, nz, N])
         return dict(var_off=i32(self.var_off), grp_row0=i32(self.group_row0), z_col=i32(self.z_col),
-                    cost_cx=f64(cx), cost_cu=f64(cu), cost_w=f64([w for w, *_r in self.coupled]),
+                    cost_cx=f64(cx), cost_cu=f64(cu), cost_w=f64([0.0 if is_expr(w) else w for w, *_r in self.coupled]),
                     cost_MzT=f64(MzT), cost_e_ptr=e_ptr, cost_e_col=e_col, cost_e_val=e_val,
                     Pzz=f64(self.Pzz), Gz=f64(self.Gz), h_ptr=h_ptr, h_col=h_col, h_val=h_val,
                     row_kind=i32(self.row_kind))
@@ -439,6 +447,32 @@ class LtiPlan:
             cx[:, c] = _dense(fv.cx, self.n, params, batch, xp)
             cu[:, c] = _dense(fv.cu, self.m, params, batch, xp)
         return cx, cu
+
+    def coupled_symbolic(self):
+        """Whether anything about the coupled costs differs between the instances."""
+        return bool(self.Pzz_terms) or any(a is not None for a in self.coupled_aims) or any(
+            is_expr(w) or fv.symbolic() for w, fv, _Mz, _E in self.coupled)
+
+    def coupled_extras(self, params, batch, dev=None):
+        """(cost_w [B, nC], cost_aim [B, nC], Pzz [B, nz, nz]) of mpci_lti_coupled_tables for the
+        coupled costs with a per-instance weight / aim -- each None when nothing in it varies."""
+        xp = _Host if dev is None else _Device(dev)
+        params = xp.params(params, batch)
+        nC, nz = len(self.coupled), self.nz
+        w = aim = Pzz = None
+        if any(is_expr(wc) for wc, *_r in self.coupled):
+            w = xp.zeros([batch, nC])
+            for c, (wc, *_r) in enumerate(self.coupled):
+                w[:, c] = _value(wc, params)
+            Pzz = xp.full(xp.const(self.Pzz)[None], batch)
+            for wc, MM in self.Pzz_terms:
+                Pzz = Pzz + _col(_value(wc, params), 2) * xp.const(MM)[None]
+        if any(a is not None for a in self.coupled_aims):
+            aim = xp.zeros([batch, nC])
+            for c, a in enumerate(self.coupled_aims):
+                if a is not None:
+                    aim[:, c] = _value(a, params)
+        return w, aim, Pzz
 
     def instance_tables(self, params, batch, dev=None):
         """Per-instance tables of a plan with ``Param`` coefficients: ``{name: [B, ...]}`` for
@@ -492,6 +526,9 @@ class LtiPlan:
             out += [x for x in (w, aim, caim) if is_expr(x)]
             for form in (fv, fc):
                 out += [c for c in list(form.cx.values()) + list(form.cu.values()) if is_expr(c)]
+        for (w, fv, _Mz, _E), aim in zip(self.coupled, self.coupled_aims):
+            out += [x for x in (w, aim) if is_expr(x)]
+            out += [c for c in list(fv.cx.values()) + list(fv.cu.values()) if is_expr(c)]
         return out
 
     # ---- costs with a schedule ---------------------------------------------------
@@ -950,10 +987,11 @@ def lower(form, plant_name):
             # What the fused kernel's stage weights (and the coupling stage's constant tables) cannot
             # express goes through the general stage of mpci_sched.cu, row by row: a schedule; a cost
             # that couples states and inputs (no Qxu block in T' Qxx T + Quu x I); a crossed cost or a
-            # per-instance weight / aim on a signal with a part outside the plant.
+            # per-instance aim on a signal outside the plant that has fewer samples than the horizon.
             mixes = (fv.touches_states() and fc.touches_inputs()) or (fv.touches_inputs() and fc.touches_states())
             outside = fv.has_aux() or fc.has_aux()
-            general = mixes or (outside and (fv is not fc or is_expr(w) or is_expr(aim) or is_expr(caim)))
+            short = not fv.has_plant() and fv.rows != N  # (e.g. a cost on the footsteps themselves)
+            general = mixes or (outside and (fv is not fc or ((is_expr(aim) or is_expr(caim)) and short)))
             if cost.schedule or general:
                 rows = N if (fv.has_plant() or fc.has_plant() or not plan.embedded) else fv.rows
                 if rows is None or rows > N or (fc.rows is not None and not fc.has_plant() and fc.rows < rows):
@@ -975,9 +1013,13 @@ def lower(form, plant_name):
                 if fv.Mg is not None:
                     Mg[:rows] = fv.Mg
                 E = np.zeros([N, form.given_len + 1])  # e = Mg given - aim
-                E[:, :-1], E[:rows, -1] = Mg, -float(aim)
+                E[:, :-1], E[:rows, -1] = Mg, (0.0 if is_expr(aim) else -float(aim))
                 plan.coupled.append((w, fv, Mz, E))
-                Pzz += w * (Mz.T @ Mz)  # body.py:292 with Vo = Co = [T | Mz]
+                plan.coupled_aims.append(aim if is_expr(aim) else None)  # (then subtracted per instance)
+                if is_expr(w):  # body.py:292 with Vo = Co = [T | Mz]
+                    plan.Pzz_terms.append((w, Mz.T @ Mz))
+                else:
+                    Pzz += w * (Mz.T @ Mz)
             if fv.has_plant() or fc.has_plant() or not plan.embedded:
                 # (a coupled cost's aim is carried by E alone: the plant part must not subtract it again)
                 coupled_here = fv.has_aux() or fc.has_aux()
@@ -1103,7 +1145,7 @@ class LtiJob:
         self.A, self.B = A.contiguous(), B.contiguous()
         self.strideA = n * n if A.dim() == 3 else 0
         self.strideB = n * m if B.dim() == 3 else 0
-        self.tables = self.scalars = self.ccx = self.ccu = None
+        self.tables = self.scalars = self.ccx = self.ccu = self.coupled = None
         if plan.per_instance or plan.embedded or plan.sched_terms:
             missing = [nm for nm in plan.parameter_names() if nm not in (params or {})]
             if missing:
@@ -1111,10 +1153,17 @@ class LtiJob:
         if plan.per_instance:
             self.tensors = plan.instance_tables(params, batch, dev)
             self.tables = _lti_tables(self.tensors)
-            if plan.coupled:
-                self.ccx, self.ccu = plan.coupled_tables(params, batch, dev)
         elif len(plan.slots.exprs):
             self.scalars = to_dev(plan.slots.evaluate(params or {}, batch))
+        if plan.coupled and plan.coupled_symbolic():
+            from . import device
+
+            self.ccx, self.ccu = (t.contiguous() for t in plan.coupled_tables(params, batch, dev))
+            self.cextra = tuple(t.contiguous() if t is not None else None
+                                for t in plan.coupled_extras(params, batch, dev))
+            at = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
+            self.coupled = LtiCoupledTables(at(self.ccx), at(self.ccu), at(self.cextra[0]), at(self.cextra[1]),
+                                            at(self.cextra[2]))
         self.sched_terms = None
         if plan.sched_terms:
             self.sched = plan.device_sched()
@@ -1139,8 +1188,9 @@ class LtiJob:
         head = (self.handle, ptr(self.A), self.strideA, ptr(self.B), self.strideB, ptr(self.x0))
         lib = device.lib()
         if plan.embedded:
-            rc = lib.mpci_lti_assemble_coupled(*head, ptr(self.given), ptr(self.scalars), tables,
-                                               ptr(self.ccx), ptr(self.ccu), *outs, batch, int(hessian), stream)
+            coupled = ctypes.byref(self.coupled) if self.coupled is not None else None
+            rc = lib.mpci_lti_assemble_coupled_ex(*head, ptr(self.given), ptr(self.scalars), tables, coupled,
+                                                  *outs, batch, int(hessian), stream)
         elif plan.per_instance:
             rc = lib.mpci_lti_assemble_ex(*head, None, tables, *outs, batch, int(hessian), stream)
         else:

@@ -74,6 +74,26 @@ def run(batch, steps):
     A, B = lti.named_system_batched("dP->CCC", vals["tau"], vals["omega"])
     measure("biped_n100_plants", plans, A, B, given, {k: vals[k] for k in ("omega", "vel_x", "vel_y")})
 
+    # one weight per robot on `relax ankles`, a cost on (b + n - s): per-instance cost_w / Pzz of the
+    # coupling stage ("with") against the constant weight ("without"); no extra pass over P
+    plans = {}
+    for key, weight in (("without", 1.0), ("with", Param("w_ankles"))):
+        conf = biped.default_configuration(N)
+        conf.system = "dP->CCC"
+        conf.cost_weights["relax ankles"] = weight
+        form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                     target_vel=[Param("vel_x"), Param("vel_y")])
+        plans[key] = form.lti_plan("LIP")
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    params["w_ankles"] = np.random.default_rng(8).uniform(0.5, 2.0, batch)
+    res = {}
+    out = None
+    for key, plan in plans.items():
+        job = lti.LtiJob(plan, A, B, given, params)
+        out = device.QPBatch(batch, plan.nv, plan.nc, dev) if out is None else out
+        res[key + "_ms"] = timed(torch, flush, lambda: job.launch(out, lti.HESSIAN_RECURSION), steps)
+    line["biped_n100_per_instance_ankle_weight"] = res
+
     nx, nu, N = 12, 4, 50
     _, _, Q, R = synthetic.generic_system(1004, nx, nu)
     A, B = synthetic.generic_plants(1004, batch, nx, nu)

@@ -53,11 +53,13 @@ def evaluate(plan, A, B, x0, scalars, instance=None):
     return G, h, P, q
 
 
-def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None):
+def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None, extras=None):
     """An embedded plan (variables / givens / rows outside the plant, lti.lower): what the
     fused kernel writes at its place in the larger matrices plus what the coupling kernel
     (csrc/mpci_couple.cu) adds, from the plan's tables.  ``given`` [given_len];
-    ``coupled`` = (cost_cx [nC, n], cost_cu [nC, m]) of this instance for a per-instance plan."""
+    ``coupled`` = (cost_cx [nC, n], cost_cu [nC, m]) of this instance for a per-instance plan;
+    ``extras`` = this instance's row of ``plan.coupled_extras`` (cost_w [nC], cost_aim [nC],
+    Pzz [nz, nz]; each may be None)."""
     given = np.asarray(given, dtype=np.float64)
     x0 = given[plan.x0_index]
     Gc, hc, Pc, qc = evaluate(plan, A, B, x0, scalars, instance)
@@ -77,7 +79,8 @@ def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None):
     G[:, z] = plan.Gz
     extra = plan.Hg @ g1
     h = np.where(plan.row_kind == 1, extra, h + extra)
-    P[np.ix_(z, z)] = plan.Pzz
+    w_b, aim_b, Pzz_b = extras if extras is not None else (None, None, None)
+    P[np.ix_(z, z)] = plan.Pzz if Pzz_b is None else Pzz_b
     Ae, Be = plan.expand_numpy(A, B)
     Gam = [Be]
     for _ in range(N - 1):
@@ -97,7 +100,8 @@ def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None):
             T[k, :, k] += cu
         T = T.reshape([N, m * N])
         fr = np.array([cx @ f[k] for k in range(N)])
-        ee = E @ g1
+        ee = E @ g1 - (aim_b[c] if aim_b is not None else 0.0)
+        w = tab["cost_w"][c] if w_b is None else w_b[c]
         P[np.ix_(cols, z)] += w * T.T @ Mz
         P[np.ix_(z, cols)] += w * Mz.T @ T
         q[cols] += w * T.T @ ee

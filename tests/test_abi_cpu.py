@@ -124,7 +124,8 @@ def _header_fields(struct_name):
 
 @pytest.mark.parametrize("struct_name,mirror", [("mpci_lti_desc", "LtiDesc"), ("mpci_lti_tables", "LtiTables"),
                                                 ("mpci_lti_embed", "LtiEmbed"),
-                                                ("mpci_lti_sched_desc", "LtiSchedDesc")])
+                                                ("mpci_lti_sched_desc", "LtiSchedDesc"),
+                                                ("mpci_lti_coupled_tables", "LtiCoupledTables")])
 def test_lti_structs_of_the_binding_match_the_header(struct_name, mirror):
     """The ctypes mirrors in lti.py list the fields of include/mpci.h in the same order with
     the same kinds (int / pointer): a field added on one side only would shift every later one."""

@@ -311,3 +311,52 @@ def test_biped_plants_host_results():
     host = lti.assemble_host(plan, A, B, given, params, hessian=lti.HESSIAN_RECURSION, chunk=4)
     for got, ref in zip(host, (want.P, want.q, want.G, want.h)):
         assert got.is_pinned() and torch.equal(got, ref.cpu())
+
+
+@pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
+@pytest.mark.parametrize("N,batch", [(24, 6), (100, 3)])
+def test_biped_plants_with_per_instance_cost_weights(N, batch):
+    """One weight per robot on EVERY cost of the biped (biped_configuration.py:44-50): jerk and
+    velocity tracking stay inside the plant (per-instance Qxx / Quu), `relax ankles` acts on
+    (b + n - s) -- a signal with footstep and bias parts: per-instance cost_w and Pzz of the
+    coupling stage, mpci_lti_coupled_tables --, and the terminal cost is a scheduled one.  Every
+    instance formulated by the unmodified reference with its own plant and its own numbers."""
+    import copy
+    import types
+
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                DomainVariable=ref.DomainVariable, Formulation=ref.Formulation,
+                                LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box, tools=ref.tools)
+    conf = biped.default_configuration(N)
+    conf.system = "dP->CCC"
+    names = {"minimize jerk": "w_jerk", "track velocity": "w_vel", "relax ankles": "w_ankles", "terminal": "w_end"}
+    conf.cost_weights = {k: Param(v) for k, v in names.items()}
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and len(plan.Pzz_terms) == 2 and len(plan.sched_terms) == 2
+    rng = np.random.default_rng(N)
+    vals = synthetic.biped_inputs(9 + N, batch, N)
+    vals["tau"] = rng.uniform(0.08, 0.12, batch) * min(1.0, 30.0 / N)
+    for v, (lo, hi) in zip(names.values(), ((1e-4, 1e-2), (0.005, 0.05), (0.2, 3.0), (1.0, 50.0))):
+        vals[v] = rng.uniform(lo, hi, batch)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ["omega", "vel_x", "vel_y"] + list(names.values())}
+    wants = []
+    for b in range(batch):
+        one_conf = copy.copy(conf)
+        one_conf.cost_weights = {k: float(vals[v][b]) for k, v in names.items()}
+        one = biped.formulate_biped(one_conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                    target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        wants.append(one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID})))
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, params, dynamics={"LIP": ("dP->CCC", vals["tau"], vals["omega"])}, hessian=mode)
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        for b in range(batch):
+            cases.assert_qp_close(tuple(x[b] for x in got), wants[b])

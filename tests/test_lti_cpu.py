@@ -277,8 +277,9 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
             {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}))
         plant = dynamics.ControlSystem.from_name(spec["system"], ["_x"], tau=float(vals["tau"][b]),
                                                  omega=float(vals["omega"][b]))
+        extras = tuple(None if t is None else t[b] for t in plan.coupled_extras(params, batch))
         got = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], None,
-                                           {key: v[b] for key, v in tables.items()}, (ccx[b], ccu[b]))
+                                           {key: v[b] for key, v in tables.items()}, (ccx[b], ccu[b]), extras)
         if plan.sched_terms:
             terms = plan.sched_tables(params, batch)
             got = got[:2] + _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b],
@@ -401,16 +402,23 @@ def test_costs_beyond_the_stage_weights_take_the_general_stage(cpu_extend):
     form.incorporate_goal("steps", Cost("(c-s)", Param("w_steps"), aim=[Param("lead"), 0], axes=["_x", "_y"]))
     form.incorporate_goal("crossed", Cost("(c-s)", 0.7, aim=[0.05], cross="CoM", cross_aim=[0.1], axes=["_x"]))
     plan = form.lti_plan("LIP")
-    assert plan.embedded and len(plan.sched_terms) == 3 and not plan.per_instance
+    # the per-instance weight / aim stay with the coupling stage (per-instance cost_w, cost_aim, Pzz);
+    # the crossed cost is one whole-horizon term of the general stage
+    assert plan.embedded and len(plan.sched_terms) == 1 and plan.per_instance
+    assert [a is not None for a in plan.coupled_aims[-2:]] == [True, False] and len(plan.Pzz_terms) == 2
     vals = synthetic.biped_inputs(5, batch, N)
     given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
     params = {"w_steps": np.array([0.5, 1.0, 2.0]), "lead": np.array([0.0, 0.1, -0.2])}
     terms = plan.sched_tables(params, batch)
-    assert terms.shape[0] == batch
     from mpc_interface_b200 import dynamics
     plant = dynamics.ControlSystem.from_name(conf.system, ["_x"], tau=conf.mpc_period, omega=conf.omega)
     for b in range(batch):
         one = {k: float(v[b]) for k, v in params.items()}
-        got = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], np.zeros([0]))
-        P, q = _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b], terms[b], got[2], got[3])
+        tables = {key: v[b] for key, v in plan.instance_tables(params, batch).items()}
+        ccx, ccu = plan.coupled_tables(params, batch)
+        extras = tuple(None if t is None else t[b] for t in plan.coupled_extras(params, batch))
+        got = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], np.zeros([0]), tables,
+                                           (ccx[b], ccu[b]), extras)
+        P, q = _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b], terms[b if terms.shape[0] > 1 else 0],
+                                        got[2], got[3])
         cases.assert_qp_close((got[0], got[1], P, q), qp_oracle.all_qp_matrices(form, given[b][:, None], one))
