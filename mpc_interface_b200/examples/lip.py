@@ -37,17 +37,18 @@ def default_configuration(horizon_lenght=40):
     return c
 
 
-def formulate_lip(conf, omega=None, tau=None, target_vel=None, backend=None, api=None, nominal=None):
+def formulate_lip(conf, omega=None, tau=None, target_vel=None, backend=None, api=None, nominal=None, yaw=None):
     """``omega`` / ``tau`` / ``target_vel`` default to the configuration's numbers; ``Param``s
     make them per-instance (then ``nominal = (tau, omega)`` numbers build the structure-only
-    plant the formulation is created with)."""
+    plant the formulation is created with).  ``yaw`` (a number or a ``Param``) turns the foot
+    polygon and the terminal box in the task space (restrictions.py:380-401 ``rotate_in_TS``)."""
     if api is None:
         from .. import body, combinations, dynamics, goal, restrictions, tools
 
         api = SimpleNamespace(ControlSystem=dynamics.ControlSystem, ExtendedSystem=dynamics.ExtendedSystem,
                               Formulation=body.Formulation, LineCombo=combinations.LineCombo,
                               Cost=goal.Cost, Box=restrictions.Box,
-                              make_simetric_vertices=tools.make_simetric_vertices)
+                              make_simetric_vertices=tools.make_simetric_vertices, rotation2D=tools.rotation2D)
     w = conf.omega if omega is None else omega
     T = conf.mpc_period if tau is None else tau
     vel = conf.target_vel if target_vel is None else target_vel
@@ -67,6 +68,10 @@ def formulate_lip(conf, omega=None, tau=None, target_vel=None, backend=None, api
     terminal = api.Box.task_space("DCM", foot, AXES, schedule=range(N - 1, N))
     support.set_safety_margin(conf.cop_safety_margin)
     terminal.set_safety_margin(conf.cop_safety_margin)
+
+    if yaw is not None:
+        support.rotate_in_TS(api.rotation2D(yaw))
+        terminal.rotate_in_TS(api.rotation2D(yaw))
 
     weights = conf.cost_weights
     goals = {

@@ -27,7 +27,8 @@ no slower fallback):
   * limits: no ``L``; ``schedule`` a contiguous ``range`` (the terminal constraint of the
     biped, biped_formulation.py:97-102); one axis with ``arrow`` / ``center`` / ``extreme``
     of one row or one row per sample, or several axes with a single-row ``arrow`` (a facet
-    of a ``Box.task_space``); ``center`` / ``extreme`` may hold ``Param`` expressions.
+    of a ``Box.task_space``); ``center`` / ``extreme`` may hold ``Param`` expressions, and so may
+    a single-row ``arrow`` of a limit on plant signals (a box turned per instance).
 
 Without ``Param`` coefficients the tables are formulation constants (per-instance aims
 travel as the plan's scalar slots).  With them the tables are evaluated per instance --
@@ -921,16 +922,25 @@ def lower(form, plant_name):
                 _unsupported("a limit whose schedule is not a contiguous range inside the horizon")
             k0, cnt = sched.start, len(sched)
         arrow = np.asarray(limit.arrow)
-        if arrow.dtype == object:
-            _unsupported("a per-instance arrow (a limit turned by a Param)")
-        arrow = arrow.astype(np.float64)
+        turned = arrow.dtype == object and any(is_expr(x) for x in arrow.ravel())
+        if turned:  # a limit turned per instance (rotate_in_TS by a Param): its arrow joins the form's coefficients
+            if arrow.shape[0] != 1 or any(f.has_aux() for f in members):
+                _unsupported("a per-instance arrow that changes from row to row, or on a signal with a part "
+                             "outside the plant")
+        else:
+            arrow = arrow.astype(np.float64)
         nlines = limit.nlines
         if nlines is not None and int(nlines) != cnt:
             raise ValueError(
                 "operands could not be broadcast together with shapes ({},1) ({},{})".format(
                     int(nlines), cnt, plan.nv))
         rows_form, rows_arrow = _Form(), np.ones([rows])
-        if len(names) == 1:
+        if turned:
+            for a, f in enumerate(members):
+                rows_form.add(f, arrow[0, a] if is_expr(arrow[0, a]) else float(arrow[0, a]))
+            rows_arrow = np.zeros([rows])
+            rows_arrow[k0:k0 + cnt] = 1.0
+        elif len(names) == 1:
             rows_form.add(members[0], 1.0)
             column = arrow[:, 0]
             rows_arrow = np.zeros([rows])

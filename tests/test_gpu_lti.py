@@ -278,3 +278,46 @@ def test_permuted_inputs_scheduled_limit_and_param_weight(dev, monkeypatch, hess
     with pytest.raises(ValueError):  # a negative per-instance extreme would be flipped by the reference
         form.generate_all_qp_matrices_batched(
             g["x0"], dict(params, lim=-params["lim"]), dynamics={"plant": (g["A_sys"], g["B_sys"])})
+
+
+@pytest.mark.parametrize("N,batch", [(12, 7), (40, 5)])
+def test_lip_per_instance_plants_and_per_instance_yaw(dev, N, batch):
+    """SURVEY 8(f) row 4 on the per-instance path: the foot polygon and the terminal DCM box turned
+    by one yaw per robot (`rotate_in_TS(rotation2D(Param("yaw")))`, restrictions.py:380-401) while
+    every robot also has its own plant (tau_b, omega_b).  The turned arrow joins the per-instance
+    coefficients of the limit's form.  Every instance formulated, rotated and assembled by the
+    unmodified reference."""
+    import types
+
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import lip
+    from oracle import reference
+
+    if not reference.available():
+        pytest.skip("oracle/_ref is not staged")
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                Formulation=ref.Formulation, LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box,
+                                make_simetric_vertices=ref.tools.make_simetric_vertices,
+                                rotation2D=ref.tools.rotation2D)
+    conf = lip.default_configuration(N)
+    form = lip.formulate_lip(conf, omega=Param("omega"), tau=Param("tau"),
+                             target_vel=[Param("vel_x"), Param("vel_y")], yaw=Param("yaw"))
+    vals = lip.lip_inputs(40 + N, batch)
+    vals["tau"] = vals["tau"] * min(1.0, 30.0 / N)
+    vals["yaw"] = np.random.default_rng(N).uniform(-np.pi, np.pi, batch)
+    given = np.hstack([vals["x0_x"], vals["x0_y"]])
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y", "yaw")}
+    wants = []
+    for b in range(batch):
+        one = lip.formulate_lip(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])],
+                                yaw=float(vals["yaw"][b]), api=api)
+        wants.append(one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID})))
+    for hessian in ("dmma", "recursion"):
+        out = form.generate_all_qp_matrices_batched(
+            given, params, dynamics={"LIP": ("dP->CCC", vals["tau"], vals["omega"])}, hessian=hessian)
+        got = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+        for b in range(batch):
+            cases.assert_qp_close(tuple(x[b] for x in got), wants[b])

@@ -422,3 +422,45 @@ def test_costs_beyond_the_stage_weights_take_the_general_stage(cpu_extend):
         P, q = _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b], terms[b if terms.shape[0] > 1 else 0],
                                         got[2], got[3])
         cases.assert_qp_close((got[0], got[1], P, q), qp_oracle.all_qp_matrices(form, given[b][:, None], one))
+
+
+def test_lip_per_instance_plants_and_yaw_lowering(cpu_extend):
+    """A box turned per instance (rotate_in_TS by a Param) on plant signals: the arrow's
+    expressions join the limit's form (per-instance cx); on a signal with a part outside the plant
+    it is refused.  NumPy restatement of the kernel against the live reference."""
+    import types
+
+    from mpc_interface_b200 import dynamics
+    from mpc_interface_b200.examples import biped, lip
+    from oracle import reference
+
+    if not reference.available():
+        pytest.skip("oracle/_ref is not staged")
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                Formulation=ref.Formulation, LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box,
+                                make_simetric_vertices=ref.tools.make_simetric_vertices,
+                                rotation2D=ref.tools.rotation2D)
+    conf = lip.default_configuration(11)
+    form = lip.formulate_lip(conf, omega=Param("omega"), tau=Param("tau"),
+                             target_vel=[Param("vel_x"), Param("vel_y")], yaw=Param("yaw"), backend=NumpyBackend())
+    plan = form.lti_plan("LIP")
+    assert not plan.embedded and "cx" in plan.varying and "yaw" in plan.parameter_names()
+    batch = 3
+    vals = lip.lip_inputs(5, batch)
+    vals["yaw"] = np.array([0.4, -2.0, 3.0])
+    given = np.hstack([vals["x0_x"], vals["x0_y"]])
+    tables = plan.instance_tables({k: vals[k] for k in plan.parameter_names()}, batch)
+    for b in range(batch):
+        one = lip.formulate_lip(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])],
+                                yaw=float(vals["yaw"][b]), api=api)
+        want = one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID}))
+        plant = dynamics.ControlSystem.from_name("dP->CCC", ["_x"], tau=float(vals["tau"][b]),
+                                                 omega=float(vals["omega"][b]))
+        got = _lti_numpy.evaluate(plan, plant.A, plant.B, given[b], np.zeros([0]), {k: v[b] for k, v in tables.items()})
+        cases.assert_qp_close(got, want)
+    walker = biped.formulate_biped(biped.default_configuration(12), yaw=Param("yaw"), backend=NumpyBackend())
+    with pytest.raises(NotImplementedError, match="per-instance arrow"):
+        walker.lti_plan("LIP")
