@@ -378,6 +378,11 @@ typedef struct {
   const double* cost_w;    /* [batch][n_costs]    */
   const double* cost_aim;  /* [batch][n_costs]    */
   const double* Pzz;       /* [batch][nz][nz]     */
+  /* limits turned per instance (a Box rotated by one yaw per robot) on signals with auxiliary
+   * parts: the rows' entries under the auxiliary variables and the values of the plan's h map
+   * (same pattern h_ptr / h_col) per instance                                              */
+  const double* Gz;        /* [batch][nc_total][nz]   */
+  const double* h_val;     /* [batch][h_ptr[nc_total]] */
 } mpci_lti_coupled_tables;
 int mpci_lti_assemble_coupled_ex(const mpci_lti_plan* plan, const double* A_dev, long strideA,
                                  const double* B_dev, long strideB, const double* x0_dev,

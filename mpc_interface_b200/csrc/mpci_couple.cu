@@ -29,7 +29,7 @@ struct CoupleArgs {
 
   const int *voff, *zcol;
   const double *ccx, *ccu;  // [nC][n], [nC][m] (+ instance strides)
-  long sccx, sccu, scw;     // (scw: stride of the per-instance weights and aims, 0 = the plan's / none)
+  long sccx, sccu, scw, sGz, shv;     // (scw: stride of the per-instance weights and aims, 0 = the plan's / none)
   const double* caim;       // [batch][nC] per-instance aims, or nullptr
   const double *cw, *MzT;   // [nC], [nC][nz][N]
   const unsigned char* act; // [nC][nz]: column z of Mz_c is not identically zero
@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
       for (int e = tid; e < a.n_aux_rows * a.nvt; e += nthr) {
         const int i = e / a.nvt, col = e - i * a.nvt, what = colmap[col], r = a.aux_rows[i];
         if (what == INT32_MIN) continue;
-        __stcs(Gb + (size_t)r * a.nvt + col, what >= 0 ? 0.0 : __ldg(a.Gz + r * nz + (-1 - what)));
+        __stcs(Gb + (size_t)r * a.nvt + col, what >= 0 ? 0.0 : __ldg(a.Gz + b * a.sGz + r * nz + (-1 - what)));
       }
     }
     if (a.h) {
@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(kThreads) lti_couple_kernel(CoupleArgs a) {
         const int z0 = a.h_ptr[r], z1 = a.h_ptr[r + 1], kind = a.row_kind[r];
         if (z0 == z1 && !kind) continue;
         double acc = 0.0;
-        for (int z = z0; z < z1; ++z) acc = fma(a.h_val[z], gv[a.h_col[z]], acc);
+        for (int z = z0; z < z1; ++z) acc = fma(a.h_val[b * a.shv + z], gv[a.h_col[z]], acc);
         hb[r] = kind ? acc : hb[r] + acc;
       }
     }
@@ -199,6 +199,7 @@ struct CouplePlan {
   void* dev;
   size_t smem_bytes;
   int blocks_per_sm;
+  int h_nnz;  // entries of the h map (instance stride of per-instance values)
 };
 
 int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out) {
@@ -308,6 +309,7 @@ int couple_create(int n, int m, int N, const mpci_lti_embed* e, CouplePlan** out
   a.act = reinterpret_cast<const unsigned char*>(base + bytes_d + bytes_i);
   a.d_ptr = i + o_dp; a.d_tau = i + o_dt; a.d_val = d + o_dv;
   p->smem_bytes = smem;
+  p->h_nnz = h_nnz;
   p->blocks_per_sm = per_sm < 1 ? 1 : per_sm;
   *out = p;
   return 0;
@@ -333,12 +335,14 @@ int couple_launch(const CouplePlan* p, const double* A, long strideA, const doub
   CoupleArgs a = p->args;
   if (a.glen && !given) return fail(-3, "lti_assemble_coupled: NULL given");
   a.A = A; a.B = B; a.x0 = x0; a.given = given; a.sA = strideA; a.sB = strideB;
-  a.sccx = a.sccu = a.scw = 0;
+  a.sccx = a.sccu = a.scw = a.sGz = a.shv = 0;
   a.caim = nullptr;
   if (ct && ct->cost_cx) { a.ccx = ct->cost_cx; a.sccx = (long)a.nC * a.n; }
   if (ct && ct->cost_cu) { a.ccu = ct->cost_cu; a.sccu = (long)a.nC * a.m; }
   if (ct && ct->cost_w) { a.cw = ct->cost_w; a.scw = a.nC; }
   if (ct && ct->cost_aim) a.caim = ct->cost_aim;
+  if (ct && ct->Gz) { a.Gz = ct->Gz; a.sGz = (long)a.nct * a.nz; }
+  if (ct && ct->h_val) { a.h_val = ct->h_val; a.shv = p->h_nnz; }
   a.q = q; a.G = G; a.h = h; a.batch = batch;
   int dev = 0, sms = 148;
   MPCI_CUDA(cudaGetDevice(&dev));

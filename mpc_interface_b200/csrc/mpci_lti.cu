@@ -82,7 +82,7 @@ struct LtiArgs {
   // their Mz as CSR differences over (cost, z), and the constant block Pzz
   int nC;
   const double *ccx, *ccu, *ccw, *d_val, *Pzz;
-  long sccx, sccu, sccw, sPzz;  // (instance strides, 0 = the plan's table)
+  long sccx, sccu, sccw, sPzz, sGz;  // (instance strides, 0 = the plan's table)
   const int *d_ptr, *d_tau;
 };
 
@@ -1050,7 +1050,7 @@ __device__ void constraint_rows_emb(const LtiArgs& a, const Smem& s, const EmbSt
       }
       for (int e = tid; e < cnt * a.nz; e += nthr) {
         const int kk = e / a.nz, z = e - kk * a.nz;
-        __stcs(Gb + (size_t)(row0 + kk) * nv + a.zcol[z], __ldg(a.Gz + (size_t)(row0 + kk) * a.nz + z));
+        __stcs(Gb + (size_t)(row0 + kk) * nv + a.zcol[z], __ldg(a.Gz + b * a.sGz + (size_t)(row0 + kk) * a.nz + z));
       }
     }
     if (hb && tid < cnt) {
@@ -1134,7 +1134,7 @@ __device__ void constraint_rows_emb(const LtiArgs& a, const Smem& s, const EmbSt
     // the rows' entries under the auxiliary variables (constants of the formulation)
     for (int e = tid; e < cnt * a.nz; e += nthr) {
       const int kk = e / a.nz, z = e - kk * a.nz;
-      __stcs(rows + (size_t)kk * nv + a.zcol[z], __ldg(a.Gz + (size_t)(row0 + kk) * a.nz + z));
+      __stcs(rows + (size_t)kk * nv + a.zcol[z], __ldg(a.Gz + b * a.sGz + (size_t)(row0 + kk) * a.nz + z));
     }
   }
 }
@@ -1612,7 +1612,7 @@ static int lti_plan_create(const mpci_lti_desc* d, const mpci_lti_embed* emb, mp
     a.Gz = sh.Gz; a.zcol = sh.z_col; a.nz = sh.nz;
     a.nC = sh.n_costs; a.ccx = sh.cost_cx; a.ccu = sh.cost_cu; a.ccw = sh.cost_w;
     a.d_ptr = sh.d_ptr; a.d_tau = sh.d_tau; a.d_val = sh.d_val; a.Pzz = sh.Pzz;
-    a.sccx = a.sccu = a.sccw = a.sPzz = 0;
+    a.sccx = a.sccu = a.sccw = a.sPzz = a.sGz = 0;
     a.emb_even = (emb->nv_total % 2 == 0);
     for (int j = 0; j < m; ++j) a.emb_even = a.emb_even && (emb->var_off[j] % 2 == 0);
   }
@@ -1774,6 +1774,7 @@ static int lti_launch(const mpci_lti_plan* p, const double* A, long strideA, con
   if (ct && ct->cost_cu) { a.ccu = ct->cost_cu; a.sccu = (long)a.nC * p->m; }
   if (ct && ct->cost_w) { a.ccw = ct->cost_w; a.sccw = a.nC; }
   if (ct && ct->Pzz) { a.Pzz = ct->Pzz; a.sPzz = (long)a.nz * a.nz; }
+  if (ct && ct->Gz) { a.Gz = ct->Gz; a.sGz = (long)a.nct * a.nz; }
   if (tab) {  // per-instance tables replace the plan's
     const long n = p->n, m = p->m, Gn = p->n_groups, N = p->N;
     if (tab->Qxx) { a.Qxx = tab->Qxx; a.sQ = n * n; }

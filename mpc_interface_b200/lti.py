@@ -52,7 +52,7 @@ NAMED_SYSTEMS = {"J->CCC": (0, 3), "P->CC": (1, 2), "P->X": (2, 1), "dP->CCC": (
 class LtiCoupledTables(ctypes.Structure):
     """mpci_lti_coupled_tables of include/mpci.h"""
 
-    _fields_ = [(name, ctypes.c_void_p) for name in ("cost_cx", "cost_cu", "cost_w", "cost_aim", "Pzz")]
+    _fields_ = [(name, ctypes.c_void_p) for name in ("cost_cx", "cost_cu", "cost_w", "cost_aim", "Pzz", "Gz", "h_val")]
 
 
 class LtiSchedDesc(ctypes.Structure):
@@ -297,6 +297,9 @@ class LtiPlan:
         self.group_row0 = []  # first row of every plant group in G / h
         self.coupled = []     # costs on signals with an auxiliary part: (w, form, Mz [N,nz], E [N,ng+1])
         self.Pzz = self.Gz = self.Hg = self.row_kind = None
+        # limits turned per instance on signals with auxiliary parts: (arrow expression, first row,
+        # matrix) to be added to Gz [nc, nz] / to Hg [nc, ng + 1] per instance
+        self.Gz_terms, self.Hg_terms = [], []
         self.coupled_aims = []  # per coupled cost: its aim when that is a Param expression, else None
         self.Pzz_terms = []     # (Param weight, Mz' Mz) of the coupled costs with a per-instance weight
         # costs with a schedule (the stage of csrc/mpci_sched.cu, added to P and q afterwards):
@@ -429,7 +432,9 @@ class LtiPlan:
             for c, (_w, fv, _Mz, _E) in enumerate(self.coupled):
                 cx[c], cu[c] = _dense(fv.cx, n, {}, 1)[0], _dense(fv.cu, m, {}, 1)[0]
         e_ptr, e_col, e_val = csr(np.vstack([E for *_r, E in self.coupled]) if nC else np.zeros([0, self.ng + 1]))
-        h_ptr, h_col, h_val = csr(self.Hg)
+        mask = self.h_mask()  # (the entries a turned limit may fill are part of the pattern)
+        h_ptr = i32(np.concatenate([[0], np.cumsum(mask.sum(axis=1))]))
+        h_col, h_val = i32(np.nonzero(mask)[1]), f64(self.Hg[mask])
         MzT = np.stack([Mz.T for _w, _f, Mz, _E in self.coupled]) if nC else np.zeros([0, nz, N])
         return dict(var_off=i32(self.var_off), grp_row0=i32(self.group_row0), z_col=i32(self.z_col),
                     cost_cx=f64(cx), cost_cu=f64(cu), cost_w=f64([0.0 if is_expr(w) else w for w, *_r in self.coupled]),
@@ -449,14 +454,23 @@ class LtiPlan:
             cu[:, c] = _dense(fv.cu, self.m, params, batch, xp)
         return cx, cu
 
+    def h_mask(self):
+        """[nc, ng + 1] pattern of the h map: the non-zeros of Hg and of every per-instance term."""
+        mask = self.Hg != 0.0
+        for _expr, row0, M in self.Hg_terms:
+            mask[row0:row0 + len(M)] |= M != 0.0
+        return mask
+
     def coupled_symbolic(self):
-        """Whether anything about the coupled costs differs between the instances."""
-        return bool(self.Pzz_terms) or any(a is not None for a in self.coupled_aims) or any(
+        """Whether anything about the coupling stage's tables differs between the instances."""
+        return bool(self.Pzz_terms or self.Gz_terms or self.Hg_terms) or any(
+            a is not None for a in self.coupled_aims) or any(
             is_expr(w) or fv.symbolic() for w, fv, _Mz, _E in self.coupled)
 
     def coupled_extras(self, params, batch, dev=None):
-        """(cost_w [B, nC], cost_aim [B, nC], Pzz [B, nz, nz]) of mpci_lti_coupled_tables for the
-        coupled costs with a per-instance weight / aim -- each None when nothing in it varies."""
+        """(cost_w [B, nC], cost_aim [B, nC], Pzz [B, nz, nz], Gz [B, nc, nz], h_val [B, nnz]) of
+        mpci_lti_coupled_tables: per-instance weights / aims of the coupled costs, and the auxiliary
+        parts of limits turned per instance -- each None when nothing in it varies."""
         xp = _Host if dev is None else _Device(dev)
         params = xp.params(params, batch)
         nC, nz = len(self.coupled), self.nz
@@ -473,7 +487,19 @@ class LtiPlan:
             for c, a in enumerate(self.coupled_aims):
                 if a is not None:
                     aim[:, c] = _value(a, params)
-        return w, aim, Pzz
+        Gz = hval = None
+        if self.Gz_terms:
+            Gz = xp.full(xp.const(self.Gz)[None], batch)
+            for expr, row0, M in self.Gz_terms:
+                Gz[:, row0:row0 + len(M)] += _col(_value(expr, params), 2) * xp.const(M)[None]
+        if self.Hg_terms:
+            mask = self.h_mask()
+            hval = xp.full(xp.const(self.Hg[mask])[None], batch)
+            for expr, row0, M in self.Hg_terms:
+                full = np.zeros_like(self.Hg)
+                full[row0:row0 + len(M)] = M
+                hval = hval + _col(_value(expr, params), 1) * xp.const(full[mask])[None]
+        return w, aim, Pzz, Gz, hval
 
     def instance_tables(self, params, batch, dev=None):
         """Per-instance tables of a plan with ``Param`` coefficients: ``{name: [B, ...]}`` for
@@ -527,6 +553,7 @@ class LtiPlan:
             out += [x for x in (w, aim, caim) if is_expr(x)]
             for form in (fv, fc):
                 out += [c for c in list(form.cx.values()) + list(form.cu.values()) if is_expr(c)]
+        out += [expr for expr, _r, _M in self.Gz_terms + self.Hg_terms]
         for (w, fv, _Mz, _E), aim in zip(self.coupled, self.coupled_aims):
             out += [x for x in (w, aim) if is_expr(x)]
             out += [c for c in list(fv.cx.values()) + list(fv.cu.values()) if is_expr(c)]
@@ -924,9 +951,8 @@ def lower(form, plant_name):
         arrow = np.asarray(limit.arrow)
         turned = arrow.dtype == object and any(is_expr(x) for x in arrow.ravel())
         if turned:  # a limit turned per instance (rotate_in_TS by a Param): its arrow joins the form's coefficients
-            if arrow.shape[0] != 1 or any(f.has_aux() for f in members):
-                _unsupported("a per-instance arrow that changes from row to row, or on a signal with a part "
-                             "outside the plant")
+            if arrow.shape[0] != 1:
+                _unsupported("a per-instance arrow that changes from row to row")
         else:
             arrow = arrow.astype(np.float64)
         nlines = limit.nlines
@@ -935,9 +961,15 @@ def lower(form, plant_name):
                 "operands could not be broadcast together with shapes ({},1) ({},{})".format(
                     int(nlines), cnt, plan.nv))
         rows_form, rows_arrow = _Form(), np.ones([rows])
+        turned_aux = []  # (arrow expression, Mz [rows, nz] or None, Mg [rows, ng] or None) per axis
         if turned:
             for a, f in enumerate(members):
-                rows_form.add(f, arrow[0, a] if is_expr(arrow[0, a]) else float(arrow[0, a]))
+                if is_expr(arrow[0, a]):  # the plant part joins the per-instance coefficients of the form,
+                    rows_form.add(_Form(f.cx, f.cu, f.rows), arrow[0, a])
+                    if f.has_aux():       # the part outside the plant the per-instance Gz / h map
+                        turned_aux.append((arrow[0, a], f.Mz, f.Mg))
+                else:
+                    rows_form.add(f, float(arrow[0, a]))
             rows_arrow = np.zeros([rows])
             rows_arrow[k0:k0 + cnt] = 1.0
         elif len(names) == 1:
@@ -967,11 +999,21 @@ def lower(form, plant_name):
             Gz_rows.append((rows_arrow[:, None] * Mz)[k0:k0 + cnt])
             Hg = np.zeros([cnt, form.given_len + 1])
             Hg[:, :-1] = -(rows_arrow[:, None] * Mg)[k0:k0 + cnt]
-            if not on_plant:
-                if any(is_expr(coef) for coef, _ in parts):
-                    _unsupported("a per-instance bound on a limit outside the plant")
+            if not on_plant:  # (the bounds of the plant's groups travel in the group tables)
                 for coef, col in parts:
-                    Hg[:, -1] += float(coef) * col[k0:k0 + cnt]
+                    if is_expr(coef):
+                        term = np.zeros([cnt, form.given_len + 1])
+                        term[:, -1] = col[k0:k0 + cnt]
+                        plan.Hg_terms.append((coef, plan.nc, term))
+                    else:
+                        Hg[:, -1] += float(coef) * col[k0:k0 + cnt]
+            for coef, Mz_a, Mg_a in turned_aux:
+                if Mz_a is not None and np.any(Mz_a):
+                    plan.Gz_terms.append((coef, plan.nc, np.array(Mz_a[k0:k0 + cnt])))
+                if Mg_a is not None and np.any(Mg_a):
+                    term = np.zeros([cnt, form.given_len + 1])
+                    term[:, :-1] = -Mg_a[k0:k0 + cnt]
+                    plan.Hg_terms.append((coef, plan.nc, term))
             Hg_rows.append(Hg)
             kinds += [0 if on_plant else 1] * cnt
         if on_plant:
@@ -1165,15 +1207,14 @@ class LtiJob:
             self.tables = _lti_tables(self.tensors)
         elif len(plan.slots.exprs):
             self.scalars = to_dev(plan.slots.evaluate(params or {}, batch))
-        if plan.coupled and plan.coupled_symbolic():
+        if plan.embedded and plan.coupled_symbolic():
             from . import device
 
             self.ccx, self.ccu = (t.contiguous() for t in plan.coupled_tables(params, batch, dev))
             self.cextra = tuple(t.contiguous() if t is not None else None
                                 for t in plan.coupled_extras(params, batch, dev))
             at = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
-            self.coupled = LtiCoupledTables(at(self.ccx), at(self.ccu), at(self.cextra[0]), at(self.cextra[1]),
-                                            at(self.cextra[2]))
+            self.coupled = LtiCoupledTables(at(self.ccx), at(self.ccu), *(at(t) for t in self.cextra))
         self.sched_terms = None
         if plan.sched_terms:
             self.sched = plan.device_sched()

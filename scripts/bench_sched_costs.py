@@ -32,6 +32,12 @@ def timed(torch, flush, fn, steps, warmup=3):
     return float(np.mean(times))
 
 
+def biped_conf(N, biped):
+    conf = biped.default_configuration(N)
+    conf.system = "dP->CCC"
+    return conf
+
+
 def run(batch, steps):
     import torch
 
@@ -93,6 +99,22 @@ def run(batch, steps):
         out = device.QPBatch(batch, plan.nv, plan.nc, dev) if out is None else out
         res[key + "_ms"] = timed(torch, flush, lambda: job.launch(out, lti.HESSIAN_RECURSION), steps)
     line["biped_n100_per_instance_ankle_weight"] = res
+
+    # one heading per robot: support polygon and terminal box turned by Param("yaw") -- the turned rows'
+    # entries under the footsteps and their given parts are per-instance tables (Gz 63 kB, h map 7 kB per QP)
+    form = biped.formulate_biped(biped_conf(N, biped), omega=Param("omega"), tau=Param("tau"), yaw=Param("yaw"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    params["yaw"] = np.random.default_rng(9).uniform(-np.pi, np.pi, batch)
+    import time
+
+    t0 = time.perf_counter()
+    job = lti.LtiJob(form.lti_plan("LIP"), A, B, given, params)
+    torch.cuda.synchronize()
+    build_ms = (time.perf_counter() - t0) * 1e3
+    line["biped_n100_plants_yaw"] = {
+        "ms": timed(torch, flush, lambda: job.launch(out, lti.HESSIAN_RECURSION), steps), "job_build_ms": build_ms,
+        "per_instance_table_bytes": int(sum(t.numel() * 8 for t in job.cextra if t is not None) // batch)}
 
     nx, nu, N = 12, 4, 50
     _, _, Q, R = synthetic.generic_system(1004, nx, nu)

@@ -22,14 +22,15 @@ INPUT = {"dP->CCC": "cCoP_dot", "J->CCC": "CoM_dddot", "dP->CCP": "cCoP_dot", "P
 OMEGA_COEFS = ("inv", "neg_inv2", "times", "num")
 
 
-def draw(seed, scheduled=False, general=False, with_L=False):
+def draw(seed, scheduled=False, general=False, with_L=False, turned=False):
     """The structure as plain data (a dict of lists and numbers).  ``scheduled``: some of the
     costs act on a few samples only (goal.py `schedule`).  ``general``: also costs that the stage
     weights of the fused kernel cannot express -- crossed costs between any two signals, per-instance
     weights and aims on signals with a part outside the plant, a definition that mixes states and
     the input.  ``with_L``: some uncrossed costs and some limits combine their samples through a
     matrix ``L`` (goal.py:88-104, restrictions.py:75-90) -- mode A only, the per-instance path
-    refuses ``L``."""
+    refuses ``L``.  ``turned``: the facets over both axes and some one-axis limits are turned / scaled
+    per instance (their one-row arrows are rotated by the angle ``vel``, as rotate_in_TS does)."""
     rng = np.random.default_rng(seed)
     system = SYSTEMS[rng.integers(len(SYSTEMS))]
     axes = ["_x", "_y"] if rng.random() < 0.4 else ["_x"]
@@ -137,6 +138,8 @@ def draw(seed, scheduled=False, general=False, with_L=False):
     optim += ["e" + ax for ax in axes] if has_e else []
     optim += ["Ds" + ax for ax in axes] if has_s else []
     spec["order"] = [optim[i] for i in rng.permutation(len(optim))]
+    for lim in limits:
+        lim["turned"] = bool(turned and np.asarray(lim["arrow"]).shape[0] == 1 and rng.random() < 0.7)
     if with_L:
         def samples_of(var, schedule):
             rows = spec["steps_U"].shape[1] if var == "Ds" else N
@@ -209,6 +212,14 @@ def build(spec, api, omega, tau, vel, gain, nominal=(0.1, 3.3), backend=None):
     for lim in spec["limits"]:
         extreme = lim["extreme"] + vel if lim["extreme_param"] else lim["extreme"]
         kargs = {"axes": lim["axes"], "arrow": np.array(lim["arrow"])}
+        if lim.get("turned"):
+            from mpc_interface_b200.params import cos, sin
+
+            a = np.array(lim["arrow"])[0]
+            if len(a) == 2:  # the facet's normal turned by the angle `vel`
+                kargs["arrow"] = np.array([[a[0] * cos(vel) - a[1] * sin(vel), a[0] * sin(vel) + a[1] * cos(vel)]])
+            else:            # one axis: the arrow scaled by cos(vel) > 0
+                kargs["arrow"] = np.array([[a[0] * cos(vel)]])
         if lim["schedule"] is not None:
             kargs["schedule"] = range(*lim["schedule"])
         if lim["center"] is not None:

@@ -59,7 +59,7 @@ def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None, e
     (csrc/mpci_couple.cu) adds, from the plan's tables.  ``given`` [given_len];
     ``coupled`` = (cost_cx [nC, n], cost_cu [nC, m]) of this instance for a per-instance plan;
     ``extras`` = this instance's row of ``plan.coupled_extras`` (cost_w [nC], cost_aim [nC],
-    Pzz [nz, nz]; each may be None)."""
+    Pzz [nz, nz], Gz [nc, nz], h_val [nnz of plan.h_mask()]; each may be None)."""
     given = np.asarray(given, dtype=np.float64)
     x0 = given[plan.x0_index]
     Gc, hc, Pc, qc = evaluate(plan, A, B, x0, scalars, instance)
@@ -76,10 +76,14 @@ def evaluate_embedded(plan, A, B, given, scalars, instance=None, coupled=None, e
         h[rows] = hc[at:at + cnt]
         at += cnt
     g1 = np.append(given, 1.0)
-    G[:, z] = plan.Gz
-    extra = plan.Hg @ g1
+    w_b, aim_b, Pzz_b, Gz_b, hval_b = (tuple(extras) + (None,) * 5)[:5] if extras is not None else (None,) * 5
+    G[:, z] = plan.Gz if Gz_b is None else Gz_b
+    Hg = plan.Hg
+    if hval_b is not None:
+        Hg = np.zeros_like(plan.Hg)
+        Hg[plan.h_mask()] = hval_b
+    extra = Hg @ g1
     h = np.where(plan.row_kind == 1, extra, h + extra)
-    w_b, aim_b, Pzz_b = extras if extras is not None else (None, None, None)
     P[np.ix_(z, z)] = plan.Pzz if Pzz_b is None else Pzz_b
     Ae, Be = plan.expand_numpy(A, B)
     Gam = [Be]

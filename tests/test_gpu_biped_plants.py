@@ -360,3 +360,45 @@ def test_biped_plants_with_per_instance_cost_weights(N, batch):
         got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
         for b in range(batch):
             cases.assert_qp_close(tuple(x[b] for x in got), wants[b])
+
+
+@pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
+@pytest.mark.parametrize("system,N,batch", [("dP->CCC", 24, 6), ("J->CCC", 37, 4), ("dP->CCC", 100, 3)])
+def test_biped_with_per_instance_plants_and_per_instance_yaw(system, N, batch):
+    """Every robot with its own plant (tau_b, omega_b) AND its own heading: support polygon and
+    terminal box turned by `rotate_in_TS(rotation2D(Param("yaw")))` (restrictions.py:380-401) on
+    (b + n - s) and (DCM - s) -- the rows' entries under the footsteps and their given parts travel
+    as the per-instance Gz / h_val of mpci_lti_coupled_tables.  Every instance formulated, turned
+    and assembled by the unmodified reference."""
+    import types
+
+    from mpc_interface_b200 import Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                DomainVariable=ref.DomainVariable, Formulation=ref.Formulation,
+                                LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box, tools=ref.tools)
+    conf = biped.default_configuration(N)
+    conf.system = system
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"), yaw=Param("yaw"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")])
+    vals = synthetic.biped_inputs(50 + N, batch, N)
+    rng = np.random.default_rng(N)
+    vals["tau"] = rng.uniform(0.08, 0.12, batch) * min(1.0, 30.0 / N)
+    vals["yaw"] = rng.uniform(-np.pi, np.pi, batch)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y", "yaw")}
+    wants = []
+    for b in range(batch):
+        one = biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                    yaw=float(vals["yaw"][b]),
+                                    target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        wants.append(one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID})))
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, params, dynamics={"LIP": (system, vals["tau"], vals["omega"])}, hessian=mode)
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        for b in range(batch):
+            cases.assert_qp_close(tuple(x[b] for x in got), wants[b])

@@ -84,9 +84,11 @@ def test_soft_constrained_lip_against_the_live_reference(N, order):
 
 
 @pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
-@pytest.mark.parametrize("seed,scheduled,general", [(s, False, False) for s in range(300, 324)]
-                         + [(s, True, False) for s in range(400, 424)] + [(s, True, True) for s in range(500, 532)])
-def test_random_embedded_formulations_against_the_live_reference(seed, scheduled, general):
+@pytest.mark.parametrize("seed,scheduled,general,turned", [(s, False, False, False) for s in range(300, 324)]
+                         + [(s, True, False, False) for s in range(400, 424)]
+                         + [(s, True, True, False) for s in range(500, 532)]
+                         + [(s, True, True, True) for s in range(700, 732)])
+def test_random_embedded_formulations_against_the_live_reference(seed, scheduled, general, turned):
     """tests/_embedded_forms.py through the kernels: random structures around a per-instance plant
     (four named plants, one or two axes, slack / footsteps / disturbance, costs with aims and on
     signals shorter than the horizon, facets, row-wise arrows, centres, schedules, any variable
@@ -94,11 +96,12 @@ def test_random_embedded_formulations_against_the_live_reference(seed, scheduled
     ``scheduled``: some costs act on a few samples only (terminal, a window, every 2nd / 3rd sample;
     per-instance weights and aims) -- the stage of csrc/mpci_sched.cu after the two kernels.
     ``general``: also crossed costs between any two signals, per-instance weights / aims on signals with
-    a part outside the plant, a definition that mixes states and the input."""
+    a part outside the plant, a definition that mixes states and the input.  ``turned``: limits turned /
+    scaled per instance, on signals with parts outside the plant too."""
     import _embedded_forms as forms
     from mpc_interface_b200 import Param
 
-    spec = forms.draw(seed, scheduled, general)
+    spec = forms.draw(seed, scheduled, general, turned=turned)
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"))
     plan = form.lti_plan("LIP")
     assert plan.embedded

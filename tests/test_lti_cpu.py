@@ -234,9 +234,11 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
         cases.assert_qp_close(got, (g["A"][b], g["h"][b], g["Q"][b], g["q"][b]))
 
 
-@pytest.mark.parametrize("seed,scheduled,general", [(s, False, False) for s in range(200, 212)]
-                         + [(s, True, False) for s in range(220, 232)] + [(s, True, True) for s in range(240, 256)])
-def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, general):
+@pytest.mark.parametrize("seed,scheduled,general,turned", [(s, False, False, False) for s in range(200, 212)]
+                         + [(s, True, False, False) for s in range(220, 232)]
+                         + [(s, True, True, False) for s in range(240, 256)]
+                         + [(s, True, True, True) for s in range(260, 276)])
+def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, general, turned):
     """tests/_embedded_forms.py: random structures around a per-instance plant (four named
     plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
     with aims and on signals shorter than the horizon, facets, row-wise arrows, centres,
@@ -245,7 +247,9 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
     ``scheduled``: some costs act on a few samples only (terminal, a window, every 2nd / 3rd
     sample; per-instance weights and aims) -- the stage of csrc/mpci_sched.cu.  ``general``: also
     crossed costs between any two signals, per-instance weights / aims on signals with a part outside
-    the plant and a definition that mixes states and the input (whole-horizon terms of that stage)."""
+    the plant and a definition that mixes states and the input (whole-horizon terms of that stage).
+    ``turned``: limits turned / scaled per instance, on signals with parts outside the plant too
+    (per-instance Gz and h map of the coupling stage)."""
     import _embedded_forms as forms
     from oracle import reference
 
@@ -253,7 +257,7 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
         pytest.skip("oracle/_ref is not staged")
     from mpc_interface_b200 import dynamics
 
-    spec = forms.draw(seed, scheduled, general)
+    spec = forms.draw(seed, scheduled, general, turned=turned)
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
                        backend=NumpyBackend())
     plan = form.lti_plan("LIP")
@@ -426,12 +430,12 @@ def test_costs_beyond_the_stage_weights_take_the_general_stage(cpu_extend):
 
 def test_lip_per_instance_plants_and_yaw_lowering(cpu_extend):
     """A box turned per instance (rotate_in_TS by a Param) on plant signals: the arrow's
-    expressions join the limit's form (per-instance cx); on a signal with a part outside the plant
-    it is refused.  NumPy restatement of the kernel against the live reference."""
+    expressions join the limit's form (per-instance cx).  NumPy restatement of the kernel against
+    the live reference."""
     import types
 
     from mpc_interface_b200 import dynamics
-    from mpc_interface_b200.examples import biped, lip
+    from mpc_interface_b200.examples import lip
     from oracle import reference
 
     if not reference.available():
@@ -461,6 +465,52 @@ def test_lip_per_instance_plants_and_yaw_lowering(cpu_extend):
                                                  omega=float(vals["omega"][b]))
         got = _lti_numpy.evaluate(plan, plant.A, plant.B, given[b], np.zeros([0]), {k: v[b] for k, v in tables.items()})
         cases.assert_qp_close(got, want)
-    walker = biped.formulate_biped(biped.default_configuration(12), yaw=Param("yaw"), backend=NumpyBackend())
-    with pytest.raises(NotImplementedError, match="per-instance arrow"):
-        walker.lti_plan("LIP")
+
+
+@pytest.mark.parametrize("system,N", [("dP->CCC", 14), ("J->CCC", 24)])
+def test_biped_with_per_instance_plants_and_yaw_lowering(cpu_extend, system, N):
+    """The walking biped with EVERYTHING per robot: its plant (tau_b, omega_b) and its heading --
+    support polygon and terminal box turned by `rotate_in_TS(rotation2D(Param("yaw")))` on
+    (b + n - s) and (DCM - s), signals with footstep and bias parts: the turned rows' entries under
+    the footsteps (Gz) and their given parts (the h map) become per-instance tables of the
+    coupling stage.  NumPy restatement of the kernels against the live reference."""
+    import types
+
+    from mpc_interface_b200 import dynamics
+    from mpc_interface_b200.examples import biped, synthetic
+    from oracle import reference
+
+    if not reference.available():
+        pytest.skip("oracle/_ref is not staged")
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                DomainVariable=ref.DomainVariable, Formulation=ref.Formulation,
+                                LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box, tools=ref.tools)
+    conf = biped.default_configuration(N)
+    conf.system = system
+    form = biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"), yaw=Param("yaw"),
+                                 target_vel=[Param("vel_x"), Param("vel_y")], backend=NumpyBackend())
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and plan.Gz_terms and plan.Hg_terms and "yaw" in plan.parameter_names()
+    batch = 3
+    vals = synthetic.biped_inputs(3 + N, batch, N)
+    vals["tau"] = np.array([0.09, 0.1, 0.11])
+    vals["yaw"] = np.array([0.5, -1.3, 2.8])
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in plan.parameter_names()}
+    tables = plan.instance_tables(params, batch)
+    ccx, ccu = plan.coupled_tables(params, batch)
+    extras = plan.coupled_extras(params, batch)
+    assert extras[3].shape == (batch, plan.nc, plan.nz) and extras[4].shape == (batch, int(plan.h_mask().sum()))
+    for b in range(batch):
+        one = biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                    yaw=float(vals["yaw"][b]),
+                                    target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        want = one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID}))
+        plant = dynamics.ControlSystem.from_name(system, ["_x"], tau=float(vals["tau"][b]),
+                                                 omega=float(vals["omega"][b]))
+        got = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], None,
+                                           {k: v[b] for k, v in tables.items()}, (ccx[b], ccu[b]),
+                                           tuple(None if t is None else t[b] for t in extras))
+        cases.assert_qp_close(got, want)
