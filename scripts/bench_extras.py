@@ -230,10 +230,23 @@ def biped_plants(batch=16384, N=100):
     return keep
 
 
+def biped_plants_variants(batch=16384):
+    """scripts/bench_sched_costs.py: the same path with the biped's terminal cost switched on (the
+    scheduled-cost stage), one `relax ankles` weight per robot, one heading per robot (turned limits),
+    and a dense terminal weight on generic plants at C4's shape."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("bench_sched_costs", os.path.join(ROOT, "scripts", "bench_sched_costs.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.run(batch, 5)
+
+
 def run():
     out = {}
     for name, fn in (("receding_tick", receding_tick), ("generic_stream", generic_stream),
-                     ("k1_extend_matrices", k1_extend), ("biped_per_instance_plants", biped_plants)):
+                     ("k1_extend_matrices", k1_extend), ("biped_per_instance_plants", biped_plants),
+                     ("per_instance_plants_variants", biped_plants_variants)):
         try:
             out[name] = fn()
         except Exception as e:  # an extra must never cost the headline line
