@@ -207,3 +207,23 @@ def random_form(g, seed, backend=None):
     given = np.repeat(g[tag + "given"][None, :], batch, 0)
     ref = tuple(g[tag + k] for k in "AhQq")
     return form, given, vals, ref
+
+
+def transform_boxes(form, rotation, shift, scale, recenter):
+    """The Box transforms of restrictions.py:380-486 on the biped's boxes, the same calls for this
+    package's formulation (arguments may hold Params: one value per robot) and for the
+    reference's (numbers): the support polygon turned, shifted and scaled, the terminal box
+    re-centred."""
+    box = form.constraint_boxes["support_polygon"]
+    box.rotate_in_TS(rotation)
+    box.translate_in_TS(np.array(list(shift)))
+    box.scale_box(scale)
+    form.constraint_boxes["terminal_Constraint"].recenter_in_TS(np.array([recenter, 0.0]))
+    return form
+
+
+def transform_values(batch, seed):
+    rng = np.random.default_rng(seed)
+    return {"yaw": rng.uniform(-np.pi, np.pi, batch), "dx": rng.uniform(-0.03, 0.03, batch),
+            "dy": rng.uniform(-0.02, 0.02, batch), "sc": rng.uniform(0.7, 1.4, batch),
+            "rc": rng.uniform(-0.02, 0.02, batch)}

@@ -402,3 +402,45 @@ def test_biped_with_per_instance_plants_and_per_instance_yaw(system, N, batch):
         got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
         for b in range(batch):
             cases.assert_qp_close(tuple(x[b] for x in got), wants[b])
+
+
+@pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
+@pytest.mark.parametrize("plants", [False, True])
+def test_box_transforms_per_instance(plants):
+    """SURVEY 8(f) row 4 through the kernels: the support polygon turned, shifted and scaled and the
+    terminal box re-centred with one value per robot (restrictions.py:380-486 with Params) -- in
+    mode A (shared plant) and on the per-instance path (one plant per robot as well).  Every
+    instance formulated and transformed by the unmodified reference."""
+    import types
+
+    from mpc_interface_b200 import Param, tools
+    from mpc_interface_b200.examples import biped, synthetic
+
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                DomainVariable=ref.DomainVariable, Formulation=ref.Formulation,
+                                LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box, tools=ref.tools)
+    N, batch = 30, 5
+    conf = biped.default_configuration(N)
+    conf.system = "dP->CCC" if plants else conf.system
+    kw = {"tau": Param("tau")} if plants else {}
+    form = biped.formulate_biped(conf, omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")], **kw)
+    cases.transform_boxes(form, tools.rotation2D(Param("yaw")), (Param("dx"), Param("dy")), Param("sc"), Param("rc"))
+    vals = synthetic.biped_inputs(13, batch, N)
+    vals.update(cases.transform_values(batch, 14))
+    vals["tau"] = np.random.default_rng(15).uniform(0.08, 0.12, batch) if plants else np.full(batch, conf.mpc_period)
+    if not plants and conf.system != "J->CCC":
+        pytest.skip("the shared plant must not depend on omega")
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y", "yaw", "dx", "dy", "sc", "rc")}
+    dynamics = {"dynamics": {"LIP": ("dP->CCC", vals["tau"], vals["omega"])}} if plants else {}
+    out = form.generate_all_qp_matrices_batched(given, params, **dynamics)
+    got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+    for b in range(batch):
+        one = biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                    target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        cases.transform_boxes(one, ref.tools.rotation2D(float(vals["yaw"][b])),
+                              (float(vals["dx"][b]), float(vals["dy"][b])), float(vals["sc"][b]), float(vals["rc"][b]))
+        want = one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID}))
+        cases.assert_qp_close(tuple(x[b] for x in got), want)

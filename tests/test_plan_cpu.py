@@ -259,6 +259,43 @@ def test_random_structures_around_a_shared_plant_against_the_live_reference(cpu_
         cases.assert_qp_close((out.G[b], out.h[b], out.P[b], out.q[b]), want)
 
 
+def test_box_transforms_per_instance_against_the_live_reference(cpu_extend):
+    """rotate_in_TS, translate_in_TS, scale_box and recenter_in_TS
+    (restrictions.py:380-486) with one value per robot -- the boxes' arrows, centres and extremes
+    hold Param expressions, the plan splits them into monomials.  The reference applies the same
+    calls with numbers to a formulation of its own per instance."""
+    import types
+
+    from mpc_interface_b200 import Param, tools
+    from mpc_interface_b200.examples import biped, synthetic
+    from oracle import reference
+
+    if not reference.available():
+        pytest.skip("oracle/_ref is not staged")
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                DomainVariable=ref.DomainVariable, Formulation=ref.Formulation,
+                                LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box, tools=ref.tools)
+    N, batch = 16, 4
+    conf = biped.default_configuration(N)
+    form = biped.formulate_biped(conf, omega=Param("omega"), target_vel=[Param("vel_x"), Param("vel_y")],
+                                 backend=NumpyBackend())
+    cases.transform_boxes(form, tools.rotation2D(Param("yaw")), (Param("dx"), Param("dy")), Param("sc"), Param("rc"))
+    vals = synthetic.biped_inputs(3, batch, N)
+    vals.update(cases.transform_values(batch, 4))
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y", "yaw", "dx", "dy", "sc", "rc")}
+    out = form.generate_all_qp_matrices_batched(given, params)
+    for b in range(batch):
+        one = biped.formulate_biped(conf, omega=float(vals["omega"][b]),
+                                    target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api)
+        cases.transform_boxes(one, ref.tools.rotation2D(float(vals["yaw"][b])),
+                              (float(vals["dx"][b]), float(vals["dy"][b])), float(vals["sc"][b]), float(vals["rc"][b]))
+        want = one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID}))
+        cases.assert_qp_close((out.G[b], out.h[b], out.P[b], out.q[b]), want)
+
+
 def test_negative_per_instance_extreme_is_refused(cpu_extend):
     """The reference flips a limit with a negative extreme (restrictions.py:190-194);
     for a Param extreme the batch is checked and refused instead of differing."""
