@@ -420,6 +420,19 @@ typedef struct {
   const double* v_Mg;     /* [row_ptr[n_terms]][given_len] or NULL                            */
   const double* c_Mz;     /* the crossed variable's; NULL = the variable's own                */
   const double* c_Mg;
+  /* Rows that COMBINE samples -- a Cost's / Constraint's `L` (goal.py:88-104, restrictions.py:75-90;
+   * vMo = L @ Mo[sigma], body.py:279-290): row r = sum over e in ent_ptr[r] .. ent_ptr[r + 1] of
+   * ent_val[e] * (row ent_k[e] of the preview matrix).  NULL = the single sample row_k[r] (then
+   * row_k is required).  c_ent_*: the crossed variable's combination (`cross_L`), NULL = the same.
+   * The Mz / Mg tables above hold one row per ROW (the combination already applied).           */
+  const int* ent_ptr;     /* [rows + 1] or NULL */
+  const int* ent_k;
+  const double* ent_val;
+  const int* c_ent_ptr;
+  const int* c_ent_k;
+  const double* c_ent_val;
+  /* Limit rows (mpci_lti_sched_rows): the row of G / h every row is added to; NULL for costs.  */
+  const int* row_out;     /* [rows] or NULL */
 } mpci_lti_sched_desc;
 
 typedef struct mpci_lti_sched mpci_lti_sched;
@@ -436,6 +449,19 @@ int mpci_lti_sched_add(const mpci_lti_sched* sched, const double* A_dev, long st
                        const double* B_dev, long strideB, const double* x0_dev,
                        const double* given_dev, const double* terms_dev, long stride_terms,
                        double* P_dev, double* q_dev, long batch, void* stream);
+
+/* Limits with `L` on the per-instance path (restrictions.py:175-179: matrices() = arrow * L;
+ * body.py:253-255: cMo += c @ Mo[sigma]): the fused kernel's row generator writes single samples,
+ * so these rows are left to it as rows WITHOUT a plant part (row_kind 1 of the embedded layout: the
+ * coupling kernel writes their auxiliary entries, zeros under the plant's inputs and h = the bound
+ * and given parts) and this call ADDS the plant part afterwards, on the same stream:
+ *   G[row_out[r]][plant columns] += w_t v_r      h[row_out[r]] -= w_t (cx_t . sum_e val_e A^{k_e + 1} x0)
+ * for a description created with row_out (terms: w = 1 unless the arrow is folded into it; aims
+ * unused).  nc_total = rows of G / h per instance.                                              */
+int mpci_lti_sched_rows(const mpci_lti_sched* sched, const double* A_dev, long strideA,
+                        const double* B_dev, long strideB, const double* x0_dev,
+                        const double* terms_dev, long stride_terms, double* G_dev, double* h_dev,
+                        long nc_total, long batch, void* stream);
 
 /* Closed forms of the reference's named LIP systems (tools.get_system_matrices,
  * python/mpc_interface/tools.py:240-285: A = exp(G tau), B = int_0^tau exp(G t) dt h, there

@@ -26,11 +26,15 @@ constexpr size_t kSmemLimit = 200 * 1024;   // ... unless one row pair needs mor
 
 struct SchedArgs {
   int n, m, N, nv, nz, glen, T, R, K, chunk;
-  const int *voff, *zcol, *row_term, *row_k;
+  const int *voff, *zcol, *row_term, *row_out;
+  const int *ent_ptr, *ent_k, *cent_ptr, *cent_k;  // row r = sum over its entries of val * (sample k's row)
+  const double *ent_val, *cent_val;                // (cent_*: the crossed variable's, nullptr = the same)
   const double *vMz, *vMg, *cMz, *cMg;
   const double *A, *B, *x0, *given, *terms;
   long sA, sB, sT;
   double *P, *q;
+  double *G, *h;  // rows mode (mpci_lti_sched_rows): the rows are ADDED to rows row_out[r] of G / taken from h
+  long nc;
   long batch;
 };
 
@@ -63,7 +67,7 @@ __device__ __forceinline__ void update_rows(double* __restrict__ Pb, const doubl
   }
 }
 
-__global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
+__global__ void __launch_bounds__(kThreads, 3) lti_sched_kernel(SchedArgs a) {
   extern __shared__ double sched_smem[];
   const int n = a.n, m = a.m, nv = a.nv, K = a.K, tl = 3 + 2 * a.n + 2 * a.m, w1 = a.m + 1, slab = a.n * w1;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthr = (int)blockDim.x, nwarps = nthr >> 5;
@@ -118,25 +122,43 @@ __global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
       for (int e = tid; e < rows * nv; e += nthr) V[e] = 0.0, C[e] = 0.0;
       __syncthreads();
       for (int rr = warp; rr < rows; rr += nwarps) {  // a warp per row; V is kept scaled by the weight
-        const int r = r0 + rr, t = a.row_term[r], k = a.row_k[r];
+        const int r = r0 + rr, t = a.row_term[r];
         const double* tt = tb + (long)t * tl;
         const double *vcx = tt + 3, *vcu = vcx + n, *ccx = vcu + m, *ccu = ccx + n;
         const double w = tt[0];
         double* Vr = V + (size_t)rr * nv;
         double* Cr = C + (size_t)rr * nv;
+        const int e0 = a.ent_ptr[r], e1 = a.ent_ptr[r + 1];
+        const bool own = a.cent_ptr == nullptr;  // the crossed variable combines the same samples
+        const int c0 = own ? e0 : a.cent_ptr[r], c1 = own ? e1 : a.cent_ptr[r + 1];
         for (int j = 0; j < m; ++j) {
           double* Vj = Vr + a.voff[j];
           double* Cj = Cr + a.voff[j];
-          for (int p = lane; p <= k; p += 32) {
-            const double* Wd = S + (size_t)(k - p) * slab + j;
-            double av = p == k ? vcu[j] : 0.0, ac = p == k ? ccu[j] : 0.0;
-            for (int i = 0; i < n; ++i) {
-              const double wv = Wd[i * w1];
-              av = fma(vcx[i], wv, av);
-              ac = fma(ccx[i], wv, ac);
+          for (int p = lane; p < K; p += 32) {
+            double sv = 0.0, sc = 0.0;
+            for (int e = e0; e < e1; ++e) {
+              const int k = a.ent_k[e];
+              if (p > k) continue;
+              const double* Wd = S + (size_t)(k - p) * slab + j;
+              double av = p == k ? vcu[j] : 0.0, ac = p == k ? ccu[j] : 0.0;
+              for (int i = 0; i < n; ++i) {
+                const double wv = Wd[i * w1];
+                av = fma(vcx[i], wv, av);
+                ac = fma(ccx[i], wv, ac);
+              }
+              sv = fma(a.ent_val[e], av, sv);
+              if (own) sc = fma(a.ent_val[e], ac, sc);
             }
-            Vj[p] = w * av;
-            Cj[p] = ac;
+            for (int e = own ? c1 : c0; e < c1; ++e) {
+              const int k = a.cent_k[e];
+              if (p > k) continue;
+              const double* Wd = S + (size_t)(k - p) * slab + j;
+              double ac = p == k ? ccu[j] : 0.0;
+              for (int i = 0; i < n; ++i) ac = fma(ccx[i], Wd[i * w1], ac);
+              sc = fma(a.cent_val[e], ac, sc);
+            }
+            Vj[p] = w * sv;
+            Cj[p] = sc;
           }
         }
         const double* cMz = a.cMz ? a.cMz : a.vMz;
@@ -148,9 +170,13 @@ __global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
         const double* cMg = a.cMg ? a.cMg : a.vMg;
         double fv = 0.0, fc = 0.0;
         for (int i = lane; i < n; i += 32) {
-          const double xk = S[(size_t)(k + 1) * slab + i * w1 + m];
-          fv = fma(vcx[i], xk, fv);
-          fc = fma(ccx[i], xk, fc);
+          double xv = 0.0, xc = 0.0;  // the combined free responses sum_e val_e (A^{k_e + 1} x0)[i]
+          for (int e = e0; e < e1; ++e) xv = fma(a.ent_val[e], S[(size_t)(a.ent_k[e] + 1) * slab + i * w1 + m], xv);
+          if (own) xc = xv;
+          for (int e = own ? c1 : c0; e < c1; ++e)
+            xc = fma(a.cent_val[e], S[(size_t)(a.cent_k[e] + 1) * slab + i * w1 + m], xc);
+          fv = fma(vcx[i], xv, fv);
+          fc = fma(ccx[i], xc, fc);
         }
         if (gb) {
           for (int g = lane; g < a.glen; g += 32) {
@@ -164,11 +190,27 @@ __global__ void __launch_bounds__(kThreads) lti_sched_kernel(SchedArgs a) {
           fc += __shfl_xor_sync(0xffffffffu, fc, o);
         }
         if (lane == 0) {
-          epsV[rr] = 0.5 * w * (fv - tt[1]);  // times c_r
-          epsC[rr] = 0.5 * (fc - tt[2]);      // times w v_r
+          epsV[rr] = a.G || a.h ? fv : 0.5 * w * (fv - tt[1]);  // times c_r  (rows mode: the given part itself)
+          epsC[rr] = 0.5 * (fc - tt[2]);                        // times w v_r
         }
       }
       __syncthreads();
+      if (a.G || a.h) {  // rows mode: G[row_out[r]][plant columns] += w v_r,  h[row_out[r]] -= w fv_r
+        for (int rr = warp; rr < rows; rr += nwarps) {
+          const int r = r0 + rr, t = a.row_term[r];
+          const long row = (long)b * a.nc + a.row_out[r];
+          if (a.G) {
+            double* Gr = a.G + row * nv;
+            for (int e = lane; e < m * a.N; e += 32) {
+              const int j = e / a.N, p = e - j * a.N, col = a.voff[j] + p;
+              const double v = V[(size_t)rr * nv + col];
+              if (v != 0.0) atomicAdd(Gr + col, v);  // (the axes of one limit are terms of their own on the same rows)
+            }
+          }
+          if (a.h && lane == 0) atomicAdd(a.h + row, -tb[(long)t * tl] * epsV[rr]);
+        }
+        continue;
+      }
       if (a.P) {
         double* Pb = a.P + b * (long)nv * nv;
         if ((nv & 1) == 0 && (reinterpret_cast<size_t>(Pb) & 15) == 0) {
@@ -217,13 +259,17 @@ int upload(T** dst, const T* src, size_t count) {
 struct mpci_lti_sched {
   int n = 0, m = 0, N = 0, nv = 0, nz = 0, glen = 0, T = 0, R = 0, K = 0, chunk = 0, device = 0;
   size_t smem = 0;
-  int *voff = nullptr, *zcol = nullptr, *row_term = nullptr, *row_k = nullptr;
+  int *voff = nullptr, *zcol = nullptr, *row_term = nullptr, *row_out = nullptr;
+  int *ent_ptr = nullptr, *ent_k = nullptr, *cent_ptr = nullptr, *cent_k = nullptr;
+  double *ent_val = nullptr, *cent_val = nullptr;
   double *vMz = nullptr, *vMg = nullptr, *cMz = nullptr, *cMg = nullptr;
 };
 
 extern "C" int mpci_lti_sched_destroy(mpci_lti_sched* s) {
   if (!s) return 0;
-  cudaFree(s->voff), cudaFree(s->zcol), cudaFree(s->row_term), cudaFree(s->row_k);
+  cudaFree(s->voff), cudaFree(s->zcol), cudaFree(s->row_term), cudaFree(s->row_out);
+  cudaFree(s->ent_ptr), cudaFree(s->ent_k), cudaFree(s->ent_val);
+  cudaFree(s->cent_ptr), cudaFree(s->cent_k), cudaFree(s->cent_val);
   cudaFree(s->vMz), cudaFree(s->vMg), cudaFree(s->cMz), cudaFree(s->cMg);
   delete s;
   return 0;
@@ -236,23 +282,55 @@ extern "C" int mpci_lti_sched_create(const mpci_lti_sched_desc* d, mpci_lti_sche
   if (d->n <= 0 || d->m <= 0 || d->N <= 0 || d->nv <= 0 || d->nz < 0 || d->given_len < 0 || d->n_terms <= 0)
     return fail(-2, "mpci_lti_sched_create: bad sizes (n %d, m %d, N %d, nv %d, nz %d, given_len %d, terms %d)",
                 d->n, d->m, d->N, d->nv, d->nz, d->given_len, d->n_terms);
-  if (!d->row_ptr || !d->row_k) return fail(-1, "mpci_lti_sched_create: row_ptr / row_k missing");
+  if (!d->row_ptr || (!d->row_k && !d->ent_ptr))
+    return fail(-1, "mpci_lti_sched_create: row_ptr / row_k (or ent_ptr) missing");
+  if (d->ent_ptr && (!d->ent_k || !d->ent_val)) return fail(-1, "mpci_lti_sched_create: ent_k / ent_val missing");
+  if (d->c_ent_ptr && (!d->ent_ptr || !d->c_ent_k || !d->c_ent_val))
+    return fail(-1, "mpci_lti_sched_create: c_ent_* needs ent_* and its own c_ent_k / c_ent_val");
   if (d->nz > 0 && !d->z_col) return fail(-1, "mpci_lti_sched_create: z_col missing");
   if (d->row_ptr[0] != 0) return fail(-2, "mpci_lti_sched_create: row_ptr[0] must be 0");
   const int R = d->row_ptr[d->n_terms];
   if (R <= 0) return fail(-2, "mpci_lti_sched_create: no scheduled rows");
-  std::vector<int> row_term(R), voff(d->m);
-  int K = 0;
+  std::vector<int> row_term(R), voff(d->m), ent_ptr(R + 1), ent_k;
+  std::vector<double> ent_val;
   for (int t = 0; t < d->n_terms; ++t) {
     if (d->row_ptr[t + 1] < d->row_ptr[t]) return fail(-2, "mpci_lti_sched_create: row_ptr decreases at term %d", t);
-    for (int r = d->row_ptr[t]; r < d->row_ptr[t + 1]; ++r) {
-      if (d->row_k[r] < 0 || d->row_k[r] >= d->N)
-        return fail(-3, "mpci_lti_sched_create: term %d schedules sample %d outside the horizon of %d", t,
-                    d->row_k[r], d->N);
-      row_term[r] = t;
-      K = std::max(K, d->row_k[r] + 1);
-    }
+    for (int r = d->row_ptr[t]; r < d->row_ptr[t + 1]; ++r) row_term[r] = t;
   }
+  if (d->ent_ptr) {  // rows that combine samples (`L`)
+    if (d->ent_ptr[0] != 0) return fail(-2, "mpci_lti_sched_create: ent_ptr[0] must be 0");
+    for (int r = 0; r < R; ++r)
+      if (d->ent_ptr[r + 1] < d->ent_ptr[r]) return fail(-2, "mpci_lti_sched_create: ent_ptr decreases at row %d", r);
+    ent_ptr.assign(d->ent_ptr, d->ent_ptr + R + 1);
+    ent_k.assign(d->ent_k, d->ent_k + ent_ptr[R]);
+    ent_val.assign(d->ent_val, d->ent_val + ent_ptr[R]);
+  } else {  // one sample per row
+    for (int r = 0; r <= R; ++r) ent_ptr[r] = r;
+    ent_k.assign(d->row_k, d->row_k + R);
+    ent_val.assign(R, 1.0);
+  }
+  int K = 0;
+  auto check = [&](const int* k, int count) {
+    for (int e = 0; e < count; ++e) {
+      if (k[e] < 0 || k[e] >= d->N) return k[e];
+      K = std::max(K, k[e] + 1);
+    }
+    return 0;
+  };
+  int bad = check(ent_k.data(), (int)ent_k.size());
+  if (!bad && d->c_ent_ptr) {
+    if (d->c_ent_ptr[0] != 0) return fail(-2, "mpci_lti_sched_create: c_ent_ptr[0] must be 0");
+    for (int r = 0; r < R; ++r)
+      if (d->c_ent_ptr[r + 1] < d->c_ent_ptr[r])
+        return fail(-2, "mpci_lti_sched_create: c_ent_ptr decreases at row %d", r);
+    bad = check(d->c_ent_k, d->c_ent_ptr[R]);
+  }
+  if (bad || (ent_k.size() && K == 0))
+    return fail(-3, "mpci_lti_sched_create: a term schedules sample %d outside the horizon of %d", bad, d->N);
+  if (K == 0) K = 1;
+  if (d->row_out)
+    for (int r = 0; r < R; ++r)
+      if (d->row_out[r] < 0) return fail(-3, "mpci_lti_sched_create: row %d goes to row %d of G", r, d->row_out[r]);
   for (int j = 0; j < d->m; ++j) {
     voff[j] = d->var_off ? d->var_off[j] : j * d->N;
     if (voff[j] < 0 || voff[j] + d->N > d->nv)
@@ -289,7 +367,15 @@ extern "C" int mpci_lti_sched_create(const mpci_lti_sched_desc* d, mpci_lti_sche
   if (!rc) rc = upload(&s->voff, voff.data(), (size_t)d->m);
   if (!rc) rc = upload(&s->zcol, d->z_col, (size_t)d->nz);
   if (!rc) rc = upload(&s->row_term, row_term.data(), (size_t)R);
-  if (!rc) rc = upload(&s->row_k, d->row_k, (size_t)R);
+  if (!rc) rc = upload(&s->row_out, d->row_out, (size_t)R);
+  if (!rc) rc = upload(&s->ent_ptr, ent_ptr.data(), (size_t)R + 1);
+  if (!rc) rc = upload(&s->ent_k, ent_k.data(), ent_k.size());
+  if (!rc) rc = upload(&s->ent_val, ent_val.data(), ent_val.size());
+  if (!rc && d->c_ent_ptr) {
+    rc = upload(&s->cent_ptr, d->c_ent_ptr, (size_t)R + 1);
+    if (!rc) rc = upload(&s->cent_k, d->c_ent_k, (size_t)d->c_ent_ptr[R]);
+    if (!rc) rc = upload(&s->cent_val, d->c_ent_val, (size_t)d->c_ent_ptr[R]);
+  }
   if (!rc) rc = upload(&s->vMz, d->v_Mz, (size_t)R * d->nz);
   if (!rc) rc = upload(&s->vMg, d->v_Mg, (size_t)R * d->given_len);
   if (!rc) rc = upload(&s->cMz, d->c_Mz, (size_t)R * d->nz);
@@ -307,29 +393,49 @@ extern "C" int mpci_lti_sched_create(const mpci_lti_sched_desc* d, mpci_lti_sche
   return 0;
 }
 
-extern "C" int mpci_lti_sched_add(const mpci_lti_sched* s, const double* A, long strideA, const double* B,
-                                  long strideB, const double* x0, const double* given, const double* terms,
-                                  long stride_terms, double* P, double* q, long batch, void* stream) {
+static int sched_launch(const mpci_lti_sched* s, const char* who, const double* A, long strideA, const double* B,
+                        long strideB, const double* x0, const double* given, const double* terms,
+                        long stride_terms, double* P, double* q, double* G, double* h, long nc, long batch,
+                        void* stream) {
   using mpci::fail;
-  if (!s || !A || !B || !x0 || !terms) return fail(-1, "mpci_lti_sched_add: null argument");
-  if (batch < 0) return fail(-2, "mpci_lti_sched_add: negative batch");
-  if (s->vMg && !given) return fail(-1, "mpci_lti_sched_add: the scheduled costs read `given`, which is NULL");
+  if (!s || !A || !B || !x0 || !terms) return fail(-1, "%s: null argument", who);
+  if (batch < 0) return fail(-2, "%s: negative batch", who);
+  if (s->vMg && !given) return fail(-1, "%s: the terms read `given`, which is NULL", who);
   const long tl = (long)s->T * (3 + 2 * s->n + 2 * s->m);
   if (stride_terms != 0 && stride_terms != tl)
-    return fail(-2, "mpci_lti_sched_add: stride_terms %ld (0 or %ld expected)", stride_terms, tl);
-  if (batch == 0 || (!P && !q)) return 0;
+    return fail(-2, "%s: stride_terms %ld (0 or %ld expected)", who, stride_terms, tl);
+  if (batch == 0 || (!P && !q && !G && !h)) return 0;
   SchedArgs a{};
   a.n = s->n, a.m = s->m, a.N = s->N, a.nv = s->nv, a.nz = s->nz, a.glen = s->glen, a.T = s->T, a.R = s->R;
   a.K = s->K, a.chunk = s->chunk;
-  a.voff = s->voff, a.zcol = s->zcol, a.row_term = s->row_term, a.row_k = s->row_k;
+  a.voff = s->voff, a.zcol = s->zcol, a.row_term = s->row_term, a.row_out = s->row_out;
+  a.ent_ptr = s->ent_ptr, a.ent_k = s->ent_k, a.ent_val = s->ent_val;
+  a.cent_ptr = s->cent_ptr, a.cent_k = s->cent_k, a.cent_val = s->cent_val;
   a.vMz = s->vMz, a.vMg = s->vMg, a.cMz = s->cMz, a.cMg = s->cMg;
   a.A = A, a.B = B, a.x0 = x0, a.given = given, a.terms = terms;
   a.sA = strideA, a.sB = strideB, a.sT = stride_terms;
-  a.P = P, a.q = q, a.batch = batch;
+  a.P = P, a.q = q, a.G = G, a.h = h, a.nc = nc, a.batch = batch;
   int sms = 148;
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, s->device);
   const long grid = std::min<long>(batch, (long)sms * 8);
   lti_sched_kernel<<<(unsigned)grid, kThreads, s->smem, mpci::as_stream(stream)>>>(a);
   MPCI_LAUNCH_CHECK("lti_sched_kernel");
   return 0;
+}
+
+extern "C" int mpci_lti_sched_add(const mpci_lti_sched* s, const double* A, long strideA, const double* B,
+                                  long strideB, const double* x0, const double* given, const double* terms,
+                                  long stride_terms, double* P, double* q, long batch, void* stream) {
+  if (s && s->row_out) return mpci::fail(-1, "mpci_lti_sched_add: the description holds limit rows (row_out)");
+  return sched_launch(s, "mpci_lti_sched_add", A, strideA, B, strideB, x0, given, terms, stride_terms, P, q,
+                      nullptr, nullptr, 0, batch, stream);
+}
+
+extern "C" int mpci_lti_sched_rows(const mpci_lti_sched* s, const double* A, long strideA, const double* B,
+                                   long strideB, const double* x0, const double* terms, long stride_terms,
+                                   double* G, double* h, long nc_total, long batch, void* stream) {
+  if (s && !s->row_out) return mpci::fail(-1, "mpci_lti_sched_rows: the description has no row_out");
+  if (s && (s->vMz || s->vMg)) return mpci::fail(-1, "mpci_lti_sched_rows: limit rows carry no auxiliary tables");
+  return sched_launch(s, "mpci_lti_sched_rows", A, strideA, B, strideB, x0, nullptr, terms, stride_terms, nullptr,
+                      nullptr, G, h, nc_total, batch, stream);
 }

@@ -161,6 +161,11 @@ _SIGNATURES = {
         [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p, _c_double_p,
          _c_double_p, ctypes.c_long, _c_double_p, _c_double_p, ctypes.c_long, ctypes.c_void_p],
     ),
+    "mpci_lti_sched_rows": (
+        ctypes.c_int,
+        [ctypes.c_void_p, _c_double_p, ctypes.c_long, _c_double_p, ctypes.c_long, _c_double_p,
+         _c_double_p, ctypes.c_long, _c_double_p, _c_double_p, ctypes.c_long, ctypes.c_long, ctypes.c_void_p],
+    ),
     "mpci_extend_matrices_static": (
         ctypes.c_int,
         [_c_double_p, _c_double_p, _c_double_p, _c_double_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,

@@ -19,16 +19,17 @@ no slower fallback):
     inputs / such definitions (a point-wise linear form).  The coefficient may be a
     ``Param`` expression: the LIP's centre of pressure ``b = CoM - CoM_ddot / omega_b^2``
     with one pendulum frequency per instance (biped_formulation.py:62);
-  * costs: scalar weight (number or ``Param``), no ``L``, aims that are numbers or ``Param``
-    expressions, optional ``cross``, one or several axes; a cost with a ``schedule`` (a terminal
-    cost: ``range(N - 1, N)``; any list of samples) is added to P and q by a second stage
+  * costs: scalar weight (number or ``Param``), aims that are numbers or ``Param`` expressions,
+    optional ``cross``, one or several axes; a cost with a ``schedule`` (a terminal cost:
+    ``range(N - 1, N)``; any list of samples) or with ``L`` is added to P and q by a second stage
     (csrc/mpci_sched.cu), and so is -- row by row over the whole horizon -- a cost that couples
     states and inputs;
-  * limits: no ``L``; ``schedule`` a contiguous ``range`` (the terminal constraint of the
+  * limits: ``schedule`` a contiguous ``range`` (the terminal constraint of the
     biped, biped_formulation.py:97-102); one axis with ``arrow`` / ``center`` / ``extreme``
     of one row or one row per sample, or several axes with a single-row ``arrow`` (a facet
     of a ``Box.task_space``); ``center`` / ``extreme`` may hold ``Param`` expressions, and so may
-    a single-row ``arrow`` of a limit on plant signals (a box turned per instance).
+    a single-row ``arrow`` (a box turned per instance); a limit with ``L`` keeps its auxiliary
+    and given parts in the coupling stage and gets its plant part from ``mpci_lti_sched_rows``.
 
 Without ``Param`` coefficients the tables are formulation constants (per-instance aims
 travel as the plan's scalar slots).  With them the tables are evaluated per instance --
@@ -74,6 +75,13 @@ class LtiSchedDesc(ctypes.Structure):
         ("v_Mg", ctypes.c_void_p),
         ("c_Mz", ctypes.c_void_p),
         ("c_Mg", ctypes.c_void_p),
+        ("ent_ptr", ctypes.c_void_p),
+        ("ent_k", ctypes.c_void_p),
+        ("ent_val", ctypes.c_void_p),
+        ("c_ent_ptr", ctypes.c_void_p),
+        ("c_ent_k", ctypes.c_void_p),
+        ("c_ent_val", ctypes.c_void_p),
+        ("row_out", ctypes.c_void_p),
     ]
 
 
@@ -305,7 +313,12 @@ class LtiPlan:
         # costs with a schedule (the stage of csrc/mpci_sched.cu, added to P and q afterwards):
         # (weight, form, cross form, aim, cross aim, samples [list of k])
         self.sched_terms = []
-        self._sched = None
+        self.sched_L = {}   # index into sched_terms -> (L, cross L): the cost combines its samples (goal.py:88-104)
+        # limits with L: the plant part of their rows, added by mpci_lti_sched_rows --
+        # (form without auxiliary part, arrow * L [lines, samples], samples, first row in G / h,
+        #  the arrow's Param expression when the limit is turned per instance -- then L alone -- or None)
+        self.lrows = []
+        self._sched = self._lrows = None
 
     # ---- numeric tables -----------------------------------------------------
     def _cost_tables(self, params, batch, xp=_Host):
@@ -554,6 +567,9 @@ class LtiPlan:
             for form in (fv, fc):
                 out += [c for c in list(form.cx.values()) + list(form.cu.values()) if is_expr(c)]
         out += [expr for expr, _r, _M in self.Gz_terms + self.Hg_terms]
+        for form, *_r, coef in self.lrows:
+            out += [c for c in list(form.cx.values()) + list(form.cu.values()) if is_expr(c)]
+            out += [coef] if coef is not None else []
         for (w, fv, _Mz, _E), aim in zip(self.coupled, self.coupled_aims):
             out += [x for x in (w, aim) if is_expr(x)]
             out += [c for c in list(fv.cx.values()) + list(fv.cu.values()) if is_expr(c)]
@@ -570,7 +586,8 @@ class LtiPlan:
         per cost.  Entries: ("one", index into sched_terms) / ("merged", [indices], a)."""
         groups, layout = {}, []
         for i, (_w, fv, fc, _aim, _caim, samples) in enumerate(self.sched_terms):
-            states_only = not (fv.touches_inputs() or fc.touches_inputs() or fv.has_aux() or fc.has_aux())
+            states_only = not (fv.touches_inputs() or fc.touches_inputs() or fv.has_aux() or fc.has_aux()
+                               or i in self.sched_L)
             if states_only:
                 groups.setdefault(tuple(samples), []).append(i)
             else:
@@ -631,12 +648,19 @@ class LtiPlan:
     def sched_desc_tables(self):
         """The constant tables of mpci_lti_sched_desc (include/mpci.h), terms as ``sched_layout``."""
         i32 = lambda x: np.ascontiguousarray(x, dtype=np.int32)  # noqa: E731
+        f64 = lambda x: np.ascontiguousarray(x, dtype=np.float64)  # noqa: E731
         nz, ng = self.nz, (self.ng if self.embedded else 0)
         layout = self.sched_layout()
-        ptr, rows = [0], []
+        combos = []  # per term: (samples, L or None, cross L or None)
         for entry in layout:
-            rows += list(self.sched_terms[entry[1] if entry[0] == "one" else entry[1][0]][5])
-            ptr.append(len(rows))
+            if entry[0] == "one":
+                Lv, Lc = self.sched_L.get(entry[1], (None, None))
+                combos.append((list(self.sched_terms[entry[1]][5]), Lv, Lc))
+            else:
+                combos.append((list(self.sched_terms[entry[1][0]][5]), None, None))
+        ptr = [0]
+        for samples, Lv, _Lc in combos:
+            ptr.append(ptr[-1] + (len(samples) if Lv is None else Lv.shape[0]))
 
         def stack(which, attr, width):
             singles = [self.sched_terms[e[1]] for e in layout if e[0] == "one"]
@@ -644,17 +668,22 @@ class LtiPlan:
                 return None
             blocks = []
             for t, entry in enumerate(layout):
-                count = ptr[t + 1] - ptr[t]
                 term = self.sched_terms[entry[1]] if entry[0] == "one" else None
                 M = getattr(term[which], attr) if term is not None else None
-                blocks.append(np.zeros([count, width]) if M is None else np.asarray(M)[list(term[5])])
-            return np.ascontiguousarray(np.vstack(blocks), dtype=np.float64)
+                if M is None:
+                    blocks.append(np.zeros([ptr[t + 1] - ptr[t], width]))
+                    continue
+                picked = np.asarray(M)[combos[t][0]]
+                L = combos[t][which]
+                blocks.append(picked if L is None else L @ picked)  # vMo = L @ Mo[sigma]  (body.py:279-290)
+            return f64(np.vstack(blocks))
 
         crossed = any(e[0] == "one" and self.sched_terms[e[1]][1] is not self.sched_terms[e[1]][2] for e in layout)
-        t = dict(row_ptr=i32(ptr), row_k=i32(rows), v_Mz=stack(1, "Mz", nz), v_Mg=stack(1, "Mg", ng),
+        t = dict(row_ptr=i32(ptr), row_k=None, v_Mz=stack(1, "Mz", nz), v_Mg=stack(1, "Mg", ng),
                  c_Mz=stack(2, "Mz", nz) if crossed else None, c_Mg=stack(2, "Mg", ng) if crossed else None,
                  var_off=i32(self.var_off) if self.embedded else None,
-                 z_col=i32(self.z_col) if nz else None)
+                 z_col=i32(self.z_col) if nz else None, row_out=None)
+        t.update(_combination_tables(combos))
         for own, cross in (("v_Mz", "c_Mz"), ("v_Mg", "c_Mg")):
             if t[cross] is not None and t[own] is None:  # (the C side wants the own table beside a crossed one)
                 t[own] = np.zeros_like(t[cross])
@@ -662,9 +691,42 @@ class LtiPlan:
                 t[cross] = np.zeros_like(t[own])
         return t
 
+    # ---- limits with L ------------------------------------------------------------
+    def lrow_desc_tables(self):
+        """mpci_lti_sched_desc of the limits with ``L``: one term per (limit, axis with a plant part),
+        its rows the lines of ``arrow * L`` (restrictions.py:175-179), each added to its row of G / h."""
+        i32 = lambda x: np.ascontiguousarray(x, dtype=np.int32)  # noqa: E731
+        combos = [(list(samples), C, None) for _form, C, samples, _row0, _coef in self.lrows]
+        ptr, out = [0], []
+        for _form, C, _samples, row0, _coef in self.lrows:
+            ptr.append(ptr[-1] + C.shape[0])
+            out += list(range(row0, row0 + C.shape[0]))
+        t = dict(row_ptr=i32(ptr), row_k=None, v_Mz=None, v_Mg=None, c_Mz=None, c_Mg=None,
+                 var_off=i32(self.var_off), z_col=i32(self.z_col) if self.nz else None, row_out=i32(out))
+        t.update(_combination_tables(combos))
+        return t
+
+    def lrow_tables(self, params, batch, dev=None):
+        """terms [R, T, 3 + 2n + 2m] of mpci_lti_sched_rows: weight 1 and the plant form of every term."""
+        xp = _Host if dev is None else _Device(dev)
+        params = xp.params(params, batch)
+        n, m = self.n, self.m
+        symbolic = any(form.symbolic() or coef is not None for form, *_r, coef in self.lrows)
+        out = xp.zeros([batch if symbolic else 1, len(self.lrows), 3 + 2 * n + 2 * m])
+        for t, (form, *_r, coef) in enumerate(self.lrows):
+            out[:, t, 0] = 1.0 if coef is None else _value(coef, params)
+            out[:, t, 3:3 + n] = _dense(form.cx, n, params, batch, xp)
+            out[:, t, 3 + n:3 + n + m] = _dense(form.cu, m, params, batch, xp)
+        return out
+
+    def device_lrows(self):
+        if self._lrows is None:
+            self._lrows = _DeviceLtiSched(self, self.lrow_desc_tables())
+        return self._lrows
+
     def device_sched(self):
         if self._sched is None:
-            self._sched = _DeviceLtiSched(self)
+            self._sched = _DeviceLtiSched(self, self.sched_desc_tables())
         return self._sched
 
     # ---- the plant as the kernel sees it --------------------------------------
@@ -756,15 +818,16 @@ class _DeviceLtiPlan:
 class _DeviceLtiSched:
     """mpci_lti_sched of a plan with scheduled costs."""
 
-    def __init__(self, plan):
+    def __init__(self, plan, tables):
         from . import device
 
         device.require_gpu()
-        t = self._keep = plan.sched_desc_tables()
-        at = lambda k: t[k].ctypes.data if t[k] is not None else None  # noqa: E731
+        t = self._keep = tables
+        at = lambda k: t[k].ctypes.data if t.get(k) is not None else None  # noqa: E731
         desc = LtiSchedDesc(plan.n, plan.m, plan.N, plan.nv, at("var_off"), plan.nz, at("z_col"),
                             plan.ng if plan.embedded else 0, len(t["row_ptr"]) - 1, at("row_ptr"), at("row_k"),
-                            at("v_Mz"), at("v_Mg"), at("c_Mz"), at("c_Mg"))
+                            at("v_Mz"), at("v_Mg"), at("c_Mz"), at("c_Mg"), at("ent_ptr"), at("ent_k"),
+                            at("ent_val"), at("c_ent_ptr"), at("c_ent_k"), at("c_ent_val"), at("row_out"))
         handle = ctypes.c_void_p()
         device.check(device.lib().mpci_lti_sched_create(ctypes.byref(desc), ctypes.byref(handle)))
         self.handle = handle
@@ -774,6 +837,35 @@ class _DeviceLtiSched:
         handle, self.handle = getattr(self, "handle", None), None
         if handle:
             self._lib.mpci_lti_sched_destroy(handle)
+
+
+def _combination_tables(combos):
+    """``combos``: per term (samples, L or None, cross L or None).  The rows as combinations of
+    samples for mpci_lti_sched_desc: CSR ``ent_ptr / ent_k / ent_val`` over all rows (a term
+    without L has one entry of 1 per row), ``c_ent_*`` when some cross L differs from its L."""
+    i32 = lambda x: np.ascontiguousarray(x, dtype=np.int32)  # noqa: E731
+
+    def csr(which):
+        ptr, ks, vals = [0], [], []
+        for samples, Lv, Lc in combos:
+            L = (Lv, Lc if Lc is not None else Lv)[which]
+            if L is None:
+                ks += list(samples)
+                vals += [1.0] * len(samples)
+                ptr += list(range(ptr[-1] + 1, ptr[-1] + len(samples) + 1))
+                continue
+            for line in np.asarray(L, dtype=np.float64):
+                cols = np.nonzero(line)[0]
+                ks += [samples[c] for c in cols]
+                vals += list(line[cols])
+                ptr.append(len(ks))
+        return i32(ptr), i32(ks), np.ascontiguousarray(vals, dtype=np.float64)
+
+    out = dict(zip(("ent_ptr", "ent_k", "ent_val"), csr(0)))
+    out.update(c_ent_ptr=None, c_ent_k=None, c_ent_val=None)
+    if any(Lc is not None and Lc is not Lv for _s, Lv, Lc in combos):
+        out.update(zip(("c_ent_ptr", "c_ent_k", "c_ent_val"), csr(1)))
+    return out
 
 
 # ---------------------------------------------------------------------------
@@ -914,7 +1006,8 @@ def lower(form, plant_name):
     plan.n0, plan.m0, plan.blocks, plan.inputs = n0, m0, blocks, inputs
     plan.optim_ID = dict(form.optim_ID)
     plan.given_ID = dict(form.given_ID)
-    plan.embedded = bool(nz or aux_given)
+    # (limits with L are rows of the embedded layout: the fused kernel leaves them to the later stages)
+    plan.embedded = bool(nz or aux_given or any(limit.L for limit in _plan.ordered_limits(form)))
     if plan.embedded:
         plan.nv, plan.ng, plan.nz, plan.z_col = form.optim_len, form.given_len, nz, list(z_col)
         plant_optim = [v for v in form.optim_variables if v not in z_of]
@@ -934,10 +1027,61 @@ def lower(form, plant_name):
     # ---- limits, in the reference's stacking order (body.py:306-318) -------
     Gz_rows, Hg_rows, kinds = [], [], []
     for limit in _plan.ordered_limits(form):
-        if limit.L:
-            _unsupported("a limit with L")
         names = [limit.variable + ax for ax in limit.axes]
         members = [form_of(nm, "a limit") for nm in names]
+        if limit.L:  # rows that combine samples: c @ Mo[sigma] with c = arrow * L  (body.py:253-255)
+            rows = N if any(f.has_plant() for f in members) else members[0].rows
+            if rows is None or rows > N:
+                _unsupported("a limit on '{}' ({} samples, the horizon has {})".format(names[0], rows, N))
+            samples = [int(k) for k in limit.schedule] if limit.schedule else list(range(rows))
+            if any(k < 0 or k >= rows for k in samples):
+                raise IndexError("index {} is out of bounds for axis 0 with size {}".format(
+                    next(k for k in samples if k < 0 or k >= rows), rows))
+            arrow = np.asarray(limit.arrow)
+            turned = arrow.dtype == object and any(is_expr(x) for x in arrow.ravel())
+            if turned and arrow.shape[0] != 1:
+                _unsupported("a per-instance arrow that changes from row to row")
+            lines = int(np.asarray(limit.L[0]).shape[0])
+            Gz_new, Hg_new = np.zeros([lines, nz]), np.zeros([lines, form.given_len + 1])
+            for a, f in enumerate(members):
+                La = np.asarray(limit.L[a], dtype=np.float64)
+                if La.shape != (lines, len(samples)):
+                    raise ValueError("matmul: L is {} for {} scheduled samples and {} lines".format(
+                        La.shape, len(samples), lines))
+                # c = arrow * L (restrictions.py:175-179); a per-instance arrow travels as the term's weight
+                coef = arrow[0, a] if turned and is_expr(arrow[0, a]) else None
+                C = La if coef is not None else np.asarray(arrow[:, a], dtype=np.float64)[:, None] * La
+                if f.Mz is not None and np.any(f.Mz):
+                    if coef is not None:
+                        plan.Gz_terms.append((coef, plan.nc, C @ f.Mz[samples]))
+                    else:
+                        Gz_new += C @ f.Mz[samples]
+                if f.Mg is not None and np.any(f.Mg):
+                    if coef is not None:
+                        term = np.zeros([lines, form.given_len + 1])
+                        term[:, :-1] = -(C @ f.Mg[samples])
+                        plan.Hg_terms.append((coef, plan.nc, term))
+                    else:
+                        Hg_new[:, :-1] -= C @ f.Mg[samples]
+                if f.has_plant():
+                    plan.lrows.append((_Form(f.cx, f.cu, f.rows), C, samples, plan.nc, coef))
+            for coef, col in _bound_parts(limit, lines):
+                if is_expr(coef):
+                    term = np.zeros([lines, form.given_len + 1])
+                    term[:, -1] = col
+                    plan.Hg_terms.append((coef, plan.nc, term))
+                else:
+                    Hg_new[:, -1] += float(coef) * col
+            for e in np.asarray(limit.extreme, dtype=object).ravel():
+                if is_expr(e):
+                    plan.slots.require_nonnegative(e, "limit on '{}'".format(limit.variable))
+            plan.row_offsets.append(plan.nc)
+            plan.limit_rows.append(lines)
+            Gz_rows.append(Gz_new)
+            Hg_rows.append(Hg_new)
+            kinds += [1] * lines
+            plan.nc += lines
+            continue
         on_plant = any(f.has_plant() for f in members) or not plan.embedded
         rows = N if on_plant else members[0].rows
         if rows is None:
@@ -1029,8 +1173,6 @@ def lower(form, plant_name):
         w = cost.weight if is_expr(cost.weight) else float(cost.weight)
         if not is_expr(w) and w == 0.0 and (plan.embedded or cost.L or cost.cross_L or cost.schedule):
             continue  # adds exact zeros (the biped's terminal cost, biped_configuration.py:49)
-        if cost.L or cost.cross_L:
-            _unsupported("a cost with L")
         for a, ax in enumerate(cost.axes):
             vname, cname = cost.variable + ax, cost.cross + ax
             fv, fc = form_of(vname, "a cost"), form_of(cname, "a cost")
@@ -1044,7 +1186,7 @@ def lower(form, plant_name):
             outside = fv.has_aux() or fc.has_aux()
             short = not fv.has_plant() and fv.rows != N  # (e.g. a cost on the footsteps themselves)
             general = mixes or (outside and (fv is not fc or ((is_expr(aim) or is_expr(caim)) and short)))
-            if cost.schedule or general:
+            if cost.schedule or general or cost.L or cost.cross_L:
                 rows = N if (fv.has_plant() or fc.has_plant() or not plan.embedded) else fv.rows
                 if rows is None or rows > N or (fc.rows is not None and not fc.has_plant() and fc.rows < rows):
                     _unsupported("a cost on '{}' ({} samples, the horizon has {})".format(vname, rows, N))
@@ -1052,6 +1194,16 @@ def lower(form, plant_name):
                 if any(k < 0 or k >= rows for k in samples):
                     raise IndexError("index {} is out of bounds for axis 0 with size {}".format(
                         next(k for k in samples if k < 0 or k >= rows), rows))
+                if cost.L or cost.cross_L:  # vMo = L @ Mo[sigma], cMo = cross_L @ Mo_c[sigma]  (body.py:279-290)
+                    Lv = np.asarray(cost.L[a], dtype=np.float64) if cost.L else np.eye(len(samples))
+                    same = (not cost.cross_L and not cost.L) or cost.cross_L is cost.L
+                    Lc = Lv if same else (np.asarray(cost.cross_L[a], dtype=np.float64) if cost.cross_L
+                                          else np.eye(len(samples)))
+                    for M in (Lv, Lc):
+                        if M.ndim != 2 or M.shape[1] != len(samples) or M.shape[0] != Lv.shape[0]:
+                            raise ValueError("matmul: L is {} for {} scheduled samples ({} lines)".format(
+                                M.shape, len(samples), Lv.shape[0]))
+                    plan.sched_L[len(plan.sched_terms)] = (Lv, Lc)
                 plan.sched_terms.append((w, fv, fc, aim, caim, samples))
                 continue
             if outside:
@@ -1215,6 +1367,10 @@ class LtiJob:
                                 for t in plan.coupled_extras(params, batch, dev))
             at = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
             self.coupled = LtiCoupledTables(at(self.ccx), at(self.ccu), *(at(t) for t in self.cextra))
+        self.lrow_terms = None
+        if plan.lrows:
+            self.lrows = plan.device_lrows()
+            self.lrow_terms = plan.lrow_tables(params, batch, dev).contiguous()
         self.sched_terms = None
         if plan.sched_terms:
             self.sched = plan.device_sched()
@@ -1247,6 +1403,12 @@ class LtiJob:
         else:
             rc = lib.mpci_lti_assemble(*head, ptr(self.scalars), *outs, batch, int(hessian), stream)
         device.check(rc)
+        if self.lrow_terms is not None and (outs[2] is not None or outs[3] is not None):
+            terms = self.lrow_terms
+            stride = terms.shape[1] * terms.shape[2] if terms.shape[0] == batch and batch > 1 else 0
+            device.check(lib.mpci_lti_sched_rows(
+                self.lrows.handle, ptr(self.A), self.strideA, ptr(self.B), self.strideB, ptr(self.x0),
+                ptr(terms), stride, outs[2], outs[3], plan.nc, batch, stream))
         if self.sched_terms is not None and (outs[0] is not None or outs[1] is not None):
             terms = self.sched_terms
             stride = terms.shape[1] * terms.shape[2] if terms.shape[0] == batch and batch > 1 else 0

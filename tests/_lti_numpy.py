@@ -136,20 +136,55 @@ def add_scheduled(plan, A, B, given, terms, P, q):
         vcx, vcu = terms[t, 3:3 + n], terms[t, 3 + n:3 + n + m]
         ccx, ccu = terms[t, 3 + n + m:3 + 2 * n + m], terms[t, 3 + 2 * n + m:]
         for r in range(tab["row_ptr"][t], tab["row_ptr"][t + 1]):
-            k = int(tab["row_k"][r])
             rows = []
-            for cx, cu, Mz, Mg in ((vcx, vcu, tab["v_Mz"], tab["v_Mg"]),
-                                   (ccx, ccu, tab["c_Mz"] if tab["c_Mz"] is not None else tab["v_Mz"],
-                                    tab["c_Mg"] if tab["c_Mg"] is not None else tab["v_Mg"])):
-                v = np.zeros([nv])
-                for j in range(m):
-                    for p in range(k + 1):
-                        v[voff[j] + p] = cx @ W[k - p][:, j] + (cu[j] if p == k else 0.0)
+            own = tab["c_ent_ptr"] is None
+            for cx, cu, Mz, Mg, ent in ((vcx, vcu, tab["v_Mz"], tab["v_Mg"], ("ent_ptr", "ent_k", "ent_val")),
+                                        (ccx, ccu, tab["c_Mz"] if tab["c_Mz"] is not None else tab["v_Mz"],
+                                         tab["c_Mg"] if tab["c_Mg"] is not None else tab["v_Mg"],
+                                         ("ent_ptr", "ent_k", "ent_val") if own else ("c_ent_ptr", "c_ent_k", "c_ent_val"))):
+                v, free = np.zeros([nv]), 0.0
+                for e in range(tab[ent[0]][r], tab[ent[0]][r + 1]):
+                    k, val = int(tab[ent[1]][e]), tab[ent[2]][e]
+                    for j in range(m):
+                        for p in range(k + 1):
+                            v[voff[j] + p] += val * (cx @ W[k - p][:, j] + (cu[j] if p == k else 0.0))
+                    free += val * (cx @ xs[k])
                 if Mz is not None:
                     v[np.array(plan.z_col, dtype=int)] = Mz[r]
-                free = cx @ xs[k] + (Mg[r] @ given if Mg is not None else 0.0)
+                free += Mg[r] @ given if Mg is not None else 0.0
                 rows.append((v, free))
             (v, fv), (c, fc) = rows
             P += w * np.outer(v, c)
             q += w / 2 * (v * (fc - caim) + c * (fv - aim))
     return P, q
+
+
+def add_limit_rows(plan, A, B, given, terms, G, h):
+    """What mpci_lti_sched_rows adds for the limits with ``L`` (``plan.lrows``): the plant part of
+    their rows of G and of h, from ``terms`` [T, 3 + 2n + 2m] of this instance
+    (``plan.lrow_tables`` row) and ``plan.lrow_desc_tables``.  Returns (G, h)."""
+    n, m, N, nv = plan.n, plan.m, plan.N, plan.nv
+    given = np.asarray(given, dtype=np.float64)
+    x0 = given[plan.x0_index]
+    Ae, Be = plan.expand_numpy(A, B)
+    W, xs, x = [Be], [], x0
+    for _ in range(N - 1):
+        W.append(Ae @ W[-1])
+    for _ in range(N):
+        x = Ae @ x
+        xs.append(x)
+    tab = plan.lrow_desc_tables()
+    G, h = G.copy(), h.copy()
+    for t in range(len(tab["row_ptr"]) - 1):
+        w, cx, cu = terms[t, 0], terms[t, 3:3 + n], terms[t, 3 + n:3 + n + m]
+        for r in range(tab["row_ptr"][t], tab["row_ptr"][t + 1]):
+            v, free = np.zeros([nv]), 0.0
+            for e in range(tab["ent_ptr"][r], tab["ent_ptr"][r + 1]):
+                k, val = int(tab["ent_k"][e]), tab["ent_val"][e]
+                for j in range(m):
+                    for p in range(k + 1):
+                        v[plan.var_off[j] + p] += val * (cx @ W[k - p][:, j] + (cu[j] if p == k else 0.0))
+                free += val * (cx @ xs[k])
+            G[tab["row_out"][r]] += w * v
+            h[tab["row_out"][r]] -= w * free
+    return G, h

@@ -189,3 +189,51 @@ def test_costs_beyond_the_stage_weights_on_generic_plants(monkeypatch):
         ref = orc.all_qp_matrices(ref_form, vals["x0"][b][:, None])
         for mode in outs:
             cases.assert_qp_close([x[b] for x in outs[mode]], ref)
+
+
+@pytest.mark.parametrize("nx,nu,N,batch", [(3, 2, 8, 5), (6, 2, 60, 9), (12, 4, 50, 4)])
+def test_costs_and_limits_with_L_on_generic_plants(monkeypatch, nx, nu, N, batch):
+    """``L`` on the per-instance path (goal.py:88-104, restrictions.py:75-90): costs whose rows combine
+    the samples of the horizon (also crossed with its own ``cross_L``, also on a window) through the
+    scheduled-cost stage; limits as rows of the embedded layout whose plant part mpci_lti_sched_rows
+    adds.  Generic plants: the embedded layout without any auxiliary variable.  Against the oracle."""
+    import mpc_interface_b200.tools as tools
+    from _numpy_backend import NumpyBackend
+    from mpc_interface_b200 import Constraint, Cost, Param
+    from mpc_interface_b200.examples import synthetic
+
+    seed = 900 + nx
+    rng = np.random.default_rng(seed)
+    _, _, Q, R = synthetic.generic_system(seed, nx, nu)
+    A, B = synthetic.generic_plants(seed, batch, nx, nu)
+    A = np.eye(nx) + 0.3 * (A - np.eye(nx))
+    vals = synthetic.generic_inputs(seed, batch, nx)
+    gain = rng.uniform(0.5, 2.0, batch)
+    L1, L2, L3 = rng.normal(size=[3, N]), rng.normal(size=[3, N]), rng.normal(size=[2, 4])
+    lin = rng.normal(size=[1, nx])
+
+    def build(b, refs, weight, backend=None):
+        f = cases.formulate_generic(A[b], B[b], Q, R, N, lin, refs=refs, backend=backend)
+        f.incorporate_goal("smooth", Cost("z0", weight, aim=[refs[0]], L=L1))
+        f.incorporate_goal("crossed", Cost("z1", 0.4, aim=[0.1], L=L1, cross="u0", cross_aim=[refs[1]], cross_L=L2))
+        f.incorporate_goal("window", Cost("u1", 2.0, L=L3, schedule=range(3, 7)))
+        f.incorporate_constraint("mean", Constraint("z2", 1.5, L=L1, arrow=[[-1.0]]))
+        f.incorporate_constraint("late", Constraint("u0", np.array([0.5, 0.7]), L=L3, schedule=range(2, 6), center=[[0.1]]))
+        f.make_preview_matrices()
+        return f
+
+    form = build(0, [Param("ref%d" % i) for i in range(nx)], Param("gain"))
+    plan = form.lti_plan("plant")
+    assert plan.embedded and plan.nz == 0 and len(plan.lrows) == 2
+    params = {"ref%d" % i: vals["ref"][:, i] for i in range(nx)}
+    params["gain"] = gain
+    outs = {}
+    for mode in ("dmma", "recursion"):
+        out = form.generate_all_qp_matrices_batched(vals["x0"], params, dynamics={"plant": (A, B)}, hessian=mode)
+        outs[mode] = (out.G_numpy(), out.h_numpy(), out.P_numpy(), out.q_numpy())
+    monkeypatch.setattr(tools, "extend_matrices", orc.extend_matrices)
+    for b in sorted({0, batch // 2, batch - 1}):
+        ref_form = build(b, [float(x) for x in vals["ref"][b]], float(gain[b]), backend=NumpyBackend())
+        ref = orc.all_qp_matrices(ref_form, vals["x0"][b][:, None])
+        for mode in outs:
+            cases.assert_qp_close([x[b] for x in outs[mode]], ref)

@@ -43,16 +43,17 @@ def test_lowering_matches_reference(cpu_extend, name, per_instance):
 def test_lowering_refuses_unsupported(cpu_extend):
     g = cases.golden("generic_small")
     form = _formulation(g, cpu_extend, False)
-    form.incorporate_goal("weighted rows", Cost("z0", 1.0, L=np.eye(int(g["N"]))))
-    with pytest.raises(NotImplementedError):
-        form.lti_plan("plant")
-    form = _formulation(g, cpu_extend, False)
     form.incorporate_goal("sched", Cost("z0", 1.0, schedule=range(2, int(g["N"]) + 1)))
     with pytest.raises(IndexError):  # (the reference's fancy index fails the same way, body.py:283)
         form.lti_plan("plant")
     form = _formulation(g, cpu_extend, False)
-    form.incorporate_constraint("L", Constraint("z1", 3.0, L=np.eye(int(g["N"]))))
-    with pytest.raises(NotImplementedError):
+    form.incorporate_goal("short L", Cost("z0", 1.0, L=np.eye(int(g["N"]) - 1)))
+    with pytest.raises(ValueError, match="matmul"):  # (as the reference's L @ Mo[schedule], body.py:280)
+        form.lti_plan("plant")
+    form = _formulation(g, cpu_extend, False)
+    form.incorporate_constraint("rowwise turn", Constraint("z1", 3.0, arrow=np.array(
+        [[Param("ref0")]] * int(g["N"]), dtype=object)))
+    with pytest.raises(NotImplementedError, match="row to row"):
         form.lti_plan("plant")
     form = _formulation(g, cpu_extend, False)
     with pytest.raises(KeyError):
@@ -237,7 +238,8 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
 @pytest.mark.parametrize("seed,scheduled,general,turned", [(s, False, False, False) for s in range(200, 212)]
                          + [(s, True, False, False) for s in range(220, 232)]
                          + [(s, True, True, False) for s in range(240, 256)]
-                         + [(s, True, True, True) for s in range(260, 276)])
+                         + [(s, True, True, True) for s in range(260, 276)]
+                         + [(s, True, True, "L") for s in range(280, 296)])
 def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, general, turned):
     """tests/_embedded_forms.py: random structures around a per-instance plant (four named
     plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
@@ -249,7 +251,8 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
     crossed costs between any two signals, per-instance weights / aims on signals with a part outside
     the plant and a definition that mixes states and the input (whole-horizon terms of that stage).
     ``turned``: limits turned / scaled per instance, on signals with parts outside the plant too
-    (per-instance Gz and h map of the coupling stage)."""
+    (per-instance Gz and h map of the coupling stage); "L": also costs and limits with a matrix ``L``
+    over their samples."""
     import _embedded_forms as forms
     from oracle import reference
 
@@ -257,7 +260,7 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
         pytest.skip("oracle/_ref is not staged")
     from mpc_interface_b200 import dynamics
 
-    spec = forms.draw(seed, scheduled, general, turned=turned)
+    spec = forms.draw(seed, scheduled, general, with_L=turned == "L", turned=bool(turned))
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
                        backend=NumpyBackend())
     plan = form.lti_plan("LIP")
@@ -288,6 +291,10 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
             terms = plan.sched_tables(params, batch)
             got = got[:2] + _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b],
                                                      terms[b if terms.shape[0] > 1 else 0], got[2], got[3])
+        if plan.lrows:
+            rows = plan.lrow_tables(params, batch)
+            got = _lti_numpy.add_limit_rows(plan, plant.A, plant.B, given[b], rows[b if rows.shape[0] > 1 else 0],
+                                            got[0], got[1]) + tuple(got[2:])
         cases.assert_qp_close(got, want)
 
 
@@ -514,3 +521,51 @@ def test_biped_with_per_instance_plants_and_yaw_lowering(cpu_extend, system, N):
                                            {k: v[b] for k, v in tables.items()}, (ccx[b], ccu[b]),
                                            tuple(None if t is None else t[b] for t in extras))
         cases.assert_qp_close(got, want)
+
+
+@pytest.mark.parametrize("per_instance", [False, True])
+def test_costs_and_limits_with_L_on_generic_plants(cpu_extend, per_instance):
+    """``L`` (goal.py:88-104, restrictions.py:75-90): rows that combine the samples of the horizon.
+    Costs go through the scheduled-cost stage with every row a combination (also crossed, with its
+    own ``cross_L``); a limit becomes rows of the embedded layout -- bound in the h map, plant part
+    added by mpci_lti_sched_rows.  A plain generic plant: the layout is the embedded one with no
+    auxiliary variable at all.  Against the oracle's body.py:236-302."""
+    from oracle import qp_oracle
+
+    rng = np.random.default_rng(11)
+    nx, nu, N, batch = 3, 2, 8, 3
+    A = np.eye(nx) + 0.1 * rng.normal(size=[batch, nx, nx])
+    B = 0.3 * rng.normal(size=[batch, nx, nu])
+    Q, R = np.eye(nx), np.eye(nu)
+    refs = [Param("ref%d" % i) for i in range(nx)]
+    L1, L2, L3 = rng.normal(size=[3, N]), rng.normal(size=[3, N]), rng.normal(size=[2, 4])
+    gain = Param("gain") if per_instance else 1.7
+
+    def build(b):
+        f = cases.formulate_generic(A[b], B[b], Q, R, N, rng.normal(size=[0, nx]), refs=refs, backend=NumpyBackend())
+        f.incorporate_goal("smooth", Cost("z0", gain, aim=[refs[0]], L=L1))
+        f.incorporate_goal("crossed", Cost("z1", 0.4, aim=[0.1], L=L1, cross="u0", cross_aim=[refs[1]], cross_L=L2))
+        f.incorporate_goal("window", Cost("u1", 2.0, L=L3, schedule=range(3, 7)))
+        f.incorporate_constraint("mean", Constraint("z2", 1.5, L=L1, arrow=[[-1.0]]))
+        f.incorporate_constraint("late", Constraint("u0", np.array([0.5, 0.7]), L=L3, schedule=range(2, 6), center=[[0.1]]))
+        f.make_preview_matrices()
+        return f
+
+    form = build(0)
+    plan = form.lti_plan("plant")
+    assert plan.embedded and plan.nz == 0 and len(plan.lrows) == 2 and sorted(plan.sched_L) == [0, 1, 2]
+    assert plan.nc == form.lti_plan("plant").nc == 2 * nu * N + 3 + 2
+    x0 = rng.normal(size=[batch, nx])
+    params = {"ref%d" % i: rng.normal(size=batch) for i in range(nx)}
+    params["gain"] = rng.uniform(0.5, 2.0, batch)
+    terms, rows = plan.sched_tables(params, batch), plan.lrow_tables(params, batch)
+    tables = plan.instance_tables(params, batch) if plan.per_instance else None
+    names = [repr(e) for e in plan.slots.exprs]
+    for b in range(batch):
+        one = {k: float(v[b]) for k, v in params.items()}
+        scalars = np.array([one[nm] for nm in names])
+        inst = {k: v[b] for k, v in tables.items()} if tables is not None else None
+        G, h, P, q = _lti_numpy.evaluate_embedded(plan, A[b], B[b], x0[b], scalars, inst)
+        P, q = _lti_numpy.add_scheduled(plan, A[b], B[b], x0[b], terms[b if terms.shape[0] > 1 else 0], P, q)
+        G, h = _lti_numpy.add_limit_rows(plan, A[b], B[b], x0[b], rows[b if rows.shape[0] > 1 else 0], G, h)
+        cases.assert_qp_close((G, h, P, q), qp_oracle.all_qp_matrices(build(b), x0[b][:, None], one))
