@@ -170,9 +170,9 @@ def test_scheduled_cost_stage_validation_needs_no_gpu(lib):
     i32 = lambda *v: np.array(v, dtype=np.int32)  # noqa: E731
     ptr, rows, zcol = i32(0, 2), i32(1, 4), i32(2)
 
-    def create(n=2, m=1, N=4, nv=5, nz=0, zc=None, rp=ptr, rk=rows, terms=1):
+    def create(n=2, m=1, N=4, nv=5, nz=0, zc=None, rp=ptr, rk=rows, terms=1, ep=None):
         desc = lti.LtiSchedDesc(n, m, N, nv, None, nz, zc, 0, terms, rp.ctypes.data, rk.ctypes.data,
-                                None, None, None, None)
+                                None, None, None, None, ep, None, None, None, None, None, None)
         return lib.mpci_lti_sched_create(ctypes.byref(desc), ctypes.byref(handle))
 
     assert create() < 0 and b"outside the horizon" in lib.mpci_last_error()  # sample 4 of 4
@@ -180,7 +180,10 @@ def test_scheduled_cost_stage_validation_needs_no_gpu(lib):
     assert create(nz=1, zc=zcol.ctypes.data, rk=i32(1, 3)) < 0 and b"inside input" in lib.mpci_last_error()
     assert create(terms=0) < 0 and b"bad sizes" in lib.mpci_last_error()
     assert create(rp=i32(0, 0), rk=i32(1, 3)) < 0 and b"no scheduled rows" in lib.mpci_last_error()
+    assert create(rk=i32(1, 3), ep=ptr.ctypes.data) < 0 and b"ent_k / ent_val missing" in lib.mpci_last_error()
     assert not handle.value
+    rc = lib.mpci_lti_sched_rows(None, None, 0, None, 0, None, None, 0, None, None, 4, 1, None)
+    assert rc < 0 and b"null argument" in lib.mpci_last_error()
     rc = lib.mpci_lti_sched_add(None, None, 0, None, 0, None, None, None, 0, None, None, 1, None)
     assert rc < 0 and b"null argument" in lib.mpci_last_error()
     assert lib.mpci_lti_sched_destroy(None) == 0
