@@ -15,8 +15,9 @@ no slower fallback):
     several axes (the same ``(A_b, B_b)`` on ``_x`` and ``_y``: the kernel sees the
     block-diagonal plant); the plant's inputs are the optimisation variables, in any
     order; the initial states ``<vector>0<axis>`` are the only given variables;
-  * every other definition is a scalar-coefficient ``LineCombo`` of plant states /
-    inputs / such definitions (a point-wise linear form).  The coefficient may be a
+  * every other definition is a ``LineCombo`` of plant states / inputs / such definitions with
+    scalar coefficients (a point-wise linear form), or with numeric matrix coefficients (a rate
+    ``(I - shift) @ b``: no stage form, handled row by row by mpci_sched.cu).  The coefficient may be a
     ``Param`` expression: the LIP's centre of pressure ``b = CoM - CoM_ddot / omega_b^2``
     with one pendulum frequency per instance (biped_formulation.py:62);
   * costs: scalar weight (number or ``Param``), aims that are numbers or ``Param`` expressions,
@@ -149,18 +150,25 @@ class _Form:
     (a float or a ``Param`` expression), plus an auxiliary part ``Mz @ z + Mg @ given`` over
     the optimisation variables that are not plant inputs and the given variables that are not
     the plant's initial state (dense numeric [rows, nz] / [rows, given_len], or None).
-    ``rows``: samples of the signal (None: not fixed yet; a plant part means the horizon)."""
+    ``rows``: samples of the signal (None: not fixed yet; a plant part means the horizon).
+    ``mix``: plant parts that enter through a MATRIX coefficient -- ``M @ (cx . x + cu . u)`` with M
+    numeric [rows, N] (a delayed plant signal, a rate ``(I - shift) @ b``): [(M, cx, cu)].  Such a
+    signal has no stage form; its costs and limits go row by row through mpci_sched.cu."""
 
     def __init__(self, cx=None, cu=None, rows=None, Mz=None, Mg=None):
         self.cx, self.cu = dict(cx or {}), dict(cu or {})
         self.rows, self.Mz, self.Mg = rows, Mz, Mg
+        self.mix = []
 
     def add(self, other, coef):
         """self += coef * other, ``coef`` a float or a ``Param`` expression (the latter on a
         form without auxiliary part only)."""
         if other.has_aux() and is_expr(coef):
             _unsupported("a Param coefficient on a variable outside the plant")
+        if other.mix and is_expr(coef):
+            _unsupported("a Param coefficient on a signal that holds a matrix coefficient")
         self._fit_rows(other.rows)
+        self.mix += [(coef * M, cx, cu) for M, cx, cu in other.mix]
         for mine, theirs in ((self.cx, other.cx), (self.cu, other.cu)):
             for idx, c in theirs.items():
                 term = coef * c
@@ -174,13 +182,14 @@ class _Form:
 
     def add_matrix(self, other, matrix, where):
         """self += matrix @ other for a numeric [rows, other.rows] coefficient (the shifted
-        bias of biped_formulation.py:57,63); ``other`` must not have a plant part."""
-        if other.cx or other.cu:
-            _unsupported("a matrix coefficient on a plant variable in the definition '{}'".format(where))
+        bias of biped_formulation.py:57,63); a plant part of ``other`` joins ``mix``."""
         if other.rows is not None and matrix.shape[1] != other.rows:
             raise ValueError("matmul: a [{}x{}] coefficient on a variable of {} samples in '{}'".format(
                 matrix.shape[0], matrix.shape[1], other.rows, where))
         self._fit_rows(matrix.shape[0])
+        if other.cx or other.cu:
+            self.mix.append((np.array(matrix, dtype=np.float64), dict(other.cx), dict(other.cu)))
+        self.mix += [(matrix @ M, cx, cu) for M, cx, cu in other.mix]
         for name in ("Mz", "Mg"):
             theirs = getattr(other, name)
             if theirs is not None:
@@ -202,14 +211,23 @@ class _Form:
     def has_plant(self):
         return self.touches_states() or self.touches_inputs()
 
+    def _maps(self, which):
+        return [getattr(self, which)] + [part[1 if which == "cx" else 2] for part in self.mix]
+
     def symbolic(self):
-        return any(is_expr(c) for c in list(self.cx.values()) + list(self.cu.values()))
+        return any(is_expr(c) for which in ("cx", "cu") for mp in self._maps(which) for c in mp.values())
 
     def touches_states(self):
-        return any(is_expr(c) or c != 0.0 for c in self.cx.values())
+        return any(is_expr(c) or c != 0.0 for mp in self._maps("cx") for c in mp.values())
 
     def touches_inputs(self):
-        return any(is_expr(c) or c != 0.0 for c in self.cu.values())
+        return any(is_expr(c) or c != 0.0 for mp in self._maps("cu") for c in mp.values())
+
+    def parts(self, N):
+        """The signal as ``sum_a M_a @ (form_a)``: [(form without mix, M_a [rows, N] or None = identity)],
+        the first one carrying the direct plant part and the auxiliary part."""
+        out = [(_Form(self.cx, self.cu, self.rows, self.Mz, self.Mg), None)]
+        return out + [(_Form(cx, cu, N), M) for M, cx, cu in self.mix]
 
 
 class _Host:
@@ -1007,7 +1025,11 @@ def lower(form, plant_name):
     plan.optim_ID = dict(form.optim_ID)
     plan.given_ID = dict(form.given_ID)
     # (limits with L are rows of the embedded layout: the fused kernel leaves them to the later stages)
-    plan.embedded = bool(nz or aux_given or any(limit.L for limit in _plan.ordered_limits(form)))
+    def rows_stage(limit):  # L, or a signal with a matrix coefficient on a plant variable
+        members = [forms.get(limit.variable + ax) for ax in limit.axes]
+        return bool(limit.L) or any(isinstance(f, _Form) and f.mix for f in members)
+
+    plan.embedded = bool(nz or aux_given or any(rows_stage(limit) for limit in _plan.ordered_limits(form)))
     if plan.embedded:
         plan.nv, plan.ng, plan.nz, plan.z_col = form.optim_len, form.given_len, nz, list(z_col)
         plant_optim = [v for v in form.optim_variables if v not in z_of]
@@ -1029,9 +1051,9 @@ def lower(form, plant_name):
     for limit in _plan.ordered_limits(form):
         names = [limit.variable + ax for ax in limit.axes]
         members = [form_of(nm, "a limit") for nm in names]
-        if limit.L:  # rows that combine samples: c @ Mo[sigma] with c = arrow * L  (body.py:253-255)
-            rows = N if any(f.has_plant() for f in members) else members[0].rows
-            if rows is None or rows > N:
+        if rows_stage(limit):  # rows that combine samples: c @ Mo[sigma] with c = arrow * L  (body.py:253-255)
+            rows = members[0].rows if members[0].rows is not None else N
+            if rows > N or any(f.has_plant() and f.rows != N for f in members):
                 _unsupported("a limit on '{}' ({} samples, the horizon has {})".format(names[0], rows, N))
             samples = [int(k) for k in limit.schedule] if limit.schedule else list(range(rows))
             if any(k < 0 or k >= rows for k in samples):
@@ -1041,10 +1063,13 @@ def lower(form, plant_name):
             turned = arrow.dtype == object and any(is_expr(x) for x in arrow.ravel())
             if turned and arrow.shape[0] != 1:
                 _unsupported("a per-instance arrow that changes from row to row")
-            lines = int(np.asarray(limit.L[0]).shape[0])
+            lines = int(np.asarray(limit.L[0]).shape[0]) if limit.L else len(samples)
+            if not limit.L and limit.nlines is not None and int(limit.nlines) != lines:
+                raise ValueError("operands could not be broadcast together with shapes ({},1) ({},{})".format(
+                    int(limit.nlines), lines, plan.nv))
             Gz_new, Hg_new = np.zeros([lines, nz]), np.zeros([lines, form.given_len + 1])
             for a, f in enumerate(members):
-                La = np.asarray(limit.L[a], dtype=np.float64)
+                La = np.asarray(limit.L[a], dtype=np.float64) if limit.L else np.eye(lines)
                 if La.shape != (lines, len(samples)):
                     raise ValueError("matmul: L is {} for {} scheduled samples and {} lines".format(
                         La.shape, len(samples), lines))
@@ -1063,8 +1088,15 @@ def lower(form, plant_name):
                         plan.Hg_terms.append((coef, plan.nc, term))
                     else:
                         Hg_new[:, :-1] -= C @ f.Mg[samples]
-                if f.has_plant():
-                    plan.lrows.append((_Form(f.cx, f.cu, f.rows), C, samples, plan.nc, coef))
+                for part, M in f.parts(N):  # the plant parts: direct, and through matrix coefficients
+                    if not part.has_plant():
+                        continue
+                    if M is None:
+                        full = np.zeros([lines, N])
+                        full[:, samples] = C
+                    else:
+                        full = C @ M[samples, :]
+                    plan.lrows.append((_Form(part.cx, part.cu, N), full, list(range(N)), plan.nc, coef))
             for coef, col in _bound_parts(limit, lines):
                 if is_expr(coef):
                     term = np.zeros([lines, form.given_len + 1])
@@ -1185,7 +1217,8 @@ def lower(form, plant_name):
             mixes = (fv.touches_states() and fc.touches_inputs()) or (fv.touches_inputs() and fc.touches_states())
             outside = fv.has_aux() or fc.has_aux()
             short = not fv.has_plant() and fv.rows != N  # (e.g. a cost on the footsteps themselves)
-            general = mixes or (outside and (fv is not fc or ((is_expr(aim) or is_expr(caim)) and short)))
+            mixed = bool(fv.mix or fc.mix)  # a matrix coefficient on a plant variable: no stage form
+            general = mixes or mixed or (outside and (fv is not fc or ((is_expr(aim) or is_expr(caim)) and short)))
             if cost.schedule or general or cost.L or cost.cross_L:
                 rows = N if (fv.has_plant() or fc.has_plant() or not plan.embedded) else fv.rows
                 if rows is None or rows > N or (fc.rows is not None and not fc.has_plant() and fc.rows < rows):
@@ -1194,7 +1227,8 @@ def lower(form, plant_name):
                 if any(k < 0 or k >= rows for k in samples):
                     raise IndexError("index {} is out of bounds for axis 0 with size {}".format(
                         next(k for k in samples if k < 0 or k >= rows), rows))
-                if cost.L or cost.cross_L:  # vMo = L @ Mo[sigma], cMo = cross_L @ Mo_c[sigma]  (body.py:279-290)
+                Lv = Lc = None
+                if cost.L or cost.cross_L or mixed:  # vMo = L @ Mo[sigma], cMo = cross_L @ Mo_c[sigma]  (body.py:279-290)
                     Lv = np.asarray(cost.L[a], dtype=np.float64) if cost.L else np.eye(len(samples))
                     same = (not cost.cross_L and not cost.L) or cost.cross_L is cost.L
                     Lc = Lv if same else (np.asarray(cost.cross_L[a], dtype=np.float64) if cost.cross_L
@@ -1203,6 +1237,26 @@ def lower(form, plant_name):
                         if M.ndim != 2 or M.shape[1] != len(samples) or M.shape[0] != Lv.shape[0]:
                             raise ValueError("matmul: L is {} for {} scheduled samples ({} lines)".format(
                                 M.shape, len(samples), Lv.shape[0]))
+                if mixed:  # V = sum_a L_a T_a, C = sum_b L_b T_b: one crossed term per pair of parts
+                    if rows != N:
+                        _unsupported("a cost on '{}' ({} samples, the horizon has {})".format(vname, rows, N))
+
+                    def over_horizon(L0, M):
+                        if M is not None:
+                            return L0 @ M[samples, :]
+                        full = np.zeros([L0.shape[0], N])
+                        full[:, samples] = L0
+                        return full
+
+                    vparts = fv.parts(N)
+                    cparts = vparts if fc is fv else fc.parts(N)
+                    for ia, (pa, Ma) in enumerate(vparts):
+                        for ib, (pb, Mb) in enumerate(cparts):
+                            plan.sched_L[len(plan.sched_terms)] = (over_horizon(Lv, Ma), over_horizon(Lc, Mb))
+                            plan.sched_terms.append((w, pa, pb, aim if ia == 0 else 0.0, caim if ib == 0 else 0.0,
+                                                     list(range(N))))
+                    continue
+                if Lv is not None:
                     plan.sched_L[len(plan.sched_terms)] = (Lv, Lc)
                 plan.sched_terms.append((w, fv, fc, aim, caim, samples))
                 continue

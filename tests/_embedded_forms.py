@@ -22,7 +22,7 @@ INPUT = {"dP->CCC": "cCoP_dot", "J->CCC": "CoM_dddot", "dP->CCP": "cCoP_dot", "P
 OMEGA_COEFS = ("inv", "neg_inv2", "times", "num")
 
 
-def draw(seed, scheduled=False, general=False, with_L=False, turned=False):
+def draw(seed, scheduled=False, general=False, with_L=False, turned=False, delayed=False):
     """The structure as plain data (a dict of lists and numbers).  ``scheduled``: some of the
     costs act on a few samples only (goal.py `schedule`).  ``general``: also costs that the stage
     weights of the fused kernel cannot express -- crossed costs between any two signals, per-instance
@@ -30,7 +30,9 @@ def draw(seed, scheduled=False, general=False, with_L=False, turned=False):
     the input.  ``with_L``: some uncrossed costs and some limits combine their samples through a
     matrix ``L`` (goal.py:88-104, restrictions.py:75-90) -- mode A only, the per-instance path
     refuses ``L``.  ``turned``: the facets over both axes and some one-axis limits are turned / scaled
-    per instance (their one-row arrows are rotated by the angle ``vel``, as rotate_in_TS does)."""
+    per instance (their one-row arrows are rotated by the angle ``vel``, as rotate_in_TS does).
+    ``delayed``: definitions with a MATRIX coefficient on a plant signal (a rate ``(I - shift) @ u1``,
+    a delayed state)."""
     rng = np.random.default_rng(seed)
     system = SYSTEMS[rng.integers(len(SYSTEMS))]
     axes = ["_x", "_y"] if rng.random() < 0.4 else ["_x"]
@@ -70,6 +72,11 @@ def draw(seed, scheduled=False, general=False, with_L=False, turned=False):
         defs.append(("side", aux_terms()))
     if rng.random() < 0.5:
         defs.append(("mix2", [("mix", "num", float(rng.uniform(0.5, 2.0)))] + plant_terms(1)))
+    if delayed:
+        defs.append(("rate", [("u1", "rate", float(rng.uniform(0.5, 2.0)))]
+                     + ([(aux_vars[0], "num", float(rng.uniform(-1.0, 1.0)))] if rng.random() < 0.5 else [])))
+        if rng.random() < 0.5:
+            defs.append(("late", [(str(STATES[system][0]), "shift", 1.0), ("rate", "num", float(rng.uniform(-1.0, 1.0)))]))
     if general and rng.random() < 0.7:
         defs.append(("ux", plant_terms(1) + [(INPUT[system], "num", float(rng.uniform(-0.5, 0.5)))]))
     spec["defs"] = defs
@@ -189,6 +196,8 @@ def build(spec, api, omega, tau, vel, gain, nominal=(0.1, 3.3), backend=None):
             return -value / omega**2
         if kind == "times":
             return value * omega
+        if kind == "rate":
+            return value * (np.eye(N) - shift.T)
         if kind == "shift":
             return value * shift
         if kind == "diag":

@@ -444,3 +444,54 @@ def test_box_transforms_per_instance(plants):
         want = one.generate_all_qp_matrices(one.arrange_given(
             {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID}))
         cases.assert_qp_close(tuple(x[b] for x in got), want)
+
+
+@pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
+@pytest.mark.parametrize("N,batch", [(24, 5), (60, 3)])
+def test_biped_plants_with_cop_rate_limits_and_costs(N, batch):
+    """A matrix coefficient ON a plant signal: the CoP rate ``(I - shift) @ b`` (b with its
+    per-instance 1 / omega_b^2) next to the footsteps, penalised and limited -- crossed terms of
+    the scheduled-cost stage over the pairs of the signal's parts, rows of mpci_lti_sched_rows.
+    One plant per robot; every instance formulated by the unmodified reference."""
+    import types
+
+    from mpc_interface_b200 import Constraint, Cost, LineCombo, Param
+    from mpc_interface_b200.examples import biped, synthetic
+
+    ref = reference.load()
+    api = types.SimpleNamespace(ControlSystem=ref.ControlSystem, ExtendedSystem=ref.ExtendedSystem,
+                                DomainVariable=ref.DomainVariable, Formulation=ref.Formulation,
+                                LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box, tools=ref.tools)
+    D = np.eye(N) - np.eye(N, k=-1)
+
+    def with_rates(form, combo, cost, constraint):
+        for ax in ("_x", "_y"):
+            form.incorporate_definition("db" + ax, combo({"b" + ax: D, "s" + ax: -0.5}))
+        form.incorporate_goal("CoP rate", cost("db", 0.3, aim=[0.01, 0.0], axes=["_x", "_y"]))
+        form.incorporate_constraint("CoP rate limit", constraint("db", 0.2, axes=["_x"]))
+        form.incorporate_constraint("late rate", constraint("db", 0.1, axes=["_y"], arrow=[[-1.0]],
+                                                            schedule=range(N - 3, N)))
+        form.make_preview_matrices()
+        return form
+
+    conf = biped.default_configuration(N)
+    conf.system = "dP->CCC"
+    form = with_rates(biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
+                                            target_vel=[Param("vel_x"), Param("vel_y")]), LineCombo, Cost, Constraint)
+    vals = synthetic.biped_inputs(21 + N, batch, N)
+    vals["tau"] = np.random.default_rng(N).uniform(0.08, 0.12, batch) * min(1.0, 30.0 / N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    wants = []
+    for b in range(batch):
+        one = with_rates(biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
+                                               target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api),
+                         ref.LineCombo, ref.Cost, ref.Constraint)
+        wants.append(one.generate_all_qp_matrices(one.arrange_given(
+            {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID})))
+    for mode in ("recursion", "dmma"):
+        out = form.generate_all_qp_matrices_batched(
+            given, params, dynamics={"LIP": ("dP->CCC", vals["tau"], vals["omega"])}, hessian=mode)
+        got = [x.cpu().numpy() for x in (out.G, out.h, out.P, out.q)]
+        for b in range(batch):
+            cases.assert_qp_close(tuple(x[b] for x in got), wants[b])

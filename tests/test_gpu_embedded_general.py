@@ -88,7 +88,8 @@ def test_soft_constrained_lip_against_the_live_reference(N, order):
                          + [(s, True, False, False) for s in range(400, 424)]
                          + [(s, True, True, False) for s in range(500, 532)]
                          + [(s, True, True, True) for s in range(700, 732)]
-                         + [(s, True, True, "L") for s in range(800, 832)])
+                         + [(s, True, True, "L") for s in range(800, 832)]
+                         + [(s, True, True, "LD") for s in range(900, 932)])
 def test_random_embedded_formulations_against_the_live_reference(seed, scheduled, general, turned):
     """tests/_embedded_forms.py through the kernels: random structures around a per-instance plant
     (four named plants, one or two axes, slack / footsteps / disturbance, costs with aims and on
@@ -99,11 +100,13 @@ def test_random_embedded_formulations_against_the_live_reference(seed, scheduled
     ``general``: also crossed costs between any two signals, per-instance weights / aims on signals with
     a part outside the plant, a definition that mixes states and the input.  ``turned``: limits turned /
     scaled per instance, on signals with parts outside the plant too; "L": also costs and limits that
-    combine their samples through a matrix ``L`` (mpci_lti_sched_rows for the limits' plant part)."""
+    combine their samples through a matrix ``L`` (mpci_lti_sched_rows for the limits' plant part);
+    "LD": also definitions with a matrix coefficient on a plant signal (a rate, a delayed state)."""
     import _embedded_forms as forms
     from mpc_interface_b200 import Param
 
-    spec = forms.draw(seed, scheduled, general, with_L=turned == "L", turned=bool(turned))
+    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD"), turned=bool(turned),
+                      delayed=turned == "LD")
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"))
     plan = form.lti_plan("LIP")
     assert plan.embedded

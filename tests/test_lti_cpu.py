@@ -239,7 +239,8 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
                          + [(s, True, False, False) for s in range(220, 232)]
                          + [(s, True, True, False) for s in range(240, 256)]
                          + [(s, True, True, True) for s in range(260, 276)]
-                         + [(s, True, True, "L") for s in range(280, 296)])
+                         + [(s, True, True, "L") for s in range(280, 296)]
+                         + [(s, True, True, "LD") for s in range(300, 316)])
 def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, general, turned):
     """tests/_embedded_forms.py: random structures around a per-instance plant (four named
     plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
@@ -252,7 +253,8 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
     the plant and a definition that mixes states and the input (whole-horizon terms of that stage).
     ``turned``: limits turned / scaled per instance, on signals with parts outside the plant too
     (per-instance Gz and h map of the coupling stage); "L": also costs and limits with a matrix ``L``
-    over their samples."""
+    over their samples; "LD": also definitions with a matrix coefficient on a plant signal (a rate
+    ``(I - shift) @ u1``, a delayed state), whose costs and limits go row by row through mpci_sched.cu."""
     import _embedded_forms as forms
     from oracle import reference
 
@@ -260,7 +262,8 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
         pytest.skip("oracle/_ref is not staged")
     from mpc_interface_b200 import dynamics
 
-    spec = forms.draw(seed, scheduled, general, with_L=turned == "L", turned=bool(turned))
+    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD"), turned=bool(turned),
+                      delayed=turned == "LD")
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
                        backend=NumpyBackend())
     plan = form.lti_plan("LIP")
@@ -370,15 +373,58 @@ def test_per_instance_tables_built_with_torch_equal_the_numpy_ones(cpu_extend):
         assert np.array_equal(a, b.numpy())
 
 
-def test_embedded_lowering_refuses_what_the_coupling_stage_cannot_do(cpu_extend):
+def test_embedded_lowering_refuses_what_the_stages_cannot_do(cpu_extend):
     from mpc_interface_b200.examples import biped
 
     conf = biped.default_configuration(16)
     form = biped.formulate_biped(conf, backend=NumpyBackend())
-    form.incorporate_definition("odd_x", LineCombo({"CoM_x": np.eye(16), "s_x": 1.0}))
+    form.incorporate_definition("odd_x", LineCombo({"CoM_x": 1.0, "s_x": Param("k")}))
     form.incorporate_goal("odd", Cost("odd", 1.0, axes=["_x"]))
+    with pytest.raises(NotImplementedError, match="outside the plant"):
+        form.lti_plan("LIP")
+    form = biped.formulate_biped(conf, backend=NumpyBackend())
+    form.incorporate_definition("rate_x", LineCombo({"CoM_x": np.eye(16) - np.eye(16, k=-1)}))
+    form.incorporate_definition("scaled_x", LineCombo({"rate_x": Param("k")}))
+    form.incorporate_goal("odd", Cost("scaled", 1.0, axes=["_x"]))
     with pytest.raises(NotImplementedError, match="matrix coefficient"):
         form.lti_plan("LIP")
+
+
+def test_rate_limits_and_rate_costs_on_plant_signals(cpu_extend):
+    """A matrix coefficient ON a plant signal -- the CoP rate ``(I - shift) @ b`` of a jerk-driven
+    LIP, limited and penalised: such a signal has no stage form, its cost becomes crossed terms of
+    the scheduled-cost stage over the pairs of its parts, its limit rows of mpci_lti_sched_rows.
+    With the biped's footsteps in the same signal; against the oracle."""
+    from mpc_interface_b200 import dynamics
+    from mpc_interface_b200.examples import biped, synthetic
+    from oracle import qp_oracle
+
+    N, batch = 12, 3
+    conf = biped.default_configuration(N)
+    form = biped.formulate_biped(conf, omega=Param("omega"), backend=NumpyBackend())
+    D = np.eye(N) - np.eye(N, k=-1)
+    for ax in ("_x", "_y"):
+        form.incorporate_definition("db" + ax, LineCombo({"b" + ax: D, "s" + ax: -0.5}))
+    form.incorporate_goal("CoP rate", Cost("db", 0.3, aim=[0.01, 0.0], axes=["_x", "_y"]))
+    form.incorporate_constraint("CoP rate limit", Constraint("db", 0.2, axes=["_x"]))
+    form.incorporate_constraint("late rate", Constraint("db", 0.1, axes=["_y"], arrow=[[-1.0]], schedule=range(N - 3, N)))
+    form.make_preview_matrices()
+    plan = form.lti_plan("LIP")
+    assert plan.embedded and len(plan.lrows) == 2 and len(plan.sched_terms) == 2 * 4
+    vals = synthetic.biped_inputs(8, batch, N)
+    given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
+    params = {"omega": vals["omega"]}
+    tables = plan.instance_tables(params, batch)
+    ccx, ccu = plan.coupled_tables(params, batch)
+    terms, rows = plan.sched_tables(params, batch), plan.lrow_tables(params, batch)
+    plant = dynamics.ControlSystem.from_name(conf.system, ["_x"], tau=conf.mpc_period, omega=conf.omega)
+    for b in range(batch):
+        one = {"omega": float(vals["omega"][b])}
+        G, h, P, q = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], np.zeros([0]),
+                                                   {k: v[b] for k, v in tables.items()}, (ccx[b], ccu[b]))
+        P, q = _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b], terms[b if terms.shape[0] > 1 else 0], P, q)
+        G, h = _lti_numpy.add_limit_rows(plan, plant.A, plant.B, given[b], rows[b if rows.shape[0] > 1 else 0], G, h)
+        cases.assert_qp_close((G, h, P, q), qp_oracle.all_qp_matrices(form, given[b][:, None], one))
 
 
 def test_costs_beyond_the_stage_weights_take_the_general_stage(cpu_extend):
