@@ -42,9 +42,10 @@ def _conf(N, system):
 def _reference_instance(conf, vals, b, tick=None):
     from mpc_interface_b200.examples import biped
 
+    yaw = {"yaw": float(vals["yaw"][b])} if "yaw" in vals else {}
     one = biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
                                 target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])],
-                                api=reference.load())
+                                api=reference.load(), **yaw)
     if tick is not None:
         one.update(**tick)
     collector = {name: np.asarray(vals[name][b]).reshape([-1, 1]) for name in one.given_ID}
@@ -238,11 +239,13 @@ def test_embedded_plan_without_auxiliary_variables():
                 raise AssertionError("seed {} instance {} ({}): {}".format(seed, b, mode, e))
 
 
-def test_receding_tick_with_per_instance_plants():
+@pytest.mark.parametrize("everything", [False, True])
+def test_receding_tick_with_per_instance_plants(everything):
     """StructureBuckets.assemble_device(..., dynamics=...): robots at different walking phases
     (different QP sizes) AND with one plant each -- every bucket through the fused per-instance
     kernel; bitwise the matrices of a direct batched call on the bucket's instances, and the
-    live reference on a sample."""
+    live reference on a sample.  ``everything``: also one heading per robot (turned boxes) and the
+    terminal cost switched on (the scheduled-cost stage inside the tick)."""
     import torch
 
     from mpc_interface_b200 import Param, lti, receding
@@ -251,10 +254,14 @@ def test_receding_tick_with_per_instance_plants():
     N, batch, system = 30, 61, "dP->CCC"
     seed = int.from_bytes(os.urandom(4), "little")
     conf = _conf(N, system)
+    extra = {}
+    if everything:
+        conf.cost_weights["terminal"] = 25.0
+        extra = {"yaw": Param("yaw")}
 
     def factory():
         return biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
-                                     target_vel=[Param("vel_x"), Param("vel_y")])
+                                     target_vel=[Param("vel_x"), Param("vel_y")], **extra)
 
     rng = np.random.default_rng(seed)
     ticks = [dict(step_times=np.array([5, 17, 29]), step_count=1), dict(step_times=np.array([0, 12, 24]), step_count=2),
@@ -264,6 +271,8 @@ def test_receding_tick_with_per_instance_plants():
     count = np.array([ticks[t]["step_count"] for t in phase])
     vals = _inputs(seed, batch, N)
     params = {k: vals[k] for k in ("omega", "vel_x", "vel_y")}
+    if everything:
+        vals["yaw"] = params["yaw"] = rng.uniform(-np.pi, np.pi, batch)
     collector = {k: torch.from_numpy(np.ascontiguousarray(vals[k])).cuda()
                  for k in ("s0_x", "s0_y", "x0_x", "x0_y", "n_x", "n_y")}
     A, B = lti.named_system_batched(system, vals["tau"], vals["omega"])
