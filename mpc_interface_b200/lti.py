@@ -153,26 +153,32 @@ class _Form:
     ``rows``: samples of the signal (None: not fixed yet; a plant part means the horizon).
     ``mix``: plant parts that enter through a MATRIX coefficient -- ``M @ (cx . x + cu . u)`` with M
     numeric [rows, N] (a delayed plant signal, a rate ``(I - shift) @ b``): [(M, cx, cu)].  Such a
-    signal has no stage form; its costs and limits go row by row through mpci_sched.cu."""
+    signal has no stage form; its costs and limits go row by row through mpci_sched.cu.
+    ``sym_aux``: auxiliary parts under a ``Param`` coefficient -- ``coef * (Mz @ z + Mg @ given)``:
+    [(coef, Mz or None, Mg or None)]; limits keep them as per-instance Gz / h-map terms, costs take
+    the row-by-row stage with the coefficient in the terms' weights."""
 
     def __init__(self, cx=None, cu=None, rows=None, Mz=None, Mg=None):
         self.cx, self.cu = dict(cx or {}), dict(cu or {})
         self.rows, self.Mz, self.Mg = rows, Mz, Mg
-        self.mix = []
+        self.mix, self.sym_aux = [], []
 
     def add(self, other, coef):
         """self += coef * other, ``coef`` a float or a ``Param`` expression (the latter on a
         form without auxiliary part only)."""
-        if other.has_aux() and is_expr(coef):
-            _unsupported("a Param coefficient on a variable outside the plant")
         if other.mix and is_expr(coef):
             _unsupported("a Param coefficient on a signal that holds a matrix coefficient")
         self._fit_rows(other.rows)
         self.mix += [(coef * M, cx, cu) for M, cx, cu in other.mix]
+        self.sym_aux += [(coef * c2, Mz, Mg) for c2, Mz, Mg in other.sym_aux]
         for mine, theirs in ((self.cx, other.cx), (self.cu, other.cu)):
             for idx, c in theirs.items():
                 term = coef * c
                 mine[idx] = mine[idx] + term if idx in mine else term
+        if is_expr(coef):  # the auxiliary part under a per-instance coefficient
+            if any(M is not None and np.any(M) for M in (other.Mz, other.Mg)):
+                self.sym_aux.append((coef, other.Mz, other.Mg))
+            return self
         for name in ("Mz", "Mg"):
             theirs = getattr(other, name)
             if theirs is not None:
@@ -190,6 +196,8 @@ class _Form:
         if other.cx or other.cu:
             self.mix.append((np.array(matrix, dtype=np.float64), dict(other.cx), dict(other.cu)))
         self.mix += [(matrix @ M, cx, cu) for M, cx, cu in other.mix]
+        self.sym_aux += [(c2, None if Mz is None else matrix @ Mz, None if Mg is None else matrix @ Mg)
+                         for c2, Mz, Mg in other.sym_aux]
         for name in ("Mz", "Mg"):
             theirs = getattr(other, name)
             if theirs is not None:
@@ -206,7 +214,7 @@ class _Form:
         self.rows = rows
 
     def has_aux(self):
-        return any(M is not None and np.any(M) for M in (self.Mz, self.Mg))
+        return bool(self.sym_aux) or any(M is not None and np.any(M) for M in (self.Mz, self.Mg))
 
     def has_plant(self):
         return self.touches_states() or self.touches_inputs()
@@ -224,10 +232,12 @@ class _Form:
         return any(is_expr(c) or c != 0.0 for mp in self._maps("cu") for c in mp.values())
 
     def parts(self, N):
-        """The signal as ``sum_a M_a @ (form_a)``: [(form without mix, M_a [rows, N] or None = identity)],
-        the first one carrying the direct plant part and the auxiliary part."""
-        out = [(_Form(self.cx, self.cu, self.rows, self.Mz, self.Mg), None)]
-        return out + [(_Form(cx, cu, N), M) for M, cx, cu in self.mix]
+        """The signal as ``sum_a coef_a * M_a @ (form_a)``: [(form without mix / sym_aux, M_a [rows, N] or
+        None = identity, coef_a a Param expression or None = 1)], the first one carrying the direct plant
+        part and the numeric auxiliary part."""
+        out = [(_Form(self.cx, self.cu, self.rows, self.Mz, self.Mg), None, None)]
+        out += [(_Form(cx, cu, N), M, None) for M, cx, cu in self.mix]
+        return out + [(_Form(rows=self.rows, Mz=Mz, Mg=Mg), None, coef) for coef, Mz, Mg in self.sym_aux]
 
 
 class _Host:
@@ -1088,7 +1098,15 @@ def lower(form, plant_name):
                         plan.Hg_terms.append((coef, plan.nc, term))
                     else:
                         Hg_new[:, :-1] -= C @ f.Mg[samples]
-                for part, M in f.parts(N):  # the plant parts: direct, and through matrix coefficients
+                for c2, Mz2, Mg2 in f.sym_aux:  # auxiliary parts under a per-instance coefficient
+                    both = c2 if coef is None else coef * c2
+                    if Mz2 is not None and np.any(Mz2):
+                        plan.Gz_terms.append((both, plan.nc, C @ Mz2[samples]))
+                    if Mg2 is not None and np.any(Mg2):
+                        term = np.zeros([lines, form.given_len + 1])
+                        term[:, :-1] = -(C @ Mg2[samples])
+                        plan.Hg_terms.append((both, plan.nc, term))
+                for part, M, _c in f.parts(N):  # the plant parts: direct, and through matrix coefficients
                     if not part.has_plant():
                         continue
                     if M is None:
@@ -1144,6 +1162,7 @@ def lower(form, plant_name):
                     rows_form.add(_Form(f.cx, f.cu, f.rows), arrow[0, a])
                     if f.has_aux():       # the part outside the plant the per-instance Gz / h map
                         turned_aux.append((arrow[0, a], f.Mz, f.Mg))
+                        turned_aux += [(arrow[0, a] * c2, Mz2, Mg2) for c2, Mz2, Mg2 in f.sym_aux]
                 else:
                     rows_form.add(f, float(arrow[0, a]))
             rows_arrow = np.zeros([rows])
@@ -1183,6 +1202,9 @@ def lower(form, plant_name):
                         plan.Hg_terms.append((coef, plan.nc, term))
                     else:
                         Hg[:, -1] += float(coef) * col[k0:k0 + cnt]
+            # (auxiliary parts under a per-instance coefficient of a definition: scaled by the rows' arrows)
+            turned_aux += [(c2, None if Mz2 is None else rows_arrow[:, None] * Mz2,
+                            None if Mg2 is None else rows_arrow[:, None] * Mg2) for c2, Mz2, Mg2 in rows_form.sym_aux]
             for coef, Mz_a, Mg_a in turned_aux:
                 if Mz_a is not None and np.any(Mz_a):
                     plan.Gz_terms.append((coef, plan.nc, np.array(Mz_a[k0:k0 + cnt])))
@@ -1217,7 +1239,8 @@ def lower(form, plant_name):
             mixes = (fv.touches_states() and fc.touches_inputs()) or (fv.touches_inputs() and fc.touches_states())
             outside = fv.has_aux() or fc.has_aux()
             short = not fv.has_plant() and fv.rows != N  # (e.g. a cost on the footsteps themselves)
-            mixed = bool(fv.mix or fc.mix)  # a matrix coefficient on a plant variable: no stage form
+            # a matrix coefficient on a plant variable, a Param coefficient on an auxiliary one: no stage form
+            mixed = bool(fv.mix or fc.mix or fv.sym_aux or fc.sym_aux)
             general = mixes or mixed or (outside and (fv is not fc or ((is_expr(aim) or is_expr(caim)) and short)))
             if cost.schedule or general or cost.L or cost.cross_L:
                 rows = N if (fv.has_plant() or fc.has_plant() or not plan.embedded) else fv.rows
@@ -1250,11 +1273,15 @@ def lower(form, plant_name):
 
                     vparts = fv.parts(N)
                     cparts = vparts if fc is fv else fc.parts(N)
-                    for ia, (pa, Ma) in enumerate(vparts):
-                        for ib, (pb, Mb) in enumerate(cparts):
+                    for ia, (pa, Ma, ka) in enumerate(vparts):
+                        for ib, (pb, Mb, kb) in enumerate(cparts):
+                            weight = w  # w coef_a coef_b: the parts' per-instance coefficients ride in the weight
+                            for k in (ka, kb):
+                                weight = weight if k is None else (k * weight if is_expr(k) or is_expr(weight)
+                                                                   else float(k) * weight)
                             plan.sched_L[len(plan.sched_terms)] = (over_horizon(Lv, Ma), over_horizon(Lc, Mb))
-                            plan.sched_terms.append((w, pa, pb, aim if ia == 0 else 0.0, caim if ib == 0 else 0.0,
-                                                     list(range(N))))
+                            plan.sched_terms.append((weight, pa, pb, aim if ia == 0 else 0.0,
+                                                     caim if ib == 0 else 0.0, list(range(N))))
                     continue
                 if Lv is not None:
                     plan.sched_L[len(plan.sched_terms)] = (Lv, Lc)

@@ -22,7 +22,7 @@ INPUT = {"dP->CCC": "cCoP_dot", "J->CCC": "CoM_dddot", "dP->CCP": "cCoP_dot", "P
 OMEGA_COEFS = ("inv", "neg_inv2", "times", "num")
 
 
-def draw(seed, scheduled=False, general=False, with_L=False, turned=False, delayed=False):
+def draw(seed, scheduled=False, general=False, with_L=False, turned=False, delayed=False, paramaux=False):
     """The structure as plain data (a dict of lists and numbers).  ``scheduled``: some of the
     costs act on a few samples only (goal.py `schedule`).  ``general``: also costs that the stage
     weights of the fused kernel cannot express -- crossed costs between any two signals, per-instance
@@ -32,7 +32,8 @@ def draw(seed, scheduled=False, general=False, with_L=False, turned=False, delay
     refuses ``L``.  ``turned``: the facets over both axes and some one-axis limits are turned / scaled
     per instance (their one-row arrows are rotated by the angle ``vel``, as rotate_in_TS does).
     ``delayed``: definitions with a MATRIX coefficient on a plant signal (a rate ``(I - shift) @ u1``,
-    a delayed state)."""
+    a delayed state).  ``paramaux``: per-instance coefficients (1 / omega, omega) on the variables
+    OUTSIDE the plant too."""
     rng = np.random.default_rng(seed)
     system = SYSTEMS[rng.integers(len(SYSTEMS))]
     axes = ["_x", "_y"] if rng.random() < 0.4 else ["_x"]
@@ -63,6 +64,8 @@ def draw(seed, scheduled=False, general=False, with_L=False, turned=False, delay
                 kind = "num"
                 if v != "s" and rng.random() < 0.4:
                     kind = ("shift", "diag")[rng.integers(2)]
+                elif paramaux and rng.random() < 0.6:
+                    kind = ("inv", "times")[rng.integers(2)]
                 terms.append((v, kind, float(rng.uniform(-1.5, 1.5))))
         return terms or [(aux_vars[0], "num", -1.0)]
 

@@ -86,10 +86,11 @@ def test_soft_constrained_lip_against_the_live_reference(N, order):
 @pytest.mark.skipif(not reference.available(), reason="oracle/_ref is not staged")
 @pytest.mark.parametrize("seed,scheduled,general,turned", [(s, False, False, False) for s in range(300, 324)]
                          + [(s, True, False, False) for s in range(400, 424)]
-                         + [(s, True, True, False) for s in range(500, 532)]
-                         + [(s, True, True, True) for s in range(700, 732)]
-                         + [(s, True, True, "L") for s in range(800, 832)]
-                         + [(s, True, True, "LD") for s in range(900, 932)])
+                         + [(s, True, True, False) for s in range(500, 524)]
+                         + [(s, True, True, True) for s in range(700, 720)]
+                         + [(s, True, True, "L") for s in range(800, 820)]
+                         + [(s, True, True, "LD") for s in range(900, 920)]
+                         + [(s, True, True, "LDP") for s in range(1000, 1024)])
 def test_random_embedded_formulations_against_the_live_reference(seed, scheduled, general, turned):
     """tests/_embedded_forms.py through the kernels: random structures around a per-instance plant
     (four named plants, one or two axes, slack / footsteps / disturbance, costs with aims and on
@@ -101,12 +102,13 @@ def test_random_embedded_formulations_against_the_live_reference(seed, scheduled
     a part outside the plant, a definition that mixes states and the input.  ``turned``: limits turned /
     scaled per instance, on signals with parts outside the plant too; "L": also costs and limits that
     combine their samples through a matrix ``L`` (mpci_lti_sched_rows for the limits' plant part);
-    "LD": also definitions with a matrix coefficient on a plant signal (a rate, a delayed state)."""
+    "LD": also definitions with a matrix coefficient on a plant signal (a rate, a delayed state);
+    "LDP": also per-instance coefficients (1 / omega, omega) on the variables outside the plant."""
     import _embedded_forms as forms
     from mpc_interface_b200 import Param
 
-    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD"), turned=bool(turned),
-                      delayed=turned == "LD")
+    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD", "LDP"), turned=bool(turned),
+                      delayed=turned in ("LD", "LDP"), paramaux=turned == "LDP")
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"))
     plan = form.lti_plan("LIP")
     assert plan.embedded

@@ -238,9 +238,10 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
 @pytest.mark.parametrize("seed,scheduled,general,turned", [(s, False, False, False) for s in range(200, 212)]
                          + [(s, True, False, False) for s in range(220, 232)]
                          + [(s, True, True, False) for s in range(240, 256)]
-                         + [(s, True, True, True) for s in range(260, 276)]
-                         + [(s, True, True, "L") for s in range(280, 296)]
-                         + [(s, True, True, "LD") for s in range(300, 316)])
+                         + [(s, True, True, True) for s in range(260, 272)]
+                         + [(s, True, True, "L") for s in range(280, 290)]
+                         + [(s, True, True, "LD") for s in range(300, 310)]
+                         + [(s, True, True, "LDP") for s in range(320, 332)])
 def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, general, turned):
     """tests/_embedded_forms.py: random structures around a per-instance plant (four named
     plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
@@ -254,7 +255,8 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
     ``turned``: limits turned / scaled per instance, on signals with parts outside the plant too
     (per-instance Gz and h map of the coupling stage); "L": also costs and limits with a matrix ``L``
     over their samples; "LD": also definitions with a matrix coefficient on a plant signal (a rate
-    ``(I - shift) @ u1``, a delayed state), whose costs and limits go row by row through mpci_sched.cu."""
+    ``(I - shift) @ u1``, a delayed state), whose costs and limits go row by row through mpci_sched.cu;
+    "LDP": also per-instance coefficients (1 / omega, omega) on the variables outside the plant."""
     import _embedded_forms as forms
     from oracle import reference
 
@@ -262,8 +264,8 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
         pytest.skip("oracle/_ref is not staged")
     from mpc_interface_b200 import dynamics
 
-    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD"), turned=bool(turned),
-                      delayed=turned == "LD")
+    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD", "LDP"), turned=bool(turned),
+                      delayed=turned in ("LD", "LDP"), paramaux=turned == "LDP")
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
                        backend=NumpyBackend())
     plan = form.lti_plan("LIP")
@@ -378,9 +380,9 @@ def test_embedded_lowering_refuses_what_the_stages_cannot_do(cpu_extend):
 
     conf = biped.default_configuration(16)
     form = biped.formulate_biped(conf, backend=NumpyBackend())
-    form.incorporate_definition("odd_x", LineCombo({"CoM_x": 1.0, "s_x": Param("k")}))
+    form.incorporate_definition("odd_x", LineCombo({"CoM_x": 1.0, "Ds_x": Param("k")}))
     form.incorporate_goal("odd", Cost("odd", 1.0, axes=["_x"]))
-    with pytest.raises(NotImplementedError, match="outside the plant"):
+    with pytest.raises(ValueError, match="broadcast"):  # (N samples + fewer footsteps: the reference fails too)
         form.lti_plan("LIP")
     form = biped.formulate_biped(conf, backend=NumpyBackend())
     form.incorporate_definition("rate_x", LineCombo({"CoM_x": np.eye(16) - np.eye(16, k=-1)}))
