@@ -166,10 +166,12 @@ class _Form:
     def add(self, other, coef):
         """self += coef * other, ``coef`` a float or a ``Param`` expression (the latter on a
         form without auxiliary part only)."""
-        if other.mix and is_expr(coef):
-            _unsupported("a Param coefficient on a signal that holds a matrix coefficient")
         self._fit_rows(other.rows)
-        self.mix += [(coef * M, cx, cu) for M, cx, cu in other.mix]
+        if is_expr(coef):  # (a per-instance coefficient joins the part's form, the matrix stays numeric)
+            self.mix += [(M, {i: coef * c for i, c in cx.items()}, {j: coef * c for j, c in cu.items()})
+                         for M, cx, cu in other.mix]
+        else:
+            self.mix += [(coef * M, cx, cu) for M, cx, cu in other.mix]
         self.sym_aux += [(coef * c2, Mz, Mg) for c2, Mz, Mg in other.sym_aux]
         for mine, theirs in ((self.cx, other.cx), (self.cu, other.cu)):
             for idx, c in theirs.items():

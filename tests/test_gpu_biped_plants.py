@@ -473,9 +473,10 @@ def test_biped_plants_with_cop_rate_limits_and_costs(N, batch):
                                 LineCombo=ref.LineCombo, Cost=ref.Cost, Box=ref.Box, tools=ref.tools)
     D = np.eye(N) - np.eye(N, k=-1)
 
-    def with_rates(form, combo, cost, constraint):
+    def with_rates(form, combo, cost, constraint, omega):
         for ax in ("_x", "_y"):
-            form.incorporate_definition("db" + ax, combo({"b" + ax: D, "s" + ax: -0.5}))
+            form.incorporate_definition("raw" + ax, combo({"b" + ax: D, "s" + ax: -0.5}))
+            form.incorporate_definition("db" + ax, combo({"raw" + ax: 1 / omega}))  # (a per-instance scaling on top)
         form.incorporate_goal("CoP rate", cost("db", 0.3, aim=[0.01, 0.0], axes=["_x", "_y"]))
         form.incorporate_constraint("CoP rate limit", constraint("db", 0.2, axes=["_x"]))
         form.incorporate_constraint("late rate", constraint("db", 0.1, axes=["_y"], arrow=[[-1.0]],
@@ -486,7 +487,8 @@ def test_biped_plants_with_cop_rate_limits_and_costs(N, batch):
     conf = biped.default_configuration(N)
     conf.system = "dP->CCC"
     form = with_rates(biped.formulate_biped(conf, omega=Param("omega"), tau=Param("tau"),
-                                            target_vel=[Param("vel_x"), Param("vel_y")]), LineCombo, Cost, Constraint)
+                                            target_vel=[Param("vel_x"), Param("vel_y")]), LineCombo, Cost, Constraint,
+                      Param("omega"))
     vals = synthetic.biped_inputs(21 + N, batch, N)
     vals["tau"] = np.random.default_rng(N).uniform(0.08, 0.12, batch) * min(1.0, 30.0 / N)
     given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
@@ -495,7 +497,7 @@ def test_biped_plants_with_cop_rate_limits_and_costs(N, batch):
     for b in range(batch):
         one = with_rates(biped.formulate_biped(conf, omega=float(vals["omega"][b]), tau=float(vals["tau"][b]),
                                                target_vel=[float(vals["vel_x"][b]), float(vals["vel_y"][b])], api=api),
-                         ref.LineCombo, ref.Cost, ref.Constraint)
+                         ref.LineCombo, ref.Cost, ref.Constraint, float(vals["omega"][b]))
         wants.append(one.generate_all_qp_matrices(one.arrange_given(
             {v: np.asarray(vals[v][b]).reshape([-1, 1]) for v in one.given_ID})))
     for mode in ("recursion", "dmma"):

@@ -387,8 +387,9 @@ def test_embedded_lowering_refuses_what_the_stages_cannot_do(cpu_extend):
     form = biped.formulate_biped(conf, backend=NumpyBackend())
     form.incorporate_definition("rate_x", LineCombo({"CoM_x": np.eye(16) - np.eye(16, k=-1)}))
     form.incorporate_definition("scaled_x", LineCombo({"rate_x": Param("k")}))
-    form.incorporate_goal("odd", Cost("scaled", 1.0, axes=["_x"]))
-    with pytest.raises(NotImplementedError, match="matrix coefficient"):
+    form.incorporate_constraint("turning rows", Constraint("scaled", 1.0, axes=["_x"], arrow=np.array(
+        [[Param("k") * (1 + r)] for r in range(16)], dtype=object)))
+    with pytest.raises(NotImplementedError, match="row to row"):
         form.lti_plan("LIP")
 
 
@@ -406,13 +407,15 @@ def test_rate_limits_and_rate_costs_on_plant_signals(cpu_extend):
     form = biped.formulate_biped(conf, omega=Param("omega"), backend=NumpyBackend())
     D = np.eye(N) - np.eye(N, k=-1)
     for ax in ("_x", "_y"):
-        form.incorporate_definition("db" + ax, LineCombo({"b" + ax: D, "s" + ax: -0.5}))
+        form.incorporate_definition("raw" + ax, LineCombo({"b" + ax: D, "s" + ax: -0.5}))
+        form.incorporate_definition("db" + ax, LineCombo({"raw" + ax: 1 / Param("omega")}))  # (per-instance scaling)
     form.incorporate_goal("CoP rate", Cost("db", 0.3, aim=[0.01, 0.0], axes=["_x", "_y"]))
     form.incorporate_constraint("CoP rate limit", Constraint("db", 0.2, axes=["_x"]))
     form.incorporate_constraint("late rate", Constraint("db", 0.1, axes=["_y"], arrow=[[-1.0]], schedule=range(N - 3, N)))
     form.make_preview_matrices()
     plan = form.lti_plan("LIP")
-    assert plan.embedded and len(plan.lrows) == 2 and len(plan.sched_terms) == 2 * 4
+    # parts of db: (empty direct part), (I - shift) @ b / omega, -0.5 s / omega: 3 x 3 crossed terms per axis
+    assert plan.embedded and len(plan.lrows) == 2 and len(plan.sched_terms) == 2 * 9
     vals = synthetic.biped_inputs(8, batch, N)
     given = synthetic.pack_given(form.given_ID, form.given_len, vals, batch)
     params = {"omega": vals["omega"]}
@@ -422,8 +425,9 @@ def test_rate_limits_and_rate_costs_on_plant_signals(cpu_extend):
     plant = dynamics.ControlSystem.from_name(conf.system, ["_x"], tau=conf.mpc_period, omega=conf.omega)
     for b in range(batch):
         one = {"omega": float(vals["omega"][b])}
+        extras = tuple(None if t is None else t[b] for t in plan.coupled_extras(params, batch))
         G, h, P, q = _lti_numpy.evaluate_embedded(plan, plant.A, plant.B, given[b], np.zeros([0]),
-                                                   {k: v[b] for k, v in tables.items()}, (ccx[b], ccu[b]))
+                                                   {k: v[b] for k, v in tables.items()}, (ccx[b], ccu[b]), extras)
         P, q = _lti_numpy.add_scheduled(plan, plant.A, plant.B, given[b], terms[b if terms.shape[0] > 1 else 0], P, q)
         G, h = _lti_numpy.add_limit_rows(plan, plant.A, plant.B, given[b], rows[b if rows.shape[0] > 1 else 0], G, h)
         cases.assert_qp_close((G, h, P, q), qp_oracle.all_qp_matrices(form, given[b][:, None], one))
