@@ -1037,9 +1037,11 @@ def lower(form, plant_name):
     plan.optim_ID = dict(form.optim_ID)
     plan.given_ID = dict(form.given_ID)
     # (limits with L are rows of the embedded layout: the fused kernel leaves them to the later stages)
-    def rows_stage(limit):  # L, or a signal with a matrix coefficient on a plant variable
+    def rows_stage(limit):  # L, a signal with a matrix coefficient on a plant variable, row-wise Param arrows
         members = [forms.get(limit.variable + ax) for ax in limit.axes]
-        return bool(limit.L) or any(isinstance(f, _Form) and f.mix for f in members)
+        arrow = np.asarray(limit.arrow)
+        rowwise = arrow.dtype == object and arrow.shape[0] != 1 and any(is_expr(x) for x in arrow.ravel())
+        return bool(limit.L) or rowwise or any(isinstance(f, _Form) and f.mix for f in members)
 
     plan.embedded = bool(nz or aux_given or any(rows_stage(limit) for limit in _plan.ordered_limits(form)))
     if plan.embedded:
@@ -1073,50 +1075,60 @@ def lower(form, plant_name):
                     next(k for k in samples if k < 0 or k >= rows), rows))
             arrow = np.asarray(limit.arrow)
             turned = arrow.dtype == object and any(is_expr(x) for x in arrow.ravel())
-            if turned and arrow.shape[0] != 1:
-                _unsupported("a per-instance arrow that changes from row to row")
             lines = int(np.asarray(limit.L[0]).shape[0]) if limit.L else len(samples)
             if not limit.L and limit.nlines is not None and int(limit.nlines) != lines:
                 raise ValueError("operands could not be broadcast together with shapes ({},1) ({},{})".format(
                     int(limit.nlines), lines, plan.nv))
+            if arrow.shape[0] not in (1, lines):
+                raise ValueError("operands could not be broadcast together with shapes ({},1) ({},{})".format(
+                    arrow.shape[0], lines, plan.nv))
             Gz_new, Hg_new = np.zeros([lines, nz]), np.zeros([lines, form.given_len + 1])
+
+            def emit(f, r0, C, coef):
+                """Rows r0 .. r0 + len(C) of this limit: C [k, samples] numeric, times ``coef`` (a Param
+                expression: it travels as the terms' weight / per-instance Gz and h-map terms) or None."""
+                k = C.shape[0]
+                for c2, Mz2, Mg2 in [(None, f.Mz, f.Mg)] + list(f.sym_aux):
+                    both = coef if c2 is None else (c2 if coef is None else coef * c2)
+                    if Mz2 is not None and np.any(Mz2):
+                        if both is not None:
+                            plan.Gz_terms.append((both, plan.nc + r0, C @ Mz2[samples]))
+                        else:
+                            Gz_new[r0:r0 + k] += C @ Mz2[samples]
+                    if Mg2 is not None and np.any(Mg2):
+                        if both is not None:
+                            term = np.zeros([k, form.given_len + 1])
+                            term[:, :-1] = -(C @ Mg2[samples])
+                            plan.Hg_terms.append((both, plan.nc + r0, term))
+                        else:
+                            Hg_new[r0:r0 + k, :-1] -= C @ Mg2[samples]
+                for part, M, _c in f.parts(N):  # the plant parts: direct, and through matrix coefficients
+                    if not part.has_plant():
+                        continue
+                    if M is None:
+                        full = np.zeros([k, N])
+                        full[:, samples] = C
+                    else:
+                        full = C @ M[samples, :]
+                    plan.lrows.append((_Form(part.cx, part.cu, N), full, list(range(N)), plan.nc + r0, coef))
+
             for a, f in enumerate(members):
                 La = np.asarray(limit.L[a], dtype=np.float64) if limit.L else np.eye(lines)
                 if La.shape != (lines, len(samples)):
                     raise ValueError("matmul: L is {} for {} scheduled samples and {} lines".format(
                         La.shape, len(samples), lines))
-                # c = arrow * L (restrictions.py:175-179); a per-instance arrow travels as the term's weight
-                coef = arrow[0, a] if turned and is_expr(arrow[0, a]) else None
-                C = La if coef is not None else np.asarray(arrow[:, a], dtype=np.float64)[:, None] * La
-                if f.Mz is not None and np.any(f.Mz):
-                    if coef is not None:
-                        plan.Gz_terms.append((coef, plan.nc, C @ f.Mz[samples]))
-                    else:
-                        Gz_new += C @ f.Mz[samples]
-                if f.Mg is not None and np.any(f.Mg):
-                    if coef is not None:
-                        term = np.zeros([lines, form.given_len + 1])
-                        term[:, :-1] = -(C @ f.Mg[samples])
-                        plan.Hg_terms.append((coef, plan.nc, term))
-                    else:
-                        Hg_new[:, :-1] -= C @ f.Mg[samples]
-                for c2, Mz2, Mg2 in f.sym_aux:  # auxiliary parts under a per-instance coefficient
-                    both = c2 if coef is None else coef * c2
-                    if Mz2 is not None and np.any(Mz2):
-                        plan.Gz_terms.append((both, plan.nc, C @ Mz2[samples]))
-                    if Mg2 is not None and np.any(Mg2):
-                        term = np.zeros([lines, form.given_len + 1])
-                        term[:, :-1] = -(C @ Mg2[samples])
-                        plan.Hg_terms.append((both, plan.nc, term))
-                for part, M, _c in f.parts(N):  # the plant parts: direct, and through matrix coefficients
-                    if not part.has_plant():
-                        continue
-                    if M is None:
-                        full = np.zeros([lines, N])
-                        full[:, samples] = C
-                    else:
-                        full = C @ M[samples, :]
-                    plan.lrows.append((_Form(part.cx, part.cu, N), full, list(range(N)), plan.nc, coef))
+                # c = arrow * L (restrictions.py:175-179)
+                column = arrow[:, a]
+                if not any(is_expr(x) for x in column):
+                    emit(f, 0, np.asarray(column, dtype=np.float64)[:, None] * La, None)
+                elif column.shape[0] == 1:
+                    emit(f, 0, La, column[0])
+                else:  # an arrow that turns from row to row: every row its own weight
+                    for r in range(lines):
+                        if is_expr(column[r]):
+                            emit(f, r, La[r:r + 1], column[r])
+                        else:
+                            emit(f, r, float(column[r]) * La[r:r + 1], None)
             for coef, col in _bound_parts(limit, lines):
                 if is_expr(coef):
                     term = np.zeros([lines, form.given_len + 1])

@@ -150,6 +150,7 @@ def draw(seed, scheduled=False, general=False, with_L=False, turned=False, delay
     spec["order"] = [optim[i] for i in rng.permutation(len(optim))]
     for lim in limits:
         lim["turned"] = bool(turned and np.asarray(lim["arrow"]).shape[0] == 1 and rng.random() < 0.7)
+        lim["rowwise"] = bool(turned == "rows" and np.asarray(lim["arrow"]).shape[0] > 1)
     if with_L:
         def samples_of(var, schedule):
             rows = spec["steps_U"].shape[1] if var == "Ds" else N
@@ -167,6 +168,7 @@ def draw(seed, scheduled=False, general=False, with_L=False, turned=False, delay
                 lines = int(rng.integers(1, 5))
                 lim["L"] = rng.normal(size=[lines, samples_of(lim["var"], schedule)])
                 lim["arrow"] = np.array(lim["arrow"])[:1]  # (one arrow for all lines)
+                lim["rowwise"] = False
     return spec
 
 
@@ -232,6 +234,12 @@ def build(spec, api, omega, tau, vel, gain, nominal=(0.1, 3.3), backend=None):
                 kargs["arrow"] = np.array([[a[0] * cos(vel) - a[1] * sin(vel), a[0] * sin(vel) + a[1] * cos(vel)]])
             else:            # one axis: the arrow scaled by cos(vel) > 0
                 kargs["arrow"] = np.array([[a[0] * cos(vel)]])
+        elif lim.get("rowwise"):  # every row its own per-instance scaling (the 2nd one numeric)
+            from mpc_interface_b200.params import cos
+
+            column = np.array(lim["arrow"])[:, 0]
+            kargs["arrow"] = np.array([[c * cos(vel) * (1 + 0.1 * r) if r != 1 else c] for r, c in enumerate(column)],
+                                      dtype=object if hasattr(cos(vel), "evaluate") else float)
         if lim["schedule"] is not None:
             kargs["schedule"] = range(*lim["schedule"])
         if lim["center"] is not None:

@@ -90,7 +90,8 @@ def test_soft_constrained_lip_against_the_live_reference(N, order):
                          + [(s, True, True, True) for s in range(700, 720)]
                          + [(s, True, True, "L") for s in range(800, 820)]
                          + [(s, True, True, "LD") for s in range(900, 920)]
-                         + [(s, True, True, "LDP") for s in range(1000, 1024)])
+                         + [(s, True, True, "LDP") for s in range(1000, 1024)]
+                         + [(s, True, True, "rows") for s in range(1100, 1116)])
 def test_random_embedded_formulations_against_the_live_reference(seed, scheduled, general, turned):
     """tests/_embedded_forms.py through the kernels: random structures around a per-instance plant
     (four named plants, one or two axes, slack / footsteps / disturbance, costs with aims and on
@@ -103,12 +104,14 @@ def test_random_embedded_formulations_against_the_live_reference(seed, scheduled
     scaled per instance, on signals with parts outside the plant too; "L": also costs and limits that
     combine their samples through a matrix ``L`` (mpci_lti_sched_rows for the limits' plant part);
     "LD": also definitions with a matrix coefficient on a plant signal (a rate, a delayed state);
-    "LDP": also per-instance coefficients (1 / omega, omega) on the variables outside the plant."""
+    "LDP": also per-instance coefficients (1 / omega, omega) on the variables outside the plant;
+    "rows": also arrows that turn from row to row per instance."""
     import _embedded_forms as forms
     from mpc_interface_b200 import Param
 
-    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD", "LDP"), turned=bool(turned),
-                      delayed=turned in ("LD", "LDP"), paramaux=turned == "LDP")
+    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD", "LDP", "rows"),
+                      turned="rows" if turned == "rows" else bool(turned),
+                      delayed=turned in ("LD", "LDP", "rows"), paramaux=turned in ("LDP", "rows"))
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"))
     plan = form.lti_plan("LIP")
     assert plan.embedded

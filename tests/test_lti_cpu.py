@@ -51,9 +51,9 @@ def test_lowering_refuses_unsupported(cpu_extend):
     with pytest.raises(ValueError, match="matmul"):  # (as the reference's L @ Mo[schedule], body.py:280)
         form.lti_plan("plant")
     form = _formulation(g, cpu_extend, False)
-    form.incorporate_constraint("rowwise turn", Constraint("z1", 3.0, arrow=np.array(
-        [[Param("ref0")]] * int(g["N"]), dtype=object)))
-    with pytest.raises(NotImplementedError, match="row to row"):
+    form.incorporate_constraint("Param in L", Constraint("z1", 3.0, L=np.array(
+        [[Param("ref0")] * int(g["N"])], dtype=object)))
+    with pytest.raises((NotImplementedError, TypeError, ValueError)):
         form.lti_plan("plant")
     form = _formulation(g, cpu_extend, False)
     with pytest.raises(KeyError):
@@ -241,7 +241,8 @@ def test_soft_constrained_lip_lowering(cpu_extend, name):
                          + [(s, True, True, True) for s in range(260, 272)]
                          + [(s, True, True, "L") for s in range(280, 290)]
                          + [(s, True, True, "LD") for s in range(300, 310)]
-                         + [(s, True, True, "LDP") for s in range(320, 332)])
+                         + [(s, True, True, "LDP") for s in range(320, 332)]
+                         + [(s, True, True, "rows") for s in range(340, 350)])
 def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, general, turned):
     """tests/_embedded_forms.py: random structures around a per-instance plant (four named
     plants, one or two axes, slack / footsteps / disturbance, definitions of definitions, costs
@@ -256,7 +257,8 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
     (per-instance Gz and h map of the coupling stage); "L": also costs and limits with a matrix ``L``
     over their samples; "LD": also definitions with a matrix coefficient on a plant signal (a rate
     ``(I - shift) @ u1``, a delayed state), whose costs and limits go row by row through mpci_sched.cu;
-    "LDP": also per-instance coefficients (1 / omega, omega) on the variables outside the plant."""
+    "LDP": also per-instance coefficients (1 / omega, omega) on the variables outside the plant;
+    "rows": also arrows that turn from row to row per instance."""
     import _embedded_forms as forms
     from oracle import reference
 
@@ -264,8 +266,9 @@ def test_random_embedded_formulations_lowering(cpu_extend, seed, scheduled, gene
         pytest.skip("oracle/_ref is not staged")
     from mpc_interface_b200 import dynamics
 
-    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD", "LDP"), turned=bool(turned),
-                      delayed=turned in ("LD", "LDP"), paramaux=turned == "LDP")
+    spec = forms.draw(seed, scheduled, general, with_L=turned in ("L", "LD", "LDP", "rows"),
+                      turned="rows" if turned == "rows" else bool(turned),
+                      delayed=turned in ("LD", "LDP", "rows"), paramaux=turned in ("LDP", "rows"))
     form = forms.build(spec, forms.own_api(), Param("omega"), Param("tau"), Param("vel"), Param("gain"),
                        backend=NumpyBackend())
     plan = form.lti_plan("LIP")
@@ -387,9 +390,9 @@ def test_embedded_lowering_refuses_what_the_stages_cannot_do(cpu_extend):
     form = biped.formulate_biped(conf, backend=NumpyBackend())
     form.incorporate_definition("rate_x", LineCombo({"CoM_x": np.eye(16) - np.eye(16, k=-1)}))
     form.incorporate_definition("scaled_x", LineCombo({"rate_x": Param("k")}))
-    form.incorporate_constraint("turning rows", Constraint("scaled", 1.0, axes=["_x"], arrow=np.array(
-        [[Param("k") * (1 + r)] for r in range(16)], dtype=object)))
-    with pytest.raises(NotImplementedError, match="row to row"):
+    form.incorporate_constraint("short arrows", Constraint("scaled", 1.0, axes=["_x"], arrow=np.array(
+        [[Param("k") * (1 + r)] for r in range(5)], dtype=object)))
+    with pytest.raises(ValueError, match="broadcast"):  # (5 arrows for 16 samples: the reference fails too)
         form.lti_plan("LIP")
 
 
